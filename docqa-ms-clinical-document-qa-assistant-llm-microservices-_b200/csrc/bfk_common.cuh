@@ -1,0 +1,141 @@
+// Shared helpers for libbfk.so (sm_100a only).
+#pragma once
+
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <algorithm>
+#include <cstdio>
+#include <mutex>
+#include <string>
+
+#include "../../include/bfk.h"
+
+namespace bfk {
+
+// ---- error plumbing -------------------------------------------------------
+void set_error(const std::string& msg);
+int fail(const std::string& msg);  // sets the message, returns 1
+
+#define BFK_CUDA(expr)                                                                      \
+    do {                                                                                    \
+        cudaError_t _e = (expr);                                                            \
+        if (_e != cudaSuccess) {                                                            \
+            return ::bfk::fail(std::string(#expr) + ": " + cudaGetErrorString(_e) + " (" + \
+                               __FILE__ + ":" + std::to_string(__LINE__) + ")");           \
+        }                                                                                   \
+    } while (0)
+
+#define BFK_TRY(expr)          \
+    do {                       \
+        int _rc = (expr);      \
+        if (_rc) return _rc;   \
+    } while (0)
+
+struct DeviceGuard {
+    int prev = -1;
+    bool ok = true;
+    explicit DeviceGuard(int dev) {
+        if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
+        if (prev != dev) ok = (cudaSetDevice(dev) == cudaSuccess);
+    }
+    ~DeviceGuard() {
+        if (prev >= 0) cudaSetDevice(prev);
+    }
+};
+
+static inline int64_t round_up(int64_t a, int64_t b) { return (a + b - 1) / b * b; }
+static inline int next_pow2(int v) {
+    int p = 1;
+    while (p < v) p <<= 1;
+    return p;
+}
+
+// ---- the index object -----------------------------------------------------
+// Data layout in HBM (DESIGN.md "Data layout"):
+//   x32  [cap, ld32] fp32 master rows, ld32 = round_up(d, 4)   (BFK_STORE_F32 only)
+//   x16  [cap, ld16] bf16 scan copy,   ld16 = round_up(d, 64)  (zero padded)
+//   nrm  [cap]       fp32 squared norms of the stored (fp32 or bf16) rows
+//   maxn [1]         fp32 bits of max_i ||x_i||^2 (monotone under atomicMax)
+struct Workspace {
+    void* ptr = nullptr;
+    size_t bytes = 0;
+};
+
+}  // namespace bfk
+
+struct bfk_index {
+    int d = 0;
+    int metric = BFK_METRIC_L2;
+    int device = 0;
+    int storage = BFK_STORE_F32;
+    int ld32 = 0;
+    int ld16 = 0;
+    int num_sms = 148;
+    int64_t ntotal = 0;
+    int64_t cap = 0;
+    float* x32 = nullptr;
+    __nv_bfloat16* x16 = nullptr;
+    float* nrm = nullptr;
+    unsigned int* maxn = nullptr;
+    bfk::Workspace ws;       // search scratch, grow-only
+    cudaEvent_t ws_free = nullptr;  // recorded after the last search that used `ws`
+    std::mutex mu;
+};
+
+namespace bfk {
+
+int ensure_capacity(bfk_index* idx, int64_t need, cudaStream_t st);
+int ensure_workspace(bfk_index* idx, size_t bytes);
+
+// kernels / launchers implemented across the .cu files -----------------------
+// K2: append rows (cast + norms)
+int launch_append_f32(bfk_index* idx, const float* src_dev, int64_t src_ld, int64_t n, cudaStream_t st);
+// K1: pool + normalise (+ optional append into the index tail)
+int launch_pool(const void* tok, int tok_dtype, const void* mask, int mask_dtype, int64_t B, int T,
+                int H, float* out32, int64_t out32_ld, __nv_bfloat16* out16, int64_t out16_ld,
+                float* out_nrm, unsigned int* maxn, cudaStream_t st);
+// K3a: exact fp32 scan of up to 8 queries; writes sorted partial lists
+//   part [nq][nparts][k] composite keys; returns nparts through *nparts_out
+int scan_exact_workspace(const bfk_index* idx, int nq, int k, size_t* bytes, int* nparts_out);
+int launch_scan_exact(const bfk_index* idx, const float* q_dev /*[nq, ldq]*/, int ldq, int nq, int k,
+                      uint64_t* part, int nparts, cudaStream_t st);
+// K4/K6: per query, top-k of m composite keys -> (D, I)
+int launch_select(const uint64_t* cand, int64_t m_per_query, int64_t nq, int k, int metric,
+                  int64_t id_offset, float* D, int64_t* I, int64_t out_ld, cudaStream_t st);
+// K6 front end: pack (D, I) lists into composite keys
+int launch_pack_parts(const float* Dparts, const int64_t* Iparts, int nparts, int64_t nq, int k,
+                      int metric, uint64_t* cand, cudaStream_t st);
+// K3b + K5 (tensor path); defined in bfk_scan_tc.cu
+int tensor_path_supported(const bfk_index* idx, int64_t nq, int k);
+size_t tensor_workspace_bytes(const bfk_index* idx, int64_t nq, int k);
+int search_tensor(bfk_index* idx, const float* q_dev, int64_t nq, int k, float* D_dev, int64_t* I_dev,
+                  int64_t id_offset, cudaStream_t st, bfk_search_stats* stats);
+
+// ---- device helpers ---------------------------------------------------------
+// order-preserving map float -> uint32 (smaller float <=> smaller uint)
+__host__ __device__ __forceinline__ uint32_t f2ord(float f) {
+#ifdef __CUDA_ARCH__
+    uint32_t u = __float_as_uint(f);
+#else
+    union { float f; uint32_t u; } c; c.f = f; uint32_t u = c.u;
+#endif
+    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__host__ __device__ __forceinline__ float ord2f(uint32_t o) {
+    uint32_t u = (o & 0x80000000u) ? (o & 0x7fffffffu) : ~o;
+#ifdef __CUDA_ARCH__
+    return __uint_as_float(u);
+#else
+    union { float f; uint32_t u; } c; c.u = u; return c.f;
+#endif
+}
+// composite = (ordered key << 32) | row id : total order (key, id)
+__host__ __device__ __forceinline__ uint64_t make_comp(float key, uint32_t id) {
+    return (uint64_t(f2ord(key)) << 32) | uint64_t(id);
+}
+constexpr uint64_t COMP_EMPTY = ~0ull;
+
+}  // namespace bfk

@@ -1,0 +1,671 @@
+// libbfk.so: index object, storage management and the C ABI (include/bfk.h).
+//
+// Stands in for the faiss.IndexFlat* object that the reference builds in
+// semantic-indexer/indexer.py:39,104, fills at :41, persists at :27, reloads at :99 and
+// llm-qa/main.py:35, and searches through LangChain at llm-qa/main.py:101,117.
+#include <algorithm>
+#include <cfloat>
+#include <cstring>
+#include <vector>
+
+#include "bfk_common.cuh"
+
+namespace bfk {
+
+static thread_local std::string g_err;
+void set_error(const std::string& msg) { g_err = msg; }
+int fail(const std::string& msg) {
+    g_err = msg;
+    return 1;
+}
+
+static int check_device(int device) {
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0) {
+        cudaGetLastError();
+        return fail("no CUDA device available: libbfk has no CPU fallback");
+    }
+    if (device < 0 || device >= n) return fail("device index out of range");
+    return 0;
+}
+
+static int free_storage(bfk_index* idx) {
+    if (idx->x32) cudaFree(idx->x32);
+    if (idx->x16) cudaFree(idx->x16);
+    if (idx->nrm) cudaFree(idx->nrm);
+    idx->x32 = nullptr;
+    idx->x16 = nullptr;
+    idx->nrm = nullptr;
+    idx->cap = 0;
+    return 0;
+}
+
+static int alloc_storage(bfk_index* idx, int64_t cap, float** x32, __nv_bfloat16** x16, float** nrm) {
+    *x32 = nullptr;
+    *x16 = nullptr;
+    *nrm = nullptr;
+    cudaError_t e = cudaSuccess;
+    if (idx->storage == BFK_STORE_F32) e = cudaMalloc((void**)x32, sizeof(float) * (size_t)cap * idx->ld32);
+    if (e == cudaSuccess) e = cudaMalloc((void**)x16, sizeof(__nv_bfloat16) * (size_t)cap * idx->ld16);
+    if (e == cudaSuccess) e = cudaMalloc((void**)nrm, sizeof(float) * (size_t)cap);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        if (*x32) cudaFree(*x32);
+        if (*x16) cudaFree(*x16);
+        if (*nrm) cudaFree(*nrm);
+        *x32 = nullptr;
+        *x16 = nullptr;
+        *nrm = nullptr;
+        return 1;
+    }
+    return 0;
+}
+
+// grow corpus storage to hold at least `need` rows (amortised doubling)
+int ensure_capacity(bfk_index* idx, int64_t need, cudaStream_t st) {
+    if (need <= idx->cap) return 0;
+    int64_t want = std::max<int64_t>(std::max<int64_t>(need, idx->cap * 2), 1024);
+    float* x32;
+    __nv_bfloat16* x16;
+    float* nrm;
+    if (alloc_storage(idx, want, &x32, &x16, &nrm)) {
+        want = need;  // doubling did not fit in HBM: take exactly what is needed
+        if (alloc_storage(idx, want, &x32, &x16, &nrm))
+            return fail("out of device memory growing the index to " + std::to_string(need) + " rows");
+    }
+    if (idx->ntotal > 0) {
+        if (x32) BFK_CUDA(cudaMemcpyAsync(x32, idx->x32, sizeof(float) * (size_t)idx->ntotal * idx->ld32,
+                                          cudaMemcpyDeviceToDevice, st));
+        BFK_CUDA(cudaMemcpyAsync(x16, idx->x16, sizeof(__nv_bfloat16) * (size_t)idx->ntotal * idx->ld16,
+                                 cudaMemcpyDeviceToDevice, st));
+        BFK_CUDA(cudaMemcpyAsync(nrm, idx->nrm, sizeof(float) * (size_t)idx->ntotal, cudaMemcpyDeviceToDevice, st));
+        BFK_CUDA(cudaStreamSynchronize(st));
+    }
+    free_storage(idx);
+    idx->x32 = x32;
+    idx->x16 = x16;
+    idx->nrm = nrm;
+    idx->cap = want;
+    return 0;
+}
+
+int ensure_workspace(bfk_index* idx, size_t bytes) {
+    if (bytes <= idx->ws.bytes) return 0;
+    // the previous buffer may still be in use by an enqueued search
+    if (idx->ws_free) BFK_CUDA(cudaEventSynchronize(idx->ws_free));
+    if (idx->ws.ptr) cudaFree(idx->ws.ptr);
+    idx->ws.ptr = nullptr;
+    idx->ws.bytes = 0;
+    size_t want = std::max(bytes, (size_t)(4u << 20));
+    want = (size_t)round_up((int64_t)want, 1 << 20);
+    BFK_CUDA(cudaMalloc(&idx->ws.ptr, want));
+    idx->ws.bytes = want;
+    return 0;
+}
+
+struct WsCarver {
+    char* base;
+    size_t off = 0;
+    explicit WsCarver(void* p) : base((char*)p) {}
+    template <typename T>
+    T* take(size_t count) {
+        off = (size_t)round_up((int64_t)off, 256);
+        T* p = base ? (T*)(base + off) : nullptr;
+        off += sizeof(T) * count;
+        return p;
+    }
+};
+
+static int make_index(int d, int metric, int device, int storage, bfk_index** out) {
+    if (!out) return fail("null output pointer");
+    *out = nullptr;
+    if (d <= 0 || d > BFK_MAX_D) return fail("dimension must be in [1, " + std::to_string(BFK_MAX_D) + "]");
+    if (metric != BFK_METRIC_L2 && metric != BFK_METRIC_INNER_PRODUCT)
+        return fail("only METRIC_L2 and METRIC_INNER_PRODUCT flat indexes are supported");
+    if (storage != BFK_STORE_F32 && storage != BFK_STORE_BF16) return fail("unknown storage mode");
+    BFK_TRY(check_device(device));
+    DeviceGuard g(device);
+    if (!g.ok) return fail("cudaSetDevice failed");
+    bfk_index* idx = new bfk_index();
+    idx->d = d;
+    idx->metric = metric;
+    idx->device = device;
+    idx->storage = storage;
+    idx->ld32 = (int)round_up(d, 4);
+    idx->ld16 = (int)round_up(d, 64);
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device) == cudaSuccess) idx->num_sms = prop.multiProcessorCount;
+    if (prop.major < 10) {
+        delete idx;
+        return fail("libbfk is built for sm_100a (B200) only; device compute capability is " +
+                    std::to_string(prop.major) + "." + std::to_string(prop.minor));
+    }
+    if (cudaMalloc((void**)&idx->maxn, sizeof(unsigned int)) != cudaSuccess ||
+        cudaMemset(idx->maxn, 0, sizeof(unsigned int)) != cudaSuccess ||
+        cudaEventCreateWithFlags(&idx->ws_free, cudaEventDisableTiming) != cudaSuccess) {
+        delete idx;
+        return fail(std::string("index allocation failed: ") + cudaGetErrorString(cudaGetLastError()));
+    }
+    *out = idx;
+    return 0;
+}
+
+// ---- flat file format (faiss IxF2 / IxFI), see oracle/faiss_io.py for the layout ----
+static const int64_t HEADER_BYTES = 45;
+
+static void put_header(uint8_t* h, int d, int64_t n, int metric) {
+    memcpy(h, metric == BFK_METRIC_L2 ? "IxF2" : "IxFI", 4);
+    int32_t d32 = d;
+    memcpy(h + 4, &d32, 4);
+    memcpy(h + 8, &n, 8);
+    int64_t dummy = 1 << 20;
+    memcpy(h + 16, &dummy, 8);
+    memcpy(h + 24, &dummy, 8);
+    h[32] = 1;
+    int32_t m32 = metric;
+    memcpy(h + 33, &m32, 4);
+    uint64_t count = (uint64_t)n * (uint64_t)d;
+    memcpy(h + 37, &count, 8);
+}
+
+static int parse_header(const uint8_t* h, int64_t len, int* d, int64_t* n, int* metric, int64_t* payload_off) {
+    if (len < HEADER_BYTES) return fail("flat index: file too short");
+    bool f2 = !memcmp(h, "IxF2", 4), fi = !memcmp(h, "IxFI", 4), fl = !memcmp(h, "IxFl", 4);
+    if (!f2 && !fi && !fl)
+        return fail(std::string("Index type ") + std::string((const char*)h, 4) + " not recognized (only flat L2/IP)");
+    int32_t d32, m32;
+    memcpy(&d32, h + 4, 4);
+    memcpy(n, h + 8, 8);
+    memcpy(&m32, h + 33, 4);
+    int64_t off = 37;
+    if (m32 > 1) off += 4;
+    if (len < off + 8) return fail("flat index: truncated header");
+    uint64_t count;
+    memcpy(&count, h + off, 8);
+    off += 8;
+    if (d32 <= 0 || *n < 0 || count != (uint64_t)(*n) * (uint64_t)d32) return fail("flat index: corrupt header");
+    *d = d32;
+    *metric = f2 ? BFK_METRIC_L2 : fi ? BFK_METRIC_INNER_PRODUCT : m32;
+    if (*metric != BFK_METRIC_L2 && *metric != BFK_METRIC_INNER_PRODUCT)
+        return fail("flat index: unsupported metric type " + std::to_string(m32));
+    *payload_off = off;
+    return 0;
+}
+
+// copy rows [i0, i0+n) as packed fp32 [n, d] into a host or device buffer
+int launch_rows_to_f32(const bfk_index* idx, int64_t i0, int64_t n, float* out_dev, cudaStream_t st);
+
+static int rows_out(const bfk_index* idx, int64_t i0, int64_t n, float* out, int out_is_device) {
+    if (n == 0) return 0;
+    cudaStream_t st = 0;
+    if (idx->storage == BFK_STORE_F32) {
+        BFK_CUDA(cudaMemcpy2DAsync(out, sizeof(float) * idx->d, idx->x32 + (size_t)i0 * idx->ld32,
+                                   sizeof(float) * idx->ld32, sizeof(float) * idx->d, (size_t)n,
+                                   out_is_device ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, st));
+        BFK_CUDA(cudaStreamSynchronize(st));
+        return 0;
+    }
+    if (out_is_device) {
+        BFK_TRY(launch_rows_to_f32(idx, i0, n, out, st));
+        BFK_CUDA(cudaStreamSynchronize(st));
+        return 0;
+    }
+    const int64_t chunk = std::max<int64_t>(1, (64ll << 20) / (int64_t)(sizeof(float) * idx->d));
+    float* tmp = nullptr;
+    BFK_CUDA(cudaMalloc((void**)&tmp, sizeof(float) * (size_t)std::min(chunk, n) * idx->d));
+    int rc = 0;
+    for (int64_t j = 0; j < n && !rc; j += chunk) {
+        int64_t m = std::min(chunk, n - j);
+        rc = launch_rows_to_f32(idx, i0 + j, m, tmp, st);
+        if (!rc && cudaMemcpyAsync(out + (size_t)j * idx->d, tmp, sizeof(float) * (size_t)m * idx->d,
+                                   cudaMemcpyDeviceToHost, st) != cudaSuccess)
+            rc = fail("D2H copy failed");
+        if (!rc && cudaStreamSynchronize(st) != cudaSuccess) rc = fail("stream sync failed");
+    }
+    cudaFree(tmp);
+    return rc;
+}
+
+static int add_rows(bfk_index* idx, const float* x, int64_t n, int x_is_device, cudaStream_t st) {
+    if (n == 0) return 0;
+    if (!x) return fail("add: null input");
+    if (idx->ntotal + n > 0x7fffffffll) return fail("add: a single shard holds at most 2^31-1 rows");
+    BFK_TRY(ensure_capacity(idx, idx->ntotal + n, st));
+    if (x_is_device) {
+        BFK_TRY(launch_append_f32(idx, x, idx->d, n, st));
+        idx->ntotal += n;
+        return 0;
+    }
+    // host rows: stage through device scratch in <= 64 MiB pieces
+    const int64_t chunk = std::max<int64_t>(1, (64ll << 20) / (int64_t)(sizeof(float) * idx->d));
+    std::lock_guard<std::mutex> lk(idx->mu);
+    BFK_TRY(ensure_workspace(idx, sizeof(float) * (size_t)std::min(chunk, n) * idx->d));
+    BFK_CUDA(cudaStreamWaitEvent(st, idx->ws_free, 0));
+    for (int64_t j = 0; j < n; j += chunk) {
+        int64_t m = std::min(chunk, n - j);
+        BFK_CUDA(cudaMemcpyAsync(idx->ws.ptr, x + (size_t)j * idx->d, sizeof(float) * (size_t)m * idx->d,
+                                 cudaMemcpyHostToDevice, st));
+        BFK_TRY(launch_append_f32(idx, (const float*)idx->ws.ptr, idx->d, m, st));
+        idx->ntotal += m;
+        // the staging buffer is reused by the next piece (and the caller owns x again on return)
+        BFK_CUDA(cudaStreamSynchronize(st));
+    }
+    BFK_CUDA(cudaEventRecord(idx->ws_free, st));
+    return 0;
+}
+
+// ---- search orchestration ---------------------------------------------------
+static int search_exact(bfk_index* idx, const float* q_dev, int ldq, int64_t nq, int k, float* D_dev,
+                        int64_t* I_dev, int64_t id_offset, char* ws_tail, size_t ws_tail_bytes,
+                        cudaStream_t st, bfk_search_stats* stats, cudaEvent_t ev0, cudaEvent_t ev1);
+
+}  // namespace bfk
+
+using namespace bfk;
+
+extern "C" {
+
+const char* bfk_last_error(void) { return g_err.c_str(); }
+int bfk_version(void) { return 100; }
+
+int bfk_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    return n;
+}
+
+int bfk_create(int d, int metric, int device, int storage, bfk_index** out) {
+    return make_index(d, metric, device, storage, out);
+}
+
+int bfk_free(bfk_index* idx) {
+    if (!idx) return 0;
+    DeviceGuard g(idx->device);
+    cudaDeviceSynchronize();
+    free_storage(idx);
+    if (idx->ws.ptr) cudaFree(idx->ws.ptr);
+    if (idx->maxn) cudaFree(idx->maxn);
+    if (idx->ws_free) cudaEventDestroy(idx->ws_free);
+    delete idx;
+    return 0;
+}
+
+int bfk_dim(const bfk_index* idx) { return idx ? idx->d : -1; }
+int bfk_metric(const bfk_index* idx) { return idx ? idx->metric : -1; }
+int bfk_storage(const bfk_index* idx) { return idx ? idx->storage : -1; }
+int bfk_device(const bfk_index* idx) { return idx ? idx->device : -1; }
+int64_t bfk_ntotal(const bfk_index* idx) { return idx ? idx->ntotal : -1; }
+
+int bfk_reserve(bfk_index* idx, int64_t n) {
+    if (!idx) return fail("null index");
+    DeviceGuard g(idx->device);
+    if (n <= idx->cap) return 0;
+    // exact-size allocation: callers reserve when they know the final size
+    float* x32;
+    __nv_bfloat16* x16;
+    float* nrm;
+    if (alloc_storage(idx, n, &x32, &x16, &nrm)) return fail("reserve: out of device memory");
+    cudaStream_t st = 0;
+    if (idx->ntotal > 0) {
+        if (x32) BFK_CUDA(cudaMemcpyAsync(x32, idx->x32, sizeof(float) * (size_t)idx->ntotal * idx->ld32,
+                                          cudaMemcpyDeviceToDevice, st));
+        BFK_CUDA(cudaMemcpyAsync(x16, idx->x16, sizeof(__nv_bfloat16) * (size_t)idx->ntotal * idx->ld16,
+                                 cudaMemcpyDeviceToDevice, st));
+        BFK_CUDA(cudaMemcpyAsync(nrm, idx->nrm, sizeof(float) * (size_t)idx->ntotal, cudaMemcpyDeviceToDevice, st));
+    }
+    BFK_CUDA(cudaStreamSynchronize(st));
+    free_storage(idx);
+    idx->x32 = x32;
+    idx->x16 = x16;
+    idx->nrm = nrm;
+    idx->cap = n;
+    return 0;
+}
+
+int bfk_add(bfk_index* idx, const float* x, int64_t n, int x_is_device, void* stream) {
+    if (!idx) return fail("null index");
+    if (n < 0) return fail("add: negative row count");
+    DeviceGuard g(idx->device);
+    return add_rows(idx, x, n, x_is_device, (cudaStream_t)stream);
+}
+
+int bfk_add_pooled(bfk_index* idx, const void* tok, int tok_dtype, const void* mask, int mask_dtype,
+                   int64_t B, int T, int H, void* stream) {
+    if (!idx) return fail("null index");
+    if (H != idx->d) return fail("add_pooled: hidden size != index dimension");
+    if (B < 0 || T <= 0) return fail("add_pooled: bad shape");
+    if (B == 0) return 0;
+    if (idx->ntotal + B > 0x7fffffffll) return fail("add: a single shard holds at most 2^31-1 rows");
+    DeviceGuard g(idx->device);
+    cudaStream_t st = (cudaStream_t)stream;
+    BFK_TRY(ensure_capacity(idx, idx->ntotal + B, st));
+    float* o32 = idx->x32 ? idx->x32 + (size_t)idx->ntotal * idx->ld32 : nullptr;
+    __nv_bfloat16* o16 = idx->x16 + (size_t)idx->ntotal * idx->ld16;
+    BFK_TRY(launch_pool(tok, tok_dtype, mask, mask_dtype, B, T, H, o32, idx->ld32, o16, idx->ld16,
+                        idx->nrm + idx->ntotal, idx->maxn, st));
+    idx->ntotal += B;
+    return 0;
+}
+
+int bfk_pool_normalize(const void* tok, int tok_dtype, const void* mask, int mask_dtype, int64_t B, int T,
+                       int H, float* out_f32, int io_is_device, int device, void* stream) {
+    BFK_TRY(check_device(device));
+    if (B < 0 || T <= 0 || H <= 0) return fail("pool_normalize: bad shape");
+    if (B == 0) return 0;
+    DeviceGuard g(device);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (io_is_device)
+        return launch_pool(tok, tok_dtype, mask, mask_dtype, B, T, H, out_f32, H, nullptr, 0, nullptr, nullptr, st);
+    size_t tsz = tok_dtype == BFK_DT_F32 ? 4 : 2;
+    size_t msz = mask_dtype == BFK_DT_I64 ? 8 : mask_dtype == BFK_DT_I32 ? 4 : 1;
+    void *dtok = nullptr, *dmask = nullptr;
+    float* dout = nullptr;
+    int rc = 0;
+    if (cudaMalloc(&dtok, tsz * (size_t)B * T * H) != cudaSuccess || cudaMalloc(&dmask, msz * (size_t)B * T) != cudaSuccess ||
+        cudaMalloc((void**)&dout, sizeof(float) * (size_t)B * H) != cudaSuccess)
+        rc = fail("pool_normalize: out of device memory");
+    if (!rc && (cudaMemcpyAsync(dtok, tok, tsz * (size_t)B * T * H, cudaMemcpyHostToDevice, st) != cudaSuccess ||
+                cudaMemcpyAsync(dmask, mask, msz * (size_t)B * T, cudaMemcpyHostToDevice, st) != cudaSuccess))
+        rc = fail("pool_normalize: H2D copy failed");
+    if (!rc) rc = launch_pool(dtok, tok_dtype, dmask, mask_dtype, B, T, H, dout, H, nullptr, 0, nullptr, nullptr, st);
+    if (!rc && (cudaMemcpyAsync(out_f32, dout, sizeof(float) * (size_t)B * H, cudaMemcpyDeviceToHost, st) != cudaSuccess ||
+                cudaStreamSynchronize(st) != cudaSuccess))
+        rc = fail("pool_normalize: D2H copy failed");
+    cudaFree(dtok);
+    cudaFree(dmask);
+    cudaFree(dout);
+    return rc;
+}
+
+int bfk_search(bfk_index* idx, const float* q, int64_t nq, int64_t k, float* D, int64_t* I, int io_is_device,
+               void* stream) {
+    return bfk_search_ex(idx, q, nq, k, D, I, io_is_device, stream, BFK_ALGO_AUTO, 0, nullptr);
+}
+
+int bfk_search_ex(bfk_index* idx, const float* q, int64_t nq, int64_t k64, float* D, int64_t* I,
+                  int io_is_device, void* stream, int algo, int64_t id_offset, bfk_search_stats* stats) {
+    if (!idx) return fail("null index");
+    if (nq < 0) return fail("search: negative query count");
+    if (k64 <= 0) return fail("search: k must be positive");
+    if (k64 > BFK_MAX_K) return fail("search: k > " + std::to_string(BFK_MAX_K) + " is not supported");
+    if (stats) memset(stats, 0, sizeof(*stats));
+    if (nq == 0) return 0;
+    if (!q || !D || !I) return fail("search: null buffer");
+    const int k = (int)k64;
+    DeviceGuard g(idx->device);
+    cudaStream_t st = (cudaStream_t)stream;
+    std::lock_guard<std::mutex> lk(idx->mu);
+
+    if (algo == BFK_ALGO_AUTO) {
+        algo = (nq > 8 && tensor_path_supported(idx, nq, k)) ? BFK_ALGO_TENSOR : BFK_ALGO_EXACT_SIMT;
+    } else if (algo == BFK_ALGO_TENSOR) {
+        if (!tensor_path_supported(idx, nq, k)) return fail("search: tensor path does not support this shape");
+    } else if (algo != BFK_ALGO_EXACT_SIMT) {
+        return fail("search: unknown algorithm");
+    }
+
+    // workspace: [queries fp32 padded][D][I][algorithm scratch...]
+    const int ldq = idx->ld32;
+    size_t scratch = 0;
+    int nparts = 0;
+    BFK_TRY(scan_exact_workspace(idx, (int)std::min<int64_t>(nq, 8), k, &scratch, &nparts));
+    size_t exact_bytes = sizeof(uint64_t) * (size_t)nq * nparts * k;
+    size_t tail_bytes = exact_bytes;
+    if (algo == BFK_ALGO_TENSOR) {
+        // the tensor path sizes its own scratch inside search_tensor via ensure_workspace's tail
+        tail_bytes = std::max(tail_bytes, tensor_workspace_bytes(idx, nq, k));
+    }
+    WsCarver sizing(nullptr);
+    sizing.take<float>((size_t)nq * ldq);
+    sizing.take<float>((size_t)nq * k);
+    sizing.take<int64_t>((size_t)nq * k);
+    sizing.take<char>(256);
+    size_t head = sizing.off;
+    BFK_TRY(ensure_workspace(idx, head + tail_bytes + 512));
+    BFK_CUDA(cudaStreamWaitEvent(st, idx->ws_free, 0));
+    WsCarver ws(idx->ws.ptr);
+    float* q_dev = ws.take<float>((size_t)nq * ldq);
+    float* D_dev = ws.take<float>((size_t)nq * k);
+    int64_t* I_dev = ws.take<int64_t>((size_t)nq * k);
+    char* tail = ws.take<char>(256);
+    size_t tail_avail = idx->ws.bytes - (size_t)(tail - (char*)idx->ws.ptr);
+
+    if (ldq != idx->d) BFK_CUDA(cudaMemsetAsync(q_dev, 0, sizeof(float) * (size_t)nq * ldq, st));
+    BFK_CUDA(cudaMemcpy2DAsync(q_dev, sizeof(float) * ldq, q, sizeof(float) * idx->d, sizeof(float) * idx->d,
+                               (size_t)nq, io_is_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, st));
+    float* D_out = io_is_device ? D : D_dev;
+    int64_t* I_out = io_is_device ? I : I_dev;
+
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    if (stats) {
+        BFK_CUDA(cudaEventCreate(&ev0));
+        BFK_CUDA(cudaEventCreate(&ev1));
+    }
+    int rc;
+    if (algo == BFK_ALGO_TENSOR) {
+        if (stats) cudaEventRecord(ev0, st);
+        rc = search_tensor(idx, q_dev, nq, k, D_out, I_out, id_offset, st, stats);
+        if (stats) cudaEventRecord(ev1, st);
+    } else {
+        rc = search_exact(idx, q_dev, ldq, nq, k, D_out, I_out, id_offset, tail, tail_avail, st, stats, ev0, ev1);
+    }
+    if (!rc && !io_is_device) {
+        if (cudaMemcpyAsync(D, D_dev, sizeof(float) * (size_t)nq * k, cudaMemcpyDeviceToHost, st) != cudaSuccess ||
+            cudaMemcpyAsync(I, I_dev, sizeof(int64_t) * (size_t)nq * k, cudaMemcpyDeviceToHost, st) != cudaSuccess)
+            rc = fail("search: D2H copy failed");
+    }
+    if (!rc && cudaEventRecord(idx->ws_free, st) != cudaSuccess) rc = fail("search: event record failed");
+    if (!rc && (!io_is_device || stats)) {
+        cudaError_t e = cudaStreamSynchronize(st);
+        if (e != cudaSuccess) rc = fail(std::string("search: kernel execution failed: ") + cudaGetErrorString(e));
+    }
+    if (stats) {
+        if (!rc) {
+            float ms = 0.f;
+            if (cudaEventElapsedTime(&ms, ev0, ev1) == cudaSuccess) stats->scan_ms = ms;
+            stats->algo_used = algo;
+        }
+        cudaEventDestroy(ev0);
+        cudaEventDestroy(ev1);
+    }
+    return rc;
+}
+
+int bfk_reset(bfk_index* idx) {
+    if (!idx) return fail("null index");
+    DeviceGuard g(idx->device);
+    std::lock_guard<std::mutex> lk(idx->mu);
+    BFK_CUDA(cudaDeviceSynchronize());
+    idx->ntotal = 0;
+    BFK_CUDA(cudaMemset(idx->maxn, 0, sizeof(unsigned int)));
+    return 0;
+}
+
+int bfk_reconstruct(const bfk_index* idx, int64_t i0, int64_t n, float* out, int out_is_device) {
+    if (!idx) return fail("null index");
+    if (n < 0 || i0 < 0 || i0 + n > idx->ntotal) return fail("reconstruct: id range out of bounds");
+    if (n == 0) return 0;
+    if (!out) return fail("reconstruct: null output");
+    DeviceGuard g(idx->device);
+    return rows_out(idx, i0, n, out, out_is_device);
+}
+
+int bfk_remove_ids(bfk_index* idx, const int64_t* ids, int64_t n, int64_t* nremoved) {
+    if (!idx) return fail("null index");
+    if (nremoved) *nremoved = 0;
+    if (n < 0 || (n > 0 && !ids)) return fail("remove_ids: bad arguments");
+    DeviceGuard g(idx->device);
+    std::lock_guard<std::mutex> lk(idx->mu);
+    std::vector<int64_t> rm;
+    rm.reserve((size_t)n);
+    for (int64_t i = 0; i < n; i++)
+        if (ids[i] >= 0 && ids[i] < idx->ntotal) rm.push_back(ids[i]);
+    std::sort(rm.begin(), rm.end());
+    rm.erase(std::unique(rm.begin(), rm.end()), rm.end());
+    if (rm.empty()) return 0;
+    BFK_CUDA(cudaDeviceSynchronize());
+    // IndexFlatCodes::remove_ids keeps the surviving rows in order: move each kept segment down
+    // through fresh buffers (device copies must not overlap)
+    float* x32;
+    __nv_bfloat16* x16;
+    float* nrm;
+    const int64_t left = idx->ntotal - (int64_t)rm.size();
+    const int64_t newcap = std::max<int64_t>(left, 1024);
+    if (alloc_storage(idx, newcap, &x32, &x16, &nrm)) return fail("remove_ids: out of device memory");
+    int64_t dst = 0, src = 0;
+    cudaStream_t st = 0;
+    auto copy_seg = [&](int64_t s, int64_t e) -> int {
+        int64_t m = e - s;
+        if (m <= 0) return 0;
+        if (x32) BFK_CUDA(cudaMemcpyAsync(x32 + (size_t)dst * idx->ld32, idx->x32 + (size_t)s * idx->ld32,
+                                          sizeof(float) * (size_t)m * idx->ld32, cudaMemcpyDeviceToDevice, st));
+        BFK_CUDA(cudaMemcpyAsync(x16 + (size_t)dst * idx->ld16, idx->x16 + (size_t)s * idx->ld16,
+                                 sizeof(__nv_bfloat16) * (size_t)m * idx->ld16, cudaMemcpyDeviceToDevice, st));
+        BFK_CUDA(cudaMemcpyAsync(nrm + dst, idx->nrm + s, sizeof(float) * (size_t)m, cudaMemcpyDeviceToDevice, st));
+        dst += m;
+        return 0;
+    };
+    int rc = 0;
+    for (size_t r = 0; r < rm.size() && !rc; r++) {
+        rc = copy_seg(src, rm[r]);
+        src = rm[r] + 1;
+    }
+    if (!rc) rc = copy_seg(src, idx->ntotal);
+    if (!rc && cudaStreamSynchronize(st) != cudaSuccess) rc = fail("remove_ids: copy failed");
+    if (rc) {
+        if (x32) cudaFree(x32);
+        cudaFree(x16);
+        cudaFree(nrm);
+        return rc;
+    }
+    free_storage(idx);
+    idx->x32 = x32;
+    idx->x16 = x16;
+    idx->nrm = nrm;
+    idx->cap = newcap;
+    idx->ntotal = left;
+    if (nremoved) *nremoved = (int64_t)rm.size();
+    return 0;
+}
+
+int64_t bfk_serialized_size(const bfk_index* idx) {
+    if (!idx) return -1;
+    return HEADER_BYTES + (int64_t)sizeof(float) * idx->ntotal * idx->d;
+}
+
+int bfk_serialize(const bfk_index* idx, uint8_t* buf, int64_t buf_len) {
+    if (!idx || !buf) return fail("serialize: null argument");
+    if (buf_len < bfk_serialized_size(idx)) return fail("serialize: buffer too small");
+    DeviceGuard g(idx->device);
+    put_header(buf, idx->d, idx->ntotal, idx->metric);
+    return rows_out(idx, 0, idx->ntotal, (float*)(buf + HEADER_BYTES), 0);
+}
+
+int bfk_deserialize(const uint8_t* buf, int64_t len, int device, int storage, bfk_index** out) {
+    if (!buf || !out) return fail("deserialize: null argument");
+    int d, metric;
+    int64_t n, off;
+    BFK_TRY(parse_header(buf, len, &d, &n, &metric, &off));
+    if (len < off + (int64_t)sizeof(float) * n * d) return fail("flat index: truncated payload");
+    BFK_TRY(make_index(d, metric, device, storage, out));
+    DeviceGuard g(device);
+    // payload starts at byte 45: not 4-byte aligned in general, so bounce through an aligned copy
+    std::vector<float> tmp((size_t)n * d);
+    memcpy(tmp.data(), buf + off, sizeof(float) * (size_t)n * d);
+    int rc = add_rows(*out, tmp.data(), n, 0, 0);
+    if (rc) {
+        bfk_free(*out);
+        *out = nullptr;
+    }
+    return rc;
+}
+
+int bfk_write(const bfk_index* idx, const char* path) {
+    if (!idx || !path) return fail("write_index: null argument");
+    DeviceGuard g(idx->device);
+    FILE* f = fopen(path, "wb");
+    if (!f) return fail(std::string("could not open ") + path + " for writing");
+    uint8_t h[HEADER_BYTES];
+    put_header(h, idx->d, idx->ntotal, idx->metric);
+    int rc = fwrite(h, 1, HEADER_BYTES, f) == (size_t)HEADER_BYTES ? 0 : fail("write_index: short write");
+    const int64_t chunk = std::max<int64_t>(1, (256ll << 20) / (int64_t)(sizeof(float) * idx->d));
+    std::vector<float> tmp((size_t)std::min(chunk, std::max<int64_t>(idx->ntotal, 1)) * idx->d);
+    for (int64_t j = 0; j < idx->ntotal && !rc; j += chunk) {
+        int64_t m = std::min(chunk, idx->ntotal - j);
+        rc = rows_out(idx, j, m, tmp.data(), 0);
+        if (!rc && fwrite(tmp.data(), sizeof(float), (size_t)m * idx->d, f) != (size_t)m * idx->d)
+            rc = fail("write_index: short write");
+    }
+    if (fclose(f) != 0 && !rc) rc = fail("write_index: close failed");
+    return rc;
+}
+
+int bfk_read(const char* path, int device, int storage, bfk_index** out) {
+    if (!path || !out) return fail("read_index: null argument");
+    *out = nullptr;
+    FILE* f = fopen(path, "rb");
+    if (!f) return fail(std::string("could not open ") + path + " for reading");
+    uint8_t h[HEADER_BYTES + 4];
+    size_t got = fread(h, 1, sizeof(h), f);
+    int d, metric;
+    int64_t n, off;
+    int rc = parse_header(h, (int64_t)got, &d, &n, &metric, &off);
+    if (!rc) rc = make_index(d, metric, device, storage, out);
+    if (!rc) {
+        DeviceGuard g(device);
+        fseek(f, (long)off, SEEK_SET);
+        const int64_t chunk = std::max<int64_t>(1, (256ll << 20) / (int64_t)(sizeof(float) * d));
+        std::vector<float> tmp((size_t)std::min(chunk, std::max<int64_t>(n, 1)) * d);
+        rc = bfk_reserve(*out, std::max<int64_t>(n, 1));
+        for (int64_t j = 0; j < n && !rc; j += chunk) {
+            int64_t m = std::min(chunk, n - j);
+            if (fread(tmp.data(), sizeof(float), (size_t)m * d, f) != (size_t)m * d)
+                rc = fail("read_index: truncated payload");
+            if (!rc) rc = add_rows(*out, tmp.data(), m, 0, 0);
+        }
+        if (rc) {
+            bfk_free(*out);
+            *out = nullptr;
+        }
+    }
+    fclose(f);
+    return rc;
+}
+
+}  // extern "C"
+
+namespace bfk {
+
+// Exact path: groups of <= 8 queries, one corpus pass per group, then one select launch.
+static int search_exact(bfk_index* idx, const float* q_dev, int ldq, int64_t nq, int k, float* D_dev,
+                        int64_t* I_dev, int64_t id_offset, char* ws_tail, size_t ws_tail_bytes,
+                        cudaStream_t st, bfk_search_stats* stats, cudaEvent_t ev0, cudaEvent_t ev1) {
+    size_t scratch = 0;
+    int nparts = 0;
+    BFK_TRY(scan_exact_workspace(idx, (int)std::min<int64_t>(nq, 8), k, &scratch, &nparts));
+    size_t need = sizeof(uint64_t) * (size_t)nq * nparts * k;
+    if (need > ws_tail_bytes) return fail("internal: exact-scan workspace under-sized");
+    uint64_t* part = (uint64_t*)ws_tail;
+    int launches = 0;
+    if (stats) cudaEventRecord(ev0, st);
+    for (int64_t q0 = 0; q0 < nq;) {
+        int g = (int)std::min<int64_t>(nq - q0, 8);
+        BFK_TRY(launch_scan_exact(idx, q_dev + (size_t)q0 * ldq, ldq, g, k, part + (size_t)q0 * nparts * k, nparts, st));
+        launches++;
+        q0 += g;
+    }
+    if (stats) cudaEventRecord(ev1, st);
+    BFK_TRY(launch_select(part, (int64_t)nparts * k, nq, k, idx->metric, id_offset, D_dev, I_dev, k, st));
+    launches++;
+    if (stats) {
+        stats->n_launches = launches;
+        stats->algo_used = BFK_ALGO_EXACT_SIMT;
+    }
+    return 0;
+}
+
+}  // namespace bfk

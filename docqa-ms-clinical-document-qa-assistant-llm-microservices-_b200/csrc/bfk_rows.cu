@@ -1,0 +1,139 @@
+// K2 `append_cast_norm` and the small row utilities around it.
+//
+// K2 replaces IndexFlatCodes::add as reached from semantic-indexer/indexer.py:41
+// (index.add(float32[n, d])): besides the fp32 master copy it produces the bf16 scan
+// copy (zero padded to a multiple of 64 columns, the tcgen05 K-block) and the fp32
+// squared norm of every row, and keeps max ||x||^2 for the rerank certificate.
+// HBM-bound: reads 4*d bytes/row, writes 4*ld32 + 2*ld16 + 4 bytes/row.
+#include "bfk_common.cuh"
+
+namespace bfk {
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// one warp per row; lanes stride the columns so every access is coalesced
+template <bool STORE_F32>
+__global__ void __launch_bounds__(256) append_rows_kernel(const float* __restrict__ src, int64_t src_ld, int64_t n,
+                                                          int d, float* __restrict__ x32, int ld32,
+                                                          __nv_bfloat16* __restrict__ x16, int ld16,
+                                                          float* __restrict__ nrm, unsigned int* __restrict__ maxn) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int64_t nwarps = (int64_t)gridDim.x * (blockDim.x >> 5);
+    float local_max = 0.f;
+    for (int64_t r = warp; r < n; r += nwarps) {
+        const float* s = src + r * src_ld;
+        float ss = 0.f;
+        for (int c = lane; c < ld16; c += 32) {
+            float v = (c < d) ? __ldg(s + c) : 0.f;
+            __nv_bfloat16 b = __float2bfloat16_rn(v);
+            if (STORE_F32) {
+                if (c < ld32) x32[r * ld32 + c] = v;
+                ss += v * v;
+            } else {
+                float vb = __bfloat162float(b);
+                ss += vb * vb;
+            }
+            x16[r * ld16 + c] = b;
+        }
+        ss = warp_sum(ss);
+        if (lane == 0) nrm[r] = ss;
+        local_max = fmaxf(local_max, ss);
+    }
+    // non-negative floats order like their bit patterns
+    if (lane == 0 && local_max > 0.f) atomicMax(maxn, __float_as_uint(local_max));
+}
+
+int launch_append_f32(bfk_index* idx, const float* src_dev, int64_t src_ld, int64_t n, cudaStream_t st) {
+    if (n <= 0) return 0;
+    const int warps_per_block = 8;
+    int64_t blocks = std::min<int64_t>((n + warps_per_block - 1) / warps_per_block, (int64_t)idx->num_sms * 16);
+    float* o32 = idx->x32 ? idx->x32 + (size_t)idx->ntotal * idx->ld32 : nullptr;
+    __nv_bfloat16* o16 = idx->x16 + (size_t)idx->ntotal * idx->ld16;
+    float* on = idx->nrm + idx->ntotal;
+    if (idx->storage == BFK_STORE_F32)
+        append_rows_kernel<true><<<(unsigned)blocks, 256, 0, st>>>(src_dev, src_ld, n, idx->d, o32, idx->ld32, o16,
+                                                                   idx->ld16, on, idx->maxn);
+    else
+        append_rows_kernel<false><<<(unsigned)blocks, 256, 0, st>>>(src_dev, src_ld, n, idx->d, nullptr, 0, o16,
+                                                                    idx->ld16, on, idx->maxn);
+    BFK_CUDA(cudaGetLastError());
+    return 0;
+}
+
+// bf16-stored rows -> packed fp32 [n, d] (reconstruct / write_index for BFK_STORE_BF16)
+__global__ void __launch_bounds__(256) rows_bf16_to_f32_kernel(const __nv_bfloat16* __restrict__ x16, int ld16,
+                                                               int64_t n, int d, float* __restrict__ out) {
+    const int64_t total = n * d;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        int64_t r = i / d;
+        int c = (int)(i - r * d);
+        out[i] = __bfloat162float(x16[r * ld16 + c]);
+    }
+}
+
+int launch_rows_to_f32(const bfk_index* idx, int64_t i0, int64_t n, float* out_dev, cudaStream_t st) {
+    if (n <= 0) return 0;
+    int64_t total = n * idx->d;
+    int64_t blocks = std::min<int64_t>((total + 255) / 256, (int64_t)idx->num_sms * 16);
+    rows_bf16_to_f32_kernel<<<(unsigned)blocks, 256, 0, st>>>(idx->x16 + (size_t)i0 * idx->ld16, idx->ld16, n, idx->d,
+                                                              out_dev);
+    BFK_CUDA(cudaGetLastError());
+    return 0;
+}
+
+// faiss.normalize_L2 (fvec_renorm_L2): x[i] *= 1/sqrt(||x[i]||^2) when the norm is > 0
+__global__ void __launch_bounds__(256) renorm_rows_kernel(float* __restrict__ x, int64_t n, int d) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int64_t nwarps = (int64_t)gridDim.x * (blockDim.x >> 5);
+    for (int64_t r = warp; r < n; r += nwarps) {
+        float* row = x + r * d;
+        float ss = 0.f;
+        for (int c = lane; c < d; c += 32) ss += row[c] * row[c];
+        ss = warp_sum(ss);
+        if (ss > 0.f) {
+            float inv = 1.0f / sqrtf(ss);
+            for (int c = lane; c < d; c += 32) row[c] *= inv;
+        }
+    }
+}
+
+}  // namespace bfk
+
+extern "C" int bfk_normalize_l2(float* x, int64_t n, int d, int x_is_device, int device, void* stream) {
+    using namespace bfk;
+    if (n < 0 || d <= 0) return fail("normalize_L2: bad shape");
+    if (n == 0) return 0;
+    if (!x) return fail("normalize_L2: null input");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        return fail("no CUDA device available: libbfk has no CPU fallback");
+    }
+    DeviceGuard g(device);
+    cudaStream_t st = (cudaStream_t)stream;
+    float* dx = x;
+    if (!x_is_device) {
+        BFK_CUDA(cudaMalloc((void**)&dx, sizeof(float) * (size_t)n * d));
+        if (cudaMemcpyAsync(dx, x, sizeof(float) * (size_t)n * d, cudaMemcpyHostToDevice, st) != cudaSuccess) {
+            cudaFree(dx);
+            return fail("normalize_L2: H2D copy failed");
+        }
+    }
+    int64_t blocks = std::min<int64_t>((n + 7) / 8, 148 * 16);
+    renorm_rows_kernel<<<(unsigned)blocks, 256, 0, st>>>(dx, n, d);
+    int rc = 0;
+    if (cudaGetLastError() != cudaSuccess) rc = fail("normalize_L2: launch failed");
+    if (!x_is_device) {
+        if (!rc && (cudaMemcpyAsync(x, dx, sizeof(float) * (size_t)n * d, cudaMemcpyDeviceToHost, st) != cudaSuccess ||
+                    cudaStreamSynchronize(st) != cudaSuccess))
+            rc = fail("normalize_L2: D2H copy failed");
+        cudaFree(dx);
+    }
+    return rc;
+}

@@ -1,0 +1,156 @@
+// K4 `select_topk` / K6 `merge_parts`: per query, the k smallest of m composite keys,
+// written best-first as the (D, I) pair faiss returns.
+//
+// Stands in for faiss's heap_reorder + result hand-off at the end of IndexFlat::search
+// (reached from llm-qa/main.py:101,117) and, for the row-sharded index, for the merge
+// that follows the all-gather of per-GPU lists (BASELINE config 5; no reference
+// counterpart).  Missing results follow faiss: I = -1, D = +FLT_MAX (L2) / -FLT_MAX (IP).
+#include <cfloat>
+
+#include "bfk_common.cuh"
+
+namespace bfk {
+
+constexpr int SEL_THREADS = 512;
+constexpr int SEL_N = 4096;  // sort window (composites), 32 KiB of shared memory
+
+__device__ void block_bitonic_sort(uint64_t* a, int n, int tid, int nthr) {
+    for (int k2 = 2; k2 <= n; k2 <<= 1) {
+        for (int j = k2 >> 1; j > 0; j >>= 1) {
+            for (int i = tid; i < (n >> 1); i += nthr) {
+                int lo = ((i & ~(j - 1)) << 1) | (i & (j - 1));
+                int hi = lo + j;
+                bool asc = (lo & k2) == 0;
+                uint64_t x = a[lo], y = a[hi];
+                if ((x > y) == asc) {
+                    a[lo] = y;
+                    a[hi] = x;
+                }
+            }
+            __syncthreads();
+        }
+    }
+}
+
+// cand [nq][m]; if `gather` != nullptr the low 32 bits of a composite index gather[q*... ]
+// (see pack_parts_kernel) instead of being the row id itself.
+__global__ void __launch_bounds__(SEL_THREADS) select_topk_kernel(const uint64_t* __restrict__ cand, int64_t m, int k,
+                                                                  int metric, int64_t id_offset,
+                                                                  const int64_t* __restrict__ gather, int64_t gather_q_stride,
+                                                                  int64_t gather_p_stride, int gather_k,
+                                                                  float* __restrict__ D, int64_t* __restrict__ I,
+                                                                  int64_t out_ld) {
+    __shared__ uint64_t buf[SEL_N];
+    const int tid = threadIdx.x;
+    const int64_t q = blockIdx.x;
+    const uint64_t* src = cand + q * m;
+
+    if (m <= SEL_N) {
+        int n = 32;
+        while (n < m || n < k) n <<= 1;
+        for (int i = tid; i < n; i += SEL_THREADS) buf[i] = (i < m) ? src[i] : COMP_EMPTY;
+        __syncthreads();
+        block_bitonic_sort(buf, n, tid, SEL_THREADS);
+    } else {
+        // keep the best kpad at the front, fold the rest through the window
+        int kpad = 32;
+        while (kpad < k) kpad <<= 1;
+        const int step = SEL_N - kpad;
+        for (int i = tid; i < kpad; i += SEL_THREADS) buf[i] = COMP_EMPTY;
+        for (int64_t base = 0; base < m; base += step) {
+            for (int i = tid; i < step; i += SEL_THREADS) buf[kpad + i] = (base + i < m) ? src[base + i] : COMP_EMPTY;
+            __syncthreads();
+            block_bitonic_sort(buf, SEL_N, tid, SEL_THREADS);
+        }
+    }
+    for (int i = tid; i < k; i += SEL_THREADS) {
+        const uint64_t c = (i < SEL_N) ? buf[i] : COMP_EMPTY;
+        float dv;
+        int64_t iv;
+        if (c == COMP_EMPTY) {
+            dv = (metric == BFK_METRIC_L2) ? FLT_MAX : -FLT_MAX;
+            iv = -1;
+        } else {
+            float key = ord2f((uint32_t)(c >> 32));
+            dv = (metric == BFK_METRIC_L2) ? key : -key;
+            uint32_t lo = (uint32_t)(c & 0xffffffffu);
+            if (gather) {
+                uint32_t part = lo / (uint32_t)gather_k, slot = lo - part * (uint32_t)gather_k;
+                iv = gather[(int64_t)part * gather_p_stride + q * gather_q_stride + slot];
+            } else {
+                iv = (int64_t)lo + id_offset;
+            }
+        }
+        D[q * out_ld + i] = dv;
+        I[q * out_ld + i] = iv;
+    }
+}
+
+int launch_select(const uint64_t* cand, int64_t m_per_query, int64_t nq, int k, int metric, int64_t id_offset,
+                  float* D, int64_t* I, int64_t out_ld, cudaStream_t st) {
+    if (nq <= 0) return 0;
+    select_topk_kernel<<<(unsigned)nq, SEL_THREADS, 0, st>>>(cand, m_per_query, k, metric, id_offset, nullptr, 0, 0, 1,
+                                                            D, I, out_ld);
+    BFK_CUDA(cudaGetLastError());
+    return 0;
+}
+
+// (D, I) lists [nparts][nq][k] -> composites [nq][nparts*k]; low word = part*k + slot so that
+// equal distances resolve by shard then by the shard's own (distance, id) order.
+__global__ void __launch_bounds__(256) pack_parts_kernel(const float* __restrict__ Dp, const int64_t* __restrict__ Ip,
+                                                         int nparts, int64_t nq, int k, int metric,
+                                                         uint64_t* __restrict__ cand) {
+    const int64_t total = (int64_t)nparts * nq * k;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        int64_t p = i / (nq * k);
+        int64_t r = i - p * nq * k;
+        int64_t q = r / k;
+        int s = (int)(r - q * k);
+        uint64_t c = COMP_EMPTY;
+        if (Ip[i] >= 0) {
+            float key = (metric == BFK_METRIC_L2) ? Dp[i] : -Dp[i];
+            c = make_comp(key, (uint32_t)(p * k + s));
+        }
+        cand[q * ((int64_t)nparts * k) + p * k + s] = c;
+    }
+}
+
+int launch_pack_parts(const float* Dparts, const int64_t* Iparts, int nparts, int64_t nq, int k, int metric,
+                      uint64_t* cand, cudaStream_t st) {
+    const int64_t total = (int64_t)nparts * nq * k;
+    if (total <= 0) return 0;
+    int64_t blocks = std::min<int64_t>((total + 255) / 256, 148 * 8);
+    pack_parts_kernel<<<(unsigned)blocks, 256, 0, st>>>(Dparts, Iparts, nparts, nq, k, metric, cand);
+    BFK_CUDA(cudaGetLastError());
+    return 0;
+}
+
+}  // namespace bfk
+
+// Merge step of the row-sharded search.  Scratch: nq*nparts*k composites, allocated per call
+// with the stream-ordered allocator (the payload is tiny; BASELINE config 5).
+extern "C" int bfk_merge_topk(const float* Dparts, const int64_t* Iparts, int nparts, int64_t nq, int64_t k,
+                              int metric, float* D, int64_t* I, int device, void* stream) {
+    using namespace bfk;
+    if (nparts <= 0 || nq < 0 || k <= 0 || k > BFK_MAX_K) return fail("merge_topk: bad arguments");
+    if (nq == 0) return 0;
+    if (!Dparts || !Iparts || !D || !I) return fail("merge_topk: null buffer");
+    if ((int64_t)nparts * k >= (1ll << 32)) return fail("merge_topk: too many candidates per query");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        return fail("no CUDA device available: libbfk has no CPU fallback");
+    }
+    DeviceGuard g(device);
+    cudaStream_t st = (cudaStream_t)stream;
+    uint64_t* cand = nullptr;
+    BFK_CUDA(cudaMallocAsync((void**)&cand, sizeof(uint64_t) * (size_t)nq * nparts * k, st));
+    int rc = launch_pack_parts(Dparts, Iparts, nparts, nq, (int)k, metric, cand, st);
+    if (!rc) {
+        select_topk_kernel<<<(unsigned)nq, SEL_THREADS, 0, st>>>(cand, (int64_t)nparts * k, (int)k, metric, 0, Iparts,
+                                                                k, nq * k, (int)k, D, I, k);
+        if (cudaGetLastError() != cudaSuccess) rc = fail("merge_topk: launch failed");
+    }
+    cudaFreeAsync(cand, st);
+    return rc;
+}

@@ -1,0 +1,139 @@
+/*
+ * bfk.h -- C ABI of libbfk.so: exact brute-force flat kNN (+ pool/normalise) on B200.
+ *
+ * This is the drop-in boundary for the semantic-indexer retrieval hot path of the
+ * DocQA-MS reference.  The reference reaches this path through the SWIG surface of
+ * the third-party faiss-cpu wheel; each entry point below names the reference call
+ * site (file:line under /root/reference) and the faiss symbol it stands in for.
+ * INTEGRATION.md shows the ctypes binding a maintainer adds on the reference side.
+ *
+ * Conventions
+ *   - every function returns 0 on success, non-zero on failure; bfk_last_error()
+ *     then returns a thread-local message (the Python layer raises RuntimeError,
+ *     mirroring faiss's FaissException -> RuntimeError).
+ *   - no CPU fallback exists: without a CUDA device every compute entry point fails.
+ *   - `stream` is a cudaStream_t passed as void* (NULL = the legacy default stream).
+ *   - *_is_device = 0: pointers are host memory, the call copies H2D/D2H on `stream`
+ *     and returns after the results are in the host buffers.
+ *     *_is_device = 1: pointers are device memory on the index's GPU; the call only
+ *     enqueues work on `stream` and returns without synchronising.
+ *   - the index owns all corpus storage; inputs are borrowed for the call; outputs
+ *     are caller-allocated.
+ *   - concurrent bfk_search on one index is serialised internally; bfk_add /
+ *     bfk_remove_ids / bfk_reset must not run concurrently with anything else on
+ *     the same index (same rule as faiss.IndexFlat).
+ */
+#ifndef BFK_H
+#define BFK_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define BFK_METRIC_INNER_PRODUCT 0 /* faiss.METRIC_INNER_PRODUCT */
+#define BFK_METRIC_L2 1            /* faiss.METRIC_L2 (squared distances) */
+
+/* corpus storage: what the index keeps in HBM */
+#define BFK_STORE_F32 0  /* fp32 master rows (+ bf16 scan copy + fp32 norms)           */
+#define BFK_STORE_BF16 1 /* rows rounded to bf16 at add (BASELINE configs 3 and 5)     */
+
+/* element types of encoder outputs / masks handed to the pooling entry points */
+#define BFK_DT_F32 0
+#define BFK_DT_F16 1
+#define BFK_DT_BF16 2
+#define BFK_DT_I64 3
+#define BFK_DT_I32 4
+#define BFK_DT_U8 5
+
+/* search algorithm selector for bfk_search_ex */
+#define BFK_ALGO_AUTO 0
+#define BFK_ALGO_EXACT_SIMT 1  /* fp32 direct-distance scan (faiss's nq<20 arithmetic)  */
+#define BFK_ALGO_TENSOR 2      /* bf16 tcgen05 scan + exact fp32 rerank + certificate   */
+
+#define BFK_MAX_K 2048 /* faiss-cpu has no cap; faiss-gpu's historic cap is 2048 */
+#define BFK_MAX_D 2048
+
+typedef struct bfk_index bfk_index;
+
+typedef struct bfk_search_stats {
+    int32_t algo_used;        /* BFK_ALGO_* actually run for the bulk of the queries   */
+    int32_t n_launches;       /* kernels launched by this call                         */
+    int64_t n_fallback;       /* queries re-run exactly after a failed certificate     */
+    int64_t n_candidates;     /* candidates reranked in fp32 (tensor path)             */
+    float scan_ms;            /* device time of the dominant scan kernel (if timed)    */
+    float reserved;
+} bfk_search_stats;
+
+const char* bfk_last_error(void);
+int bfk_version(void);
+/* number of CUDA devices visible; 0 (and no error) on a machine without a GPU */
+int bfk_device_count(void);
+
+/* faiss.IndexFlatL2(d) / IndexFlatIP(d) -- semantic-indexer/indexer.py:39,104 */
+int bfk_create(int d, int metric, int device, int storage, bfk_index** out);
+int bfk_free(bfk_index* idx);
+
+/* index.d / index.metric_type / index.ntotal -- indexer.py:109, llm-qa/main.py:59 */
+int bfk_dim(const bfk_index* idx);
+int bfk_metric(const bfk_index* idx);
+int bfk_storage(const bfk_index* idx);
+int bfk_device(const bfk_index* idx);
+int64_t bfk_ntotal(const bfk_index* idx);
+
+/* pre-size the corpus storage (no faiss counterpart; avoids regrowth copies) */
+int bfk_reserve(bfk_index* idx, int64_t n);
+
+/* index.add(float32[n, d]) -- indexer.py:41.  Copies; ids are sequential. */
+int bfk_add(bfk_index* idx, const float* x, int64_t n, int x_is_device, void* stream);
+
+/* SentenceTransformer.encode's Pooling(mean)+Normalize tail fused with index.add
+ * -- indexer.py:37 + :41.  tok [B,T,H] (F32/F16/BF16), mask [B,T] (I64/I32/U8),
+ * both device pointers; appends B unit-norm rows. */
+int bfk_add_pooled(bfk_index* idx, const void* tok, int tok_dtype, const void* mask,
+                   int mask_dtype, int64_t B, int T, int H, void* stream);
+
+/* the same pooling without an index: out_f32 [B,H] -- indexer.py:37, llm-qa/main.py:25 */
+int bfk_pool_normalize(const void* tok, int tok_dtype, const void* mask, int mask_dtype,
+                       int64_t B, int T, int H, float* out_f32, int io_is_device, int device,
+                       void* stream);
+
+/* index.search(float32[nq, d], k) -> D float32[nq,k], I int64[nq,k]
+ * -- llm-qa/main.py:101,117 (through langchain_community FAISS).
+ * L2: squared distances ascending; IP: inner products descending; missing
+ * results I = -1, D = +/-FLT_MAX. */
+int bfk_search(bfk_index* idx, const float* q, int64_t nq, int64_t k, float* D, int64_t* I,
+               int io_is_device, void* stream);
+int bfk_search_ex(bfk_index* idx, const float* q, int64_t nq, int64_t k, float* D, int64_t* I,
+                  int io_is_device, void* stream, int algo, int64_t id_offset,
+                  bfk_search_stats* stats);
+
+/* index.reset() / reconstruct / reconstruct_n / remove_ids -- LangChain side paths
+ * on the object built at llm-qa/main.py:53-58 */
+int bfk_reset(bfk_index* idx);
+int bfk_reconstruct(const bfk_index* idx, int64_t i0, int64_t n, float* out, int out_is_device);
+int bfk_remove_ids(bfk_index* idx, const int64_t* ids, int64_t n, int64_t* nremoved);
+
+/* faiss.write_index / read_index -- indexer.py:27,99; llm-qa/main.py:35.
+ * Byte-identical to faiss's IxF2 / IxFI files. */
+int bfk_write(const bfk_index* idx, const char* path);
+int bfk_read(const char* path, int device, int storage, bfk_index** out);
+/* faiss.serialize_index / deserialize_index */
+int64_t bfk_serialized_size(const bfk_index* idx);
+int bfk_serialize(const bfk_index* idx, uint8_t* buf, int64_t buf_len);
+int bfk_deserialize(const uint8_t* buf, int64_t len, int device, int storage, bfk_index** out);
+
+/* faiss.normalize_L2(x): in place, host float32[n, d] (zero rows untouched) */
+int bfk_normalize_l2(float* x, int64_t n, int d, int x_is_device, int device, void* stream);
+
+/* Row-sharded search, merge step (BASELINE config 5; no reference counterpart, the
+ * reference is single-process): Dparts/Iparts [nparts, nq, k] are the per-shard
+ * sorted results after the all-gather; writes the global top-k.  Device pointers. */
+int bfk_merge_topk(const float* Dparts, const int64_t* Iparts, int nparts, int64_t nq, int64_t k,
+                   int metric, float* D, int64_t* I, int device, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* BFK_H */

@@ -1,0 +1,271 @@
+"""Parity of the CUDA flat index (through the C ABI) against the CPU oracle. GPU only."""
+import ctypes
+import os
+
+import numpy as np
+import pytest
+
+from oracle import cpu_baseline, faiss_io, flat_ref
+from tests.parity import check_knn
+
+pytestmark = pytest.mark.gpu
+
+L2, IP = flat_ref.METRIC_L2, flat_ref.METRIC_INNER_PRODUCT
+
+
+def unit(rng, n, d):
+    x = rng.standard_normal((n, d)).astype(np.float32)
+    x /= np.linalg.norm(x, axis=1, keepdims=True)
+    return x
+
+
+@pytest.fixture(scope="module")
+def bfk():
+    import docqa_b200
+
+    assert docqa_b200.get_num_gpus() >= 1, "GPU tests need a CUDA device"
+    return docqa_b200
+
+
+def test_reference_fixture_read_search_write(bfk, golden_dir, fixture_index_bytes, fixture_corpus, tmp_path):
+    """BASELINE config 1: the reference's own 649x384 index, nq=1, k=3 and k=5."""
+    idx = bfk.read_index(os.path.join(golden_dir, "docqa_vector_store.faiss"))
+    assert isinstance(idx, bfk.IndexFlatL2)
+    assert (idx.d, idx.ntotal, idx.metric_type, idx.is_trained) == (384, 649, 1, True)
+    g = np.load(os.path.join(golden_dir, "docqa_search_golden.npz"))
+    q = np.concatenate([fixture_corpus, g["perturbed_queries"]], axis=0)
+    for r in range(q.shape[0]):  # one query per call, like llm-qa/main.py:117
+        k = 3 if r % 2 else 5
+        D, I = idx.search(q[r : r + 1], k)
+        check_knn(D, I, q[r : r + 1], fixture_corpus, k, L2, I_ref=g["I"][r : r + 1, :k],
+                  D_ref64=g["D64"][r : r + 1, :k], tight=True)
+        if r < 649:
+            assert D[0, 0] == 0.0  # direct-difference form: duplicates / self are exactly 0
+    # all 713 queries in one call (exact path explicitly)
+    D, I = idx.search(q, 5, algo="exact")
+    check_knn(D, I, q, fixture_corpus, 5, L2, I_ref=g["I"], D_ref64=g["D64"], tight=True)
+    # and whatever AUTO picks for a batch
+    D, I = idx.search(q, 5)
+    check_knn(D, I, q, fixture_corpus, 5, L2, I_ref=g["I"], D_ref64=g["D64"])
+    # write_index reproduces the reference artefact byte for byte
+    out = tmp_path / "vector_store.faiss"
+    bfk.write_index(idx, str(out))
+    assert out.read_bytes() == fixture_index_bytes
+    assert bfk.serialize_index(idx).tobytes() == fixture_index_bytes
+    idx2 = bfk.deserialize_index(fixture_index_bytes)
+    assert idx2.ntotal == 649 and (idx2.reconstruct_n(0, 649) == fixture_corpus).all()
+
+
+def test_incremental_add_like_the_indexer(bfk, fixture_corpus):
+    """indexer.py:41 adds one (1, 384) row per call; ids are sequential."""
+    idx = bfk.IndexFlatL2(384)
+    assert idx.ntotal == 0
+    for i in range(40):
+        idx.add(np.array(fixture_corpus[i : i + 1]).astype("float32"))
+        assert idx.ntotal == i + 1
+    idx.add(fixture_corpus[40:].astype(np.float64))  # dtype is cast, as faiss's wrapper does
+    assert idx.ntotal == 649
+    assert (idx.reconstruct_n(0, 649) == fixture_corpus).all()
+    assert (idx.reconstruct(648) == fixture_corpus[648]).all()
+    D, I = idx.search(fixture_corpus[100:101], 3)
+    Dr, Ir = flat_ref.knn(fixture_corpus[100:101], fixture_corpus, 3, L2)
+    check_knn(D, I, fixture_corpus[100:101], fixture_corpus, 3, L2, tight=True)
+
+
+@pytest.mark.parametrize("metric", [L2, IP])
+@pytest.mark.parametrize("d", [384, 768, 100, 3, 1])
+@pytest.mark.parametrize("nq", [1, 2, 3, 5, 8, 13])
+def test_exact_path_random(bfk, metric, d, nq):
+    rng = np.random.default_rng(d * 100 + nq + metric)
+    n = 5003
+    xb = unit(rng, n, d) if d > 1 else rng.standard_normal((n, 1)).astype(np.float32)
+    xq = unit(rng, nq, d) if d > 1 else rng.standard_normal((nq, 1)).astype(np.float32)
+    idx = bfk.IndexFlat(d, metric)
+    idx.add(xb)
+    for k in (1, 10, 100):
+        D, I = idx.search(xq, k, algo="exact")
+        check_knn(D, I, xq, xb, k, metric, tight=(metric == L2 or d > 1))
+        Dc, Ic = cpu_baseline.knn_seq(xq, xb, k, metric)
+        assert (I == Ic).mean() > 0.995
+
+
+@pytest.mark.parametrize("metric", [L2, IP])
+def test_edge_cases(bfk, metric):
+    pad = np.float32(3.4028235e38) if metric == L2 else np.float32(-3.4028235e38)
+    rng = np.random.default_rng(5)
+    idx = bfk.IndexFlat(16, metric)
+    # empty index
+    D, I = idx.search(unit(rng, 3, 16), 4)
+    assert D.shape == (3, 4) and (I == -1).all() and (D == pad).all()
+    # zero queries
+    D, I = idx.search(np.zeros((0, 16), np.float32), 4)
+    assert D.shape == (0, 4) and I.shape == (0, 4)
+    # k > ntotal
+    xb = unit(rng, 5, 16)
+    idx.add(xb)
+    xq = unit(rng, 2, 16)
+    D, I = idx.search(xq, 9)
+    check_knn(D, I, xq, xb, 9, metric, tight=True)
+    assert (I[:, 5:] == -1).all() and (D[:, 5:] == pad).all()
+    # caller-provided outputs
+    D2 = np.empty((2, 9), np.float32)
+    I2 = np.empty((2, 9), np.int64)
+    r = idx.search(xq, 9, D=D2, I=I2)
+    assert r[0] is D2 and (I2 == I).all()
+    # argument checks are assertions, like faiss's python wrapper
+    with pytest.raises(AssertionError):
+        idx.search(np.zeros((1, 15), np.float32), 3)
+    with pytest.raises(AssertionError):
+        idx.search(xq, 0)
+    with pytest.raises(AssertionError):
+        idx.add(np.zeros((1, 17), np.float32))
+    with pytest.raises(RuntimeError):
+        idx.search(xq, 5000)  # beyond MAX_K
+    with pytest.raises(RuntimeError):
+        idx.reconstruct(99)
+    with pytest.raises(RuntimeError):
+        idx.add_with_ids(xb, np.arange(5))
+    # maximum k
+    xb2 = unit(rng, 3000, 16)
+    idx.reset()
+    assert idx.ntotal == 0
+    idx.add(xb2)
+    D, I = idx.search(xq, 2048)
+    check_knn(D, I, xq, xb2, 2048, metric)
+
+
+def test_duplicates_and_adversarial_order(bfk):
+    """1% exact duplicates + rows sorted by decreasing distance (every row improves the top-k)."""
+    rng = np.random.default_rng(11)
+    d, n = 64, 20000
+    xb = unit(rng, n, d)
+    dup = rng.integers(0, n, size=200)
+    xb[rng.integers(0, n, size=200)] = xb[dup]
+    q = unit(rng, 4, d)
+    order = np.argsort(-((xb - q[0]) ** 2).sum(1))  # farthest first for query 0
+    xb = np.ascontiguousarray(xb[order])
+    idx = bfk.IndexFlatL2(d)
+    idx.add(xb)
+    for k in (1, 10, 64):
+        D, I = idx.search(q, k, algo="exact")
+        check_knn(D, I, q, xb, k, L2, tight=True)
+    # all-identical corpus: any k ids are right, distances all equal, smallest ids win
+    same = np.repeat(unit(rng, 1, d), 1000, axis=0)
+    idx2 = bfk.IndexFlatL2(d)
+    idx2.add(same)
+    D, I = idx2.search(q[:1], 10)
+    assert I[0].tolist() == list(range(10)) and np.ptp(D) == 0
+
+
+def test_remove_ids_merge_from_reset(bfk):
+    rng = np.random.default_rng(6)
+    xb = unit(rng, 300, 32)
+    idx = bfk.IndexFlatL2(32)
+    ref = flat_ref.IndexFlatRef(32)
+    idx.add(xb)
+    ref.add(xb)
+    ids = np.array([0, 5, 5, 17, 299, 1000, -3], dtype=np.int64)
+    assert idx.remove_ids(ids) == ref.remove_ids(ids) == 4
+    assert idx.ntotal == ref.ntotal == 296
+    assert (idx.reconstruct_n(0, 296) == ref.reconstruct_n(0, 296)).all()
+    q = unit(rng, 3, 32)
+    D, I = idx.search(q, 7)
+    check_knn(D, I, q, ref.reconstruct_n(0, 296), 7, L2, tight=True)
+    other = bfk.IndexFlatL2(32)
+    other.add(xb[:10])
+    idx.merge_from(other)
+    assert idx.ntotal == 306 and other.ntotal == 0
+    assert (idx.reconstruct_n(296, 10) == xb[:10]).all()
+
+
+def test_ip_file_round_trip_and_bf16_storage(bfk, tmp_path):
+    rng = np.random.default_rng(8)
+    xb = unit(rng, 1000, 48)
+    idx = bfk.IndexFlatIP(48)
+    idx.add(xb)
+    p = tmp_path / "ip.faiss"
+    bfk.write_index(idx, str(p))
+    assert p.read_bytes() == faiss_io.write_index_bytes(xb, IP)
+    back = bfk.read_index(str(p))
+    assert isinstance(back, bfk.IndexFlatIP) and back.ntotal == 1000
+    # bf16-stored corpus: the oracle sees the bf16 -> fp32 upcast (BASELINE config 3)
+    import torch
+
+    xb16 = torch.from_numpy(xb).to(torch.bfloat16).to(torch.float32).numpy()
+    idx16 = bfk.IndexFlatIP(48, storage="bf16")
+    idx16.add(xb)
+    assert (idx16.reconstruct_n(0, 1000) == xb16).all()
+    q = unit(rng, 5, 48)
+    D, I = idx16.search(q, 10)
+    check_knn(D, I, q, xb16, 10, IP, tight=True)
+    idx16l2 = bfk.IndexFlatL2(48, storage="bf16")
+    idx16l2.add(xb)
+    D, I = idx16l2.search(q, 10)
+    check_knn(D, I, q, xb16, 10, L2, tight=True)
+
+
+def test_torch_cuda_in_cuda_out(bfk):
+    import torch
+
+    rng = np.random.default_rng(9)
+    xb, q = unit(rng, 4000, 384), unit(rng, 6, 384)
+    idx = bfk.IndexFlatL2(384)
+    idx.add(torch.from_numpy(xb).cuda())
+    D, I = idx.search(torch.from_numpy(q).cuda(), 10)
+    assert D.is_cuda and I.is_cuda and I.dtype == torch.int64
+    check_knn(D.cpu().numpy(), I.cpu().numpy(), q, xb, 10, L2, tight=True)
+    # id_offset (used by the row-sharded index) shifts ids but not the -1 padding
+    D2, I2 = idx.search(q[:1], 10, id_offset=1000)
+    assert (I2 == I[:1].cpu().numpy() + 1000).all()
+
+
+def test_faiss_shim_runs_the_indexer_call_sequence(bfk, fixture_corpus, tmp_path):
+    """`import faiss` -> this library; then indexer.py:39-41,27,99 and llm-qa/main.py:35,101."""
+    bfk.install_as_faiss(force=True)
+    import faiss
+
+    index = faiss.IndexFlatL2(384)
+    for i in range(5):
+        index.add(np.array(fixture_corpus[i : i + 1]).astype("float32"))
+    path = str(tmp_path / "vector_store.faiss")
+    faiss.write_index(index, path)
+    raw_index = faiss.read_index(path)
+    assert raw_index.ntotal == 5
+    vector = np.array([fixture_corpus[3].tolist()], dtype=np.float32)  # LangChain's call shape
+    scores, indices = raw_index.search(vector, 3)
+    assert indices[0][0] == 3 and scores[0][0] == 0.0
+
+
+def test_full_size_properties_1m_x_384(bfk):
+    """BASELINE config 2 at full size: oracle on a query subsample + size-independent properties."""
+    import torch
+
+    n, d, k = 1_000_000, 384, 10
+    g = torch.Generator(device="cuda").manual_seed(1234)
+    xb = torch.randn((n, d), generator=g, device="cuda", dtype=torch.float32)
+    xb /= xb.norm(dim=1, keepdim=True)
+    g2 = torch.Generator(device="cuda").manual_seed(4321)
+    q = torch.randn((64, d), generator=g2, device="cuda", dtype=torch.float32)
+    q /= q.norm(dim=1, keepdim=True)
+    idx = bfk.IndexFlatL2(d)
+    idx.add(xb)
+    assert idx.ntotal == n
+    D, I = idx.search(q, k)
+    D, I = D.cpu().numpy(), I.cpu().numpy()
+    xb_h, q_h = xb.cpu().numpy(), q.cpu().numpy()
+    # oracle (threaded C restatement) on 8 of the queries
+    Dc, Ic = cpu_baseline.knn(q_h[:8], xb_h, k, L2)
+    assert (I[:8] == Ic).all()
+    np.testing.assert_allclose(D[:8], Dc, rtol=1e-3, atol=1e-6)
+    # properties: sorted, in range, unique, distances recomputable from the ids
+    assert (np.diff(D, axis=1) >= 0).all() and I.min() >= 0 and I.max() < n
+    assert all(len(set(r)) == k for r in I.tolist())
+    rec = ((xb_h[I.reshape(-1)].reshape(64, k, d) - q_h[:, None, :]) ** 2).sum(-1)
+    np.testing.assert_allclose(D, rec, rtol=1e-3, atol=1e-6)
+    # querying with corpus rows returns the row itself at distance 0
+    rows = torch.tensor([0, 123456, n - 1], device="cuda")
+    D0, I0 = idx.search(xb[rows], 1)
+    assert I0.flatten().tolist() == rows.tolist() and (D0 == 0).all()
+    # nq=1 and nq=64 agree with each other
+    D1, I1 = idx.search(q[:1], k)
+    assert (I1.cpu().numpy() == I[:1]).all()
