@@ -38,7 +38,7 @@ EXPORTS = [
     "bfk_metric", "bfk_storage", "bfk_device", "bfk_ntotal", "bfk_reserve", "bfk_add",
     "bfk_add_pooled", "bfk_pool_normalize", "bfk_search", "bfk_search_ex", "bfk_reset",
     "bfk_reconstruct", "bfk_remove_ids", "bfk_write", "bfk_read", "bfk_serialized_size",
-    "bfk_serialize", "bfk_deserialize", "bfk_normalize_l2", "bfk_merge_topk",
+    "bfk_serialize", "bfk_deserialize", "bfk_normalize_l2", "bfk_merge_topk", "bfk_search_noalloc",
 ]
 
 _lib = None
@@ -83,6 +83,7 @@ def load() -> ctypes.CDLL:
     L.bfk_deserialize.argtypes = [vp, i64, i32, i32, ctypes.POINTER(vp)]
     L.bfk_normalize_l2.argtypes = [vp, i64, i32, i32, i32, vp]
     L.bfk_merge_topk.argtypes = [vp, vp, i32, i64, i64, i32, vp, vp, i32, vp]
+    L.bfk_search_noalloc.argtypes = [vp, vp, i64, i64, vp, vp, vp]
     _lib = L
     return L
 

@@ -133,6 +133,19 @@ int bfk_normalize_l2(float* x, int64_t n, int d, int x_is_device, int device, vo
 int bfk_merge_topk(const float* Dparts, const int64_t* Iparts, int nparts, int64_t nq, int64_t k,
                    int metric, float* D, int64_t* I, int device, void* stream);
 
+/* Exact search that allocates nothing (no counterpart in the reference, whose faiss-cpu
+ * index simply mallocs).  For callers that must not call cudaMalloc once they are running:
+ * processes that gave all of HBM to their own pool at start-up, request handlers that cannot
+ * take the driver's allocation lock, threads that only hold pre-registered buffers.  Same
+ * results as bfk_search_ex(..., BFK_ALGO_EXACT_SIMT) for nq <= 8 and k <= 128; q, D, I are
+ * DEVICE pointers on the index's GPU (q row stride = d); work is only enqueued on `stream`.
+ * Scratch is a fixed 1.25 MiB array inside the library image (held by every GPU that loads
+ * libbfk.so until exit) shared by all calls on that GPU: calls that overlap on the GPU race;
+ * calls on one stream do not.  The first call on each device resolves the array's device
+ * address -- make it before any stream capture.  Larger nq / k / SM counts are rejected. */
+int bfk_search_noalloc(const bfk_index* idx, const float* q_dev, int64_t nq, int64_t k, float* D_dev,
+                       int64_t* I_dev, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
