@@ -111,8 +111,9 @@ int launch_pack_parts(const float* Dparts, const int64_t* Iparts, int nparts, in
 // K3b + K5 (tensor path); defined in bfk_scan_tc.cu
 int tensor_path_supported(const bfk_index* idx, int64_t nq, int k);
 size_t tensor_workspace_bytes(const bfk_index* idx, int64_t nq, int k);
-int search_tensor(bfk_index* idx, const float* q_dev, int64_t nq, int k, float* D_dev, int64_t* I_dev,
-                  int64_t id_offset, cudaStream_t st, bfk_search_stats* stats);
+int search_tensor(bfk_index* idx, const float* q_dev, int ldq, int64_t nq, int k, float* D_dev, int64_t* I_dev,
+                  int64_t id_offset, char* ws_tail, size_t ws_tail_bytes, cudaStream_t st,
+                  bfk_search_stats* stats, cudaEvent_t ev0, cudaEvent_t ev1);
 
 // ---- device helpers ---------------------------------------------------------
 // order-preserving map float -> uint32 (smaller float <=> smaller uint)

@@ -447,9 +447,7 @@ int bfk_search_ex(bfk_index* idx, const float* q, int64_t nq, int64_t k64, float
     }
     int rc;
     if (algo == BFK_ALGO_TENSOR) {
-        if (stats) cudaEventRecord(ev0, st);
-        rc = search_tensor(idx, q_dev, nq, k, D_out, I_out, id_offset, st, stats);
-        if (stats) cudaEventRecord(ev1, st);
+        rc = search_tensor(idx, q_dev, ldq, nq, k, D_out, I_out, id_offset, tail, tail_avail, st, stats, ev0, ev1);
     } else {
         rc = search_exact(idx, q_dev, ldq, nq, k, D_out, I_out, id_offset, tail, tail_avail, st, stats, ev0, ev1);
     }

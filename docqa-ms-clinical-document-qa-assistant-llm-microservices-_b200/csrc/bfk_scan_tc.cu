@@ -1,9 +1,684 @@
-// placeholder until the tcgen05 path lands
+// K3b `scan_tc_kernel` + K5 `rerank_kernel`: the tensor-core search path.
+//
+// Stands in for faiss IndexFlat::search's BLAS path (knn_L2sqr -> exhaustive_L2sqr_blas:
+// sgemm + ||x||^2 + ||y||^2 - 2<x,y>, reached from llm-qa/main.py:101,117 when a batch of
+// queries is searched) -- restructured for B200: the contraction runs on tcgen05 with a bf16
+// scan copy of the corpus, selection is fused into the epilogue, and the survivors are
+// re-scored exactly in fp32 with faiss's nq<20 arithmetic (direct sum((x-y)^2)).
+//
+// K3b (one CTA per SM, 8 warps, queries on M, corpus rows on N):
+//   warp 0  TMA producer: the 128-query tile is loaded once (KB boxes of 64x128, SWIZZLE_128B)
+//           and stays resident; corpus tiles stream as 64x256 boxes through an mbarrier ring
+//   warp 1  one thread issues tcgen05.mma kind::f16 (bf16 x bf16 -> fp32), M=128 N=256 K=16,
+//           4 per K-block; tcgen05.commit frees the smem stage / publishes the accumulator
+//   warp 2  TMEM allocator (512 columns = two 128x256 fp32 accumulators, double buffered)
+//   warps 4-7  epilogue, thread == query row: tcgen05.ld 32x32b.x32, key = ||x||^2 - 2*acc (L2)
+//           or -acc (IP) with the bias staged in smem, compare against the thread's threshold,
+//           append survivors to a per-thread pending list (coalesced [slot][thread] layout in
+//           global scratch); when a list fills, the warp flushes: every thread bubbles its own
+//           pending entries into a register-resident sorted top-KP, and the threshold tightens
+//   CTA c works on query tile c % QT and corpus stream c / QT (a contiguous range of tiles), so
+//   CTAs sharing a stream walk the same corpus rows together and share them through L2.
+// Output per (query, stream): the KP best approximate keys + T = the KP-th key (every row the
+//   stream dropped has approximate key >= T).
+//
+// K5 (one CTA per query): merge the streams' lists by approximate key; A_k = k-th best;
+//   everything with key <= A_k + 2*eps is re-scored exactly from the stored rows; eps bounds
+//   |approximate - exact| from bf16 rounding: |<q,x> - <bf16 q, bf16 x>| <= (2^-8+) ||q|| ||x||.
+//   The answer is certified exact when no dropped row can reach the cut (min_s T_s > A_k + 2*eps
+//   and the re-score window was not exhausted); uncertified queries are flagged and re-run
+//   through the exact scan K3a on the GPU -- never on the CPU.
+//
+// Roofline: HBM-bound while nq <~ 128 (2 bytes/element scanned, one pass per call); tensor-bound
+// at large nq.  Algorithmic bytes per launch: N*ld16*2 + N*4 (norms, L2) + nq*d*2 + lists.
+#include <cuda.h>
+
+#include <cfloat>
+#include <vector>
+
 #include "bfk_common.cuh"
+#include "bfk_ptx.cuh"
+
 namespace bfk {
-int tensor_path_supported(const bfk_index*, int64_t, int) { return 0; }
-size_t tensor_workspace_bytes(const bfk_index*, int64_t, int) { return 0; }
-int search_tensor(bfk_index*, const float*, int64_t, int, float*, int64_t*, int64_t, cudaStream_t, bfk_search_stats*) {
-    return fail("tensor path not built");
+
+constexpr int TC_BM = 128;
+constexpr int TC_BN = 256;
+constexpr int TC_THREADS = 256;
+constexpr int TC_A_BLOCK = TC_BM * 128;  // bytes of one 64-column K-block of the query tile
+constexpr int TC_B_BLOCK = TC_BN * 128;  // bytes of one 64-column K-block of a corpus tile
+constexpr int TC_MAX_STAGES = 8;
+constexpr int TC_BUFCAP = 64;            // pending slots per epilogue thread
+constexpr int TC_SMEM_LIMIT = 232448;    // 227 KiB
+constexpr int TC_RMAX = 64;              // exact re-scores per query at most
+constexpr int TC_MERGE_N = 4096;
+constexpr int TC_TAIL_BYTES = 2 * TC_BN * 4 + (2 * TC_MAX_STAGES + 5) * 8 + 16;  // bias + barriers + tmem slot
+
+struct TcParams {
+    const float* nrm;
+    int64_t n;
+    int KB;
+    int QT;
+    int S;
+    int64_t tiles_total;
+    int smem_bytes;      // dynamic shared memory given to the launch
+    int is_l2;
+    int nq;
+    uint64_t* pend;      // [grid][TC_BUFCAP][128]
+    uint64_t* out_cand;  // [QT*128][S][KP]
+    float* out_thr;      // [QT*128][S]
+};
+
+__device__ __forceinline__ void epi_sync() { asm volatile("bar.sync 2, 128;" ::: "memory"); }
+
+template <int KP>
+__global__ void __launch_bounds__(TC_THREADS, 1)
+scan_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmX, const TcParams p) {
+    extern __shared__ __align__(1024) unsigned char smem_raw[];
+    const uint32_t raw_addr = smem_u32(smem_raw);
+    const uint32_t pad = (1024u - (raw_addr & 1023u)) & 1023u;  // 0 when the base is already 1 KiB aligned
+    unsigned char* smem = smem_raw + pad;
+    // stages: whatever fits after the resident query tile and the fixed tail (host sizes for pad = 0;
+    // a misaligned base just costs one stage)
+    const int stages = min(TC_MAX_STAGES, (int)((p.smem_bytes - (int)pad - p.KB * TC_A_BLOCK - TC_TAIL_BYTES) / TC_B_BLOCK));
+    unsigned char* sA = smem;
+    unsigned char* sB = sA + (size_t)p.KB * TC_A_BLOCK;
+    float* bias_s = reinterpret_cast<float*>(sB + (size_t)stages * TC_B_BLOCK);
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(bias_s + 2 * TC_BN);
+    uint64_t* empty_bar = full_bar + TC_MAX_STAGES;
+    uint64_t* q_bar = empty_bar + TC_MAX_STAGES;
+    uint64_t* tfull_bar = q_bar + 1;   // [2]
+    uint64_t* tempty_bar = tfull_bar + 2;  // [2]
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int qt = blockIdx.x % p.QT;
+    const int s = blockIdx.x / p.QT;
+    const int64_t t_begin = p.tiles_total * s / p.S;
+    const int64_t t_end = p.tiles_total * (s + 1) / p.S;
+
+    if (tid == 0) {
+        for (int i = 0; i < stages; i++) {
+            mbar_init(&full_bar[i], 1);
+            mbar_init(&empty_bar[i], 1);
+        }
+        mbar_init(q_bar, 1);
+        for (int a = 0; a < 2; a++) {
+            mbar_init(&tfull_bar[a], 1);
+            mbar_init(&tempty_bar[a], 128);
+        }
+        fence_mbar_init();
+    }
+    if (warp == 2) tmem_alloc<512>(tmem_slot);
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmQ);
+        tma_prefetch_desc(&tmX);
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(tmem_slot);
+
+    if (warp == 0) {
+        // ===================== TMA producer =====================
+        if (lane == 0) {
+            mbar_expect_tx(q_bar, (uint32_t)p.KB * TC_A_BLOCK);
+            for (int kb = 0; kb < p.KB; kb++) tma_load_2d(sA + (size_t)kb * TC_A_BLOCK, &tmQ, kb * 64, qt * TC_BM, q_bar);
+            uint32_t it = 0;
+            for (int64_t t = t_begin; t < t_end; t++) {
+                for (int kb = 0; kb < p.KB; kb++, it++) {
+                    const int st = it % stages;
+                    const uint32_t ph = (it / stages) & 1u;
+                    mbar_wait(&empty_bar[st], ph ^ 1u);
+                    mbar_expect_tx(&full_bar[st], TC_B_BLOCK);
+                    tma_load_2d(sB + (size_t)st * TC_B_BLOCK, &tmX, kb * 64, (int)(t * TC_BN), &full_bar[st]);
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===================== MMA issuer (one thread) =====================
+        if (lane == 0) {
+            const uint32_t idesc = make_idesc_bf16(TC_BM, TC_BN);
+            const uint32_t a_base = smem_u32(sA), b_base = smem_u32(sB);
+            mbar_wait(q_bar, 0);
+            uint32_t it = 0, tcount = 0;
+            for (int64_t t = t_begin; t < t_end; t++, tcount++) {
+                const uint32_t a = tcount & 1u, aph = (tcount >> 1) & 1u;
+                mbar_wait(&tempty_bar[a], aph ^ 1u);  // epilogue has drained this accumulator
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + a * TC_BN;
+                for (int kb = 0; kb < p.KB; kb++, it++) {
+                    const int st = it % stages;
+                    const uint32_t ph = (it / stages) & 1u;
+                    mbar_wait(&full_bar[st], ph);
+                    tc_fence_after();
+#pragma unroll
+                    for (int kk = 0; kk < 4; kk++) {
+                        const uint64_t da = make_smem_desc_sw128(a_base + kb * TC_A_BLOCK + kk * 32);
+                        const uint64_t db = make_smem_desc_sw128(b_base + st * TC_B_BLOCK + kk * 32);
+                        umma_bf16(d_tmem, da, db, idesc, (kb | kk) != 0 ? 1u : 0u);
+                    }
+                    umma_commit(&empty_bar[st]);  // smem stage reusable once these MMAs retire
+                }
+                umma_commit(&tfull_bar[a]);  // accumulator complete
+            }
+        }
+    } else if (warp >= 4) {
+        // ===================== epilogue: thread == query row =====================
+        const int et = tid - 128;
+        const int qrow = qt * TC_BM + et;
+        const bool active = qrow < p.nq;
+        float skey[KP];
+        uint32_t sidx[KP];
+#pragma unroll
+        for (int i = 0; i < KP; i++) {
+            skey[i] = FLT_MAX;
+            sidx[i] = 0xffffffffu;
+        }
+        float thr = FLT_MAX;
+        int cnt = 0;
+        uint64_t* my_pend = p.pend + (size_t)blockIdx.x * TC_BUFCAP * 128 + et;
+        const float scale = p.is_l2 ? -2.0f : -1.0f;
+
+        auto flush = [&]() {
+            const int maxc = __reduce_max_sync(0xffffffffu, cnt);
+#pragma unroll 4
+            for (int i = 0; i < maxc; i++) {
+                const bool has = i < cnt;
+                const uint64_t e = has ? my_pend[(size_t)i * 128] : 0ull;
+                float x = __uint_as_float((uint32_t)(e >> 32));
+                uint32_t xi = (uint32_t)e;
+                if (has && x < skey[KP - 1]) {
+#pragma unroll
+                    for (int j = 0; j < KP; j++) {
+                        const bool sw = x < skey[j];
+                        const float tk = skey[j];
+                        const uint32_t ti = sidx[j];
+                        skey[j] = sw ? x : tk;
+                        sidx[j] = sw ? xi : ti;
+                        x = sw ? tk : x;
+                        xi = sw ? ti : xi;
+                    }
+                }
+            }
+            cnt = 0;
+            thr = skey[KP - 1];
+        };
+
+        uint32_t tcount = 0;
+        for (int64_t t = t_begin; t < t_end; t++, tcount++) {
+            const uint32_t a = tcount & 1u, aph = (tcount >> 1) & 1u;
+            for (int j = et; j < TC_BN; j += 128) {
+                const int64_t col = t * TC_BN + j;
+                bias_s[a * TC_BN + j] = (col < p.n) ? (p.is_l2 ? __ldg(p.nrm + col) : 0.f) : INFINITY;
+            }
+            epi_sync();
+            mbar_wait(&tfull_bar[a], aph);
+            tc_fence_after();
+            const uint32_t taddr = tmem_base + ((uint32_t)((warp - 4) * 32) << 16) + a * TC_BN;
+            const uint32_t col0 = (uint32_t)(t * TC_BN);
+            for (int c0 = 0; c0 < TC_BN; c0 += 32) {
+                uint32_t r[32];
+                tmem_ld_32x32(taddr + c0, r);
+                tmem_ld_wait();
+                const float4* b4 = reinterpret_cast<const float4*>(bias_s + a * TC_BN + c0);
+#pragma unroll
+                for (int j4 = 0; j4 < 8; j4++) {
+                    const float4 b = b4[j4];
+                    const float bb[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+                    for (int e = 0; e < 4; e++) {
+                        const float key = fmaf(scale, __uint_as_float(r[4 * j4 + e]), bb[e]);
+                        if (active && key < thr) {
+                            my_pend[(size_t)cnt * 128] =
+                                ((uint64_t)__float_as_uint(key) << 32) | (uint64_t)(col0 + c0 + 4 * j4 + e);
+                            cnt++;
+                        }
+                    }
+                }
+                if (__any_sync(0xffffffffu, cnt > TC_BUFCAP - 32)) flush();
+            }
+            tc_fence_before();
+            mbar_arrive(&tempty_bar[a]);
+        }
+        flush();
+        if (active) {
+            uint64_t* dst = p.out_cand + ((size_t)qrow * p.S + s) * KP;
+#pragma unroll
+            for (int i = 0; i < KP; i++) dst[i] = (sidx[i] == 0xffffffffu) ? COMP_EMPTY : make_comp(skey[i], sidx[i]);
+            p.out_thr[(size_t)qrow * p.S + s] = skey[KP - 1];
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 2) {
+        tc_fence_after();
+        tmem_dealloc<512>(tmem_base);
+    }
 }
+
+// queries fp32 [nq, ldq] -> bf16 [nq_pad, ld16] (zero padded rows and columns) + ||q||^2
+__global__ void __launch_bounds__(256) prep_queries_kernel(const float* __restrict__ q, int ldq, int d, int64_t nq,
+                                                           int64_t nq_pad, __nv_bfloat16* __restrict__ q16, int ld16,
+                                                           float* __restrict__ qn) {
+    const int lane = threadIdx.x & 31;
+    const int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (row >= nq_pad) return;
+    float ss = 0.f;
+    for (int c = lane; c < ld16; c += 32) {
+        float v = (row < nq && c < d) ? q[row * ldq + c] : 0.f;
+        ss += v * v;
+        q16[row * ld16 + c] = __float2bfloat16_rn(v);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
+    if (lane == 0) qn[row] = ss;
 }
+
+struct RerankParams {
+    const uint64_t* out_cand;  // [nq_pad][S][KP]
+    const float* out_thr;      // [nq_pad][S]
+    const float* qn;           // [nq_pad]
+    const float* q;            // [nq][ldq] fp32
+    int ldq;
+    int S;
+    int KP;
+    int k;
+    int is_l2;
+    int storage;
+    const float* x32;
+    int ld32;
+    const __nv_bfloat16* x16;
+    int ld16;
+    int d;
+    const unsigned int* maxn;
+    float c_round;             // relative bound on the bf16 inner-product error
+    int64_t id_offset;
+    float* D;                  // [nq][k]
+    int64_t* I;
+    int* nflag;
+    int* flag_list;
+};
+
+__device__ void rr_bitonic(uint64_t* a, int n, int tid, int nthr) {
+    for (int k2 = 2; k2 <= n; k2 <<= 1) {
+        for (int j = k2 >> 1; j > 0; j >>= 1) {
+            for (int i = tid; i < (n >> 1); i += nthr) {
+                int lo = ((i & ~(j - 1)) << 1) | (i & (j - 1));
+                int hi = lo + j;
+                bool asc = (lo & k2) == 0;
+                uint64_t x = a[lo], y = a[hi];
+                if ((x > y) == asc) {
+                    a[lo] = y;
+                    a[hi] = x;
+                }
+            }
+            __syncthreads();
+        }
+    }
+}
+
+__global__ void __launch_bounds__(256) rerank_kernel(const RerankParams p) {
+    __shared__ uint64_t buf[TC_MERGE_N];
+    __shared__ uint64_t ex[TC_RMAX];
+    __shared__ float q_s[BFK_MAX_D];
+    __shared__ float red[8];
+    __shared__ int info[4];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int64_t q = blockIdx.x;
+    const int64_t M = (int64_t)p.S * p.KP;
+    const uint64_t* src = p.out_cand + q * M;
+
+    for (int c = tid; c < p.ld32; c += 256) q_s[c] = (c < p.ldq) ? p.q[q * p.ldq + c] : 0.f;
+    // min over streams of the drop threshold
+    float tmin = FLT_MAX;
+    for (int s = tid; s < p.S; s += 256) tmin = fminf(tmin, p.out_thr[q * p.S + s]);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) tmin = fminf(tmin, __shfl_xor_sync(0xffffffffu, tmin, o));
+    if (lane == 0) red[warp] = tmin;
+
+    // ---- merge by approximate key: the best TC_RMAX end up sorted at the front of buf ----
+    int window;
+    if (M <= TC_MERGE_N) {
+        int n = TC_RMAX;
+        while (n < M) n <<= 1;
+        for (int i = tid; i < n; i += 256) buf[i] = (i < M) ? src[i] : COMP_EMPTY;
+        __syncthreads();
+        rr_bitonic(buf, n, tid, 256);
+        window = n;
+    } else {
+        const int step = TC_MERGE_N - TC_RMAX;
+        for (int i = tid; i < TC_RMAX; i += 256) buf[i] = COMP_EMPTY;
+        for (int64_t base = 0; base < M; base += step) {
+            for (int i = tid; i < step; i += 256) buf[TC_RMAX + i] = (base + i < M) ? src[base + i] : COMP_EMPTY;
+            __syncthreads();
+            rr_bitonic(buf, TC_MERGE_N, tid, 256);
+        }
+        window = TC_MERGE_N;
+    }
+    (void)window;
+    tmin = fminf(fminf(fminf(red[0], red[1]), fminf(red[2], red[3])), fminf(fminf(red[4], red[5]), fminf(red[6], red[7])));
+
+    // ---- the cut: A_k + 2*eps in approximate-key space ----
+    if (tid == 0) {
+        int nvalid = 0;
+        while (nvalid < TC_RMAX && buf[nvalid] != COMP_EMPTY) nvalid++;
+        int R = 0;
+        int certified = 1;
+        if (nvalid > 0) {
+            const int kk = min(p.k, nvalid);
+            const float a_k = ord2f((uint32_t)(buf[kk - 1] >> 32));
+            const float qn = p.qn[q];
+            const float maxn = __uint_as_float(*p.maxn);
+            const float eps_ip = p.c_round * sqrtf(qn * maxn);
+            const float margin = (p.is_l2 ? 4.f : 2.f) * eps_ip + 1e-6f * (qn + maxn);
+            const float cut = a_k + margin;
+            while (R < nvalid && ord2f((uint32_t)(buf[R] >> 32)) <= cut) R++;
+            if (R < kk) R = kk;
+            // rows a stream dropped have approximate key >= its T; rows beyond the window >= buf[RMAX-1]
+            if (!(tmin > cut)) certified = 0;
+            if (R == TC_RMAX && M > TC_RMAX) certified = 0;
+        }
+        info[0] = R;
+        info[1] = certified;
+    }
+    for (int i = tid; i < TC_RMAX; i += 256) ex[i] = COMP_EMPTY;
+    __syncthreads();
+    const int R = info[0];
+
+    // ---- exact re-score of the R survivors (faiss's direct-difference arithmetic) ----
+    for (int i = warp; i < R; i += 8) {
+        const uint32_t id = (uint32_t)(buf[i] & 0xffffffffu);
+        float acc = 0.f;
+        if (p.storage == BFK_STORE_F32) {
+            const float4* row = reinterpret_cast<const float4*>(p.x32 + (size_t)id * p.ld32);
+            for (int c = lane; c < (p.ld32 >> 2); c += 32) {
+                const float4 x = __ldg(row + c);
+                const float4 y = *reinterpret_cast<const float4*>(q_s + 4 * c);
+                if (p.is_l2) {
+                    float t0 = x.x - y.x, t1 = x.y - y.y, t2 = x.z - y.z, t3 = x.w - y.w;
+                    acc = fmaf(t0, t0, acc); acc = fmaf(t1, t1, acc); acc = fmaf(t2, t2, acc); acc = fmaf(t3, t3, acc);
+                } else {
+                    acc = fmaf(x.x, y.x, acc); acc = fmaf(x.y, y.y, acc); acc = fmaf(x.z, y.z, acc); acc = fmaf(x.w, y.w, acc);
+                }
+            }
+        } else {
+            const __nv_bfloat16* row = p.x16 + (size_t)id * p.ld16;
+            for (int c = lane; c < p.d; c += 32) {
+                const float x = __bfloat162float(row[c]);
+                const float y = q_s[c];
+                if (p.is_l2) {
+                    float t0 = x - y;
+                    acc = fmaf(t0, t0, acc);
+                } else {
+                    acc = fmaf(x, y, acc);
+                }
+            }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+        if (lane == 0) {
+            const float key = p.is_l2 ? acc : -acc;
+            ex[i] = (key < FLT_MAX) ? make_comp(key, id) : COMP_EMPTY;
+        }
+    }
+    __syncthreads();
+    rr_bitonic(ex, TC_RMAX, tid, 256);
+    for (int i = tid; i < p.k; i += 256) {
+        const uint64_t c = (i < TC_RMAX) ? ex[i] : COMP_EMPTY;
+        float dv;
+        int64_t iv;
+        if (c == COMP_EMPTY) {
+            dv = p.is_l2 ? FLT_MAX : -FLT_MAX;
+            iv = -1;
+        } else {
+            const float key = ord2f((uint32_t)(c >> 32));
+            dv = p.is_l2 ? key : -key;
+            iv = (int64_t)(c & 0xffffffffu) + p.id_offset;
+        }
+        p.D[q * p.k + i] = dv;
+        p.I[q * p.k + i] = iv;
+    }
+    if (tid == 0 && !info[1]) {
+        const int slot = atomicAdd(p.nflag, 1);
+        p.flag_list[slot] = (int)q;
+    }
+}
+
+// ---- host side -------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn() {
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+            qres == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(p);
+        else
+            cudaGetLastError();
+    }
+    return fn;
+}
+
+// bf16 matrix [rows, ld] row-major; box = 64 columns x box_rows, 128-byte swizzle, OOB rows read as 0
+static int make_tmap(CUtensorMap* m, const void* base, int64_t rows, int ld, int box_rows) {
+    EncodeTiledFn enc = get_encode_fn();
+    if (!enc) return fail("cuTensorMapEncodeTiled is not available from this driver");
+    cuuint64_t gdim[2] = {(cuuint64_t)ld, (cuuint64_t)std::max<int64_t>(rows, 1)};
+    cuuint64_t gstr[1] = {(cuuint64_t)ld * 2};
+    cuuint32_t box[2] = {64, (cuuint32_t)box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstr, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail("cuTensorMapEncodeTiled failed with code " + std::to_string((int)r));
+    return 0;
+}
+
+struct TcPlan {
+    int KB, stages, QT, S, KP, grid;
+    int64_t nq_pad, tiles_total;
+    size_t smem;
+};
+
+static int tc_plan(const bfk_index* idx, int64_t nq, int k, TcPlan* pl) {
+    pl->KB = idx->ld16 / 64;
+    const size_t fixed = (size_t)pl->KB * TC_A_BLOCK + TC_TAIL_BYTES;
+    if (fixed + 1024 + 2 * (size_t)TC_B_BLOCK > TC_SMEM_LIMIT) return 1;  // query tile cannot stay resident
+    pl->stages = (int)std::min<size_t>(TC_MAX_STAGES, (TC_SMEM_LIMIT - fixed) / TC_B_BLOCK);
+    pl->smem = fixed + (size_t)pl->stages * TC_B_BLOCK;
+    pl->QT = (int)((nq + TC_BM - 1) / TC_BM);
+    pl->nq_pad = (int64_t)pl->QT * TC_BM;
+    pl->tiles_total = (idx->ntotal + TC_BN - 1) / TC_BN;
+    pl->S = (int)std::max<int64_t>(1, std::min<int64_t>(idx->num_sms / pl->QT, pl->tiles_total));
+    pl->grid = pl->QT * pl->S;
+    pl->KP = (k <= 16 && pl->S >= 8) ? 16 : 32;
+    return 0;
+}
+
+static int64_t tc_chunk_queries(const bfk_index* idx) { return (int64_t)idx->num_sms * TC_BM; }
+
+int tensor_path_supported(const bfk_index* idx, int64_t nq, int k) {
+    if (k > 32 || nq <= 0 || idx->ntotal <= 0) return 0;
+    TcPlan pl;
+    if (tc_plan(idx, std::min<int64_t>(nq, tc_chunk_queries(idx)), k, &pl)) return 0;
+    return get_encode_fn() != nullptr;
+}
+
+struct TcWs {
+    __nv_bfloat16* q16;
+    float* qn;
+    uint64_t* pend;
+    uint64_t* out_cand;
+    float* out_thr;
+    int* flags;      // [0] = count, [1..] = list
+    float* fb_q;     // [8][ldq] compacted fallback queries
+    float* fb_D;     // [8][k]
+    int64_t* fb_I;   // [8][k]
+    uint64_t* fb_part;
+    size_t bytes;
+};
+
+static void tc_carve(const bfk_index* idx, int64_t nqc, int k, const TcPlan& pl, int fb_nparts, char* base, TcWs* w) {
+    size_t off = 0;
+    auto take = [&](size_t bytes) {
+        off = (size_t)round_up((int64_t)off, 256);
+        char* p = base ? base + off : nullptr;
+        off += bytes;
+        return p;
+    };
+    w->q16 = (__nv_bfloat16*)take((size_t)pl.nq_pad * idx->ld16 * 2);
+    w->qn = (float*)take((size_t)pl.nq_pad * 4);
+    w->pend = (uint64_t*)take((size_t)pl.grid * TC_BUFCAP * 128 * 8);
+    w->out_cand = (uint64_t*)take((size_t)pl.nq_pad * pl.S * pl.KP * 8);
+    w->out_thr = (float*)take((size_t)pl.nq_pad * pl.S * 4);
+    w->flags = (int*)take((size_t)(nqc + 1) * 4);
+    w->fb_q = (float*)take((size_t)8 * idx->ld32 * 4);
+    w->fb_D = (float*)take((size_t)8 * k * 4);
+    w->fb_I = (int64_t*)take((size_t)8 * k * 8);
+    w->fb_part = (uint64_t*)take((size_t)8 * fb_nparts * k * 8);
+    w->bytes = off + 256;
+}
+
+size_t tensor_workspace_bytes(const bfk_index* idx, int64_t nq, int k) {
+    const int64_t nqc = std::min<int64_t>(nq, tc_chunk_queries(idx));
+    TcPlan pl;
+    if (tc_plan(idx, nqc, k, &pl)) return 0;
+    size_t sb = 0;
+    int nparts = 0;
+    if (scan_exact_workspace(idx, 8, k, &sb, &nparts)) return 0;
+    TcWs w;
+    tc_carve(idx, nqc, k, pl, nparts, nullptr, &w);
+    return w.bytes;
+}
+
+template <int KP>
+static int launch_scan_tc(const CUtensorMap& tmQ, const CUtensorMap& tmX, const TcParams& p, const TcPlan& pl,
+                          cudaStream_t st) {
+    auto kern = scan_tc_kernel<KP>;
+    static bool attr_set = false;
+    if (!attr_set) {
+        BFK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_LIMIT));
+        attr_set = true;
+    }
+    kern<<<pl.grid, TC_THREADS, pl.smem, st>>>(tmQ, tmX, p);
+    BFK_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int search_tensor(bfk_index* idx, const float* q_dev, int ldq, int64_t nq, int k, float* D_dev, int64_t* I_dev,
+                  int64_t id_offset, char* ws_tail, size_t ws_tail_bytes, cudaStream_t st, bfk_search_stats* stats,
+                  cudaEvent_t ev0, cudaEvent_t ev1) {
+    const int64_t chunk = tc_chunk_queries(idx);
+    int launches = 0;
+    int64_t n_fallback = 0;
+    int fb_nparts = 0;
+    size_t sb = 0;
+    BFK_TRY(scan_exact_workspace(idx, 8, k, &sb, &fb_nparts));
+    const bool l2 = idx->metric == BFK_METRIC_L2;
+    for (int64_t q0 = 0; q0 < nq; q0 += chunk) {
+        const int64_t nqc = std::min(chunk, nq - q0);
+        TcPlan pl;
+        if (tc_plan(idx, nqc, k, &pl)) return fail("tensor path: shape not supported");
+        TcWs w;
+        tc_carve(idx, nqc, k, pl, fb_nparts, ws_tail, &w);
+        if (w.bytes > ws_tail_bytes) return fail("internal: tensor-path workspace under-sized");
+        const float* qc = q_dev + (size_t)q0 * ldq;
+
+        BFK_CUDA(cudaMemsetAsync(w.flags, 0, sizeof(int), st));
+        prep_queries_kernel<<<(unsigned)((pl.nq_pad + 7) / 8), 256, 0, st>>>(qc, ldq, idx->d, nqc, pl.nq_pad, w.q16,
+                                                                            idx->ld16, w.qn);
+        BFK_CUDA(cudaGetLastError());
+        CUtensorMap tmQ, tmX;
+        BFK_TRY(make_tmap(&tmQ, w.q16, pl.nq_pad, idx->ld16, TC_BM));
+        BFK_TRY(make_tmap(&tmX, idx->x16, idx->ntotal, idx->ld16, TC_BN));
+        TcParams p;
+        p.nrm = idx->nrm;
+        p.n = idx->ntotal;
+        p.KB = pl.KB;
+        p.QT = pl.QT;
+        p.S = pl.S;
+        p.tiles_total = pl.tiles_total;
+        p.smem_bytes = (int)pl.smem;
+        p.is_l2 = l2 ? 1 : 0;
+        p.nq = (int)nqc;
+        p.pend = w.pend;
+        p.out_cand = w.out_cand;
+        p.out_thr = w.out_thr;
+        if (ev0 && q0 == 0) cudaEventRecord(ev0, st);
+        if (pl.KP == 16)
+            BFK_TRY(launch_scan_tc<16>(tmQ, tmX, p, pl, st));
+        else
+            BFK_TRY(launch_scan_tc<32>(tmQ, tmX, p, pl, st));
+        if (ev1 && q0 + chunk >= nq) cudaEventRecord(ev1, st);
+
+        RerankParams r;
+        r.out_cand = w.out_cand;
+        r.out_thr = w.out_thr;
+        r.qn = w.qn;
+        r.q = qc;
+        r.ldq = ldq;
+        r.S = pl.S;
+        r.KP = pl.KP;
+        r.k = k;
+        r.is_l2 = l2 ? 1 : 0;
+        r.storage = idx->storage;
+        r.x32 = idx->x32;
+        r.ld32 = idx->ld32;
+        r.x16 = idx->x16;
+        r.ld16 = idx->ld16;
+        r.d = idx->d;
+        r.maxn = idx->maxn;
+        // |<q,x> - <bf16(q),bf16(x)>| <= (2u + u^2) ||q|| ||x|| with u = 2^-9 when both operands are
+        // rounded, u ||q|| ||x|| when the corpus is stored in bf16; + 2^-14 for tensor-core accumulation
+        r.c_round = (idx->storage == BFK_STORE_F32 ? 1.01f / 256.f : 1.01f / 512.f) + 1.0f / 16384.f;
+        r.id_offset = id_offset;
+        r.D = D_dev + (size_t)q0 * k;
+        r.I = I_dev + (size_t)q0 * k;
+        r.nflag = w.flags;
+        r.flag_list = w.flags + 1;
+        rerank_kernel<<<(unsigned)nqc, 256, 0, st>>>(r);
+        BFK_CUDA(cudaGetLastError());
+        launches += 3;
+
+        // ---- uncertified queries: exact re-run on the GPU (K3a + K4) ----
+        int nflag = 0;
+        BFK_CUDA(cudaMemcpyAsync(&nflag, w.flags, sizeof(int), cudaMemcpyDeviceToHost, st));
+        BFK_CUDA(cudaStreamSynchronize(st));
+        if (nflag > 0) {
+            std::vector<int> list((size_t)nflag);
+            BFK_CUDA(cudaMemcpyAsync(list.data(), w.flags + 1, sizeof(int) * (size_t)nflag, cudaMemcpyDeviceToHost, st));
+            BFK_CUDA(cudaStreamSynchronize(st));
+            std::sort(list.begin(), list.end());
+            for (int g0 = 0; g0 < nflag; g0 += 8) {
+                const int g = std::min(8, nflag - g0);
+                for (int j = 0; j < g; j++)
+                    BFK_CUDA(cudaMemcpyAsync(w.fb_q + (size_t)j * ldq, qc + (size_t)list[g0 + j] * ldq,
+                                             sizeof(float) * ldq, cudaMemcpyDeviceToDevice, st));
+                BFK_TRY(launch_scan_exact(idx, w.fb_q, ldq, g, k, w.fb_part, fb_nparts, st));
+                BFK_TRY(launch_select(w.fb_part, (int64_t)fb_nparts * k, g, k, idx->metric, id_offset, w.fb_D, w.fb_I, k, st));
+                launches += 2;
+                for (int j = 0; j < g; j++) {
+                    const size_t row = (size_t)(q0 + list[g0 + j]) * k;
+                    BFK_CUDA(cudaMemcpyAsync(D_dev + row, w.fb_D + (size_t)j * k, sizeof(float) * k,
+                                             cudaMemcpyDeviceToDevice, st));
+                    BFK_CUDA(cudaMemcpyAsync(I_dev + row, w.fb_I + (size_t)j * k, sizeof(int64_t) * k,
+                                             cudaMemcpyDeviceToDevice, st));
+                }
+            }
+            n_fallback += nflag;
+        }
+    }
+    if (stats) {
+        stats->n_launches = launches;
+        stats->n_fallback = n_fallback;
+        stats->algo_used = BFK_ALGO_TENSOR;
+    }
+    return 0;
+}
+
+}  // namespace bfk

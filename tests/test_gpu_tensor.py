@@ -1,0 +1,174 @@
+"""Tensor-core search path (bf16 tcgen05 scan + exact fp32 rerank + certificate). GPU only."""
+import numpy as np
+import pytest
+
+from oracle import cpu_baseline, flat_ref
+from tests.parity import check_knn
+
+pytestmark = pytest.mark.gpu
+
+L2, IP = flat_ref.METRIC_L2, flat_ref.METRIC_INNER_PRODUCT
+
+
+def unit(rng, n, d):
+    x = rng.standard_normal((n, d)).astype(np.float32)
+    x /= np.linalg.norm(x, axis=1, keepdims=True)
+    return x
+
+
+@pytest.fixture(scope="module")
+def bfk():
+    import docqa_b200
+
+    assert docqa_b200.get_num_gpus() >= 1
+    return docqa_b200
+
+
+def run(bfk, idx, q, k):
+    st = bfk.SearchStats()
+    D, I = idx.search(q, k, algo="tensor", stats=st)
+    assert st.algo_used == bfk.ALGO_TENSOR
+    return D, I, st
+
+
+@pytest.mark.parametrize("metric", [L2, IP])
+def test_tensor_path_on_reference_fixture(bfk, golden_dir, fixture_corpus, metric):
+    import os
+
+    g = np.load(os.path.join(golden_dir, "docqa_search_golden.npz"))
+    q = np.concatenate([fixture_corpus[:200], g["perturbed_queries"]], axis=0)
+    idx = bfk.IndexFlat(384, metric)
+    idx.add(fixture_corpus)
+    for k in (3, 5, 10):
+        D, I, st = run(bfk, idx, q, k)
+        check_knn(D, I, q, fixture_corpus, k, metric, tight=True)
+    if metric == L2:
+        D, I, st = run(bfk, idx, fixture_corpus, 5)  # every row as a query: 23 duplicate groups
+        check_knn(D, I, fixture_corpus, fixture_corpus, 5, L2, I_ref=g["I"][:649], D_ref64=g["D64"][:649], tight=True)
+        assert (D[:, 0] == 0).all()
+
+
+@pytest.mark.parametrize("metric", [L2, IP])
+@pytest.mark.parametrize("d", [384, 100, 64, 37])
+@pytest.mark.parametrize("nq", [9, 64, 128, 129, 300])
+def test_tensor_path_random(bfk, metric, d, nq):
+    rng = np.random.default_rng(1000 * d + nq + metric)
+    n = 20011
+    xb, xq = unit(rng, n, d), unit(rng, nq, d)
+    idx = bfk.IndexFlat(d, metric)
+    idx.add(xb)
+    for k in (1, 10, 32):
+        D, I, st = run(bfk, idx, xq, k)
+        check_knn(D, I, xq, xb, k, metric, tight=True)
+        De, Ie = idx.search(xq, k, algo="exact")
+        assert (I == Ie).all()
+        np.testing.assert_allclose(D, De, rtol=1e-5, atol=1e-6)
+
+
+def test_tensor_path_small_and_ragged_corpora(bfk):
+    rng = np.random.default_rng(3)
+    for n in (1, 5, 255, 256, 257, 1000):
+        xb, xq = unit(rng, n, 384), unit(rng, 17, 384)
+        idx = bfk.IndexFlatL2(384)
+        idx.add(xb)
+        D, I, st = run(bfk, idx, xq, 10)
+        check_knn(D, I, xq, xb, 10, L2, tight=True)
+
+
+def test_tensor_path_unnormalised_rows(bfk):
+    rng = np.random.default_rng(4)
+    xb = (rng.standard_normal((30000, 128)) * rng.uniform(0.1, 5.0, size=(30000, 1))).astype(np.float32)
+    xq = (rng.standard_normal((40, 128)) * 2.0).astype(np.float32)
+    for metric in (L2, IP):
+        idx = bfk.IndexFlat(128, metric)
+        idx.add(xb)
+        D, I, st = run(bfk, idx, xq, 10)
+        check_knn(D, I, xq, xb, 10, metric)
+
+
+def test_certificate_fallback_on_ties_and_adversarial_order(bfk):
+    rng = np.random.default_rng(5)
+    d = 384
+    # (a) all rows identical: nothing can be certified -> exact re-run on the GPU, smallest ids win
+    same = np.repeat(unit(rng, 1, d), 5000, axis=0)
+    idx = bfk.IndexFlatL2(d)
+    idx.add(same)
+    q = unit(rng, 12, d)
+    D, I, st = run(bfk, idx, q, 10)
+    assert st.n_fallback == 12
+    assert (I == np.arange(10)[None, :]).all() and np.ptp(D, axis=1).max() == 0
+    # (b) 1% duplicates + farthest-first order for query 0
+    xb = unit(rng, 40000, d)
+    src = rng.integers(0, 40000, size=400)
+    xb[rng.integers(0, 40000, size=400)] = xb[src]
+    q = unit(rng, 33, d)
+    xb = np.ascontiguousarray(xb[np.argsort(-((xb - q[0]) ** 2).sum(1))])
+    idx2 = bfk.IndexFlatL2(d)
+    idx2.add(xb)
+    D, I, st = run(bfk, idx2, q, 10)
+    check_knn(D, I, q, xb, 10, L2, tight=True)
+    # (c) queries that are corpus rows: distance exactly 0 first
+    D, I, st = run(bfk, idx2, xb[100:120], 5)
+    assert (D[:, 0] == 0).all()
+    check_knn(D, I, xb[100:120], xb, 5, L2, tight=True)
+
+
+def test_tensor_path_bf16_storage(bfk):
+    import torch
+
+    rng = np.random.default_rng(6)
+    xb, xq = unit(rng, 50000, 384), unit(rng, 70, 384)
+    xb16 = torch.from_numpy(xb).to(torch.bfloat16).to(torch.float32).numpy()
+    for metric in (L2, IP):
+        idx = bfk.IndexFlat(384, metric, storage="bf16")
+        idx.add(xb)
+        D, I, st = run(bfk, idx, xq, 10)
+        check_knn(D, I, xq, xb16, 10, metric, tight=True)
+
+
+def test_tensor_path_limits_and_auto_dispatch(bfk):
+    rng = np.random.default_rng(7)
+    xb, xq = unit(rng, 3000, 384), unit(rng, 40, 384)
+    idx = bfk.IndexFlatL2(384)
+    idx.add(xb)
+    with pytest.raises(RuntimeError):
+        idx.search(xq, 100, algo="tensor")  # k > 32 is served by the exact path only (for now)
+    st = bfk.SearchStats()
+    D, I = idx.search(xq, 100, stats=st)
+    assert st.algo_used == bfk.ALGO_EXACT_SIMT
+    check_knn(D, I, xq, xb, 100, L2, tight=True)
+    D, I = idx.search(xq, 10, stats=st)
+    assert st.algo_used == bfk.ALGO_TENSOR
+    D, I = idx.search(xq[:8], 10, stats=st)
+    assert st.algo_used == bfk.ALGO_EXACT_SIMT
+
+
+def test_tensor_path_full_size_1m_x_384(bfk):
+    """BASELINE config 2 at full size, batches 64 and 1024."""
+    import torch
+
+    n, d, k = 1_000_000, 384, 10
+    g = torch.Generator(device="cuda").manual_seed(1234)
+    xb = torch.randn((n, d), generator=g, device="cuda", dtype=torch.float32)
+    xb /= xb.norm(dim=1, keepdim=True)
+    g2 = torch.Generator(device="cuda").manual_seed(4321)
+    q = torch.randn((1024, d), generator=g2, device="cuda", dtype=torch.float32)
+    q /= q.norm(dim=1, keepdim=True)
+    idx = bfk.IndexFlatL2(d)
+    idx.add(xb)
+    st = bfk.SearchStats()
+    D, I = idx.search(q, k, algo="tensor", stats=st)
+    assert st.n_fallback == 0  # random unit vectors certify
+    D, I = D.cpu().numpy(), I.cpu().numpy()
+    xb_h, q_h = xb.cpu().numpy(), q.cpu().numpy()
+    Dc, Ic = cpu_baseline.knn(q_h[:64], xb_h, k, L2)  # BLAS form of the CPU restatement
+    check_knn(D[:64], I[:64], q_h[:64], xb_h, k, L2, I_ref=Ic, D_ref64=Dc.astype(np.float64))
+    # size-independent properties on all 1024 rows
+    assert (np.diff(D, axis=1) >= 0).all() and I.min() >= 0 and I.max() < n
+    rec = ((xb_h[I.reshape(-1)].reshape(1024, k, d) - q_h[:, None, :]) ** 2).sum(-1)
+    np.testing.assert_allclose(D, rec, rtol=1e-3, atol=1e-6)
+    # a 64-query call and the exact path agree with the 1024-query call
+    D64, I64 = idx.search(q[:64], k, algo="tensor")
+    assert (I64.cpu().numpy() == I[:64]).all()
+    De, Ie = idx.search(q[:16], k, algo="exact")
+    assert (Ie.cpu().numpy() == I[:16]).all()
