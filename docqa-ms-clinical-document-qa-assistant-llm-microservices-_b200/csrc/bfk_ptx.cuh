@@ -50,6 +50,31 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
     }
 }
 
+// Same, for the single-thread producer / MMA-issuer roles: the suspend-time hint lets the hardware
+// park the thread until the phase completes instead of spinning on issue slots that the epilogue
+// warps of the same scheduler need.
+__device__ __forceinline__ bool mbar_try_wait_hint(uint64_t* bar, uint32_t parity, uint32_t hint_ns) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity), "r"(hint_ns)
+        : "memory");
+    return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait_parked(uint64_t* bar, uint32_t parity) {
+    if (mbar_try_wait_hint(bar, parity, 100000u)) return;
+    const long long t0 = clock64();
+    while (!mbar_try_wait_hint(bar, parity, 100000u)) {
+        if (clock64() - t0 > 4000000000ll) {
+            printf("libbfk: mbarrier wait timed out (block %d thread %d)\n", (int)blockIdx.x, (int)threadIdx.x);
+            __trap();
+        }
+    }
+}
+
 // ---- 1-D bulk copy global -> shared (TMA engine, no tensor map) -----------------
 __device__ __forceinline__ void bulk_g2s(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
     asm volatile(

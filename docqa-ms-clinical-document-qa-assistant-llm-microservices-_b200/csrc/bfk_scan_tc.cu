@@ -6,17 +6,19 @@
 // scan copy of the corpus, selection is fused into the epilogue, and the survivors are
 // re-scored exactly in fp32 with faiss's nq<20 arithmetic (direct sum((x-y)^2)).
 //
-// K3b (one CTA per SM, 8 warps, queries on M, corpus rows on N):
+// K3b (one CTA per SM, 12 warps, queries on M, corpus rows on N):
 //   warp 0  TMA producer: the 128-query tile is loaded once (KB boxes of 64x128, SWIZZLE_128B)
 //           and stays resident; corpus tiles stream as 64x256 boxes through an mbarrier ring
 //   warp 1  one thread issues tcgen05.mma kind::f16 (bf16 x bf16 -> fp32), M=128 N=256 K=16,
 //           4 per K-block; tcgen05.commit frees the smem stage / publishes the accumulator
 //   warp 2  TMEM allocator (512 columns = two 128x256 fp32 accumulators, double buffered)
-//   warps 4-7  epilogue, thread == query row: tcgen05.ld 32x32b.x32, key = ||x||^2 - 2*acc (L2)
-//           or -acc (IP) with the bias staged in smem, compare against the thread's threshold,
-//           append survivors to a per-thread pending list (coalesced [slot][thread] layout in
-//           global scratch); when a list fills, the warp flushes: every thread bubbles its own
-//           pending entries into a register-resident sorted top-KP, and the threshold tightens
+//   warps 4-11 epilogue, thread == (query row, 128-column half of the tile): tcgen05.ld 32x32b.x32,
+//           key = ||x||^2 - 2*acc (L2) or -acc (IP) with the bias staged in smem, compare against
+//           the thread's threshold (one warp vote per 4 columns skips the common no-survivor
+//           case), append survivors to a per-thread pending list (coalesced [slot][thread] layout
+//           in global scratch); when a list fills, the warp flushes: every thread bubbles its own
+//           pending entries into a register-resident sorted top-KP, and the threshold tightens;
+//           at the end of the stream the two halves of a query are folded through shared memory
 //   CTA c works on query tile c % QT and corpus stream c / QT (a contiguous range of tiles), so
 //   CTAs sharing a stream walk the same corpus rows together and share them through L2.
 // Output per (query, stream): the KP best approximate keys + T = the KP-th key (every row the
@@ -34,6 +36,7 @@
 #include <cuda.h>
 
 #include <cfloat>
+#include <cstdlib>
 #include <vector>
 
 #include "bfk_common.cuh"
@@ -43,14 +46,16 @@ namespace bfk {
 
 constexpr int TC_BM = 128;
 constexpr int TC_BN = 256;
-constexpr int TC_THREADS = 256;
+constexpr int TC_THREADS = 384;       // 4 control warps + 8 epilogue warps
+constexpr int TC_EPI_THREADS = 256;
 constexpr int TC_A_BLOCK = TC_BM * 128;  // bytes of one 64-column K-block of the query tile
 constexpr int TC_B_BLOCK = TC_BN * 128;  // bytes of one 64-column K-block of a corpus tile
 constexpr int TC_MAX_STAGES = 8;
-constexpr int TC_BUFCAP = 64;            // pending slots per epilogue thread
+constexpr int TC_BUFCAP = 16;            // pending slots per epilogue thread (shared memory)
 constexpr int TC_SMEM_LIMIT = 232448;    // 227 KiB
 constexpr int TC_RMAX = 64;              // exact re-scores per query at most
 constexpr int TC_MERGE_N = 4096;
+constexpr int TC_PEND_BYTES = TC_BUFCAP * 256 * 8;  // 32 KiB
 constexpr int TC_TAIL_BYTES = 2 * TC_BN * 4 + (2 * TC_MAX_STAGES + 5) * 8 + 16;  // bias + barriers + tmem slot
 
 struct TcParams {
@@ -63,12 +68,24 @@ struct TcParams {
     int smem_bytes;      // dynamic shared memory given to the launch
     int is_l2;
     int nq;
-    uint64_t* pend;      // [grid][TC_BUFCAP][128]
+    unsigned int* thr_g; // [nq_pad] ordered bits of the best KP-th key any thread has seen, per query
+    const float* qmargin;  // [nq_pad] 2*eps in key space (see prep_queries_kernel)
     uint64_t* out_cand;  // [QT*128][S][KP]
     float* out_thr;      // [QT*128][S]
+    unsigned long long* dbg;  // optional [grid][8] cycle counters (BFK_TC_DEBUG=1), else nullptr
+    int parked;          // producer/MMA waits use the suspend-time hint
 };
 
-__device__ __forceinline__ void epi_sync() { asm volatile("bar.sync 2, 128;" ::: "memory"); }
+// wait flavour for the single-thread roles + optional cycle accounting
+#define TC_WAIT(bar, parity, slot)                                   \
+    do {                                                             \
+        const long long _t0 = p.dbg ? clock64() : 0;                 \
+        if (p.parked) mbar_wait_parked(bar, parity);                 \
+        else mbar_wait(bar, parity);                                 \
+        if (p.dbg) dbg_acc[slot] += (unsigned long long)(clock64() - _t0); \
+    } while (0)
+
+__device__ __forceinline__ void epi_sync() { asm volatile("bar.sync 2, 256;" ::: "memory"); }
 
 template <int KP>
 __global__ void __launch_bounds__(TC_THREADS, 1)
@@ -79,10 +96,11 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
     unsigned char* smem = smem_raw + pad;
     // stages: whatever fits after the resident query tile and the fixed tail (host sizes for pad = 0;
     // a misaligned base just costs one stage)
-    const int stages = min(TC_MAX_STAGES, (int)((p.smem_bytes - (int)pad - p.KB * TC_A_BLOCK - TC_TAIL_BYTES) / TC_B_BLOCK));
+    const int stages = min(TC_MAX_STAGES, (int)((p.smem_bytes - (int)pad - p.KB * TC_A_BLOCK - TC_PEND_BYTES - TC_TAIL_BYTES) / TC_B_BLOCK));
     unsigned char* sA = smem;
     unsigned char* sB = sA + (size_t)p.KB * TC_A_BLOCK;
-    float* bias_s = reinterpret_cast<float*>(sB + (size_t)stages * TC_B_BLOCK);
+    uint64_t* pend_s = reinterpret_cast<uint64_t*>(sB + (size_t)stages * TC_B_BLOCK);  // [TC_BUFCAP][256]
+    float* bias_s = reinterpret_cast<float*>(reinterpret_cast<unsigned char*>(pend_s) + TC_PEND_BYTES);
     uint64_t* full_bar = reinterpret_cast<uint64_t*>(bias_s + 2 * TC_BN);
     uint64_t* empty_bar = full_bar + TC_MAX_STAGES;
     uint64_t* q_bar = empty_bar + TC_MAX_STAGES;
@@ -91,6 +109,8 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    unsigned long long dbg_acc[4] = {0, 0, 0, 0};
+    const long long dbg_t0 = p.dbg ? clock64() : 0;
     const int qt = blockIdx.x % p.QT;
     const int s = blockIdx.x / p.QT;
     const int64_t t_begin = p.tiles_total * s / p.S;
@@ -104,7 +124,7 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
         mbar_init(q_bar, 1);
         for (int a = 0; a < 2; a++) {
             mbar_init(&tfull_bar[a], 1);
-            mbar_init(&tempty_bar[a], 128);
+            mbar_init(&tempty_bar[a], TC_EPI_THREADS);
         }
         fence_mbar_init();
     }
@@ -128,28 +148,29 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
                 for (int kb = 0; kb < p.KB; kb++, it++) {
                     const int st = it % stages;
                     const uint32_t ph = (it / stages) & 1u;
-                    mbar_wait(&empty_bar[st], ph ^ 1u);
+                    TC_WAIT(&empty_bar[st], ph ^ 1u, 0);
                     mbar_expect_tx(&full_bar[st], TC_B_BLOCK);
                     tma_load_2d(sB + (size_t)st * TC_B_BLOCK, &tmX, kb * 64, (int)(t * TC_BN), &full_bar[st]);
                 }
             }
+            if (p.dbg) p.dbg[blockIdx.x * 8 + 0] = dbg_acc[0];
         }
     } else if (warp == 1) {
         // ===================== MMA issuer (one thread) =====================
         if (lane == 0) {
             const uint32_t idesc = make_idesc_bf16(TC_BM, TC_BN);
             const uint32_t a_base = smem_u32(sA), b_base = smem_u32(sB);
-            mbar_wait(q_bar, 0);
+            TC_WAIT(q_bar, 0, 3);
             uint32_t it = 0, tcount = 0;
             for (int64_t t = t_begin; t < t_end; t++, tcount++) {
                 const uint32_t a = tcount & 1u, aph = (tcount >> 1) & 1u;
-                mbar_wait(&tempty_bar[a], aph ^ 1u);  // epilogue has drained this accumulator
+                TC_WAIT(&tempty_bar[a], aph ^ 1u, 2);  // epilogue has drained this accumulator
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + a * TC_BN;
                 for (int kb = 0; kb < p.KB; kb++, it++) {
                     const int st = it % stages;
                     const uint32_t ph = (it / stages) & 1u;
-                    mbar_wait(&full_bar[st], ph);
+                    TC_WAIT(&full_bar[st], ph, 1);
                     tc_fence_after();
 #pragma unroll
                     for (int kk = 0; kk < 4; kk++) {
@@ -161,11 +182,17 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
                 }
                 umma_commit(&tfull_bar[a]);  // accumulator complete
             }
+            if (p.dbg) {
+                p.dbg[blockIdx.x * 8 + 1] = dbg_acc[1];
+                p.dbg[blockIdx.x * 8 + 2] = dbg_acc[2];
+            }
         }
     } else if (warp >= 4) {
-        // ===================== epilogue: thread == query row =====================
-        const int et = tid - 128;
-        const int qrow = qt * TC_BM + et;
+        // ============ epilogue: 8 warps; thread == (query row, column half of the tile) ============
+        const int et = tid - 128;          // 0..255
+        const int half = et >> 7;          // which 128 columns of each 256-column tile
+        const int row = et & 127;          // query row in the tile == TMEM lane
+        const int qrow = qt * TC_BM + row;
         const bool active = qrow < p.nq;
         float skey[KP];
         uint32_t sidx[KP];
@@ -174,78 +201,145 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
             skey[i] = FLT_MAX;
             sidx[i] = 0xffffffffu;
         }
-        float thr = FLT_MAX;
+        // effective threshold = min(own KP-th best, best KP-th any thread has published for this
+        // query + the query's error margin): rows above it can be neither in this thread's top-KP nor
+        // within the margin band of the global top-KP, which is all K5's certificate needs
+        const float qmargin = active ? p.qmargin[qrow] : 0.f;
+        unsigned int* thr_g = p.thr_g + (active ? qrow : 0);
+        float thr = active ? FLT_MAX : -FLT_MAX;
         int cnt = 0;
-        uint64_t* my_pend = p.pend + (size_t)blockIdx.x * TC_BUFCAP * 128 + et;
+        uint64_t* my_pend = pend_s + et;   // [slot][thread] in shared memory
         const float scale = p.is_l2 ? -2.0f : -1.0f;
 
+        auto insert = [&](float x, uint32_t xi) {
+#pragma unroll
+            for (int j = 0; j < KP; j++) {
+                const bool sw = x < skey[j];
+                const float tk = skey[j];
+                const uint32_t ti = sidx[j];
+                skey[j] = sw ? x : tk;
+                sidx[j] = sw ? xi : ti;
+                x = sw ? tk : x;
+                xi = sw ? ti : xi;
+            }
+        };
+        auto refresh_thr = [&]() {
+            if (active) {
+                const float g = ord2f(*reinterpret_cast<volatile unsigned int*>(thr_g));
+                thr = fminf(skey[KP - 1], g < FLT_MAX ? g + qmargin : FLT_MAX);
+            }
+        };
         auto flush = [&]() {
             const int maxc = __reduce_max_sync(0xffffffffu, cnt);
-#pragma unroll 4
+#pragma unroll 2
             for (int i = 0; i < maxc; i++) {
                 const bool has = i < cnt;
-                const uint64_t e = has ? my_pend[(size_t)i * 128] : 0ull;
-                float x = __uint_as_float((uint32_t)(e >> 32));
-                uint32_t xi = (uint32_t)e;
-                if (has && x < skey[KP - 1]) {
-#pragma unroll
-                    for (int j = 0; j < KP; j++) {
-                        const bool sw = x < skey[j];
-                        const float tk = skey[j];
-                        const uint32_t ti = sidx[j];
-                        skey[j] = sw ? x : tk;
-                        sidx[j] = sw ? xi : ti;
-                        x = sw ? tk : x;
-                        xi = sw ? ti : xi;
-                    }
-                }
+                const uint64_t e = my_pend[(size_t)i * TC_EPI_THREADS];
+                const float x = __uint_as_float((uint32_t)(e >> 32));
+                if (has && x < skey[KP - 1]) insert(x, (uint32_t)e);
             }
             cnt = 0;
-            thr = skey[KP - 1];
+            if (active && skey[KP - 1] < FLT_MAX) atomicMin(thr_g, f2ord(skey[KP - 1]));
+            refresh_thr();
         };
 
         uint32_t tcount = 0;
         for (int64_t t = t_begin; t < t_end; t++, tcount++) {
             const uint32_t a = tcount & 1u, aph = (tcount >> 1) & 1u;
-            for (int j = et; j < TC_BN; j += 128) {
-                const int64_t col = t * TC_BN + j;
-                bias_s[a * TC_BN + j] = (col < p.n) ? (p.is_l2 ? __ldg(p.nrm + col) : 0.f) : INFINITY;
+            {
+                const int64_t col = t * TC_BN + et;
+                bias_s[a * TC_BN + et] = (col < p.n) ? (p.is_l2 ? __ldg(p.nrm + col) : 0.f) : INFINITY;
             }
-            epi_sync();
-            mbar_wait(&tfull_bar[a], aph);
+            refresh_thr();  // pick up what other CTAs learned while this tile was being computed
+            {
+                const long long _t0 = p.dbg ? clock64() : 0;
+                epi_sync();
+                mbar_wait(&tfull_bar[a], aph);
+                if (p.dbg) dbg_acc[0] += (unsigned long long)(clock64() - _t0);
+            }
             tc_fence_after();
-            const uint32_t taddr = tmem_base + ((uint32_t)((warp - 4) * 32) << 16) + a * TC_BN;
-            const uint32_t col0 = (uint32_t)(t * TC_BN);
-            for (int c0 = 0; c0 < TC_BN; c0 += 32) {
+            const uint32_t taddr = tmem_base + ((uint32_t)(((warp - 4) & 3) * 32) << 16) + a * TC_BN + half * 128;
+            const uint32_t col0 = (uint32_t)(t * TC_BN) + half * 128;
+            const float* bias = bias_s + a * TC_BN + half * 128;
+#pragma unroll 1
+            for (int c0 = 0; c0 < 128; c0 += 32) {
                 uint32_t r[32];
                 tmem_ld_32x32(taddr + c0, r);
                 tmem_ld_wait();
-                const float4* b4 = reinterpret_cast<const float4*>(bias_s + a * TC_BN + c0);
+                const float4* b4 = reinterpret_cast<const float4*>(bias + c0);
 #pragma unroll
                 for (int j4 = 0; j4 < 8; j4++) {
                     const float4 b = b4[j4];
-                    const float bb[4] = {b.x, b.y, b.z, b.w};
+                    const float k0 = fmaf(scale, __uint_as_float(r[4 * j4 + 0]), b.x);
+                    const float k1 = fmaf(scale, __uint_as_float(r[4 * j4 + 1]), b.y);
+                    const float k2 = fmaf(scale, __uint_as_float(r[4 * j4 + 2]), b.z);
+                    const float k3 = fmaf(scale, __uint_as_float(r[4 * j4 + 3]), b.w);
+                    const float kmin = fminf(fminf(k0, k1), fminf(k2, k3));
+                    // most groups of 4 have no survivor in any lane: one vote skips the append code
+                    if (__any_sync(0xffffffffu, kmin < thr)) {
+                        const float kk[4] = {k0, k1, k2, k3};
 #pragma unroll
-                    for (int e = 0; e < 4; e++) {
-                        const float key = fmaf(scale, __uint_as_float(r[4 * j4 + e]), bb[e]);
-                        if (active && key < thr) {
-                            my_pend[(size_t)cnt * 128] =
-                                ((uint64_t)__float_as_uint(key) << 32) | (uint64_t)(col0 + c0 + 4 * j4 + e);
-                            cnt++;
+                        for (int e = 0; e < 4; e++) {
+                            if (kk[e] < thr) {
+                                my_pend[(size_t)cnt * TC_EPI_THREADS] =
+                                    ((uint64_t)__float_as_uint(kk[e]) << 32) | (uint64_t)(col0 + c0 + 4 * j4 + e);
+                                cnt++;
+                            }
+                        }
+                        if (__any_sync(0xffffffffu, cnt > TC_BUFCAP - 4)) {
+                            const long long _t0 = p.dbg ? clock64() : 0;
+                            dbg_acc[2] += (unsigned long long)cnt;
+                            flush();
+                            if (p.dbg) {
+                                dbg_acc[1] += (unsigned long long)(clock64() - _t0);
+                                dbg_acc[3] += 1;
+                            }
                         }
                     }
                 }
-                if (__any_sync(0xffffffffu, cnt > TC_BUFCAP - 32)) flush();
             }
             tc_fence_before();
             mbar_arrive(&tempty_bar[a]);
         }
+        dbg_acc[2] += (unsigned long long)cnt;
         flush();
-        if (active) {
-            uint64_t* dst = p.out_cand + ((size_t)qrow * p.S + s) * KP;
+        if (p.dbg && et == 0) {
+            p.dbg[blockIdx.x * 8 + 3] = dbg_acc[0];                         // epilogue: waiting for an accumulator
+            p.dbg[blockIdx.x * 8 + 4] = dbg_acc[1];                         // epilogue: cycles inside flush()
+            p.dbg[blockIdx.x * 8 + 5] = dbg_acc[2];                         // entries appended by thread 0
+            p.dbg[blockIdx.x * 8 + 6] = dbg_acc[3];                         // flushes of warp 4
+            p.dbg[blockIdx.x * 8 + 7] = (unsigned long long)(clock64() - dbg_t0);  // CTA lifetime
+        }
+        // ---- fold the two column halves of every query: half 1 publishes through the (now idle)
+        //      corpus stages, half 0 absorbs and writes the stream's list and drop threshold ----
+        float* xk = reinterpret_cast<float*>(sB);
+        uint32_t* xi = reinterpret_cast<uint32_t*>(sB + (size_t)KP * 128 * 4);
+        float* xt = reinterpret_cast<float*>(sB + (size_t)KP * 128 * 8);
+        if (half == 1) {
 #pragma unroll
-            for (int i = 0; i < KP; i++) dst[i] = (sidx[i] == 0xffffffffu) ? COMP_EMPTY : make_comp(skey[i], sidx[i]);
-            p.out_thr[(size_t)qrow * p.S + s] = skey[KP - 1];
+            for (int i = 0; i < KP; i++) {
+                xk[i * 128 + row] = skey[i];
+                xi[i * 128 + row] = sidx[i];
+            }
+            xt[row] = thr;
+        }
+        epi_sync();
+        if (half == 0) {
+#pragma unroll 1
+            for (int i = 0; i < KP; i++) {
+                const float x = xk[i * 128 + row];
+                if (x < skey[KP - 1]) insert(x, xi[i * 128 + row]);
+            }
+            if (active) {
+                uint64_t* dst = p.out_cand + ((size_t)qrow * p.S + s) * KP;
+#pragma unroll
+                for (int i = 0; i < KP; i++)
+                    dst[i] = (sidx[i] == 0xffffffffu) ? COMP_EMPTY : make_comp(skey[i], sidx[i]);
+                // every row this stream dropped had key >= the threshold in force at that moment, and
+                // thresholds only fall: the smallest final threshold of the two halves (and of the
+                // folded list) bounds them all
+                p.out_thr[(size_t)qrow * p.S + s] = fminf(fminf(thr, xt[row]), skey[KP - 1]);
+            }
         }
     }
 
@@ -260,7 +354,9 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
 // queries fp32 [nq, ldq] -> bf16 [nq_pad, ld16] (zero padded rows and columns) + ||q||^2
 __global__ void __launch_bounds__(256) prep_queries_kernel(const float* __restrict__ q, int ldq, int d, int64_t nq,
                                                            int64_t nq_pad, __nv_bfloat16* __restrict__ q16, int ld16,
-                                                           float* __restrict__ qn) {
+                                                           float* __restrict__ qn, const unsigned int* __restrict__ maxn,
+                                                           float c_round, int is_l2, float* __restrict__ qmargin,
+                                                           unsigned int* __restrict__ thr_g) {
     const int lane = threadIdx.x & 31;
     const int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (row >= nq_pad) return;
@@ -272,13 +368,19 @@ __global__ void __launch_bounds__(256) prep_queries_kernel(const float* __restri
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
-    if (lane == 0) qn[row] = ss;
+    if (lane == 0) {
+        qn[row] = ss;
+        // 2*eps in key space: |<q,x> - <bf16 q, bf16 x>| <= c_round ||q|| max||x||; L2 keys carry 2x that
+        const float mx = __uint_as_float(*maxn);
+        qmargin[row] = (is_l2 ? 4.f : 2.f) * c_round * sqrtf(ss * mx) + 1e-6f * (ss + mx);
+        thr_g[row] = f2ord(FLT_MAX);
+    }
 }
 
 struct RerankParams {
     const uint64_t* out_cand;  // [nq_pad][S][KP]
     const float* out_thr;      // [nq_pad][S]
-    const float* qn;           // [nq_pad]
+    const float* qmargin;      // [nq_pad] 2*eps in key space
     const float* q;            // [nq][ldq] fp32
     int ldq;
     int S;
@@ -291,8 +393,6 @@ struct RerankParams {
     const __nv_bfloat16* x16;
     int ld16;
     int d;
-    const unsigned int* maxn;
-    float c_round;             // relative bound on the bf16 inner-product error
     int64_t id_offset;
     float* D;                  // [nq][k]
     int64_t* I;
@@ -368,11 +468,7 @@ __global__ void __launch_bounds__(256) rerank_kernel(const RerankParams p) {
         if (nvalid > 0) {
             const int kk = min(p.k, nvalid);
             const float a_k = ord2f((uint32_t)(buf[kk - 1] >> 32));
-            const float qn = p.qn[q];
-            const float maxn = __uint_as_float(*p.maxn);
-            const float eps_ip = p.c_round * sqrtf(qn * maxn);
-            const float margin = (p.is_l2 ? 4.f : 2.f) * eps_ip + 1e-6f * (qn + maxn);
-            const float cut = a_k + margin;
+            const float cut = a_k + p.qmargin[q];
             while (R < nvalid && ord2f((uint32_t)(buf[R] >> 32)) <= cut) R++;
             if (R < kk) R = kk;
             // rows a stream dropped have approximate key >= its T; rows beyond the window >= buf[RMAX-1]
@@ -487,7 +583,7 @@ struct TcPlan {
 
 static int tc_plan(const bfk_index* idx, int64_t nq, int k, TcPlan* pl) {
     pl->KB = idx->ld16 / 64;
-    const size_t fixed = (size_t)pl->KB * TC_A_BLOCK + TC_TAIL_BYTES;
+    const size_t fixed = (size_t)pl->KB * TC_A_BLOCK + TC_PEND_BYTES + TC_TAIL_BYTES;
     if (fixed + 1024 + 2 * (size_t)TC_B_BLOCK > TC_SMEM_LIMIT) return 1;  // query tile cannot stay resident
     pl->stages = (int)std::min<size_t>(TC_MAX_STAGES, (TC_SMEM_LIMIT - fixed) / TC_B_BLOCK);
     pl->smem = fixed + (size_t)pl->stages * TC_B_BLOCK;
@@ -496,14 +592,16 @@ static int tc_plan(const bfk_index* idx, int64_t nq, int k, TcPlan* pl) {
     pl->tiles_total = (idx->ntotal + TC_BN - 1) / TC_BN;
     pl->S = (int)std::max<int64_t>(1, std::min<int64_t>(idx->num_sms / pl->QT, pl->tiles_total));
     pl->grid = pl->QT * pl->S;
-    pl->KP = (k <= 16 && pl->S >= 8) ? 16 : 32;
+    // KP slots per (query, stream): the candidates inside the error band of the global top-k must fit
+    // in the streams' lists, so few streams need longer lists
+    pl->KP = (k <= 12 && pl->S >= 8) ? 16 : 32;  // KP must exceed k: the certificate needs A_KP > A_k
     return 0;
 }
 
 static int64_t tc_chunk_queries(const bfk_index* idx) { return (int64_t)idx->num_sms * TC_BM; }
 
 int tensor_path_supported(const bfk_index* idx, int64_t nq, int k) {
-    if (k > 32 || nq <= 0 || idx->ntotal <= 0) return 0;
+    if (k > 24 || nq <= 0 || idx->ntotal <= 0) return 0;
     TcPlan pl;
     if (tc_plan(idx, std::min<int64_t>(nq, tc_chunk_queries(idx)), k, &pl)) return 0;
     return get_encode_fn() != nullptr;
@@ -512,7 +610,8 @@ int tensor_path_supported(const bfk_index* idx, int64_t nq, int k) {
 struct TcWs {
     __nv_bfloat16* q16;
     float* qn;
-    uint64_t* pend;
+    unsigned int* thr_g;
+    float* qmargin;
     uint64_t* out_cand;
     float* out_thr;
     int* flags;      // [0] = count, [1..] = list
@@ -520,6 +619,7 @@ struct TcWs {
     float* fb_D;     // [8][k]
     int64_t* fb_I;   // [8][k]
     uint64_t* fb_part;
+    unsigned long long* dbg;
     size_t bytes;
 };
 
@@ -533,7 +633,8 @@ static void tc_carve(const bfk_index* idx, int64_t nqc, int k, const TcPlan& pl,
     };
     w->q16 = (__nv_bfloat16*)take((size_t)pl.nq_pad * idx->ld16 * 2);
     w->qn = (float*)take((size_t)pl.nq_pad * 4);
-    w->pend = (uint64_t*)take((size_t)pl.grid * TC_BUFCAP * 128 * 8);
+    w->thr_g = (unsigned int*)take((size_t)pl.nq_pad * 4);
+    w->qmargin = (float*)take((size_t)pl.nq_pad * 4);
     w->out_cand = (uint64_t*)take((size_t)pl.nq_pad * pl.S * pl.KP * 8);
     w->out_thr = (float*)take((size_t)pl.nq_pad * pl.S * 4);
     w->flags = (int*)take((size_t)(nqc + 1) * 4);
@@ -541,6 +642,7 @@ static void tc_carve(const bfk_index* idx, int64_t nqc, int k, const TcPlan& pl,
     w->fb_D = (float*)take((size_t)8 * k * 4);
     w->fb_I = (int64_t*)take((size_t)8 * k * 8);
     w->fb_part = (uint64_t*)take((size_t)8 * fb_nparts * k * 8);
+    w->dbg = (unsigned long long*)take((size_t)pl.grid * 8 * 8);
     w->bytes = off + 256;
 }
 
@@ -590,8 +692,12 @@ int search_tensor(bfk_index* idx, const float* q_dev, int ldq, int64_t nq, int k
         const float* qc = q_dev + (size_t)q0 * ldq;
 
         BFK_CUDA(cudaMemsetAsync(w.flags, 0, sizeof(int), st));
+        // |<q,x> - <bf16(q),bf16(x)>| <= (2u + u^2) ||q|| ||x|| with u = 2^-9 when both operands are
+        // rounded, u ||q|| ||x|| when the corpus is stored in bf16; + 2^-14 for tensor-core accumulation
+        const float c_round = (idx->storage == BFK_STORE_F32 ? 1.01f / 256.f : 1.01f / 512.f) + 1.0f / 16384.f;
         prep_queries_kernel<<<(unsigned)((pl.nq_pad + 7) / 8), 256, 0, st>>>(qc, ldq, idx->d, nqc, pl.nq_pad, w.q16,
-                                                                            idx->ld16, w.qn);
+                                                                            idx->ld16, w.qn, idx->maxn, c_round,
+                                                                            l2 ? 1 : 0, w.qmargin, w.thr_g);
         BFK_CUDA(cudaGetLastError());
         CUtensorMap tmQ, tmX;
         BFK_TRY(make_tmap(&tmQ, w.q16, pl.nq_pad, idx->ld16, TC_BM));
@@ -606,20 +712,38 @@ int search_tensor(bfk_index* idx, const float* q_dev, int ldq, int64_t nq, int k
         p.smem_bytes = (int)pl.smem;
         p.is_l2 = l2 ? 1 : 0;
         p.nq = (int)nqc;
-        p.pend = w.pend;
+        p.thr_g = w.thr_g;
+        p.qmargin = w.qmargin;
         p.out_cand = w.out_cand;
         p.out_thr = w.out_thr;
+        static const bool dbg_on = getenv("BFK_TC_DEBUG") != nullptr;
+        static const bool parked = getenv("BFK_TC_PARKED") != nullptr;
+        p.dbg = dbg_on ? w.dbg : nullptr;
+        p.parked = parked ? 1 : 0;
+        if (dbg_on) BFK_CUDA(cudaMemsetAsync(w.dbg, 0, (size_t)pl.grid * 64, st));
         if (ev0 && q0 == 0) cudaEventRecord(ev0, st);
         if (pl.KP == 16)
             BFK_TRY(launch_scan_tc<16>(tmQ, tmX, p, pl, st));
         else
             BFK_TRY(launch_scan_tc<32>(tmQ, tmX, p, pl, st));
         if (ev1 && q0 + chunk >= nq) cudaEventRecord(ev1, st);
+        if (p.dbg) {  // diagnostics only: per-role wait cycles averaged over the CTAs
+            std::vector<unsigned long long> h((size_t)pl.grid * 8);
+            BFK_CUDA(cudaMemcpyAsync(h.data(), w.dbg, h.size() * 8, cudaMemcpyDeviceToHost, st));
+            BFK_CUDA(cudaStreamSynchronize(st));
+            double a[8] = {0};
+            for (int c = 0; c < pl.grid; c++)
+                for (int j = 0; j < 8; j++) a[j] += (double)h[(size_t)c * 8 + j] / pl.grid;
+            fprintf(stderr,
+                    "[bfk tc] grid=%d QT=%d S=%d KP=%d tiles/cta=%.1f | cycles/cta: life=%.0f tma_wait_empty=%.0f "
+                    "mma_wait_full=%.0f mma_wait_tmem=%.0f epi_wait_acc=%.0f epi_flush=%.0f | appended/thread=%.0f flushes=%.1f\n",
+                    pl.grid, pl.QT, pl.S, pl.KP, (double)pl.tiles_total / pl.S, a[7], a[0], a[1], a[2], a[3], a[4], a[5], a[6]);
+        }
 
         RerankParams r;
         r.out_cand = w.out_cand;
         r.out_thr = w.out_thr;
-        r.qn = w.qn;
+        r.qmargin = w.qmargin;
         r.q = qc;
         r.ldq = ldq;
         r.S = pl.S;
@@ -632,10 +756,6 @@ int search_tensor(bfk_index* idx, const float* q_dev, int ldq, int64_t nq, int k
         r.x16 = idx->x16;
         r.ld16 = idx->ld16;
         r.d = idx->d;
-        r.maxn = idx->maxn;
-        // |<q,x> - <bf16(q),bf16(x)>| <= (2u + u^2) ||q|| ||x|| with u = 2^-9 when both operands are
-        // rounded, u ||q|| ||x|| when the corpus is stored in bf16; + 2^-14 for tensor-core accumulation
-        r.c_round = (idx->storage == BFK_STORE_F32 ? 1.01f / 256.f : 1.01f / 512.f) + 1.0f / 16384.f;
         r.id_offset = id_offset;
         r.D = D_dev + (size_t)q0 * k;
         r.I = I_dev + (size_t)q0 * k;

@@ -57,7 +57,7 @@ def test_tensor_path_random(bfk, metric, d, nq):
     xb, xq = unit(rng, n, d), unit(rng, nq, d)
     idx = bfk.IndexFlat(d, metric)
     idx.add(xb)
-    for k in (1, 10, 32):
+    for k in (1, 10, 24):
         D, I, st = run(bfk, idx, xq, k)
         check_knn(D, I, xq, xb, k, metric, tight=True)
         De, Ie = idx.search(xq, k, algo="exact")
@@ -132,7 +132,7 @@ def test_tensor_path_limits_and_auto_dispatch(bfk):
     idx = bfk.IndexFlatL2(384)
     idx.add(xb)
     with pytest.raises(RuntimeError):
-        idx.search(xq, 100, algo="tensor")  # k > 32 is served by the exact path only (for now)
+        idx.search(xq, 100, algo="tensor")  # k > 24 is served by the exact path only (for now)
     st = bfk.SearchStats()
     D, I = idx.search(xq, 100, stats=st)
     assert st.algo_used == bfk.ALGO_EXACT_SIMT
