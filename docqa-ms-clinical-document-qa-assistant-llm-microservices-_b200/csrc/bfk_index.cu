@@ -48,7 +48,8 @@ static int alloc_storage(bfk_index* idx, int64_t cap, float** x32, __nv_bfloat16
     cudaError_t e = cudaSuccess;
     if (idx->storage == BFK_STORE_F32) e = cudaMalloc((void**)x32, sizeof(float) * (size_t)cap * idx->ld32);
     if (e == cudaSuccess) e = cudaMalloc((void**)x16, sizeof(__nv_bfloat16) * (size_t)cap * idx->ld16);
-    if (e == cudaSuccess) e = cudaMalloc((void**)nrm, sizeof(float) * (size_t)cap);
+    // norms are fetched a whole 256-row tile at a time (1 KiB bulk copies): pad to the tile
+    if (e == cudaSuccess) e = cudaMalloc((void**)nrm, sizeof(float) * (size_t)round_up(cap, 256));
     if (e != cudaSuccess) {
         cudaGetLastError();
         if (*x32) cudaFree(*x32);

@@ -56,7 +56,7 @@ constexpr int TC_SMEM_LIMIT = 232448;    // 227 KiB
 constexpr int TC_RMAX = 64;              // exact re-scores per query at most
 constexpr int TC_MERGE_N = 4096;
 constexpr int TC_PEND_BYTES = TC_BUFCAP * 256 * 8;  // 32 KiB
-constexpr int TC_TAIL_BYTES = 2 * TC_BN * 4 + (2 * TC_MAX_STAGES + 5) * 8 + 16;  // bias + barriers + tmem slot
+constexpr int TC_TAIL_BYTES = 2 * TC_BN * 4 + (2 * TC_MAX_STAGES + 7) * 8 + 16 + 128 * 4;  // bias + barriers + tmem slot/flag + thr_sh
 
 struct TcParams {
     const float* nrm;
@@ -68,7 +68,11 @@ struct TcParams {
     int smem_bytes;      // dynamic shared memory given to the launch
     int is_l2;
     int nq;
-    unsigned int* thr_g; // [nq_pad] ordered bits of the best KP-th key any thread has seen, per query
+    unsigned int* slots; // [nq_pad][KP] ordered key bits, slot (g*J + j) = min over the thread-streams of
+                         // group g of their j-th best key: KP distinct rows, so max over the slots bounds
+                         // the global KP-th best key of the query from above
+    int G;               // groups (power of two, G*J == KP)
+    int J;               // ranks each thread publishes
     const float* qmargin;  // [nq_pad] 2*eps in key space (see prep_queries_kernel)
     uint64_t* out_cand;  // [QT*128][S][KP]
     float* out_thr;      // [QT*128][S]
@@ -106,7 +110,10 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
     uint64_t* q_bar = empty_bar + TC_MAX_STAGES;
     uint64_t* tfull_bar = q_bar + 1;   // [2]
     uint64_t* tempty_bar = tfull_bar + 2;  // [2]
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+    uint64_t* nfull_bar = tempty_bar + 2;  // [2] norms of the tile have landed in bias slot a
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(nfull_bar + 2);
+    volatile int* done_flag = reinterpret_cast<volatile int*>(tmem_slot + 1);
+    float* thr_sh = reinterpret_cast<float*>(tmem_slot + 4);  // [128] bound on the global KP-th best key per query row
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     unsigned long long dbg_acc[4] = {0, 0, 0, 0};
@@ -125,9 +132,13 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
         for (int a = 0; a < 2; a++) {
             mbar_init(&tfull_bar[a], 1);
             mbar_init(&tempty_bar[a], TC_EPI_THREADS);
+            mbar_init(&nfull_bar[a], 1);
         }
         fence_mbar_init();
     }
+    if (tid < 128) thr_sh[tid] = FLT_MAX;
+    for (int i = tid; i < 2 * TC_BN; i += TC_THREADS) bias_s[i] = 0.f;  // inner product: no bias
+    if (tid == 0) *done_flag = 0;
     if (warp == 2) tmem_alloc<512>(tmem_slot);
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmQ);
@@ -166,6 +177,12 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
                 const uint32_t a = tcount & 1u, aph = (tcount >> 1) & 1u;
                 TC_WAIT(&tempty_bar[a], aph ^ 1u, 2);  // epilogue has drained this accumulator
                 tc_fence_after();
+                if (p.is_l2) {
+                    // bias slot a is free for the same reason: fetch this tile's 256 squared norms now, they
+                    // land long before the epilogue reaches the tile
+                    mbar_expect_tx(&nfull_bar[a], TC_BN * 4);
+                    bulk_g2s(bias_s + a * TC_BN, p.nrm + t * TC_BN, TC_BN * 4, &nfull_bar[a]);
+                }
                 const uint32_t d_tmem = tmem_base + a * TC_BN;
                 for (int kb = 0; kb < p.KB; kb++, it++) {
                     const int st = it % stages;
@@ -187,6 +204,32 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
                 p.dbg[blockIdx.x * 8 + 2] = dbg_acc[2];
             }
         }
+    } else if (warp == 3) {
+        // ===================== threshold helper =====================
+        // keeps thr_sh[row] = max over the query's KP published slots (an upper bound on its global
+        // KP-th best key) fresh, so the epilogue never waits on global memory for it
+        const unsigned int unset = f2ord(FLT_MAX);
+        while (*done_flag == 0) {
+#pragma unroll 1
+            for (int rr = 0; rr < 4; rr++) {
+                const int row = rr * 32 + lane;
+                const int qrow = qt * TC_BM + row;
+                if (qrow < p.nq) {
+                    const uint4* sl = reinterpret_cast<const uint4*>(p.slots + (size_t)qrow * KP);
+                    unsigned int m = 0;
+#pragma unroll
+                    for (int i = 0; i < KP / 4; i++) {
+                        uint4 v;
+                        asm volatile("ld.global.cg.v4.u32 {%0, %1, %2, %3}, [%4];"
+                                     : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+                                     : "l"(sl + i));
+                        m = max(max(m, v.x), max(max(v.y, v.z), v.w));
+                    }
+                    if (m < unset) thr_sh[row] = ord2f(m);
+                }
+            }
+            __nanosleep(1000);
+        }
     } else if (warp >= 4) {
         // ============ epilogue: 8 warps; thread == (query row, column half of the tile) ============
         const int et = tid - 128;          // 0..255
@@ -205,33 +248,35 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
         // query + the query's error margin): rows above it can be neither in this thread's top-KP nor
         // within the margin band of the global top-KP, which is all K5's certificate needs
         const float qmargin = active ? p.qmargin[qrow] : 0.f;
-        unsigned int* thr_g = p.thr_g + (active ? qrow : 0);
+        unsigned int* my_slots = p.slots + (size_t)(active ? qrow : 0) * KP;
+        const int grp = (s * 2 + half) & (p.G - 1);
         float thr = active ? FLT_MAX : -FLT_MAX;
         int cnt = 0;
         uint64_t* my_pend = pend_s + et;   // [slot][thread] in shared memory
         const float scale = p.is_l2 ? -2.0f : -1.0f;
 
+        // sorted insert without a dependency chain: every slot decides from the OLD neighbours
         auto insert = [&](float x, uint32_t xi) {
+            bool cj = x < skey[KP - 1];
 #pragma unroll
-            for (int j = 0; j < KP; j++) {
-                const bool sw = x < skey[j];
-                const float tk = skey[j];
-                const uint32_t ti = sidx[j];
-                skey[j] = sw ? x : tk;
-                sidx[j] = sw ? xi : ti;
-                x = sw ? tk : x;
-                xi = sw ? ti : xi;
+            for (int j = KP - 1; j >= 1; j--) {
+                const bool cjm1 = x < skey[j - 1];
+                skey[j] = cjm1 ? skey[j - 1] : (cj ? x : skey[j]);
+                sidx[j] = cjm1 ? sidx[j - 1] : (cj ? xi : sidx[j]);
+                cj = cjm1;
             }
+            skey[0] = cj ? x : skey[0];
+            sidx[0] = cj ? xi : sidx[0];
         };
         auto refresh_thr = [&]() {
             if (active) {
-                const float g = ord2f(*reinterpret_cast<volatile unsigned int*>(thr_g));
+                const float g = *reinterpret_cast<volatile float*>(thr_sh + row);
                 thr = fminf(skey[KP - 1], g < FLT_MAX ? g + qmargin : FLT_MAX);
             }
         };
         auto flush = [&]() {
             const int maxc = __reduce_max_sync(0xffffffffu, cnt);
-#pragma unroll 2
+#pragma unroll 1
             for (int i = 0; i < maxc; i++) {
                 const bool has = i < cnt;
                 const uint64_t e = my_pend[(size_t)i * TC_EPI_THREADS];
@@ -239,70 +284,92 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
                 if (has && x < skey[KP - 1]) insert(x, (uint32_t)e);
             }
             cnt = 0;
-            if (active && skey[KP - 1] < FLT_MAX) atomicMin(thr_g, f2ord(skey[KP - 1]));
+            if (active) {
+#pragma unroll
+                for (int j = 0; j < KP; j++)
+                    if (j < p.J && skey[j] < FLT_MAX) atomicMin(my_slots + grp * p.J + j, f2ord(skey[j]));
+            }
             refresh_thr();
         };
 
         uint32_t tcount = 0;
         for (int64_t t = t_begin; t < t_end; t++, tcount++) {
             const uint32_t a = tcount & 1u, aph = (tcount >> 1) & 1u;
-            {
-                const int64_t col = t * TC_BN + et;
-                bias_s[a * TC_BN + et] = (col < p.n) ? (p.is_l2 ? __ldg(p.nrm + col) : 0.f) : INFINITY;
-            }
-            refresh_thr();  // pick up what other CTAs learned while this tile was being computed
+            refresh_thr();
             {
                 const long long _t0 = p.dbg ? clock64() : 0;
-                epi_sync();
-                mbar_wait(&tfull_bar[a], aph);
+                mbar_wait(&tfull_bar[a], aph);  // accumulator complete
+                if (p.is_l2) mbar_wait(&nfull_bar[a], aph);  // and the tile's norms have landed
                 if (p.dbg) dbg_acc[0] += (unsigned long long)(clock64() - _t0);
+            }
+            if ((t + 1) * TC_BN > p.n) {  // ragged last tile of the corpus: columns past the end never win
+                if (t * TC_BN + et >= p.n) bias_s[a * TC_BN + et] = INFINITY;
+                epi_sync();
             }
             tc_fence_after();
             const uint32_t taddr = tmem_base + ((uint32_t)(((warp - 4) & 3) * 32) << 16) + a * TC_BN + half * 128;
             const uint32_t col0 = (uint32_t)(t * TC_BN) + half * 128;
             const float* bias = bias_s + a * TC_BN + half * 128;
-#pragma unroll 1
-            for (int c0 = 0; c0 < 128; c0 += 32) {
-                uint32_t r[32];
-                tmem_ld_32x32(taddr + c0, r);
-                tmem_ld_wait();
+            // 16 columns at a time, kept as a rolled loop (two register sets, next load in flight while
+            // the current set is filtered): the fully unrolled form of this loop was 58 KB of SASS and
+            // stalled on instruction fetch
+            auto process16 = [&](const uint32_t (&r)[16], int c0) {
                 const float4* b4 = reinterpret_cast<const float4*>(bias + c0);
+                float kk[16];
 #pragma unroll
-                for (int j4 = 0; j4 < 8; j4++) {
+                for (int j4 = 0; j4 < 4; j4++) {
                     const float4 b = b4[j4];
-                    const float k0 = fmaf(scale, __uint_as_float(r[4 * j4 + 0]), b.x);
-                    const float k1 = fmaf(scale, __uint_as_float(r[4 * j4 + 1]), b.y);
-                    const float k2 = fmaf(scale, __uint_as_float(r[4 * j4 + 2]), b.z);
-                    const float k3 = fmaf(scale, __uint_as_float(r[4 * j4 + 3]), b.w);
-                    const float kmin = fminf(fminf(k0, k1), fminf(k2, k3));
-                    // most groups of 4 have no survivor in any lane: one vote skips the append code
-                    if (__any_sync(0xffffffffu, kmin < thr)) {
-                        const float kk[4] = {k0, k1, k2, k3};
+                    kk[4 * j4 + 0] = fmaf(scale, __uint_as_float(r[4 * j4 + 0]), b.x);
+                    kk[4 * j4 + 1] = fmaf(scale, __uint_as_float(r[4 * j4 + 1]), b.y);
+                    kk[4 * j4 + 2] = fmaf(scale, __uint_as_float(r[4 * j4 + 2]), b.z);
+                    kk[4 * j4 + 3] = fmaf(scale, __uint_as_float(r[4 * j4 + 3]), b.w);
+                }
+                float kmin = kk[0];
 #pragma unroll
-                        for (int e = 0; e < 4; e++) {
-                            if (kk[e] < thr) {
-                                my_pend[(size_t)cnt * TC_EPI_THREADS] =
-                                    ((uint64_t)__float_as_uint(kk[e]) << 32) | (uint64_t)(col0 + c0 + 4 * j4 + e);
-                                cnt++;
-                            }
+                for (int j = 1; j < 16; j++) kmin = fminf(kmin, kk[j]);
+                // after the first tiles most groups of 16 have no survivor in any lane
+                if (__any_sync(0xffffffffu, kmin < thr)) {
+                    unsigned int hm = 0;
+#pragma unroll
+                    for (int j = 0; j < 16; j++) hm |= (kk[j] < thr) ? (1u << j) : 0u;
+                    // flush only when this group's survivors would not fit behind the pending ones, so
+                    // one flush serves many groups
+                    if (__any_sync(0xffffffffu, cnt + __popc(hm) > TC_BUFCAP)) {
+                        const long long _t0 = p.dbg ? clock64() : 0;
+                        dbg_acc[2] += (unsigned long long)cnt;
+                        flush();
+                        if (p.dbg) {
+                            dbg_acc[1] += (unsigned long long)(clock64() - _t0);
+                            dbg_acc[3] += 1;
                         }
-                        if (__any_sync(0xffffffffu, cnt > TC_BUFCAP - 4)) {
-                            const long long _t0 = p.dbg ? clock64() : 0;
-                            dbg_acc[2] += (unsigned long long)cnt;
-                            flush();
-                            if (p.dbg) {
-                                dbg_acc[1] += (unsigned long long)(clock64() - _t0);
-                                dbg_acc[3] += 1;
-                            }
+                    }
+#pragma unroll
+                    for (int j = 0; j < 16; j++) {
+                        if (hm & (1u << j)) {
+                            my_pend[(size_t)cnt * TC_EPI_THREADS] =
+                                ((uint64_t)__float_as_uint(kk[j]) << 32) | (uint64_t)(col0 + c0 + j);
+                            cnt++;
                         }
                     }
                 }
+            };
+            uint32_t ra[16], rb[16];
+            tmem_ld_32x16(taddr, ra);
+#pragma unroll 1
+            for (int sc = 0; sc < 8; sc += 2) {
+                tmem_ld_wait();
+                tmem_ld_32x16(taddr + (sc + 1) * 16, rb);
+                process16(ra, sc * 16);
+                tmem_ld_wait();
+                if (sc + 2 < 8) tmem_ld_32x16(taddr + (sc + 2) * 16, ra);
+                process16(rb, (sc + 1) * 16);
             }
             tc_fence_before();
             mbar_arrive(&tempty_bar[a]);
         }
         dbg_acc[2] += (unsigned long long)cnt;
         flush();
+        if (et == 0) *done_flag = 1;
         if (p.dbg && et == 0) {
             p.dbg[blockIdx.x * 8 + 3] = dbg_acc[0];                         // epilogue: waiting for an accumulator
             p.dbg[blockIdx.x * 8 + 4] = dbg_acc[1];                         // epilogue: cycles inside flush()
@@ -356,7 +423,7 @@ __global__ void __launch_bounds__(256) prep_queries_kernel(const float* __restri
                                                            int64_t nq_pad, __nv_bfloat16* __restrict__ q16, int ld16,
                                                            float* __restrict__ qn, const unsigned int* __restrict__ maxn,
                                                            float c_round, int is_l2, float* __restrict__ qmargin,
-                                                           unsigned int* __restrict__ thr_g) {
+                                                           unsigned int* __restrict__ slots, int KP) {
     const int lane = threadIdx.x & 31;
     const int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (row >= nq_pad) return;
@@ -373,8 +440,8 @@ __global__ void __launch_bounds__(256) prep_queries_kernel(const float* __restri
         // 2*eps in key space: |<q,x> - <bf16 q, bf16 x>| <= c_round ||q|| max||x||; L2 keys carry 2x that
         const float mx = __uint_as_float(*maxn);
         qmargin[row] = (is_l2 ? 4.f : 2.f) * c_round * sqrtf(ss * mx) + 1e-6f * (ss + mx);
-        thr_g[row] = f2ord(FLT_MAX);
     }
+    if (lane < KP) slots[row * KP + lane] = f2ord(FLT_MAX);
 }
 
 struct RerankParams {
@@ -610,7 +677,7 @@ int tensor_path_supported(const bfk_index* idx, int64_t nq, int k) {
 struct TcWs {
     __nv_bfloat16* q16;
     float* qn;
-    unsigned int* thr_g;
+    unsigned int* slots;
     float* qmargin;
     uint64_t* out_cand;
     float* out_thr;
@@ -633,7 +700,7 @@ static void tc_carve(const bfk_index* idx, int64_t nqc, int k, const TcPlan& pl,
     };
     w->q16 = (__nv_bfloat16*)take((size_t)pl.nq_pad * idx->ld16 * 2);
     w->qn = (float*)take((size_t)pl.nq_pad * 4);
-    w->thr_g = (unsigned int*)take((size_t)pl.nq_pad * 4);
+    w->slots = (unsigned int*)take((size_t)pl.nq_pad * pl.KP * 4);
     w->qmargin = (float*)take((size_t)pl.nq_pad * 4);
     w->out_cand = (uint64_t*)take((size_t)pl.nq_pad * pl.S * pl.KP * 8);
     w->out_thr = (float*)take((size_t)pl.nq_pad * pl.S * 4);
@@ -697,7 +764,7 @@ int search_tensor(bfk_index* idx, const float* q_dev, int ldq, int64_t nq, int k
         const float c_round = (idx->storage == BFK_STORE_F32 ? 1.01f / 256.f : 1.01f / 512.f) + 1.0f / 16384.f;
         prep_queries_kernel<<<(unsigned)((pl.nq_pad + 7) / 8), 256, 0, st>>>(qc, ldq, idx->d, nqc, pl.nq_pad, w.q16,
                                                                             idx->ld16, w.qn, idx->maxn, c_round,
-                                                                            l2 ? 1 : 0, w.qmargin, w.thr_g);
+                                                                            l2 ? 1 : 0, w.qmargin, w.slots, pl.KP);
         BFK_CUDA(cudaGetLastError());
         CUtensorMap tmQ, tmX;
         BFK_TRY(make_tmap(&tmQ, w.q16, pl.nq_pad, idx->ld16, TC_BM));
@@ -712,7 +779,13 @@ int search_tensor(bfk_index* idx, const float* q_dev, int ldq, int64_t nq, int k
         p.smem_bytes = (int)pl.smem;
         p.is_l2 = l2 ? 1 : 0;
         p.nq = (int)nqc;
-        p.thr_g = w.thr_g;
+        p.slots = w.slots;
+        {
+            int G = 1;
+            while (G * 2 <= std::min(16, 2 * pl.S) && G * 2 <= pl.KP) G *= 2;
+            p.G = G;
+            p.J = pl.KP / G;
+        }
         p.qmargin = w.qmargin;
         p.out_cand = w.out_cand;
         p.out_thr = w.out_thr;
