@@ -96,9 +96,36 @@ def gen_unit_rows(torch, n, d, seed, device, chunk=1 << 20):
         yield r0, x
 
 
-def scan_bytes(n_rows, d_bytes, nq, k, l2_norm_bytes=0):
-    """one corpus pass + norms + queries + results."""
-    return n_rows * d_bytes + n_rows * l2_norm_bytes + nq * D * 4 + nq * k * 12
+def roofline_of(res, nq, n_rows, elem, hbm_peak, tf_peak, peak_kind):
+    """Roofline of the dominant (scan) kernel for one measured batch size.
+
+    Algorithmic work per launch follows SURVEY 8(d) / DESIGN.md section 4:
+      exact SIMT scan (<= 8 queries per corpus pass): N*d*s bytes + queries + per-CTA lists
+      tensor scan, HBM regime (nq <= 128): N*d*2 (bf16 copy) + N*4 (norms) + nq*d*2 + lists
+      tensor scan, tensor regime (nq > 128): 2*nq*N*d flop
+    `launch_ms` is the library's own CUDA-event bracket around the scan launches of one search.
+    """
+    if res["algo"] == "exact_simt":
+        passes = -(-nq // 8)
+        per_q = min(nq, 8)
+        bytes_launch = n_rows * D * elem + per_q * D * 4 + per_q * K * 8 * 148
+        launch_ms = res["scan_ms"] / passes
+        ach = bytes_launch / (launch_ms * 1e-3) / 1e9 if launch_ms > 0 else 0.0
+        return {"bound": "hbm", "kernel": "scan_exact_kernel", "achieved": ach, "peak": hbm_peak, "unit": "GB/s",
+                "frac": ach / hbm_peak, "peak_kind": peak_kind, "bytes_per_launch": bytes_launch,
+                "launch_ms": launch_ms, "launches_per_step": passes, "traffic": None}
+    launch_ms = res["scan_ms"]
+    if nq <= 128:
+        bytes_launch = n_rows * D * 2 + n_rows * 4 + nq * D * 2 + nq * 148 * 16 * 12
+        ach = bytes_launch / (launch_ms * 1e-3) / 1e9 if launch_ms > 0 else 0.0
+        return {"bound": "hbm", "kernel": "scan_tc_kernel", "achieved": ach, "peak": hbm_peak, "unit": "GB/s",
+                "frac": ach / hbm_peak, "peak_kind": peak_kind, "bytes_per_launch": bytes_launch,
+                "launch_ms": launch_ms, "launches_per_step": 1, "traffic": None}
+    flops = 2.0 * nq * n_rows * D
+    ach = flops / (launch_ms * 1e-3) / 1e12 if launch_ms > 0 else 0.0
+    return {"bound": "tensor", "kernel": "scan_tc_kernel", "achieved": ach, "peak": tf_peak, "unit": "TFLOP/s",
+            "frac": ach / tf_peak, "peak_kind": peak_kind + " (burst bf16 GEMM)", "flops_per_launch": flops,
+            "launch_ms": launch_ms, "launches_per_step": 1, "traffic": None}
 
 
 def run_reference(args):
@@ -160,7 +187,7 @@ def main():
     ap.add_argument("--rows", type=int, default=None, help="override corpus rows (debugging)")
     ap.add_argument("--algo", default=None, choices=[None, "auto", "exact", "tensor"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--batches", default="1,64,1024", help="extra batch sizes reported under `batches`")
+    ap.add_argument("--batches", default="1,64,1024,4096", help="extra batch sizes reported under `batches`")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     if args.impl == "reference":
@@ -297,18 +324,10 @@ def main():
     hbm_peak, tf_peak, peak_kind = peaks()
     elem = 4 if storage == "f32" else 2
     n_local = hi - lo
-    passes = -(-args.nq // 8) if head["algo"] == "exact_simt" else 1
-    per_launch_q = min(args.nq, 8) if head["algo"] == "exact_simt" else args.nq
-    if head["algo"] == "exact_simt":
-        bytes_launch = n_local * D * elem + per_launch_q * D * 4 + per_launch_q * K * 8 * 148
-    else:
-        bytes_launch = scan_bytes(n_local, 2, args.nq, K, l2_norm_bytes=4)
-    launch_ms = head["scan_ms"] / passes
-    achieved = bytes_launch / (launch_ms * 1e-3) / 1e9 if launch_ms > 0 else 0.0
-    roofline = {"bound": "hbm", "kernel": "scan_exact_kernel" if head["algo"] == "exact_simt" else "scan_tc_kernel",
-                "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
-                "peak_kind": peak_kind, "bytes_per_launch": bytes_launch, "launch_ms": launch_ms,
-                "launches_per_step": passes, "traffic": None}
+    roofline = roofline_of(head, args.nq, n_local, elem, hbm_peak, tf_peak, peak_kind)
+    for b, r in extra.items():
+        r["roofline"] = roofline_of({"algo": r["algo"], "scan_ms": r["scan_ms"]}, int(b), n_local, elem, hbm_peak,
+                                    tf_peak, peak_kind)
 
     # ---- CPU baseline on this box (rank 0, N = 1 only) ----
     cpu = None

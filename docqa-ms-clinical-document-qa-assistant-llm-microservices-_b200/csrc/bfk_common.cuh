@@ -82,6 +82,7 @@ struct bfk_index {
     unsigned int* maxn = nullptr;
     bfk::Workspace ws;       // search scratch, grow-only
     cudaEvent_t ws_free = nullptr;  // recorded after the last search that used `ws`
+    int* h_flag = nullptr;          // pinned host word: count of uncertified queries (tensor path)
     std::mutex mu;
 };
 

@@ -144,7 +144,8 @@ static int make_index(int d, int metric, int device, int storage, bfk_index** ou
     }
     if (cudaMalloc((void**)&idx->maxn, sizeof(unsigned int)) != cudaSuccess ||
         cudaMemset(idx->maxn, 0, sizeof(unsigned int)) != cudaSuccess ||
-        cudaEventCreateWithFlags(&idx->ws_free, cudaEventDisableTiming) != cudaSuccess) {
+        cudaEventCreateWithFlags(&idx->ws_free, cudaEventDisableTiming) != cudaSuccess ||
+        cudaHostAlloc((void**)&idx->h_flag, sizeof(int), cudaHostAllocDefault) != cudaSuccess) {
         delete idx;
         return fail(std::string("index allocation failed: ") + cudaGetErrorString(cudaGetLastError()));
     }
@@ -291,6 +292,7 @@ int bfk_free(bfk_index* idx) {
     if (idx->ws.ptr) cudaFree(idx->ws.ptr);
     if (idx->maxn) cudaFree(idx->maxn);
     if (idx->ws_free) cudaEventDestroy(idx->ws_free);
+    if (idx->h_flag) cudaFreeHost(idx->h_flag);
     delete idx;
     return 0;
 }

@@ -485,51 +485,54 @@ __device__ void rr_bitonic(uint64_t* a, int n, int tid, int nthr) {
     }
 }
 
-__global__ void __launch_bounds__(256) rerank_kernel(const RerankParams p) {
+constexpr int RR_THREADS = 512;
+
+__global__ void __launch_bounds__(RR_THREADS) rerank_kernel(const RerankParams p) {
     __shared__ uint64_t buf[TC_MERGE_N];
     __shared__ uint64_t ex[TC_RMAX];
     __shared__ float q_s[BFK_MAX_D];
-    __shared__ float red[8];
+    __shared__ float red[RR_THREADS / 32];
     __shared__ int info[4];
+    __shared__ int cnt_s;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int64_t q = blockIdx.x;
     const int64_t M = (int64_t)p.S * p.KP;
     const uint64_t* src = p.out_cand + q * M;
 
-    for (int c = tid; c < p.ld32; c += 256) q_s[c] = (c < p.ldq) ? p.q[q * p.ldq + c] : 0.f;
-    // min over streams of the drop threshold
+    for (int c = tid; c < p.ld32; c += RR_THREADS) q_s[c] = (c < p.ldq) ? p.q[q * p.ldq + c] : 0.f;
+    // T = min over streams of the drop threshold: every row some stream dropped has approximate key >= T
     float tmin = FLT_MAX;
-    for (int s = tid; s < p.S; s += 256) tmin = fminf(tmin, p.out_thr[q * p.S + s]);
+    for (int s = tid; s < p.S; s += RR_THREADS) tmin = fminf(tmin, p.out_thr[q * p.S + s]);
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) tmin = fminf(tmin, __shfl_xor_sync(0xffffffffu, tmin, o));
     if (lane == 0) red[warp] = tmin;
+    if (tid == 0) cnt_s = 0;
+    __syncthreads();
+    tmin = red[0];
+#pragma unroll
+    for (int w = 1; w < RR_THREADS / 32; w++) tmin = fminf(tmin, red[w]);
 
-    // ---- merge by approximate key: the best TC_RMAX end up sorted at the front of buf ----
-    int window;
-    if (M <= TC_MERGE_N) {
-        int n = TC_RMAX;
-        while (n < M) n <<= 1;
-        for (int i = tid; i < n; i += 256) buf[i] = (i < M) ? src[i] : COMP_EMPTY;
-        __syncthreads();
-        rr_bitonic(buf, n, tid, 256);
-        window = n;
-    } else {
-        const int step = TC_MERGE_N - TC_RMAX;
-        for (int i = tid; i < TC_RMAX; i += 256) buf[i] = COMP_EMPTY;
-        for (int64_t base = 0; base < M; base += step) {
-            for (int i = tid; i < step; i += 256) buf[TC_RMAX + i] = (base + i < M) ? src[base + i] : COMP_EMPTY;
-            __syncthreads();
-            rr_bitonic(buf, TC_MERGE_N, tid, 256);
+    // ---- keep only candidates with approximate key <= T (a certified answer never needs the rest:
+    //      the cut A_k + 2*eps must lie below T), then sort the few survivors ----
+    for (int64_t i = tid; i < M; i += RR_THREADS) {
+        const uint64_t c = src[i];
+        if (c != COMP_EMPTY && ord2f((uint32_t)(c >> 32)) <= tmin) {
+            const int slot = atomicAdd(&cnt_s, 1);
+            if (slot < TC_MERGE_N) buf[slot] = c;
         }
-        window = TC_MERGE_N;
     }
-    (void)window;
-    tmin = fminf(fminf(fminf(red[0], red[1]), fminf(red[2], red[3])), fminf(fminf(red[4], red[5]), fminf(red[6], red[7])));
+    __syncthreads();
+    const int total = cnt_s;
+    const int cnt = min(total, TC_MERGE_N);
+    int n = TC_RMAX;
+    while (n < cnt) n <<= 1;
+    for (int i = cnt + tid; i < n; i += RR_THREADS) buf[i] = COMP_EMPTY;
+    __syncthreads();
+    rr_bitonic(buf, n, tid, RR_THREADS);
 
     // ---- the cut: A_k + 2*eps in approximate-key space ----
     if (tid == 0) {
-        int nvalid = 0;
-        while (nvalid < TC_RMAX && buf[nvalid] != COMP_EMPTY) nvalid++;
+        const int nvalid = min(cnt, TC_RMAX);
         int R = 0;
         int certified = 1;
         if (nvalid > 0) {
@@ -538,19 +541,20 @@ __global__ void __launch_bounds__(256) rerank_kernel(const RerankParams p) {
             const float cut = a_k + p.qmargin[q];
             while (R < nvalid && ord2f((uint32_t)(buf[R] >> 32)) <= cut) R++;
             if (R < kk) R = kk;
-            // rows a stream dropped have approximate key >= its T; rows beyond the window >= buf[RMAX-1]
-            if (!(tmin > cut)) certified = 0;
-            if (R == TC_RMAX && M > TC_RMAX) certified = 0;
+            if (!(tmin > cut)) certified = 0;          // a dropped row could still reach the cut
+            if (total > TC_MERGE_N) certified = 0;     // survivors did not fit the sort window
+            if (R == TC_RMAX && cnt > TC_RMAX && ord2f((uint32_t)(buf[TC_RMAX] >> 32)) <= cut)
+                certified = 0;                         // more rows inside the cut than we re-score
         }
         info[0] = R;
         info[1] = certified;
     }
-    for (int i = tid; i < TC_RMAX; i += 256) ex[i] = COMP_EMPTY;
+    for (int i = tid; i < TC_RMAX; i += RR_THREADS) ex[i] = COMP_EMPTY;
     __syncthreads();
     const int R = info[0];
 
     // ---- exact re-score of the R survivors (faiss's direct-difference arithmetic) ----
-    for (int i = warp; i < R; i += 8) {
+    for (int i = warp; i < R; i += RR_THREADS / 32) {
         const uint32_t id = (uint32_t)(buf[i] & 0xffffffffu);
         float acc = 0.f;
         if (p.storage == BFK_STORE_F32) {
@@ -586,8 +590,8 @@ __global__ void __launch_bounds__(256) rerank_kernel(const RerankParams p) {
         }
     }
     __syncthreads();
-    rr_bitonic(ex, TC_RMAX, tid, 256);
-    for (int i = tid; i < p.k; i += 256) {
+    rr_bitonic(ex, TC_RMAX, tid, RR_THREADS);
+    for (int i = tid; i < p.k; i += RR_THREADS) {
         const uint64_t c = (i < TC_RMAX) ? ex[i] : COMP_EMPTY;
         float dv;
         int64_t iv;
@@ -834,14 +838,14 @@ int search_tensor(bfk_index* idx, const float* q_dev, int ldq, int64_t nq, int k
         r.I = I_dev + (size_t)q0 * k;
         r.nflag = w.flags;
         r.flag_list = w.flags + 1;
-        rerank_kernel<<<(unsigned)nqc, 256, 0, st>>>(r);
+        rerank_kernel<<<(unsigned)nqc, RR_THREADS, 0, st>>>(r);
         BFK_CUDA(cudaGetLastError());
         launches += 3;
 
         // ---- uncertified queries: exact re-run on the GPU (K3a + K4) ----
-        int nflag = 0;
-        BFK_CUDA(cudaMemcpyAsync(&nflag, w.flags, sizeof(int), cudaMemcpyDeviceToHost, st));
+        BFK_CUDA(cudaMemcpyAsync(idx->h_flag, w.flags, sizeof(int), cudaMemcpyDeviceToHost, st));
         BFK_CUDA(cudaStreamSynchronize(st));
+        const int nflag = *idx->h_flag;
         if (nflag > 0) {
             std::vector<int> list((size_t)nflag);
             BFK_CUDA(cudaMemcpyAsync(list.data(), w.flags + 1, sizeof(int) * (size_t)nflag, cudaMemcpyDeviceToHost, st));
