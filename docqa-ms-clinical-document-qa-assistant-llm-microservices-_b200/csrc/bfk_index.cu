@@ -404,7 +404,10 @@ int bfk_search_ex(bfk_index* idx, const float* q, int64_t nq, int64_t k64, float
     std::lock_guard<std::mutex> lk(idx->mu);
 
     if (algo == BFK_ALGO_AUTO) {
-        algo = (nq > 8 && tensor_path_supported(idx, nq, k)) ? BFK_ALGO_TENSOR : BFK_ALGO_EXACT_SIMT;
+        // fp32 rows: up to 8 queries the exact scan is one HBM-speed pass; bf16-stored rows scan faster
+        // through the tensor path at any batch size
+        algo = ((nq > 8 || idx->storage == BFK_STORE_BF16) && tensor_path_supported(idx, nq, k)) ? BFK_ALGO_TENSOR
+                                                                                                  : BFK_ALGO_EXACT_SIMT;
     } else if (algo == BFK_ALGO_TENSOR) {
         if (!tensor_path_supported(idx, nq, k)) return fail("search: tensor path does not support this shape");
     } else if (algo != BFK_ALGO_EXACT_SIMT) {

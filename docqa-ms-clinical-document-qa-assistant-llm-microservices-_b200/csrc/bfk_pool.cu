@@ -14,27 +14,64 @@
 
 namespace bfk {
 
+// Token loads are split into "fetch the raw 16 bytes" and "convert + accumulate" so that the
+// kernel can issue all of a batch's loads before touching any of them (8 x 16 B in flight per
+// thread); fused load+convert made the compiler serialise them on one destination register.
+// Eight predicated 128-bit read-only loads in ONE PTX block.  Written as separate statements, ptxas
+// interleaves each load with the arithmetic on the previous one to save registers, which leaves a
+// single 16-byte load in flight per thread and a quarter of HBM bandwidth; as one block all eight
+// issue back to back.  A false predicate touches no memory and yields zeros.
+__device__ __forceinline__ void ldg128_x8_if(const void* const (&p)[8], const unsigned (&on)[8], uint4 (&r)[8]) {
+    asm volatile(
+        "{\n\t.reg .pred q0, q1, q2, q3, q4, q5, q6, q7;\n\t"
+        "setp.ne.u32 q0, %40, 0;\n\tsetp.ne.u32 q1, %41, 0;\n\tsetp.ne.u32 q2, %42, 0;\n\tsetp.ne.u32 q3, %43, 0;\n\t"
+        "setp.ne.u32 q4, %44, 0;\n\tsetp.ne.u32 q5, %45, 0;\n\tsetp.ne.u32 q6, %46, 0;\n\tsetp.ne.u32 q7, %47, 0;\n\t"
+        "mov.u32 %0, 0;\n\tmov.u32 %1, 0;\n\tmov.u32 %2, 0;\n\tmov.u32 %3, 0;\n\t"
+        "mov.u32 %4, 0;\n\tmov.u32 %5, 0;\n\tmov.u32 %6, 0;\n\tmov.u32 %7, 0;\n\t"
+        "mov.u32 %8, 0;\n\tmov.u32 %9, 0;\n\tmov.u32 %10, 0;\n\tmov.u32 %11, 0;\n\t"
+        "mov.u32 %12, 0;\n\tmov.u32 %13, 0;\n\tmov.u32 %14, 0;\n\tmov.u32 %15, 0;\n\t"
+        "mov.u32 %16, 0;\n\tmov.u32 %17, 0;\n\tmov.u32 %18, 0;\n\tmov.u32 %19, 0;\n\t"
+        "mov.u32 %20, 0;\n\tmov.u32 %21, 0;\n\tmov.u32 %22, 0;\n\tmov.u32 %23, 0;\n\t"
+        "mov.u32 %24, 0;\n\tmov.u32 %25, 0;\n\tmov.u32 %26, 0;\n\tmov.u32 %27, 0;\n\t"
+        "mov.u32 %28, 0;\n\tmov.u32 %29, 0;\n\tmov.u32 %30, 0;\n\tmov.u32 %31, 0;\n\t"
+        "@q0 ld.global.nc.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%32];\n\t"
+        "@q1 ld.global.nc.L1::no_allocate.v4.u32 {%4, %5, %6, %7}, [%33];\n\t"
+        "@q2 ld.global.nc.L1::no_allocate.v4.u32 {%8, %9, %10, %11}, [%34];\n\t"
+        "@q3 ld.global.nc.L1::no_allocate.v4.u32 {%12, %13, %14, %15}, [%35];\n\t"
+        "@q4 ld.global.nc.L1::no_allocate.v4.u32 {%16, %17, %18, %19}, [%36];\n\t"
+        "@q5 ld.global.nc.L1::no_allocate.v4.u32 {%20, %21, %22, %23}, [%37];\n\t"
+        "@q6 ld.global.nc.L1::no_allocate.v4.u32 {%24, %25, %26, %27}, [%38];\n\t"
+        "@q7 ld.global.nc.L1::no_allocate.v4.u32 {%28, %29, %30, %31}, [%39];\n\t}"
+        : "=r"(r[0].x), "=r"(r[0].y), "=r"(r[0].z), "=r"(r[0].w), "=r"(r[1].x), "=r"(r[1].y), "=r"(r[1].z), "=r"(r[1].w),
+          "=r"(r[2].x), "=r"(r[2].y), "=r"(r[2].z), "=r"(r[2].w), "=r"(r[3].x), "=r"(r[3].y), "=r"(r[3].z), "=r"(r[3].w),
+          "=r"(r[4].x), "=r"(r[4].y), "=r"(r[4].z), "=r"(r[4].w), "=r"(r[5].x), "=r"(r[5].y), "=r"(r[5].z), "=r"(r[5].w),
+          "=r"(r[6].x), "=r"(r[6].y), "=r"(r[6].z), "=r"(r[6].w), "=r"(r[7].x), "=r"(r[7].y), "=r"(r[7].z), "=r"(r[7].w)
+        : "l"(p[0]), "l"(p[1]), "l"(p[2]), "l"(p[3]), "l"(p[4]), "l"(p[5]), "l"(p[6]), "l"(p[7]), "r"(on[0]), "r"(on[1]),
+          "r"(on[2]), "r"(on[3]), "r"(on[4]), "r"(on[5]), "r"(on[6]), "r"(on[7]));
+}
+
 template <typename T>
 struct TokLoad;
 template <>
 struct TokLoad<float> {
     static constexpr int VEC = 4;
-    __device__ static __forceinline__ void vec(const float* p, float (&v)[4]) {
-        float4 t = __ldg(reinterpret_cast<const float4*>(p));
-        v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+    __device__ static __forceinline__ void fma(const uint4& t, float m, float (&acc)[4]) {
+        acc[0] = fmaf(__uint_as_float(t.x), m, acc[0]);
+        acc[1] = fmaf(__uint_as_float(t.y), m, acc[1]);
+        acc[2] = fmaf(__uint_as_float(t.z), m, acc[2]);
+        acc[3] = fmaf(__uint_as_float(t.w), m, acc[3]);
     }
     __device__ static __forceinline__ float one(const float* p) { return __ldg(p); }
 };
 template <>
 struct TokLoad<__nv_bfloat16> {
     static constexpr int VEC = 8;
-    __device__ static __forceinline__ void vec(const __nv_bfloat16* p, float (&v)[8]) {
-        uint4 t = __ldg(reinterpret_cast<const uint4*>(p));
+    __device__ static __forceinline__ void fma(const uint4& t, float m, float (&acc)[8]) {
         const uint32_t w[4] = {t.x, t.y, t.z, t.w};
 #pragma unroll
         for (int i = 0; i < 4; i++) {
-            v[2 * i] = __uint_as_float(w[i] << 16);
-            v[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u);
+            acc[2 * i] = fmaf(__uint_as_float(w[i] << 16), m, acc[2 * i]);
+            acc[2 * i + 1] = fmaf(__uint_as_float(w[i] & 0xffff0000u), m, acc[2 * i + 1]);
         }
     }
     __device__ static __forceinline__ float one(const __nv_bfloat16* p) { return __bfloat162float(*p); }
@@ -42,15 +79,13 @@ struct TokLoad<__nv_bfloat16> {
 template <>
 struct TokLoad<__half> {
     static constexpr int VEC = 8;
-    __device__ static __forceinline__ void vec(const __half* p, float (&v)[8]) {
-        uint4 t = __ldg(reinterpret_cast<const uint4*>(p));
+    __device__ static __forceinline__ void fma(const uint4& t, float m, float (&acc)[8]) {
         const uint32_t w[4] = {t.x, t.y, t.z, t.w};
 #pragma unroll
         for (int i = 0; i < 4; i++) {
-            __half2 h = *reinterpret_cast<const __half2*>(&w[i]);
-            float2 f = __half22float2(h);
-            v[2 * i] = f.x;
-            v[2 * i + 1] = f.y;
+            const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&w[i]));
+            acc[2 * i] = fmaf(f.x, m, acc[2 * i]);
+            acc[2 * i + 1] = fmaf(f.y, m, acc[2 * i + 1]);
         }
     }
     __device__ static __forceinline__ float one(const __half* p) { return __half2float(*p); }
@@ -107,27 +142,32 @@ __global__ void __launch_bounds__(512) pool_norm_kernel(const TokT* __restrict__
         const TokT* base = tok + (size_t)b * T * H + (size_t)cv * VEC;
         constexpr int UN = 8;
         for (int t0 = tg; t0 < T; t0 += TG * UN) {
-            float v[UN][VEC];
             float m[UN];
+            if constexpr (VECTOR) {
+                uint4 raw[UN];
+                const void* ptr[UN];
+                unsigned on[UN];
 #pragma unroll
-            for (int u = 0; u < UN; u++) {
-                const int t = t0 + u * TG;
-                m[u] = (t < T) ? mask_s[t] : 0.f;
-                if (m[u] != 0.f) {
-                    if constexpr (VECTOR) {
-                        TokLoad<TokT>::vec(base + (size_t)t * H, v[u]);
-                    } else {
-                        v[u][0] = TokLoad<TokT>::one(base + (size_t)t * H);
-                    }
-                } else {
-#pragma unroll
-                    for (int e = 0; e < VEC; e++) v[u][e] = 0.f;
+                for (int u = 0; u < UN; u++) {
+                    const int t = t0 + u * TG;
+                    m[u] = (t < T) ? mask_s[t] : 0.f;
+                    on[u] = m[u] != 0.f;
+                    ptr[u] = base + (size_t)min(t, T - 1) * H;
                 }
+                ldg128_x8_if(ptr, on, raw);
+#pragma unroll
+                for (int u = 0; u < UN; u++) TokLoad<TokT>::fma(raw[u], m[u], acc);
+            } else {
+                float v[UN];
+#pragma unroll
+                for (int u = 0; u < UN; u++) {
+                    const int t = t0 + u * TG;
+                    m[u] = (t < T) ? mask_s[t] : 0.f;
+                    v[u] = (m[u] != 0.f) ? TokLoad<TokT>::one(base + (size_t)t * H) : 0.f;
+                }
+#pragma unroll
+                for (int u = 0; u < UN; u++) acc[0] = fmaf(v[u], m[u], acc[0]);
             }
-#pragma unroll
-            for (int u = 0; u < UN; u++)
-#pragma unroll
-                for (int e = 0; e < VEC; e++) acc[e] = fmaf(v[u][e], m[u], acc[e]);
         }
 #pragma unroll
         for (int e = 0; e < VEC; e++) red[(tg * CV + cv) * VEC + e] = acc[e];

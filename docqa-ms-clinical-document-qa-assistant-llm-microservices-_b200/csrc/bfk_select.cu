@@ -34,28 +34,71 @@ __device__ void block_bitonic_sort(uint64_t* a, int n, int tid, int nthr) {
 
 // cand [nq][m]; if `gather` != nullptr the low 32 bits of a composite index gather[q*... ]
 // (see pack_parts_kernel) instead of being the row id itself.
+// list_len > 0 promises that cand[q] is a concatenation of ascending lists of that length (the
+// per-CTA lists of K3a, the per-shard lists of K6).  Then a cheap bound on the k-th smallest
+// exists: split the lists into k groups, take each group's smallest head, and the largest of
+// those k distinct elements is >= the k-th smallest overall -- only the few composites under
+// that bound need sorting (a 64-element sort instead of a 2048-element one at nq = 1).
 __global__ void __launch_bounds__(SEL_THREADS) select_topk_kernel(const uint64_t* __restrict__ cand, int64_t m, int k,
-                                                                  int metric, int64_t id_offset,
+                                                                  int list_len, int metric, int64_t id_offset,
                                                                   const int64_t* __restrict__ gather, int64_t gather_q_stride,
                                                                   int64_t gather_p_stride, int gather_k,
                                                                   float* __restrict__ D, int64_t* __restrict__ I,
                                                                   int64_t out_ld) {
     __shared__ uint64_t buf[SEL_N];
+    __shared__ unsigned long long gmin[128];
+    __shared__ unsigned long long bound_s;
+    __shared__ int cnt_s;
     const int tid = threadIdx.x;
     const int64_t q = blockIdx.x;
     const uint64_t* src = cand + q * m;
+    bool done = false;
 
-    if (m <= SEL_N) {
+    const int64_t nlists = list_len > 0 ? m / list_len : 0;
+    if (list_len > 0 && k <= 128 && nlists >= k) {
+        if (tid < k) gmin[tid] = COMP_EMPTY;
+        if (tid == 0) {
+            bound_s = 0ull;
+            cnt_s = 0;
+        }
+        __syncthreads();
+        for (int64_t l = tid; l < nlists; l += SEL_THREADS) atomicMin(&gmin[l % k], (unsigned long long)src[l * list_len]);
+        __syncthreads();
+        if (tid < k) atomicMax(&bound_s, gmin[tid]);
+        __syncthreads();
+        const uint64_t bound = bound_s;
+        for (int64_t i = tid; i < m; i += SEL_THREADS) {
+            const uint64_t c = src[i];
+            if (c <= bound && c != COMP_EMPTY) {
+                const int slot = atomicAdd(&cnt_s, 1);
+                if (slot < SEL_N) buf[slot] = c;
+            }
+        }
+        __syncthreads();
+        const int cnt = cnt_s;
+        if (cnt <= SEL_N) {
+            int n = 32;
+            while (n < cnt || n < k) n <<= 1;
+            for (int i = cnt + tid; i < n; i += SEL_THREADS) buf[i] = COMP_EMPTY;
+            __syncthreads();
+            block_bitonic_sort(buf, n, tid, SEL_THREADS);
+            done = true;
+        }
+        // (more survivors than the window holds: only with massive ties; take the general path)
+    }
+    if (!done && m <= SEL_N) {
         int n = 32;
         while (n < m || n < k) n <<= 1;
+        __syncthreads();
         for (int i = tid; i < n; i += SEL_THREADS) buf[i] = (i < m) ? src[i] : COMP_EMPTY;
         __syncthreads();
         block_bitonic_sort(buf, n, tid, SEL_THREADS);
-    } else {
+    } else if (!done) {
         // keep the best kpad at the front, fold the rest through the window
         int kpad = 32;
         while (kpad < k) kpad <<= 1;
         const int step = SEL_N - kpad;
+        __syncthreads();
         for (int i = tid; i < kpad; i += SEL_THREADS) buf[i] = COMP_EMPTY;
         for (int64_t base = 0; base < m; base += step) {
             for (int i = tid; i < step; i += SEL_THREADS) buf[kpad + i] = (base + i < m) ? src[base + i] : COMP_EMPTY;
@@ -89,8 +132,9 @@ __global__ void __launch_bounds__(SEL_THREADS) select_topk_kernel(const uint64_t
 int launch_select(const uint64_t* cand, int64_t m_per_query, int64_t nq, int k, int metric, int64_t id_offset,
                   float* D, int64_t* I, int64_t out_ld, cudaStream_t st) {
     if (nq <= 0) return 0;
-    select_topk_kernel<<<(unsigned)nq, SEL_THREADS, 0, st>>>(cand, m_per_query, k, metric, id_offset, nullptr, 0, 0, 1,
-                                                            D, I, out_ld);
+    // every caller hands over ascending lists of length k (K3a's per-CTA lists)
+    select_topk_kernel<<<(unsigned)nq, SEL_THREADS, 0, st>>>(cand, m_per_query, k, k, metric, id_offset, nullptr, 0, 0,
+                                                            1, D, I, out_ld);
     BFK_CUDA(cudaGetLastError());
     return 0;
 }
@@ -147,8 +191,8 @@ extern "C" int bfk_merge_topk(const float* Dparts, const int64_t* Iparts, int np
     BFK_CUDA(cudaMallocAsync((void**)&cand, sizeof(uint64_t) * (size_t)nq * nparts * k, st));
     int rc = launch_pack_parts(Dparts, Iparts, nparts, nq, (int)k, metric, cand, st);
     if (!rc) {
-        select_topk_kernel<<<(unsigned)nq, SEL_THREADS, 0, st>>>(cand, (int64_t)nparts * k, (int)k, metric, 0, Iparts,
-                                                                k, nq * k, (int)k, D, I, k);
+        select_topk_kernel<<<(unsigned)nq, SEL_THREADS, 0, st>>>(cand, (int64_t)nparts * k, (int)k, (int)k, metric, 0,
+                                                                Iparts, k, nq * k, (int)k, D, I, k);
         if (cudaGetLastError() != cudaSuccess) rc = fail("merge_topk: launch failed");
     }
     cudaFreeAsync(cand, st);
