@@ -53,7 +53,7 @@ constexpr int TC_B_BLOCK = TC_BN * 128;  // bytes of one 64-column K-block of a 
 constexpr int TC_MAX_STAGES = 8;
 constexpr int TC_BUFCAP = 16;            // pending slots per epilogue thread (shared memory)
 constexpr int TC_SMEM_LIMIT = 232448;    // 227 KiB
-constexpr int TC_RMAX = 64;              // exact re-scores per query at most
+constexpr int TC_RMAX = 512;             // exact re-scores per query at most
 constexpr int TC_MERGE_N = 4096;
 constexpr int TC_PEND_BYTES = TC_BUFCAP * 256 * 8;  // 32 KiB
 constexpr int TC_TAIL_BYTES = 2 * TC_BN * 4 + (2 * TC_MAX_STAGES + 7) * 8 + 16 + 128 * 4;  // bias + barriers + tmem slot/flag + thr_sh
@@ -68,16 +68,18 @@ struct TcParams {
     int smem_bytes;      // dynamic shared memory given to the launch
     int is_l2;
     int nq;
-    unsigned int* slots; // [nq_pad][KP] ordered key bits, slot (g*J + j) = min over the thread-streams of
-                         // group g of their j-th best key: KP distinct rows, so max over the slots bounds
-                         // the global KP-th best key of the query from above
-    int G;               // groups (power of two, G*J == KP)
+    unsigned int* slots; // [nq_pad][NS] ordered key bits, slot (g*J + j) = min over the thread-streams of
+                         // group g of their j-th best key: NS distinct rows, so max over the slots bounds
+                         // the global NS-th (hence k-th, NS >= k) best key of the query from above
+    int NS;              // slots per query (multiple of 4, >= k)
+    int G;               // groups (power of two, G*J == NS, J <= KP)
     int J;               // ranks each thread publishes
     const float* qmargin;  // [nq_pad] 2*eps in key space (see prep_queries_kernel)
     uint64_t* out_cand;  // [QT*128][S][KP]
     float* out_thr;      // [QT*128][S]
     unsigned long long* dbg;  // optional [grid][8] cycle counters (BFK_TC_DEBUG=1), else nullptr
     int parked;          // producer/MMA waits use the suspend-time hint
+    int a_resident;      // query tile resident in smem (else its K-blocks stream with the corpus)
 };
 
 // wait flavour for the single-thread roles + optional cycle accounting
@@ -100,10 +102,12 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
     unsigned char* smem = smem_raw + pad;
     // stages: whatever fits after the resident query tile and the fixed tail (host sizes for pad = 0;
     // a misaligned base just costs one stage)
-    const int stages = min(TC_MAX_STAGES, (int)((p.smem_bytes - (int)pad - p.KB * TC_A_BLOCK - TC_PEND_BYTES - TC_TAIL_BYTES) / TC_B_BLOCK));
+    const int a_bytes = p.a_resident ? p.KB * TC_A_BLOCK : 0;
+    const int stage_bytes = p.a_resident ? TC_B_BLOCK : TC_B_BLOCK + TC_A_BLOCK;  // streamed: [B block | A block]
+    const int stages = min(TC_MAX_STAGES, (int)((p.smem_bytes - (int)pad - a_bytes - TC_PEND_BYTES - TC_TAIL_BYTES) / stage_bytes));
     unsigned char* sA = smem;
-    unsigned char* sB = sA + (size_t)p.KB * TC_A_BLOCK;
-    uint64_t* pend_s = reinterpret_cast<uint64_t*>(sB + (size_t)stages * TC_B_BLOCK);  // [TC_BUFCAP][256]
+    unsigned char* sB = sA + (size_t)a_bytes;
+    uint64_t* pend_s = reinterpret_cast<uint64_t*>(sB + (size_t)stages * stage_bytes);  // [TC_BUFCAP][256]
     float* bias_s = reinterpret_cast<float*>(reinterpret_cast<unsigned char*>(pend_s) + TC_PEND_BYTES);
     uint64_t* full_bar = reinterpret_cast<uint64_t*>(bias_s + 2 * TC_BN);
     uint64_t* empty_bar = full_bar + TC_MAX_STAGES;
@@ -152,16 +156,21 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
     if (warp == 0) {
         // ===================== TMA producer =====================
         if (lane == 0) {
-            mbar_expect_tx(q_bar, (uint32_t)p.KB * TC_A_BLOCK);
-            for (int kb = 0; kb < p.KB; kb++) tma_load_2d(sA + (size_t)kb * TC_A_BLOCK, &tmQ, kb * 64, qt * TC_BM, q_bar);
+            if (p.a_resident) {
+                mbar_expect_tx(q_bar, (uint32_t)p.KB * TC_A_BLOCK);
+                for (int kb = 0; kb < p.KB; kb++)
+                    tma_load_2d(sA + (size_t)kb * TC_A_BLOCK, &tmQ, kb * 64, qt * TC_BM, q_bar);
+            }
             uint32_t it = 0;
             for (int64_t t = t_begin; t < t_end; t++) {
                 for (int kb = 0; kb < p.KB; kb++, it++) {
                     const int st = it % stages;
                     const uint32_t ph = (it / stages) & 1u;
                     TC_WAIT(&empty_bar[st], ph ^ 1u, 0);
-                    mbar_expect_tx(&full_bar[st], TC_B_BLOCK);
-                    tma_load_2d(sB + (size_t)st * TC_B_BLOCK, &tmX, kb * 64, (int)(t * TC_BN), &full_bar[st]);
+                    mbar_expect_tx(&full_bar[st], (uint32_t)stage_bytes);
+                    tma_load_2d(sB + (size_t)st * stage_bytes, &tmX, kb * 64, (int)(t * TC_BN), &full_bar[st]);
+                    if (!p.a_resident)
+                        tma_load_2d(sB + (size_t)st * stage_bytes + TC_B_BLOCK, &tmQ, kb * 64, qt * TC_BM, &full_bar[st]);
                 }
             }
             if (p.dbg) p.dbg[blockIdx.x * 8 + 0] = dbg_acc[0];
@@ -171,7 +180,7 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
         if (lane == 0) {
             const uint32_t idesc = make_idesc_bf16(TC_BM, TC_BN);
             const uint32_t a_base = smem_u32(sA), b_base = smem_u32(sB);
-            TC_WAIT(q_bar, 0, 3);
+            if (p.a_resident) TC_WAIT(q_bar, 0, 3);
             uint32_t it = 0, tcount = 0;
             for (int64_t t = t_begin; t < t_end; t++, tcount++) {
                 const uint32_t a = tcount & 1u, aph = (tcount >> 1) & 1u;
@@ -191,8 +200,9 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
                     tc_fence_after();
 #pragma unroll
                     for (int kk = 0; kk < 4; kk++) {
-                        const uint64_t da = make_smem_desc_sw128(a_base + kb * TC_A_BLOCK + kk * 32);
-                        const uint64_t db = make_smem_desc_sw128(b_base + st * TC_B_BLOCK + kk * 32);
+                        const uint32_t a_blk = p.a_resident ? a_base + kb * TC_A_BLOCK : b_base + st * stage_bytes + TC_B_BLOCK;
+                        const uint64_t da = make_smem_desc_sw128(a_blk + kk * 32);
+                        const uint64_t db = make_smem_desc_sw128(b_base + st * stage_bytes + kk * 32);
                         umma_bf16(d_tmem, da, db, idesc, (kb | kk) != 0 ? 1u : 0u);
                     }
                     umma_commit(&empty_bar[st]);  // smem stage reusable once these MMAs retire
@@ -215,10 +225,10 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
                 const int row = rr * 32 + lane;
                 const int qrow = qt * TC_BM + row;
                 if (qrow < p.nq) {
-                    const uint4* sl = reinterpret_cast<const uint4*>(p.slots + (size_t)qrow * KP);
+                    const uint4* sl = reinterpret_cast<const uint4*>(p.slots + (size_t)qrow * p.NS);
                     unsigned int m = 0;
-#pragma unroll
-                    for (int i = 0; i < KP / 4; i++) {
+#pragma unroll 4
+                    for (int i = 0; i < p.NS / 4; i++) {
                         uint4 v;
                         asm volatile("ld.global.cg.v4.u32 {%0, %1, %2, %3}, [%4];"
                                      : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
@@ -248,7 +258,7 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
         // query + the query's error margin): rows above it can be neither in this thread's top-KP nor
         // within the margin band of the global top-KP, which is all K5's certificate needs
         const float qmargin = active ? p.qmargin[qrow] : 0.f;
-        unsigned int* my_slots = p.slots + (size_t)(active ? qrow : 0) * KP;
+        unsigned int* my_slots = p.slots + (size_t)(active ? qrow : 0) * p.NS;
         const int grp = (s * 2 + half) & (p.G - 1);
         float thr = active ? FLT_MAX : -FLT_MAX;
         int cnt = 0;
@@ -423,7 +433,7 @@ __global__ void __launch_bounds__(256) prep_queries_kernel(const float* __restri
                                                            int64_t nq_pad, __nv_bfloat16* __restrict__ q16, int ld16,
                                                            float* __restrict__ qn, const unsigned int* __restrict__ maxn,
                                                            float c_round, int is_l2, float* __restrict__ qmargin,
-                                                           unsigned int* __restrict__ slots, int KP) {
+                                                           unsigned int* __restrict__ slots, int NS) {
     const int lane = threadIdx.x & 31;
     const int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (row >= nq_pad) return;
@@ -441,7 +451,7 @@ __global__ void __launch_bounds__(256) prep_queries_kernel(const float* __restri
         const float mx = __uint_as_float(*maxn);
         qmargin[row] = (is_l2 ? 4.f : 2.f) * c_round * sqrtf(ss * mx) + 1e-6f * (ss + mx);
     }
-    if (lane < KP) slots[row * KP + lane] = f2ord(FLT_MAX);
+    for (int i = lane; i < NS; i += 32) slots[row * NS + i] = f2ord(FLT_MAX);
 }
 
 struct RerankParams {
@@ -524,7 +534,7 @@ __global__ void __launch_bounds__(RR_THREADS) rerank_kernel(const RerankParams p
     __syncthreads();
     const int total = cnt_s;
     const int cnt = min(total, TC_MERGE_N);
-    int n = TC_RMAX;
+    int n = 64;
     while (n < cnt) n <<= 1;
     for (int i = cnt + tid; i < n; i += RR_THREADS) buf[i] = COMP_EMPTY;
     __syncthreads();
@@ -552,6 +562,8 @@ __global__ void __launch_bounds__(RR_THREADS) rerank_kernel(const RerankParams p
     for (int i = tid; i < TC_RMAX; i += RR_THREADS) ex[i] = COMP_EMPTY;
     __syncthreads();
     const int R = info[0];
+    int n_ex = 32;
+    while (n_ex < R || n_ex < p.k) n_ex <<= 1;  // <= TC_RMAX since R, k <= TC_RMAX
 
     // ---- exact re-score of the R survivors (faiss's direct-difference arithmetic) ----
     for (int i = warp; i < R; i += RR_THREADS / 32) {
@@ -590,7 +602,7 @@ __global__ void __launch_bounds__(RR_THREADS) rerank_kernel(const RerankParams p
         }
     }
     __syncthreads();
-    rr_bitonic(ex, TC_RMAX, tid, RR_THREADS);
+    rr_bitonic(ex, min(n_ex, TC_RMAX), tid, RR_THREADS);
     for (int i = tid; i < p.k; i += RR_THREADS) {
         const uint64_t c = (i < TC_RMAX) ? ex[i] : COMP_EMPTY;
         float dv;
@@ -647,32 +659,50 @@ static int make_tmap(CUtensorMap* m, const void* base, int64_t rows, int ld, int
 }
 
 struct TcPlan {
-    int KB, stages, QT, S, KP, grid;
+    int KB, stages, QT, S, KP, NS, G, J, grid, a_resident;
     int64_t nq_pad, tiles_total;
     size_t smem;
 };
 
 static int tc_plan(const bfk_index* idx, int64_t nq, int k, TcPlan* pl) {
     pl->KB = idx->ld16 / 64;
-    const size_t fixed = (size_t)pl->KB * TC_A_BLOCK + TC_PEND_BYTES + TC_TAIL_BYTES;
-    if (fixed + 1024 + 2 * (size_t)TC_B_BLOCK > TC_SMEM_LIMIT) return 1;  // query tile cannot stay resident
-    pl->stages = (int)std::min<size_t>(TC_MAX_STAGES, (TC_SMEM_LIMIT - fixed) / TC_B_BLOCK);
-    pl->smem = fixed + (size_t)pl->stages * TC_B_BLOCK;
+    // the 128-query tile stays resident in shared memory when it leaves room for >= 3 corpus stages;
+    // otherwise (d > 384) its K-blocks stream through the ring next to the corpus K-blocks
+    const size_t tail = (size_t)TC_PEND_BYTES + TC_TAIL_BYTES;
+    const size_t res_fixed = (size_t)pl->KB * TC_A_BLOCK + tail;
+    pl->a_resident = (res_fixed + 3 * (size_t)TC_B_BLOCK <= TC_SMEM_LIMIT) ? 1 : 0;
+    const size_t fixed = pl->a_resident ? res_fixed : tail;
+    const size_t stage = pl->a_resident ? TC_B_BLOCK : TC_B_BLOCK + TC_A_BLOCK;
+    if (fixed + 2 * stage > TC_SMEM_LIMIT) return 1;
+    pl->stages = (int)std::min<size_t>(TC_MAX_STAGES, (TC_SMEM_LIMIT - fixed) / stage);
+    pl->smem = fixed + (size_t)pl->stages * stage;
     pl->QT = (int)((nq + TC_BM - 1) / TC_BM);
     pl->nq_pad = (int64_t)pl->QT * TC_BM;
     pl->tiles_total = (idx->ntotal + TC_BN - 1) / TC_BN;
     pl->S = (int)std::max<int64_t>(1, std::min<int64_t>(idx->num_sms / pl->QT, pl->tiles_total));
     pl->grid = pl->QT * pl->S;
-    // KP slots per (query, stream): the candidates inside the error band of the global top-k must fit
-    // in the streams' lists, so few streams need longer lists
-    pl->KP = (k <= 12 && pl->S >= 8) ? 16 : 32;  // KP must exceed k: the certificate needs A_KP > A_k
+    // KP list slots per (query, thread-stream).  The certificate is global: the streams' lists together
+    // must hold the k best rows plus the error band, so KP may be smaller than k when there are many
+    // streams; few streams get the longer lists.
+    pl->KP = (k <= 12 && pl->S >= 8) ? 16 : 32;
+    const int TS = 2 * pl->S;  // thread-streams per query
+    if (k > 24 && (int64_t)TS * pl->KP < 3 * (int64_t)k) return 1;  // lists too short to certify: exact path
+    // NS >= k published slots bound the global k-th best key; G groups x J ranks
+    int NS = pl->KP;
+    while (NS < k + k / 4) NS <<= 1;
+    int G = 1;
+    while (G * 2 <= std::min(16, TS) && G * 2 <= NS) G *= 2;
+    if (NS / G > pl->KP) G = NS / pl->KP;  // ranks per thread cannot exceed its list (extra groups stay unset)
+    pl->NS = NS;
+    pl->G = G;
+    pl->J = NS / G;
     return 0;
 }
 
 static int64_t tc_chunk_queries(const bfk_index* idx) { return (int64_t)idx->num_sms * TC_BM; }
 
 int tensor_path_supported(const bfk_index* idx, int64_t nq, int k) {
-    if (k > 24 || nq <= 0 || idx->ntotal <= 0) return 0;
+    if (k > 128 || nq <= 0 || idx->ntotal <= 0) return 0;
     TcPlan pl;
     if (tc_plan(idx, std::min<int64_t>(nq, tc_chunk_queries(idx)), k, &pl)) return 0;
     return get_encode_fn() != nullptr;
@@ -704,7 +734,7 @@ static void tc_carve(const bfk_index* idx, int64_t nqc, int k, const TcPlan& pl,
     };
     w->q16 = (__nv_bfloat16*)take((size_t)pl.nq_pad * idx->ld16 * 2);
     w->qn = (float*)take((size_t)pl.nq_pad * 4);
-    w->slots = (unsigned int*)take((size_t)pl.nq_pad * pl.KP * 4);
+    w->slots = (unsigned int*)take((size_t)pl.nq_pad * pl.NS * 4);
     w->qmargin = (float*)take((size_t)pl.nq_pad * 4);
     w->out_cand = (uint64_t*)take((size_t)pl.nq_pad * pl.S * pl.KP * 8);
     w->out_thr = (float*)take((size_t)pl.nq_pad * pl.S * 4);
@@ -768,7 +798,7 @@ int search_tensor(bfk_index* idx, const float* q_dev, int ldq, int64_t nq, int k
         const float c_round = (idx->storage == BFK_STORE_F32 ? 1.01f / 256.f : 1.01f / 512.f) + 1.0f / 16384.f;
         prep_queries_kernel<<<(unsigned)((pl.nq_pad + 7) / 8), 256, 0, st>>>(qc, ldq, idx->d, nqc, pl.nq_pad, w.q16,
                                                                             idx->ld16, w.qn, idx->maxn, c_round,
-                                                                            l2 ? 1 : 0, w.qmargin, w.slots, pl.KP);
+                                                                            l2 ? 1 : 0, w.qmargin, w.slots, pl.NS);
         BFK_CUDA(cudaGetLastError());
         CUtensorMap tmQ, tmX;
         BFK_TRY(make_tmap(&tmQ, w.q16, pl.nq_pad, idx->ld16, TC_BM));
@@ -784,12 +814,10 @@ int search_tensor(bfk_index* idx, const float* q_dev, int ldq, int64_t nq, int k
         p.is_l2 = l2 ? 1 : 0;
         p.nq = (int)nqc;
         p.slots = w.slots;
-        {
-            int G = 1;
-            while (G * 2 <= std::min(16, 2 * pl.S) && G * 2 <= pl.KP) G *= 2;
-            p.G = G;
-            p.J = pl.KP / G;
-        }
+        p.NS = pl.NS;
+        p.G = pl.G;
+        p.J = pl.J;
+        p.a_resident = pl.a_resident;
         p.qmargin = w.qmargin;
         p.out_cand = w.out_cand;
         p.out_thr = w.out_thr;

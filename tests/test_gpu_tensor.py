@@ -132,15 +132,38 @@ def test_tensor_path_limits_and_auto_dispatch(bfk):
     idx = bfk.IndexFlatL2(384)
     idx.add(xb)
     with pytest.raises(RuntimeError):
-        idx.search(xq, 100, algo="tensor")  # k > 24 is served by the exact path only (for now)
+        idx.search(xq, 200, algo="tensor")  # k > 128 is served by the exact path only
     st = bfk.SearchStats()
-    D, I = idx.search(xq, 100, stats=st)
+    D, I = idx.search(xq, 200, stats=st)
     assert st.algo_used == bfk.ALGO_EXACT_SIMT
-    check_knn(D, I, xq, xb, 100, L2, tight=True)
+    check_knn(D, I, xq, xb, 200, L2, tight=True)
     D, I = idx.search(xq, 10, stats=st)
     assert st.algo_used == bfk.ALGO_TENSOR
     D, I = idx.search(xq[:8], 10, stats=st)
     assert st.algo_used == bfk.ALGO_EXACT_SIMT
+
+
+@pytest.mark.parametrize("metric", [L2, IP])
+@pytest.mark.parametrize("storage", ["f32", "bf16"])
+def test_tensor_path_k100_and_d768(bfk, metric, storage):
+    """BASELINE config 3 in miniature: 768-d rows (query tile streamed, not resident), k = 100."""
+    import torch
+
+    rng = np.random.default_rng(8)
+    xb, xq = unit(rng, 60000, 768), unit(rng, 300, 768)
+    ref = xb if storage == "f32" else torch.from_numpy(xb).to(torch.bfloat16).to(torch.float32).numpy()
+    idx = bfk.IndexFlat(768, metric, storage=storage)
+    idx.add(xb)
+    for k in (10, 100, 128):
+        D, I, st = run(bfk, idx, xq, k)
+        check_knn(D, I, xq, ref, k, metric, tight=True)
+        assert st.n_fallback <= 3, (k, st.n_fallback)
+    # 384-d, k = 100 on a batch of one query tile
+    xb2, xq2 = unit(rng, 40000, 384), unit(rng, 50, 384)
+    idx2 = bfk.IndexFlat(384, metric)
+    idx2.add(xb2)
+    D, I, st = run(bfk, idx2, xq2, 100)
+    check_knn(D, I, xq2, xb2, 100, metric, tight=True)
 
 
 def test_tensor_path_full_size_1m_x_384(bfk):
