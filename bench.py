@@ -35,6 +35,7 @@ import numpy as np  # noqa: E402
 METRIC = "kNN queries/sec at k=10"
 K = 10
 D = 384
+METRIC_ID = 1  # faiss METRIC_L2; config 3 switches to inner product (0), d = 768, k = 100
 CORPUS_SEED, QUERY_SEED = 1234, 4321
 
 
@@ -116,7 +117,7 @@ def roofline_of(res, nq, n_rows, elem, hbm_peak, tf_peak, peak_kind):
                 "launch_ms": launch_ms, "launches_per_step": passes, "traffic": None}
     launch_ms = res["scan_ms"]
     if nq <= 128:
-        bytes_launch = n_rows * D * 2 + n_rows * 4 + nq * D * 2 + nq * 148 * 16 * 12
+        bytes_launch = n_rows * D * 2 + (n_rows * 4 if METRIC_ID == 1 else 0) + nq * D * 2 + nq * 148 * 16 * 12
         ach = bytes_launch / (launch_ms * 1e-3) / 1e9 if launch_ms > 0 else 0.0
         return {"bound": "hbm", "kernel": "scan_tc_kernel", "achieved": ach, "peak": hbm_peak, "unit": "GB/s",
                 "frac": ach / hbm_peak, "peak_kind": peak_kind, "bytes_per_launch": bytes_launch,
@@ -198,7 +199,7 @@ def run_reference(args):
 
     cpu_baseline.build()
     workload = args.workload or ("c2" if args.gpus == 1 else "c5")
-    n_full = 1_000_000 if workload == "c2" else 100_000_000
+    n_full = {"c2": 1_000_000, "c3": 10_000_000}.get(workload, 100_000_000)
     n_sample = 1_000_000
     rng = np.random.default_rng(CORPUS_SEED)
     xb = rng.standard_normal((n_sample, D), dtype=np.float32)
@@ -209,9 +210,9 @@ def run_reference(args):
 
     def step():
         if args.nq < 20:
-            cpu_baseline.knn_seq(xq, xb, K)
+            cpu_baseline.knn_seq(xq, xb, K, METRIC_ID)
         else:
-            cpu_baseline.knn_blas(xq, xb, K, bn=bn)
+            cpu_baseline.knn_blas(xq, xb, K, METRIC_ID, bn=bn)
 
     for _ in range(args.warmup):
         step()
@@ -229,7 +230,7 @@ def run_reference(args):
         "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3 / scale, "higher_is_better": True,
         "scaling": "strong" if args.gpus > 1 else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "impl": "reference",
-        "config": {"workload": f"{workload}: {n_full}x{D} corpus, IndexFlatL2, k={K}, nq={args.nq}",
+        "config": {"workload": f"{workload}: {n_full}x{D} corpus, {'IndexFlatL2' if METRIC_ID == 1 else 'IndexFlatIP'}, k={K}, nq={args.nq}",
                    "reference_kind": "CPU restatement of faiss-cpu IndexFlatL2.search (faiss not installable here)"},
         "cpu_baseline": {"value": qps, "unit": "queries/s", "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": qps, "unit": "queries/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -242,8 +243,8 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
-    ap.add_argument("--nq", type=int, default=64)
-    ap.add_argument("--workload", choices=["c2", "c5", "c4"], default=None)
+    ap.add_argument("--nq", type=int, default=None)
+    ap.add_argument("--workload", choices=["c2", "c3", "c5", "c4"], default=None)
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--rows", type=int, default=None, help="override corpus rows (debugging)")
     ap.add_argument("--algo", default=None, choices=[None, "auto", "exact", "tensor"])
@@ -251,6 +252,13 @@ def main():
     ap.add_argument("--batches", default="1,64,1024,4096", help="extra batch sizes reported under `batches`")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
+    global D, K, METRIC_ID, METRIC
+    if args.workload == "c3":  # BASELINE config 3: 10M x 768 bf16-stored, IndexFlatIP, batch 4096, k = 100
+        D, K, METRIC_ID, METRIC = 768, 100, 0, "kNN queries/sec at k=100"
+        args.nq = args.nq or 4096
+        if args.batches == "1,64,1024,4096":
+            args.batches = ""
+    args.nq = args.nq or 64
     if args.impl == "reference":
         return run_reference(args)
     if args.workload == "c4":
@@ -276,16 +284,18 @@ def main():
     workload = args.workload or ("c2" if world == 1 else "c5")
     if workload == "c2":
         n_total, storage, scaling = args.rows or 1_000_000, "f32", "weak" if world == 1 else "strong"
+    elif workload == "c3":
+        n_total, storage, scaling = args.rows or 10_000_000, "bf16", "weak" if world == 1 else "strong"
     else:
         n_total, storage, scaling = args.rows or 100_000_000, "bf16", "strong"
     lo, hi = bfk.shard_range(n_total, rank, world)
 
     # ---- build the (sharded) index on the device ----
     if world > 1:
-        index = bfk.ShardedIndexFlat(D, bfk.METRIC_L2, device=local_rank, storage=storage)
+        index = bfk.ShardedIndexFlat(D, METRIC_ID, device=local_rank, storage=storage)
         local = index.local
     else:
-        index = local = bfk.IndexFlatL2(D, device=local_rank, storage=storage)
+        index = local = bfk.IndexFlat(D, METRIC_ID, device=local_rank, storage=storage)
     local.reserve(hi - lo)
     # every rank draws the same global stream and keeps its slice, so the corpus does not depend on N
     for r0, x in gen_unit_rows(torch, n_total, D, CORPUS_SEED, dev):
@@ -409,8 +419,8 @@ def main():
         xb_h = local.reconstruct_n(0, min(n_local, 1_000_000))
         xq_h = queries(args.nq).cpu().numpy()
         bn = np.einsum("ij,ij->i", xb_h, xb_h, dtype=np.float32)
-        fn = (lambda: cpu_baseline.knn_seq(xq_h, xb_h, K)) if args.nq < 20 else (
-            lambda: cpu_baseline.knn_blas(xq_h, xb_h, K, bn=bn))
+        fn = (lambda: cpu_baseline.knn_seq(xq_h, xb_h, K, METRIC_ID)) if args.nq < 20 else (
+            lambda: cpu_baseline.knn_blas(xq_h, xb_h, K, METRIC_ID, bn=bn))
         fn()
         t0 = time.perf_counter()
         reps = 0
@@ -431,7 +441,7 @@ def main():
             "vs_baseline": None, "dtype": "f32" if head["algo"] == "exact_simt" else "bf16 scan + f32 rerank",
             "data": "synthetic",
             "config": {"workload": f"{workload}: {n_total}x{D} {'fp32' if storage == 'f32' else 'bf16-stored'} corpus, "
-                                   f"IndexFlatL2, k={K}, nq={args.nq}" + (f", row-sharded over {world} GPUs" if world > 1 else ""),
+                                   f"{'IndexFlatL2' if METRIC_ID == 1 else 'IndexFlatIP'}, k={K}, nq={args.nq}" + (f", row-sharded over {world} GPUs" if world > 1 else ""),
                        "l2_policy": "corpus pass (>= 0.77 GB/GPU at N=1) far exceeds the 126 MB L2; no flush needed",
                        "algo": head["algo"]},
             "e2e": head["e2e"], "gpu_launches": head["launches_per_step"] * args.steps, "clocks": clocks,

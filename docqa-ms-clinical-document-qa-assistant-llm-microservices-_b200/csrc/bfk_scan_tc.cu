@@ -17,12 +17,11 @@
 //           the thread's threshold (one warp vote per 4 columns skips the common no-survivor
 //           case), append survivors to a per-thread pending list (coalesced [slot][thread] layout
 //           in global scratch); when a list fills, the warp flushes: every thread bubbles its own
-//           pending entries into a register-resident sorted top-KP, and the threshold tightens;
-//           at the end of the stream the two halves of a query are folded through shared memory
+//           pending entries into a register-resident sorted top-KP, and the threshold tightens
 //   CTA c works on query tile c % QT and corpus stream c / QT (a contiguous range of tiles), so
 //   CTAs sharing a stream walk the same corpus rows together and share them through L2.
-// Output per (query, stream): the KP best approximate keys + T = the KP-th key (every row the
-//   stream dropped has approximate key >= T).
+// Output per thread-stream (query, stream, column half): its KP best approximate keys + T, its final
+//   threshold (every row it dropped has approximate key >= T).
 //
 // K5 (one CTA per query): merge the streams' lists by approximate key; A_k = k-th best;
 //   everything with key <= A_k + 2*eps is re-scored exactly from the stored rows; eps bounds
@@ -75,8 +74,8 @@ struct TcParams {
     int G;               // groups (power of two, G*J == NS, J <= KP)
     int J;               // ranks each thread publishes
     const float* qmargin;  // [nq_pad] 2*eps in key space (see prep_queries_kernel)
-    uint64_t* out_cand;  // [QT*128][S][KP]
-    float* out_thr;      // [QT*128][S]
+    uint64_t* out_cand;  // [QT*128][2*S][KP]  one list per thread-stream (query, stream, column half)
+    float* out_thr;      // [QT*128][2*S]
     unsigned long long* dbg;  // optional [grid][8] cycle counters (BFK_TC_DEBUG=1), else nullptr
     int parked;          // producer/MMA waits use the suspend-time hint
     int a_resident;      // query tile resident in smem (else its K-blocks stream with the corpus)
@@ -387,36 +386,15 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
             p.dbg[blockIdx.x * 8 + 6] = dbg_acc[3];                         // flushes of warp 4
             p.dbg[blockIdx.x * 8 + 7] = (unsigned long long)(clock64() - dbg_t0);  // CTA lifetime
         }
-        // ---- fold the two column halves of every query: half 1 publishes through the (now idle)
-        //      corpus stages, half 0 absorbs and writes the stream's list and drop threshold ----
-        float* xk = reinterpret_cast<float*>(sB);
-        uint32_t* xi = reinterpret_cast<uint32_t*>(sB + (size_t)KP * 128 * 4);
-        float* xt = reinterpret_cast<float*>(sB + (size_t)KP * 128 * 8);
-        if (half == 1) {
+        // ---- every thread-stream (query, stream, column half) publishes its own list + drop threshold ----
+        if (active) {
+            const size_t ts = (size_t)qrow * (2 * p.S) + (size_t)s * 2 + half;
+            uint64_t* dst = p.out_cand + ts * KP;
 #pragma unroll
-            for (int i = 0; i < KP; i++) {
-                xk[i * 128 + row] = skey[i];
-                xi[i * 128 + row] = sidx[i];
-            }
-            xt[row] = thr;
-        }
-        epi_sync();
-        if (half == 0) {
-#pragma unroll 1
-            for (int i = 0; i < KP; i++) {
-                const float x = xk[i * 128 + row];
-                if (x < skey[KP - 1]) insert(x, xi[i * 128 + row]);
-            }
-            if (active) {
-                uint64_t* dst = p.out_cand + ((size_t)qrow * p.S + s) * KP;
-#pragma unroll
-                for (int i = 0; i < KP; i++)
-                    dst[i] = (sidx[i] == 0xffffffffu) ? COMP_EMPTY : make_comp(skey[i], sidx[i]);
-                // every row this stream dropped had key >= the threshold in force at that moment, and
-                // thresholds only fall: the smallest final threshold of the two halves (and of the
-                // folded list) bounds them all
-                p.out_thr[(size_t)qrow * p.S + s] = fminf(fminf(thr, xt[row]), skey[KP - 1]);
-            }
+            for (int i = 0; i < KP; i++) dst[i] = (sidx[i] == 0xffffffffu) ? COMP_EMPTY : make_comp(skey[i], sidx[i]);
+            // every row this thread dropped had key >= the threshold in force at that moment, and
+            // thresholds only fall
+            p.out_thr[ts] = fminf(thr, skey[KP - 1]);
         }
     }
 
@@ -686,7 +664,7 @@ static int tc_plan(const bfk_index* idx, int64_t nq, int k, TcPlan* pl) {
     // streams; few streams get the longer lists.
     pl->KP = (k <= 12 && pl->S >= 8) ? 16 : 32;
     const int TS = 2 * pl->S;  // thread-streams per query
-    if (k > 24 && (int64_t)TS * pl->KP < 3 * (int64_t)k) return 1;  // lists too short to certify: exact path
+    if (k > 24 && (int64_t)TS * pl->KP < 2 * (int64_t)k) return 1;  // lists too short to certify: exact path
     // NS >= k published slots bound the global k-th best key; G groups x J ranks
     int NS = pl->KP;
     while (NS < k + k / 4) NS <<= 1;
@@ -721,10 +699,17 @@ struct TcWs {
     int64_t* fb_I;   // [8][k]
     uint64_t* fb_part;
     unsigned long long* dbg;
+    // second-chance pass over the uncertified queries only (fewer queries -> more streams -> more list room)
+    int* r_list;     // [nq/2 + 1] query indices (copy of the first pass's flag list)
+    float* r_q;      // [nq/2][ldq]
+    float* r_D;      // [nq/2][k]
+    int64_t* r_I;    // [nq/2][k]
     size_t bytes;
 };
 
-static void tc_carve(const bfk_index* idx, int64_t nqc, int k, const TcPlan& pl, int fb_nparts, char* base, TcWs* w) {
+// sizes depend on the query count only (list space is bounded by the grid), so a workspace carved for
+// nqc queries also fits every smaller second-chance pass
+static void tc_carve(const bfk_index* idx, int64_t nqc, int k, int fb_nparts, char* base, TcWs* w) {
     size_t off = 0;
     auto take = [&](size_t bytes) {
         off = (size_t)round_up((int64_t)off, 256);
@@ -732,18 +717,27 @@ static void tc_carve(const bfk_index* idx, int64_t nqc, int k, const TcPlan& pl,
         off += bytes;
         return p;
     };
-    w->q16 = (__nv_bfloat16*)take((size_t)pl.nq_pad * idx->ld16 * 2);
-    w->qn = (float*)take((size_t)pl.nq_pad * 4);
-    w->slots = (unsigned int*)take((size_t)pl.nq_pad * pl.NS * 4);
-    w->qmargin = (float*)take((size_t)pl.nq_pad * 4);
-    w->out_cand = (uint64_t*)take((size_t)pl.nq_pad * pl.S * pl.KP * 8);
-    w->out_thr = (float*)take((size_t)pl.nq_pad * pl.S * 4);
+    const int64_t nq_pad = round_up(nqc, TC_BM);
+    int NS = 32;
+    while (NS < k + k / 4) NS <<= 1;
+    const size_t max_lists = (size_t)idx->num_sms * TC_BM * 2;  // thread-streams per launch, at most
+    w->q16 = (__nv_bfloat16*)take((size_t)nq_pad * idx->ld16 * 2);
+    w->qn = (float*)take((size_t)nq_pad * 4);
+    w->slots = (unsigned int*)take((size_t)nq_pad * NS * 4);
+    w->qmargin = (float*)take((size_t)nq_pad * 4);
+    w->out_cand = (uint64_t*)take(max_lists * 32 * 8);
+    w->out_thr = (float*)take(max_lists * 4);
     w->flags = (int*)take((size_t)(nqc + 1) * 4);
     w->fb_q = (float*)take((size_t)8 * idx->ld32 * 4);
     w->fb_D = (float*)take((size_t)8 * k * 4);
     w->fb_I = (int64_t*)take((size_t)8 * k * 8);
     w->fb_part = (uint64_t*)take((size_t)8 * fb_nparts * k * 8);
-    w->dbg = (unsigned long long*)take((size_t)pl.grid * 8 * 8);
+    w->dbg = (unsigned long long*)take((size_t)idx->num_sms * 8 * 8);
+    const int64_t nr = nqc / 2 + 1;
+    w->r_list = (int*)take((size_t)(nr + 1) * 4);
+    w->r_q = (float*)take((size_t)nr * idx->ld32 * 4);
+    w->r_D = (float*)take((size_t)nr * k * 4);
+    w->r_I = (int64_t*)take((size_t)nr * k * 8);
     w->bytes = off + 256;
 }
 
@@ -755,7 +749,7 @@ size_t tensor_workspace_bytes(const bfk_index* idx, int64_t nq, int k) {
     int nparts = 0;
     if (scan_exact_workspace(idx, 8, k, &sb, &nparts)) return 0;
     TcWs w;
-    tc_carve(idx, nqc, k, pl, nparts, nullptr, &w);
+    tc_carve(idx, nqc, k, nparts, nullptr, &w);
     return w.bytes;
 }
 
@@ -773,134 +767,196 @@ static int launch_scan_tc(const CUtensorMap& tmQ, const CUtensorMap& tmX, const 
     return 0;
 }
 
+// rows of (rD, rI) [n][k] -> rows list[i] of (D, I); and queries list[i] -> compact rows
+__global__ void __launch_bounds__(256) gather_queries_kernel(const float* __restrict__ q, int ldq, const int* __restrict__ list,
+                                                             int n, float* __restrict__ out) {
+    const int64_t total = (int64_t)n * ldq;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int r = (int)(i / ldq), c = (int)(i - (int64_t)r * ldq);
+        out[i] = q[(size_t)list[r] * ldq + c];
+    }
+}
+__global__ void __launch_bounds__(256) scatter_results_kernel(const float* __restrict__ rD, const int64_t* __restrict__ rI,
+                                                              const int* __restrict__ list, int n, int k,
+                                                              float* __restrict__ D, int64_t* __restrict__ I) {
+    const int64_t total = (int64_t)n * k;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int r = (int)(i / k), c = (int)(i - (int64_t)r * k);
+        D[(size_t)list[r] * k + c] = rD[i];
+        I[(size_t)list[r] * k + c] = rI[i];
+    }
+}
+
+// one tensor pass: prep -> K3b scan -> K5 rerank, all enqueued on `st`; w.flags[0] = #uncertified,
+// w.flags[1..] = their indices (relative to qc)
+static int tc_pass(bfk_index* idx, const float* qc, int ldq, int64_t nqc, int k, float* D_out, int64_t* I_out,
+                   int64_t id_offset, const TcWs& w, const TcPlan& pl, cudaStream_t st, cudaEvent_t ev0, cudaEvent_t ev1,
+                   int* launches) {
+    const bool l2 = idx->metric == BFK_METRIC_L2;
+    BFK_CUDA(cudaMemsetAsync(w.flags, 0, sizeof(int), st));
+    // |<q,x> - <bf16(q),bf16(x)>| <= (2u + u^2) ||q|| ||x|| with u = 2^-9 when both operands are
+    // rounded, u ||q|| ||x|| when the corpus is stored in bf16; + 2^-14 for tensor-core accumulation
+    const float c_round = (idx->storage == BFK_STORE_F32 ? 1.01f / 256.f : 1.01f / 512.f) + 1.0f / 16384.f;
+    prep_queries_kernel<<<(unsigned)((pl.nq_pad + 7) / 8), 256, 0, st>>>(qc, ldq, idx->d, nqc, pl.nq_pad, w.q16, idx->ld16,
+                                                                        w.qn, idx->maxn, c_round, l2 ? 1 : 0, w.qmargin,
+                                                                        w.slots, pl.NS);
+    BFK_CUDA(cudaGetLastError());
+    CUtensorMap tmQ, tmX;
+    BFK_TRY(make_tmap(&tmQ, w.q16, pl.nq_pad, idx->ld16, TC_BM));
+    BFK_TRY(make_tmap(&tmX, idx->x16, idx->ntotal, idx->ld16, TC_BN));
+    TcParams p;
+    p.nrm = idx->nrm;
+    p.n = idx->ntotal;
+    p.KB = pl.KB;
+    p.QT = pl.QT;
+    p.S = pl.S;
+    p.tiles_total = pl.tiles_total;
+    p.smem_bytes = (int)pl.smem;
+    p.is_l2 = l2 ? 1 : 0;
+    p.nq = (int)nqc;
+    p.slots = w.slots;
+    p.NS = pl.NS;
+    p.G = pl.G;
+    p.J = pl.J;
+    p.a_resident = pl.a_resident;
+    p.qmargin = w.qmargin;
+    p.out_cand = w.out_cand;
+    p.out_thr = w.out_thr;
+    static const bool dbg_on = getenv("BFK_TC_DEBUG") != nullptr;
+    static const bool parked = getenv("BFK_TC_PARKED") != nullptr;
+    p.dbg = dbg_on ? w.dbg : nullptr;
+    p.parked = parked ? 1 : 0;
+    if (dbg_on) BFK_CUDA(cudaMemsetAsync(w.dbg, 0, (size_t)pl.grid * 64, st));
+    if (ev0) cudaEventRecord(ev0, st);
+    if (pl.KP == 16)
+        BFK_TRY(launch_scan_tc<16>(tmQ, tmX, p, pl, st));
+    else
+        BFK_TRY(launch_scan_tc<32>(tmQ, tmX, p, pl, st));
+    if (ev1) cudaEventRecord(ev1, st);
+    if (p.dbg) {  // diagnostics only: per-role wait cycles averaged over the CTAs
+        std::vector<unsigned long long> h((size_t)pl.grid * 8);
+        BFK_CUDA(cudaMemcpyAsync(h.data(), w.dbg, h.size() * 8, cudaMemcpyDeviceToHost, st));
+        BFK_CUDA(cudaStreamSynchronize(st));
+        double a[8] = {0};
+        for (int c = 0; c < pl.grid; c++)
+            for (int j = 0; j < 8; j++) a[j] += (double)h[(size_t)c * 8 + j] / pl.grid;
+        fprintf(stderr,
+                "[bfk tc] nq=%lld grid=%d QT=%d S=%d KP=%d NS=%d G=%d J=%d tiles/cta=%.1f | cycles/cta: life=%.0f "
+                "tma_wait_empty=%.0f mma_wait_full=%.0f mma_wait_tmem=%.0f epi_wait_acc=%.0f epi_flush=%.0f | "
+                "appended/thread=%.0f flushes=%.1f\n",
+                (long long)nqc, pl.grid, pl.QT, pl.S, pl.KP, pl.NS, pl.G, pl.J, (double)pl.tiles_total / pl.S, a[7], a[0],
+                a[1], a[2], a[3], a[4], a[5], a[6]);
+    }
+    RerankParams r;
+    r.out_cand = w.out_cand;
+    r.out_thr = w.out_thr;
+    r.qmargin = w.qmargin;
+    r.q = qc;
+    r.ldq = ldq;
+    r.S = 2 * pl.S;  // thread-streams
+    r.KP = pl.KP;
+    r.k = k;
+    r.is_l2 = l2 ? 1 : 0;
+    r.storage = idx->storage;
+    r.x32 = idx->x32;
+    r.ld32 = idx->ld32;
+    r.x16 = idx->x16;
+    r.ld16 = idx->ld16;
+    r.d = idx->d;
+    r.id_offset = id_offset;
+    r.D = D_out;
+    r.I = I_out;
+    r.nflag = w.flags;
+    r.flag_list = w.flags + 1;
+    rerank_kernel<<<(unsigned)nqc, RR_THREADS, 0, st>>>(r);
+    BFK_CUDA(cudaGetLastError());
+    *launches += 3;
+    return 0;
+}
+
 int search_tensor(bfk_index* idx, const float* q_dev, int ldq, int64_t nq, int k, float* D_dev, int64_t* I_dev,
                   int64_t id_offset, char* ws_tail, size_t ws_tail_bytes, cudaStream_t st, bfk_search_stats* stats,
                   cudaEvent_t ev0, cudaEvent_t ev1) {
     const int64_t chunk = tc_chunk_queries(idx);
     int launches = 0;
-    int64_t n_fallback = 0;
+    int64_t n_fallback = 0, n_retry = 0;
     int fb_nparts = 0;
     size_t sb = 0;
     BFK_TRY(scan_exact_workspace(idx, 8, k, &sb, &fb_nparts));
-    const bool l2 = idx->metric == BFK_METRIC_L2;
     for (int64_t q0 = 0; q0 < nq; q0 += chunk) {
         const int64_t nqc = std::min(chunk, nq - q0);
         TcPlan pl;
         if (tc_plan(idx, nqc, k, &pl)) return fail("tensor path: shape not supported");
         TcWs w;
-        tc_carve(idx, nqc, k, pl, fb_nparts, ws_tail, &w);
+        tc_carve(idx, nqc, k, fb_nparts, ws_tail, &w);
         if (w.bytes > ws_tail_bytes) return fail("internal: tensor-path workspace under-sized");
         const float* qc = q_dev + (size_t)q0 * ldq;
+        float* Dc = D_dev + (size_t)q0 * k;
+        int64_t* Ic = I_dev + (size_t)q0 * k;
+        BFK_TRY(tc_pass(idx, qc, ldq, nqc, k, Dc, Ic, id_offset, w, pl, st, q0 == 0 ? ev0 : nullptr,
+                        q0 + chunk >= nq ? ev1 : nullptr, &launches));
 
-        BFK_CUDA(cudaMemsetAsync(w.flags, 0, sizeof(int), st));
-        // |<q,x> - <bf16(q),bf16(x)>| <= (2u + u^2) ||q|| ||x|| with u = 2^-9 when both operands are
-        // rounded, u ||q|| ||x|| when the corpus is stored in bf16; + 2^-14 for tensor-core accumulation
-        const float c_round = (idx->storage == BFK_STORE_F32 ? 1.01f / 256.f : 1.01f / 512.f) + 1.0f / 16384.f;
-        prep_queries_kernel<<<(unsigned)((pl.nq_pad + 7) / 8), 256, 0, st>>>(qc, ldq, idx->d, nqc, pl.nq_pad, w.q16,
-                                                                            idx->ld16, w.qn, idx->maxn, c_round,
-                                                                            l2 ? 1 : 0, w.qmargin, w.slots, pl.NS);
-        BFK_CUDA(cudaGetLastError());
-        CUtensorMap tmQ, tmX;
-        BFK_TRY(make_tmap(&tmQ, w.q16, pl.nq_pad, idx->ld16, TC_BM));
-        BFK_TRY(make_tmap(&tmX, idx->x16, idx->ntotal, idx->ld16, TC_BN));
-        TcParams p;
-        p.nrm = idx->nrm;
-        p.n = idx->ntotal;
-        p.KB = pl.KB;
-        p.QT = pl.QT;
-        p.S = pl.S;
-        p.tiles_total = pl.tiles_total;
-        p.smem_bytes = (int)pl.smem;
-        p.is_l2 = l2 ? 1 : 0;
-        p.nq = (int)nqc;
-        p.slots = w.slots;
-        p.NS = pl.NS;
-        p.G = pl.G;
-        p.J = pl.J;
-        p.a_resident = pl.a_resident;
-        p.qmargin = w.qmargin;
-        p.out_cand = w.out_cand;
-        p.out_thr = w.out_thr;
-        static const bool dbg_on = getenv("BFK_TC_DEBUG") != nullptr;
-        static const bool parked = getenv("BFK_TC_PARKED") != nullptr;
-        p.dbg = dbg_on ? w.dbg : nullptr;
-        p.parked = parked ? 1 : 0;
-        if (dbg_on) BFK_CUDA(cudaMemsetAsync(w.dbg, 0, (size_t)pl.grid * 64, st));
-        if (ev0 && q0 == 0) cudaEventRecord(ev0, st);
-        if (pl.KP == 16)
-            BFK_TRY(launch_scan_tc<16>(tmQ, tmX, p, pl, st));
-        else
-            BFK_TRY(launch_scan_tc<32>(tmQ, tmX, p, pl, st));
-        if (ev1 && q0 + chunk >= nq) cudaEventRecord(ev1, st);
-        if (p.dbg) {  // diagnostics only: per-role wait cycles averaged over the CTAs
-            std::vector<unsigned long long> h((size_t)pl.grid * 8);
-            BFK_CUDA(cudaMemcpyAsync(h.data(), w.dbg, h.size() * 8, cudaMemcpyDeviceToHost, st));
-            BFK_CUDA(cudaStreamSynchronize(st));
-            double a[8] = {0};
-            for (int c = 0; c < pl.grid; c++)
-                for (int j = 0; j < 8; j++) a[j] += (double)h[(size_t)c * 8 + j] / pl.grid;
-            fprintf(stderr,
-                    "[bfk tc] grid=%d QT=%d S=%d KP=%d tiles/cta=%.1f | cycles/cta: life=%.0f tma_wait_empty=%.0f "
-                    "mma_wait_full=%.0f mma_wait_tmem=%.0f epi_wait_acc=%.0f epi_flush=%.0f | appended/thread=%.0f flushes=%.1f\n",
-                    pl.grid, pl.QT, pl.S, pl.KP, (double)pl.tiles_total / pl.S, a[7], a[0], a[1], a[2], a[3], a[4], a[5], a[6]);
-        }
-
-        RerankParams r;
-        r.out_cand = w.out_cand;
-        r.out_thr = w.out_thr;
-        r.qmargin = w.qmargin;
-        r.q = qc;
-        r.ldq = ldq;
-        r.S = pl.S;
-        r.KP = pl.KP;
-        r.k = k;
-        r.is_l2 = l2 ? 1 : 0;
-        r.storage = idx->storage;
-        r.x32 = idx->x32;
-        r.ld32 = idx->ld32;
-        r.x16 = idx->x16;
-        r.ld16 = idx->ld16;
-        r.d = idx->d;
-        r.id_offset = id_offset;
-        r.D = D_dev + (size_t)q0 * k;
-        r.I = I_dev + (size_t)q0 * k;
-        r.nflag = w.flags;
-        r.flag_list = w.flags + 1;
-        rerank_kernel<<<(unsigned)nqc, RR_THREADS, 0, st>>>(r);
-        BFK_CUDA(cudaGetLastError());
-        launches += 3;
-
-        // ---- uncertified queries: exact re-run on the GPU (K3a + K4) ----
+        // ---- uncertified queries ----
         BFK_CUDA(cudaMemcpyAsync(idx->h_flag, w.flags, sizeof(int), cudaMemcpyDeviceToHost, st));
         BFK_CUDA(cudaStreamSynchronize(st));
-        const int nflag = *idx->h_flag;
-        if (nflag > 0) {
-            std::vector<int> list((size_t)nflag);
-            BFK_CUDA(cudaMemcpyAsync(list.data(), w.flags + 1, sizeof(int) * (size_t)nflag, cudaMemcpyDeviceToHost, st));
+        int nflag = *idx->h_flag;
+        if (nflag == 0) continue;
+        std::vector<int> list((size_t)nflag);
+        BFK_CUDA(cudaMemcpyAsync(list.data(), w.flags + 1, sizeof(int) * (size_t)nflag, cudaMemcpyDeviceToHost, st));
+        BFK_CUDA(cudaStreamSynchronize(st));
+
+        // second chance: the same tensor pass over the uncertified queries alone.  Fewer queries means
+        // more corpus streams per query, hence more list room and a better chance to certify -- for the
+        // price of one HBM-bound corpus pass instead of nflag/8 exact passes.
+        TcPlan pl2;
+        if (2 * (int64_t)nflag <= nqc && !tc_plan(idx, nflag, k, &pl2) && pl2.S >= 2 * pl.S) {
+            BFK_CUDA(cudaMemcpyAsync(w.r_list, w.flags + 1, sizeof(int) * (size_t)nflag, cudaMemcpyDeviceToDevice, st));
+            gather_queries_kernel<<<(unsigned)std::min<int64_t>(((int64_t)nflag * ldq + 255) / 256, 1184), 256, 0, st>>>(
+                qc, ldq, w.r_list, nflag, w.r_q);
+            BFK_CUDA(cudaGetLastError());
+            BFK_TRY(tc_pass(idx, w.r_q, ldq, nflag, k, w.r_D, w.r_I, id_offset, w, pl2, st, nullptr, nullptr, &launches));
+            scatter_results_kernel<<<(unsigned)std::min<int64_t>(((int64_t)nflag * k + 255) / 256, 1184), 256, 0, st>>>(
+                w.r_D, w.r_I, w.r_list, nflag, k, Dc, Ic);
+            BFK_CUDA(cudaGetLastError());
+            launches += 2;
+            BFK_CUDA(cudaMemcpyAsync(idx->h_flag, w.flags, sizeof(int), cudaMemcpyDeviceToHost, st));
             BFK_CUDA(cudaStreamSynchronize(st));
-            std::sort(list.begin(), list.end());
-            for (int g0 = 0; g0 < nflag; g0 += 8) {
-                const int g = std::min(8, nflag - g0);
-                for (int j = 0; j < g; j++)
-                    BFK_CUDA(cudaMemcpyAsync(w.fb_q + (size_t)j * ldq, qc + (size_t)list[g0 + j] * ldq,
-                                             sizeof(float) * ldq, cudaMemcpyDeviceToDevice, st));
-                BFK_TRY(launch_scan_exact(idx, w.fb_q, ldq, g, k, w.fb_part, fb_nparts, st));
-                BFK_TRY(launch_select(w.fb_part, (int64_t)fb_nparts * k, g, k, idx->metric, id_offset, w.fb_D, w.fb_I, k, st));
-                launches += 2;
-                for (int j = 0; j < g; j++) {
-                    const size_t row = (size_t)(q0 + list[g0 + j]) * k;
-                    BFK_CUDA(cudaMemcpyAsync(D_dev + row, w.fb_D + (size_t)j * k, sizeof(float) * k,
-                                             cudaMemcpyDeviceToDevice, st));
-                    BFK_CUDA(cudaMemcpyAsync(I_dev + row, w.fb_I + (size_t)j * k, sizeof(int64_t) * k,
-                                             cudaMemcpyDeviceToDevice, st));
-                }
+            const int nflag2 = *idx->h_flag;
+            std::vector<int> list2((size_t)nflag2);
+            if (nflag2 > 0) {
+                BFK_CUDA(cudaMemcpyAsync(list2.data(), w.flags + 1, sizeof(int) * (size_t)nflag2, cudaMemcpyDeviceToHost, st));
+                BFK_CUDA(cudaStreamSynchronize(st));
             }
-            n_fallback += nflag;
+            n_retry += nflag;
+            std::vector<int> still;
+            still.reserve((size_t)nflag2);
+            for (int j : list2) still.push_back(list[(size_t)j]);
+            list.swap(still);
+            nflag = nflag2;
         }
+
+        // ---- last resort: exact re-run on the GPU (K3a + K4), 8 queries per corpus pass ----
+        std::sort(list.begin(), list.end());
+        for (int g0 = 0; g0 < nflag; g0 += 8) {
+            const int g = std::min(8, nflag - g0);
+            for (int j = 0; j < g; j++)
+                BFK_CUDA(cudaMemcpyAsync(w.fb_q + (size_t)j * ldq, qc + (size_t)list[g0 + j] * ldq, sizeof(float) * ldq,
+                                         cudaMemcpyDeviceToDevice, st));
+            BFK_TRY(launch_scan_exact(idx, w.fb_q, ldq, g, k, w.fb_part, fb_nparts, st));
+            BFK_TRY(launch_select(w.fb_part, (int64_t)fb_nparts * k, g, k, idx->metric, id_offset, w.fb_D, w.fb_I, k, st));
+            launches += 2;
+            for (int j = 0; j < g; j++) {
+                const size_t row = (size_t)list[g0 + j] * k;
+                BFK_CUDA(cudaMemcpyAsync(Dc + row, w.fb_D + (size_t)j * k, sizeof(float) * k, cudaMemcpyDeviceToDevice, st));
+                BFK_CUDA(cudaMemcpyAsync(Ic + row, w.fb_I + (size_t)j * k, sizeof(int64_t) * k, cudaMemcpyDeviceToDevice, st));
+            }
+        }
+        n_fallback += nflag;
     }
     if (stats) {
         stats->n_launches = launches;
         stats->n_fallback = n_fallback;
+        stats->n_candidates = n_retry;
         stats->algo_used = BFK_ALGO_TENSOR;
     }
     return 0;

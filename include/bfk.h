@@ -61,7 +61,7 @@ typedef struct bfk_search_stats {
     int32_t algo_used;        /* BFK_ALGO_* actually run for the bulk of the queries   */
     int32_t n_launches;       /* kernels launched by this call                         */
     int64_t n_fallback;       /* queries re-run exactly after a failed certificate     */
-    int64_t n_candidates;     /* candidates reranked in fp32 (tensor path)             */
+    int64_t n_candidates;     /* queries that needed the second tensor pass (tensor path) */
     float scan_ms;            /* device time of the dominant scan kernel (if timed)    */
     float reserved;
 } bfk_search_stats;

@@ -195,3 +195,40 @@ def test_tensor_path_full_size_1m_x_384(bfk):
     assert (I64.cpu().numpy() == I[:64]).all()
     De, Ie = idx.search(q[:16], k, algo="exact")
     assert (Ie.cpu().numpy() == I[:16]).all()
+
+
+def test_config3_full_size_10m_x_768_bf16_ip(bfk):
+    """BASELINE config 3 at full size: bf16-stored 10M x 768, IndexFlatIP, batch 4096, k = 100.
+
+    The CPU oracle cannot hold this corpus; the tensor path is checked against the independent
+    exact fp32-accumulate scan (K3a) on a query subsample, plus size-independent properties.
+    """
+    import torch
+
+    n, d, k, nq = 10_000_000, 768, 100, 4096
+    idx = bfk.IndexFlatIP(d, storage="bf16")
+    idx.reserve(n)
+    g = torch.Generator(device="cuda").manual_seed(1234)
+    for r0 in range(0, n, 1 << 20):
+        m = min(1 << 20, n - r0)
+        x = torch.randn((m, d), generator=g, device="cuda", dtype=torch.float32)
+        x /= x.norm(dim=1, keepdim=True)
+        idx.add(x)
+        del x
+    assert idx.ntotal == n
+    g2 = torch.Generator(device="cuda").manual_seed(4321)
+    q = torch.randn((nq, d), generator=g2, device="cuda", dtype=torch.float32)
+    q /= q.norm(dim=1, keepdim=True)
+    st = bfk.SearchStats()
+    D, I = idx.search(q, k, algo="tensor", stats=st)
+    assert st.algo_used == bfk.ALGO_TENSOR and st.n_fallback <= nq // 100, st.n_fallback
+    De, Ie = idx.search(q[:16], k, algo="exact")
+    assert torch.equal(I[:16], Ie)
+    torch.testing.assert_close(D[:16], De, rtol=1e-5, atol=1e-6)
+    Dh, Ih = D.cpu().numpy(), I.cpu().numpy()
+    assert (np.diff(Dh, axis=1) <= 0).all()  # inner products, best (largest) first
+    assert Ih.min() >= 0 and Ih.max() < n
+    assert all(len(set(r)) == k for r in Ih[::64].tolist())
+    # distances recomputable from the stored (bf16) rows
+    rows = torch.from_numpy(idx.reconstruct_n(int(Ih[5, 0]), 1)).cuda()
+    assert abs(float((rows[0] * q[5]).sum()) - float(Dh[5, 0])) < 1e-5
