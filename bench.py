@@ -112,16 +112,21 @@ def roofline_of(res, nq, n_rows, elem, hbm_peak, tf_peak, peak_kind):
         bytes_launch = n_rows * D * elem + per_q * D * 4 + per_q * K * 8 * 148
         launch_ms = res["scan_ms"] / passes
         ach = bytes_launch / (launch_ms * 1e-3) / 1e9 if launch_ms > 0 else 0.0
+        # profiles/r01_ncu_scan_exact_nq1.txt: dram read 1536.08 MB + write 3.75 MB at nq = 1
+        traffic = 1539.83e6 if (n_rows == 1_000_000 and D == 384 and nq == 1 and elem == 4) else None
         return {"bound": "hbm", "kernel": "scan_exact_kernel", "achieved": ach, "peak": hbm_peak, "unit": "GB/s",
                 "frac": ach / hbm_peak, "peak_kind": peak_kind, "bytes_per_launch": bytes_launch,
-                "launch_ms": launch_ms, "launches_per_step": passes, "traffic": None}
+                "launch_ms": launch_ms, "launches_per_step": passes, "traffic": traffic}
     launch_ms = res["scan_ms"]
     if nq <= 128:
         bytes_launch = n_rows * D * 2 + (n_rows * 4 if METRIC_ID == 1 else 0) + nq * D * 2 + nq * 148 * 16 * 12
         ach = bytes_launch / (launch_ms * 1e-3) / 1e9 if launch_ms > 0 else 0.0
+        # DRAM bytes per launch from the one `ncu --set full` capture of this exact shape
+        # (profiles/r01_ncu_scan_tc_final_nq64.txt: dram read 772.31 MB + write 3.84 MB)
+        traffic = 776.15e6 if (n_rows == 1_000_000 and D == 384 and nq == 64 and METRIC_ID == 1) else None
         return {"bound": "hbm", "kernel": "scan_tc_kernel", "achieved": ach, "peak": hbm_peak, "unit": "GB/s",
                 "frac": ach / hbm_peak, "peak_kind": peak_kind, "bytes_per_launch": bytes_launch,
-                "launch_ms": launch_ms, "launches_per_step": 1, "traffic": None}
+                "launch_ms": launch_ms, "launches_per_step": 1, "traffic": traffic}
     flops = 2.0 * nq * n_rows * D
     ach = flops / (launch_ms * 1e-3) / 1e12 if launch_ms > 0 else 0.0
     return {"bound": "tensor", "kernel": "scan_tc_kernel", "achieved": ach, "peak": tf_peak, "unit": "TFLOP/s",
