@@ -328,10 +328,12 @@ int scan_exact_workspace(const bfk_index* idx, int nq, int k, size_t* bytes, int
 template <int NQ, int R, bool IS_L2, typename RowT>
 static int launch_one(const ScanExactParams& p, size_t smem, int grid, cudaStream_t st) {
     auto kern = scan_exact_kernel<NQ, R, IS_L2, RowT>;
-    static bool attr_set = false;  // per instantiation
-    if (!attr_set) {
+    static bool attr_set[64] = {false};  // per instantiation and per device
+    int dev = 0;
+    BFK_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64 || !attr_set[dev]) {
         BFK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SE_SMEM_BUDGET + 4096));
-        attr_set = true;
+        if (dev >= 0 && dev < 64) attr_set[dev] = true;
     }
     kern<<<grid, SE_THREADS, smem, st>>>(p);
     BFK_CUDA(cudaGetLastError());

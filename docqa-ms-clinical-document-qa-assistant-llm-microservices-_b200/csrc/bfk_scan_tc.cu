@@ -79,6 +79,10 @@ struct TcParams {
     unsigned long long* dbg;  // optional [grid][8] cycle counters (BFK_TC_DEBUG=1), else nullptr
     int parked;          // producer/MMA waits use the suspend-time hint
     int a_resident;      // query tile resident in smem (else its K-blocks stream with the corpus)
+    int csize;           // cluster size (1, 2 or 4): CTAs of one cluster share each corpus tile by TMA multicast
+    uint64_t* pend_g;    // global pending lists [grid][TC_BUFCAP][256], or nullptr: lists live in shared memory.
+                         // Long streams (several query tiles) append rarely and need the 32 KiB for a 4th
+                         // corpus stage instead; short streams (nq <= 128) append often and keep them on chip.
 };
 
 // wait flavour for the single-thread roles + optional cycle accounting
@@ -103,11 +107,12 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
     // a misaligned base just costs one stage)
     const int a_bytes = p.a_resident ? p.KB * TC_A_BLOCK : 0;
     const int stage_bytes = p.a_resident ? TC_B_BLOCK : TC_B_BLOCK + TC_A_BLOCK;  // streamed: [B block | A block]
-    const int stages = min(TC_MAX_STAGES, (int)((p.smem_bytes - (int)pad - a_bytes - TC_PEND_BYTES - TC_TAIL_BYTES) / stage_bytes));
+    const int pend_bytes = p.pend_g ? 0 : TC_PEND_BYTES;
+    const int stages = min(TC_MAX_STAGES, (int)((p.smem_bytes - (int)pad - a_bytes - pend_bytes - TC_TAIL_BYTES) / stage_bytes));
     unsigned char* sA = smem;
     unsigned char* sB = sA + (size_t)a_bytes;
     uint64_t* pend_s = reinterpret_cast<uint64_t*>(sB + (size_t)stages * stage_bytes);  // [TC_BUFCAP][256]
-    float* bias_s = reinterpret_cast<float*>(reinterpret_cast<unsigned char*>(pend_s) + TC_PEND_BYTES);
+    float* bias_s = reinterpret_cast<float*>(reinterpret_cast<unsigned char*>(pend_s) + pend_bytes);
     uint64_t* full_bar = reinterpret_cast<uint64_t*>(bias_s + 2 * TC_BN);
     uint64_t* empty_bar = full_bar + TC_MAX_STAGES;
     uint64_t* q_bar = empty_bar + TC_MAX_STAGES;
@@ -119,8 +124,11 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
     float* thr_sh = reinterpret_cast<float*>(tmem_slot + 4);  // [128] bound on the global KP-th best key per query row
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    unsigned long long dbg_acc[4] = {0, 0, 0, 0};
     const long long dbg_t0 = p.dbg ? clock64() : 0;
+    unsigned long long dbg_acc[4] = {0, 0, 0, 0};
+    // CTA 0 also records a per-tile event timeline (first 64 tiles) behind the counters: [event][tile]
+    unsigned long long* tl = (p.dbg && blockIdx.x == 0) ? p.dbg + (size_t)gridDim.x * 8 : nullptr;
+#define TC_MARK(ev, tile) do { if (tl && (tile) < 64) tl[(ev) * 64 + (tile)] = (unsigned long long)(clock64() - dbg_t0); } while (0)
     const int qt = blockIdx.x % p.QT;
     const int s = blockIdx.x / p.QT;
     const int64_t t_begin = p.tiles_total * s / p.S;
@@ -129,7 +137,7 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
     if (tid == 0) {
         for (int i = 0; i < stages; i++) {
             mbar_init(&full_bar[i], 1);
-            mbar_init(&empty_bar[i], 1);
+            mbar_init(&empty_bar[i], (uint32_t)p.csize);  // every CTA of the cluster must have consumed the stage
         }
         mbar_init(q_bar, 1);
         for (int a = 0; a < 2; a++) {
@@ -149,8 +157,12 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
     }
     tc_fence_before();
     __syncthreads();
+    if (p.csize > 1) cluster_sync_all();  // peers' barriers are initialised before anyone signals them
     tc_fence_after();
     const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(tmem_slot);
+    const uint32_t crank = p.csize > 1 ? cluster_ctarank() : 0u;
+    const uint16_t cmask = (uint16_t)((1u << p.csize) - 1u);
+    const int slice_rows = TC_BN / p.csize;  // this CTA fetches rows [crank*slice_rows, +slice_rows) of every tile
 
     if (warp == 0) {
         // ===================== TMA producer =====================
@@ -167,7 +179,13 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
                     const uint32_t ph = (it / stages) & 1u;
                     TC_WAIT(&empty_bar[st], ph ^ 1u, 0);
                     mbar_expect_tx(&full_bar[st], (uint32_t)stage_bytes);
-                    tma_load_2d(sB + (size_t)st * stage_bytes, &tmX, kb * 64, (int)(t * TC_BN), &full_bar[st]);
+                    if (kb == 0) TC_MARK(0, t - t_begin);
+                    if (kb == p.KB - 1) TC_MARK(1, t - t_begin);
+                    if (p.csize > 1)
+                        tma_load_2d_mc(sB + (size_t)st * stage_bytes + (size_t)crank * slice_rows * 128, &tmX, kb * 64,
+                                       (int)(t * TC_BN) + (int)crank * slice_rows, &full_bar[st], cmask);
+                    else
+                        tma_load_2d(sB + (size_t)st * stage_bytes, &tmX, kb * 64, (int)(t * TC_BN), &full_bar[st]);
                     if (!p.a_resident)
                         tma_load_2d(sB + (size_t)st * stage_bytes + TC_B_BLOCK, &tmQ, kb * 64, qt * TC_BM, &full_bar[st]);
                 }
@@ -184,6 +202,7 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
             for (int64_t t = t_begin; t < t_end; t++, tcount++) {
                 const uint32_t a = tcount & 1u, aph = (tcount >> 1) & 1u;
                 TC_WAIT(&tempty_bar[a], aph ^ 1u, 2);  // epilogue has drained this accumulator
+                TC_MARK(2, tcount);
                 tc_fence_after();
                 if (p.is_l2) {
                     // bias slot a is free for the same reason: fetch this tile's 256 squared norms now, they
@@ -196,7 +215,12 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
                     const int st = it % stages;
                     const uint32_t ph = (it / stages) & 1u;
                     TC_WAIT(&full_bar[st], ph, 1);
+                    if (kb == 0) TC_MARK(3, tcount);
+                    if (kb == p.KB - 1) TC_MARK(4, tcount);
+                    const bool fine = tl && tcount == 12 && kb < 8;  // fine-grained marks inside one tile
+                    if (fine) tl[7 * 64 + kb * 4 + 0] = (unsigned long long)(clock64() - dbg_t0);
                     tc_fence_after();
+                    if (fine) tl[7 * 64 + kb * 4 + 1] = (unsigned long long)(clock64() - dbg_t0);
 #pragma unroll
                     for (int kk = 0; kk < 4; kk++) {
                         const uint32_t a_blk = p.a_resident ? a_base + kb * TC_A_BLOCK : b_base + st * stage_bytes + TC_B_BLOCK;
@@ -204,7 +228,10 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
                         const uint64_t db = make_smem_desc_sw128(b_base + st * stage_bytes + kk * 32);
                         umma_bf16(d_tmem, da, db, idesc, (kb | kk) != 0 ? 1u : 0u);
                     }
-                    umma_commit(&empty_bar[st]);  // smem stage reusable once these MMAs retire
+                    if (fine) tl[7 * 64 + kb * 4 + 2] = (unsigned long long)(clock64() - dbg_t0);
+                    if (p.csize > 1) umma_commit_mc(&empty_bar[st], cmask);  // release the stage in every peer too
+                    else umma_commit(&empty_bar[st]);  // smem stage reusable once these MMAs retire
+                    if (fine) tl[7 * 64 + kb * 4 + 3] = (unsigned long long)(clock64() - dbg_t0);
                 }
                 umma_commit(&tfull_bar[a]);  // accumulator complete
             }
@@ -261,7 +288,7 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
         const int grp = (s * 2 + half) & (p.G - 1);
         float thr = active ? FLT_MAX : -FLT_MAX;
         int cnt = 0;
-        uint64_t* my_pend = pend_s + et;   // [slot][thread] in shared memory
+        uint64_t* my_pend = (p.pend_g ? p.pend_g + (size_t)blockIdx.x * TC_BUFCAP * TC_EPI_THREADS : pend_s) + et;  // [slot][thread]
         const float scale = p.is_l2 ? -2.0f : -1.0f;
 
         // sorted insert without a dependency chain: every slot decides from the OLD neighbours
@@ -310,6 +337,7 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
                 mbar_wait(&tfull_bar[a], aph);  // accumulator complete
                 if (p.is_l2) mbar_wait(&nfull_bar[a], aph);  // and the tile's norms have landed
                 if (p.dbg) dbg_acc[0] += (unsigned long long)(clock64() - _t0);
+                if (et == 0) TC_MARK(5, tcount);
             }
             if ((t + 1) * TC_BN > p.n) {  // ragged last tile of the corpus: columns past the end never win
                 if (t * TC_BN + et >= p.n) bias_s[a * TC_BN + et] = INFINITY;
@@ -375,6 +403,7 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
             }
             tc_fence_before();
             mbar_arrive(&tempty_bar[a]);
+            if (et == 0) TC_MARK(6, tcount);
         }
         dbg_acc[2] += (unsigned long long)cnt;
         flush();
@@ -400,6 +429,7 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
 
     tc_fence_before();
     __syncthreads();
+    if (p.csize > 1) cluster_sync_all();  // nobody leaves while a peer may still signal its barriers
     if (warp == 2) {
         tc_fence_after();
         tmem_dealloc<512>(tmem_base);
@@ -637,16 +667,19 @@ static int make_tmap(CUtensorMap* m, const void* base, int64_t rows, int ld, int
 }
 
 struct TcPlan {
-    int KB, stages, QT, S, KP, NS, G, J, grid, a_resident;
+    int KB, stages, QT, S, KP, NS, G, J, grid, a_resident, pend_global, csize;
     int64_t nq_pad, tiles_total;
     size_t smem;
 };
 
 static int tc_plan(const bfk_index* idx, int64_t nq, int k, TcPlan* pl) {
     pl->KB = idx->ld16 / 64;
+    // measured: moving the lists to global memory to win a 4th stage made flushes ~10x slower and the extra
+    // stage bought nothing (the multi-tile regime is bound by L2 -> SM bandwidth, not by ring depth)
+    pl->pend_global = 0;
     // the 128-query tile stays resident in shared memory when it leaves room for >= 3 corpus stages;
     // otherwise (d > 384) its K-blocks stream through the ring next to the corpus K-blocks
-    const size_t tail = (size_t)TC_PEND_BYTES + TC_TAIL_BYTES;
+    const size_t tail = (size_t)(pl->pend_global ? 0 : TC_PEND_BYTES) + TC_TAIL_BYTES;
     const size_t res_fixed = (size_t)pl->KB * TC_A_BLOCK + tail;
     pl->a_resident = (res_fixed + 3 * (size_t)TC_B_BLOCK <= TC_SMEM_LIMIT) ? 1 : 0;
     const size_t fixed = pl->a_resident ? res_fixed : tail;
@@ -659,6 +692,15 @@ static int tc_plan(const bfk_index* idx, int64_t nq, int k, TcPlan* pl) {
     pl->tiles_total = (idx->ntotal + TC_BN - 1) / TC_BN;
     pl->S = (int)std::max<int64_t>(1, std::min<int64_t>(idx->num_sms / pl->QT, pl->tiles_total));
     pl->grid = pl->QT * pl->S;
+    // Optional (BFK_TC_CLUSTER=2|4): CTAs c, c+1, .. of one cluster are consecutive query tiles on the same
+    // corpus stream; each fetches 1/csize of every corpus tile and multicasts it.  Measured on B200 it
+    // changes nothing (nq=1024: 0.866 vs 0.847 ms; nq=4096: 3.96 / 4.17 vs 3.82 ms for 2 / 4): multicast at
+    // cluster sizes <= 4 does not reduce what the L2 serves, so it stays off by default.
+    pl->csize = 1;
+    if (const char* e = getenv("BFK_TC_CLUSTER")) {
+        const int c = atoi(e);
+        if ((c == 1 || c == 2 || c == 4) && pl->QT % c == 0) pl->csize = c;
+    }
     // KP list slots per (query, thread-stream).  The certificate is global: the streams' lists together
     // must hold the k best rows plus the error band, so KP may be smaller than k when there are many
     // streams; few streams get the longer lists.
@@ -699,6 +741,7 @@ struct TcWs {
     int64_t* fb_I;   // [8][k]
     uint64_t* fb_part;
     unsigned long long* dbg;
+    uint64_t* pend_g;
     // second-chance pass over the uncertified queries only (fewer queries -> more streams -> more list room)
     int* r_list;     // [nq/2 + 1] query indices (copy of the first pass's flag list)
     float* r_q;      // [nq/2][ldq]
@@ -732,7 +775,8 @@ static void tc_carve(const bfk_index* idx, int64_t nqc, int k, int fb_nparts, ch
     w->fb_D = (float*)take((size_t)8 * k * 4);
     w->fb_I = (int64_t*)take((size_t)8 * k * 8);
     w->fb_part = (uint64_t*)take((size_t)8 * fb_nparts * k * 8);
-    w->dbg = (unsigned long long*)take((size_t)idx->num_sms * 8 * 8);
+    w->dbg = (unsigned long long*)take((size_t)idx->num_sms * 8 * 8 + 8 * 64 * 8);
+    w->pend_g = (uint64_t*)take((size_t)idx->num_sms * TC_BUFCAP * TC_EPI_THREADS * 8);
     const int64_t nr = nqc / 2 + 1;
     w->r_list = (int*)take((size_t)(nr + 1) * 4);
     w->r_q = (float*)take((size_t)nr * idx->ld32 * 4);
@@ -753,16 +797,55 @@ size_t tensor_workspace_bytes(const bfk_index* idx, int64_t nq, int k) {
     return w.bytes;
 }
 
+// co-resident clusters of `csize` CTAs for this kernel and shared-memory size (cluster size 4 strands SMs
+// in GPCs whose SM count is not a multiple of 4: 132 of 148 on B200)
+template <int KP>
+static int max_cluster_ctas(int csize, size_t smem) {
+    auto kern = scan_tc_kernel<KP>;
+    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_LIMIT);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(148 * 4);
+    cfg.blockDim = dim3(TC_THREADS);
+    cfg.dynamicSmemBytes = smem;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = (unsigned)csize;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    int n = 0;
+    if (cudaOccupancyMaxActiveClusters(&n, kern, &cfg) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    return n * csize;
+}
+
 template <int KP>
 static int launch_scan_tc(const CUtensorMap& tmQ, const CUtensorMap& tmX, const TcParams& p, const TcPlan& pl,
                           cudaStream_t st) {
     auto kern = scan_tc_kernel<KP>;
-    static bool attr_set = false;
-    if (!attr_set) {
+    static bool attr_set[64] = {false};  // the attribute is per device
+    int dev = 0;
+    BFK_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64 || !attr_set[dev]) {
         BFK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_LIMIT));
-        attr_set = true;
+        if (dev >= 0 && dev < 64) attr_set[dev] = true;
     }
-    kern<<<pl.grid, TC_THREADS, pl.smem, st>>>(tmQ, tmX, p);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)pl.grid);
+    cfg.blockDim = dim3(TC_THREADS);
+    cfg.dynamicSmemBytes = pl.smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = (unsigned)pl.csize;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    BFK_CUDA(cudaLaunchKernelEx(&cfg, kern, tmQ, tmX, p));
     BFK_CUDA(cudaGetLastError());
     return 0;
 }
@@ -790,9 +873,16 @@ __global__ void __launch_bounds__(256) scatter_results_kernel(const float* __res
 // one tensor pass: prep -> K3b scan -> K5 rerank, all enqueued on `st`; w.flags[0] = #uncertified,
 // w.flags[1..] = their indices (relative to qc)
 static int tc_pass(bfk_index* idx, const float* qc, int ldq, int64_t nqc, int k, float* D_out, int64_t* I_out,
-                   int64_t id_offset, const TcWs& w, const TcPlan& pl, cudaStream_t st, cudaEvent_t ev0, cudaEvent_t ev1,
+                   int64_t id_offset, const TcWs& w, const TcPlan& plan, cudaStream_t st, cudaEvent_t ev0, cudaEvent_t ev1,
                    int* launches) {
     const bool l2 = idx->metric == BFK_METRIC_L2;
+    TcPlan pl = plan;
+    // every CTA of the persistent grid must be resident at once for the cluster size chosen
+    while (pl.csize > 1) {
+        const int fit = pl.KP == 16 ? max_cluster_ctas<16>(pl.csize, pl.smem) : max_cluster_ctas<32>(pl.csize, pl.smem);
+        if (fit >= pl.grid) break;
+        pl.csize >>= 1;
+    }
     BFK_CUDA(cudaMemsetAsync(w.flags, 0, sizeof(int), st));
     // |<q,x> - <bf16(q),bf16(x)>| <= (2u + u^2) ||q|| ||x|| with u = 2^-9 when both operands are
     // rounded, u ||q|| ||x|| when the corpus is stored in bf16; + 2^-14 for tensor-core accumulation
@@ -803,7 +893,7 @@ static int tc_pass(bfk_index* idx, const float* qc, int ldq, int64_t nqc, int k,
     BFK_CUDA(cudaGetLastError());
     CUtensorMap tmQ, tmX;
     BFK_TRY(make_tmap(&tmQ, w.q16, pl.nq_pad, idx->ld16, TC_BM));
-    BFK_TRY(make_tmap(&tmX, idx->x16, idx->ntotal, idx->ld16, TC_BN));
+    BFK_TRY(make_tmap(&tmX, idx->x16, idx->ntotal, idx->ld16, TC_BN / pl.csize));  // box = this CTA's slice
     TcParams p;
     p.nrm = idx->nrm;
     p.n = idx->ntotal;
@@ -822,11 +912,13 @@ static int tc_pass(bfk_index* idx, const float* qc, int ldq, int64_t nqc, int k,
     p.qmargin = w.qmargin;
     p.out_cand = w.out_cand;
     p.out_thr = w.out_thr;
+    p.pend_g = pl.pend_global ? w.pend_g : nullptr;
+    p.csize = pl.csize;
     static const bool dbg_on = getenv("BFK_TC_DEBUG") != nullptr;
     static const bool parked = getenv("BFK_TC_PARKED") != nullptr;
     p.dbg = dbg_on ? w.dbg : nullptr;
     p.parked = parked ? 1 : 0;
-    if (dbg_on) BFK_CUDA(cudaMemsetAsync(w.dbg, 0, (size_t)pl.grid * 64, st));
+    if (dbg_on) BFK_CUDA(cudaMemsetAsync(w.dbg, 0, (size_t)pl.grid * 64 + 8 * 64 * 8, st));
     if (ev0) cudaEventRecord(ev0, st);
     if (pl.KP == 16)
         BFK_TRY(launch_scan_tc<16>(tmQ, tmX, p, pl, st));
@@ -834,7 +926,7 @@ static int tc_pass(bfk_index* idx, const float* qc, int ldq, int64_t nqc, int k,
         BFK_TRY(launch_scan_tc<32>(tmQ, tmX, p, pl, st));
     if (ev1) cudaEventRecord(ev1, st);
     if (p.dbg) {  // diagnostics only: per-role wait cycles averaged over the CTAs
-        std::vector<unsigned long long> h((size_t)pl.grid * 8);
+        std::vector<unsigned long long> h((size_t)pl.grid * 8 + 8 * 64);
         BFK_CUDA(cudaMemcpyAsync(h.data(), w.dbg, h.size() * 8, cudaMemcpyDeviceToHost, st));
         BFK_CUDA(cudaStreamSynchronize(st));
         double a[8] = {0};
@@ -846,6 +938,17 @@ static int tc_pass(bfk_index* idx, const float* qc, int ldq, int64_t nqc, int k,
                 "appended/thread=%.0f flushes=%.1f\n",
                 (long long)nqc, pl.grid, pl.QT, pl.S, pl.KP, pl.NS, pl.G, pl.J, (double)pl.tiles_total / pl.S, a[7], a[0],
                 a[1], a[2], a[3], a[4], a[5], a[6]);
+        if (getenv("BFK_TC_TIMELINE")) {
+            const unsigned long long* tl = h.data() + (size_t)pl.grid * 8;
+            fprintf(stderr, "[bfk tc timeline, CTA 0, cycles] tile tma_first tma_last mma_acq mma_kb0 mma_kbL epi_start epi_done\n");
+            for (int t = 8; t < 24; t++)
+                fprintf(stderr, "  %2d %8llu %8llu %8llu %8llu %8llu %8llu %8llu\n", t, tl[0 * 64 + t], tl[1 * 64 + t],
+                        tl[2 * 64 + t], tl[3 * 64 + t], tl[4 * 64 + t], tl[5 * 64 + t], tl[6 * 64 + t]);
+            fprintf(stderr, "[tile 12, MMA thread] kb wait_done fenced mmas_issued committed\n");
+            for (int kb = 0; kb < std::min(pl.KB, 8); kb++)
+                fprintf(stderr, "  %d %8llu %8llu %8llu %8llu\n", kb, tl[7 * 64 + kb * 4], tl[7 * 64 + kb * 4 + 1],
+                        tl[7 * 64 + kb * 4 + 2], tl[7 * 64 + kb * 4 + 3]);
+        }
     }
     RerankParams r;
     r.out_cand = w.out_cand;
