@@ -55,7 +55,7 @@ constexpr int TC_SMEM_LIMIT = 232448;    // 227 KiB
 constexpr int TC_RMAX = 512;             // exact re-scores per query at most
 constexpr int TC_MERGE_N = 4096;
 constexpr int TC_PEND_BYTES = TC_BUFCAP * 256 * 8;  // 32 KiB
-constexpr int TC_TAIL_BYTES = 2 * TC_BN * 4 + (2 * TC_MAX_STAGES + 7) * 8 + 16 + 128 * 4;  // bias + barriers + tmem slot/flag + thr_sh
+constexpr int TC_TAIL_BYTES = 2 * TC_BN * 4 + (2 * TC_MAX_STAGES + 9) * 8 + 16 + 128 * 4;  // bias + barriers + tmem slot/flag + thr_sh
 
 struct TcParams {
     const float* nrm;
@@ -79,7 +79,8 @@ struct TcParams {
     unsigned long long* dbg;  // optional [grid][8] cycle counters (BFK_TC_DEBUG=1), else nullptr
     int parked;          // producer/MMA waits use the suspend-time hint
     int a_resident;      // query tile resident in smem (else its K-blocks stream with the corpus)
-    int csize;           // cluster size (1, 2 or 4): CTAs of one cluster share each corpus tile by TMA multicast
+    int csize;           // 1: every CTA on its own; 2: CTA pairs (cta_group::2) -- two query tiles share one
+                         // corpus stream, each CTA stages only half of every corpus tile
     uint64_t* pend_g;    // global pending lists [grid][TC_BUFCAP][256], or nullptr: lists live in shared memory.
                          // Long streams (several query tiles) append rarely and need the 32 KiB for a 4th
                          // corpus stage instead; short streams (nq <= 128) append often and keep them on chip.
@@ -96,7 +97,9 @@ struct TcParams {
 
 __device__ __forceinline__ void epi_sync() { asm volatile("bar.sync 2, 256;" ::: "memory"); }
 
-template <int KP>
+// PAIR is a template parameter, not a run-time flag: a kernel that contains cta_group::2 instructions can
+// only be launched with an even cluster size.
+template <int KP, bool PAIR>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 scan_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmX, const TcParams p) {
     extern __shared__ __align__(1024) unsigned char smem_raw[];
@@ -106,7 +109,9 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
     // stages: whatever fits after the resident query tile and the fixed tail (host sizes for pad = 0;
     // a misaligned base just costs one stage)
     const int a_bytes = p.a_resident ? p.KB * TC_A_BLOCK : 0;
-    const int stage_bytes = p.a_resident ? TC_B_BLOCK : TC_B_BLOCK + TC_A_BLOCK;  // streamed: [B block | A block]
+    constexpr bool pair = PAIR;
+    const int b_bytes = pair ? TC_B_BLOCK / 2 : TC_B_BLOCK;  // a paired CTA stages 128 of the tile's 256 rows
+    const int stage_bytes = p.a_resident ? b_bytes : b_bytes + TC_A_BLOCK;  // streamed: [B block | A block]
     const int pend_bytes = p.pend_g ? 0 : TC_PEND_BYTES;
     const int stages = min(TC_MAX_STAGES, (int)((p.smem_bytes - (int)pad - a_bytes - pend_bytes - TC_TAIL_BYTES) / stage_bytes));
     unsigned char* sA = smem;
@@ -119,7 +124,8 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
     uint64_t* tfull_bar = q_bar + 1;   // [2]
     uint64_t* tempty_bar = tfull_bar + 2;  // [2]
     uint64_t* nfull_bar = tempty_bar + 2;  // [2] norms of the tile have landed in bias slot a
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(nfull_bar + 2);
+    uint64_t* tlocal_bar = nfull_bar + 2;  // [2] THIS CTA's epilogue has released accumulator / bias slot a
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tlocal_bar + 2);
     volatile int* done_flag = reinterpret_cast<volatile int*>(tmem_slot + 1);
     float* thr_sh = reinterpret_cast<float*>(tmem_slot + 4);  // [128] bound on the global KP-th best key per query row
 
@@ -135,85 +141,108 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
     const int64_t t_end = p.tiles_total * (s + 1) / p.S;
 
     if (tid == 0) {
+        // pair: the leader's full / q / tempty barriers collect both CTAs (one producer arrival and the
+        // bytes of each; every epilogue thread of the pair); empty / tfull exist per CTA and are signalled
+        // together by the leader's multicast commits
         for (int i = 0; i < stages; i++) {
-            mbar_init(&full_bar[i], 1);
-            mbar_init(&empty_bar[i], (uint32_t)p.csize);  // every CTA of the cluster must have consumed the stage
+            mbar_init(&full_bar[i], (uint32_t)p.csize);
+            mbar_init(&empty_bar[i], 1);
         }
-        mbar_init(q_bar, 1);
+        mbar_init(q_bar, (uint32_t)p.csize);
         for (int a = 0; a < 2; a++) {
             mbar_init(&tfull_bar[a], 1);
-            mbar_init(&tempty_bar[a], TC_EPI_THREADS);
+            mbar_init(&tempty_bar[a], TC_EPI_THREADS * (uint32_t)p.csize);
             mbar_init(&nfull_bar[a], 1);
+            mbar_init(&tlocal_bar[a], TC_EPI_THREADS);
         }
         fence_mbar_init();
     }
     if (tid < 128) thr_sh[tid] = FLT_MAX;
     for (int i = tid; i < 2 * TC_BN; i += TC_THREADS) bias_s[i] = 0.f;  // inner product: no bias
     if (tid == 0) *done_flag = 0;
-    if (warp == 2) tmem_alloc<512>(tmem_slot);
+    if (warp == 2) {
+        if constexpr (PAIR) tmem_alloc2<512>(tmem_slot);
+        else tmem_alloc<512>(tmem_slot);
+    }
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmQ);
         tma_prefetch_desc(&tmX);
     }
     tc_fence_before();
     __syncthreads();
-    if (p.csize > 1) cluster_sync_all();  // peers' barriers are initialised before anyone signals them
+    if constexpr (PAIR) cluster_sync_all();  // the peer's barriers are initialised before anyone signals them
     tc_fence_after();
     const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(tmem_slot);
-    const uint32_t crank = p.csize > 1 ? cluster_ctarank() : 0u;
-    const uint16_t cmask = (uint16_t)((1u << p.csize) - 1u);
-    const int slice_rows = TC_BN / p.csize;  // this CTA fetches rows [crank*slice_rows, +slice_rows) of every tile
+    uint32_t crank = 0u;
+    if constexpr (PAIR) crank = cluster_ctarank();
+    const bool leader = crank == 0;
 
     if (warp == 0) {
         // ===================== TMA producer =====================
         if (lane == 0) {
             if (p.a_resident) {
-                mbar_expect_tx(q_bar, (uint32_t)p.KB * TC_A_BLOCK);
-                for (int kb = 0; kb < p.KB; kb++)
-                    tma_load_2d(sA + (size_t)kb * TC_A_BLOCK, &tmQ, kb * 64, qt * TC_BM, q_bar);
+                if constexpr (!PAIR) {
+                    mbar_expect_tx(q_bar, (uint32_t)p.KB * TC_A_BLOCK);
+                    for (int kb = 0; kb < p.KB; kb++)
+                        tma_load_2d(sA + (size_t)kb * TC_A_BLOCK, &tmQ, kb * 64, qt * TC_BM, q_bar);
+                } else {
+                    if (leader) mbar_expect_tx(q_bar, 2u * (uint32_t)p.KB * TC_A_BLOCK);
+                    for (int kb = 0; kb < p.KB; kb++)
+                        tma_load_2d_2sm(sA + (size_t)kb * TC_A_BLOCK, &tmQ, kb * 64, qt * TC_BM, q_bar);
+                    if (!leader) mbar_arrive_remote(q_bar, 0);
+                }
             }
-            uint32_t it = 0;
+            uint32_t st = 0, ph = 0;
             for (int64_t t = t_begin; t < t_end; t++) {
-                for (int kb = 0; kb < p.KB; kb++, it++) {
-                    const int st = it % stages;
-                    const uint32_t ph = (it / stages) & 1u;
+                for (int kb = 0; kb < p.KB; kb++) {
                     TC_WAIT(&empty_bar[st], ph ^ 1u, 0);
-                    mbar_expect_tx(&full_bar[st], (uint32_t)stage_bytes);
                     if (kb == 0) TC_MARK(0, t - t_begin);
                     if (kb == p.KB - 1) TC_MARK(1, t - t_begin);
-                    if (p.csize > 1)
-                        tma_load_2d_mc(sB + (size_t)st * stage_bytes + (size_t)crank * slice_rows * 128, &tmX, kb * 64,
-                                       (int)(t * TC_BN) + (int)crank * slice_rows, &full_bar[st], cmask);
-                    else
-                        tma_load_2d(sB + (size_t)st * stage_bytes, &tmX, kb * 64, (int)(t * TC_BN), &full_bar[st]);
-                    if (!p.a_resident)
-                        tma_load_2d(sB + (size_t)st * stage_bytes + TC_B_BLOCK, &tmQ, kb * 64, qt * TC_BM, &full_bar[st]);
+                    unsigned char* stage = sB + (size_t)st * stage_bytes;
+                    if constexpr (!PAIR) {
+                        mbar_expect_tx(&full_bar[st], (uint32_t)stage_bytes);
+                        tma_load_2d(stage, &tmX, kb * 64, (int)(t * TC_BN), &full_bar[st]);
+                        if (!p.a_resident) tma_load_2d(stage + b_bytes, &tmQ, kb * 64, qt * TC_BM, &full_bar[st]);
+                    } else {
+                        // each CTA stages its half of the corpus tile (and its own query K-block) in its own
+                        // shared memory; all bytes are accounted on the leader's barrier
+                        if (leader) mbar_expect_tx(&full_bar[st], 2u * (uint32_t)stage_bytes);
+                        tma_load_2d_2sm(stage, &tmX, kb * 64, (int)(t * TC_BN) + (int)crank * (TC_BN / 2), &full_bar[st]);
+                        if (!p.a_resident) tma_load_2d_2sm(stage + b_bytes, &tmQ, kb * 64, qt * TC_BM, &full_bar[st]);
+                        if (!leader) mbar_arrive_remote(&full_bar[st], 0);
+                    }
+                    if (++st == (uint32_t)stages) {
+                        st = 0;
+                        ph ^= 1u;
+                    }
                 }
             }
             if (p.dbg) p.dbg[blockIdx.x * 8 + 0] = dbg_acc[0];
         }
     } else if (warp == 1) {
         // ===================== MMA issuer (one thread) =====================
-        if (lane == 0) {
-            const uint32_t idesc = make_idesc_bf16(TC_BM, TC_BN);
-            const uint32_t a_base = smem_u32(sA), b_base = smem_u32(sB);
+        if (lane == 0 && leader) {
+            const uint32_t idesc = make_idesc_bf16(pair ? 2 * TC_BM : TC_BM, TC_BN);
+            // This one thread paces the tensor pipe, so its loop is kept to a handful of 32-bit
+            // instructions per K-block: running stage / phase counters instead of div/mod, and smem
+            // descriptors advanced by adding to their low word (start address >> 4); a first version that
+            // rebuilt everything per K-block spent ~600 cycles between commits (timeline diagnostics).
+            const uint64_t desc_hi = make_smem_desc_sw128(0) & 0xffffffff00000000ull;
+            const uint32_t desc_lo0 = (uint32_t)(make_smem_desc_sw128(0) & 0xffffffffull);
+            const uint32_t a_lo0 = desc_lo0 + ((smem_u32(sA) & 0x3ffffu) >> 4);
+            const uint32_t b_lo0 = desc_lo0 + ((smem_u32(sB) & 0x3ffffu) >> 4);
+            const uint32_t stage_lo = (uint32_t)stage_bytes >> 4;
+            const uint32_t a_in_stage_lo = (uint32_t)b_bytes >> 4;
             if (p.a_resident) TC_WAIT(q_bar, 0, 3);
-            uint32_t it = 0, tcount = 0;
+            uint32_t st = 0, ph = 0, tcount = 0;
             for (int64_t t = t_begin; t < t_end; t++, tcount++) {
                 const uint32_t a = tcount & 1u, aph = (tcount >> 1) & 1u;
-                TC_WAIT(&tempty_bar[a], aph ^ 1u, 2);  // epilogue has drained this accumulator
+                TC_WAIT(&tempty_bar[a], aph ^ 1u, 2);  // every epilogue thread (of the pair) has drained accumulator a
                 TC_MARK(2, tcount);
                 tc_fence_after();
-                if (p.is_l2) {
-                    // bias slot a is free for the same reason: fetch this tile's 256 squared norms now, they
-                    // land long before the epilogue reaches the tile
-                    mbar_expect_tx(&nfull_bar[a], TC_BN * 4);
-                    bulk_g2s(bias_s + a * TC_BN, p.nrm + t * TC_BN, TC_BN * 4, &nfull_bar[a]);
-                }
                 const uint32_t d_tmem = tmem_base + a * TC_BN;
-                for (int kb = 0; kb < p.KB; kb++, it++) {
-                    const int st = it % stages;
-                    const uint32_t ph = (it / stages) & 1u;
+                uint32_t a_lo = a_lo0;  // resident query tile: K-block kb at + kb * 16 KiB
+                for (int kb = 0; kb < p.KB; kb++) {
                     TC_WAIT(&full_bar[st], ph, 1);
                     if (kb == 0) TC_MARK(3, tcount);
                     if (kb == p.KB - 1) TC_MARK(4, tcount);
@@ -221,23 +250,45 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
                     if (fine) tl[7 * 64 + kb * 4 + 0] = (unsigned long long)(clock64() - dbg_t0);
                     tc_fence_after();
                     if (fine) tl[7 * 64 + kb * 4 + 1] = (unsigned long long)(clock64() - dbg_t0);
+                    const uint32_t b_lo = b_lo0 + st * stage_lo;
+                    const uint32_t a_blk = p.a_resident ? a_lo : b_lo + a_in_stage_lo;
 #pragma unroll
                     for (int kk = 0; kk < 4; kk++) {
-                        const uint32_t a_blk = p.a_resident ? a_base + kb * TC_A_BLOCK : b_base + st * stage_bytes + TC_B_BLOCK;
-                        const uint64_t da = make_smem_desc_sw128(a_blk + kk * 32);
-                        const uint64_t db = make_smem_desc_sw128(b_base + st * stage_bytes + kk * 32);
-                        umma_bf16(d_tmem, da, db, idesc, (kb | kk) != 0 ? 1u : 0u);
+                        const uint64_t da = desc_hi | (uint64_t)(a_blk + 2 * kk);  // + 32 bytes per K = 16 step
+                        const uint64_t db = desc_hi | (uint64_t)(b_lo + 2 * kk);
+                        const uint32_t acc = (kb | kk) != 0 ? 1u : 0u;
+                        if constexpr (PAIR) umma_bf16_2sm(d_tmem, da, db, idesc, acc);
+                        else umma_bf16(d_tmem, da, db, idesc, acc);
                     }
                     if (fine) tl[7 * 64 + kb * 4 + 2] = (unsigned long long)(clock64() - dbg_t0);
-                    if (p.csize > 1) umma_commit_mc(&empty_bar[st], cmask);  // release the stage in every peer too
-                    else umma_commit(&empty_bar[st]);  // smem stage reusable once these MMAs retire
+                    if constexpr (PAIR) umma_commit_2sm(&empty_bar[st]);  // frees the stage in both CTAs
+                    else umma_commit(&empty_bar[st]);           // smem stage reusable once these MMAs retire
                     if (fine) tl[7 * 64 + kb * 4 + 3] = (unsigned long long)(clock64() - dbg_t0);
+                    a_lo += TC_A_BLOCK >> 4;
+                    if (++st == (uint32_t)stages) {
+                        st = 0;
+                        ph ^= 1u;
+                    }
                 }
-                umma_commit(&tfull_bar[a]);  // accumulator complete
+                if constexpr (PAIR) umma_commit_2sm(&tfull_bar[a]);  // accumulator complete, in both CTAs
+                else umma_commit(&tfull_bar[a]);
             }
             if (p.dbg) {
                 p.dbg[blockIdx.x * 8 + 1] = dbg_acc[1];
                 p.dbg[blockIdx.x * 8 + 2] = dbg_acc[2];
+            }
+        }
+    } else if (warp == 2) {
+        // ===================== norms fetcher =====================
+        // bias slot a is free once THIS CTA's epilogue has released accumulator a: fetch the tile's 256
+        // squared norms then; they land long before the epilogue reaches the tile
+        if (lane == 0 && p.is_l2) {
+            uint32_t tcount = 0;
+            for (int64_t t = t_begin; t < t_end; t++, tcount++) {
+                const uint32_t a = tcount & 1u, aph = (tcount >> 1) & 1u;
+                mbar_wait_parked(&tlocal_bar[a], aph ^ 1u);
+                mbar_expect_tx(&nfull_bar[a], TC_BN * 4);
+                bulk_g2s(bias_s + a * TC_BN, p.nrm + t * TC_BN, TC_BN * 4, &nfull_bar[a]);
             }
         }
     } else if (warp == 3) {
@@ -402,7 +453,9 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
                 process16(rb, (sc + 1) * 16);
             }
             tc_fence_before();
-            mbar_arrive(&tempty_bar[a]);
+            mbar_arrive(&tlocal_bar[a]);
+            if (leader) mbar_arrive(&tempty_bar[a]);
+            else if constexpr (PAIR) mbar_arrive_remote(&tempty_bar[a], 0);  // the MMA issuer lives in the leader CTA
             if (et == 0) TC_MARK(6, tcount);
         }
         dbg_acc[2] += (unsigned long long)cnt;
@@ -429,10 +482,11 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
 
     tc_fence_before();
     __syncthreads();
-    if (p.csize > 1) cluster_sync_all();  // nobody leaves while a peer may still signal its barriers
+    if constexpr (PAIR) cluster_sync_all();  // nobody leaves while the peer may still signal its barriers
     if (warp == 2) {
         tc_fence_after();
-        tmem_dealloc<512>(tmem_base);
+        if constexpr (PAIR) tmem_dealloc2<512>(tmem_base);
+        else tmem_dealloc<512>(tmem_base);
     }
 }
 
@@ -677,30 +731,28 @@ static int tc_plan(const bfk_index* idx, int64_t nq, int k, TcPlan* pl) {
     // measured: moving the lists to global memory to win a 4th stage made flushes ~10x slower and the extra
     // stage bought nothing (the multi-tile regime is bound by L2 -> SM bandwidth, not by ring depth)
     pl->pend_global = 0;
+    pl->QT = (int)((nq + TC_BM - 1) / TC_BM);
+    // Optional CTA pairs (BFK_TC_PAIR=1, needs an even number of query tiles): tcgen05.mma.cta_group::2 with
+    // M = 256 -- the pair shares one corpus stream and each CTA stages half of every corpus tile, halving the
+    // L2 -> SM bytes per MMA.  Parity-tested, but measured no faster than single CTAs on B200 (nq=1024:
+    // 0.798 vs 0.792 ms; nq=4096: 3.91 vs 3.46 ms), so it is off by default.
+    pl->csize = 1;
+    if (const char* e = getenv("BFK_TC_PAIR")) pl->csize = (atoi(e) != 0 && pl->QT % 2 == 0) ? 2 : 1;
+    const size_t b_block = pl->csize == 2 ? TC_B_BLOCK / 2 : TC_B_BLOCK;
     // the 128-query tile stays resident in shared memory when it leaves room for >= 3 corpus stages;
     // otherwise (d > 384) its K-blocks stream through the ring next to the corpus K-blocks
     const size_t tail = (size_t)(pl->pend_global ? 0 : TC_PEND_BYTES) + TC_TAIL_BYTES;
     const size_t res_fixed = (size_t)pl->KB * TC_A_BLOCK + tail;
     pl->a_resident = (res_fixed + 3 * (size_t)TC_B_BLOCK <= TC_SMEM_LIMIT) ? 1 : 0;
     const size_t fixed = pl->a_resident ? res_fixed : tail;
-    const size_t stage = pl->a_resident ? TC_B_BLOCK : TC_B_BLOCK + TC_A_BLOCK;
+    const size_t stage = pl->a_resident ? b_block : b_block + TC_A_BLOCK;
     if (fixed + 2 * stage > TC_SMEM_LIMIT) return 1;
     pl->stages = (int)std::min<size_t>(TC_MAX_STAGES, (TC_SMEM_LIMIT - fixed) / stage);
     pl->smem = fixed + (size_t)pl->stages * stage;
-    pl->QT = (int)((nq + TC_BM - 1) / TC_BM);
     pl->nq_pad = (int64_t)pl->QT * TC_BM;
     pl->tiles_total = (idx->ntotal + TC_BN - 1) / TC_BN;
     pl->S = (int)std::max<int64_t>(1, std::min<int64_t>(idx->num_sms / pl->QT, pl->tiles_total));
     pl->grid = pl->QT * pl->S;
-    // Optional (BFK_TC_CLUSTER=2|4): CTAs c, c+1, .. of one cluster are consecutive query tiles on the same
-    // corpus stream; each fetches 1/csize of every corpus tile and multicasts it.  Measured on B200 it
-    // changes nothing (nq=1024: 0.866 vs 0.847 ms; nq=4096: 3.96 / 4.17 vs 3.82 ms for 2 / 4): multicast at
-    // cluster sizes <= 4 does not reduce what the L2 serves, so it stays off by default.
-    pl->csize = 1;
-    if (const char* e = getenv("BFK_TC_CLUSTER")) {
-        const int c = atoi(e);
-        if ((c == 1 || c == 2 || c == 4) && pl->QT % c == 0) pl->csize = c;
-    }
     // KP list slots per (query, thread-stream).  The certificate is global: the streams' lists together
     // must hold the k best rows plus the error band, so KP may be smaller than k when there are many
     // streams; few streams get the longer lists.
@@ -801,7 +853,7 @@ size_t tensor_workspace_bytes(const bfk_index* idx, int64_t nq, int k) {
 // in GPCs whose SM count is not a multiple of 4: 132 of 148 on B200)
 template <int KP>
 static int max_cluster_ctas(int csize, size_t smem) {
-    auto kern = scan_tc_kernel<KP>;
+    auto kern = scan_tc_kernel<KP, true>;
     cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_LIMIT);
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(148 * 4);
@@ -822,10 +874,10 @@ static int max_cluster_ctas(int csize, size_t smem) {
     return n * csize;
 }
 
-template <int KP>
+template <int KP, bool PAIR>
 static int launch_scan_tc(const CUtensorMap& tmQ, const CUtensorMap& tmX, const TcParams& p, const TcPlan& pl,
                           cudaStream_t st) {
-    auto kern = scan_tc_kernel<KP>;
+    auto kern = scan_tc_kernel<KP, PAIR>;
     static bool attr_set[64] = {false};  // the attribute is per device
     int dev = 0;
     BFK_CUDA(cudaGetDevice(&dev));
@@ -878,10 +930,9 @@ static int tc_pass(bfk_index* idx, const float* qc, int ldq, int64_t nqc, int k,
     const bool l2 = idx->metric == BFK_METRIC_L2;
     TcPlan pl = plan;
     // every CTA of the persistent grid must be resident at once for the cluster size chosen
-    while (pl.csize > 1) {
-        const int fit = pl.KP == 16 ? max_cluster_ctas<16>(pl.csize, pl.smem) : max_cluster_ctas<32>(pl.csize, pl.smem);
-        if (fit >= pl.grid) break;
-        pl.csize >>= 1;
+    if (pl.csize == 2) {
+        const int fit = pl.KP == 16 ? max_cluster_ctas<16>(2, pl.smem) : max_cluster_ctas<32>(2, pl.smem);
+        if (fit < pl.grid) return fail("tensor path: CTA pairs do not all fit on the GPU");
     }
     BFK_CUDA(cudaMemsetAsync(w.flags, 0, sizeof(int), st));
     // |<q,x> - <bf16(q),bf16(x)>| <= (2u + u^2) ||q|| ||x|| with u = 2^-9 when both operands are
@@ -920,10 +971,13 @@ static int tc_pass(bfk_index* idx, const float* qc, int ldq, int64_t nqc, int k,
     p.parked = parked ? 1 : 0;
     if (dbg_on) BFK_CUDA(cudaMemsetAsync(w.dbg, 0, (size_t)pl.grid * 64 + 8 * 64 * 8, st));
     if (ev0) cudaEventRecord(ev0, st);
-    if (pl.KP == 16)
-        BFK_TRY(launch_scan_tc<16>(tmQ, tmX, p, pl, st));
-    else
-        BFK_TRY(launch_scan_tc<32>(tmQ, tmX, p, pl, st));
+    if (pl.KP == 16) {
+        if (pl.csize == 2) BFK_TRY((launch_scan_tc<16, true>(tmQ, tmX, p, pl, st)));
+        else BFK_TRY((launch_scan_tc<16, false>(tmQ, tmX, p, pl, st)));
+    } else {
+        if (pl.csize == 2) BFK_TRY((launch_scan_tc<32, true>(tmQ, tmX, p, pl, st)));
+        else BFK_TRY((launch_scan_tc<32, false>(tmQ, tmX, p, pl, st)));
+    }
     if (ev1) cudaEventRecord(ev1, st);
     if (p.dbg) {  // diagnostics only: per-role wait cycles averaged over the CTAs
         std::vector<unsigned long long> h((size_t)pl.grid * 8 + 8 * 64);
