@@ -8,12 +8,13 @@ from ._lib import (ALGO_AUTO, ALGO_EXACT_SIMT, ALGO_TENSOR, MAX_D, MAX_K, METRIC
 from .faiss_shim import install_as_faiss
 from .flat import (IndexFlat, IndexFlatIP, IndexFlatL2, deserialize_index, get_num_gpus, normalize_L2,
                    read_index, serialize_index, write_index)
+from .indexer_host import SemanticIndexer
 from .pooling import pool_normalize
 from .sharded import ShardedIndexFlat, shard_range
 
 __all__ = [
     "IndexFlat", "IndexFlatL2", "IndexFlatIP", "write_index", "read_index", "serialize_index",
     "deserialize_index", "normalize_L2", "METRIC_L2", "METRIC_INNER_PRODUCT", "pool_normalize",
-    "install_as_faiss", "ShardedIndexFlat", "shard_range", "get_num_gpus", "SearchStats",
+    "install_as_faiss", "SemanticIndexer", "ShardedIndexFlat", "shard_range", "get_num_gpus", "SearchStats",
     "ALGO_AUTO", "ALGO_EXACT_SIMT", "ALGO_TENSOR", "MAX_K", "MAX_D",
 ]

@@ -269,3 +269,31 @@ def test_full_size_properties_1m_x_384(bfk):
     # nq=1 and nq=64 agree with each other
     D1, I1 = idx.search(q[:1], k)
     assert (I1.cpu().numpy() == I[:1]).all()
+
+
+def test_indexer_host_on_the_gpu_index(bfk, tmp_path):
+    """SURVEY 8f row 1 end to end: message -> chunks -> one batched add on the GPU -> atomic files -> reload."""
+    import hashlib
+    import json
+    import pickle
+
+    class Model:
+        def encode(self, texts):
+            out = np.empty((len(texts), 384), np.float32)
+            for i, t in enumerate(texts):
+                rng = np.random.default_rng(int(hashlib.sha1(t.encode()).hexdigest()[:8], 16))
+                v = rng.standard_normal(384)
+                out[i] = v / np.linalg.norm(v)
+            return out
+
+    ix = bfk.SemanticIndexer(Model(), 384, index_file=str(tmp_path / "vector_store.faiss"),
+                             metadata_file=str(tmp_path / "metadata_store.pkl"))
+    body = json.dumps({"doc_id": 3, "original_text_masked": "x" * 700 + "y" * 700}).encode()
+    assert ix.handle_message(body) is True
+    assert isinstance(ix.index, bfk.IndexFlatL2) and ix.index.ntotal == 3
+    raw_index = bfk.read_index(str(tmp_path / "vector_store.faiss"))          # llm-qa/main.py:35
+    meta = pickle.load(open(tmp_path / "metadata_store.pkl", "rb"))             # llm-qa/main.py:37-38
+    assert raw_index.ntotal == len(meta) == 3
+    vec = Model().encode([meta[1]["text_content"]])
+    D, I = raw_index.search(vec, 3)                                             # llm-qa/main.py:101,117
+    assert I[0, 0] == 1 and D[0, 0] == 0.0

@@ -1,0 +1,138 @@
+"""Host mirror of semantic-indexer/indexer.py. CPU only: encoder and index are fakes.
+
+Follows the reference's own tests (semantic-indexer/tests/test_indexer.py:34-59) -- encode is called with
+the text list, the index is created once, add is called, metadata is appended, blank text is ignored --
+and adds the behaviours the reference does not test: chunking, batching, atomic persistence, and the CSV
+templates, which must regenerate the texts behind the shipped index (tests/golden manifest).
+"""
+import hashlib
+import json
+import os
+import pickle
+
+import numpy as np
+import pytest
+
+from oracle import faiss_io, flat_ref
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+class FakeModel:
+    """encode(list[str]) -> deterministic unit vectors; records calls like the reference's MagicMock."""
+
+    def __init__(self, d=8):
+        self.d = d
+        self.calls = []
+
+    def encode(self, texts):
+        self.calls.append(list(texts))
+        out = np.empty((len(texts), self.d), np.float32)
+        for i, t in enumerate(texts):
+            rng = np.random.default_rng(int(hashlib.sha1(t.encode()).hexdigest()[:8], 16))
+            v = rng.standard_normal(self.d)
+            out[i] = v / np.linalg.norm(v)
+        return out
+
+
+def ref_write(index, path):
+    open(path, "wb").write(faiss_io.write_index_bytes(index.reconstruct_n(0, index.ntotal), index.metric_type))
+
+
+def ref_read(path):
+    d, n, metric, x = faiss_io.read_index_bytes(open(path, "rb").read())
+    idx = flat_ref.IndexFlatRef(d, metric)
+    idx.add(x)
+    return idx
+
+
+def make(tmp_path, **kw):
+    from docqa_b200.indexer_host import SemanticIndexer
+
+    created = []
+
+    def factory(d):
+        created.append(d)
+        return flat_ref.IndexFlatRef(d)
+
+    ix = SemanticIndexer(FakeModel(), 8, index_file=str(tmp_path / "vector_store.faiss"),
+                         metadata_file=str(tmp_path / "metadata_store.pkl"), index_factory=factory,
+                         write_index=ref_write, read_index=ref_read, **kw)
+    return ix, created
+
+
+def test_add_to_index_like_the_reference_test(tmp_path):
+    ix, created = make(tmp_path)
+    ix.add_to_index("Test sentence", "test_source.txt")
+    assert ix.model.calls == [["Test sentence"]]          # model.encode([text])
+    assert created == [8]                                  # IndexFlatL2(dimension) once
+    assert ix.index.ntotal == 1
+    assert ix.metadata_store == [{"doc_id": "KB_MTC", "text_content": "Test sentence",
+                                  "source": "test_source.txt", "type": "knowledge_base"}]
+    ix.add_to_index("second", "s2", "patient_file")
+    assert created == [8] and ix.index.ntotal == 2 and ix.metadata_store[1]["type"] == "patient_file"
+
+
+def test_add_to_index_empty(tmp_path):
+    ix, created = make(tmp_path)
+    ix.add_to_index("   ", "source")
+    assert ix.metadata_store == [] and ix.index is None and ix.model.calls == []
+
+
+def test_handle_message_chunks_batches_and_persists_atomically(tmp_path):
+    ix, _ = make(tmp_path)
+    text = "".join(chr(ord("a") + i % 26) for i in range(1203))  # 3 chunks: 500, 500, 203
+    assert ix.handle_message(json.dumps({"doc_id": 7, "original_text_masked": text}).encode()) is True
+    assert len(ix.model.calls) == 1 and [len(c) for c in ix.model.calls[0]] == [500, 500, 203]  # ONE encode call
+    assert ix.index.ntotal == 3
+    assert [m["source"] for m in ix.metadata_store] == ["Dossier Patient 7"] * 3
+    assert all(m["doc_id"] == "KB_MTC" and m["type"] == "patient_file" for m in ix.metadata_store)
+    # both files exist, no temporaries left, and they agree row for row
+    assert sorted(os.listdir(tmp_path)) == ["metadata_store.pkl", "vector_store.faiss"]
+    meta = pickle.load(open(tmp_path / "metadata_store.pkl", "rb"))
+    d, n, metric, x = faiss_io.read_index_bytes(open(tmp_path / "vector_store.faiss", "rb").read())
+    assert n == len(meta) == 3 and metric == 1
+    np.testing.assert_array_equal(x, FakeModel().encode([m["text_content"] for m in meta]))
+    # malformed message -> nack, state untouched
+    assert ix.handle_message(b"not json") is False
+    assert ix.handle_message(json.dumps({"doc_id": 1}).encode()) is False  # no text: the reference nacks too
+    assert ix.index.ntotal == 3
+    # restart: load_or_build picks the files up (indexer.py:97-101)
+    ix2, created2 = make(tmp_path)
+    ix2.load_or_build()
+    assert created2 == [] and ix2.index.ntotal == 3 and ix2.metadata_store == meta
+
+
+def test_csv_templates_regenerate_the_shipped_corpus(tmp_path):
+    ref = "/root/reference/semantic-indexer/default_data"
+    if not os.path.isdir(ref):
+        pytest.skip("reference checkout not present (GPU box)")
+    ix, _ = make(tmp_path, default_data_dir=ref)
+    n = ix.ingest_csv_data(batch_rows=64)
+    man = json.load(open(os.path.join(ROOT, "tests", "golden", "docqa_metadata_manifest.json")))["rows"]
+    assert n == 647 == ix.index.ntotal
+    assert max(len(c) for c in ix.model.calls) == 64       # batched encode calls
+    for got, want in zip(ix.metadata_store, man[:647]):    # same texts, same order, same sources
+        assert hashlib.sha1(got["text_content"].encode("utf-8")).hexdigest() == want["text_sha1"]
+        assert got["source"] == want["source"] and got["type"] == want["type"] == "knowledge_base"
+
+
+def test_device_encoder_path_uses_fused_pooling(tmp_path):
+    """An encoder that returns token states is routed to add_pooled (K1 fused with the append)."""
+    from docqa_b200.indexer_host import SemanticIndexer
+
+    class TokenModel:
+        def encode_tokens(self, texts):
+            return ("tok", len(texts)), ("mask", len(texts))
+
+    class PooledIndex:
+        ntotal = 0
+
+        def add_pooled(self, tok, mask):
+            assert tok[0] == "tok" and mask[0] == "mask"
+            self.ntotal += tok[1]
+
+    ix = SemanticIndexer(TokenModel(), 8, index_factory=lambda d: PooledIndex(),
+                         index_file=str(tmp_path / "i"), metadata_file=str(tmp_path / "m"))
+    assert ix.add_many(["a", " ", "b"], "src") == 2
+    assert ix.index.ntotal == 2 and len(ix.metadata_store) == 2
