@@ -17,6 +17,7 @@ STORE_F32 = 0
 STORE_BF16 = 1
 DT_F32, DT_F16, DT_BF16, DT_I64, DT_I32, DT_U8 = 0, 1, 2, 3, 4, 5
 ALGO_AUTO, ALGO_EXACT_SIMT, ALGO_TENSOR = 0, 1, 2
+ALGO_FLAG_DEFER = 0x100
 MAX_K = 2048
 MAX_D = 2048
 
@@ -36,9 +37,11 @@ class SearchStats(ctypes.Structure):
 EXPORTS = [
     "bfk_last_error", "bfk_version", "bfk_device_count", "bfk_create", "bfk_free", "bfk_dim",
     "bfk_metric", "bfk_storage", "bfk_device", "bfk_ntotal", "bfk_reserve", "bfk_add",
-    "bfk_add_pooled", "bfk_pool_normalize", "bfk_search", "bfk_search_ex", "bfk_reset",
+    "bfk_add_pooled", "bfk_pool_normalize", "bfk_search", "bfk_search_ex", "bfk_search_finish", "bfk_search_pending_nflag_ptr", "bfk_reset",
+    "bfk_xchg_create", "bfk_xchg_connect", "bfk_xchg_capacity", "bfk_xchg_merge", "bfk_xchg_last_max_nflag",
+    "bfk_xchg_free",
     "bfk_reconstruct", "bfk_remove_ids", "bfk_write", "bfk_read", "bfk_serialized_size",
-    "bfk_serialize", "bfk_deserialize", "bfk_normalize_l2", "bfk_merge_topk", "bfk_search_noalloc",
+    "bfk_serialize", "bfk_deserialize", "bfk_normalize_l2", "bfk_merge_topk", "bfk_merge_topk_strided", "bfk_search_noalloc",
 ]
 
 _lib = None
@@ -72,6 +75,17 @@ def load() -> ctypes.CDLL:
     L.bfk_pool_normalize.argtypes = [vp, i32, vp, i32, i64, i32, i32, vp, i32, i32, vp]
     L.bfk_search.argtypes = [vp, vp, i64, i64, vp, vp, i32, vp]
     L.bfk_search_ex.argtypes = [vp, vp, i64, i64, vp, vp, i32, vp, i32, i64, ctypes.POINTER(SearchStats)]
+    L.bfk_search_finish.argtypes = [vp, vp, ctypes.POINTER(i64)]
+    L.bfk_search_pending_nflag_ptr.argtypes = [vp]
+    L.bfk_search_pending_nflag_ptr.restype = vp
+    L.bfk_xchg_create.argtypes = [i32, i32, i32, i64, ctypes.POINTER(vp), vp]
+    L.bfk_xchg_connect.argtypes = [vp, vp]
+    L.bfk_xchg_capacity.argtypes = [vp]
+    L.bfk_xchg_capacity.restype = i64
+    L.bfk_xchg_merge.argtypes = [vp, vp, vp, i64, i64, i32, vp, vp, vp, vp]
+    L.bfk_xchg_last_max_nflag.argtypes = [vp]
+    L.bfk_xchg_last_max_nflag.restype = i64
+    L.bfk_xchg_free.argtypes = [vp]
     L.bfk_reset.argtypes = [vp]
     L.bfk_reconstruct.argtypes = [vp, i64, i64, vp, i32]
     L.bfk_remove_ids.argtypes = [vp, vp, i64, ctypes.POINTER(i64)]
@@ -83,6 +97,7 @@ def load() -> ctypes.CDLL:
     L.bfk_deserialize.argtypes = [vp, i64, i32, i32, ctypes.POINTER(vp)]
     L.bfk_normalize_l2.argtypes = [vp, i64, i32, i32, i32, vp]
     L.bfk_merge_topk.argtypes = [vp, vp, i32, i64, i64, i32, vp, vp, i32, vp]
+    L.bfk_merge_topk_strided.argtypes = [vp, i64, vp, i64, i32, i64, i64, i32, vp, vp, i32, vp]
     L.bfk_search_noalloc.argtypes = [vp, vp, i64, i64, vp, vp, vp]
     _lib = L
     return L

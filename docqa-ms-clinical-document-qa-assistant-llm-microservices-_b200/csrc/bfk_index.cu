@@ -231,6 +231,7 @@ static int rows_out(const bfk_index* idx, int64_t i0, int64_t n, float* out, int
 
 static int add_rows(bfk_index* idx, const float* x, int64_t n, int x_is_device, cudaStream_t st) {
     if (n == 0) return 0;
+    BFK_TRY(search_tensor_finish(idx, st, nullptr));  // a deferred search still owns the workspace
     if (!x) return fail("add: null input");
     if (idx->ntotal + n > 0x7fffffffll) return fail("add: a single shard holds at most 2^31-1 rows");
     BFK_TRY(ensure_capacity(idx, idx->ntotal + n, st));
@@ -288,6 +289,7 @@ int bfk_free(bfk_index* idx) {
     if (!idx) return 0;
     DeviceGuard g(idx->device);
     cudaDeviceSynchronize();
+    search_tensor_forget(idx);
     free_storage(idx);
     if (idx->ws.ptr) cudaFree(idx->ws.ptr);
     if (idx->maxn) cudaFree(idx->maxn);
@@ -345,6 +347,7 @@ int bfk_add_pooled(bfk_index* idx, const void* tok, int tok_dtype, const void* m
     if (idx->ntotal + B > 0x7fffffffll) return fail("add: a single shard holds at most 2^31-1 rows");
     DeviceGuard g(idx->device);
     cudaStream_t st = (cudaStream_t)stream;
+    BFK_TRY(search_tensor_finish(idx, st, nullptr));
     BFK_TRY(ensure_capacity(idx, idx->ntotal + B, st));
     float* o32 = idx->x32 ? idx->x32 + (size_t)idx->ntotal * idx->ld32 : nullptr;
     __nv_bfloat16* o16 = idx->x16 + (size_t)idx->ntotal * idx->ld16;
@@ -402,6 +405,9 @@ int bfk_search_ex(bfk_index* idx, const float* q, int64_t nq, int64_t k64, float
     DeviceGuard g(idx->device);
     cudaStream_t st = (cudaStream_t)stream;
     std::lock_guard<std::mutex> lk(idx->mu);
+    const int defer = (algo & BFK_ALGO_FLAG_DEFER) && io_is_device && !stats;
+    algo &= ~BFK_ALGO_FLAG_DEFER;
+    BFK_TRY(search_tensor_finish(idx, st, nullptr));  // a deferred search nobody settled: settle it first
 
     if (algo == BFK_ALGO_AUTO) {
         // fp32 rows: up to 8 queries the exact scan is one HBM-speed pass; bf16-stored rows scan faster
@@ -453,7 +459,7 @@ int bfk_search_ex(bfk_index* idx, const float* q, int64_t nq, int64_t k64, float
     }
     int rc;
     if (algo == BFK_ALGO_TENSOR) {
-        rc = search_tensor(idx, q_dev, ldq, nq, k, D_out, I_out, id_offset, tail, tail_avail, st, stats, ev0, ev1);
+        rc = search_tensor(idx, q_dev, ldq, nq, k, D_out, I_out, id_offset, tail, tail_avail, st, stats, ev0, ev1, defer);
     } else {
         rc = search_exact(idx, q_dev, ldq, nq, k, D_out, I_out, id_offset, tail, tail_avail, st, stats, ev0, ev1);
     }
@@ -479,10 +485,20 @@ int bfk_search_ex(bfk_index* idx, const float* q, int64_t nq, int64_t k64, float
     return rc;
 }
 
+int bfk_search_finish(bfk_index* idx, void* stream, int64_t* n_rewritten) {
+    if (!idx) return fail("null index");
+    DeviceGuard g(idx->device);
+    std::lock_guard<std::mutex> lk(idx->mu);
+    return search_tensor_finish(idx, (cudaStream_t)stream, n_rewritten);
+}
+
+const void* bfk_search_pending_nflag_ptr(bfk_index* idx) { return idx ? (const void*)search_tensor_pending_nflag(idx) : nullptr; }
+
 int bfk_reset(bfk_index* idx) {
     if (!idx) return fail("null index");
     DeviceGuard g(idx->device);
     std::lock_guard<std::mutex> lk(idx->mu);
+    BFK_TRY(search_tensor_finish(idx, 0, nullptr));
     BFK_CUDA(cudaDeviceSynchronize());
     idx->ntotal = 0;
     BFK_CUDA(cudaMemset(idx->maxn, 0, sizeof(unsigned int)));
@@ -511,6 +527,7 @@ int bfk_remove_ids(bfk_index* idx, const int64_t* ids, int64_t n, int64_t* nremo
     std::sort(rm.begin(), rm.end());
     rm.erase(std::unique(rm.begin(), rm.end()), rm.end());
     if (rm.empty()) return 0;
+    BFK_TRY(search_tensor_finish(idx, 0, nullptr));
     BFK_CUDA(cudaDeviceSynchronize());
     // IndexFlatCodes::remove_ids keeps the surviving rows in order: move each kept segment down
     // through fresh buffers (device copies must not overlap)

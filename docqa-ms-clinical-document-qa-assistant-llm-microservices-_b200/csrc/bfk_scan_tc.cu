@@ -36,6 +36,8 @@
 
 #include <cfloat>
 #include <cstdlib>
+#include <mutex>
+#include <utility>
 #include <vector>
 
 #include "bfk_common.cuh"
@@ -1031,9 +1033,131 @@ static int tc_pass(bfk_index* idx, const float* qc, int ldq, int64_t nqc, int k,
     return 0;
 }
 
+// everything needed to settle the uncertified queries of one tensor pass after the fact
+struct TcPending {
+    const float* qc;
+    int ldq;
+    int64_t nqc;
+    int k;
+    float* Dc;
+    int64_t* Ic;
+    int64_t id_offset;
+    TcWs w;
+    TcPlan pl;
+    int fb_nparts;
+};
+
+// Reads the pass's flag list (one stream sync) and settles what was not certified: a second tensor pass
+// over those queries alone, then the exact scan for what is still open.  Returns how many result rows
+// were rewritten through *n_rewritten.
+static int tc_resolve(bfk_index* idx, const TcPending& c, cudaStream_t st, int64_t* n_retry, int64_t* n_fallback,
+                      int64_t* n_rewritten, int* launches) {
+    const TcWs& w = c.w;
+    BFK_CUDA(cudaMemcpyAsync(idx->h_flag, w.flags, sizeof(int), cudaMemcpyDeviceToHost, st));
+    BFK_CUDA(cudaStreamSynchronize(st));
+    int nflag = *idx->h_flag;
+    if (n_rewritten) *n_rewritten += nflag;
+    if (nflag == 0) return 0;
+    std::vector<int> list((size_t)nflag);
+    BFK_CUDA(cudaMemcpyAsync(list.data(), w.flags + 1, sizeof(int) * (size_t)nflag, cudaMemcpyDeviceToHost, st));
+    BFK_CUDA(cudaStreamSynchronize(st));
+
+    // second chance: the same tensor pass over the uncertified queries alone.  Fewer queries means
+    // more corpus streams per query, hence more list room and a better chance to certify -- for the
+    // price of one HBM-bound corpus pass instead of nflag/8 exact passes.
+    TcPlan pl2;
+    if (2 * (int64_t)nflag <= c.nqc && !tc_plan(idx, nflag, c.k, &pl2) && pl2.S >= 2 * c.pl.S) {
+        BFK_CUDA(cudaMemcpyAsync(w.r_list, w.flags + 1, sizeof(int) * (size_t)nflag, cudaMemcpyDeviceToDevice, st));
+        gather_queries_kernel<<<(unsigned)std::min<int64_t>(((int64_t)nflag * c.ldq + 255) / 256, 1184), 256, 0, st>>>(
+            c.qc, c.ldq, w.r_list, nflag, w.r_q);
+        BFK_CUDA(cudaGetLastError());
+        BFK_TRY(tc_pass(idx, w.r_q, c.ldq, nflag, c.k, w.r_D, w.r_I, c.id_offset, w, pl2, st, nullptr, nullptr, launches));
+        scatter_results_kernel<<<(unsigned)std::min<int64_t>(((int64_t)nflag * c.k + 255) / 256, 1184), 256, 0, st>>>(
+            w.r_D, w.r_I, w.r_list, nflag, c.k, c.Dc, c.Ic);
+        BFK_CUDA(cudaGetLastError());
+        *launches += 2;
+        BFK_CUDA(cudaMemcpyAsync(idx->h_flag, w.flags, sizeof(int), cudaMemcpyDeviceToHost, st));
+        BFK_CUDA(cudaStreamSynchronize(st));
+        const int nflag2 = *idx->h_flag;
+        std::vector<int> list2((size_t)nflag2);
+        if (nflag2 > 0) {
+            BFK_CUDA(cudaMemcpyAsync(list2.data(), w.flags + 1, sizeof(int) * (size_t)nflag2, cudaMemcpyDeviceToHost, st));
+            BFK_CUDA(cudaStreamSynchronize(st));
+        }
+        *n_retry += nflag;
+        std::vector<int> still;
+        still.reserve((size_t)nflag2);
+        for (int j : list2) still.push_back(list[(size_t)j]);
+        list.swap(still);
+        nflag = nflag2;
+    }
+
+    // ---- last resort: exact re-run on the GPU (K3a + K4), 8 queries per corpus pass ----
+    std::sort(list.begin(), list.end());
+    for (int g0 = 0; g0 < nflag; g0 += 8) {
+        const int g = std::min(8, nflag - g0);
+        for (int j = 0; j < g; j++)
+            BFK_CUDA(cudaMemcpyAsync(w.fb_q + (size_t)j * c.ldq, c.qc + (size_t)list[g0 + j] * c.ldq, sizeof(float) * c.ldq,
+                                     cudaMemcpyDeviceToDevice, st));
+        BFK_TRY(launch_scan_exact(idx, w.fb_q, c.ldq, g, c.k, w.fb_part, c.fb_nparts, st));
+        BFK_TRY(launch_select(w.fb_part, (int64_t)c.fb_nparts * c.k, g, c.k, idx->metric, c.id_offset, w.fb_D, w.fb_I, c.k, st));
+        *launches += 2;
+        for (int j = 0; j < g; j++) {
+            const size_t row = (size_t)list[g0 + j] * c.k;
+            BFK_CUDA(cudaMemcpyAsync(c.Dc + row, w.fb_D + (size_t)j * c.k, sizeof(float) * c.k, cudaMemcpyDeviceToDevice, st));
+            BFK_CUDA(cudaMemcpyAsync(c.Ic + row, w.fb_I + (size_t)j * c.k, sizeof(int64_t) * c.k, cudaMemcpyDeviceToDevice, st));
+        }
+    }
+    *n_fallback += nflag;
+    return 0;
+}
+
+// one deferred pass per index at most; settled by search_tensor_finish (or by the next search)
+static std::mutex g_pending_mu;
+static std::vector<std::pair<bfk_index*, TcPending>> g_pending;
+
+int search_tensor_finish(bfk_index* idx, cudaStream_t st, int64_t* n_rewritten) {
+    TcPending c;
+    bool have = false;
+    {
+        std::lock_guard<std::mutex> lk(g_pending_mu);
+        for (size_t i = 0; i < g_pending.size(); i++)
+            if (g_pending[i].first == idx) {
+                c = g_pending[i].second;
+                g_pending.erase(g_pending.begin() + (long)i);
+                have = true;
+                break;
+            }
+    }
+    if (n_rewritten) *n_rewritten = 0;
+    if (!have) return 0;
+    int launches = 0;
+    int64_t n_retry = 0, n_fallback = 0;
+    return tc_resolve(idx, c, st, &n_retry, &n_fallback, n_rewritten, &launches);
+}
+
+// device address of the uncertified-query count of the pass a deferred search left pending (or nullptr)
+const int* search_tensor_pending_nflag(bfk_index* idx) {
+    std::lock_guard<std::mutex> lk(g_pending_mu);
+    for (size_t i = 0; i < g_pending.size(); i++)
+        if (g_pending[i].first == idx) return g_pending[i].second.w.flags;
+    return nullptr;
+}
+
+void search_tensor_forget(bfk_index* idx) {
+    std::lock_guard<std::mutex> lk(g_pending_mu);
+    for (size_t i = 0; i < g_pending.size(); i++)
+        if (g_pending[i].first == idx) {
+            g_pending.erase(g_pending.begin() + (long)i);
+            break;
+        }
+}
+
+// defer != 0 (single chunk only): enqueue the pass and return without looking at the flags; the caller
+// must settle with search_tensor_finish before trusting the results.
 int search_tensor(bfk_index* idx, const float* q_dev, int ldq, int64_t nq, int k, float* D_dev, int64_t* I_dev,
                   int64_t id_offset, char* ws_tail, size_t ws_tail_bytes, cudaStream_t st, bfk_search_stats* stats,
-                  cudaEvent_t ev0, cudaEvent_t ev1) {
+                  cudaEvent_t ev0, cudaEvent_t ev1, int defer) {
     const int64_t chunk = tc_chunk_queries(idx);
     int launches = 0;
     int64_t n_fallback = 0, n_retry = 0;
@@ -1042,73 +1166,26 @@ int search_tensor(bfk_index* idx, const float* q_dev, int ldq, int64_t nq, int k
     BFK_TRY(scan_exact_workspace(idx, 8, k, &sb, &fb_nparts));
     for (int64_t q0 = 0; q0 < nq; q0 += chunk) {
         const int64_t nqc = std::min(chunk, nq - q0);
-        TcPlan pl;
-        if (tc_plan(idx, nqc, k, &pl)) return fail("tensor path: shape not supported");
-        TcWs w;
-        tc_carve(idx, nqc, k, fb_nparts, ws_tail, &w);
-        if (w.bytes > ws_tail_bytes) return fail("internal: tensor-path workspace under-sized");
-        const float* qc = q_dev + (size_t)q0 * ldq;
-        float* Dc = D_dev + (size_t)q0 * k;
-        int64_t* Ic = I_dev + (size_t)q0 * k;
-        BFK_TRY(tc_pass(idx, qc, ldq, nqc, k, Dc, Ic, id_offset, w, pl, st, q0 == 0 ? ev0 : nullptr,
+        TcPending c;
+        if (tc_plan(idx, nqc, k, &c.pl)) return fail("tensor path: shape not supported");
+        tc_carve(idx, nqc, k, fb_nparts, ws_tail, &c.w);
+        if (c.w.bytes > ws_tail_bytes) return fail("internal: tensor-path workspace under-sized");
+        c.qc = q_dev + (size_t)q0 * ldq;
+        c.ldq = ldq;
+        c.nqc = nqc;
+        c.k = k;
+        c.Dc = D_dev + (size_t)q0 * k;
+        c.Ic = I_dev + (size_t)q0 * k;
+        c.id_offset = id_offset;
+        c.fb_nparts = fb_nparts;
+        BFK_TRY(tc_pass(idx, c.qc, ldq, nqc, k, c.Dc, c.Ic, id_offset, c.w, c.pl, st, q0 == 0 ? ev0 : nullptr,
                         q0 + chunk >= nq ? ev1 : nullptr, &launches));
-
-        // ---- uncertified queries ----
-        BFK_CUDA(cudaMemcpyAsync(idx->h_flag, w.flags, sizeof(int), cudaMemcpyDeviceToHost, st));
-        BFK_CUDA(cudaStreamSynchronize(st));
-        int nflag = *idx->h_flag;
-        if (nflag == 0) continue;
-        std::vector<int> list((size_t)nflag);
-        BFK_CUDA(cudaMemcpyAsync(list.data(), w.flags + 1, sizeof(int) * (size_t)nflag, cudaMemcpyDeviceToHost, st));
-        BFK_CUDA(cudaStreamSynchronize(st));
-
-        // second chance: the same tensor pass over the uncertified queries alone.  Fewer queries means
-        // more corpus streams per query, hence more list room and a better chance to certify -- for the
-        // price of one HBM-bound corpus pass instead of nflag/8 exact passes.
-        TcPlan pl2;
-        if (2 * (int64_t)nflag <= nqc && !tc_plan(idx, nflag, k, &pl2) && pl2.S >= 2 * pl.S) {
-            BFK_CUDA(cudaMemcpyAsync(w.r_list, w.flags + 1, sizeof(int) * (size_t)nflag, cudaMemcpyDeviceToDevice, st));
-            gather_queries_kernel<<<(unsigned)std::min<int64_t>(((int64_t)nflag * ldq + 255) / 256, 1184), 256, 0, st>>>(
-                qc, ldq, w.r_list, nflag, w.r_q);
-            BFK_CUDA(cudaGetLastError());
-            BFK_TRY(tc_pass(idx, w.r_q, ldq, nflag, k, w.r_D, w.r_I, id_offset, w, pl2, st, nullptr, nullptr, &launches));
-            scatter_results_kernel<<<(unsigned)std::min<int64_t>(((int64_t)nflag * k + 255) / 256, 1184), 256, 0, st>>>(
-                w.r_D, w.r_I, w.r_list, nflag, k, Dc, Ic);
-            BFK_CUDA(cudaGetLastError());
-            launches += 2;
-            BFK_CUDA(cudaMemcpyAsync(idx->h_flag, w.flags, sizeof(int), cudaMemcpyDeviceToHost, st));
-            BFK_CUDA(cudaStreamSynchronize(st));
-            const int nflag2 = *idx->h_flag;
-            std::vector<int> list2((size_t)nflag2);
-            if (nflag2 > 0) {
-                BFK_CUDA(cudaMemcpyAsync(list2.data(), w.flags + 1, sizeof(int) * (size_t)nflag2, cudaMemcpyDeviceToHost, st));
-                BFK_CUDA(cudaStreamSynchronize(st));
-            }
-            n_retry += nflag;
-            std::vector<int> still;
-            still.reserve((size_t)nflag2);
-            for (int j : list2) still.push_back(list[(size_t)j]);
-            list.swap(still);
-            nflag = nflag2;
+        if (defer && nq <= chunk) {
+            std::lock_guard<std::mutex> lk(g_pending_mu);
+            g_pending.emplace_back(idx, c);
+            break;
         }
-
-        // ---- last resort: exact re-run on the GPU (K3a + K4), 8 queries per corpus pass ----
-        std::sort(list.begin(), list.end());
-        for (int g0 = 0; g0 < nflag; g0 += 8) {
-            const int g = std::min(8, nflag - g0);
-            for (int j = 0; j < g; j++)
-                BFK_CUDA(cudaMemcpyAsync(w.fb_q + (size_t)j * ldq, qc + (size_t)list[g0 + j] * ldq, sizeof(float) * ldq,
-                                         cudaMemcpyDeviceToDevice, st));
-            BFK_TRY(launch_scan_exact(idx, w.fb_q, ldq, g, k, w.fb_part, fb_nparts, st));
-            BFK_TRY(launch_select(w.fb_part, (int64_t)fb_nparts * k, g, k, idx->metric, id_offset, w.fb_D, w.fb_I, k, st));
-            launches += 2;
-            for (int j = 0; j < g; j++) {
-                const size_t row = (size_t)list[g0 + j] * k;
-                BFK_CUDA(cudaMemcpyAsync(Dc + row, w.fb_D + (size_t)j * k, sizeof(float) * k, cudaMemcpyDeviceToDevice, st));
-                BFK_CUDA(cudaMemcpyAsync(Ic + row, w.fb_I + (size_t)j * k, sizeof(int64_t) * k, cudaMemcpyDeviceToDevice, st));
-            }
-        }
-        n_fallback += nflag;
+        BFK_TRY(tc_resolve(idx, c, st, &n_retry, &n_fallback, nullptr, &launches));
     }
     if (stats) {
         stats->n_launches = launches;

@@ -141,7 +141,8 @@ int launch_select(const uint64_t* cand, int64_t m_per_query, int64_t nq, int k, 
 
 // (D, I) lists [nparts][nq][k] -> composites [nq][nparts*k]; low word = part*k + slot so that
 // equal distances resolve by shard then by the shard's own (distance, id) order.
-__global__ void __launch_bounds__(256) pack_parts_kernel(const float* __restrict__ Dp, const int64_t* __restrict__ Ip,
+__global__ void __launch_bounds__(256) pack_parts_kernel(const float* __restrict__ Dp, int64_t d_part_stride,
+                                                         const int64_t* __restrict__ Ip, int64_t i_part_stride,
                                                          int nparts, int64_t nq, int k, int metric,
                                                          uint64_t* __restrict__ cand) {
     const int64_t total = (int64_t)nparts * nq * k;
@@ -151,8 +152,9 @@ __global__ void __launch_bounds__(256) pack_parts_kernel(const float* __restrict
         int64_t q = r / k;
         int s = (int)(r - q * k);
         uint64_t c = COMP_EMPTY;
-        if (Ip[i] >= 0) {
-            float key = (metric == BFK_METRIC_L2) ? Dp[i] : -Dp[i];
+        if (Ip[p * i_part_stride + r] >= 0) {
+            const float dv = Dp[p * d_part_stride + r];
+            float key = (metric == BFK_METRIC_L2) ? dv : -dv;
             c = make_comp(key, (uint32_t)(p * k + s));
         }
         cand[q * ((int64_t)nparts * k) + p * k + s] = c;
@@ -164,7 +166,7 @@ int launch_pack_parts(const float* Dparts, const int64_t* Iparts, int nparts, in
     const int64_t total = (int64_t)nparts * nq * k;
     if (total <= 0) return 0;
     int64_t blocks = std::min<int64_t>((total + 255) / 256, 148 * 8);
-    pack_parts_kernel<<<(unsigned)blocks, 256, 0, st>>>(Dparts, Iparts, nparts, nq, k, metric, cand);
+    pack_parts_kernel<<<(unsigned)blocks, 256, 0, st>>>(Dparts, nq * k, Iparts, nq * k, nparts, nq, k, metric, cand);
     BFK_CUDA(cudaGetLastError());
     return 0;
 }
@@ -172,9 +174,12 @@ int launch_pack_parts(const float* Dparts, const int64_t* Iparts, int nparts, in
 }  // namespace bfk
 
 // Merge step of the row-sharded search.  Scratch: nq*nparts*k composites, allocated per call
-// with the stream-ordered allocator (the payload is tiny; BASELINE config 5).
-extern "C" int bfk_merge_topk(const float* Dparts, const int64_t* Iparts, int nparts, int64_t nq, int64_t k,
-                              int metric, float* D, int64_t* I, int device, void* stream) {
+// with the stream-ordered allocator (the payload is tiny; BASELINE config 5).  Part p's lists start at
+// Dparts + p*d_part_stride / Iparts + p*i_part_stride (elements), so the caller can hand over the
+// all-gather buffer as it is, without repacking.
+extern "C" int bfk_merge_topk_strided(const float* Dparts, int64_t d_part_stride, const int64_t* Iparts,
+                                      int64_t i_part_stride, int nparts, int64_t nq, int64_t k, int metric, float* D,
+                                      int64_t* I, int device, void* stream) {
     using namespace bfk;
     if (nparts <= 0 || nq < 0 || k <= 0 || k > BFK_MAX_K) return fail("merge_topk: bad arguments");
     if (nq == 0) return 0;
@@ -189,12 +194,21 @@ extern "C" int bfk_merge_topk(const float* Dparts, const int64_t* Iparts, int np
     cudaStream_t st = (cudaStream_t)stream;
     uint64_t* cand = nullptr;
     BFK_CUDA(cudaMallocAsync((void**)&cand, sizeof(uint64_t) * (size_t)nq * nparts * k, st));
-    int rc = launch_pack_parts(Dparts, Iparts, nparts, nq, (int)k, metric, cand, st);
+    const int64_t total = (int64_t)nparts * nq * k;
+    const int64_t blocks = std::min<int64_t>((total + 255) / 256, 148 * 8);
+    pack_parts_kernel<<<(unsigned)blocks, 256, 0, st>>>(Dparts, d_part_stride, Iparts, i_part_stride, nparts, nq, (int)k,
+                                                        metric, cand);
+    int rc = cudaGetLastError() == cudaSuccess ? 0 : fail("merge_topk: launch failed");
     if (!rc) {
         select_topk_kernel<<<(unsigned)nq, SEL_THREADS, 0, st>>>(cand, (int64_t)nparts * k, (int)k, (int)k, metric, 0,
-                                                                Iparts, k, nq * k, (int)k, D, I, k);
+                                                                Iparts, k, i_part_stride, (int)k, D, I, k);
         if (cudaGetLastError() != cudaSuccess) rc = fail("merge_topk: launch failed");
     }
     cudaFreeAsync(cand, st);
     return rc;
+}
+
+extern "C" int bfk_merge_topk(const float* Dparts, const int64_t* Iparts, int nparts, int64_t nq, int64_t k,
+                              int metric, float* D, int64_t* I, int device, void* stream) {
+    return bfk_merge_topk_strided(Dparts, nq * k, Iparts, nq * k, nparts, nq, k, metric, D, I, device, stream);
 }

@@ -159,7 +159,8 @@ class IndexFlat:
         other.reset()
 
     # -- queries ------------------------------------------------------------------------
-    def search(self, x, k, *, params=None, D=None, I=None, algo=None, id_offset: int = 0, stats=None):
+    def search(self, x, k, *, params=None, D=None, I=None, algo=None, id_offset: int = 0, stats=None,
+               defer: bool = False):
         n, d = x.shape
         assert d == self.d
         assert k > 0
@@ -181,7 +182,8 @@ class IndexFlat:
                 assert tuple(I.shape) == (n, k) and I.dtype == torch.int64 and I.is_contiguous()
             _lib.check(self._L.bfk_search_ex(self._h, ctypes.c_void_p(xq.data_ptr()), n, k,
                                               ctypes.c_void_p(D.data_ptr()), ctypes.c_void_p(I.data_ptr()), 1,
-                                              _torch_stream(self.device), _ALGO[algo], int(id_offset), stp))
+                                              _torch_stream(self.device),
+                                              _ALGO[algo] | (_lib.ALGO_FLAG_DEFER if defer else 0), int(id_offset), stp))
             return D, I
         x = np.ascontiguousarray(x, dtype="float32")
         if D is None:
@@ -197,6 +199,16 @@ class IndexFlat:
         _lib.check(self._L.bfk_search_ex(self._h, _np_ptr(x), n, k, _np_ptr(D), _np_ptr(I), 0, None,
                                           _ALGO[algo], int(id_offset), stp))
         return D, I
+
+    def finish(self) -> int:
+        """Settle a `search(..., defer=True)`: wait, re-run uncertified queries, return rows rewritten.
+
+        Extension (no faiss counterpart): with defer=True a CUDA-tensor search only enqueues work, so the
+        caller can queue more GPU work behind it; (D, I) are final once finish() has returned.
+        """
+        n = ctypes.c_int64(0)
+        _lib.check(self._L.bfk_search_finish(self._h, _torch_stream(self.device), ctypes.byref(n)))
+        return int(n.value)
 
     def reconstruct(self, key, x=None):
         key = int(key)

@@ -64,6 +64,7 @@ class ShardedIndexFlat:
             local_index = IndexFlat(d, metric, device=device, storage=storage)
         self.local = local_index
         self._merge = merge_fn
+        self._redo_check = True
         # piecewise-linear local -> global id map: local rows [ls, ls+n) are global [gs, gs+n)
         self._seg_local: list[int] = []
         self._seg_global: list[int] = []
@@ -118,6 +119,65 @@ class ShardedIndexFlat:
         out = gstarts[seg] + (I - starts[seg])
         return torch.where(I >= 0, out, I)
 
+    def _exchange(self, nk, device):
+        """The NVLink peer-memory exchange (K6x), created collectively on first use / when it must grow."""
+        import torch
+
+        L = _lib.load()
+        if getattr(self, "_xh", None) is not None and L.bfk_xchg_capacity(self._xh) >= nk:
+            return self._xh
+        if getattr(self, "_xh", None) is not None:
+            torch.cuda.synchronize(device)
+            self._dist.barrier(group=self.group)
+            L.bfk_xchg_free(self._xh)
+            self._xh = None
+        cap = max(int(nk) * 2, 1 << 16)
+        h = ctypes.c_void_p()
+        mine = np.zeros(64, dtype=np.uint8)
+        _lib.check(L.bfk_xchg_create(device.index, self.world, self.rank, cap, ctypes.byref(h),
+                                      ctypes.c_void_p(mine.ctypes.data)))
+        # 64-byte CUDA IPC handles travel as 8 int64 words through the existing process group
+        mine_t = torch.from_numpy(mine.view(np.int64).copy()).to(device)
+        all_t = torch.empty((self.world, 8), dtype=torch.int64, device=device)
+        self._dist.all_gather_into_tensor(all_t, mine_t, group=self.group)
+        allh = np.ascontiguousarray(all_t.cpu().numpy()).view(np.uint8)
+        _lib.check(L.bfk_xchg_connect(h, ctypes.c_void_p(allh.ctypes.data)))
+        self._dist.barrier(group=self.group)
+        self._xh = h
+        return h
+
+    def __del__(self):
+        h, self._xh = getattr(self, "_xh", None), None
+        if h:
+            try:
+                _lib.load().bfk_xchg_free(h)
+            except Exception:
+                pass
+
+    def _gpu_buffers(self, n, k, device):
+        """Per (n, k): one byte buffer holding this rank's D then I, the gather target, and the outputs."""
+        import torch
+
+        key = (n, k)
+        buf = self._bufs.get(key) if hasattr(self, "_bufs") else None
+        if buf is None:
+            if not hasattr(self, "_bufs"):
+                self._bufs = {}
+            # int64 words: [ceil(n*k/2) words holding the fp32 distances][n*k words holding the ids]
+            wd = (n * k + 1) // 2
+            nwords = wd + n * k
+            mine = torch.empty(nwords, dtype=torch.int64, device=device)
+            allb = torch.empty((self.world, nwords), dtype=torch.int64, device=device)
+            buf = {
+                "mine": mine, "all": allb, "off_i": wd * 8, "nbytes": nwords * 8,
+                "D": mine[:wd].view(torch.float32)[: n * k].view(n, k),
+                "I": mine[wd:].view(n, k),
+            }
+            if len(self._bufs) > 16:
+                self._bufs.clear()
+            self._bufs[key] = buf
+        return buf
+
     def search(self, x, k, *, algo=None):
         import torch
 
@@ -130,13 +190,41 @@ class ShardedIndexFlat:
         kw = {}
         if algo is not None:
             kw["algo"] = algo
-        if single and hasattr(self.local, "_h"):
+        on_gpu = hasattr(self.local, "_h")
+        if on_gpu and single and self._merge is None and self.world > 1:
+            # fast path: the kernels write (D, I) with global ids straight into the send buffer, ONE
+            # all-gather of raw bytes, and the merge kernel reads the gather buffer in place
+            dev = torch.device("cuda", self.local.device)
+            b = self._gpu_buffers(n, k, dev)
+            xq = x if is_torch else torch.from_numpy(np.ascontiguousarray(x, dtype=np.float32)).to(dev)
+            # the local search is only ENQUEUED (defer); the peer-memory exchange + merge kernels queue up
+            # behind it, so the host never waits for the scan before launching them, and no host-launched
+            # collective sits on the critical path
+            L = _lib.load()
+            xh = self._exchange(n * k, dev)
+            off = self._seg_global[0] - self._seg_local[0]
+            self.local.search(xq, k, D=b["D"], I=b["I"], id_offset=off, defer=True, **kw)
+            st = ctypes.c_void_p(torch.cuda.current_stream(dev.index).cuda_stream)
+            Dout = torch.empty((n, k), dtype=torch.float32, device=dev)
+            Iout = torch.empty((n, k), dtype=torch.int64, device=dev)
+            args = (ctypes.c_void_p(b["D"].data_ptr()), ctypes.c_void_p(b["I"].data_ptr()), n, k, self.metric_type)
+            outs = (ctypes.c_void_p(Dout.data_ptr()), ctypes.c_void_p(Iout.data_ptr()), st)
+            _lib.check(L.bfk_xchg_merge(xh, *args, L.bfk_search_pending_nflag_ptr(self.local._h), *outs))
+            self.local.finish()  # waits for the stream when a tensor pass was pending; re-runs uncertified queries
+            torch.cuda.current_stream(dev.index).synchronize()
+            if L.bfk_xchg_last_max_nflag(xh) > 0:
+                # some rank had to rewrite answers: every rank saw the same count, so all repeat the exchange
+                _lib.check(L.bfk_xchg_merge(xh, *args, None, *outs))
+                torch.cuda.current_stream(dev.index).synchronize()
+            if is_torch:
+                return Dout, Iout
+            return Dout.cpu().numpy(), Iout.cpu().numpy()
+        if single and on_gpu:
             # ids come back global straight from the kernel's epilogue
             kw["id_offset"] = self._seg_global[0] - self._seg_local[0]
         Dl, Il = self.local.search(x, k, **kw)
         if isinstance(Dl, np.ndarray):
             Dl, Il = torch.from_numpy(np.ascontiguousarray(Dl)), torch.from_numpy(np.ascontiguousarray(Il))
-        on_gpu = hasattr(self.local, "_h")
         if on_gpu and not Dl.is_cuda:
             dev = torch.device("cuda", self.local.device)
             Dl, Il = Dl.to(dev), Il.to(dev)

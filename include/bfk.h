@@ -52,6 +52,12 @@ extern "C" {
 #define BFK_ALGO_EXACT_SIMT 1  /* fp32 direct-distance scan (faiss's nq<20 arithmetic)  */
 #define BFK_ALGO_TENSOR 2      /* bf16 tcgen05 scan + exact fp32 rerank + certificate   */
 
+/* OR-ed into `algo`, device pointers only: enqueue the search and return without checking which
+ * answers were certified exact; (D, I) are final only after bfk_search_finish.  Lets a caller queue
+ * more GPU work (the row-sharded index queues its all-gather and merge) behind the scan instead of
+ * idling the GPU while the host waits. */
+#define BFK_ALGO_FLAG_DEFER 0x100
+
 #define BFK_MAX_K 2048 /* faiss-cpu has no cap; faiss-gpu's historic cap is 2048 */
 #define BFK_MAX_D 2048
 
@@ -109,6 +115,13 @@ int bfk_search_ex(bfk_index* idx, const float* q, int64_t nq, int64_t k, float* 
                   int io_is_device, void* stream, int algo, int64_t id_offset,
                   bfk_search_stats* stats);
 
+/* settles a search started with BFK_ALGO_FLAG_DEFER: waits for it, re-runs the queries whose answer
+ * was not certified (on the GPU) and reports how many result rows it rewrote; a no-op otherwise */
+int bfk_search_finish(bfk_index* idx, void* stream, int64_t* n_rewritten);
+/* device address of the int holding how many answers of the pending deferred search are not yet
+ * certified (NULL when nothing is pending); consumed by bfk_xchg_merge */
+const void* bfk_search_pending_nflag_ptr(bfk_index* idx);
+
 /* index.reset() / reconstruct / reconstruct_n / remove_ids -- LangChain side paths
  * on the object built at llm-qa/main.py:53-58 */
 int bfk_reset(bfk_index* idx);
@@ -132,6 +145,25 @@ int bfk_normalize_l2(float* x, int64_t n, int d, int x_is_device, int device, vo
  * sorted results after the all-gather; writes the global top-k.  Device pointers. */
 int bfk_merge_topk(const float* Dparts, const int64_t* Iparts, int nparts, int64_t nq, int64_t k,
                    int metric, float* D, int64_t* I, int device, void* stream);
+/* same, for parts that are not densely packed: part p starts at Dparts + p*d_part_stride and
+ * Iparts + p*i_part_stride (strides in elements) -- the all-gather buffer can be merged in place */
+int bfk_merge_topk_strided(const float* Dparts, int64_t d_part_stride, const int64_t* Iparts,
+                           int64_t i_part_stride, int nparts, int64_t nq, int64_t k, int metric, float* D,
+                           int64_t* I, int device, void* stream);
+
+/* Row-sharded search, latency path (BASELINE config 5; no reference counterpart): exchange of the
+ * per-GPU lists over NVLink peer memory fused with the merge, instead of a host-launched collective.
+ * One process per GPU: create -> all-gather the 64-byte IPC handles by any means -> connect; then per
+ * search bfk_xchg_merge(local lists) on every rank.  After synchronising `stream`,
+ * bfk_xchg_last_max_nflag() > 0 (the same value on every rank) means some rank still has to settle
+ * uncertified answers (bfk_search_finish) and ALL ranks must call bfk_xchg_merge again. */
+int bfk_xchg_create(int device, int world, int rank, int64_t max_nq_times_k, void** out, uint8_t* ipc_handle_out);
+int bfk_xchg_connect(void* handle, const uint8_t* all_handles);
+int64_t bfk_xchg_capacity(void* handle);
+int bfk_xchg_merge(void* handle, const float* D_local, const int64_t* I_local, int64_t nq, int64_t k, int metric,
+                   const int* nflag_dev, float* D_out, int64_t* I_out, void* stream);
+int64_t bfk_xchg_last_max_nflag(void* handle);
+int bfk_xchg_free(void* handle);
 
 /* Exact search that allocates nothing (no counterpart in the reference, whose faiss-cpu
  * index simply mallocs).  For callers that must not call cudaMalloc once they are running:
