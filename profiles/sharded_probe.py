@@ -40,6 +40,25 @@ for nq in (1, 64):
     Dg, Ig = unpack()
     from docqa_b200.sharded import _cuda_merge
     t_mg = timeit(lambda: _cuda_merge(Dg, Ig, k, 1))
+    # the peer-memory exchange alone (static lists), and the deferred local search + finish alone
+    import ctypes
+    from docqa_b200 import _lib
+    L = _lib.load()
+    xh = idx._exchange(nq * k, dev)
+    b = idx._gpu_buffers(nq, k, dev)
+    Do = torch.empty((nq, k), device=dev); Io = torch.empty((nq, k), dtype=torch.int64, device=dev)
+    stp = ctypes.c_void_p(torch.cuda.current_stream(dev.index).cuda_stream)
+    def xonly():
+        _lib.check(L.bfk_xchg_merge(xh, ctypes.c_void_p(b["D"].data_ptr()), ctypes.c_void_p(b["I"].data_ptr()), nq, k, 1,
+                                    None, ctypes.c_void_p(Do.data_ptr()), ctypes.c_void_p(Io.data_ptr()), stp))
+    t_x = timeit(xonly)
+    def xsync():
+        xonly(); torch.cuda.current_stream().synchronize()
+    t_xs = timeit(xsync)
+    def defer_finish():
+        idx.local.search(q, k, D=b["D"], I=b["I"], id_offset=lo, defer=True); idx.local.finish()
+    t_df = timeit(defer_finish)
     if rank == 0:
+        print(f"nq={nq} xchg pipelined {t_x:.3f} xchg+sync {t_xs:.3f} defer+finish {t_df:.3f}", flush=True)
         print(f"nq={nq} world={world}: local {t_local:.3f} ms | full {t_full:.3f} numpy-api {t_np:.3f} | pack {t_pack:.3f} allgather {t_ag:.3f} unpack {t_un:.3f} merge {t_mg:.3f}", flush=True)
 dist.destroy_process_group()
