@@ -87,6 +87,10 @@ class ClockSampler:
                 "samples": len(sm), "reasons": sorted(reasons)}
 
 
+SPEC_HBM_GBS = 8000.0      # B200 data sheet; the north star quotes "~8 TB/s"
+SPEC_BF16_TFLOPS = 2250.0  # dense bf16
+
+
 def gen_unit_rows(torch, n, d, seed, device, chunk=1 << 20):
     """Seeded N(0, I) rows normalised to unit length, generated on the device in chunks."""
     g = torch.Generator(device=device).manual_seed(seed)
@@ -97,7 +101,14 @@ def gen_unit_rows(torch, n, d, seed, device, chunk=1 << 20):
         yield r0, x
 
 
-def roofline_of(res, nq, n_rows, elem, hbm_peak, tf_peak, peak_kind):
+def roofline_of(*a):
+    """`_roofline_core` plus the fraction against the spec-sheet denominator (SURVEY 8d asks for both)."""
+    r = _roofline_core(*a)
+    r["frac_of_spec"] = r["achieved"] / (SPEC_HBM_GBS if r["bound"] == "hbm" else SPEC_BF16_TFLOPS)
+    return r
+
+
+def _roofline_core(res, nq, n_rows, elem, hbm_peak, tf_peak, peak_kind):
     """Roofline of the dominant (scan) kernel for one measured batch size.
 
     Algorithmic work per launch follows SURVEY 8(d) / DESIGN.md section 4:
@@ -292,6 +303,8 @@ def main():
         print(f"warning: --gpus {args.gpus} but WORLD_SIZE={world}", file=sys.stderr)
 
     workload = args.workload or ("c2" if world == 1 else "c5")
+    if workload == "c5" and args.batches == "1,64,1024,4096":
+        args.batches = "1,64,1024,8192"  # C5 batches
     if workload == "c2":
         n_total, storage, scaling = args.rows or 1_000_000, "f32", "weak" if world == 1 else "strong"
     elif workload == "c3":
