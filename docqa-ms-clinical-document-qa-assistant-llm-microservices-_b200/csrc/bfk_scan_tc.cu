@@ -89,19 +89,21 @@ struct TcParams {
 };
 
 // wait flavour for the single-thread roles + optional cycle accounting
+// (DBG is a template parameter of the kernel: the shipped instantiation carries none of this)
+#define TC_DBG (DBG && p.dbg != nullptr)
 #define TC_WAIT(bar, parity, slot)                                   \
     do {                                                             \
-        const long long _t0 = p.dbg ? clock64() : 0;                 \
-        if (p.parked) mbar_wait_parked(bar, parity);                 \
+        const long long _t0 = TC_DBG ? clock64() : 0;                \
+        if (DBG && p.parked) mbar_wait_parked(bar, parity);          \
         else mbar_wait(bar, parity);                                 \
-        if (p.dbg) dbg_acc[slot] += (unsigned long long)(clock64() - _t0); \
+        if (TC_DBG) dbg_acc[slot] += (unsigned long long)(clock64() - _t0); \
     } while (0)
 
 __device__ __forceinline__ void epi_sync() { asm volatile("bar.sync 2, 256;" ::: "memory"); }
 
 // PAIR is a template parameter, not a run-time flag: a kernel that contains cta_group::2 instructions can
 // only be launched with an even cluster size.
-template <int KP, bool PAIR>
+template <int KP, bool PAIR, bool DBG>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 scan_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmX, const TcParams p) {
     extern __shared__ __align__(1024) unsigned char smem_raw[];
@@ -132,10 +134,10 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
     float* thr_sh = reinterpret_cast<float*>(tmem_slot + 4);  // [128] bound on the global KP-th best key per query row
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const long long dbg_t0 = p.dbg ? clock64() : 0;
+    const long long dbg_t0 = TC_DBG ? clock64() : 0;
     unsigned long long dbg_acc[4] = {0, 0, 0, 0};
     // CTA 0 also records a per-tile event timeline (first 64 tiles) behind the counters: [event][tile]
-    unsigned long long* tl = (p.dbg && blockIdx.x == 0) ? p.dbg + (size_t)gridDim.x * 8 : nullptr;
+    unsigned long long* tl = (TC_DBG && blockIdx.x == 0) ? p.dbg + (size_t)gridDim.x * 8 : nullptr;
 #define TC_MARK(ev, tile) do { if (tl && (tile) < 64) tl[(ev) * 64 + (tile)] = (unsigned long long)(clock64() - dbg_t0); } while (0)
     const int qt = blockIdx.x % p.QT;
     const int s = blockIdx.x / p.QT;
@@ -219,16 +221,17 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
                     }
                 }
             }
-            if (p.dbg) p.dbg[blockIdx.x * 8 + 0] = dbg_acc[0];
+            if (TC_DBG) p.dbg[blockIdx.x * 8 + 0] = dbg_acc[0];
         }
     } else if (warp == 1) {
-        // ===================== MMA issuer (one thread) =====================
-        if (lane == 0 && leader) {
+        // ===================== MMA issuer (converged warp, one elected lane issues) =====================
+        // This warp paces the tensor pipe: 4 MMAs of 128 tensor-cycles per K-block, so its loop has to issue
+        // in well under 512 cycles.  All 32 lanes run the loop together (waits included) and only the
+        // tcgen05 instructions are predicated on elect.sync: with a single active lane ptxas wraps every
+        // tcgen05.mma in a vote/elect/broadcast loop (ncu: ~125 SASS instructions per K-block, the warp
+        // issuing for >50 % of its samples and the epilogue idle a third of the time).
+        if (leader) {
             const uint32_t idesc = make_idesc_bf16(pair ? 2 * TC_BM : TC_BM, TC_BN);
-            // This one thread paces the tensor pipe, so its loop is kept to a handful of 32-bit
-            // instructions per K-block: running stage / phase counters instead of div/mod, and smem
-            // descriptors advanced by adding to their low word (start address >> 4); a first version that
-            // rebuilt everything per K-block spent ~600 cycles between commits (timeline diagnostics).
             const uint64_t desc_hi = make_smem_desc_sw128(0) & 0xffffffff00000000ull;
             const uint32_t desc_lo0 = (uint32_t)(make_smem_desc_sw128(0) & 0xffffffffull);
             const uint32_t a_lo0 = desc_lo0 + ((smem_u32(sA) & 0x3ffffu) >> 4);
@@ -240,42 +243,45 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
             for (int64_t t = t_begin; t < t_end; t++, tcount++) {
                 const uint32_t a = tcount & 1u, aph = (tcount >> 1) & 1u;
                 TC_WAIT(&tempty_bar[a], aph ^ 1u, 2);  // every epilogue thread (of the pair) has drained accumulator a
-                TC_MARK(2, tcount);
+                if (lane == 0) TC_MARK(2, tcount);
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + a * TC_BN;
                 uint32_t a_lo = a_lo0;  // resident query tile: K-block kb at + kb * 16 KiB
                 for (int kb = 0; kb < p.KB; kb++) {
                     TC_WAIT(&full_bar[st], ph, 1);
-                    if (kb == 0) TC_MARK(3, tcount);
-                    if (kb == p.KB - 1) TC_MARK(4, tcount);
-                    const bool fine = tl && tcount == 12 && kb < 8;  // fine-grained marks inside one tile
-                    if (fine) tl[7 * 64 + kb * 4 + 0] = (unsigned long long)(clock64() - dbg_t0);
+                    if (lane == 0) {
+                        if (kb == 0) TC_MARK(3, tcount);
+                        if (kb == p.KB - 1) TC_MARK(4, tcount);
+                    }
                     tc_fence_after();
-                    if (fine) tl[7 * 64 + kb * 4 + 1] = (unsigned long long)(clock64() - dbg_t0);
                     const uint32_t b_lo = b_lo0 + st * stage_lo;
                     const uint32_t a_blk = p.a_resident ? a_lo : b_lo + a_in_stage_lo;
+                    if (elect_one()) {
 #pragma unroll
-                    for (int kk = 0; kk < 4; kk++) {
-                        const uint64_t da = desc_hi | (uint64_t)(a_blk + 2 * kk);  // + 32 bytes per K = 16 step
-                        const uint64_t db = desc_hi | (uint64_t)(b_lo + 2 * kk);
-                        const uint32_t acc = (kb | kk) != 0 ? 1u : 0u;
-                        if constexpr (PAIR) umma_bf16_2sm(d_tmem, da, db, idesc, acc);
-                        else umma_bf16(d_tmem, da, db, idesc, acc);
+                        for (int kk = 0; kk < 4; kk++) {
+                            const uint64_t da = desc_hi | (uint64_t)(a_blk + 2 * kk);  // + 32 bytes per K = 16 step
+                            const uint64_t db = desc_hi | (uint64_t)(b_lo + 2 * kk);
+                            const uint32_t acc = (kb | kk) != 0 ? 1u : 0u;
+                            if constexpr (PAIR) umma_bf16_2sm(d_tmem, da, db, idesc, acc);
+                            else umma_bf16(d_tmem, da, db, idesc, acc);
+                        }
+                        if constexpr (PAIR) umma_commit_2sm(&empty_bar[st]);  // frees the stage in both CTAs
+                        else umma_commit(&empty_bar[st]);           // smem stage reusable once these MMAs retire
                     }
-                    if (fine) tl[7 * 64 + kb * 4 + 2] = (unsigned long long)(clock64() - dbg_t0);
-                    if constexpr (PAIR) umma_commit_2sm(&empty_bar[st]);  // frees the stage in both CTAs
-                    else umma_commit(&empty_bar[st]);           // smem stage reusable once these MMAs retire
-                    if (fine) tl[7 * 64 + kb * 4 + 3] = (unsigned long long)(clock64() - dbg_t0);
+                    __syncwarp();
                     a_lo += TC_A_BLOCK >> 4;
                     if (++st == (uint32_t)stages) {
                         st = 0;
                         ph ^= 1u;
                     }
                 }
-                if constexpr (PAIR) umma_commit_2sm(&tfull_bar[a]);  // accumulator complete, in both CTAs
-                else umma_commit(&tfull_bar[a]);
+                if (elect_one()) {
+                    if constexpr (PAIR) umma_commit_2sm(&tfull_bar[a]);  // accumulator complete, in both CTAs
+                    else umma_commit(&tfull_bar[a]);
+                }
+                __syncwarp();
             }
-            if (p.dbg) {
+            if (TC_DBG && lane == 0) {
                 p.dbg[blockIdx.x * 8 + 1] = dbg_acc[1];
                 p.dbg[blockIdx.x * 8 + 2] = dbg_acc[2];
             }
@@ -386,10 +392,10 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
             const uint32_t a = tcount & 1u, aph = (tcount >> 1) & 1u;
             refresh_thr();
             {
-                const long long _t0 = p.dbg ? clock64() : 0;
+                const long long _t0 = TC_DBG ? clock64() : 0;
                 mbar_wait(&tfull_bar[a], aph);  // accumulator complete
                 if (p.is_l2) mbar_wait(&nfull_bar[a], aph);  // and the tile's norms have landed
-                if (p.dbg) dbg_acc[0] += (unsigned long long)(clock64() - _t0);
+                if (TC_DBG) dbg_acc[0] += (unsigned long long)(clock64() - _t0);
                 if (et == 0) TC_MARK(5, tcount);
             }
             if ((t + 1) * TC_BN > p.n) {  // ragged last tile of the corpus: columns past the end never win
@@ -425,10 +431,10 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
                     // flush only when this group's survivors would not fit behind the pending ones, so
                     // one flush serves many groups
                     if (__any_sync(0xffffffffu, cnt + __popc(hm) > TC_BUFCAP)) {
-                        const long long _t0 = p.dbg ? clock64() : 0;
-                        dbg_acc[2] += (unsigned long long)cnt;
+                        const long long _t0 = TC_DBG ? clock64() : 0;
+                        if (DBG) dbg_acc[2] += (unsigned long long)cnt;
                         flush();
-                        if (p.dbg) {
+                        if (TC_DBG) {
                             dbg_acc[1] += (unsigned long long)(clock64() - _t0);
                             dbg_acc[3] += 1;
                         }
@@ -460,10 +466,10 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
             else if constexpr (PAIR) mbar_arrive_remote(&tempty_bar[a], 0);  // the MMA issuer lives in the leader CTA
             if (et == 0) TC_MARK(6, tcount);
         }
-        dbg_acc[2] += (unsigned long long)cnt;
+        if (DBG) dbg_acc[2] += (unsigned long long)cnt;
         flush();
         if (et == 0) *done_flag = 1;
-        if (p.dbg && et == 0) {
+        if (TC_DBG && et == 0) {
             p.dbg[blockIdx.x * 8 + 3] = dbg_acc[0];                         // epilogue: waiting for an accumulator
             p.dbg[blockIdx.x * 8 + 4] = dbg_acc[1];                         // epilogue: cycles inside flush()
             p.dbg[blockIdx.x * 8 + 5] = dbg_acc[2];                         // entries appended by thread 0
@@ -855,7 +861,7 @@ size_t tensor_workspace_bytes(const bfk_index* idx, int64_t nq, int k) {
 // in GPCs whose SM count is not a multiple of 4: 132 of 148 on B200)
 template <int KP>
 static int max_cluster_ctas(int csize, size_t smem) {
-    auto kern = scan_tc_kernel<KP, true>;
+    auto kern = scan_tc_kernel<KP, true, false>;
     cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_LIMIT);
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(148 * 4);
@@ -876,10 +882,10 @@ static int max_cluster_ctas(int csize, size_t smem) {
     return n * csize;
 }
 
-template <int KP, bool PAIR>
+template <int KP, bool PAIR, bool DBG>
 static int launch_scan_tc(const CUtensorMap& tmQ, const CUtensorMap& tmX, const TcParams& p, const TcPlan& pl,
                           cudaStream_t st) {
-    auto kern = scan_tc_kernel<KP, PAIR>;
+    auto kern = scan_tc_kernel<KP, PAIR, DBG>;
     static bool attr_set[64] = {false};  // the attribute is per device
     int dev = 0;
     BFK_CUDA(cudaGetDevice(&dev));
@@ -973,12 +979,18 @@ static int tc_pass(bfk_index* idx, const float* qc, int ldq, int64_t nqc, int k,
     p.parked = parked ? 1 : 0;
     if (dbg_on) BFK_CUDA(cudaMemsetAsync(w.dbg, 0, (size_t)pl.grid * 64 + 8 * 64 * 8, st));
     if (ev0) cudaEventRecord(ev0, st);
+    // the instrumented build of the kernel (wait-cycle counters, timeline marks, parked waits) is a
+    // separate instantiation: the single MMA-issuing thread paces the tensor pipe, and even predicated-off
+    // diagnostics in its loop cost issue slots
+    const bool dbgk = dbg_on || parked;
     if (pl.KP == 16) {
-        if (pl.csize == 2) BFK_TRY((launch_scan_tc<16, true>(tmQ, tmX, p, pl, st)));
-        else BFK_TRY((launch_scan_tc<16, false>(tmQ, tmX, p, pl, st)));
+        if (pl.csize == 2) BFK_TRY((launch_scan_tc<16, true, false>(tmQ, tmX, p, pl, st)));
+        else if (dbgk) BFK_TRY((launch_scan_tc<16, false, true>(tmQ, tmX, p, pl, st)));
+        else BFK_TRY((launch_scan_tc<16, false, false>(tmQ, tmX, p, pl, st)));
     } else {
-        if (pl.csize == 2) BFK_TRY((launch_scan_tc<32, true>(tmQ, tmX, p, pl, st)));
-        else BFK_TRY((launch_scan_tc<32, false>(tmQ, tmX, p, pl, st)));
+        if (pl.csize == 2) BFK_TRY((launch_scan_tc<32, true, false>(tmQ, tmX, p, pl, st)));
+        else if (dbgk) BFK_TRY((launch_scan_tc<32, false, true>(tmQ, tmX, p, pl, st)));
+        else BFK_TRY((launch_scan_tc<32, false, false>(tmQ, tmX, p, pl, st)));
     }
     if (ev1) cudaEventRecord(ev1, st);
     if (p.dbg) {  // diagnostics only: per-role wait cycles averaged over the CTAs
