@@ -420,17 +420,22 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
                     kk[4 * j4 + 2] = fmaf(scale, __uint_as_float(r[4 * j4 + 2]), b.z);
                     kk[4 * j4 + 3] = fmaf(scale, __uint_as_float(r[4 * j4 + 3]), b.w);
                 }
-                float kmin = kk[0];
+                // per-quad minima: the slow path below only touches quads that hold a survivor
+                float m4[4];
 #pragma unroll
-                for (int j = 1; j < 16; j++) kmin = fminf(kmin, kk[j]);
-                // after the first tiles most groups of 16 have no survivor in any lane
+                for (int j4 = 0; j4 < 4; j4++)
+                    m4[j4] = fminf(fminf(kk[4 * j4 + 0], kk[4 * j4 + 1]), fminf(kk[4 * j4 + 2], kk[4 * j4 + 3]));
+                const float kmin = fminf(fminf(m4[0], m4[1]), fminf(m4[2], m4[3]));
+                // after the first tiles most groups of 16 have no survivor in any lane.  The lanes of a warp
+                // are 32 different queries with 32 different thresholds, so once one lane has a survivor the
+                // whole warp walks the slow path: it is kept to the quads that are hit (one, typically)
                 if (__any_sync(0xffffffffu, kmin < thr)) {
-                    unsigned int hm = 0;
+                    unsigned int qm = 0;
 #pragma unroll
-                    for (int j = 0; j < 16; j++) hm |= (kk[j] < thr) ? (1u << j) : 0u;
-                    // flush only when this group's survivors would not fit behind the pending ones, so
-                    // one flush serves many groups
-                    if (__any_sync(0xffffffffu, cnt + __popc(hm) > TC_BUFCAP)) {
+                    for (int j4 = 0; j4 < 4; j4++) qm |= (m4[j4] < thr) ? (1u << j4) : 0u;
+                    // flush only when this group's survivors might not fit behind the pending ones, so one
+                    // flush serves many groups (thr can only fall inside: qm stays a superset)
+                    if (__any_sync(0xffffffffu, cnt + 4 * __popc(qm) > TC_BUFCAP)) {
                         const long long _t0 = TC_DBG ? clock64() : 0;
                         if (DBG) dbg_acc[2] += (unsigned long long)cnt;
                         flush();
@@ -440,11 +445,16 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
                         }
                     }
 #pragma unroll
-                    for (int j = 0; j < 16; j++) {
-                        if (hm & (1u << j)) {
-                            my_pend[(size_t)cnt * TC_EPI_THREADS] =
-                                ((uint64_t)__float_as_uint(kk[j]) << 32) | (uint64_t)(col0 + c0 + j);
-                            cnt++;
+                    for (int j4 = 0; j4 < 4; j4++) {
+                        if (__any_sync(0xffffffffu, (qm >> j4) & 1u)) {
+#pragma unroll
+                            for (int j = 0; j < 4; j++) {
+                                if (kk[4 * j4 + j] < thr) {
+                                    my_pend[(size_t)cnt * TC_EPI_THREADS] =
+                                        ((uint64_t)__float_as_uint(kk[4 * j4 + j]) << 32) | (uint64_t)(col0 + c0 + 4 * j4 + j);
+                                    cnt++;
+                                }
+                            }
                         }
                     }
                 }
@@ -768,7 +778,8 @@ static int tc_plan(const bfk_index* idx, int64_t nq, int k, TcPlan* pl) {
     const int TS = 2 * pl->S;  // thread-streams per query
     if (k > 24 && (int64_t)TS * pl->KP < 2 * (int64_t)k) return 1;  // lists too short to certify: exact path
     // NS >= k published slots bound the global k-th best key; G groups x J ranks
-    int NS = pl->KP;
+    // (the fewer slots, the tighter the bound: max over NS distinct rows bounds the NS-th best)
+    int NS = 16;
     while (NS < k + k / 4) NS <<= 1;
     int G = 1;
     while (G * 2 <= std::min(16, TS) && G * 2 <= NS) G *= 2;
@@ -984,11 +995,13 @@ static int tc_pass(bfk_index* idx, const float* qc, int ldq, int64_t nqc, int k,
     // diagnostics in its loop cost issue slots
     const bool dbgk = dbg_on || parked;
     if (pl.KP == 16) {
-        if (pl.csize == 2) BFK_TRY((launch_scan_tc<16, true, false>(tmQ, tmX, p, pl, st)));
+        if (pl.csize == 2 && dbgk) BFK_TRY((launch_scan_tc<16, true, true>(tmQ, tmX, p, pl, st)));
+        else if (pl.csize == 2) BFK_TRY((launch_scan_tc<16, true, false>(tmQ, tmX, p, pl, st)));
         else if (dbgk) BFK_TRY((launch_scan_tc<16, false, true>(tmQ, tmX, p, pl, st)));
         else BFK_TRY((launch_scan_tc<16, false, false>(tmQ, tmX, p, pl, st)));
     } else {
-        if (pl.csize == 2) BFK_TRY((launch_scan_tc<32, true, false>(tmQ, tmX, p, pl, st)));
+        if (pl.csize == 2 && dbgk) BFK_TRY((launch_scan_tc<32, true, true>(tmQ, tmX, p, pl, st)));
+        else if (pl.csize == 2) BFK_TRY((launch_scan_tc<32, true, false>(tmQ, tmX, p, pl, st)));
         else if (dbgk) BFK_TRY((launch_scan_tc<32, false, true>(tmQ, tmX, p, pl, st)));
         else BFK_TRY((launch_scan_tc<32, false, false>(tmQ, tmX, p, pl, st)));
     }
