@@ -744,18 +744,24 @@ struct TcPlan {
     size_t smem;
 };
 
-static int tc_plan(const bfk_index* idx, int64_t nq, int k, TcPlan* pl) {
+// pair_mode: -1 = default policy, 0 = single CTAs, 1 = CTA pairs when the number of query tiles is even
+static int tc_plan(const bfk_index* idx, int64_t nq, int k, TcPlan* pl, int pair_mode = -1) {
     pl->KB = idx->ld16 / 64;
     // measured: moving the lists to global memory to win a 4th stage made flushes ~10x slower and the extra
     // stage bought nothing (the multi-tile regime is bound by L2 -> SM bandwidth, not by ring depth)
     pl->pend_global = 0;
     pl->QT = (int)((nq + TC_BM - 1) / TC_BM);
-    // Optional CTA pairs (BFK_TC_PAIR=1, needs an even number of query tiles): tcgen05.mma.cta_group::2 with
-    // M = 256 -- the pair shares one corpus stream and each CTA stages half of every corpus tile, halving the
-    // L2 -> SM bytes per MMA.  Parity-tested, but measured no faster than single CTAs on B200 (nq=1024:
-    // 0.798 vs 0.792 ms; nq=4096: 3.91 vs 3.46 ms), so it is off by default.
-    pl->csize = 1;
-    if (const char* e = getenv("BFK_TC_PAIR")) pl->csize = (atoi(e) != 0 && pl->QT % 2 == 0) ? 2 : 1;
+    // CTA pairs (needs an even number of query tiles): tcgen05.mma.cta_group::2 with M = 256 -- the pair
+    // shares one corpus stream and each CTA stages half of every corpus tile, which halves the L2 -> SM bytes
+    // per MMA (single CTAs run at ~87 % of the chip's L2 throughput cap at nq = 4096) and doubles the ring
+    // depth in time.  Measured once the MMA issue loop stopped being the bottleneck: nq=1024 0.80 vs 0.77,
+    // nq=2048 0.84 vs 0.81, nq=4096 0.76 vs 0.72 of the burst bf16 peak.  BFK_TC_PAIR=0 turns it off.
+    static const int pair_env = [] {
+        const char* e = getenv("BFK_TC_PAIR");
+        return e ? (atoi(e) != 0 ? 1 : 0) : -1;
+    }();
+    if (pair_mode < 0) pair_mode = pair_env < 0 ? 1 : pair_env;
+    pl->csize = (pair_mode == 1 && pl->QT % 2 == 0) ? 2 : 1;
     const size_t b_block = pl->csize == 2 ? TC_B_BLOCK / 2 : TC_B_BLOCK;
     // the 128-query tile stays resident in shared memory when it leaves room for >= 3 corpus stages;
     // otherwise (d > 384) its K-blocks stream through the ring next to the corpus K-blocks
@@ -948,10 +954,27 @@ static int tc_pass(bfk_index* idx, const float* qc, int ldq, int64_t nqc, int k,
                    int* launches) {
     const bool l2 = idx->metric == BFK_METRIC_L2;
     TcPlan pl = plan;
-    // every CTA of the persistent grid must be resident at once for the cluster size chosen
+    // every CTA of the persistent grid must be resident at once for the cluster size chosen; when the pairs do
+    // not all fit (MIG slices, SMs held by another context) the same search runs with single CTAs
     if (pl.csize == 2) {
-        const int fit = pl.KP == 16 ? max_cluster_ctas<16>(2, pl.smem) : max_cluster_ctas<32>(2, pl.smem);
-        if (fit < pl.grid) return fail("tensor path: CTA pairs do not all fit on the GPU");
+        struct Fit { int dev, kp; size_t smem; int fit; };
+        static std::mutex fit_mu;
+        static std::vector<Fit> fits;
+        int fit = -1;
+        {
+            std::lock_guard<std::mutex> g(fit_mu);
+            for (const Fit& f : fits)
+                if (f.dev == idx->device && f.kp == pl.KP && f.smem == pl.smem) fit = f.fit;
+            if (fit < 0) {
+                fit = pl.KP == 16 ? max_cluster_ctas<16>(2, pl.smem) : max_cluster_ctas<32>(2, pl.smem);
+                fits.push_back({idx->device, pl.KP, pl.smem, fit});
+            }
+        }
+        if (fit < pl.grid) {
+            TcPlan single;
+            if (tc_plan(idx, nqc, k, &single, 0)) return fail("tensor path: shape not supported");
+            pl = single;
+        }
     }
     BFK_CUDA(cudaMemsetAsync(w.flags, 0, sizeof(int), st));
     // |<q,x> - <bf16(q),bf16(x)>| <= (2u + u^2) ||q|| ||x|| with u = 2^-9 when both operands are
