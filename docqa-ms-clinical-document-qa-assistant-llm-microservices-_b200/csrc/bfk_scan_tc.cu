@@ -796,12 +796,38 @@ static int tc_plan(const bfk_index* idx, int64_t nq, int k, TcPlan* pl, int pair
     return 0;
 }
 
-static int64_t tc_chunk_queries(const bfk_index* idx) { return (int64_t)idx->num_sms * TC_BM; }
+// Queries per pass.  A pass runs QT query tiles x S = floor(SMs / QT) corpus streams, so it leaves SMs idle
+// when SMs / QT is far from integral (QT = 32: 128 of 148).  Splitting the batch into passes of c tiles costs
+// one more corpus read from HBM per pass (cheap next to the contraction once c >= 2) and a fixed launch /
+// fill / drain overhead, and pays back when c * floor(SMs / c) covers the chip better: nq = 4096 runs as
+// 2 x 2048 (144 SMs).  Cost model in units of one CTA's tile time: a pass walks ceil(T / S) tiles per CTA, is
+// never faster than the HBM read of the corpus (~ T / 75 at d = 384), plus ~16 tiles of overhead.
+static int64_t tc_chunk_queries(const bfk_index* idx, int64_t nq) {
+    const int sms = idx->num_sms;
+    const int64_t QT = (nq + TC_BM - 1) / TC_BM;
+    const int64_t T = (idx->ntotal + TC_BN - 1) / TC_BN;
+    auto pass_cost = [&](int64_t c) {
+        const int64_t S = std::max<int64_t>(1, std::min<int64_t>(sms / c, T));
+        return (double)std::max<int64_t>((T + S - 1) / S, T / 75) + 16.0;
+    };
+    int64_t best_c = std::min<int64_t>(QT, sms);
+    double best = -1.0;
+    for (int64_t c = std::min<int64_t>(QT, sms); c >= 1; c--) {
+        const int64_t full = QT / c, rest = QT - full * c;
+        // even tile counts run as CTA pairs (measured ~4 % faster)
+        const double cost = (double)full * pass_cost(c) * ((c & 1) ? 1.04 : 1.0) + (rest ? pass_cost(rest) : 0.0);
+        if (best < 0 || cost < best * 0.97) {  // a smaller chunk has to win clearly
+            best = cost;
+            best_c = c;
+        }
+    }
+    return best_c * TC_BM;
+}
 
 int tensor_path_supported(const bfk_index* idx, int64_t nq, int k) {
     if (k > 128 || nq <= 0 || idx->ntotal <= 0) return 0;
     TcPlan pl;
-    if (tc_plan(idx, std::min<int64_t>(nq, tc_chunk_queries(idx)), k, &pl)) return 0;
+    if (tc_plan(idx, std::min<int64_t>(nq, tc_chunk_queries(idx, nq)), k, &pl)) return 0;
     return get_encode_fn() != nullptr;
 }
 
@@ -863,15 +889,21 @@ static void tc_carve(const bfk_index* idx, int64_t nqc, int k, int fb_nparts, ch
 }
 
 size_t tensor_workspace_bytes(const bfk_index* idx, int64_t nq, int k) {
-    const int64_t nqc = std::min<int64_t>(nq, tc_chunk_queries(idx));
-    TcPlan pl;
-    if (tc_plan(idx, nqc, k, &pl)) return 0;
-    size_t sb = 0;
+    const int64_t chunk = std::min<int64_t>(nq, tc_chunk_queries(idx, nq));
+    size_t sb = 0, bytes = 0;
     int nparts = 0;
     if (scan_exact_workspace(idx, 8, k, &sb, &nparts)) return 0;
-    TcWs w;
-    tc_carve(idx, nqc, k, nparts, nullptr, &w);
-    return w.bytes;
+    // the full passes and the shorter last one are planned separately: size for the larger of the two
+    const int64_t sizes[2] = {chunk, nq % chunk};
+    for (int64_t nqc : sizes) {
+        if (nqc <= 0) continue;
+        TcPlan pl;
+        if (tc_plan(idx, nqc, k, &pl)) return 0;
+        TcWs w;
+        tc_carve(idx, nqc, k, nparts, nullptr, &w);
+        bytes = std::max(bytes, w.bytes);
+    }
+    return bytes;
 }
 
 // co-resident clusters of `csize` CTAs for this kernel and shared-memory size (cluster size 4 strands SMs
@@ -1206,7 +1238,7 @@ void search_tensor_forget(bfk_index* idx) {
 int search_tensor(bfk_index* idx, const float* q_dev, int ldq, int64_t nq, int k, float* D_dev, int64_t* I_dev,
                   int64_t id_offset, char* ws_tail, size_t ws_tail_bytes, cudaStream_t st, bfk_search_stats* stats,
                   cudaEvent_t ev0, cudaEvent_t ev1, int defer) {
-    const int64_t chunk = tc_chunk_queries(idx);
+    const int64_t chunk = tc_chunk_queries(idx, nq);
     int launches = 0;
     int64_t n_fallback = 0, n_retry = 0;
     int fb_nparts = 0;
