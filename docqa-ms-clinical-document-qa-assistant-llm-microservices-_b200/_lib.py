@@ -42,6 +42,7 @@ EXPORTS = [
     "bfk_xchg_free",
     "bfk_reconstruct", "bfk_remove_ids", "bfk_write", "bfk_read", "bfk_serialized_size",
     "bfk_serialize", "bfk_deserialize", "bfk_normalize_l2", "bfk_merge_topk", "bfk_merge_topk_strided", "bfk_search_noalloc",
+    "bfk_search_sel", "bfk_range_search", "bfk_range_result_size", "bfk_range_result_copy", "bfk_range_result_free",
 ]
 
 _lib = None
@@ -99,6 +100,12 @@ def load() -> ctypes.CDLL:
     L.bfk_merge_topk.argtypes = [vp, vp, i32, i64, i64, i32, vp, vp, i32, vp]
     L.bfk_merge_topk_strided.argtypes = [vp, i64, vp, i64, i32, i64, i64, i32, vp, vp, i32, vp]
     L.bfk_search_noalloc.argtypes = [vp, vp, i64, i64, vp, vp, vp]
+    L.bfk_search_sel.argtypes = [vp, vp, i64, i64, vp, vp, i32, vp, i32, i64, vp, i32, ctypes.POINTER(SearchStats)]
+    L.bfk_range_search.argtypes = [vp, vp, i64, ctypes.c_float, i32, vp, vp, ctypes.POINTER(vp)]
+    L.bfk_range_result_size.argtypes = [vp]
+    L.bfk_range_result_size.restype = i64
+    L.bfk_range_result_copy.argtypes = [vp, vp, vp, i32]
+    L.bfk_range_result_free.argtypes = [vp]
     _lib = L
     return L
 

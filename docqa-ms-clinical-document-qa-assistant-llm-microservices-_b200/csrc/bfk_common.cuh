@@ -83,6 +83,13 @@ struct bfk_index {
     bfk::Workspace ws;       // search scratch, grow-only
     cudaEvent_t ws_free = nullptr;  // recorded after the last search that used `ws`
     int* h_flag = nullptr;          // pinned host word: count of uncertified queries (tensor path)
+    // id selector of the search in progress (bfk_search_sel; null otherwise), set and cleared under `mu`:
+    //   sel       bit i set <=> row i may be returned (faiss IDSelectorBitmap layout)
+    //   sel_bias  [tiles*256] fp32: the tensor scan's per-row bias with +inf for rows that are not selected
+    const unsigned char* sel = nullptr;
+    const float* sel_bias = nullptr;
+    void* sel_buf = nullptr;        // grow-only device buffer behind sel / sel_bias
+    size_t sel_buf_bytes = 0;
     std::mutex mu;
 };
 
@@ -109,6 +116,9 @@ int launch_select(const uint64_t* cand, int64_t m_per_query, int64_t nq, int k, 
 // K6 front end: pack (D, I) lists into composite keys
 int launch_pack_parts(const float* Dparts, const int64_t* Iparts, int nparts, int64_t nq, int k,
                       int metric, uint64_t* cand, cudaStream_t st);
+// selector support: bias[i] = selected(i) ? (l2 ? nrm[i] : 0) : +inf for i < n_pad (rows >= n: +inf)
+int launch_sel_bias(const unsigned char* sel, const float* nrm, int64_t n, int64_t n_pad, int is_l2, float* bias,
+                    cudaStream_t st);
 // K3b + K5 (tensor path); defined in bfk_scan_tc.cu
 int tensor_path_supported(const bfk_index* idx, int64_t nq, int k);
 size_t tensor_workspace_bytes(const bfk_index* idx, int64_t nq, int k);

@@ -295,6 +295,7 @@ int bfk_free(bfk_index* idx) {
     if (idx->maxn) cudaFree(idx->maxn);
     if (idx->ws_free) cudaEventDestroy(idx->ws_free);
     if (idx->h_flag) cudaFreeHost(idx->h_flag);
+    if (idx->sel_buf) cudaFree(idx->sel_buf);
     delete idx;
     return 0;
 }
@@ -392,20 +393,73 @@ int bfk_search(bfk_index* idx, const float* q, int64_t nq, int64_t k, float* D, 
     return bfk_search_ex(idx, q, nq, k, D, I, io_is_device, stream, BFK_ALGO_AUTO, 0, nullptr);
 }
 
-int bfk_search_ex(bfk_index* idx, const float* q, int64_t nq, int64_t k64, float* D, int64_t* I,
-                  int io_is_device, void* stream, int algo, int64_t id_offset, bfk_search_stats* stats) {
+static int search_args_ok(bfk_index* idx, const float* q, int64_t nq, int64_t k64, float* D, int64_t* I,
+                          bfk_search_stats* stats, bool* empty) {
+    *empty = false;
     if (!idx) return fail("null index");
     if (nq < 0) return fail("search: negative query count");
     if (k64 <= 0) return fail("search: k must be positive");
     if (k64 > BFK_MAX_K) return fail("search: k > " + std::to_string(BFK_MAX_K) + " is not supported");
     if (stats) memset(stats, 0, sizeof(*stats));
-    if (nq == 0) return 0;
+    if (nq == 0) {
+        *empty = true;
+        return 0;
+    }
     if (!q || !D || !I) return fail("search: null buffer");
-    const int k = (int)k64;
+    return 0;
+}
+
+// the search proper; idx->mu is held and the device is current.  sel_dev: optional selector bitmap on the device
+static int search_locked(bfk_index* idx, const float* q, int64_t nq, int k, float* D, int64_t* I, int io_is_device,
+                         cudaStream_t st, int algo, int64_t id_offset, bfk_search_stats* stats,
+                         const unsigned char* sel_dev);
+
+int bfk_search_ex(bfk_index* idx, const float* q, int64_t nq, int64_t k64, float* D, int64_t* I,
+                  int io_is_device, void* stream, int algo, int64_t id_offset, bfk_search_stats* stats) {
+    bool empty;
+    BFK_TRY(search_args_ok(idx, q, nq, k64, D, I, stats, &empty));
+    if (empty) return 0;
+    DeviceGuard g(idx->device);
+    std::lock_guard<std::mutex> lk(idx->mu);
+    return search_locked(idx, q, nq, (int)k64, D, I, io_is_device, (cudaStream_t)stream, algo, id_offset, stats, nullptr);
+}
+
+int bfk_search_sel(bfk_index* idx, const float* q, int64_t nq, int64_t k64, float* D, int64_t* I, int io_is_device,
+                   void* stream, int algo, int64_t id_offset, const uint8_t* bitmap, int bitmap_is_device,
+                   bfk_search_stats* stats) {
+    bool empty;
+    BFK_TRY(search_args_ok(idx, q, nq, k64, D, I, stats, &empty));
+    if (empty) return 0;
+    if (!bitmap) return fail("search_sel: null selector bitmap");
     DeviceGuard g(idx->device);
     cudaStream_t st = (cudaStream_t)stream;
     std::lock_guard<std::mutex> lk(idx->mu);
-    const int defer = (algo & BFK_ALGO_FLAG_DEFER) && io_is_device && !stats;
+    BFK_TRY(search_tensor_finish(idx, st, nullptr));
+    // selector staging: [bitmap, ceil(n/8) bytes rounded to 256][bias, tiles*256 floats]
+    const size_t bm_bytes = (size_t)((idx->ntotal + 7) / 8);
+    const size_t bm_pad = (size_t)round_up((int64_t)bm_bytes + 1, 256);
+    const int64_t n_pad = round_up(std::max<int64_t>(idx->ntotal, 1), 256);
+    const size_t need = bm_pad + sizeof(float) * (size_t)n_pad;
+    if (idx->sel_buf_bytes < need) {
+        BFK_CUDA(cudaStreamSynchronize(st));
+        if (idx->sel_buf) cudaFree(idx->sel_buf);
+        idx->sel_buf = nullptr;
+        idx->sel_buf_bytes = 0;
+        BFK_CUDA(cudaMalloc(&idx->sel_buf, need));
+        idx->sel_buf_bytes = need;
+    }
+    unsigned char* bm_dev = (unsigned char*)idx->sel_buf;
+    BFK_CUDA(cudaMemcpyAsync(bm_dev, bitmap, bm_bytes, bitmap_is_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, st));
+    int rc = search_locked(idx, q, nq, (int)k64, D, I, io_is_device, st, algo & ~BFK_ALGO_FLAG_DEFER, id_offset, stats, bm_dev);
+    idx->sel = nullptr;
+    idx->sel_bias = nullptr;
+    return rc;
+}
+
+static int search_locked(bfk_index* idx, const float* q, int64_t nq, int k, float* D, int64_t* I, int io_is_device,
+                         cudaStream_t st, int algo, int64_t id_offset, bfk_search_stats* stats,
+                         const unsigned char* sel_dev) {
+    const int defer = (algo & BFK_ALGO_FLAG_DEFER) && io_is_device && !stats && !sel_dev;
     algo &= ~BFK_ALGO_FLAG_DEFER;
     BFK_TRY(search_tensor_finish(idx, st, nullptr));  // a deferred search nobody settled: settle it first
 
@@ -451,6 +505,17 @@ int bfk_search_ex(bfk_index* idx, const float* q, int64_t nq, int64_t k64, float
                                (size_t)nq, io_is_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, st));
     float* D_out = io_is_device ? D : D_dev;
     int64_t* I_out = io_is_device ? I : I_dev;
+
+    if (sel_dev) {
+        idx->sel = sel_dev;
+        if (algo == BFK_ALGO_TENSOR) {
+            const size_t bm_pad = (size_t)round_up((idx->ntotal + 7) / 8 + 1, 256);
+            float* bias = reinterpret_cast<float*>((char*)idx->sel_buf + bm_pad);
+            const int64_t n_pad = round_up(std::max<int64_t>(idx->ntotal, 1), 256);
+            BFK_TRY(launch_sel_bias(sel_dev, idx->nrm, idx->ntotal, n_pad, idx->metric == BFK_METRIC_L2 ? 1 : 0, bias, st));
+            idx->sel_bias = bias;
+        }
+    }
 
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     if (stats) {

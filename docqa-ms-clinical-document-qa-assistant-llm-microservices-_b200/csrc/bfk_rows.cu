@@ -103,6 +103,28 @@ __global__ void __launch_bounds__(256) renorm_rows_kernel(float* __restrict__ x,
     }
 }
 
+// ---- id selector -> per-row bias of the tensor scan ------------------------------------------
+// bias[i] = +inf for rows the selector rejects (their key can then never pass a threshold), else the
+// metric's own bias (||x||^2 for L2, 0 for inner product).  One pass over n floats; the scan itself
+// runs unchanged.
+__global__ void __launch_bounds__(256) sel_bias_kernel(const unsigned char* __restrict__ sel, const float* __restrict__ nrm,
+                                                       int64_t n, int64_t n_pad, int is_l2, float* __restrict__ bias) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_pad; i += (int64_t)gridDim.x * blockDim.x) {
+        float b = INFINITY;
+        if (i < n && ((sel[i >> 3] >> (i & 7)) & 1u)) b = is_l2 ? nrm[i] : 0.f;
+        bias[i] = b;
+    }
+}
+
+int launch_sel_bias(const unsigned char* sel, const float* nrm, int64_t n, int64_t n_pad, int is_l2, float* bias,
+                    cudaStream_t st) {
+    if (n_pad <= 0) return 0;
+    const int64_t blocks = std::min<int64_t>((n_pad + 255) / 256, 148 * 16);
+    sel_bias_kernel<<<(unsigned)blocks, 256, 0, st>>>(sel, nrm, n, n_pad, is_l2, bias);
+    BFK_CUDA(cudaGetLastError());
+    return 0;
+}
+
 }  // namespace bfk
 
 extern "C" int bfk_normalize_l2(float* x, int64_t n, int d, int x_is_device, int device, void* stream) {

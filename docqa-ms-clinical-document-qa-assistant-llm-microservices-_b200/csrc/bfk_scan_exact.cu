@@ -93,6 +93,7 @@ struct ScanExactParams {
     int stages;
     uint64_t* part;      // [nq_real][nparts][k]
     int nparts;
+    const unsigned char* sel;  // optional id selector bitmap (bit i <=> row i admitted), else null
 };
 
 template <int NQ, int R, bool IS_L2, typename RowT>
@@ -229,7 +230,9 @@ __global__ void __launch_bounds__(SE_THREADS, 1) scan_exact_kernel(const ScanExa
             const float key = IS_L2 ? acc[0] : -acc[0];
             if (key < FLT_MAX) {  // also rejects NaN, as faiss's strict compare does
                 const uint64_t comp = make_comp(key, (uint32_t)row);
-                if (comp < *reinterpret_cast<volatile uint64_t*>(&thr_s[qj])) {
+                // the selector is only consulted for rows that would enter the list
+                if (comp < *reinterpret_cast<volatile uint64_t*>(&thr_s[qj]) &&
+                    (p.sel == nullptr || ((p.sel[row >> 3] >> (row & 7)) & 1u))) {
                     int slot = atomicAdd(&cnt_s[qj], 1);
                     if (slot < p.cap) cand[(size_t)qj * p.cap + slot] = comp;
                 }
@@ -391,6 +394,7 @@ int launch_scan_exact(const bfk_index* idx, const float* q_dev, int ldq, int nq,
         p.stages = sub.stages;
         p.part = part + (size_t)q0 * nparts * k;
         p.nparts = nparts;
+        p.sel = idx->sel;
         const bool l2 = idx->metric == BFK_METRIC_L2;
         int rc;
         if (f32)

@@ -81,6 +81,7 @@ struct TcParams {
     unsigned long long* dbg;  // optional [grid][8] cycle counters (BFK_TC_DEBUG=1), else nullptr
     int parked;          // producer/MMA waits use the suspend-time hint
     int a_resident;      // query tile resident in smem (else its K-blocks stream with the corpus)
+    int use_bias;        // per-row bias is fetched (L2 norms, or the selector bias for either metric)
     int csize;           // 1: every CTA on its own; 2: CTA pairs (cta_group::2) -- two query tiles share one
                          // corpus stream, each CTA stages only half of every corpus tile
     uint64_t* pend_g;    // global pending lists [grid][TC_BUFCAP][256], or nullptr: lists live in shared memory.
@@ -290,7 +291,7 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
         // ===================== norms fetcher =====================
         // bias slot a is free once THIS CTA's epilogue has released accumulator a: fetch the tile's 256
         // squared norms then; they land long before the epilogue reaches the tile
-        if (lane == 0 && p.is_l2) {
+        if (lane == 0 && p.use_bias) {
             uint32_t tcount = 0;
             for (int64_t t = t_begin; t < t_end; t++, tcount++) {
                 const uint32_t a = tcount & 1u, aph = (tcount >> 1) & 1u;
@@ -394,7 +395,7 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
             {
                 const long long _t0 = TC_DBG ? clock64() : 0;
                 mbar_wait(&tfull_bar[a], aph);  // accumulator complete
-                if (p.is_l2) mbar_wait(&nfull_bar[a], aph);  // and the tile's norms have landed
+                if (p.use_bias) mbar_wait(&nfull_bar[a], aph);  // and the tile's norms / selector bias have landed
                 if (TC_DBG) dbg_acc[0] += (unsigned long long)(clock64() - _t0);
                 if (et == 0) TC_MARK(5, tcount);
             }
@@ -1020,7 +1021,8 @@ static int tc_pass(bfk_index* idx, const float* qc, int ldq, int64_t nqc, int k,
     BFK_TRY(make_tmap(&tmQ, w.q16, pl.nq_pad, idx->ld16, TC_BM));
     BFK_TRY(make_tmap(&tmX, idx->x16, idx->ntotal, idx->ld16, TC_BN / pl.csize));  // box = this CTA's slice
     TcParams p;
-    p.nrm = idx->nrm;
+    p.nrm = idx->sel_bias ? idx->sel_bias : idx->nrm;  // a selector search masks rows through the bias
+    p.use_bias = (l2 || idx->sel_bias) ? 1 : 0;
     p.n = idx->ntotal;
     p.KB = pl.KB;
     p.QT = pl.QT;

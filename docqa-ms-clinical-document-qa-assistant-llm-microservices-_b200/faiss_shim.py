@@ -9,7 +9,7 @@ from __future__ import annotations
 import sys
 import types
 
-from . import flat
+from . import flat, idselect
 
 
 def make_module() -> types.ModuleType:
@@ -18,6 +18,9 @@ def make_module() -> types.ModuleType:
     for name in ("IndexFlat", "IndexFlatL2", "IndexFlatIP", "write_index", "read_index", "serialize_index",
                  "deserialize_index", "normalize_L2", "METRIC_L2", "METRIC_INNER_PRODUCT", "get_num_gpus"):
         setattr(m, name, getattr(flat, name))
+    for name in ("SearchParameters", "IDSelector", "IDSelectorAll", "IDSelectorRange", "IDSelectorArray",
+                 "IDSelectorBatch", "IDSelectorBitmap", "IDSelectorNot", "IDSelectorAnd", "IDSelectorOr"):
+        setattr(m, name, getattr(idselect, name))
     m.Index = flat.IndexFlat
     m.__version__ = "bfk-1.0"
     return m

@@ -167,6 +167,9 @@ class IndexFlat:
         k = int(k)
         st = stats if isinstance(stats, SearchStats) else None
         stp = ctypes.byref(st) if st is not None else None
+        sel = getattr(params, "sel", None) if params is not None else None
+        if sel is not None:
+            return self._search_sel(x, k, sel, D, I, algo, id_offset, stp)
         if _is_torch(x):
             import torch
 
@@ -199,6 +202,74 @@ class IndexFlat:
         _lib.check(self._L.bfk_search_ex(self._h, _np_ptr(x), n, k, _np_ptr(D), _np_ptr(I), 0, None,
                                           _ALGO[algo], int(id_offset), stp))
         return D, I
+
+    def _search_sel(self, x, k, sel, D, I, algo, id_offset, stp):
+        """search restricted to the rows `sel` admits (faiss SearchParameters(sel=...)): bfk_search_sel."""
+        n = x.shape[0]
+        bm = np.ascontiguousarray(sel.to_bitmap(self.ntotal), dtype=np.uint8)
+        if bm.size == 0:
+            bm = np.zeros(1, dtype=np.uint8)
+        if _is_torch(x):
+            import torch
+
+            assert x.is_cuda and x.device.index == self.device, "torch input must live on the index's GPU"
+            xq = x.to(torch.float32).contiguous()
+            D = torch.empty((n, k), dtype=torch.float32, device=x.device) if D is None else D
+            I = torch.empty((n, k), dtype=torch.int64, device=x.device) if I is None else I
+            assert tuple(D.shape) == (n, k) and tuple(I.shape) == (n, k)
+            _lib.check(self._L.bfk_search_sel(self._h, ctypes.c_void_p(xq.data_ptr()), n, k,
+                                               ctypes.c_void_p(D.data_ptr()), ctypes.c_void_p(I.data_ptr()), 1,
+                                               _torch_stream(self.device), _ALGO[algo], int(id_offset), _np_ptr(bm), 0, stp))
+            torch.cuda.current_stream(self.device).synchronize()  # `bm` is host memory borrowed for the call
+            return D, I
+        x = np.ascontiguousarray(x, dtype="float32")
+        D = np.empty((n, k), dtype=np.float32) if D is None else D
+        I = np.empty((n, k), dtype=np.int64) if I is None else I
+        assert D.shape == (n, k) and I.shape == (n, k)
+        _lib.check(self._L.bfk_search_sel(self._h, _np_ptr(x), n, k, _np_ptr(D), _np_ptr(I), 0, None, _ALGO[algo],
+                                           int(id_offset), _np_ptr(bm), 0, stp))
+        return D, I
+
+    def range_search(self, x, thresh, *, params=None):
+        """faiss index.range_search(x, radius) -> (lims, D, I): all rows with squared L2 distance < radius
+        (inner product > radius), grouped per query by lims[i]:lims[i+1]; rows of a query come in id order."""
+        n, d = x.shape
+        assert d == self.d
+        if _is_torch(x):
+            x = x.detach().to("cpu").numpy()
+        x = np.ascontiguousarray(x, dtype="float32")
+        lims = np.zeros(n + 1, dtype=np.int64)
+        res = ctypes.c_void_p()
+        _lib.check(self._L.bfk_range_search(self._h, _np_ptr(x), n, float(thresh), 0, None, _np_ptr(lims),
+                                             ctypes.byref(res)))
+        try:
+            total = int(self._L.bfk_range_result_size(res))
+            D = np.empty(total, dtype=np.float32)
+            I = np.empty(total, dtype=np.int64)
+            if total:
+                _lib.check(self._L.bfk_range_result_copy(res, _np_ptr(D), _np_ptr(I), 0))
+        finally:
+            self._L.bfk_range_result_free(res)
+        sel = getattr(params, "sel", None) if params is not None else None
+        keep = None
+        if sel is not None and total:
+            bm = sel.to_bitmap(self.ntotal)
+            keep = ((bm[I >> 3] >> (I & 7).astype(np.uint8)) & 1).astype(bool)
+        # the kernel appends in scheduling order: make each query's rows deterministic (by id)
+        out_l = np.zeros(n + 1, dtype=np.int64)
+        Ds, Is = [], []
+        for i in range(n):
+            a, b = int(lims[i]), int(lims[i + 1])
+            Di, Ii = D[a:b], I[a:b]
+            if keep is not None:
+                Di, Ii = Di[keep[a:b]], Ii[keep[a:b]]
+            o = np.argsort(Ii, kind="stable")
+            Ds.append(Di[o])
+            Is.append(Ii[o])
+            out_l[i + 1] = out_l[i] + Ii.size
+        D = np.concatenate(Ds) if Ds else D
+        I = np.concatenate(Is) if Is else I
+        return out_l, D, I
 
     def finish(self) -> int:
         """Settle a `search(..., defer=True)`: wait, re-run uncertified queries, return rows rewritten.

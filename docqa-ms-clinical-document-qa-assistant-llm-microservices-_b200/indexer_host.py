@@ -57,7 +57,7 @@ class SemanticIndexer:
 
     def __init__(self, model, dimension: int = 384, *, index_file: str = INDEX_FILE,
                  metadata_file: str = METADATA_FILE, default_data_dir: str = DEFAULT_DATA_DIR,
-                 index_factory=None, write_index=None, read_index=None):
+                 index_factory=None, write_index=None, read_index=None, keep_doc_ids: bool = False):
         self.model = model                      # .encode(list[str]) -> [n, d]; optional .encode_tokens
         self.dimension = int(dimension)
         self.index_file = index_file
@@ -67,6 +67,10 @@ class SemanticIndexer:
         self._write_index, self._read_index = write_index, read_index  # None -> this package's, resolved lazily
         self.index = None
         self.metadata_store: list[dict] = []
+        # False: every row carries doc_id "KB_MTC" like the reference (indexer.py:44).  True: patient messages
+        # keep their own doc_id plus patient_id / date when the message has them -- what the patient-snippets
+        # endpoint (search_service.py; synthese-comparative/core/retrieval_client.py:58-91) filters on.
+        self.keep_doc_ids = bool(keep_doc_ids)
 
     # ---- indexer.py:26-30 ------------------------------------------------------------
     def save_state(self) -> None:
@@ -94,7 +98,7 @@ class SemanticIndexer:
             return
         self.add_many([text], source_name, doc_type)
 
-    def add_many(self, texts, source_name, doc_type="knowledge_base") -> int:
+    def add_many(self, texts, source_name, doc_type="knowledge_base", *, doc_id="KB_MTC", extra=None) -> int:
         """All non-blank texts in one encode call and one add; returns how many were added."""
         texts = [t for t in texts if t.strip()]
         if not texts:
@@ -109,10 +113,11 @@ class SemanticIndexer:
             self.index.add(np.array(embeddings).astype("float32").reshape(len(texts), -1))
         for text in texts:
             self.metadata_store.append({
-                "doc_id": "KB_MTC",
+                "doc_id": doc_id,
                 "text_content": text,
                 "source": source_name,
                 "type": doc_type,
+                **(extra or {}),
             })
         return len(texts)
 
@@ -179,7 +184,11 @@ class SemanticIndexer:
             doc_id = message.get("doc_id")
             text = message.get("original_text_masked")
             chunks = [text[i:i + CHUNK_CHARS] for i in range(0, len(text), CHUNK_CHARS)]
-            self.add_many(chunks, f"Dossier Patient {doc_id}", "patient_file")
+            if self.keep_doc_ids:
+                extra = {key: message[key] for key in ("patient_id", "date") if message.get(key) is not None}
+                self.add_many(chunks, f"Dossier Patient {doc_id}", "patient_file", doc_id=doc_id, extra=extra)
+            else:
+                self.add_many(chunks, f"Dossier Patient {doc_id}", "patient_file")
             self.save_state()
             return True
         except Exception as e:

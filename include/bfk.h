@@ -115,6 +115,25 @@ int bfk_search_ex(bfk_index* idx, const float* q, int64_t nq, int64_t k, float* 
                   int io_is_device, void* stream, int algo, int64_t id_offset,
                   bfk_search_stats* stats);
 
+/* index.search(x, k, params=faiss.SearchParameters(sel=IDSelector...)): the same search restricted to the
+ * rows whose bit is set in `bitmap` (faiss IDSelectorBitmap layout: bit i & 7 of byte i >> 3 <=> row i;
+ * at least ceil(ntotal / 8) bytes; host or device memory).  Not used by the reference today; it is what the
+ * patient-snippets endpoint synthese-comparative/core/retrieval_client.py:58-91 expects from the indexer
+ * needs (rows of one patient / date window).  Fewer than k admitted rows -> the usual -1 padding.
+ * BFK_ALGO_FLAG_DEFER is ignored. */
+int bfk_search_sel(bfk_index* idx, const float* q, int64_t nq, int64_t k, float* D, int64_t* I,
+                   int io_is_device, void* stream, int algo, int64_t id_offset, const uint8_t* bitmap,
+                   int bitmap_is_device, bfk_search_stats* stats);
+
+/* index.range_search(x, radius) -> (lims, D, I) -- LangChain-side extra, exact fp32
+ * arithmetic: squared L2 < radius, or inner product > radius.  lims is HOST int64[nq + 1]; the (D, I) pairs
+ * stay on the device behind *result until copied out (query i owns lims[i]..lims[i+1], unordered inside). */
+int bfk_range_search(bfk_index* idx, const float* q, int64_t nq, float radius, int q_is_device, void* stream,
+                     int64_t* lims, void** result);
+int64_t bfk_range_result_size(void* result);
+int bfk_range_result_copy(void* result, float* D, int64_t* I, int out_is_device);
+int bfk_range_result_free(void* result);
+
 /* settles a search started with BFK_ALGO_FLAG_DEFER: waits for it, re-runs the queries whose answer
  * was not certified (on the GPU) and reports how many result rows it rewrote; a no-op otherwise */
 int bfk_search_finish(bfk_index* idx, void* stream, int64_t* n_rewritten);

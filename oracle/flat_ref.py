@@ -185,6 +185,47 @@ def knn_f64(xq, xb, k, metric=METRIC_L2):
     return D, I
 
 
+def bitmap_to_mask(bitmap: np.ndarray, n: int) -> np.ndarray:
+    """faiss IDSelectorBitmap layout: row i admitted <=> bit (i & 7) of byte (i >> 3) is set."""
+    bits = np.unpackbits(np.ascontiguousarray(bitmap, dtype=np.uint8), bitorder="little")
+    out = np.zeros(n, dtype=bool)
+    m = min(n, bits.size)
+    out[:m] = bits[:m].astype(bool)
+    return out
+
+
+def knn_selected(xq, xb, k, metric, mask):
+    """faiss search with SearchParameters(sel=...): the rows the selector rejects do not exist for the search
+    (IndexFlat::search hands `sel` to the distance computer loop; ids stay the original row numbers)."""
+    ids = np.flatnonzero(mask)
+    if ids.size == 0:
+        D = np.empty((xq.shape[0], 0), dtype=np.float32)
+        I = np.empty((xq.shape[0], 0), dtype=np.int64)
+        return _pad(D, I, k, metric)
+    D, I = knn(xq, np.ascontiguousarray(xb[ids]), k, metric)
+    I = np.where(I >= 0, ids[np.clip(I, 0, ids.size - 1)], -1).astype(np.int64)
+    return D, I
+
+
+def range_search(xq, xb, radius, metric):
+    """faiss IndexFlat::range_search: squared L2 < radius / inner product > radius (strict), direct fp32
+    arithmetic (RangeSearchResultHandler over exhaustive_L2sqr_seq / exhaustive_inner_product_seq).
+    Returns (lims int64[nq+1], D float32[total], I int64[total]); rows of a query in id order."""
+    nq = xq.shape[0]
+    lims = np.zeros(nq + 1, dtype=np.int64)
+    Ds, Is = [], []
+    for i in range(nq):
+        dist = pairwise_seq(xq[i : i + 1], xb, metric)[0] if xb.shape[0] else np.zeros(0, dtype=np.float32)
+        keep = dist < np.float32(radius) if metric == METRIC_L2 else dist > np.float32(radius)
+        ids = np.flatnonzero(keep).astype(np.int64)
+        Ds.append(dist[ids].astype(np.float32))
+        Is.append(ids)
+        lims[i + 1] = lims[i] + ids.size
+    D = np.concatenate(Ds) if Ds else np.zeros(0, dtype=np.float32)
+    I = np.concatenate(Is) if Is else np.zeros(0, dtype=np.int64)
+    return lims, D, I
+
+
 class IndexFlatRef:
     """CPU mirror of the faiss.IndexFlat surface the reference touches.
 
@@ -208,12 +249,20 @@ class IndexFlatRef:
         assert d == self.d
         self._x = np.concatenate([self._x, np.ascontiguousarray(x, dtype=np.float32)], axis=0)
 
-    def search(self, x, k):
+    def search(self, x, k, *, params=None):
         x = np.asarray(x)
         n, d = x.shape
         assert d == self.d
         assert k > 0
+        sel = getattr(params, "sel", None) if params is not None else None
+        if sel is not None:
+            return knn_selected(np.ascontiguousarray(x, dtype=np.float32), self._x, k, self.metric_type,
+                                bitmap_to_mask(sel.to_bitmap(self.ntotal), self.ntotal))
         return knn(np.ascontiguousarray(x, dtype=np.float32), self._x, k, self.metric_type)
+
+    def range_search(self, x, thresh):
+        return range_search(np.ascontiguousarray(np.asarray(x), dtype=np.float32), self._x, float(thresh),
+                            self.metric_type)
 
     def reset(self):
         self._x = np.empty((0, self.d), dtype=np.float32)
