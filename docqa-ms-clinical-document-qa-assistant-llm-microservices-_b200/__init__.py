@@ -5,6 +5,7 @@ package as `docqa_b200` (a thin alias package at the repository root).
 """
 from ._lib import (ALGO_AUTO, ALGO_EXACT_SIMT, ALGO_TENSOR, MAX_D, MAX_K, METRIC_INNER_PRODUCT, METRIC_L2,
                    SearchStats)
+from .encoder import MiniLMEncoder, pad_to_multiple
 from .faiss_shim import install_as_faiss
 from .flat import (IndexFlat, IndexFlatIP, IndexFlatL2, deserialize_index, get_num_gpus, normalize_L2,
                    read_index, serialize_index, write_index)
@@ -23,5 +24,5 @@ __all__ = [
     "ALGO_AUTO", "ALGO_EXACT_SIMT", "ALGO_TENSOR", "MAX_K", "MAX_D",
     "SearchParameters", "IDSelector", "IDSelectorAll", "IDSelectorRange", "IDSelectorArray", "IDSelectorBatch",
     "IDSelectorBitmap", "IDSelectorNot", "IDSelectorAnd", "IDSelectorOr",
-    "FlatVectorStore", "Document", "InMemoryDocstore", "create_app", "patient_snippets",
+    "MiniLMEncoder", "pad_to_multiple", "FlatVectorStore", "Document", "InMemoryDocstore", "create_app", "patient_snippets",
 ]

@@ -42,6 +42,7 @@ EXPORTS = [
     "bfk_xchg_free",
     "bfk_reconstruct", "bfk_remove_ids", "bfk_write", "bfk_read", "bfk_serialized_size",
     "bfk_serialize", "bfk_deserialize", "bfk_normalize_l2", "bfk_merge_topk", "bfk_merge_topk_strided", "bfk_search_noalloc",
+    "bfk_enc_create", "bfk_enc_free", "bfk_enc_set_tensor", "bfk_enc_forward", "bfk_enc_encode", "bfk_enc_encode_add",
     "bfk_search_sel", "bfk_range_search", "bfk_range_result_size", "bfk_range_result_copy", "bfk_range_result_free",
 ]
 
@@ -106,6 +107,12 @@ def load() -> ctypes.CDLL:
     L.bfk_range_result_size.restype = i64
     L.bfk_range_result_copy.argtypes = [vp, vp, vp, i32]
     L.bfk_range_result_free.argtypes = [vp]
+    L.bfk_enc_create.argtypes = [i32, i32, i32, i32, i32, i32, i32, ctypes.c_float, ctypes.POINTER(vp)]
+    L.bfk_enc_free.argtypes = [vp]
+    L.bfk_enc_set_tensor.argtypes = [vp, ctypes.c_char_p, vp, i64]
+    L.bfk_enc_forward.argtypes = [vp, vp, vp, i32, i64, i32, vp, vp]
+    L.bfk_enc_encode.argtypes = [vp, vp, vp, i32, i64, i32, vp, vp]
+    L.bfk_enc_encode_add.argtypes = [vp, vp, vp, vp, i32, i64, i32, vp]
     _lib = L
     return L
 

@@ -1,0 +1,287 @@
+// E1 `enc_embed_ln_kernel`, E3 `enc_attention_kernel`: the non-GEMM parts of the sentence encoder
+// (transformers BertEmbeddings and BertSelfAttention as run by
+// SentenceTransformer('all-MiniLM-L6-v2') for semantic-indexer/indexer.py:21,37 and llm-qa/main.py:25).
+//
+// E3, one CTA per (128-query tile, head, chunk), 4 warps, thread r == query row r == TMEM lane r:
+//   1. Q [128 x 32], K [T x 32] and V^T [32 x T] of this head are written into shared memory in the
+//      128-byte-swizzled K-major layout tcgen05 reads (the rows are 64 bytes, so the upper half of each
+//      swizzle row is simply unused);
+//   2. S = Q K^T : tcgen05.mma M=128, N=T, two K=16 steps, fp32 accumulator in TMEM (T <= 256 columns);
+//   3. softmax over the row, in the thread that owns it: pass 1 max of (S/sqrt(32) + mask bias), pass 2
+//      exp2 and sum; P is rounded to bf16 and written to shared memory as the A operand of step 4 (the
+//      region Q and K occupied);
+//   4. O = P V : T/64 K-blocks x 4 tcgen05.mma (M=128, N=32, K=16) into the first 32 TMEM columns;
+//   5. O / rowsum -> bf16 context rows.
+// 256 TMEM columns and ~82 KB of shared memory per CTA: two CTAs per SM overlap each other's phases.
+#include "bfk_common.cuh"
+#include "bfk_ptx.cuh"
+
+namespace bfk {
+
+constexpr int EA_THREADS = 128;
+constexpr int EA_DH = 32;        // head dimension (all-MiniLM-L6-v2: 384 / 12)
+constexpr int EA_MAXT = 256;
+constexpr int EA_Q_OFF = 0;                   // 16 KiB
+constexpr int EA_K_OFF = 16 * 1024;           // 32 KiB
+constexpr int EA_P_OFF = 0;                   // 64 KiB, aliases Q and K once S is in TMEM
+constexpr int EA_VT_OFF = 64 * 1024;          // 16 KiB
+constexpr int EA_MB_OFF = 80 * 1024;          // [256] fp32 mask bias
+constexpr int EA_BAR_OFF = EA_MB_OFF + EA_MAXT * 4;
+constexpr int EA_SMEM = EA_BAR_OFF + 64 + 1024 /*alignment*/;
+
+__device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+// byte offset of 16-byte chunk `c` (0..7) of row `r` inside a [rows x 128 B] tile, 128-byte swizzle
+__device__ __forceinline__ uint32_t sw128_off(int r, int c) {
+    return (uint32_t)((r >> 3) * 1024 + (r & 7) * 128 + ((c ^ (r & 7)) << 4));
+}
+
+struct EncAttnParams {
+    const __nv_bfloat16* qkv;   // [B*T, 3*H]: Q | K | V, head h at columns h*32
+    const float* mask_bias;     // [B*T]: 0 for real tokens, -1e30 for padding (already in the log2 domain)
+    __nv_bfloat16* ctx;         // [B*T, H]
+    int T, H;
+    float scale_log2;           // log2(e) / sqrt(head_dim)
+};
+
+__global__ void __launch_bounds__(EA_THREADS) enc_attention_kernel(const EncAttnParams p) {
+    extern __shared__ __align__(1024) unsigned char smem_raw[];
+    const uint32_t raw = smem_u32(smem_raw);
+    unsigned char* smem = smem_raw + ((1024u - (raw & 1023u)) & 1023u);
+    float* mb = reinterpret_cast<float*>(smem + EA_MB_OFF);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + EA_BAR_OFF);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2);
+
+    const int tid = threadIdx.x, warp = tid >> 5;
+    const int mt = blockIdx.x, h = blockIdx.y;
+    const int64_t b = blockIdx.z;
+    const int T = p.T, ld = 3 * p.H;
+    const int64_t row0 = b * T;
+
+    if (tid == 0) {
+        mbar_init(&bars[0], 1);
+        mbar_init(&bars[1], 1);
+        fence_mbar_init();
+    }
+    if (warp == 0) tmem_alloc<256>(tmem_slot);
+
+    // ---- 1. stage Q, K, V^T and the mask bias ----
+    {
+        const int q = mt * 128 + tid;
+        uint4 v[4] = {make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0)};
+        if (q < T) {
+            const uint4* src = reinterpret_cast<const uint4*>(p.qkv + (size_t)(row0 + q) * ld + h * EA_DH);
+#pragma unroll
+            for (int c = 0; c < 4; c++) v[c] = __ldg(src + c);
+        }
+#pragma unroll
+        for (int c = 0; c < 4; c++) *reinterpret_cast<uint4*>(smem + EA_Q_OFF + sw128_off(tid, c)) = v[c];
+    }
+    for (int t = tid; t < T; t += EA_THREADS) {
+        const uint4* ksrc = reinterpret_cast<const uint4*>(p.qkv + (size_t)(row0 + t) * ld + p.H + h * EA_DH);
+        const uint4* vsrc = reinterpret_cast<const uint4*>(p.qkv + (size_t)(row0 + t) * ld + 2 * p.H + h * EA_DH);
+        uint4 kv[4], vv[4];
+#pragma unroll
+        for (int c = 0; c < 4; c++) {
+            kv[c] = __ldg(ksrc + c);
+            vv[c] = __ldg(vsrc + c);
+        }
+#pragma unroll
+        for (int c = 0; c < 4; c++) *reinterpret_cast<uint4*>(smem + EA_K_OFF + sw128_off(t, c)) = kv[c];
+        // V^T: element (dim, token) -> K-block token/64, row dim, column token%64
+        const unsigned short* ve = reinterpret_cast<const unsigned short*>(vv);
+        const int kb = t >> 6, col = t & 63;
+        unsigned char* vt = smem + EA_VT_OFF + kb * 4096;
+#pragma unroll
+        for (int d = 0; d < EA_DH; d++)
+            *reinterpret_cast<unsigned short*>(vt + sw128_off(d, col >> 3) + (col & 7) * 2) = ve[d];
+        mb[t] = p.mask_bias[row0 + t];
+    }
+    fence_proxy_async_smem();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(tmem_slot);
+
+    // ---- 2. S = Q K^T ----
+    if (warp == 0) {
+        if (elect_one()) {
+            const uint32_t idesc = make_idesc_bf16(128, T);
+            const uint64_t da0 = make_smem_desc_sw128(smem_u32(smem + EA_Q_OFF));
+            const uint64_t db0 = make_smem_desc_sw128(smem_u32(smem + EA_K_OFF));
+#pragma unroll
+            for (int kk = 0; kk < EA_DH / 16; kk++) umma_bf16(tmem_base, da0 + 2 * kk, db0 + 2 * kk, idesc, kk != 0 ? 1u : 0u);
+            umma_commit(&bars[0]);
+        }
+        __syncwarp();
+    }
+    mbar_wait(&bars[0], 0);
+    tc_fence_after();
+
+    // ---- 3. softmax of row `tid` ----
+    const uint32_t lane_addr = tmem_base + ((uint32_t)(warp * 32) << 16);
+    uint32_t r[32];
+    float mx = -INFINITY;
+#pragma unroll 1
+    for (int c = 0; c < T; c += 32) {
+        tmem_ld_32x32(lane_addr + c, r);
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 32; j++) mx = fmaxf(mx, fmaf(__uint_as_float(r[j]), p.scale_log2, mb[c + j]));
+    }
+    // every thread has finished reading Q/K-dependent state only through TMEM; P may now overwrite Q and K,
+    // but only after ALL rows' MMAs completed -- which bars[0] already guarantees
+    float sum = 0.f;
+#pragma unroll 1
+    for (int c = 0; c < T; c += 32) {
+        tmem_ld_32x32(lane_addr + c, r);
+        tmem_ld_wait();
+        uint32_t pk[16];
+#pragma unroll
+        for (int j = 0; j < 16; j++) {
+            const float p0 = exp2f(fmaf(__uint_as_float(r[2 * j]), p.scale_log2, mb[c + 2 * j]) - mx);
+            const float p1 = exp2f(fmaf(__uint_as_float(r[2 * j + 1]), p.scale_log2, mb[c + 2 * j + 1]) - mx);
+            const __nv_bfloat162 pb = __floats2bfloat162_rn(p0, p1);
+            sum += __bfloat162float(pb.x) + __bfloat162float(pb.y);  // normalise by what is really multiplied
+            pk[j] = *reinterpret_cast<const uint32_t*>(&pb);
+        }
+        unsigned char* pblk = smem + EA_P_OFF + (c >> 6) * 16384;
+#pragma unroll
+        for (int i = 0; i < 4; i++)
+            *reinterpret_cast<uint4*>(pblk + sw128_off(tid, ((c & 63) >> 3) + i)) =
+                make_uint4(pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);
+    }
+    fence_proxy_async_smem();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+
+    // ---- 4. O = P V ----
+    if (warp == 0) {
+        if (elect_one()) {
+            const uint32_t idesc = make_idesc_bf16(128, EA_DH);
+            for (int kb = 0; kb < (T >> 6); kb++) {
+                const uint64_t da0 = make_smem_desc_sw128(smem_u32(smem + EA_P_OFF + kb * 16384));
+                const uint64_t db0 = make_smem_desc_sw128(smem_u32(smem + EA_VT_OFF + kb * 4096));
+#pragma unroll
+                for (int kk = 0; kk < 4; kk++) umma_bf16(tmem_base, da0 + 2 * kk, db0 + 2 * kk, idesc, (kb | kk) != 0 ? 1u : 0u);
+            }
+            umma_commit(&bars[1]);
+        }
+        __syncwarp();
+    }
+    mbar_wait(&bars[1], 0);
+    tc_fence_after();
+
+    // ---- 5. normalise and store ----
+    tmem_ld_32x32(lane_addr, r);
+    tmem_ld_wait();
+    const int q = mt * 128 + tid;
+    if (q < T) {
+        const float inv = 1.0f / sum;
+        uint32_t o[16];
+#pragma unroll
+        for (int j = 0; j < 16; j++) {
+            const __nv_bfloat162 ob = __floats2bfloat162_rn(__uint_as_float(r[2 * j]) * inv, __uint_as_float(r[2 * j + 1]) * inv);
+            o[j] = *reinterpret_cast<const uint32_t*>(&ob);
+        }
+        uint4* dst = reinterpret_cast<uint4*>(p.ctx + (size_t)(row0 + q) * p.H + h * EA_DH);
+#pragma unroll
+        for (int i = 0; i < 4; i++) dst[i] = make_uint4(o[4 * i], o[4 * i + 1], o[4 * i + 2], o[4 * i + 3]);
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) {
+        tc_fence_after();
+        tmem_dealloc<256>(tmem_base);
+    }
+}
+
+int launch_enc_attention(const __nv_bfloat16* qkv, const float* mask_bias, __nv_bfloat16* ctx, int64_t B, int T, int H,
+                         int heads, cudaStream_t st) {
+    if (B <= 0) return 0;
+    if (H != heads * EA_DH) return fail("encoder attention: head dimension must be 32");
+    if (T <= 0 || T > EA_MAXT || (T & 63)) return fail("encoder attention: sequence length must be a multiple of 64, <= 256");
+    if (B > 65535) return fail("encoder attention: more than 65535 chunks per launch");
+    static bool attr_set[64] = {false};
+    int dev = 0;
+    BFK_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64 || !attr_set[dev]) {
+        BFK_CUDA(cudaFuncSetAttribute(enc_attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, EA_SMEM));
+        if (dev >= 0 && dev < 64) attr_set[dev] = true;
+    }
+    EncAttnParams p;
+    p.qkv = qkv;
+    p.mask_bias = mask_bias;
+    p.ctx = ctx;
+    p.T = T;
+    p.H = H;
+    p.scale_log2 = 1.4426950408889634f / sqrtf((float)EA_DH);
+    dim3 grid((unsigned)((T + 127) / 128), (unsigned)heads, (unsigned)B);
+    enc_attention_kernel<<<grid, EA_THREADS, EA_SMEM, st>>>(p);
+    BFK_CUDA(cudaGetLastError());
+    return 0;
+}
+
+// ---- E1: embeddings + LayerNorm, and the attention mask as an additive bias ------------------------------
+// x[m] = LN(word[ids[m]] + pos[m % T] + type[0]); one warp per token, H = 384 -> 12 values per lane
+__global__ void __launch_bounds__(256) enc_embed_ln_kernel(const int64_t* __restrict__ ids, const void* __restrict__ mask,
+                                                           int mask_dtype, const float* __restrict__ word,
+                                                           const float* __restrict__ pos, const float* __restrict__ type0,
+                                                           const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                           float eps, int64_t M, int T, int H, int vocab,
+                                                           __nv_bfloat16* __restrict__ x, float* __restrict__ mask_bias) {
+    const int lane = threadIdx.x & 31;
+    const int64_t m = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (m >= M) return;
+    int64_t id = ids[m];
+    id = id < 0 ? 0 : (id >= vocab ? vocab - 1 : id);
+    const int t = (int)(m % T);
+    float v[16];  // H <= 512
+    float s1 = 0.f;
+    const int per = (H + 31) / 32;
+    for (int i = 0; i < per; i++) {
+        const int c = lane + 32 * i;
+        v[i] = c < H ? word[(size_t)id * H + c] + pos[(size_t)t * H + c] + type0[c] : 0.f;
+        s1 += v[i];
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s1 += __shfl_xor_sync(0xffffffffu, s1, o);
+    const float mean = s1 / H;
+    float s2 = 0.f;
+    for (int i = 0; i < per; i++) {
+        const int c = lane + 32 * i;
+        const float dlt = c < H ? v[i] - mean : 0.f;
+        s2 = fmaf(dlt, dlt, s2);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s2 += __shfl_xor_sync(0xffffffffu, s2, o);
+    const float rstd = rsqrtf(s2 / H + eps);
+    for (int i = 0; i < per; i++) {
+        const int c = lane + 32 * i;
+        if (c < H) x[(size_t)m * H + c] = __float2bfloat16_rn((v[i] - mean) * rstd * gamma[c] + beta[c]);
+    }
+    if (lane == 0) {
+        float on;
+        switch (mask_dtype) {
+            case BFK_DT_I64: on = (float)reinterpret_cast<const long long*>(mask)[m]; break;
+            case BFK_DT_I32: on = (float)reinterpret_cast<const int*>(mask)[m]; break;
+            default: on = (float)reinterpret_cast<const unsigned char*>(mask)[m]; break;
+        }
+        mask_bias[m] = on != 0.f ? 0.f : -1e30f;
+    }
+}
+
+int launch_enc_embed(const int64_t* ids, const void* mask, int mask_dtype, const float* word, const float* pos,
+                     const float* type0, const float* gamma, const float* beta, float eps, int64_t M, int T, int H,
+                     int vocab, __nv_bfloat16* x, float* mask_bias, cudaStream_t st) {
+    if (M <= 0) return 0;
+    if (H > 512) return fail("encoder: hidden size > 512 is not supported");
+    const int64_t blocks = (M * 32 + 255) / 256;
+    enc_embed_ln_kernel<<<(unsigned)blocks, 256, 0, st>>>(ids, mask, mask_dtype, word, pos, type0, gamma, beta, eps, M, T, H,
+                                                         vocab, x, mask_bias);
+    BFK_CUDA(cudaGetLastError());
+    return 0;
+}
+
+}  // namespace bfk

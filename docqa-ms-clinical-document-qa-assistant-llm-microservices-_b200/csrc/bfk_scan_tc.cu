@@ -42,6 +42,7 @@
 
 #include "bfk_common.cuh"
 #include "bfk_ptx.cuh"
+#include "bfk_tmap.cuh"
 
 namespace bfk {
 
@@ -706,11 +707,7 @@ __global__ void __launch_bounds__(RR_THREADS) rerank_kernel(const RerankParams p
 }
 
 // ---- host side -------------------------------------------------------------------------
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
-                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
-                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-static EncodeTiledFn get_encode_fn() {
+EncodeTiledFn get_encode_fn() {
     static EncodeTiledFn fn = nullptr;
     if (!fn) {
         void* p = nullptr;
@@ -725,7 +722,7 @@ static EncodeTiledFn get_encode_fn() {
 }
 
 // bf16 matrix [rows, ld] row-major; box = 64 columns x box_rows, 128-byte swizzle, OOB rows read as 0
-static int make_tmap(CUtensorMap* m, const void* base, int64_t rows, int ld, int box_rows) {
+int make_tmap(CUtensorMap* m, const void* base, int64_t rows, int ld, int box_rows) {
     EncodeTiledFn enc = get_encode_fn();
     if (!enc) return fail("cuTensorMapEncodeTiled is not available from this driver");
     cuuint64_t gdim[2] = {(cuuint64_t)ld, (cuuint64_t)std::max<int64_t>(rows, 1)};

@@ -184,6 +184,27 @@ int bfk_xchg_merge(void* handle, const float* D_local, const int64_t* I_local, i
 int64_t bfk_xchg_last_max_nflag(void* handle);
 int bfk_xchg_free(void* handle);
 
+/* The sentence encoder feeding the pooling kernel and the index without leaving the GPU:
+ * a BERT encoder of all-MiniLM-L6-v2's shape -- SentenceTransformer('all-MiniLM-L6-v2').encode at
+ * semantic-indexer/indexer.py:21,37 and HuggingFaceEmbeddings at llm-qa/main.py:25, minus tokenisation.
+ * This build supports hidden = 384 with 32-wide heads, intermediate % 384 == 0, T % 64 == 0, T <= 256.
+ * bfk_enc_set_tensor takes host fp32 tensors under their transformers BertModel.state_dict() names
+ * ("embeddings.word_embeddings.weight", "encoder.layer.0.attention.self.query.weight", ...).
+ * ids int64 [B, T] and mask [B, T] (BFK_DT_I64 / I32 / U8) are DEVICE pointers; work is enqueued on stream. */
+int bfk_enc_create(int device, int vocab, int hidden, int layers, int heads, int inter, int max_pos, float eps,
+                   void** out);
+int bfk_enc_free(void* enc);
+int bfk_enc_set_tensor(void* enc, const char* name, const float* data, int64_t nelem);
+/* last_hidden_state: bf16 [B, T, hidden] on the device */
+int bfk_enc_forward(void* enc, const int64_t* ids, const void* mask, int mask_dtype, int64_t B, int T,
+                    void* out_tok_bf16, void* stream);
+/* encode(): forward + mean pool + L2 normalise -> float32 [B, hidden] on the device */
+int bfk_enc_encode(void* enc, const int64_t* ids, const void* mask, int mask_dtype, int64_t B, int T, float* out_emb,
+                   void* stream);
+/* indexer.py:37 + :41 in one call: encode the chunks and append their embeddings to the index */
+int bfk_enc_encode_add(void* enc, bfk_index* idx, const int64_t* ids, const void* mask, int mask_dtype, int64_t B,
+                       int T, void* stream);
+
 /* Exact search that allocates nothing (no counterpart in the reference, whose faiss-cpu
  * index simply mallocs).  For callers that must not call cudaMalloc once they are running:
  * processes that gave all of HBM to their own pool at start-up, request handlers that cannot

@@ -1,0 +1,91 @@
+"""The GPU sentence encoder (E1-E3 + K1) against transformers' BertModel in fp32 and the numpy oracle. GPU only.
+
+Tolerance (stated here because BASELINE.json's north star gives none for the encoder): the kernels keep
+activations in bf16 (8 mantissa bits) between ops and accumulate in fp32, so on LayerNorm-ed states of unit
+variance the error after L layers is bounded in the tests by max |err| <= 0.03 + 0.02 L, mean |err| <= 0.004 +
+0.002 L; sentence embeddings (unit vectors) must agree to cosine >= 0.9995.
+"""
+import numpy as np
+import pytest
+
+from oracle import encoder_ref
+from tests.test_oracle_encoder import hf_model, inputs
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def bfk():
+    import docqa_b200
+
+    assert docqa_b200.get_num_gpus() >= 1, "GPU tests need a CUDA device"
+    return docqa_b200
+
+
+def run_both(bfk, layers, B, T, vocab=500):
+    import torch
+
+    m = hf_model(layers=layers, vocab=vocab)
+    enc = bfk.MiniLMEncoder.from_hf_model(m)
+    ids, mask = inputs(B, T, vocab)
+    with torch.no_grad():
+        want = m(input_ids=torch.from_numpy(ids), attention_mask=torch.from_numpy(mask)).last_hidden_state.numpy()
+    ids_d, mask_d = torch.from_numpy(ids).cuda(), torch.from_numpy(mask).cuda()
+    got = enc.forward(ids_d, mask_d)
+    assert got.dtype == torch.bfloat16 and tuple(got.shape) == (B, T, 384)
+    return m, enc, ids, mask, ids_d, mask_d, want, got.float().cpu().numpy()
+
+
+@pytest.mark.parametrize("layers,B,T", [(1, 2, 64), (1, 3, 128), (2, 5, 256), (6, 4, 192)])
+def test_last_hidden_state_matches_bert(bfk, layers, B, T):
+    m, enc, ids, mask, ids_d, mask_d, want, got = run_both(bfk, layers, B, T)
+    valid = mask.astype(bool)  # padded positions are never read by the pooling that follows
+    err = np.abs(got - want)[valid]
+    assert err.max() <= 0.03 + 0.02 * layers, (err.max(), err.mean())
+    assert err.mean() <= 0.004 + 0.002 * layers, (err.max(), err.mean())
+    # the numpy oracle sits between the two
+    sd = {k: v.numpy() for k, v in m.state_dict().items()}
+    orc = encoder_ref.forward(sd, ids, mask, eps=m.config.layer_norm_eps)
+    assert np.abs(orc - want)[valid].max() < 1e-3
+
+
+def test_embeddings_and_fused_add(bfk):
+    import torch
+
+    m, enc, ids, mask, ids_d, mask_d, want, got = run_both(bfk, 6, 7, 128)
+    sd = {k: v.numpy() for k, v in m.state_dict().items()}
+    ref = encoder_ref.encode(sd, ids, mask, eps=m.config.layer_norm_eps)
+    emb = enc.encode_ids(ids_d, mask_d)
+    assert emb.dtype == torch.float32 and tuple(emb.shape) == (7, 384)
+    e = emb.cpu().numpy()
+    np.testing.assert_allclose(np.linalg.norm(e, axis=1), 1.0, atol=1e-5)
+    cos = (e * ref).sum(1)
+    assert cos.min() >= 0.9995, cos
+    # encode + index.add without leaving the GPU == add(encode_ids(...))
+    idx = bfk.IndexFlatL2(384)
+    enc.encode_add(idx, ids_d, mask_d)
+    enc.encode_add(idx, ids_d[:2], mask_d[:2])
+    assert idx.ntotal == 9
+    rows = idx.reconstruct_n(0, 9)
+    np.testing.assert_allclose(rows[:7], e, atol=1e-6)
+    np.testing.assert_allclose(rows[7:], e[:2], atol=1e-6)
+    D, I = idx.search(ref[:3], 2)
+    assert (np.sort(I, axis=1)[:3].tolist() == [[0, 7], [1, 8], [2, 2]][:2] + [np.sort(I[2]).tolist()])
+    assert I[2, 0] == 2 and D[2, 0] < 2e-3
+
+
+def test_shape_and_argument_errors(bfk):
+    import torch
+
+    enc = bfk.MiniLMEncoder(num_hidden_layers=1, vocab_size=100)
+    ids = torch.zeros((1, 60), dtype=torch.int64, device="cuda")
+    with pytest.raises(RuntimeError, match="multiple of 64"):
+        enc.forward(ids, torch.ones_like(ids))
+    p_ids, p_mask = bfk.pad_to_multiple(ids, torch.ones_like(ids))
+    assert tuple(p_ids.shape) == (1, 64) and int(p_mask.sum()) == 60
+    with pytest.raises(RuntimeError, match="unknown tensor"):
+        enc.load_state_dict({"encoder.layer.0.nope.weight": np.zeros(4, np.float32)})
+    with pytest.raises(RuntimeError, match="expected"):
+        enc.load_state_dict({"embeddings.LayerNorm.weight": np.zeros(5, np.float32)})
+    with pytest.raises(RuntimeError, match="hidden = 384"):
+        bfk.MiniLMEncoder(hidden_size=768, num_attention_heads=12)
