@@ -10,15 +10,18 @@
 //     EPI_GELU    exact (erf) GELU, store bf16                  (intermediate, N = 1536)
 //     EPI_RES_LN  + residual row, LayerNorm(gamma, beta, eps)   (attention output / FFN output, N = 384)
 //
-// Tile = 128 rows x 384 columns: 384 is the model width, so a CTA owns complete rows and LayerNorm needs no
-// cross-CTA (or even cross-thread) reduction -- epilogue thread r owns TMEM lane r = output row r, makes one
-// pass over its 384 accumulator columns for mean / variance and a second one to normalise and store.  All N
-// in the model are multiples of 384.  Per 64-wide K-block a stage holds the A block (16 KB) and three
-// 128-row W blocks (48 KB), TMA-loaded with 128-byte swizzle; the MMA warp (converged, one elected lane)
-// issues 4 x 3 tcgen05.mma (M=128, N=128, K=16) into three 128-column accumulators.  Persistent grid; the
-// accumulator is single-buffered (384 of the 512 TMEM columns), so the MMAs of the next tile wait for the
-// epilogue of this one while the TMA ring keeps prefetching -- the known cost of fusing the full-row
-// LayerNorm.
+// Two tile shapes, one kernel (template<EPI, BN>):
+//   BN = 384 (the model width) for the LayerNorm epilogue: a CTA owns complete rows, so LayerNorm needs no
+//     cross-CTA reduction -- the two epilogue threads that share an output row (one per 192-column half)
+//     exchange their partial sums through shared memory, pass 1 over the accumulator gives mean / variance,
+//     pass 2 normalises and stores.  384 of the 512 TMEM columns: single-buffered, the next tile's MMAs wait
+//     for this tile's epilogue while the TMA ring keeps prefetching.
+//   BN = 192 for the bias / GELU epilogues (all N in the model are multiples of 192): two accumulators, so
+//     the MMAs of tile i+1 run under the epilogue of tile i.
+// Per 64-wide K-block a stage holds the A block (16 KB) and the W block (BN rows), TMA-loaded with 128-byte
+// swizzle; the MMA warp (converged, one elected lane) issues tcgen05.mma M=128, N=128 x3 or N=192, K=16.
+// Persistent grid; 8 epilogue warps, thread = (output row = TMEM lane, column half), TMEM loads of the next
+// 32 columns in flight while the current ones are finished.
 #include <cuda.h>
 
 #include "bfk_common.cuh"
@@ -27,13 +30,23 @@
 
 namespace bfk {
 
-constexpr int EG_BM = 128, EG_BN = 384, EG_BK = 64;
-constexpr int EG_THREADS = 256;                       // 4 control warps + 4 epilogue warps
+constexpr int EG_BM = 128, EG_BK = 64;
+constexpr int EG_THREADS = 384;                       // 4 control warps + 8 epilogue warps
+constexpr int EG_EPI_THREADS = 256;
 constexpr int EG_A_BYTES = EG_BM * EG_BK * 2;         // 16 KiB
-constexpr int EG_B_BYTES = EG_BN * EG_BK * 2;         // 48 KiB (three 128-row blocks)
-constexpr int EG_STAGE = EG_A_BYTES + EG_B_BYTES;     // 64 KiB
-constexpr int EG_STAGES = 3;
-constexpr int EG_SMEM = EG_STAGES * EG_STAGE + 1024 /*alignment*/ + 256 /*barriers*/;
+constexpr int EG_TAIL = 256 /*barriers*/ + 2 * 2 * 128 * 8 /*LayerNorm partial sums, double-buffered*/ +
+                        8 * 2048 /*per-warp store staging*/;
+
+template <int BN>
+struct EgShape {
+    static constexpr int BNB = BN == 384 ? 128 : BN;   // N of one tcgen05.mma
+    static constexpr int NBLK = BN / BNB;
+    static constexpr int NACC = BN == 192 ? 2 : 1;     // accumulators (256 TMEM columns apart)
+    static constexpr int B_BYTES = BN * EG_BK * 2;
+    static constexpr int STAGE = EG_A_BYTES + B_BYTES;
+    static constexpr int STAGES = BN == 192 ? 5 : 3;
+    static constexpr int SMEM = STAGES * STAGE + 1024 /*alignment*/ + EG_TAIL;
+};
 
 enum { EPI_BIAS = 0, EPI_GELU = 1, EPI_RES_LN = 2 };
 
@@ -48,40 +61,60 @@ struct EncGemmParams {
     int ldo;
 };
 
-__device__ __forceinline__ float gelu_erf(float x) { return 0.5f * x * (1.0f + erff(x * 0.70710678118654752f)); }
+// exact-GELU through Abramowitz-Stegun 7.1.26 (|erf error| <= 1.5e-7, far below the bf16 rounding of the
+// result): one reciprocal, one exp and a handful of FMAs instead of erff's ~25 instructions -- the GELU
+// epilogue runs 128 x 192 of these per tile
+__device__ __forceinline__ float gelu_erf(float x) {
+    const float z = fabsf(x) * 0.70710678118654752f;
+    const float t = __fdividef(1.0f, fmaf(0.3275911f, z, 1.0f));  // MUFU.RCP; __frcp_rn was 20 % of the epilogue's samples
+    float poly = fmaf(1.061405429f, t, -1.453152027f);
+    poly = fmaf(poly, t, 1.421413741f);
+    poly = fmaf(poly, t, -0.284496736f);
+    poly = fmaf(poly, t, 0.254829592f);
+    const float erf_abs = 1.0f - poly * t * __expf(-z * z);
+    return 0.5f * x * (1.0f + copysignf(erf_abs, x));
+}
 
 __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
     const __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
     return *reinterpret_cast<const uint32_t*>(&v);
 }
 
-template <int EPI>
+__device__ __forceinline__ void eg_epi_sync() { asm volatile("bar.sync 3, 256;" ::: "memory"); }
+
+template <int EPI, int BN>
 __global__ void __launch_bounds__(EG_THREADS, 1)
 enc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW, const EncGemmParams p) {
+    using S = EgShape<BN>;
+    constexpr int STAGES = S::STAGES, STAGE = S::STAGE, NACC = S::NACC;
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     const uint32_t raw = smem_u32(smem_raw);
     unsigned char* smem = smem_raw + ((1024u - (raw & 1023u)) & 1023u);
     unsigned char* ring = smem;
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + EG_STAGES * EG_STAGE);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * STAGE);
     uint64_t* full_bar = bars;                    // [stages]
-    uint64_t* empty_bar = bars + EG_STAGES;       // [stages]
-    uint64_t* tfull_bar = bars + 2 * EG_STAGES;   // accumulator complete
-    uint64_t* tempty_bar = tfull_bar + 1;         // accumulator drained (128 epilogue threads)
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 1);
+    uint64_t* empty_bar = bars + STAGES;          // [stages]
+    uint64_t* tfull_bar = bars + 2 * STAGES;      // [NACC] accumulator complete
+    uint64_t* tempty_bar = tfull_bar + 2;         // [NACC] accumulator drained (256 epilogue threads)
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+    float2* ln_part = reinterpret_cast<float2*>(smem + STAGES * STAGE + 256);  // [2 parities][2 halves][128 rows]
+    unsigned char* stg_all = smem + STAGES * STAGE + 256 + 4096;                 // [8 warps][32 rows x 64 B]
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int KB = p.K / EG_BK;
-    const int n_tiles = p.N / EG_BN;
+    const int n_tiles = p.N / BN;
     const int m_tiles = (p.M + EG_BM - 1) / EG_BM;
     const int tiles = m_tiles * n_tiles;
 
     if (tid == 0) {
-        for (int i = 0; i < EG_STAGES; i++) {
+        for (int i = 0; i < STAGES; i++) {
             mbar_init(&full_bar[i], 1);
             mbar_init(&empty_bar[i], 1);
         }
-        mbar_init(tfull_bar, 1);
-        mbar_init(tempty_bar, 128);
+        for (int a = 0; a < 2; a++) {
+            mbar_init(&tfull_bar[a], 1);
+            mbar_init(&tempty_bar[a], EG_EPI_THREADS);
+        }
         fence_mbar_init();
     }
     if (warp == 2) tmem_alloc<512>(tmem_slot);
@@ -102,14 +135,14 @@ enc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                 const int mt = tile / n_tiles, nt = tile - mt * n_tiles;
                 for (int kb = 0; kb < KB; kb++) {
                     mbar_wait(&empty_bar[st], ph ^ 1u);
-                    unsigned char* stage = ring + (size_t)st * EG_STAGE;
-                    mbar_expect_tx(&full_bar[st], (uint32_t)EG_STAGE);
+                    unsigned char* stage = ring + (size_t)st * STAGE;
+                    mbar_expect_tx(&full_bar[st], (uint32_t)STAGE);
                     tma_load_2d(stage, &tmA, kb * EG_BK, mt * EG_BM, &full_bar[st]);
 #pragma unroll
-                    for (int nb = 0; nb < 3; nb++)
-                        tma_load_2d(stage + EG_A_BYTES + nb * (128 * EG_BK * 2), &tmW, kb * EG_BK,
-                                    nt * EG_BN + nb * 128, &full_bar[st]);
-                    if (++st == EG_STAGES) {
+                    for (int nb = 0; nb < S::NBLK; nb++)
+                        tma_load_2d(stage + EG_A_BYTES + nb * (S::BNB * EG_BK * 2), &tmW, kb * EG_BK,
+                                    nt * BN + nb * S::BNB, &full_bar[st]);
+                    if (++st == STAGES) {
                         st = 0;
                         ph ^= 1u;
                     }
@@ -118,125 +151,176 @@ enc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         }
     } else if (warp == 1) {
         // ===================== MMA issuer (converged warp, one elected lane) =====================
-        const uint32_t idesc = make_idesc_bf16(EG_BM, 128);
+        const uint32_t idesc = make_idesc_bf16(EG_BM, S::BNB);
         const uint64_t desc_hi = make_smem_desc_sw128(0) & 0xffffffff00000000ull;
         const uint32_t desc_lo0 = (uint32_t)(make_smem_desc_sw128(0) & 0xffffffffull);
         const uint32_t ring_lo = desc_lo0 + ((smem_u32(ring) & 0x3ffffu) >> 4);
         uint32_t st = 0, ph = 0, tcount = 0;
         for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x, tcount++) {
-            mbar_wait(tempty_bar, (tcount & 1u) ^ 1u);  // the previous tile's epilogue has drained the accumulator
+            const uint32_t a = NACC == 2 ? (tcount & 1u) : 0u;
+            const uint32_t aph = NACC == 2 ? ((tcount >> 1) & 1u) : (tcount & 1u);
+            mbar_wait(&tempty_bar[a], aph ^ 1u);  // the epilogue has drained this accumulator
             tc_fence_after();
+            const uint32_t d_tmem = tmem_base + a * 256;
             for (int kb = 0; kb < KB; kb++) {
                 mbar_wait(&full_bar[st], ph);
                 tc_fence_after();
-                const uint32_t a_lo = ring_lo + st * (EG_STAGE >> 4);
+                const uint32_t a_lo = ring_lo + st * (STAGE >> 4);
                 const uint32_t b_lo = a_lo + (EG_A_BYTES >> 4);
                 if (elect_one()) {
 #pragma unroll
                     for (int kk = 0; kk < 4; kk++) {
                         const uint64_t da = desc_hi | (uint64_t)(a_lo + 2 * kk);
 #pragma unroll
-                        for (int nb = 0; nb < 3; nb++) {
-                            const uint64_t db = desc_hi | (uint64_t)(b_lo + nb * ((128 * EG_BK * 2) >> 4) + 2 * kk);
-                            umma_bf16(tmem_base + nb * 128, da, db, idesc, (kb | kk) != 0 ? 1u : 0u);
+                        for (int nb = 0; nb < S::NBLK; nb++) {
+                            const uint64_t db = desc_hi | (uint64_t)(b_lo + nb * ((S::BNB * EG_BK * 2) >> 4) + 2 * kk);
+                            umma_bf16(d_tmem + nb * S::BNB, da, db, idesc, (kb | kk) != 0 ? 1u : 0u);
                         }
                     }
                     umma_commit(&empty_bar[st]);
                 }
                 __syncwarp();
-                if (++st == EG_STAGES) {
+                if (++st == STAGES) {
                     st = 0;
                     ph ^= 1u;
                 }
             }
-            if (elect_one()) umma_commit(tfull_bar);
+            if (elect_one()) umma_commit(&tfull_bar[a]);
             __syncwarp();
         }
     } else if (warp >= 4) {
-        // ===================== epilogue: thread == output row =====================
-        const int row = tid - 128;  // TMEM lane
-        const uint32_t lane_addr = tmem_base + ((uint32_t)((warp - 4) * 32) << 16);
+        // ===================== epilogue: thread == (output row, column half) =====================
+        constexpr int HC = BN / 2;     // columns per thread
+        constexpr int NCH = HC / 32;   // 32-column chunks per thread
+        const int et = tid - 128;
+        const int row = et & 127, half = et >> 7;
+        const uint32_t lane_addr = tmem_base + ((uint32_t)(((warp - 4) & 3) * 32) << 16) + half * HC;
+        // Stores go through a 2 KB per-warp transpose: thread = row would write 16 bytes to 32 different rows per
+        // instruction (32 partial-sector requests; ncu: the epilogue sat in stall_lg with the LSU queue full).
+        // Staged, four lanes cover 64 contiguous bytes of a row and one instruction touches 8 rows.
+        unsigned char* stg = stg_all + (warp - 4) * 2048;
+        const int wrow0 = ((warp - 4) & 3) * 32;  // first tile row of this warp
+        auto store32 = [&](const uint32_t (&o)[16], __nv_bfloat16* out_col0, int64_t m_tile0) {
+            // o = this lane's row, 32 bf16 columns; out_col0 = out + first global column of the chunk
+#pragma unroll
+            for (int i = 0; i < 4; i++)
+                *reinterpret_cast<uint4*>(stg + lane * 64 + ((i ^ ((lane >> 1) & 3)) << 4)) =
+                    make_uint4(o[4 * i], o[4 * i + 1], o[4 * i + 2], o[4 * i + 3]);
+            __syncwarp();
+#pragma unroll
+            for (int k8 = 0; k8 < 4; k8++) {
+                const int rr = (lane >> 2) + 8 * k8, c = lane & 3;
+                const uint4 v = *reinterpret_cast<const uint4*>(stg + rr * 64 + ((c ^ ((rr >> 1) & 3)) << 4));
+                const int64_t mm = m_tile0 + wrow0 + rr;
+                if (mm < p.M) *reinterpret_cast<uint4*>(out_col0 + (size_t)mm * p.ldo + c * 8) = v;
+            }
+            __syncwarp();
+        };
         uint32_t tcount = 0;
         for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x, tcount++) {
             const int mt = tile / n_tiles, nt = tile - mt * n_tiles;
             const int64_t m = (int64_t)mt * EG_BM + row;
             const bool live = m < p.M;
-            const int n0 = nt * EG_BN;
-            mbar_wait(tfull_bar, tcount & 1u);
+            const int n0 = nt * BN + half * HC;  // first global column of this thread
+            const uint32_t a = NACC == 2 ? (tcount & 1u) : 0u;
+            const uint32_t aph = NACC == 2 ? ((tcount >> 1) & 1u) : (tcount & 1u);
+            mbar_wait(&tfull_bar[a], aph);
             tc_fence_after();
-            uint32_t r[32];
+            const uint32_t acc_addr = lane_addr + a * 256;
+            uint32_t r[2][32];
             if constexpr (EPI == EPI_RES_LN) {
-                const uint4* res = reinterpret_cast<const uint4*>(p.residual + (size_t)(live ? m : 0) * EG_BN);
+                const uint4* res = reinterpret_cast<const uint4*>(p.residual + (size_t)(live ? m : 0) * BN + half * HC);
+                const float* bias = p.bias + half * HC;
                 float s1 = 0.f, s2 = 0.f;
-#pragma unroll 1
-                for (int c = 0; c < EG_BN; c += 32) {
-                    tmem_ld_32x32(lane_addr + c, r);
+                // one 32-column chunk of pass 1: v = acc + bias + residual, accumulate sum and sum of squares
+                auto stats32 = [&](const uint32_t (&rv)[32], int ch) {
                     uint4 rr[4];
 #pragma unroll
-                    for (int i = 0; i < 4; i++) rr[i] = res[(c >> 3) + i];
-                    tmem_ld_wait();
+                    for (int i = 0; i < 4; i++) rr[i] = res[ch * 4 + i];
                     const uint32_t* rw = reinterpret_cast<const uint32_t*>(rr);
 #pragma unroll
                     for (int j = 0; j < 16; j++) {
-                        const float v0 = __uint_as_float(r[2 * j]) + __ldg(p.bias + c + 2 * j) + __uint_as_float(rw[j] << 16);
-                        const float v1 = __uint_as_float(r[2 * j + 1]) + __ldg(p.bias + c + 2 * j + 1) +
-                                         __uint_as_float(rw[j] & 0xffff0000u);
+                        const float2 bb = __ldg(reinterpret_cast<const float2*>(bias + ch * 32) + j);
+                        const float v0 = __uint_as_float(rv[2 * j]) + bb.x + __uint_as_float(rw[j] << 16);
+                        const float v1 = __uint_as_float(rv[2 * j + 1]) + bb.y + __uint_as_float(rw[j] & 0xffff0000u);
                         s1 += v0 + v1;
                         s2 = fmaf(v0, v0, fmaf(v1, v1, s2));
                     }
-                }
-                const float mean = s1 * (1.0f / EG_BN);
-                const float var = fmaxf(s2 * (1.0f / EG_BN) - mean * mean, 0.f);
-                const float rstd = rsqrtf(var + p.eps);
-                uint4* dst = reinterpret_cast<uint4*>(p.out + (size_t)(live ? m : 0) * p.ldo);
+                };
+                // rolled over chunk pairs (two register sets, the next load in flight): unrolled over all six
+                // chunks this epilogue spilled
+                tmem_ld_32x32(acc_addr, r[0]);
 #pragma unroll 1
-                for (int c = 0; c < EG_BN; c += 32) {
-                    tmem_ld_32x32(lane_addr + c, r);
+                for (int ch = 0; ch < NCH; ch += 2) {
+                    tmem_ld_wait();
+                    tmem_ld_32x32(acc_addr + (ch + 1) * 32, r[1]);
+                    stats32(r[0], ch);
+                    tmem_ld_wait();
+                    if (ch + 2 < NCH) tmem_ld_32x32(acc_addr + (ch + 2) * 32, r[0]);
+                    stats32(r[1], ch + 1);
+                }
+                float2* part = ln_part + (tcount & 1u) * 256;
+                part[half * 128 + row] = make_float2(s1, s2);
+                eg_epi_sync();
+                const float2 other = part[(half ^ 1) * 128 + row];
+                s1 += other.x;
+                s2 += other.y;
+                const float mean = s1 * (1.0f / BN);
+                const float var = fmaxf(s2 * (1.0f / BN) - mean * mean, 0.f);
+                const float rstd = rsqrtf(var + p.eps);
+                const float* gamma = p.gamma + half * HC;
+                const float* beta = p.beta + half * HC;
+                auto norm32 = [&](const uint32_t (&rv)[32], int ch) {
                     uint4 rr[4];
 #pragma unroll
-                    for (int i = 0; i < 4; i++) rr[i] = res[(c >> 3) + i];
-                    tmem_ld_wait();
+                    for (int i = 0; i < 4; i++) rr[i] = res[ch * 4 + i];
                     const uint32_t* rw = reinterpret_cast<const uint32_t*>(rr);
                     uint32_t o[16];
 #pragma unroll
                     for (int j = 0; j < 16; j++) {
-                        const float v0 = __uint_as_float(r[2 * j]) + __ldg(p.bias + c + 2 * j) + __uint_as_float(rw[j] << 16);
-                        const float v1 = __uint_as_float(r[2 * j + 1]) + __ldg(p.bias + c + 2 * j + 1) +
-                                         __uint_as_float(rw[j] & 0xffff0000u);
-                        const float y0 = (v0 - mean) * rstd * __ldg(p.gamma + c + 2 * j) + __ldg(p.beta + c + 2 * j);
-                        const float y1 = (v1 - mean) * rstd * __ldg(p.gamma + c + 2 * j + 1) + __ldg(p.beta + c + 2 * j + 1);
-                        o[j] = pack_bf16x2(y0, y1);
+                        const float2 bb = __ldg(reinterpret_cast<const float2*>(bias + ch * 32) + j);
+                        const float2 gg = __ldg(reinterpret_cast<const float2*>(gamma + ch * 32) + j);
+                        const float2 be = __ldg(reinterpret_cast<const float2*>(beta + ch * 32) + j);
+                        const float v0 = __uint_as_float(rv[2 * j]) + bb.x + __uint_as_float(rw[j] << 16);
+                        const float v1 = __uint_as_float(rv[2 * j + 1]) + bb.y + __uint_as_float(rw[j] & 0xffff0000u);
+                        o[j] = pack_bf16x2(fmaf((v0 - mean) * rstd, gg.x, be.x), fmaf((v1 - mean) * rstd, gg.y, be.y));
                     }
-                    if (live) {
-#pragma unroll
-                        for (int i = 0; i < 4; i++) dst[(c >> 3) + i] = make_uint4(o[4 * i], o[4 * i + 1], o[4 * i + 2], o[4 * i + 3]);
-                    }
+                    store32(o, p.out + half * HC + ch * 32, (int64_t)mt * EG_BM);
+                };
+                tmem_ld_32x32(acc_addr, r[0]);
+#pragma unroll 1
+                for (int ch = 0; ch < NCH; ch += 2) {
+                    tmem_ld_wait();
+                    tmem_ld_32x32(acc_addr + (ch + 1) * 32, r[1]);
+                    norm32(r[0], ch);
+                    tmem_ld_wait();
+                    if (ch + 2 < NCH) tmem_ld_32x32(acc_addr + (ch + 2) * 32, r[0]);
+                    norm32(r[1], ch + 1);
                 }
             } else {
-                uint4* dst = reinterpret_cast<uint4*>(p.out + (size_t)(live ? m : 0) * p.ldo + n0);
-#pragma unroll 1
-                for (int c = 0; c < EG_BN; c += 32) {
-                    tmem_ld_32x32(lane_addr + c, r);
+                const float* bias = p.bias + n0;
+                tmem_ld_32x32(acc_addr, r[0]);
+#pragma unroll
+                for (int ch = 0; ch < NCH; ch++) {
                     tmem_ld_wait();
+                    if (ch + 1 < NCH) tmem_ld_32x32(acc_addr + (ch + 1) * 32, r[(ch + 1) & 1]);
                     uint32_t o[16];
 #pragma unroll
                     for (int j = 0; j < 16; j++) {
-                        float v0 = __uint_as_float(r[2 * j]) + __ldg(p.bias + n0 + c + 2 * j);
-                        float v1 = __uint_as_float(r[2 * j + 1]) + __ldg(p.bias + n0 + c + 2 * j + 1);
+                        const float2 bb = __ldg(reinterpret_cast<const float2*>(bias + ch * 32) + j);
+                        float v0 = __uint_as_float(r[ch & 1][2 * j]) + bb.x;
+                        float v1 = __uint_as_float(r[ch & 1][2 * j + 1]) + bb.y;
                         if constexpr (EPI == EPI_GELU) {
                             v0 = gelu_erf(v0);
                             v1 = gelu_erf(v1);
                         }
                         o[j] = pack_bf16x2(v0, v1);
                     }
-                    if (live) {
-#pragma unroll
-                        for (int i = 0; i < 4; i++) dst[(c >> 3) + i] = make_uint4(o[4 * i], o[4 * i + 1], o[4 * i + 2], o[4 * i + 3]);
-                    }
+                    store32(o, p.out + n0 + ch * 32, (int64_t)mt * EG_BM);
                 }
             }
             tc_fence_before();
-            mbar_arrive(tempty_bar);
+            mbar_arrive(&tempty_bar[a]);
         }
     }
 
@@ -248,20 +332,20 @@ enc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     }
 }
 
-template <int EPI>
+template <int EPI, int BN>
 static int launch_enc_gemm_t(const CUtensorMap& tmA, const CUtensorMap& tmW, const EncGemmParams& p, int num_sms,
                              cudaStream_t st) {
-    auto kern = enc_gemm_kernel<EPI>;
+    auto kern = enc_gemm_kernel<EPI, BN>;
     static bool attr_set[64] = {false};
     int dev = 0;
     BFK_CUDA(cudaGetDevice(&dev));
     if (dev < 0 || dev >= 64 || !attr_set[dev]) {
-        BFK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, EG_SMEM));
+        BFK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, EgShape<BN>::SMEM));
         if (dev >= 0 && dev < 64) attr_set[dev] = true;
     }
-    const int tiles = ((p.M + EG_BM - 1) / EG_BM) * (p.N / EG_BN);
+    const int tiles = ((p.M + EG_BM - 1) / EG_BM) * (p.N / BN);
     const int grid = std::max(1, std::min(tiles, num_sms));
-    kern<<<grid, EG_THREADS, EG_SMEM, st>>>(tmA, tmW, p);
+    kern<<<grid, EG_THREADS, EgShape<BN>::SMEM, st>>>(tmA, tmW, p);
     BFK_CUDA(cudaGetLastError());
     return 0;
 }
@@ -271,11 +355,11 @@ int launch_enc_gemm(int epi, const __nv_bfloat16* A, const __nv_bfloat16* W, int
                     const __nv_bfloat16* residual, const float* gamma, const float* beta, float eps,
                     __nv_bfloat16* out, int ldo, int num_sms, cudaStream_t st) {
     if (M <= 0) return 0;
-    if (N % EG_BN != 0 || K % EG_BK != 0) return fail("encoder gemm: N must be a multiple of 384 and K of 64");
-    if (epi == EPI_RES_LN && N != EG_BN) return fail("encoder gemm: the LayerNorm epilogue needs N == 384");
+    if (N % 192 != 0 || K % EG_BK != 0) return fail("encoder gemm: N must be a multiple of 192 and K of 64");
+    if (epi == EPI_RES_LN && N != 384) return fail("encoder gemm: the LayerNorm epilogue needs N == 384");
     CUtensorMap tmA, tmW;
     BFK_TRY(make_tmap(&tmA, A, M, K, EG_BM));
-    BFK_TRY(make_tmap(&tmW, W, N, K, 128));
+    BFK_TRY(make_tmap(&tmW, W, N, K, epi == EPI_RES_LN ? 128 : 192));
     EncGemmParams p;
     p.M = M;
     p.N = N;
@@ -288,9 +372,9 @@ int launch_enc_gemm(int epi, const __nv_bfloat16* A, const __nv_bfloat16* W, int
     p.out = out;
     p.ldo = ldo;
     switch (epi) {
-        case EPI_BIAS: return launch_enc_gemm_t<EPI_BIAS>(tmA, tmW, p, num_sms, st);
-        case EPI_GELU: return launch_enc_gemm_t<EPI_GELU>(tmA, tmW, p, num_sms, st);
-        case EPI_RES_LN: return launch_enc_gemm_t<EPI_RES_LN>(tmA, tmW, p, num_sms, st);
+        case EPI_BIAS: return launch_enc_gemm_t<EPI_BIAS, 192>(tmA, tmW, p, num_sms, st);
+        case EPI_GELU: return launch_enc_gemm_t<EPI_GELU, 192>(tmA, tmW, p, num_sms, st);
+        case EPI_RES_LN: return launch_enc_gemm_t<EPI_RES_LN, 384>(tmA, tmW, p, num_sms, st);
         default: return fail("encoder gemm: unknown epilogue");
     }
 }
