@@ -2,7 +2,8 @@
 // (transformers BertEmbeddings and BertSelfAttention as run by
 // SentenceTransformer('all-MiniLM-L6-v2') for semantic-indexer/indexer.py:21,37 and llm-qa/main.py:25).
 //
-// E3, one CTA per (128-query tile, head, chunk), 4 warps, thread r == query row r == TMEM lane r:
+// E3, one CTA per (128-query tile, head, chunk), 8 warps, two threads per query row (row == TMEM lane; each
+// owns half of the key columns and exchanges its row max / row sum with its partner through shared memory):
 //   1. Q [128 x 32], K [T x 32] and V^T [32 x T] of this head are written into shared memory in the
 //      128-byte-swizzled K-major layout tcgen05 reads (the rows are 64 bytes, so the upper half of each
 //      swizzle row is simply unused);
@@ -18,7 +19,7 @@
 
 namespace bfk {
 
-constexpr int EA_THREADS = 128;
+constexpr int EA_THREADS = 256;      // two threads per query row: (row = TMEM lane, half of the keys)
 constexpr int EA_DH = 32;        // head dimension (all-MiniLM-L6-v2: 384 / 12)
 constexpr int EA_MAXT = 256;
 constexpr int EA_Q_OFF = 0;                   // 16 KiB
@@ -27,7 +28,8 @@ constexpr int EA_P_OFF = 0;                   // 64 KiB, aliases Q and K once S 
 constexpr int EA_VT_OFF = 64 * 1024;          // 16 KiB
 constexpr int EA_MB_OFF = 80 * 1024;          // [256] fp32 mask bias
 constexpr int EA_BAR_OFF = EA_MB_OFF + EA_MAXT * 4;
-constexpr int EA_SMEM = EA_BAR_OFF + 64 + 1024 /*alignment*/;
+constexpr int EA_RED_OFF = EA_BAR_OFF + 64;   // [2 halves][128 rows] row max, then row sums
+constexpr int EA_SMEM = EA_RED_OFF + 2 * 2 * 128 * 4 + 1024 /*alignment*/;
 
 __device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
@@ -51,8 +53,11 @@ __global__ void __launch_bounds__(EA_THREADS) enc_attention_kernel(const EncAttn
     float* mb = reinterpret_cast<float*>(smem + EA_MB_OFF);
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + EA_BAR_OFF);
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2);
+    float* red_max = reinterpret_cast<float*>(smem + EA_RED_OFF);  // [2][128]
+    float* red_sum = red_max + 256;                                // [2][128]
 
     const int tid = threadIdx.x, warp = tid >> 5;
+    const int row = tid & 127, half = tid >> 7;
     const int mt = blockIdx.x, h = blockIdx.y;
     const int64_t b = blockIdx.z;
     const int T = p.T, ld = 3 * p.H;
@@ -67,15 +72,15 @@ __global__ void __launch_bounds__(EA_THREADS) enc_attention_kernel(const EncAttn
 
     // ---- 1. stage Q, K, V^T and the mask bias ----
     {
-        const int q = mt * 128 + tid;
-        uint4 v[4] = {make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0)};
+        const int q = mt * 128 + row;
+        uint4 v[2] = {make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0)};
         if (q < T) {
-            const uint4* src = reinterpret_cast<const uint4*>(p.qkv + (size_t)(row0 + q) * ld + h * EA_DH);
-#pragma unroll
-            for (int c = 0; c < 4; c++) v[c] = __ldg(src + c);
+            const uint4* src = reinterpret_cast<const uint4*>(p.qkv + (size_t)(row0 + q) * ld + h * EA_DH) + 2 * half;
+            v[0] = __ldg(src);
+            v[1] = __ldg(src + 1);
         }
-#pragma unroll
-        for (int c = 0; c < 4; c++) *reinterpret_cast<uint4*>(smem + EA_Q_OFF + sw128_off(tid, c)) = v[c];
+        *reinterpret_cast<uint4*>(smem + EA_Q_OFF + sw128_off(row, 2 * half)) = v[0];
+        *reinterpret_cast<uint4*>(smem + EA_Q_OFF + sw128_off(row, 2 * half + 1)) = v[1];
     }
     for (int t = tid; t < T; t += EA_THREADS) {
         const uint4* ksrc = reinterpret_cast<const uint4*>(p.qkv + (size_t)(row0 + t) * ld + p.H + h * EA_DH);
@@ -118,29 +123,38 @@ __global__ void __launch_bounds__(EA_THREADS) enc_attention_kernel(const EncAttn
     mbar_wait(&bars[0], 0);
     tc_fence_after();
 
-    // ---- 3. softmax of row `tid` ----
-    const uint32_t lane_addr = tmem_base + ((uint32_t)(warp * 32) << 16);
-    uint32_t r[32];
+    // ---- 3. softmax of row `row`: this thread owns the key columns [c_lo, c_lo + T/2) ----
+    const uint32_t lane_addr = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);
+    const int c_lo = half * (T >> 1), nch = T >> 6;  // 32-column chunks per thread
+    uint32_t r[2][32];
     float mx = -INFINITY;
+    tmem_ld_32x32(lane_addr + c_lo, r[0]);
 #pragma unroll 1
-    for (int c = 0; c < T; c += 32) {
-        tmem_ld_32x32(lane_addr + c, r);
+    for (int ch = 0; ch < nch; ch += 2) {  // two register sets: the next chunk's load is in flight
         tmem_ld_wait();
+        if (ch + 1 < nch) tmem_ld_32x32(lane_addr + c_lo + (ch + 1) * 32, r[1]);
 #pragma unroll
-        for (int j = 0; j < 32; j++) mx = fmaxf(mx, fmaf(__uint_as_float(r[j]), p.scale_log2, mb[c + j]));
+        for (int j = 0; j < 32; j++) mx = fmaxf(mx, fmaf(__uint_as_float(r[0][j]), p.scale_log2, mb[c_lo + ch * 32 + j]));
+        if (ch + 1 < nch) {
+            tmem_ld_wait();
+            if (ch + 2 < nch) tmem_ld_32x32(lane_addr + c_lo + (ch + 2) * 32, r[0]);
+#pragma unroll
+            for (int j = 0; j < 32; j++)
+                mx = fmaxf(mx, fmaf(__uint_as_float(r[1][j]), p.scale_log2, mb[c_lo + (ch + 1) * 32 + j]));
+        }
     }
-    // every thread has finished reading Q/K-dependent state only through TMEM; P may now overwrite Q and K,
-    // but only after ALL rows' MMAs completed -- which bars[0] already guarantees
+    red_max[half * 128 + row] = mx;
+    tmem_ld_32x32(lane_addr + c_lo, r[0]);  // pass 2's first chunk loads while the halves exchange their maxima
+    __syncthreads();
+    mx = fmaxf(mx, red_max[(half ^ 1) * 128 + row]);
+    // P may overwrite Q and K: every row's S is complete (bars[0]) and nobody reads Q / K from shared memory
     float sum = 0.f;
-#pragma unroll 1
-    for (int c = 0; c < T; c += 32) {
-        tmem_ld_32x32(lane_addr + c, r);
-        tmem_ld_wait();
+    auto exp32 = [&](const uint32_t (&rv)[32], int c) {  // c = first key column of the chunk
         uint32_t pk[16];
 #pragma unroll
         for (int j = 0; j < 16; j++) {
-            const float p0 = exp2f(fmaf(__uint_as_float(r[2 * j]), p.scale_log2, mb[c + 2 * j]) - mx);
-            const float p1 = exp2f(fmaf(__uint_as_float(r[2 * j + 1]), p.scale_log2, mb[c + 2 * j + 1]) - mx);
+            const float p0 = exp2f(fmaf(__uint_as_float(rv[2 * j]), p.scale_log2, mb[c + 2 * j]) - mx);
+            const float p1 = exp2f(fmaf(__uint_as_float(rv[2 * j + 1]), p.scale_log2, mb[c + 2 * j + 1]) - mx);
             const __nv_bfloat162 pb = __floats2bfloat162_rn(p0, p1);
             sum += __bfloat162float(pb.x) + __bfloat162float(pb.y);  // normalise by what is really multiplied
             pk[j] = *reinterpret_cast<const uint32_t*>(&pb);
@@ -148,13 +162,26 @@ __global__ void __launch_bounds__(EA_THREADS) enc_attention_kernel(const EncAttn
         unsigned char* pblk = smem + EA_P_OFF + (c >> 6) * 16384;
 #pragma unroll
         for (int i = 0; i < 4; i++)
-            *reinterpret_cast<uint4*>(pblk + sw128_off(tid, ((c & 63) >> 3) + i)) =
+            *reinterpret_cast<uint4*>(pblk + sw128_off(row, ((c & 63) >> 3) + i)) =
                 make_uint4(pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);
+    };
+#pragma unroll 1
+    for (int ch = 0; ch < nch; ch += 2) {
+        tmem_ld_wait();
+        if (ch + 1 < nch) tmem_ld_32x32(lane_addr + c_lo + (ch + 1) * 32, r[1]);
+        exp32(r[0], c_lo + ch * 32);
+        if (ch + 1 < nch) {
+            tmem_ld_wait();
+            if (ch + 2 < nch) tmem_ld_32x32(lane_addr + c_lo + (ch + 2) * 32, r[0]);
+            exp32(r[1], c_lo + (ch + 1) * 32);
+        }
     }
+    red_sum[half * 128 + row] = sum;
     fence_proxy_async_smem();
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
+    sum += red_sum[(half ^ 1) * 128 + row];
 
     // ---- 4. O = P V ----
     if (warp == 0) {
@@ -173,21 +200,22 @@ __global__ void __launch_bounds__(EA_THREADS) enc_attention_kernel(const EncAttn
     mbar_wait(&bars[1], 0);
     tc_fence_after();
 
-    // ---- 5. normalise and store ----
-    tmem_ld_32x32(lane_addr, r);
+    // ---- 5. normalise and store: this thread writes dims [16 * half, +16) of its row ----
+    uint32_t ro[16];
+    tmem_ld_32x16(lane_addr + half * 16, ro);
     tmem_ld_wait();
-    const int q = mt * 128 + tid;
+    const int q = mt * 128 + row;
     if (q < T) {
         const float inv = 1.0f / sum;
-        uint32_t o[16];
+        uint32_t o[8];
 #pragma unroll
-        for (int j = 0; j < 16; j++) {
-            const __nv_bfloat162 ob = __floats2bfloat162_rn(__uint_as_float(r[2 * j]) * inv, __uint_as_float(r[2 * j + 1]) * inv);
+        for (int j = 0; j < 8; j++) {
+            const __nv_bfloat162 ob = __floats2bfloat162_rn(__uint_as_float(ro[2 * j]) * inv, __uint_as_float(ro[2 * j + 1]) * inv);
             o[j] = *reinterpret_cast<const uint32_t*>(&ob);
         }
-        uint4* dst = reinterpret_cast<uint4*>(p.ctx + (size_t)(row0 + q) * p.H + h * EA_DH);
-#pragma unroll
-        for (int i = 0; i < 4; i++) dst[i] = make_uint4(o[4 * i], o[4 * i + 1], o[4 * i + 2], o[4 * i + 3]);
+        uint4* dst = reinterpret_cast<uint4*>(p.ctx + (size_t)(row0 + q) * p.H + h * EA_DH + half * 16);
+        dst[0] = make_uint4(o[0], o[1], o[2], o[3]);
+        dst[1] = make_uint4(o[4], o[5], o[6], o[7]);
     }
     tc_fence_before();
     __syncthreads();
