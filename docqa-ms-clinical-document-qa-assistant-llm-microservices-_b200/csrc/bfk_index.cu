@@ -145,7 +145,8 @@ static int make_index(int d, int metric, int device, int storage, bfk_index** ou
     if (cudaMalloc((void**)&idx->maxn, sizeof(unsigned int)) != cudaSuccess ||
         cudaMemset(idx->maxn, 0, sizeof(unsigned int)) != cudaSuccess ||
         cudaEventCreateWithFlags(&idx->ws_free, cudaEventDisableTiming) != cudaSuccess ||
-        cudaHostAlloc((void**)&idx->h_flag, sizeof(int), cudaHostAllocDefault) != cudaSuccess) {
+        cudaHostAlloc((void**)&idx->h_flag, sizeof(int), cudaHostAllocMapped) != cudaSuccess ||
+        cudaHostGetDevicePointer((void**)&idx->h_flag_dev, idx->h_flag, 0) != cudaSuccess) {
         delete idx;
         return fail(std::string("index allocation failed: ") + cudaGetErrorString(cudaGetLastError()));
     }
@@ -500,9 +501,15 @@ static int search_locked(bfk_index* idx, const float* q, int64_t nq, int k, floa
     char* tail = ws.take<char>(256);
     size_t tail_avail = idx->ws.bytes - (size_t)(tail - (char*)idx->ws.ptr);
 
-    if (ldq != idx->d) BFK_CUDA(cudaMemsetAsync(q_dev, 0, sizeof(float) * (size_t)nq * ldq, st));
-    BFK_CUDA(cudaMemcpy2DAsync(q_dev, sizeof(float) * ldq, q, sizeof(float) * idx->d, sizeof(float) * idx->d,
-                               (size_t)nq, io_is_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, st));
+    if (io_is_device && ldq == idx->d && !defer && (reinterpret_cast<uintptr_t>(q) & 15u) == 0) {
+        // device queries whose row stride already is the padded one: read them in place (a deferred search
+        // keeps its own copy, its retry may run after the caller has let go of the buffer)
+        q_dev = const_cast<float*>(q);
+    } else {
+        if (ldq != idx->d) BFK_CUDA(cudaMemsetAsync(q_dev, 0, sizeof(float) * (size_t)nq * ldq, st));
+        BFK_CUDA(cudaMemcpy2DAsync(q_dev, sizeof(float) * ldq, q, sizeof(float) * idx->d, sizeof(float) * idx->d,
+                                   (size_t)nq, io_is_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, st));
+    }
     float* D_out = io_is_device ? D : D_dev;
     int64_t* I_out = io_is_device ? I : I_dev;
 

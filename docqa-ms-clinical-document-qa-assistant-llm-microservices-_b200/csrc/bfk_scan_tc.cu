@@ -515,9 +515,14 @@ __global__ void __launch_bounds__(256) prep_queries_kernel(const float* __restri
                                                            int64_t nq_pad, __nv_bfloat16* __restrict__ q16, int ld16,
                                                            float* __restrict__ qn, const unsigned int* __restrict__ maxn,
                                                            float c_round, int is_l2, float* __restrict__ qmargin,
-                                                           unsigned int* __restrict__ slots, int NS) {
+                                                           unsigned int* __restrict__ slots, int NS,
+                                                           int* __restrict__ flags) {
     const int lane = threadIdx.x & 31;
     const int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        flags[0] = 0;  // uncertified-query count of this pass (K5 appends)
+        flags[-1] = 0; // K5's CTA ticket (the last CTA to finish publishes the count to the host)
+    }
     if (row >= nq_pad) return;
     float ss = 0.f;
     for (int c = lane; c < ld16; c += 32) {
@@ -555,8 +560,9 @@ struct RerankParams {
     int64_t id_offset;
     float* D;                  // [nq][k]
     int64_t* I;
-    int* nflag;
+    int* nflag;       // [-1] = CTA ticket, [0] = count, [1..] = list
     int* flag_list;
+    int* h_nflag;     // pinned host word (device-mapped): the count, written by the last CTA
 };
 
 __device__ void rr_bitonic(uint64_t* a, int n, int tid, int nthr) {
@@ -703,6 +709,15 @@ __global__ void __launch_bounds__(RR_THREADS) rerank_kernel(const RerankParams p
     if (tid == 0 && !info[1]) {
         const int slot = atomicAdd(p.nflag, 1);
         p.flag_list[slot] = (int)q;
+    }
+    // the last CTA to get here hands the count to the host without a separate D2H copy
+    if (tid == 0) {
+        __threadfence();
+        if (atomicAdd(p.nflag - 1, 1) == (int)gridDim.x - 1) {
+            __threadfence();
+            *reinterpret_cast<volatile int*>(p.h_nflag) = *reinterpret_cast<volatile int*>(p.nflag);
+            __threadfence_system();
+        }
     }
 }
 
@@ -871,7 +886,7 @@ static void tc_carve(const bfk_index* idx, int64_t nqc, int k, int fb_nparts, ch
     w->qmargin = (float*)take((size_t)nq_pad * 4);
     w->out_cand = (uint64_t*)take(max_lists * 32 * 8);
     w->out_thr = (float*)take(max_lists * 4);
-    w->flags = (int*)take((size_t)(nqc + 1) * 4);
+    w->flags = (int*)take((size_t)(nqc + 2) * 4) + 1;  // [-1] ticket, [0] count, [1..] list
     w->fb_q = (float*)take((size_t)8 * idx->ld32 * 4);
     w->fb_D = (float*)take((size_t)8 * k * 4);
     w->fb_I = (int64_t*)take((size_t)8 * k * 8);
@@ -1006,13 +1021,12 @@ static int tc_pass(bfk_index* idx, const float* qc, int ldq, int64_t nqc, int k,
             pl = single;
         }
     }
-    BFK_CUDA(cudaMemsetAsync(w.flags, 0, sizeof(int), st));
     // |<q,x> - <bf16(q),bf16(x)>| <= (2u + u^2) ||q|| ||x|| with u = 2^-9 when both operands are
     // rounded, u ||q|| ||x|| when the corpus is stored in bf16; + 2^-14 for tensor-core accumulation
     const float c_round = (idx->storage == BFK_STORE_F32 ? 1.01f / 256.f : 1.01f / 512.f) + 1.0f / 16384.f;
     prep_queries_kernel<<<(unsigned)((pl.nq_pad + 7) / 8), 256, 0, st>>>(qc, ldq, idx->d, nqc, pl.nq_pad, w.q16, idx->ld16,
                                                                         w.qn, idx->maxn, c_round, l2 ? 1 : 0, w.qmargin,
-                                                                        w.slots, pl.NS);
+                                                                        w.slots, pl.NS, w.flags);
     BFK_CUDA(cudaGetLastError());
     CUtensorMap tmQ, tmX;
     BFK_TRY(make_tmap(&tmQ, w.q16, pl.nq_pad, idx->ld16, TC_BM));
@@ -1106,6 +1120,7 @@ static int tc_pass(bfk_index* idx, const float* qc, int ldq, int64_t nqc, int k,
     r.I = I_out;
     r.nflag = w.flags;
     r.flag_list = w.flags + 1;
+    r.h_nflag = idx->h_flag_dev;
     rerank_kernel<<<(unsigned)nqc, RR_THREADS, 0, st>>>(r);
     BFK_CUDA(cudaGetLastError());
     *launches += 3;
@@ -1132,7 +1147,6 @@ struct TcPending {
 static int tc_resolve(bfk_index* idx, const TcPending& c, cudaStream_t st, int64_t* n_retry, int64_t* n_fallback,
                       int64_t* n_rewritten, int* launches) {
     const TcWs& w = c.w;
-    BFK_CUDA(cudaMemcpyAsync(idx->h_flag, w.flags, sizeof(int), cudaMemcpyDeviceToHost, st));
     BFK_CUDA(cudaStreamSynchronize(st));
     int nflag = *idx->h_flag;
     if (n_rewritten) *n_rewritten += nflag;
@@ -1155,7 +1169,6 @@ static int tc_resolve(bfk_index* idx, const TcPending& c, cudaStream_t st, int64
             w.r_D, w.r_I, w.r_list, nflag, c.k, c.Dc, c.Ic);
         BFK_CUDA(cudaGetLastError());
         *launches += 2;
-        BFK_CUDA(cudaMemcpyAsync(idx->h_flag, w.flags, sizeof(int), cudaMemcpyDeviceToHost, st));
         BFK_CUDA(cudaStreamSynchronize(st));
         const int nflag2 = *idx->h_flag;
         std::vector<int> list2((size_t)nflag2);

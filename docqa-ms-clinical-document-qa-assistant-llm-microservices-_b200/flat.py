@@ -89,7 +89,10 @@ class IndexFlat:
 
     @property
     def device(self) -> int:
-        return int(self._L.bfk_device(self._h))
+        dev = self.__dict__.get("_device")
+        if dev is None:
+            dev = self.__dict__["_device"] = int(self._L.bfk_device(self._h))
+        return dev
 
     @property
     def storage(self) -> str:
