@@ -133,8 +133,8 @@ def _roofline_core(res, nq, n_rows, elem, hbm_peak, tf_peak, peak_kind):
         bytes_launch = n_rows * D * 2 + (n_rows * 4 if METRIC_ID == 1 else 0) + nq * D * 2 + nq * 148 * 16 * 12
         ach = bytes_launch / (launch_ms * 1e-3) / 1e9 if launch_ms > 0 else 0.0
         # DRAM bytes per launch from the one `ncu --set full` capture of this exact shape
-        # (profiles/r01_ncu_scan_tc_final_nq64.txt: dram read 772.31 MB + write 3.84 MB)
-        traffic = 776.15e6 if (n_rows == 1_000_000 and D == 384 and nq == 64 and METRIC_ID == 1) else None
+        # (profiles/r01_ncu_scan_tc_final_nq64.txt: dram read 772.29 MB + write 4.24 MB)
+        traffic = 776.53e6 if (n_rows == 1_000_000 and D == 384 and nq == 64 and METRIC_ID == 1) else None
         r = {"bound": "hbm", "kernel": "scan_tc_kernel", "achieved": ach, "peak": hbm_peak, "unit": "GB/s",
              "frac": ach / hbm_peak, "peak_kind": peak_kind, "bytes_per_launch": bytes_launch,
              "launch_ms": launch_ms, "launches_per_step": 1, "traffic": traffic}
@@ -195,6 +195,31 @@ def run_c4(args):
             del index
         del bufs
         torch.cuda.empty_cache()
+    # K2: index.add of fp32 rows already on the device (indexer.py:41 at scale): 4d bytes in, fp32 master row +
+    # bf16 scan row + norm out
+    rows_n = 4_000_000
+    g = torch.Generator(device=dev).manual_seed(CORPUS_SEED)
+    xb = torch.randn((rows_n, H), generator=g, device=dev, dtype=torch.float32)
+    for storage in ("f32", "bf16"):
+        index = bfk.IndexFlatL2(H, device=0, storage=storage)
+        reps = 6
+        index.reserve(rows_n * (reps + 2))
+        index.add(xb)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            index.add(xb)
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / reps
+        bytes_row = H * 4 + (H * 4 if storage == "f32" else 0) + H * 2 + 4
+        ach = bytes_row * rows_n / (ms * 1e-3) / 1e9
+        out[f"add_rows_{storage}"] = {"rows_per_s": rows_n / (ms * 1e-3), "ms_per_launch": ms, "bytes_per_row": bytes_row,
+                                      "achieved_gbs": ach, "frac": ach / hbm_peak, "kernel": "append_rows_kernel"}
+        del index
+    del xb
+    torch.cuda.empty_cache()
     head = out["bf16_full"]
     line = {
         "metric": "ingestion chunks/sec (pool+normalise+cast+add)", "value": head["chunks_per_s"], "unit": "chunks/s",
