@@ -465,10 +465,12 @@ static int search_locked(bfk_index* idx, const float* q, int64_t nq, int k, floa
     BFK_TRY(search_tensor_finish(idx, st, nullptr));  // a deferred search nobody settled: settle it first
 
     if (algo == BFK_ALGO_AUTO) {
-        // fp32 rows: up to 8 queries the exact scan is one HBM-speed pass; bf16-stored rows scan faster
-        // through the tensor path at any batch size
-        algo = ((nq > 8 || idx->storage == BFK_STORE_BF16) && tensor_path_supported(idx, nq, k)) ? BFK_ALGO_TENSOR
-                                                                                                  : BFK_ALGO_EXACT_SIMT;
+        // The tensor path wins at every batch size, one query included: it streams the bf16 scan copy (half the
+        // bytes of the fp32 rows: nq=1 0.168 ms against 0.248 ms, nq=8 0.171 against 0.457 on 1M x 384) and its
+        // answers are re-scored in fp32 and certified exact.  The fp32 scan remains the explicit
+        // BFK_ALGO_EXACT_SIMT, the fallback for uncertified queries, and the path for shapes the tensor path
+        // does not take (k > 128).
+        algo = tensor_path_supported(idx, nq, k) ? BFK_ALGO_TENSOR : BFK_ALGO_EXACT_SIMT;
     } else if (algo == BFK_ALGO_TENSOR) {
         if (!tensor_path_supported(idx, nq, k)) return fail("search: tensor path does not support this shape");
     } else if (algo != BFK_ALGO_EXACT_SIMT) {

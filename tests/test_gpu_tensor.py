@@ -139,7 +139,14 @@ def test_tensor_path_limits_and_auto_dispatch(bfk):
     check_knn(D, I, xq, xb, 200, L2, tight=True)
     D, I = idx.search(xq, 10, stats=st)
     assert st.algo_used == bfk.ALGO_TENSOR
+    # small batches too: the bf16 scan copy is half the bytes of the fp32 rows and the answers are certified
     D, I = idx.search(xq[:8], 10, stats=st)
+    assert st.algo_used == bfk.ALGO_TENSOR
+    check_knn(D, I, xq[:8], xb, 10, L2, tight=True)
+    D, I = idx.search(xq[:1], 10, stats=st)
+    assert st.algo_used == bfk.ALGO_TENSOR
+    check_knn(D, I, xq[:1], xb, 10, L2, tight=True)
+    D, I = idx.search(xq[:8], 10, stats=st, algo="exact")
     assert st.algo_used == bfk.ALGO_EXACT_SIMT
 
 
