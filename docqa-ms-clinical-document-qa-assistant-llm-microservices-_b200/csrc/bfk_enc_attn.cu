@@ -14,6 +14,8 @@
 //   4. O = P V : T/64 K-blocks x 4 tcgen05.mma (M=128, N=32, K=16) into the first 32 TMEM columns;
 //   5. O / rowsum -> bf16 context rows.
 // 256 TMEM columns and ~82 KB of shared memory per CTA: two CTAs per SM overlap each other's phases.
+#include <cstdlib>
+
 #include "bfk_common.cuh"
 #include "bfk_ptx.cuh"
 
@@ -225,6 +227,223 @@ __global__ void __launch_bounds__(EA_THREADS) enc_attention_kernel(const EncAttn
     }
 }
 
+// ---- E3b: the same attention in 64-key blocks, four to five CTAs per SM -----------------------------------
+// enc_attention_kernel above keeps a whole 128 x T score tile in TMEM (256 columns): two CTAs per SM, each one
+// serial latency chain (ncu: 24 % of the warps active, 465 us per layer).  This variant needs 128 TMEM columns
+// and 45 KB of shared memory per CTA, so four or five chains overlap on an SM:
+//   pass 1  S = Q K^T in 128-key pieces (columns 0..127) only to find the row maximum;
+//   pass 2  per 64-key block j: S_j recomputed into columns 0..63 (two MMAs -- cheaper than keeping it),
+//           p = exp2(s - max) in the row's thread, P_j (bf16) and V_j^T staged in shared memory,
+//           O (+)= P_j V_j into columns 64..95.  The softmax is the exact two-pass one, no rescaling.
+// Q and K use the 64-byte swizzle (their rows are 64 bytes: head dimension 32), P and V^T the 128-byte one.
+constexpr int EB_THREADS = 128;
+constexpr int EB_Q_OFF = 0;                 // [128 x 64 B]            8 KiB
+constexpr int EB_K_OFF = 8 * 1024;          // [T x 64 B]          <= 16 KiB
+constexpr int EB_V_OFF = 24 * 1024;         // [32 dims x 128 B]       4 KiB (one 64-token block)
+constexpr int EB_P_OFF = 28 * 1024;         // [128 x 128 B]          16 KiB (one 64-key block)
+constexpr int EB_MB_OFF = 44 * 1024;        // [256] fp32 mask bias
+constexpr int EB_BAR_OFF = EB_MB_OFF + EA_MAXT * 4;
+constexpr int EB_SMEM = EB_BAR_OFF + 64 + 1024 /*alignment*/;
+
+// byte offset of 16-byte chunk `c` (0..3) of row `r` inside a [rows x 64 B] tile, 64-byte swizzle
+__device__ __forceinline__ uint32_t sw64_off(int r, int c) {
+    return (uint32_t)((r >> 3) * 512 + (r & 7) * 64 + ((c ^ ((r >> 1) & 3)) << 4));
+}
+// K-major operand descriptor, 64-byte swizzle: 8-row groups 512 bytes apart
+__device__ __forceinline__ uint64_t make_smem_desc_sw64(uint32_t smem_addr_bytes) {
+    uint64_t d = 0;
+    d |= (uint64_t)((smem_addr_bytes & 0x3ffffu) >> 4);
+    d |= (uint64_t)1 << 16;
+    d |= (uint64_t)(512u >> 4) << 32;
+    d |= (uint64_t)1 << 46;
+    d |= (uint64_t)4 << 61;
+    return d;
+}
+
+__global__ void __launch_bounds__(EB_THREADS) enc_attention_blk_kernel(const EncAttnParams p) {
+    extern __shared__ __align__(1024) unsigned char smem_raw[];
+    const uint32_t raw = smem_u32(smem_raw);
+    unsigned char* smem = smem_raw + ((1024u - (raw & 1023u)) & 1023u);
+    float* mb = reinterpret_cast<float*>(smem + EB_MB_OFF);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + EB_BAR_OFF);  // [0] scores ready, [1] O block accumulated
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2);
+
+    const int tid = threadIdx.x, warp = tid >> 5;
+    const int mt = blockIdx.x, h = blockIdx.y;
+    const int64_t b = blockIdx.z;
+    const int T = p.T, ld = 3 * p.H, NB = T >> 6;
+    const int64_t row0 = b * T;
+
+    if (tid == 0) {
+        mbar_init(&bars[0], 1);
+        mbar_init(&bars[1], 1);
+        fence_mbar_init();
+    }
+    if (warp == 0) tmem_alloc<128>(tmem_slot);
+
+    // ---- stage Q (this thread's row), K (all T rows) and the mask bias ----
+    {
+        const int q = mt * 128 + tid;
+        uint4 v[4] = {make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0)};
+        if (q < T) {
+            const uint4* src = reinterpret_cast<const uint4*>(p.qkv + (size_t)(row0 + q) * ld + h * EA_DH);
+#pragma unroll
+            for (int c = 0; c < 4; c++) v[c] = __ldg(src + c);
+        }
+#pragma unroll
+        for (int c = 0; c < 4; c++) *reinterpret_cast<uint4*>(smem + EB_Q_OFF + sw64_off(tid, c)) = v[c];
+    }
+    for (int t = tid; t < T; t += EB_THREADS) {
+        const uint4* ksrc = reinterpret_cast<const uint4*>(p.qkv + (size_t)(row0 + t) * ld + p.H + h * EA_DH);
+        uint4 kv[4];
+#pragma unroll
+        for (int c = 0; c < 4; c++) kv[c] = __ldg(ksrc + c);
+#pragma unroll
+        for (int c = 0; c < 4; c++) *reinterpret_cast<uint4*>(smem + EB_K_OFF + sw64_off(t, c)) = kv[c];
+        mb[t] = p.mask_bias[row0 + t];
+    }
+    fence_proxy_async_smem();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(tmem_slot);
+    const uint32_t lane_addr = tmem_base + ((uint32_t)(warp * 32) << 16);
+    const uint64_t dq = make_smem_desc_sw64(smem_u32(smem + EB_Q_OFF));
+    uint32_t ph_s = 0, ph_o = 0;  // phases of bars[0] / bars[1]
+    uint32_t r[2][32];
+
+    // ---- pass 1: row maximum over all keys, 128 keys at a time ----
+    float mx = -INFINITY;
+    for (int k0 = 0; k0 < T; k0 += 128) {
+        const int n1 = min(128, T - k0);
+        if (warp == 0) {
+            if (elect_one()) {
+                const uint32_t idesc = make_idesc_bf16(128, n1);
+                const uint64_t dk = make_smem_desc_sw64(smem_u32(smem + EB_K_OFF + k0 * 64));
+#pragma unroll
+                for (int kk = 0; kk < EA_DH / 16; kk++) umma_bf16(tmem_base, dq + 2 * kk, dk + 2 * kk, idesc, kk != 0 ? 1u : 0u);
+                umma_commit(&bars[0]);
+            }
+            __syncwarp();
+        }
+        mbar_wait(&bars[0], ph_s);
+        ph_s ^= 1u;
+        tc_fence_after();
+        tmem_ld_32x32(lane_addr, r[0]);
+        for (int c = 0; c < n1; c += 64) {
+            tmem_ld_wait();
+            tmem_ld_32x32(lane_addr + c + 32, r[1]);
+#pragma unroll
+            for (int j = 0; j < 32; j++) mx = fmaxf(mx, fmaf(__uint_as_float(r[0][j]), p.scale_log2, mb[k0 + c + j]));
+            tmem_ld_wait();
+            if (c + 64 < n1) tmem_ld_32x32(lane_addr + c + 64, r[0]);
+#pragma unroll
+            for (int j = 0; j < 32; j++) mx = fmaxf(mx, fmaf(__uint_as_float(r[1][j]), p.scale_log2, mb[k0 + c + 32 + j]));
+        }
+        tc_fence_before();
+        __syncthreads();  // every row has read this piece before the next MMA overwrites the columns
+        tc_fence_after();
+    }
+
+    // ---- pass 2: per 64-key block, p = exp2(s - max), O += P_j V_j ----
+    float sum = 0.f;
+    const uint32_t idesc_s = make_idesc_bf16(128, 64), idesc_o = make_idesc_bf16(128, EA_DH);
+    const int tt = tid >> 1, hf = tid & 1;  // V staging: token of the block, 16-dim half
+    unsigned char* Pb = smem + EB_P_OFF;
+    unsigned char* Vb = smem + EB_V_OFF;
+    for (int j = 0; j < NB; j++) {
+        if (warp == 0) {
+            if (elect_one()) {
+                const uint64_t dk = make_smem_desc_sw64(smem_u32(smem + EB_K_OFF + j * 64 * 64));
+#pragma unroll
+                for (int kk = 0; kk < EA_DH / 16; kk++) umma_bf16(tmem_base, dq + 2 * kk, dk + 2 * kk, idesc_s, kk != 0 ? 1u : 0u);
+                umma_commit(&bars[0]);
+            }
+            __syncwarp();
+        }
+        // this block's V rows travel to registers while the MMA runs
+        const uint4* vsrc =
+            reinterpret_cast<const uint4*>(p.qkv + (size_t)(row0 + j * 64 + tt) * ld + 2 * p.H + h * EA_DH + hf * 16);
+        uint4 vv[2];
+        vv[0] = __ldg(vsrc);
+        vv[1] = __ldg(vsrc + 1);
+        mbar_wait(&bars[0], ph_s);
+        ph_s ^= 1u;
+        tc_fence_after();
+        tmem_ld_32x32(lane_addr, r[0]);
+        tmem_ld_32x32(lane_addr + 32, r[1]);
+        tmem_ld_wait();
+        // P and V^T of the previous block are free once its P V product has completed
+        if (j > 0) {
+            mbar_wait(&bars[1], ph_o);
+            ph_o ^= 1u;
+        }
+#pragma unroll
+        for (int hh = 0; hh < 2; hh++) {
+            uint32_t pk[16];
+#pragma unroll
+            for (int jj = 0; jj < 16; jj++) {
+                const int c = j * 64 + hh * 32 + 2 * jj;
+                const float p0 = exp2f(fmaf(__uint_as_float(r[hh][2 * jj]), p.scale_log2, mb[c]) - mx);
+                const float p1 = exp2f(fmaf(__uint_as_float(r[hh][2 * jj + 1]), p.scale_log2, mb[c + 1]) - mx);
+                const __nv_bfloat162 pb = __floats2bfloat162_rn(p0, p1);
+                sum += __bfloat162float(pb.x) + __bfloat162float(pb.y);  // normalise by what is really multiplied
+                pk[jj] = *reinterpret_cast<const uint32_t*>(&pb);
+            }
+#pragma unroll
+            for (int i = 0; i < 4; i++)
+                *reinterpret_cast<uint4*>(Pb + sw128_off(tid, hh * 4 + i)) = make_uint4(pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);
+        }
+        {
+            const unsigned short* ve = reinterpret_cast<const unsigned short*>(vv);
+#pragma unroll
+            for (int e = 0; e < 16; e++)
+                *reinterpret_cast<unsigned short*>(Vb + sw128_off(hf * 16 + e, tt >> 3) + (tt & 7) * 2) = ve[e];
+        }
+        fence_proxy_async_smem();
+        tc_fence_before();
+        __syncthreads();
+        tc_fence_after();
+        if (warp == 0) {
+            if (elect_one()) {
+                const uint64_t dp = make_smem_desc_sw128(smem_u32(Pb));
+                const uint64_t dv = make_smem_desc_sw128(smem_u32(Vb));
+#pragma unroll
+                for (int kk = 0; kk < 4; kk++) umma_bf16(tmem_base + 64, dp + 2 * kk, dv + 2 * kk, idesc_o, (j | kk) != 0 ? 1u : 0u);
+                umma_commit(&bars[1]);
+            }
+            __syncwarp();
+        }
+    }
+    mbar_wait(&bars[1], ph_o);
+    tc_fence_after();
+
+    // ---- normalise and store ----
+    tmem_ld_32x32(lane_addr + 64, r[0]);
+    tmem_ld_wait();
+    const int q = mt * 128 + tid;
+    if (q < T) {
+        const float inv = 1.0f / sum;
+        uint32_t o[16];
+#pragma unroll
+        for (int jj = 0; jj < 16; jj++) {
+            const __nv_bfloat162 ob =
+                __floats2bfloat162_rn(__uint_as_float(r[0][2 * jj]) * inv, __uint_as_float(r[0][2 * jj + 1]) * inv);
+            o[jj] = *reinterpret_cast<const uint32_t*>(&ob);
+        }
+        uint4* dst = reinterpret_cast<uint4*>(p.ctx + (size_t)(row0 + q) * p.H + h * EA_DH);
+#pragma unroll
+        for (int i = 0; i < 4; i++) dst[i] = make_uint4(o[4 * i], o[4 * i + 1], o[4 * i + 2], o[4 * i + 3]);
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) {
+        tc_fence_after();
+        tmem_dealloc<128>(tmem_base);
+    }
+}
+
+
 int launch_enc_attention(const __nv_bfloat16* qkv, const float* mask_bias, __nv_bfloat16* ctx, int64_t B, int T, int H,
                          int heads, cudaStream_t st) {
     if (B <= 0) return 0;
@@ -232,10 +451,15 @@ int launch_enc_attention(const __nv_bfloat16* qkv, const float* mask_bias, __nv_
     if (T <= 0 || T > EA_MAXT || (T & 63)) return fail("encoder attention: sequence length must be a multiple of 64, <= 256");
     if (B > 65535) return fail("encoder attention: more than 65535 chunks per launch");
     static bool attr_set[64] = {false};
+    static const bool whole_row = [] {  // BFK_ENC_ATTN=row: the first version (whole score row in TMEM)
+        const char* e = getenv("BFK_ENC_ATTN");
+        return e && e[0] == 'r';
+    }();
     int dev = 0;
     BFK_CUDA(cudaGetDevice(&dev));
     if (dev < 0 || dev >= 64 || !attr_set[dev]) {
         BFK_CUDA(cudaFuncSetAttribute(enc_attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, EA_SMEM));
+        BFK_CUDA(cudaFuncSetAttribute(enc_attention_blk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, EB_SMEM));
         if (dev >= 0 && dev < 64) attr_set[dev] = true;
     }
     EncAttnParams p;
@@ -246,7 +470,8 @@ int launch_enc_attention(const __nv_bfloat16* qkv, const float* mask_bias, __nv_
     p.H = H;
     p.scale_log2 = 1.4426950408889634f / sqrtf((float)EA_DH);
     dim3 grid((unsigned)((T + 127) / 128), (unsigned)heads, (unsigned)B);
-    enc_attention_kernel<<<grid, EA_THREADS, EA_SMEM, st>>>(p);
+    if (whole_row) enc_attention_kernel<<<grid, EA_THREADS, EA_SMEM, st>>>(p);
+    else enc_attention_blk_kernel<<<grid, EB_THREADS, EB_SMEM, st>>>(p);
     BFK_CUDA(cudaGetLastError());
     return 0;
 }
