@@ -242,16 +242,23 @@ enc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
             }
             __syncwarp();
         };
-        // the mirror image for the residual rows: a coalesced read of 32 rows x 64 bytes, then every lane picks
-        // up its own row (thread-per-row global reads were the LayerNorm epilogue's long-scoreboard stalls)
-        auto load32 = [&](const __nv_bfloat16* src_col0, int64_t m_tile0, uint4 (&rr)[4]) {
+        // the mirror image for the residual rows: a coalesced read of 32 rows x 64 bytes (res_fetch, issued one
+        // chunk ahead so its latency hides under the previous chunk's arithmetic), then every lane picks up its
+        // own row through the staging buffer (res_stage).  Thread-per-row global reads were the LayerNorm
+        // epilogue's long-scoreboard stalls.
+        auto res_fetch = [&](const __nv_bfloat16* src_col0, int64_t m_tile0, uint4 (&g)[4]) {
 #pragma unroll
             for (int k8 = 0; k8 < 4; k8++) {
                 const int r8 = (lane >> 2) + 8 * k8, c = lane & 3;
                 const int64_t mm = m_tile0 + wrow0 + r8;
-                const uint4 v = mm < p.M ? __ldg(reinterpret_cast<const uint4*>(src_col0 + (size_t)mm * BN + c * 8))
-                                         : make_uint4(0, 0, 0, 0);
-                *reinterpret_cast<uint4*>(stg + r8 * 64 + ((c ^ ((r8 >> 1) & 3)) << 4)) = v;
+                g[k8] = mm < p.M ? __ldg(reinterpret_cast<const uint4*>(src_col0 + (size_t)mm * BN + c * 8)) : make_uint4(0, 0, 0, 0);
+            }
+        };
+        auto res_stage = [&](const uint4 (&g)[4], uint4 (&rr)[4]) {
+#pragma unroll
+            for (int k8 = 0; k8 < 4; k8++) {
+                const int r8 = (lane >> 2) + 8 * k8, c = lane & 3;
+                *reinterpret_cast<uint4*>(stg + r8 * 64 + ((c ^ ((r8 >> 1) & 3)) << 4)) = g[k8];
             }
             __syncwarp();
 #pragma unroll
@@ -272,10 +279,13 @@ enc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                 const __nv_bfloat16* res0 = p.residual + half * HC;  // first residual column of this thread
                 const float* bias = par_s + half * HC;
                 float s1 = 0.f, s2 = 0.f;
+                uint4 gres[4];  // residual chunk in flight
+                res_fetch(res0, (int64_t)mt * EG_BM, gres);
                 // one 32-column chunk of pass 1: v = acc + bias + residual, accumulate sum and sum of squares
                 auto stats32 = [&](const uint32_t (&rv)[32], int ch) {
                     uint4 rr[4];
-                    load32(res0 + ch * 32, (int64_t)mt * EG_BM, rr);
+                    res_stage(gres, rr);
+                    res_fetch(res0 + ((ch + 1) % NCH) * 32, (int64_t)mt * EG_BM, gres);  // wraps to pass 2's first chunk
                     const uint32_t* rw = reinterpret_cast<const uint32_t*>(rr);
 #pragma unroll
                     for (int j = 0; j < 16; j++) {
@@ -311,7 +321,8 @@ enc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                 const float* beta = par_s + 2 * BN + half * HC;
                 auto norm32 = [&](const uint32_t (&rv)[32], int ch) {
                     uint4 rr[4];
-                    load32(res0 + ch * 32, (int64_t)mt * EG_BM, rr);
+                    res_stage(gres, rr);
+                    if (ch + 1 < NCH) res_fetch(res0 + (ch + 1) * 32, (int64_t)mt * EG_BM, gres);
                     const uint32_t* rw = reinterpret_cast<const uint32_t*>(rr);
                     uint32_t o[16];
 #pragma unroll
