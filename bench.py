@@ -235,6 +235,53 @@ def run_c4(args):
     print(json.dumps(line))
 
 
+def run_c1(args):
+    """BASELINE config 1: the reference's own 649 x 384 index, one query per call, k = 5 (llm-qa/main.py:101,117).
+
+    Too small for a roofline ('parity + latency only'): the number is the wall-clock latency of one
+    `index.search(np.float32[1, 384], 5)` through the numpy API, host buffers in and out, next to the CPU
+    restatement of faiss on the same box.
+    """
+    import docqa_b200 as bfk
+    from oracle import cpu_baseline, faiss_io
+
+    here = os.path.dirname(os.path.abspath(__file__))
+    path = os.path.join(here, "tests", "golden", "docqa_vector_store.faiss")
+    index = bfk.read_index(path)
+    _, n, metric, xb = faiss_io.read_index_bytes(open(path, "rb").read())
+    rng = np.random.default_rng(QUERY_SEED)
+    q = xb[rng.integers(0, n, 2000)] + 0.05 * rng.standard_normal((2000, xb.shape[1])).astype(np.float32)
+    q /= np.linalg.norm(q, axis=1, keepdims=True)
+    for i in range(50):
+        index.search(q[i : i + 1], 5)
+    lat = []
+    for i in range(2000):
+        t0 = time.perf_counter()
+        index.search(q[i : i + 1], 5)
+        lat.append(time.perf_counter() - t0)
+    lat = np.sort(np.array(lat)) * 1e3
+    cpu_baseline.build()
+    cl = []
+    for i in range(300):
+        t0 = time.perf_counter()
+        cpu_baseline.knn_seq(q[i : i + 1], xb, 5, metric)
+        cl.append(time.perf_counter() - t0)
+    cl = np.sort(np.array(cl)) * 1e3
+    line = {
+        "metric": "single-query search latency at k=5 (semantic-indexer default_data)", "value": float(np.median(lat)),
+        "unit": "ms", "n_gpus": 1, "steps": 2000, "warmup": 50, "ms_per_step": float(np.median(lat)),
+        "higher_is_better": False, "scaling": "weak", "vs_baseline": None, "dtype": "bf16 scan + f32 rerank",
+        "data": "the reference's shipped vector_store.faiss (649 x 384)",
+        "config": {"workload": "c1: 649x384 fixture, IndexFlatL2, k=5, nq=1 per call, numpy in / numpy out"},
+        "latency_ms": {"p50": float(np.median(lat)), "p90": float(lat[int(0.9 * len(lat))]), "p99": float(lat[int(0.99 * len(lat))])},
+        "e2e": {"value": float(np.median(lat)), "unit": "ms", "h2d_bytes_per_step": 384 * 4, "d2h_bytes_per_step": 5 * 12},
+        "gpu_launches": 3 * 2000, "roofline": None,
+        "cpu_baseline": {"value": float(np.median(cl)), "unit": "ms", "cores": 1, "kind": "port",
+                         "sample": "300 single-query calls of the faiss restatement (seq path) on the same 649 rows"},
+    }
+    print(json.dumps(line))
+
+
 def run_c4e(args):
     """Config 4 as a real pipeline: token ids -> 6-layer encoder -> pool + normalise -> index.add.
 
@@ -336,8 +383,21 @@ def run_reference(args):
     xq /= np.linalg.norm(xq, axis=1, keepdims=True)
     bn = np.einsum("ij,ij->i", xb, xb, dtype=np.float32)
 
+    # a real faiss-cpu is preferred the day one is importable (none is in this image)
+    real = None
+    try:
+        import faiss as _faiss
+
+        if getattr(_faiss, "__version__", "bfk-1.0") != "bfk-1.0" and hasattr(_faiss, "omp_get_max_threads"):
+            real = _faiss.IndexFlatL2(D) if METRIC_ID == 1 else _faiss.IndexFlatIP(D)
+            real.add(xb)
+    except Exception:
+        real = None
+
     def step():
-        if args.nq < 20:
+        if real is not None:
+            real.search(xq, K)
+        elif args.nq < 20:
             cpu_baseline.knn_seq(xq, xb, K, METRIC_ID)
         else:
             cpu_baseline.knn_blas(xq, xb, K, METRIC_ID, bn=bn)
@@ -351,6 +411,9 @@ def run_reference(args):
     scale = n_sample / n_full  # brute force is linear in N
     qps = args.nq * args.steps / dt * scale
     cores = min(args.nq, cpu_baseline.num_threads()) if args.nq < 20 else cpu_baseline.num_threads()
+    kind, ref_kind = "port", "CPU restatement of faiss-cpu IndexFlatL2.search (faiss not installable here)"
+    if real is not None:
+        cores, kind, ref_kind = _faiss.omp_get_max_threads(), "reference", f"faiss-cpu {_faiss.__version__}"
     sample = (f"full workload: {n_sample}x{D} fp32 corpus, nq={args.nq}" if scale == 1.0 else
               f"1M-row slice of the {n_full}-row corpus, nq={args.nq}; value extrapolated linearly in N")
     line = {
@@ -359,8 +422,8 @@ def run_reference(args):
         "scaling": "strong" if args.gpus > 1 else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "impl": "reference",
         "config": {"workload": f"{workload}: {n_full}x{D} corpus, {'IndexFlatL2' if METRIC_ID == 1 else 'IndexFlatIP'}, k={K}, nq={args.nq}",
-                   "reference_kind": "CPU restatement of faiss-cpu IndexFlatL2.search (faiss not installable here)"},
-        "cpu_baseline": {"value": qps, "unit": "queries/s", "cores": cores, "kind": "port", "sample": sample},
+                   "reference_kind": ref_kind},
+        "cpu_baseline": {"value": qps, "unit": "queries/s", "cores": cores, "kind": kind, "sample": sample},
         "e2e": {"value": qps, "unit": "queries/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line))
@@ -372,7 +435,7 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--nq", type=int, default=None)
-    ap.add_argument("--workload", choices=["c2", "c3", "c5", "c4", "c4e"], default=None)
+    ap.add_argument("--workload", choices=["c1", "c2", "c3", "c5", "c4", "c4e"], default=None)
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--rows", type=int, default=None, help="override corpus rows (debugging)")
     ap.add_argument("--algo", default=None, choices=[None, "auto", "exact", "tensor"])
@@ -390,6 +453,8 @@ def main():
     args.nq = args.nq or 64
     if args.impl == "reference":
         return run_reference(args)
+    if args.workload == "c1":
+        return run_c1(args)
     if args.workload == "c4":
         return run_c4(args)
     if args.workload == "c4e":

@@ -471,6 +471,13 @@ static int search_locked(bfk_index* idx, const float* q, int64_t nq, int k, floa
         // BFK_ALGO_EXACT_SIMT, the fallback for uncertified queries, and the path for shapes the tensor path
         // does not take (k > 128).
         algo = tensor_path_supported(idx, nq, k) ? BFK_ALGO_TENSOR : BFK_ALGO_EXACT_SIMT;
+        // ...except for a handful of queries over a small fp32 corpus, where the tensor path's fixed cost (one more
+        // launch, tensor maps, the certificate read-back: ~45 us against ~10) outweighs the bytes it saves.  The
+        // reference's own index (649 x 384) answers in 53 us through the fp32 scan, 97 us through the tensor path;
+        // the two meet near 250 k rows at d = 384 for one or two queries, earlier once the fp32 scan turns FMA-bound.
+        if (algo == BFK_ALGO_TENSOR && idx->storage == BFK_STORE_F32 && nq <= 8 &&
+            idx->ntotal * (int64_t)idx->d <= (nq <= 2 ? (int64_t)64 << 20 : (int64_t)24 << 20))
+            algo = BFK_ALGO_EXACT_SIMT;
     } else if (algo == BFK_ALGO_TENSOR) {
         if (!tensor_path_supported(idx, nq, k)) return fail("search: tensor path does not support this shape");
     } else if (algo != BFK_ALGO_EXACT_SIMT) {

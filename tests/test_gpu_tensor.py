@@ -139,13 +139,23 @@ def test_tensor_path_limits_and_auto_dispatch(bfk):
     check_knn(D, I, xq, xb, 200, L2, tight=True)
     D, I = idx.search(xq, 10, stats=st)
     assert st.algo_used == bfk.ALGO_TENSOR
-    # small batches too: the bf16 scan copy is half the bytes of the fp32 rows and the answers are certified
+    # a handful of queries over a small fp32 corpus: the fp32 scan's lower fixed cost wins
     D, I = idx.search(xq[:8], 10, stats=st)
-    assert st.algo_used == bfk.ALGO_TENSOR
+    assert st.algo_used == bfk.ALGO_EXACT_SIMT
     check_knn(D, I, xq[:8], xb, 10, L2, tight=True)
-    D, I = idx.search(xq[:1], 10, stats=st)
+    # over a large one the bf16 scan copy is half the bytes and the answers are certified: tensor path, even for nq = 1
+    big = unit(rng, 180_000, 384)
+    idx2 = bfk.IndexFlatL2(384)
+    idx2.add(big)
+    for nq in (1, 8):
+        D, I = idx2.search(xq[:nq], 10, stats=st)
+        assert st.algo_used == bfk.ALGO_TENSOR
+        check_knn(D, I, xq[:nq], big, 10, L2, tight=True)
+    # bf16-stored rows have no fp32 copy to scan faster: tensor path at any size
+    idx3 = bfk.IndexFlat(384, L2, storage="bf16")
+    idx3.add(xb)
+    D, I = idx3.search(xq[:2], 10, stats=st)
     assert st.algo_used == bfk.ALGO_TENSOR
-    check_knn(D, I, xq[:1], xb, 10, L2, tight=True)
     D, I = idx.search(xq[:8], 10, stats=st, algo="exact")
     assert st.algo_used == bfk.ALGO_EXACT_SIMT
 
