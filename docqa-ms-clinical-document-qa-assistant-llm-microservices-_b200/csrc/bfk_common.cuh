@@ -84,6 +84,7 @@ struct bfk_index {
     cudaEvent_t ws_free = nullptr;  // recorded after the last search that used `ws`
     int* h_flag = nullptr;          // pinned host word: count of uncertified queries (tensor path)
     int* h_flag_dev = nullptr;      // the same word as the GPU addresses it (K5's last CTA writes it)
+    char* h_stage = nullptr;        // pinned staging for small host-side searches (queries in, (D, I) out)
     // id selector of the search in progress (bfk_search_sel; null otherwise), set and cleared under `mu`:
     //   sel       bit i set <=> row i may be returned (faiss IDSelectorBitmap layout)
     //   sel_bias  [tiles*256] fp32: the tensor scan's per-row bias with +inf for rows that are not selected

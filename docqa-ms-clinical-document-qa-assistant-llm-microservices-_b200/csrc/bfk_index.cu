@@ -297,6 +297,7 @@ int bfk_free(bfk_index* idx) {
     if (idx->ws_free) cudaEventDestroy(idx->ws_free);
     if (idx->h_flag) cudaFreeHost(idx->h_flag);
     if (idx->sel_buf) cudaFree(idx->sel_buf);
+    if (idx->h_stage) cudaFreeHost(idx->h_stage);
     delete idx;
     return 0;
 }
@@ -510,7 +511,22 @@ static int search_locked(bfk_index* idx, const float* q, int64_t nq, int k, floa
     char* tail = ws.take<char>(256);
     size_t tail_avail = idx->ws.bytes - (size_t)(tail - (char*)idx->ws.ptr);
 
-    if (io_is_device && ldq == idx->d && !defer && (reinterpret_cast<uintptr_t>(q) & 15u) == 0) {
+    // Small host-side searches go through one pinned staging buffer: a cudaMemcpyAsync from / to pageable memory
+    // is staged by the driver anyway, synchronously and once per call (queries, D, I: three round trips).
+    constexpr size_t STAGE_BYTES = 1 << 20;
+    const size_t q_bytes = sizeof(float) * (size_t)nq * idx->d;
+    const size_t out_span = (size_t)((char*)(I_dev + (size_t)nq * k) - (char*)D_dev);  // D, padding, I: contiguous
+    const bool staged = !io_is_device && q_bytes <= STAGE_BYTES && out_span <= STAGE_BYTES;
+    if (staged && !idx->h_stage && cudaHostAlloc((void**)&idx->h_stage, STAGE_BYTES, cudaHostAllocDefault) != cudaSuccess) {
+        cudaGetLastError();
+        idx->h_stage = nullptr;
+    }
+    if (staged && idx->h_stage) {
+        memcpy(idx->h_stage, q, q_bytes);
+        if (ldq != idx->d) BFK_CUDA(cudaMemsetAsync(q_dev, 0, sizeof(float) * (size_t)nq * ldq, st));
+        BFK_CUDA(cudaMemcpy2DAsync(q_dev, sizeof(float) * ldq, idx->h_stage, sizeof(float) * idx->d, sizeof(float) * idx->d,
+                                   (size_t)nq, cudaMemcpyHostToDevice, st));
+    } else if (io_is_device && ldq == idx->d && !defer && (reinterpret_cast<uintptr_t>(q) & 15u) == 0) {
         // device queries whose row stride already is the padded one: read them in place (a deferred search
         // keeps its own copy, its retry may run after the caller has let go of the buffer)
         q_dev = const_cast<float*>(q);
@@ -544,15 +560,24 @@ static int search_locked(bfk_index* idx, const float* q, int64_t nq, int k, floa
     } else {
         rc = search_exact(idx, q_dev, ldq, nq, k, D_out, I_out, id_offset, tail, tail_avail, st, stats, ev0, ev1);
     }
+    const bool staged_out = staged && idx->h_stage;
     if (!rc && !io_is_device) {
-        if (cudaMemcpyAsync(D, D_dev, sizeof(float) * (size_t)nq * k, cudaMemcpyDeviceToHost, st) != cudaSuccess ||
-            cudaMemcpyAsync(I, I_dev, sizeof(int64_t) * (size_t)nq * k, cudaMemcpyDeviceToHost, st) != cudaSuccess)
+        if (staged_out) {
+            if (cudaMemcpyAsync(idx->h_stage, D_dev, out_span, cudaMemcpyDeviceToHost, st) != cudaSuccess)
+                rc = fail("search: D2H copy failed");
+        } else if (cudaMemcpyAsync(D, D_dev, sizeof(float) * (size_t)nq * k, cudaMemcpyDeviceToHost, st) != cudaSuccess ||
+                   cudaMemcpyAsync(I, I_dev, sizeof(int64_t) * (size_t)nq * k, cudaMemcpyDeviceToHost, st) != cudaSuccess) {
             rc = fail("search: D2H copy failed");
+        }
     }
     if (!rc && cudaEventRecord(idx->ws_free, st) != cudaSuccess) rc = fail("search: event record failed");
     if (!rc && (!io_is_device || stats)) {
         cudaError_t e = cudaStreamSynchronize(st);
         if (e != cudaSuccess) rc = fail(std::string("search: kernel execution failed: ") + cudaGetErrorString(e));
+    }
+    if (!rc && staged_out) {
+        memcpy(D, idx->h_stage, sizeof(float) * (size_t)nq * k);
+        memcpy(I, idx->h_stage + ((char*)I_dev - (char*)D_dev), sizeof(int64_t) * (size_t)nq * k);
     }
     if (stats) {
         if (!rc) {
