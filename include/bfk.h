@@ -15,8 +15,11 @@
  *   - `stream` is a cudaStream_t passed as void* (NULL = the legacy default stream).
  *   - *_is_device = 0: pointers are host memory, the call copies H2D/D2H on `stream`
  *     and returns after the results are in the host buffers.
- *     *_is_device = 1: pointers are device memory on the index's GPU; the call only
- *     enqueues work on `stream` and returns without synchronising.
+ *     *_is_device = 1: pointers are device memory on the index's GPU; the call enqueues
+ *     its work on `stream`.  add / pooling / encoder calls return without synchronising.
+ *     A search through the tensor path waits for `stream` once, to read how many answers
+ *     K5 could not certify (and re-runs those on the GPU) -- unless BFK_ALGO_FLAG_DEFER
+ *     is set, which postpones that to bfk_search_finish; the fp32 scan never waits.
  *   - the index owns all corpus storage; inputs are borrowed for the call; outputs
  *     are caller-allocated.
  *   - concurrent bfk_search on one index is serialised internally; bfk_add /
