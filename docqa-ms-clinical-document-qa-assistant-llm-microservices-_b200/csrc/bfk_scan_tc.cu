@@ -563,9 +563,56 @@ struct RerankParams {
     int* nflag;       // [-1] = CTA ticket, [0] = count, [1..] = list
     int* flag_list;
     int* h_nflag;     // pinned host word (device-mapped): the count, written by the last CTA
+    unsigned long long* dbg;  // optional [16] phase clocks of CTA 0 (BFK_TC_DEBUG), else nullptr
 };
 
+// Sorts a[0..n) ascending (n a power of two); called by every thread of the CTA, results visible on return.
+// Up to 64 * (warps in the CTA) elements, warp w keeps elements [64w, 64w + 64) in registers (two per lane):
+// compare-exchange partners i ^ j are another lane's same slot (shuffle) for j < 32, this lane's other slot for
+// j = 32, and only j >= 64 goes through shared memory with a CTA barrier -- 3 barrier steps at n = 256 where the
+// all-shared-memory network needs 36 (it was a third of K5's time at nq = 64).
 __device__ void rr_bitonic(uint64_t* a, int n, int tid, int nthr) {
+    const int lane = tid & 31, warp = tid >> 5;
+    if (n <= 64 * (nthr >> 5)) {
+        __syncthreads();
+        const int i0 = warp * 64 + lane, i1 = i0 + 32;
+        const bool mine = warp * 64 < n;
+        uint64_t v0 = (mine && i0 < n) ? a[i0] : COMP_EMPTY;
+        uint64_t v1 = (mine && i1 < n) ? a[i1] : COMP_EMPTY;
+        for (int k2 = 2; k2 <= n; k2 <<= 1) {
+            const bool up0 = (i0 & k2) == 0, up1 = (i1 & k2) == 0;
+            for (int j = k2 >> 1; j > 0; j >>= 1) {
+                if (j >= 64) {
+                    if (mine) {
+                        a[i0] = v0;
+                        a[i1] = v1;
+                    }
+                    __syncthreads();
+                    if (mine) {
+                        const uint64_t o0 = a[i0 ^ j], o1 = a[i1 ^ j];
+                        const bool lower = (i0 & j) == 0;  // bit j >= 64 is the same for both slots
+                        v0 = (lower == up0) ? (v0 < o0 ? v0 : o0) : (v0 < o0 ? o0 : v0);
+                        v1 = (lower == up1) ? (v1 < o1 ? v1 : o1) : (v1 < o1 ? o1 : v1);
+                    }
+                    __syncthreads();
+                } else if (j == 32) {
+                    const uint64_t lo = v0 < v1 ? v0 : v1, hi = v0 < v1 ? v1 : v0;
+                    v0 = up0 ? lo : hi;  // k2 >= 64 here: both slots sort in the same direction
+                    v1 = up0 ? hi : lo;
+                } else {
+                    const bool lower = (lane & j) == 0;
+                    const uint64_t o0 = __shfl_xor_sync(0xffffffffu, v0, j);
+                    const uint64_t o1 = __shfl_xor_sync(0xffffffffu, v1, j);
+                    v0 = (lower == up0) ? (v0 < o0 ? v0 : o0) : (v0 < o0 ? o0 : v0);
+                    v1 = (lower == up1) ? (v1 < o1 ? v1 : o1) : (v1 < o1 ? o1 : v1);
+                }
+            }
+        }
+        if (mine && i0 < n) a[i0] = v0;
+        if (mine && i1 < n) a[i1] = v1;
+        __syncthreads();
+        return;
+    }
     for (int k2 = 2; k2 <= n; k2 <<= 1) {
         for (int j = k2 >> 1; j > 0; j >>= 1) {
             for (int i = tid; i < (n >> 1); i += nthr) {
@@ -596,6 +643,8 @@ __global__ void __launch_bounds__(RR_THREADS) rerank_kernel(const RerankParams p
     const int64_t q = blockIdx.x;
     const int64_t M = (int64_t)p.S * p.KP;
     const uint64_t* src = p.out_cand + q * M;
+    const long long rr_t0 = p.dbg ? clock64() : 0;
+#define RR_MARK(i) do { if (p.dbg && blockIdx.x == 0 && tid == 0) p.dbg[i] = (unsigned long long)(clock64() - rr_t0); } while (0)
 
     for (int c = tid; c < p.ld32; c += RR_THREADS) q_s[c] = (c < p.ldq) ? p.q[q * p.ldq + c] : 0.f;
     // T = min over streams of the drop threshold: every row some stream dropped has approximate key >= T
@@ -609,6 +658,7 @@ __global__ void __launch_bounds__(RR_THREADS) rerank_kernel(const RerankParams p
     tmin = red[0];
 #pragma unroll
     for (int w = 1; w < RR_THREADS / 32; w++) tmin = fminf(tmin, red[w]);
+    RR_MARK(0);
 
     // ---- keep only candidates with approximate key <= T (a certified answer never needs the rest:
     //      the cut A_k + 2*eps must lie below T), then sort the few survivors ----
@@ -620,6 +670,7 @@ __global__ void __launch_bounds__(RR_THREADS) rerank_kernel(const RerankParams p
         }
     }
     __syncthreads();
+    RR_MARK(1);
     const int total = cnt_s;
     const int cnt = min(total, TC_MERGE_N);
     int n = 64;
@@ -627,70 +678,106 @@ __global__ void __launch_bounds__(RR_THREADS) rerank_kernel(const RerankParams p
     for (int i = cnt + tid; i < n; i += RR_THREADS) buf[i] = COMP_EMPTY;
     __syncthreads();
     rr_bitonic(buf, n, tid, RR_THREADS);
+    RR_MARK(2);
+    if (p.dbg && blockIdx.x == 0 && tid == 0) p.dbg[8] = (unsigned long long)total;
 
-    // ---- the cut: A_k + 2*eps in approximate-key space ----
-    if (tid == 0) {
+    // ---- the cut: A_k + 2*eps in approximate-key space (buf is sorted: the rows inside the cut are a prefix,
+    //      counted by all threads at once -- RR_THREADS == TC_RMAX, one candidate per thread) ----
+    static_assert(RR_THREADS >= TC_RMAX, "one thread per re-scored candidate");
+    {
         const int nvalid = min(cnt, TC_RMAX);
-        int R = 0;
-        int certified = 1;
+        const int kk = min(p.k, nvalid);
+        float cut = 0.f;
+        bool inside = false;
         if (nvalid > 0) {
-            const int kk = min(p.k, nvalid);
-            const float a_k = ord2f((uint32_t)(buf[kk - 1] >> 32));
-            const float cut = a_k + p.qmargin[q];
-            while (R < nvalid && ord2f((uint32_t)(buf[R] >> 32)) <= cut) R++;
-            if (R < kk) R = kk;
-            if (!(tmin > cut)) certified = 0;          // a dropped row could still reach the cut
-            if (total > TC_MERGE_N) certified = 0;     // survivors did not fit the sort window
-            if (R == TC_RMAX && cnt > TC_RMAX && ord2f((uint32_t)(buf[TC_RMAX] >> 32)) <= cut)
-                certified = 0;                         // more rows inside the cut than we re-score
+            cut = ord2f((uint32_t)(buf[kk - 1] >> 32)) + p.qmargin[q];
+            inside = tid < nvalid && ord2f((uint32_t)(buf[tid] >> 32)) <= cut;
         }
-        info[0] = R;
-        info[1] = certified;
+        int R = __syncthreads_count(inside);
+        if (tid == 0) {
+            int certified = 1;
+            if (nvalid > 0) {
+                if (R < kk) R = kk;
+                if (!(tmin > cut)) certified = 0;          // a dropped row could still reach the cut
+                if (total > TC_MERGE_N) certified = 0;     // survivors did not fit the sort window
+                if (R == TC_RMAX && cnt > TC_RMAX && ord2f((uint32_t)(buf[TC_RMAX] >> 32)) <= cut)
+                    certified = 0;                         // more rows inside the cut than we re-score
+            } else {
+                R = 0;
+            }
+            info[0] = R;
+            info[1] = certified;
+        }
     }
     for (int i = tid; i < TC_RMAX; i += RR_THREADS) ex[i] = COMP_EMPTY;
     __syncthreads();
     const int R = info[0];
+    RR_MARK(3);
+    if (p.dbg && blockIdx.x == 0 && tid == 0) p.dbg[9] = (unsigned long long)R;
     int n_ex = 32;
     while (n_ex < R || n_ex < p.k) n_ex <<= 1;  // <= TC_RMAX since R, k <= TC_RMAX
 
-    // ---- exact re-score of the R survivors (faiss's direct-difference arithmetic) ----
-    for (int i = warp; i < R; i += RR_THREADS / 32) {
-        const uint32_t id = (uint32_t)(buf[i] & 0xffffffffu);
-        float acc = 0.f;
+    // ---- exact re-score of the R survivors (faiss's direct-difference arithmetic); a warp works on two rows at
+    //      a time so that both rows' (random, DRAM-latency) loads are in flight together ----
+    constexpr int NW = RR_THREADS / 32;
+    for (int i = warp; i < R; i += 2 * NW) {
+        const int i2 = i + NW;
+        const bool two = i2 < R;
+        const uint32_t id1 = (uint32_t)(buf[i] & 0xffffffffu);
+        const uint32_t id2 = two ? (uint32_t)(buf[i2] & 0xffffffffu) : id1;
+        float acc1 = 0.f, acc2 = 0.f;
         if (p.storage == BFK_STORE_F32) {
-            const float4* row = reinterpret_cast<const float4*>(p.x32 + (size_t)id * p.ld32);
+            const float4* row1 = reinterpret_cast<const float4*>(p.x32 + (size_t)id1 * p.ld32);
+            const float4* row2 = reinterpret_cast<const float4*>(p.x32 + (size_t)id2 * p.ld32);
             for (int c = lane; c < (p.ld32 >> 2); c += 32) {
-                const float4 x = __ldg(row + c);
+                const float4 x1 = __ldg(row1 + c);
+                const float4 x2 = __ldg(row2 + c);
                 const float4 y = *reinterpret_cast<const float4*>(q_s + 4 * c);
                 if (p.is_l2) {
-                    float t0 = x.x - y.x, t1 = x.y - y.y, t2 = x.z - y.z, t3 = x.w - y.w;
-                    acc = fmaf(t0, t0, acc); acc = fmaf(t1, t1, acc); acc = fmaf(t2, t2, acc); acc = fmaf(t3, t3, acc);
+                    float t0 = x1.x - y.x, t1 = x1.y - y.y, t2 = x1.z - y.z, t3 = x1.w - y.w;
+                    acc1 = fmaf(t0, t0, acc1); acc1 = fmaf(t1, t1, acc1); acc1 = fmaf(t2, t2, acc1); acc1 = fmaf(t3, t3, acc1);
+                    t0 = x2.x - y.x; t1 = x2.y - y.y; t2 = x2.z - y.z; t3 = x2.w - y.w;
+                    acc2 = fmaf(t0, t0, acc2); acc2 = fmaf(t1, t1, acc2); acc2 = fmaf(t2, t2, acc2); acc2 = fmaf(t3, t3, acc2);
                 } else {
-                    acc = fmaf(x.x, y.x, acc); acc = fmaf(x.y, y.y, acc); acc = fmaf(x.z, y.z, acc); acc = fmaf(x.w, y.w, acc);
+                    acc1 = fmaf(x1.x, y.x, acc1); acc1 = fmaf(x1.y, y.y, acc1); acc1 = fmaf(x1.z, y.z, acc1); acc1 = fmaf(x1.w, y.w, acc1);
+                    acc2 = fmaf(x2.x, y.x, acc2); acc2 = fmaf(x2.y, y.y, acc2); acc2 = fmaf(x2.z, y.z, acc2); acc2 = fmaf(x2.w, y.w, acc2);
                 }
             }
         } else {
-            const __nv_bfloat16* row = p.x16 + (size_t)id * p.ld16;
+            const __nv_bfloat16* row1 = p.x16 + (size_t)id1 * p.ld16;
+            const __nv_bfloat16* row2 = p.x16 + (size_t)id2 * p.ld16;
             for (int c = lane; c < p.d; c += 32) {
-                const float x = __bfloat162float(row[c]);
+                const float x1 = __bfloat162float(row1[c]);
+                const float x2 = __bfloat162float(row2[c]);
                 const float y = q_s[c];
                 if (p.is_l2) {
-                    float t0 = x - y;
-                    acc = fmaf(t0, t0, acc);
+                    const float t1 = x1 - y, t2 = x2 - y;
+                    acc1 = fmaf(t1, t1, acc1);
+                    acc2 = fmaf(t2, t2, acc2);
                 } else {
-                    acc = fmaf(x, y, acc);
+                    acc1 = fmaf(x1, y, acc1);
+                    acc2 = fmaf(x2, y, acc2);
                 }
             }
         }
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+        for (int o = 16; o > 0; o >>= 1) {
+            acc1 += __shfl_xor_sync(0xffffffffu, acc1, o);
+            acc2 += __shfl_xor_sync(0xffffffffu, acc2, o);
+        }
         if (lane == 0) {
-            const float key = p.is_l2 ? acc : -acc;
-            ex[i] = (key < FLT_MAX) ? make_comp(key, id) : COMP_EMPTY;
+            const float key1 = p.is_l2 ? acc1 : -acc1;
+            ex[i] = (key1 < FLT_MAX) ? make_comp(key1, id1) : COMP_EMPTY;
+            if (two) {
+                const float key2 = p.is_l2 ? acc2 : -acc2;
+                ex[i2] = (key2 < FLT_MAX) ? make_comp(key2, id2) : COMP_EMPTY;
+            }
         }
     }
     __syncthreads();
+    RR_MARK(4);
     rr_bitonic(ex, min(n_ex, TC_RMAX), tid, RR_THREADS);
+    RR_MARK(5);
     for (int i = tid; i < p.k; i += RR_THREADS) {
         const uint64_t c = (i < TC_RMAX) ? ex[i] : COMP_EMPTY;
         float dv;
@@ -891,7 +978,7 @@ static void tc_carve(const bfk_index* idx, int64_t nqc, int k, int fb_nparts, ch
     w->fb_D = (float*)take((size_t)8 * k * 4);
     w->fb_I = (int64_t*)take((size_t)8 * k * 8);
     w->fb_part = (uint64_t*)take((size_t)8 * fb_nparts * k * 8);
-    w->dbg = (unsigned long long*)take((size_t)idx->num_sms * 8 * 8 + 8 * 64 * 8);
+    w->dbg = (unsigned long long*)take((size_t)idx->num_sms * 8 * 8 + 8 * 64 * 8 + 16 * 8);  // scan counters, timeline, K5 phases
     w->pend_g = (uint64_t*)take((size_t)idx->num_sms * TC_BUFCAP * TC_EPI_THREADS * 8);
     const int64_t nr = nqc / 2 + 1;
     w->r_list = (int*)take((size_t)(nr + 1) * 4);
@@ -1121,8 +1208,16 @@ static int tc_pass(bfk_index* idx, const float* qc, int ldq, int64_t nqc, int k,
     r.nflag = w.flags;
     r.flag_list = w.flags + 1;
     r.h_nflag = idx->h_flag_dev;
+    r.dbg = p.dbg ? w.dbg + (size_t)pl.grid * 8 + 8 * 64 : nullptr;
     rerank_kernel<<<(unsigned)nqc, RR_THREADS, 0, st>>>(r);
     BFK_CUDA(cudaGetLastError());
+    if (r.dbg) {
+        unsigned long long h[16];
+        BFK_CUDA(cudaMemcpyAsync(h, r.dbg, sizeof(h), cudaMemcpyDeviceToHost, st));
+        BFK_CUDA(cudaStreamSynchronize(st));
+        fprintf(stderr, "[bfk rerank, CTA 0, cycles] tmin=%llu filtered=%llu sorted=%llu cut=%llu rescored=%llu sorted2=%llu | survivors=%llu R=%llu\n",
+                h[0], h[1], h[2], h[3], h[4], h[5], h[8], h[9]);
+    }
     *launches += 3;
     return 0;
 }
