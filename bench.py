@@ -375,7 +375,7 @@ def run_reference(args):
     cpu_baseline.build()
     workload = args.workload or ("c2" if args.gpus == 1 else "c5")
     n_full = {"c2": 1_000_000, "c3": 10_000_000}.get(workload, 100_000_000)
-    n_sample = 1_000_000
+    n_sample = min(args.rows or 1_000_000, n_full)
     rng = np.random.default_rng(CORPUS_SEED)
     xb = rng.standard_normal((n_sample, D), dtype=np.float32)
     xb /= np.linalg.norm(xb, axis=1, keepdims=True)
@@ -415,7 +415,7 @@ def run_reference(args):
     if real is not None:
         cores, kind, ref_kind = _faiss.omp_get_max_threads(), "reference", f"faiss-cpu {_faiss.__version__}"
     sample = (f"full workload: {n_sample}x{D} fp32 corpus, nq={args.nq}" if scale == 1.0 else
-              f"1M-row slice of the {n_full}-row corpus, nq={args.nq}; value extrapolated linearly in N")
+              f"{n_sample}-row slice of the {n_full}-row corpus, nq={args.nq}; value extrapolated linearly in N")
     line = {
         "metric": METRIC, "value": qps, "unit": "queries/s", "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3 / scale, "higher_is_better": True,
