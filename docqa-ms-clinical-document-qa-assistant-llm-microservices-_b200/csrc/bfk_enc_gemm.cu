@@ -281,11 +281,12 @@ enc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                 float s1 = 0.f, s2 = 0.f;
                 uint4 gres[4];  // residual chunk in flight
                 res_fetch(res0, (int64_t)mt * EG_BM, gres);
-                // one 32-column chunk of pass 1: v = acc + bias + residual, accumulate sum and sum of squares
-                auto stats32 = [&](const uint32_t (&rv)[32], int ch) {
+                // one 32-column chunk of pass 1: v = acc + bias + residual, accumulate sum and sum of squares, and
+                // write v back over the accumulator so that pass 2 needs neither the residual nor the bias again
+                auto stats32 = [&](uint32_t (&rv)[32], int ch) {
                     uint4 rr[4];
                     res_stage(gres, rr);
-                    res_fetch(res0 + ((ch + 1) % NCH) * 32, (int64_t)mt * EG_BM, gres);  // wraps to pass 2's first chunk
+                    if (ch + 1 < NCH) res_fetch(res0 + (ch + 1) * 32, (int64_t)mt * EG_BM, gres);
                     const uint32_t* rw = reinterpret_cast<const uint32_t*>(rr);
 #pragma unroll
                     for (int j = 0; j < 16; j++) {
@@ -294,20 +295,26 @@ enc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                         const float v1 = __uint_as_float(rv[2 * j + 1]) + bb.y + __uint_as_float(rw[j] & 0xffff0000u);
                         s1 += v0 + v1;
                         s2 = fmaf(v0, v0, fmaf(v1, v1, s2));
+                        rv[2 * j] = __float_as_uint(v0);
+                        rv[2 * j + 1] = __float_as_uint(v1);
                     }
+                    tmem_st_32x32(acc_addr + ch * 32, rv);
                 };
                 // rolled over chunk pairs (two register sets, the next load in flight): unrolled over all six
-                // chunks this epilogue spilled
+                // chunks this epilogue spilled.  A register set is loaded again only after its store has drained.
                 tmem_ld_32x32(acc_addr, r[0]);
 #pragma unroll 1
                 for (int ch = 0; ch < NCH; ch += 2) {
                     tmem_ld_wait();
+                    tmem_st_wait();
                     tmem_ld_32x32(acc_addr + (ch + 1) * 32, r[1]);
                     stats32(r[0], ch);
                     tmem_ld_wait();
+                    tmem_st_wait();
                     if (ch + 2 < NCH) tmem_ld_32x32(acc_addr + (ch + 2) * 32, r[0]);
                     stats32(r[1], ch + 1);
                 }
+                tmem_st_wait();
                 float2* part = ln_part + (tcount & 1u) * 256;
                 part[half * 128 + row] = make_float2(s1, s2);
                 eg_epi_sync();
@@ -320,18 +327,12 @@ enc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                 const float* gamma = par_s + BN + half * HC;
                 const float* beta = par_s + 2 * BN + half * HC;
                 auto norm32 = [&](const uint32_t (&rv)[32], int ch) {
-                    uint4 rr[4];
-                    res_stage(gres, rr);
-                    if (ch + 1 < NCH) res_fetch(res0 + (ch + 1) * 32, (int64_t)mt * EG_BM, gres);
-                    const uint32_t* rw = reinterpret_cast<const uint32_t*>(rr);
                     uint32_t o[16];
 #pragma unroll
                     for (int j = 0; j < 16; j++) {
-                        const float2 bb = reinterpret_cast<const float2*>(bias + ch * 32)[j];
                         const float2 gg = reinterpret_cast<const float2*>(gamma + ch * 32)[j];
                         const float2 be = reinterpret_cast<const float2*>(beta + ch * 32)[j];
-                        const float v0 = __uint_as_float(rv[2 * j]) + bb.x + __uint_as_float(rw[j] << 16);
-                        const float v1 = __uint_as_float(rv[2 * j + 1]) + bb.y + __uint_as_float(rw[j] & 0xffff0000u);
+                        const float v0 = __uint_as_float(rv[2 * j]), v1 = __uint_as_float(rv[2 * j + 1]);
                         o[j] = pack_bf16x2(fmaf((v0 - mean) * rstd, gg.x, be.x), fmaf((v1 - mean) * rstd, gg.y, be.y));
                     }
                     store32(o, p.out + half * HC + ch * 32, (int64_t)mt * EG_BM);
