@@ -114,8 +114,9 @@ enc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     uint64_t* tempty_bar = tfull_bar + 2;         // [NACC] accumulator drained (256 epilogue threads)
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
     float2* ln_part = reinterpret_cast<float2*>(smem + STAGES * STAGE + 256);  // [2 parities][2 halves][128 rows]
-    unsigned char* stg_all = smem + STAGES * STAGE + 256 + 4096;                 // [8 warps][32 rows x 64 B]
-    float* par_s = reinterpret_cast<float*>(stg_all + 8 * 2048);                 // [3][384] bias | gamma | beta
+    float* par_s = reinterpret_cast<float*>(smem + STAGES * STAGE + 256 + 4096);  // [3][384] bias | gamma | beta
+    float* bias_s = reinterpret_cast<float*>(ln_part);  // bias / GELU kernels: the whole bias vector (N <= 2176 floats)
+    unsigned char* stg_all = smem + STAGES * STAGE + 256 + 4096 + 3 * 384 * 4;    // [8 warps][32 rows x 64 B]
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int KB = p.K / EG_BK;
@@ -133,6 +134,9 @@ enc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
             mbar_init(&tempty_bar[a], EG_EPI_THREADS);
         }
         fence_mbar_init();
+    }
+    if constexpr (EPI != EPI_RES_LN) {
+        for (int i = tid; i < p.N; i += EG_THREADS) bias_s[i] = p.bias[i];  // read as shared-memory broadcasts
     }
     if constexpr (EPI == EPI_RES_LN) {
         // every tile of this kernel spans the same 384 columns: keep bias / gamma / beta on chip (read as
@@ -348,7 +352,7 @@ enc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                     norm32(r[1], ch + 1);
                 }
             } else {
-                const float* bias = p.bias + n0;
+                const float* bias = bias_s + n0;
                 tmem_ld_32x32(acc_addr, r[0]);
 #pragma unroll
                 for (int ch = 0; ch < NCH; ch++) {
@@ -357,7 +361,7 @@ enc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                     uint32_t o[16];
 #pragma unroll
                     for (int j = 0; j < 16; j++) {
-                        const float2 bb = __ldg(reinterpret_cast<const float2*>(bias + ch * 32) + j);
+                        const float2 bb = reinterpret_cast<const float2*>(bias + ch * 32)[j];
                         float v0 = __uint_as_float(r[ch & 1][2 * j]) + bb.x;
                         float v1 = __uint_as_float(r[ch & 1][2 * j + 1]) + bb.y;
                         if constexpr (EPI == EPI_GELU) {
@@ -410,6 +414,7 @@ int launch_enc_gemm(int epi, const __nv_bfloat16* A, const __nv_bfloat16* W, int
                     __nv_bfloat16* out, int ldo, int num_sms, cudaStream_t st) {
     if (M <= 0) return 0;
     if (N % 192 != 0 || K % EG_BK != 0) return fail("encoder gemm: N must be a multiple of 192 and K of 64");
+    if (N > 2176) return fail("encoder gemm: N > 2176 does not fit the on-chip bias vector");
     if (epi == EPI_RES_LN && N != 384) return fail("encoder gemm: the LayerNorm epilogue needs N == 384");
     CUtensorMap tmA, tmW;
     BFK_TRY(make_tmap(&tmA, A, M, K, EG_BM));
