@@ -7,14 +7,14 @@
 //     C[M, N] = A[M, K] . W[N, K]^T + bias      (A = token states, bf16 row-major; W = the layer's weight)
 // with the op that follows fused into the epilogue:
 //     EPI_BIAS    store bf16                                   (packed QKV projection, N = 1152)
-//     EPI_GELU    exact (erf) GELU, store bf16                  (intermediate, N = 1536)
+//     EPI_GELU    GELU (tanh form on MUFU.TANH; EPI_GELU_ERF: erf polynomial), store bf16   (intermediate, N = 1536)
 //     EPI_RES_LN  + residual row, LayerNorm(gamma, beta, eps)   (attention output / FFN output, N = 384)
 //
 // Two tile shapes, one kernel (template<EPI, BN>):
 //   BN = 384 (the model width) for the LayerNorm epilogue: a CTA owns complete rows, so LayerNorm needs no
 //     cross-CTA reduction -- the two epilogue threads that share an output row (one per 192-column half)
-//     exchange their partial sums through shared memory, pass 1 over the accumulator gives mean / variance,
-//     pass 2 normalises and stores.  384 of the 512 TMEM columns: single-buffered, the next tile's MMAs wait
+//     exchange their partial sums through shared memory, pass 1 over the accumulator gives mean / variance and
+//     writes v = acc + bias + residual back into TMEM, pass 2 normalises and stores.  384 of the 512 TMEM columns: single-buffered, the next tile's MMAs wait
 //     for this tile's epilogue while the TMA ring keeps prefetching.
 //   BN = 192 for the bias / GELU epilogues (all N in the model are multiples of 192): two accumulators, so
 //     the MMAs of tile i+1 run under the epilogue of tile i.
