@@ -500,26 +500,70 @@ __global__ void __launch_bounds__(256) enc_embed_ln_kernel(const int64_t* __rest
     float v[16];  // H <= 512
     float s1 = 0.f;
     const int per = (H + 31) / 32;
-    for (int i = 0; i < per; i++) {
-        const int c = lane + 32 * i;
-        v[i] = c < H ? word[(size_t)id * H + c] + pos[(size_t)t * H + c] + type0[c] : 0.f;
-        s1 += v[i];
+    const bool vec4 = (H & 127) == 0;  // 128-bit loads: lane owns columns [4*lane + 128*i, +4)
+    if (vec4) {
+        const float4* w4 = reinterpret_cast<const float4*>(word + (size_t)id * H);
+        const float4* p4 = reinterpret_cast<const float4*>(pos + (size_t)t * H);
+        const float4* t4 = reinterpret_cast<const float4*>(type0);
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            if (i < (H >> 7)) {
+                const float4 a = __ldg(w4 + lane + 32 * i), b = __ldg(p4 + lane + 32 * i), c = __ldg(t4 + lane + 32 * i);
+                v[4 * i + 0] = a.x + b.x + c.x;
+                v[4 * i + 1] = a.y + b.y + c.y;
+                v[4 * i + 2] = a.z + b.z + c.z;
+                v[4 * i + 3] = a.w + b.w + c.w;
+                s1 += (v[4 * i] + v[4 * i + 1]) + (v[4 * i + 2] + v[4 * i + 3]);
+            }
+        }
+    } else {
+        for (int i = 0; i < per; i++) {
+            const int c = lane + 32 * i;
+            v[i] = c < H ? word[(size_t)id * H + c] + pos[(size_t)t * H + c] + type0[c] : 0.f;
+            s1 += v[i];
+        }
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) s1 += __shfl_xor_sync(0xffffffffu, s1, o);
     const float mean = s1 / H;
     float s2 = 0.f;
-    for (int i = 0; i < per; i++) {
-        const int c = lane + 32 * i;
-        const float dlt = c < H ? v[i] - mean : 0.f;
-        s2 = fmaf(dlt, dlt, s2);
+    if (vec4) {
+#pragma unroll
+        for (int i = 0; i < 16; i++)
+            if (i < (H >> 5)) {
+                const float dlt = v[i] - mean;
+                s2 = fmaf(dlt, dlt, s2);
+            }
+    } else {
+        for (int i = 0; i < per; i++) {
+            const int c = lane + 32 * i;
+            const float dlt = c < H ? v[i] - mean : 0.f;
+            s2 = fmaf(dlt, dlt, s2);
+        }
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) s2 += __shfl_xor_sync(0xffffffffu, s2, o);
     const float rstd = rsqrtf(s2 / H + eps);
-    for (int i = 0; i < per; i++) {
-        const int c = lane + 32 * i;
-        if (c < H) x[(size_t)m * H + c] = __float2bfloat16_rn((v[i] - mean) * rstd * gamma[c] + beta[c]);
+    if (vec4) {
+        const float4* g4 = reinterpret_cast<const float4*>(gamma);
+        const float4* b4 = reinterpret_cast<const float4*>(beta);
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            if (i < (H >> 7)) {
+                const float4 g = __ldg(g4 + lane + 32 * i), b = __ldg(b4 + lane + 32 * i);
+                const __nv_bfloat162 lo = __floats2bfloat162_rn((v[4 * i] - mean) * rstd * g.x + b.x, (v[4 * i + 1] - mean) * rstd * g.y + b.y);
+                const __nv_bfloat162 hi = __floats2bfloat162_rn((v[4 * i + 2] - mean) * rstd * g.z + b.z, (v[4 * i + 3] - mean) * rstd * g.w + b.w);
+                uint2 o;
+                o.x = *reinterpret_cast<const uint32_t*>(&lo);
+                o.y = *reinterpret_cast<const uint32_t*>(&hi);
+                *reinterpret_cast<uint2*>(x + (size_t)m * H + 4 * (lane + 32 * i)) = o;
+            }
+        }
+    } else {
+        for (int i = 0; i < per; i++) {
+            const int c = lane + 32 * i;
+            if (c < H) x[(size_t)m * H + c] = __float2bfloat16_rn((v[i] - mean) * rstd * gamma[c] + beta[c]);
+        }
     }
     if (lane == 0) {
         float on;
