@@ -118,3 +118,50 @@ def test_erf_gelu_variant_in_a_fresh_process():
         stats[variant] = (mx, mean)
     # the tanh form with the hardware tanh adds nothing measurable on top of the bf16 rounding of activations
     assert stats["tanh"][1] <= 1.15 * stats["erf"][1] + 1e-4, stats
+
+
+class FakeTokenizer:
+    """tokenizer(list[str], padding=True, truncation=True, max_length=..., return_tensors='pt') -> ids / mask."""
+
+    def __init__(self, vocab):
+        self.vocab = vocab
+
+    def __call__(self, texts, padding=True, truncation=True, max_length=256, return_tensors="pt"):
+        import torch
+
+        rows = [[(hash((w, 7)) % (self.vocab - 3)) + 3 for w in t.split()][:max_length] or [1] for t in texts]
+        T = max(len(r) for r in rows)
+        ids = torch.zeros((len(rows), T), dtype=torch.int64)
+        mask = torch.zeros((len(rows), T), dtype=torch.int64)
+        for i, r in enumerate(rows):
+            ids[i, : len(r)] = torch.tensor(r)
+            mask[i, : len(r)] = 1
+        return {"input_ids": ids, "attention_mask": mask}
+
+
+def test_indexer_with_the_gpu_encoder(bfk, tmp_path):
+    """indexer.py:32-48 end to end on the device: texts -> tokens -> encoder -> fused pool + add -> search."""
+    import torch
+
+    m = hf_model(layers=2, vocab=400)
+    enc = bfk.MiniLMEncoder.from_hf_model(m, tokenizer=FakeTokenizer(400))
+    ix = bfk.SemanticIndexer(enc, 384, index_file=str(tmp_path / "vector_store.faiss"),
+                             metadata_file=str(tmp_path / "metadata_store.pkl"))
+    texts = [" ".join(f"mot{(7 * i + j) % 50}" for j in range(3 + i % 9)) for i in range(40)]
+    assert ix.add_many(texts, "herbs.csv") == 40
+    assert ix.index.ntotal == 40 == len(ix.metadata_store)
+    # the rows are what encode() returns (SentenceTransformer.encode semantics: unit-norm float32 [n, 384])
+    emb = enc.encode(texts)
+    assert emb.shape == (40, 384) and emb.dtype == np.float32
+    np.testing.assert_allclose(ix.index.reconstruct_n(0, 40), emb, atol=2e-3)
+    assert enc.encode("mot1 mot2").shape == (384,)
+    # and they match the fp32 reference model on the same tokens
+    tok = enc.tokenizer(texts)
+    ids, mask = bfk.pad_to_multiple(tok["input_ids"], tok["attention_mask"])
+    sd = {k: v.numpy() for k, v in m.state_dict().items()}
+    ref = encoder_ref.encode(sd, ids.numpy(), mask.numpy(), eps=m.config.layer_norm_eps)
+    assert ((emb * ref).sum(1) >= 0.9995).all()
+    D, I = ix.index.search(ref[:5], 1)
+    assert I[:, 0].tolist() == [0, 1, 2, 3, 4]
+    ix.save_state()
+    assert bfk.read_index(ix.index_file).ntotal == 40
