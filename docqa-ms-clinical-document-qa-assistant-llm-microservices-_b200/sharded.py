@@ -79,6 +79,7 @@ class ShardedIndexFlat:
         if n_local:
             self._seg_local.append(self.local.ntotal - n_local)
             self._seg_global.append(global_start)
+        self._n_records = getattr(self, "_n_records", 0) + 1  # the same on every rank, unlike the segment list
         self._ntotal += n_global
 
     # -- mutation -----------------------------------------------------------------------
@@ -102,6 +103,8 @@ class ShardedIndexFlat:
     def reset(self) -> None:
         self.local.reset()
         self._seg_local, self._seg_global, self._ntotal = [], [], 0
+        self._seg_tensors = None
+        self._n_records = 0
 
     # -- queries ------------------------------------------------------------------------
     def _to_global(self, I):
@@ -113,8 +116,13 @@ class ShardedIndexFlat:
             return torch.where(I >= 0, I + off, I)
         if not self._seg_local:
             return I
-        starts = torch.tensor(self._seg_local, dtype=torch.int64, device=I.device)
-        gstarts = torch.tensor(self._seg_global, dtype=torch.int64, device=I.device)
+        key = (str(I.device), len(self._seg_local))
+        cached = getattr(self, "_seg_tensors", None)
+        if cached is None or cached[0] != key:
+            cached = (key, torch.tensor(self._seg_local, dtype=torch.int64, device=I.device),
+                      torch.tensor(self._seg_global, dtype=torch.int64, device=I.device))
+            self._seg_tensors = cached
+        starts, gstarts = cached[1], cached[2]
         seg = torch.bucketize(I.clamp(min=0), starts, right=True) - 1
         out = gstarts[seg] + (I - starts[seg])
         return torch.where(I >= 0, out, I)
@@ -186,12 +194,36 @@ class ShardedIndexFlat:
         assert k > 0
         k = int(k)
         is_torch = type(x).__module__.split(".")[0] == "torch"
-        single = len(self._seg_local) == 1
+        # which exchange protocol runs must be the same decision on every rank: count add calls, not the local
+        # segments (a rank that received no rows of a batch has fewer)
+        single = getattr(self, "_n_records", 0) <= 1 and len(self._seg_local) <= 1
+        one_add = getattr(self, "_n_records", 0) <= 1
         kw = {}
         if algo is not None:
             kw["algo"] = algo
         on_gpu = hasattr(self.local, "_h")
-        if on_gpu and single and self._merge is None and self.world > 1:
+        if on_gpu and not one_add and self._merge is None and self.world > 1:
+            # several id segments (incremental replicated adds): local ids are translated on the device, then
+            # the same peer-memory exchange + merge; the local search is settled first (its rewrites would
+            # otherwise land after the translation)
+            dev = torch.device("cuda", self.local.device)
+            b = self._gpu_buffers(n, k, dev)
+            xq = x if is_torch else torch.from_numpy(np.ascontiguousarray(x, dtype=np.float32)).to(dev)
+            L = _lib.load()
+            xh = self._exchange(n * k, dev)
+            self.local.search(xq, k, D=b["D"], I=b["I"], **kw)
+            b["I"].copy_(self._to_global(b["I"]))
+            st = ctypes.c_void_p(torch.cuda.current_stream(dev.index).cuda_stream)
+            Dout = torch.empty((n, k), dtype=torch.float32, device=dev)
+            Iout = torch.empty((n, k), dtype=torch.int64, device=dev)
+            _lib.check(L.bfk_xchg_merge(xh, ctypes.c_void_p(b["D"].data_ptr()), ctypes.c_void_p(b["I"].data_ptr()), n, k,
+                                         self.metric_type, None, ctypes.c_void_p(Dout.data_ptr()),
+                                         ctypes.c_void_p(Iout.data_ptr()), st))
+            torch.cuda.current_stream(dev.index).synchronize()
+            if is_torch:
+                return Dout, Iout
+            return Dout.cpu().numpy(), Iout.cpu().numpy()
+        if on_gpu and one_add and self._merge is None and self.world > 1:
             # fast path: the kernels write (D, I) with global ids straight into the send buffer, ONE
             # all-gather of raw bytes, and the merge kernel reads the gather buffer in place
             dev = torch.device("cuda", self.local.device)
@@ -202,7 +234,7 @@ class ShardedIndexFlat:
             # collective sits on the critical path
             L = _lib.load()
             xh = self._exchange(n * k, dev)
-            off = self._seg_global[0] - self._seg_local[0]
+            off = self._seg_global[0] - self._seg_local[0] if self._seg_local else 0
             self.local.search(xq, k, D=b["D"], I=b["I"], id_offset=off, defer=True, **kw)
             st = ctypes.c_void_p(torch.cuda.current_stream(dev.index).cuda_stream)
             Dout = torch.empty((n, k), dtype=torch.float32, device=dev)
@@ -219,7 +251,7 @@ class ShardedIndexFlat:
             if is_torch:
                 return Dout, Iout
             return Dout.cpu().numpy(), Iout.cpu().numpy()
-        if single and on_gpu:
+        if single and on_gpu and self._seg_local:
             # ids come back global straight from the kernel's epilogue
             kw["id_offset"] = self._seg_global[0] - self._seg_local[0]
         Dl, Il = self.local.search(x, k, **kw)
