@@ -630,8 +630,9 @@ __device__ void rr_bitonic(uint64_t* a, int n, int tid, int nthr) {
     }
 }
 
-constexpr int RR_THREADS = 512;
-
+// RR_THREADS = 512 for long candidate lists (few queries, many streams), 128 when a query has at most 1024
+// candidates (many queries): four times as many queries are then resident per SM.
+template <int RR_THREADS>
 __global__ void __launch_bounds__(RR_THREADS) rerank_kernel(const RerankParams p) {
     __shared__ uint64_t buf[TC_MERGE_N];
     __shared__ uint64_t ex[TC_RMAX];
@@ -682,18 +683,23 @@ __global__ void __launch_bounds__(RR_THREADS) rerank_kernel(const RerankParams p
     if (p.dbg && blockIdx.x == 0 && tid == 0) p.dbg[8] = (unsigned long long)total;
 
     // ---- the cut: A_k + 2*eps in approximate-key space (buf is sorted: the rows inside the cut are a prefix,
-    //      counted by all threads at once -- RR_THREADS == TC_RMAX, one candidate per thread) ----
-    static_assert(RR_THREADS >= TC_RMAX, "one thread per re-scored candidate");
+    //      counted by all threads at once) ----
     {
         const int nvalid = min(cnt, TC_RMAX);
         const int kk = min(p.k, nvalid);
         float cut = 0.f;
-        bool inside = false;
+        int inside = 0;
         if (nvalid > 0) {
             cut = ord2f((uint32_t)(buf[kk - 1] >> 32)) + p.qmargin[q];
-            inside = tid < nvalid && ord2f((uint32_t)(buf[tid] >> 32)) <= cut;
+            for (int i = tid; i < nvalid; i += RR_THREADS) inside += ord2f((uint32_t)(buf[i] >> 32)) <= cut ? 1 : 0;
         }
-        int R = __syncthreads_count(inside);
+        if (tid == 0) info[2] = 0;
+        __syncthreads();
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) inside += __shfl_xor_sync(0xffffffffu, inside, o);
+        if (lane == 0 && inside) atomicAdd(&info[2], inside);
+        __syncthreads();
+        int R = info[2];
         if (tid == 0) {
             int certified = 1;
             if (nvalid > 0) {
@@ -1209,7 +1215,8 @@ static int tc_pass(bfk_index* idx, const float* qc, int ldq, int64_t nqc, int k,
     r.flag_list = w.flags + 1;
     r.h_nflag = idx->h_flag_dev;
     r.dbg = p.dbg ? w.dbg + (size_t)pl.grid * 8 + 8 * 64 : nullptr;
-    rerank_kernel<<<(unsigned)nqc, RR_THREADS, 0, st>>>(r);
+    if ((int64_t)r.S * r.KP <= 1024 && k <= 32) rerank_kernel<128><<<(unsigned)nqc, 128, 0, st>>>(r);
+    else rerank_kernel<512><<<(unsigned)nqc, 512, 0, st>>>(r);
     BFK_CUDA(cudaGetLastError());
     if (r.dbg) {
         unsigned long long h[16];
