@@ -43,6 +43,7 @@ EXPORTS = [
     "bfk_reconstruct", "bfk_remove_ids", "bfk_write", "bfk_read", "bfk_serialized_size",
     "bfk_serialize", "bfk_deserialize", "bfk_normalize_l2", "bfk_merge_topk", "bfk_merge_topk_strided", "bfk_search_noalloc",
     "bfk_enc_create", "bfk_enc_free", "bfk_enc_set_tensor", "bfk_enc_forward", "bfk_enc_encode", "bfk_enc_encode_add",
+    "bfk_profile_begin", "bfk_profile_end",
     "bfk_search_sel", "bfk_range_search", "bfk_range_result_size", "bfk_range_result_copy", "bfk_range_result_free",
 ]
 
@@ -78,6 +79,8 @@ def load() -> ctypes.CDLL:
     L.bfk_search.argtypes = [vp, vp, i64, i64, vp, vp, i32, vp]
     L.bfk_search_ex.argtypes = [vp, vp, i64, i64, vp, vp, i32, vp, i32, i64, ctypes.POINTER(SearchStats)]
     L.bfk_search_finish.argtypes = [vp, vp, ctypes.POINTER(i64)]
+    L.bfk_profile_begin.argtypes = [vp]
+    L.bfk_profile_end.argtypes = [vp, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(i64)]
     L.bfk_search_pending_nflag_ptr.argtypes = [vp]
     L.bfk_search_pending_nflag_ptr.restype = vp
     L.bfk_xchg_create.argtypes = [i32, i32, i32, i64, ctypes.POINTER(vp), vp]

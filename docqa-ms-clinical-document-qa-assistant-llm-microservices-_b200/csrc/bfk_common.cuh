@@ -10,6 +10,7 @@
 #include <cstdio>
 #include <mutex>
 #include <string>
+#include <vector>
 
 #include "../../include/bfk.h"
 
@@ -92,12 +93,39 @@ struct bfk_index {
     const float* sel_bias = nullptr;
     void* sel_buf = nullptr;        // grow-only device buffer behind sel / sel_bias
     size_t sel_buf_bytes = 0;
-    std::mutex mu;
+    // Appends (K1 / K2) are only enqueued on the caller's stream.  `rows_ready` is recorded behind each of them;
+    // every path that reads the rows on another stream (regrowth copies, reconstruct / write_index, remove_ids,
+    // a search on a different stream) first makes its stream wait for it.
+    cudaEvent_t rows_ready = nullptr;
+    bool rows_pending = false;      // an append has been enqueued since the last full synchronisation
+    cudaStream_t rows_stream = nullptr;  // the stream of that append
+    cudaEvent_t stage_done = nullptr;    // the last H2D copy out of `h_stage` has completed
+    // tensor maps of the scan, re-encoded only when what they describe changes
+    //   [0] corpus scan copy: key (x16, ntotal, box rows)   [1] padded bf16 queries: key (q16, nq_pad)
+    struct TmapSlot {
+        alignas(64) unsigned char map[128];
+        const void* base = nullptr;
+        int64_t rows = -1;
+        int box_rows = 0;
+    } tmap[2];
+    // bfk_profile_begin/end: device timestamps of every tensor-scan launch, [slot][0] = first CTA in,
+    // [slot][1] = last CTA out (globaltimer ns), collected without synchronising inside the searches
+    unsigned long long* prof_ring = nullptr;
+    int64_t prof_cap = 0;
+    int64_t prof_used = 0;
+    bool prof_on = false;
+    mutable std::mutex mu;
 };
 
 namespace bfk {
 
 int ensure_capacity(bfk_index* idx, int64_t need, cudaStream_t st);
+// grows the storage (amortised doubling) under the index mutex; rows appended so far are carried over
+int grow_for(bfk_index* idx, int64_t need, cudaStream_t st);
+// makes `st` wait for the appends enqueued so far (no-op when none is pending)
+int wait_rows_ready(const bfk_index* idx, cudaStream_t st);
+// records `rows_ready` behind an append just enqueued on `st`
+int mark_rows_ready(bfk_index* idx, cudaStream_t st);
 int ensure_workspace(bfk_index* idx, size_t bytes);
 
 // kernels / launchers implemented across the .cu files -----------------------
@@ -110,8 +138,9 @@ int launch_pool(const void* tok, int tok_dtype, const void* mask, int mask_dtype
 // K3a: exact fp32 scan of up to 8 queries; writes sorted partial lists
 //   part [nq][nparts][k] composite keys; returns nparts through *nparts_out
 int scan_exact_workspace(const bfk_index* idx, int nq, int k, size_t* bytes, int* nparts_out);
+//   sel: optional id selector bitmap on the device (bit i <=> row i may be returned), else nullptr
 int launch_scan_exact(const bfk_index* idx, const float* q_dev /*[nq, ldq]*/, int ldq, int nq, int k,
-                      uint64_t* part, int nparts, cudaStream_t st);
+                      uint64_t* part, int nparts, cudaStream_t st, const unsigned char* sel);
 // K4/K6: per query, top-k of m composite keys -> (D, I)
 int launch_select(const uint64_t* cand, int64_t m_per_query, int64_t nq, int k, int metric,
                   int64_t id_offset, float* D, int64_t* I, int64_t out_ld, cudaStream_t st);

@@ -299,7 +299,7 @@ int bfk_enc_encode_add(void* enc, bfk_index* idx, const int64_t* ids, const void
     std::lock_guard<std::mutex> lk(e->mu);
     const int64_t mb = micro_batch(e, T);
     BFK_TRY(ensure_rows(e, std::min(B, mb) * T));
-    BFK_TRY(bfk_reserve(idx, bfk_ntotal(idx) + B));
+    BFK_TRY(grow_for(idx, bfk_ntotal(idx) + B, st));  // once for all micro-batches, amortised doubling
     for (int64_t b0 = 0; b0 < B; b0 += mb) {
         const int64_t Bm = std::min(mb, B - b0);
         const void* mk = (const char*)mask + (size_t)b0 * T * mask_elem(mask_dtype);

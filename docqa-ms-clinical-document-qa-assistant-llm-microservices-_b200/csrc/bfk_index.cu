@@ -63,9 +63,23 @@ static int alloc_storage(bfk_index* idx, int64_t cap, float** x32, __nv_bfloat16
     return 0;
 }
 
-// grow corpus storage to hold at least `need` rows (amortised doubling)
+int wait_rows_ready(const bfk_index* idx, cudaStream_t st) {
+    if (idx->rows_pending && idx->rows_ready && st != idx->rows_stream)
+        BFK_CUDA(cudaStreamWaitEvent(st, idx->rows_ready, 0));
+    return 0;
+}
+
+int mark_rows_ready(bfk_index* idx, cudaStream_t st) {
+    BFK_CUDA(cudaEventRecord(idx->rows_ready, st));
+    idx->rows_pending = true;
+    idx->rows_stream = st;
+    return 0;
+}
+
+// grow corpus storage to hold at least `need` rows (amortised doubling); idx->mu is held
 int ensure_capacity(bfk_index* idx, int64_t need, cudaStream_t st) {
     if (need <= idx->cap) return 0;
+    BFK_TRY(wait_rows_ready(idx, st));
     int64_t want = std::max<int64_t>(std::max<int64_t>(need, idx->cap * 2), 1024);
     float* x32;
     __nv_bfloat16* x16;
@@ -89,6 +103,11 @@ int ensure_capacity(bfk_index* idx, int64_t need, cudaStream_t st) {
     idx->nrm = nrm;
     idx->cap = want;
     return 0;
+}
+
+int grow_for(bfk_index* idx, int64_t need, cudaStream_t st) {
+    std::lock_guard<std::mutex> lk(idx->mu);
+    return ensure_capacity(idx, need, st);
 }
 
 int ensure_workspace(bfk_index* idx, size_t bytes) {
@@ -145,6 +164,8 @@ static int make_index(int d, int metric, int device, int storage, bfk_index** ou
     if (cudaMalloc((void**)&idx->maxn, sizeof(unsigned int)) != cudaSuccess ||
         cudaMemset(idx->maxn, 0, sizeof(unsigned int)) != cudaSuccess ||
         cudaEventCreateWithFlags(&idx->ws_free, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&idx->rows_ready, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&idx->stage_done, cudaEventDisableTiming) != cudaSuccess ||
         cudaHostAlloc((void**)&idx->h_flag, sizeof(int), cudaHostAllocMapped) != cudaSuccess ||
         cudaHostGetDevicePointer((void**)&idx->h_flag_dev, idx->h_flag, 0) != cudaSuccess) {
         delete idx;
@@ -202,6 +223,7 @@ int launch_rows_to_f32(const bfk_index* idx, int64_t i0, int64_t n, float* out_d
 static int rows_out(const bfk_index* idx, int64_t i0, int64_t n, float* out, int out_is_device) {
     if (n == 0) return 0;
     cudaStream_t st = 0;
+    BFK_TRY(wait_rows_ready(idx, st));  // appends are only enqueued, possibly on a non-blocking stream
     if (idx->storage == BFK_STORE_F32) {
         BFK_CUDA(cudaMemcpy2DAsync(out, sizeof(float) * idx->d, idx->x32 + (size_t)i0 * idx->ld32,
                                    sizeof(float) * idx->ld32, sizeof(float) * idx->d, (size_t)n,
@@ -230,29 +252,57 @@ static int rows_out(const bfk_index* idx, int64_t i0, int64_t n, float* out, int
     return rc;
 }
 
+// Small host-side adds (the reference appends ONE row per call, indexer.py:41) go through the pinned staging
+// buffer the searches use: a cudaMemcpyAsync from pageable memory is staged by the driver anyway, synchronously.
+constexpr size_t STAGE_BYTES = 1 << 20;
+static char* stage_buffer(bfk_index* idx) {
+    if (!idx->h_stage && cudaHostAlloc((void**)&idx->h_stage, STAGE_BYTES, cudaHostAllocDefault) != cudaSuccess) {
+        cudaGetLastError();
+        idx->h_stage = nullptr;
+    }
+    return idx->h_stage;
+}
+
 static int add_rows(bfk_index* idx, const float* x, int64_t n, int x_is_device, cudaStream_t st) {
     if (n == 0) return 0;
+    std::lock_guard<std::mutex> lk(idx->mu);  // searches of other threads see the index before or after, never during
     BFK_TRY(search_tensor_finish(idx, st, nullptr));  // a deferred search still owns the workspace
     if (!x) return fail("add: null input");
     if (idx->ntotal + n > 0x7fffffffll) return fail("add: a single shard holds at most 2^31-1 rows");
     BFK_TRY(ensure_capacity(idx, idx->ntotal + n, st));
     if (x_is_device) {
+        BFK_TRY(wait_rows_ready(idx, st));  // the tail norms / maxn of an append on another stream
         BFK_TRY(launch_append_f32(idx, x, idx->d, n, st));
         idx->ntotal += n;
-        return 0;
+        return mark_rows_ready(idx, st);
     }
     // host rows: stage through device scratch in <= 64 MiB pieces
     const int64_t chunk = std::max<int64_t>(1, (64ll << 20) / (int64_t)(sizeof(float) * idx->d));
-    std::lock_guard<std::mutex> lk(idx->mu);
     BFK_TRY(ensure_workspace(idx, sizeof(float) * (size_t)std::min(chunk, n) * idx->d));
     BFK_CUDA(cudaStreamWaitEvent(st, idx->ws_free, 0));
+    BFK_TRY(wait_rows_ready(idx, st));
+    const size_t small_bytes = sizeof(float) * (size_t)n * idx->d;
+    char* pin = small_bytes <= STAGE_BYTES ? stage_buffer(idx) : nullptr;
     for (int64_t j = 0; j < n; j += chunk) {
         int64_t m = std::min(chunk, n - j);
-        BFK_CUDA(cudaMemcpyAsync(idx->ws.ptr, x + (size_t)j * idx->d, sizeof(float) * (size_t)m * idx->d,
-                                 cudaMemcpyHostToDevice, st));
+        const void* src = x + (size_t)j * idx->d;
+        if (pin) {
+            memcpy(pin, src, small_bytes);
+            src = pin;
+        }
+        BFK_CUDA(cudaMemcpyAsync(idx->ws.ptr, src, sizeof(float) * (size_t)m * idx->d, cudaMemcpyHostToDevice, st));
+        if (pin) BFK_CUDA(cudaEventRecord(idx->stage_done, st));
         BFK_TRY(launch_append_f32(idx, (const float*)idx->ws.ptr, idx->d, m, st));
         idx->ntotal += m;
-        // the staging buffer is reused by the next piece (and the caller owns x again on return)
+        // the staging buffers are reused by the next piece / the next call (and the caller owns x again on
+        // return): the copy out of them must have happened.  Rows that came through the pinned buffer only wait
+        // for that copy; their append kernel stays enqueued and `rows_ready` orders every later reader behind it.
+        if (pin) {
+            BFK_CUDA(cudaEventRecord(idx->ws_free, st));
+            BFK_TRY(mark_rows_ready(idx, st));
+            BFK_CUDA(cudaEventSynchronize(idx->stage_done));
+            return 0;
+        }
         BFK_CUDA(cudaStreamSynchronize(st));
     }
     BFK_CUDA(cudaEventRecord(idx->ws_free, st));
@@ -295,6 +345,9 @@ int bfk_free(bfk_index* idx) {
     if (idx->ws.ptr) cudaFree(idx->ws.ptr);
     if (idx->maxn) cudaFree(idx->maxn);
     if (idx->ws_free) cudaEventDestroy(idx->ws_free);
+    if (idx->rows_ready) cudaEventDestroy(idx->rows_ready);
+    if (idx->stage_done) cudaEventDestroy(idx->stage_done);
+    if (idx->prof_ring) cudaFree(idx->prof_ring);
     if (idx->h_flag) cudaFreeHost(idx->h_flag);
     if (idx->sel_buf) cudaFree(idx->sel_buf);
     if (idx->h_stage) cudaFreeHost(idx->h_stage);
@@ -311,21 +364,31 @@ int64_t bfk_ntotal(const bfk_index* idx) { return idx ? idx->ntotal : -1; }
 int bfk_reserve(bfk_index* idx, int64_t n) {
     if (!idx) return fail("null index");
     DeviceGuard g(idx->device);
+    std::lock_guard<std::mutex> lk(idx->mu);
     if (n <= idx->cap) return 0;
+    BFK_TRY(search_tensor_finish(idx, 0, nullptr));
     // exact-size allocation: callers reserve when they know the final size
     float* x32;
     __nv_bfloat16* x16;
     float* nrm;
     if (alloc_storage(idx, n, &x32, &x16, &nrm)) return fail("reserve: out of device memory");
     cudaStream_t st = 0;
-    if (idx->ntotal > 0) {
-        if (x32) BFK_CUDA(cudaMemcpyAsync(x32, idx->x32, sizeof(float) * (size_t)idx->ntotal * idx->ld32,
-                                          cudaMemcpyDeviceToDevice, st));
-        BFK_CUDA(cudaMemcpyAsync(x16, idx->x16, sizeof(__nv_bfloat16) * (size_t)idx->ntotal * idx->ld16,
-                                 cudaMemcpyDeviceToDevice, st));
-        BFK_CUDA(cudaMemcpyAsync(nrm, idx->nrm, sizeof(float) * (size_t)idx->ntotal, cudaMemcpyDeviceToDevice, st));
+    int rc = wait_rows_ready(idx, st);  // rows appended on another (non-blocking) stream must have landed
+    if (!rc && idx->ntotal > 0) {
+        cudaError_t e = cudaSuccess;
+        if (x32) e = cudaMemcpyAsync(x32, idx->x32, sizeof(float) * (size_t)idx->ntotal * idx->ld32, cudaMemcpyDeviceToDevice, st);
+        if (e == cudaSuccess)
+            e = cudaMemcpyAsync(x16, idx->x16, sizeof(__nv_bfloat16) * (size_t)idx->ntotal * idx->ld16, cudaMemcpyDeviceToDevice, st);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(nrm, idx->nrm, sizeof(float) * (size_t)idx->ntotal, cudaMemcpyDeviceToDevice, st);
+        if (e != cudaSuccess) rc = fail(std::string("reserve: copy failed: ") + cudaGetErrorString(e));
     }
-    BFK_CUDA(cudaStreamSynchronize(st));
+    if (!rc && cudaStreamSynchronize(st) != cudaSuccess) rc = fail("reserve: copy failed");
+    if (rc) {
+        if (x32) cudaFree(x32);
+        cudaFree(x16);
+        cudaFree(nrm);
+        return rc;
+    }
     free_storage(idx);
     idx->x32 = x32;
     idx->x16 = x16;
@@ -350,14 +413,16 @@ int bfk_add_pooled(bfk_index* idx, const void* tok, int tok_dtype, const void* m
     if (idx->ntotal + B > 0x7fffffffll) return fail("add: a single shard holds at most 2^31-1 rows");
     DeviceGuard g(idx->device);
     cudaStream_t st = (cudaStream_t)stream;
+    std::lock_guard<std::mutex> lk(idx->mu);
     BFK_TRY(search_tensor_finish(idx, st, nullptr));
     BFK_TRY(ensure_capacity(idx, idx->ntotal + B, st));
+    BFK_TRY(wait_rows_ready(idx, st));
     float* o32 = idx->x32 ? idx->x32 + (size_t)idx->ntotal * idx->ld32 : nullptr;
     __nv_bfloat16* o16 = idx->x16 + (size_t)idx->ntotal * idx->ld16;
     BFK_TRY(launch_pool(tok, tok_dtype, mask, mask_dtype, B, T, H, o32, idx->ld32, o16, idx->ld16,
                         idx->nrm + idx->ntotal, idx->maxn, st));
     idx->ntotal += B;
-    return 0;
+    return mark_rows_ready(idx, st);
 }
 
 int bfk_pool_normalize(const void* tok, int tok_dtype, const void* mask, int mask_dtype, int64_t B, int T,
@@ -464,6 +529,7 @@ static int search_locked(bfk_index* idx, const float* q, int64_t nq, int k, floa
     const int defer = (algo & BFK_ALGO_FLAG_DEFER) && io_is_device && !stats && !sel_dev;
     algo &= ~BFK_ALGO_FLAG_DEFER;
     BFK_TRY(search_tensor_finish(idx, st, nullptr));  // a deferred search nobody settled: settle it first
+    BFK_TRY(wait_rows_ready(idx, st));                 // rows appended on another stream are only enqueued there
 
     if (algo == BFK_ALGO_AUTO) {
         // The tensor path wins at every batch size, one query included: it streams the bf16 scan copy (half the
@@ -513,14 +579,10 @@ static int search_locked(bfk_index* idx, const float* q, int64_t nq, int k, floa
 
     // Small host-side searches go through one pinned staging buffer: a cudaMemcpyAsync from / to pageable memory
     // is staged by the driver anyway, synchronously and once per call (queries, D, I: three round trips).
-    constexpr size_t STAGE_BYTES = 1 << 20;
     const size_t q_bytes = sizeof(float) * (size_t)nq * idx->d;
     const size_t out_span = (size_t)((char*)(I_dev + (size_t)nq * k) - (char*)D_dev);  // D, padding, I: contiguous
     const bool staged = !io_is_device && q_bytes <= STAGE_BYTES && out_span <= STAGE_BYTES;
-    if (staged && !idx->h_stage && cudaHostAlloc((void**)&idx->h_stage, STAGE_BYTES, cudaHostAllocDefault) != cudaSuccess) {
-        cudaGetLastError();
-        idx->h_stage = nullptr;
-    }
+    if (staged) stage_buffer(idx);
     if (staged && idx->h_stage) {
         memcpy(idx->h_stage, q, q_bytes);
         if (ldq != idx->d) BFK_CUDA(cudaMemsetAsync(q_dev, 0, sizeof(float) * (size_t)nq * ldq, st));
@@ -554,26 +616,43 @@ static int search_locked(bfk_index* idx, const float* q, int64_t nq, int k, floa
         BFK_CUDA(cudaEventCreate(&ev0));
         BFK_CUDA(cudaEventCreate(&ev1));
     }
+    // A host-side tensor search is enqueued like a deferred one: the (D, I) copy-out queues up behind K5 and the
+    // host waits ONCE, then looks at the certificate count (a re-run of uncertified queries repeats the copy-out)
+    // -- instead of waiting for the count first and for the copy afterwards.
+    const bool host_defer = !io_is_device && algo == BFK_ALGO_TENSOR && !stats && !sel_dev;
     int rc;
     if (algo == BFK_ALGO_TENSOR) {
-        rc = search_tensor(idx, q_dev, ldq, nq, k, D_out, I_out, id_offset, tail, tail_avail, st, stats, ev0, ev1, defer);
+        rc = search_tensor(idx, q_dev, ldq, nq, k, D_out, I_out, id_offset, tail, tail_avail, st, stats, ev0, ev1,
+                           (defer || host_defer) ? 1 : 0);
     } else {
         rc = search_exact(idx, q_dev, ldq, nq, k, D_out, I_out, id_offset, tail, tail_avail, st, stats, ev0, ev1);
     }
     const bool staged_out = staged && idx->h_stage;
-    if (!rc && !io_is_device) {
+    auto copy_out = [&]() -> int {
         if (staged_out) {
             if (cudaMemcpyAsync(idx->h_stage, D_dev, out_span, cudaMemcpyDeviceToHost, st) != cudaSuccess)
-                rc = fail("search: D2H copy failed");
+                return fail("search: D2H copy failed");
         } else if (cudaMemcpyAsync(D, D_dev, sizeof(float) * (size_t)nq * k, cudaMemcpyDeviceToHost, st) != cudaSuccess ||
                    cudaMemcpyAsync(I, I_dev, sizeof(int64_t) * (size_t)nq * k, cudaMemcpyDeviceToHost, st) != cudaSuccess) {
-            rc = fail("search: D2H copy failed");
+            return fail("search: D2H copy failed");
         }
-    }
+        return 0;
+    };
+    if (!rc && !io_is_device) rc = copy_out();
     if (!rc && cudaEventRecord(idx->ws_free, st) != cudaSuccess) rc = fail("search: event record failed");
     if (!rc && (!io_is_device || stats)) {
         cudaError_t e = cudaStreamSynchronize(st);
         if (e != cudaSuccess) rc = fail(std::string("search: kernel execution failed: ") + cudaGetErrorString(e));
+        if (!rc && st == idx->rows_stream) idx->rows_pending = false;
+    }
+    if (!rc && host_defer) {
+        int64_t rewritten = 0;
+        rc = search_tensor_finish(idx, st, &rewritten);  // the stream is idle: reads the count, re-runs if needed
+        if (!rc && rewritten > 0) {
+            rc = copy_out();
+            if (!rc && cudaEventRecord(idx->ws_free, st) != cudaSuccess) rc = fail("search: event record failed");
+            if (!rc && cudaStreamSynchronize(st) != cudaSuccess) rc = fail("search: kernel execution failed");
+        }
     }
     if (!rc && staged_out) {
         memcpy(D, idx->h_stage, sizeof(float) * (size_t)nq * k);
@@ -598,6 +677,52 @@ int bfk_search_finish(bfk_index* idx, void* stream, int64_t* n_rewritten) {
     return search_tensor_finish(idx, (cudaStream_t)stream, n_rewritten);
 }
 
+int bfk_profile_begin(bfk_index* idx) {
+    if (!idx) return fail("null index");
+    DeviceGuard g(idx->device);
+    std::lock_guard<std::mutex> lk(idx->mu);
+    constexpr int64_t CAP = 1 << 16;
+    if (!idx->prof_ring) {
+        BFK_CUDA(cudaMalloc((void**)&idx->prof_ring, sizeof(unsigned long long) * 2 * CAP));
+        idx->prof_cap = CAP;
+    }
+    std::vector<unsigned long long> init((size_t)2 * idx->prof_cap);
+    for (int64_t i = 0; i < idx->prof_cap; i++) {
+        init[(size_t)2 * i] = ~0ull;  // earliest start: atomicMin
+        init[(size_t)2 * i + 1] = 0;  // latest end: atomicMax
+    }
+    BFK_CUDA(cudaMemcpy(idx->prof_ring, init.data(), init.size() * sizeof(unsigned long long), cudaMemcpyHostToDevice));
+    idx->prof_used = 0;
+    idx->prof_on = true;
+    return 0;
+}
+
+int bfk_profile_end(bfk_index* idx, double* scan_ms_sum, int64_t* n_scans) {
+    if (!idx) return fail("null index");
+    if (scan_ms_sum) *scan_ms_sum = 0.0;
+    if (n_scans) *n_scans = 0;
+    DeviceGuard g(idx->device);
+    std::lock_guard<std::mutex> lk(idx->mu);
+    if (!idx->prof_on) return fail("profile_end without profile_begin");
+    idx->prof_on = false;
+    BFK_CUDA(cudaDeviceSynchronize());
+    std::vector<unsigned long long> h((size_t)2 * idx->prof_used);
+    if (idx->prof_used)
+        BFK_CUDA(cudaMemcpy(h.data(), idx->prof_ring, h.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+    double ns = 0.0;
+    int64_t n = 0;
+    for (int64_t i = 0; i < idx->prof_used; i++) {
+        const unsigned long long t0 = h[(size_t)2 * i], t1 = h[(size_t)2 * i + 1];
+        if (t0 != ~0ull && t1 >= t0) {
+            ns += (double)(t1 - t0);
+            n++;
+        }
+    }
+    if (scan_ms_sum) *scan_ms_sum = ns * 1e-6;
+    if (n_scans) *n_scans = n;
+    return 0;
+}
+
 const void* bfk_search_pending_nflag_ptr(bfk_index* idx) { return idx ? (const void*)search_tensor_pending_nflag(idx) : nullptr; }
 
 int bfk_reset(bfk_index* idx) {
@@ -606,6 +731,7 @@ int bfk_reset(bfk_index* idx) {
     std::lock_guard<std::mutex> lk(idx->mu);
     BFK_TRY(search_tensor_finish(idx, 0, nullptr));
     BFK_CUDA(cudaDeviceSynchronize());
+    idx->rows_pending = false;
     idx->ntotal = 0;
     BFK_CUDA(cudaMemset(idx->maxn, 0, sizeof(unsigned int)));
     return 0;
@@ -617,6 +743,7 @@ int bfk_reconstruct(const bfk_index* idx, int64_t i0, int64_t n, float* out, int
     if (n == 0) return 0;
     if (!out) return fail("reconstruct: null output");
     DeviceGuard g(idx->device);
+    std::lock_guard<std::mutex> lk(idx->mu);
     return rows_out(idx, i0, n, out, out_is_device);
 }
 
@@ -635,6 +762,7 @@ int bfk_remove_ids(bfk_index* idx, const int64_t* ids, int64_t n, int64_t* nremo
     if (rm.empty()) return 0;
     BFK_TRY(search_tensor_finish(idx, 0, nullptr));
     BFK_CUDA(cudaDeviceSynchronize());
+    idx->rows_pending = false;
     // IndexFlatCodes::remove_ids keeps the surviving rows in order: move each kept segment down
     // through fresh buffers (device copies must not overlap)
     float* x32;
@@ -688,6 +816,7 @@ int bfk_serialize(const bfk_index* idx, uint8_t* buf, int64_t buf_len) {
     if (!idx || !buf) return fail("serialize: null argument");
     if (buf_len < bfk_serialized_size(idx)) return fail("serialize: buffer too small");
     DeviceGuard g(idx->device);
+    std::lock_guard<std::mutex> lk(idx->mu);
     put_header(buf, idx->d, idx->ntotal, idx->metric);
     return rows_out(idx, 0, idx->ntotal, (float*)(buf + HEADER_BYTES), 0);
 }
@@ -714,6 +843,7 @@ int bfk_deserialize(const uint8_t* buf, int64_t len, int device, int storage, bf
 int bfk_write(const bfk_index* idx, const char* path) {
     if (!idx || !path) return fail("write_index: null argument");
     DeviceGuard g(idx->device);
+    std::lock_guard<std::mutex> lk(idx->mu);
     FILE* f = fopen(path, "wb");
     if (!f) return fail(std::string("could not open ") + path + " for writing");
     uint8_t h[HEADER_BYTES];
@@ -781,7 +911,7 @@ static int search_exact(bfk_index* idx, const float* q_dev, int ldq, int64_t nq,
     if (stats) cudaEventRecord(ev0, st);
     for (int64_t q0 = 0; q0 < nq;) {
         int g = (int)std::min<int64_t>(nq - q0, 8);
-        BFK_TRY(launch_scan_exact(idx, q_dev + (size_t)q0 * ldq, ldq, g, k, part + (size_t)q0 * nparts * k, nparts, st));
+        BFK_TRY(launch_scan_exact(idx, q_dev + (size_t)q0 * ldq, ldq, g, k, part + (size_t)q0 * nparts * k, nparts, st, idx->sel));
         launches++;
         q0 += g;
     }

@@ -77,6 +77,9 @@ extern "C" int bfk_search_noalloc(const bfk_index* idx, const float* q_dev, int6
     DeviceGuard g(idx->device);
     if (!g.ok) return fail("cudaSetDevice failed");
     std::lock_guard<std::mutex> lk(g_noalloc_mu);
+    // the index may be growing in another thread (add regrows and frees the row storage): read its
+    // pointers and row count under its own mutex, like every other search (a host mutex, no allocation)
+    std::lock_guard<std::mutex> lk_idx(idx->mu);
 
     size_t bytes = 0;
     int nparts = 0;
@@ -89,7 +92,9 @@ extern "C" int bfk_search_noalloc(const bfk_index* idx, const float* q_dev, int6
 
     cudaStream_t st = (cudaStream_t)stream;
     // the scan reads q with row stride d and zero-fills the padding columns itself
-    BFK_TRY(launch_scan_exact(idx, q_dev, idx->d, (int)nq, (int)k, scratch, nparts, st));
+    BFK_TRY(wait_rows_ready(idx, st));  // cudaStreamWaitEvent on an existing event: no allocation
+    // no selector: the bitmap of a bfk_search_sel running in another thread is not this call's business
+    BFK_TRY(launch_scan_exact(idx, q_dev, idx->d, (int)nq, (int)k, scratch, nparts, st, nullptr));
     BFK_TRY(launch_select(scratch, (int64_t)nparts * k, nq, (int)k, idx->metric, 0, D_dev, I_dev, k, st));
     return 0;
 }

@@ -298,9 +298,9 @@ static int plan_scan_exact(const bfk_index* idx, int nq, int k, ScanExactPlan* p
     while (R > 1 && SE_CWARPS * R * row_bytes > 48 * 1024) R >>= 1;
     const int TR = SE_CWARPS * R;
     const int cap = next_pow2(k + 2 * TR);
-    int group = 8;
-    while (group > nq) group >>= 1;
-    if (group < 1) group = 1;
+    // one pass serves up to 8 queries; 3 and 5..7 queries round UP to the next template size (the kernel
+    // masks the missing ones) instead of splitting into two corpus passes
+    int group = std::min(8, next_pow2(std::max(nq, 1)));
     for (;; group >>= 1) {
         size_t fixed = (size_t)group * ld * 4 + (size_t)group * cap * 8 + group * 8 + 2 * SE_MAX_STAGES * 8 + group * 4 + 128;
         size_t tile = (size_t)TR * row_bytes;
@@ -364,7 +364,7 @@ static int launch_nq(int NQ, int R, const ScanExactParams& p, size_t smem, int g
 
 // nq <= 8 queries; part is [nq][nparts][k]
 int launch_scan_exact(const bfk_index* idx, const float* q_dev, int ldq, int nq, int k, uint64_t* part, int nparts,
-                      cudaStream_t st) {
+                      cudaStream_t st, const unsigned char* sel) {
     ScanExactPlan pl;
     BFK_TRY(plan_scan_exact(idx, nq, k, &pl));
     if (pl.grid != nparts) {
@@ -394,7 +394,7 @@ int launch_scan_exact(const bfk_index* idx, const float* q_dev, int ldq, int nq,
         p.stages = sub.stages;
         p.part = part + (size_t)q0 * nparts * k;
         p.nparts = nparts;
-        p.sel = idx->sel;
+        p.sel = sel;
         const bool l2 = idx->metric == BFK_METRIC_L2;
         int rc;
         if (f32)

@@ -85,6 +85,8 @@ struct TcParams {
     int use_bias;        // per-row bias is fetched (L2 norms, or the selector bias for either metric)
     int csize;           // 1: every CTA on its own; 2: CTA pairs (cta_group::2) -- two query tiles share one
                          // corpus stream, each CTA stages only half of every corpus tile
+    unsigned long long* tstamp;  // optional [2]: [0] = earliest CTA start, [1] = latest CTA end (globaltimer ns), else nullptr
+    int prepass;         // J == 1: tile 0 is first read for each thread's smallest key only (see the epilogue)
     uint64_t* pend_g;    // global pending lists [grid][TC_BUFCAP][256], or nullptr: lists live in shared memory.
                          // Long streams (several query tiles) append rarely and need the 32 KiB for a 4th
                          // corpus stage instead; short streams (nq <= 128) append often and keep them on chip.
@@ -182,6 +184,12 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
     uint32_t crank = 0u;
     if constexpr (PAIR) crank = cluster_ctarank();
     const bool leader = crank == 0;
+    // Everything above (barriers, TMEM, descriptor prefetch) touched no global memory and may have run while
+    // prep_queries_kernel was still finishing (programmatic dependent launch); from here on its outputs
+    // (bf16 queries, slots, margins) are read.  K5 may be scheduled onto SMs as CTAs of this grid retire.
+    pdl_wait();
+    pdl_launch_dependents();
+    if (p.tstamp != nullptr && tid == 0) atomicMin(p.tstamp, globaltimer_ns());
 
     if (warp == 0) {
         // ===================== TMA producer =====================
@@ -368,7 +376,8 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
         auto refresh_thr = [&]() {
             if (active) {
                 const float g = *reinterpret_cast<volatile float*>(thr_sh + row);
-                thr = fminf(skey[KP - 1], g < FLT_MAX ? g + qmargin : FLT_MAX);
+                // both terms only fall over time; the min with the old value keeps the tile-0 bound until they pass it
+                thr = fminf(thr, fminf(skey[KP - 1], g < FLT_MAX ? g + qmargin : FLT_MAX));
             }
         };
         auto flush = [&]() {
@@ -408,6 +417,55 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
             const uint32_t taddr = tmem_base + ((uint32_t)(((warp - 4) & 3) * 32) << 16) + a * TC_BN + half * 128;
             const uint32_t col0 = (uint32_t)(t * TC_BN) + half * 128;
             const float* bias = bias_s + a * TC_BN + half * 128;
+            if (tcount == 0 && p.prepass) {
+                // Tile 0, first reading: only the thread's smallest key, published to its group's slot.  With
+                // J == 1 a slot is the smallest key any stream of the group has seen, so once the G >= k slots of
+                // a query are set, max(slots) bounds its k-th best key -- from 256 rows of EVERY stream of the
+                // grid rather than this thread's own 128.  Without it every thread starts at +inf: its first 16
+                // columns all survive, the list only learns over the tile, and with 32 different queries per
+                // warp nearly every group of tile 0 walks the slow path (49 appends and 4 flushes per thread).
+                float mn = FLT_MAX;
+                uint32_t r0[16];
+#pragma unroll 1
+                for (int sc = 0; sc < 8; sc++) {
+                    tmem_ld_32x16(taddr + sc * 16, r0);
+                    tmem_ld_wait();
+                    const float4* b4 = reinterpret_cast<const float4*>(bias + sc * 16);
+#pragma unroll
+                    for (int j4 = 0; j4 < 4; j4++) {
+                        const float4 b = b4[j4];
+                        mn = fminf(mn, fminf(fminf(fmaf(scale, __uint_as_float(r0[4 * j4 + 0]), b.x),
+                                                   fmaf(scale, __uint_as_float(r0[4 * j4 + 1]), b.y)),
+                                             fminf(fmaf(scale, __uint_as_float(r0[4 * j4 + 2]), b.z),
+                                                   fmaf(scale, __uint_as_float(r0[4 * j4 + 3]), b.w))));
+                    }
+                }
+                if (active && mn < FLT_MAX) atomicMin(my_slots + grp, f2ord(mn));
+                // the other streams reach this point within a microsecond or two of each other (every CTA's
+                // first tile comes out of the same HBM burst): poll the query's slots for a bounded time
+                const unsigned int unset = f2ord(FLT_MAX);
+                const long long t0 = clock64();
+                bool got = !active;
+                for (;;) {
+                    if (!got) {
+                        const uint4* sl = reinterpret_cast<const uint4*>(my_slots);
+                        unsigned int m = 0;
+                        for (int i = 0; i < p.NS / 4; i++) {
+                            uint4 v;
+                            asm volatile("ld.global.cg.v4.u32 {%0, %1, %2, %3}, [%4];"
+                                         : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+                                         : "l"(sl + i));
+                            m = max(max(m, v.x), max(max(v.y, v.z), v.w));
+                        }
+                        if (m < unset) {
+                            thr = fminf(thr, ord2f(m) + qmargin);
+                            got = true;
+                        }
+                    }
+                    const bool more = !got && (clock64() - t0 < 6000);  // ~3 us, then carry on without the bound
+                    if (!__any_sync(0xffffffffu, more)) break;
+                }
+            }
             // 16 columns at a time, kept as a rolled loop (two register sets, next load in flight while
             // the current set is filtered): the fully unrolled form of this loop was 58 KB of SASS and
             // stalled on instruction fetch
@@ -508,17 +566,19 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
         if constexpr (PAIR) tmem_dealloc2<512>(tmem_base);
         else tmem_dealloc<512>(tmem_base);
     }
+    if (p.tstamp != nullptr && tid == 0) atomicMax(p.tstamp + 1, globaltimer_ns());
 }
 
 // queries fp32 [nq, ldq] -> bf16 [nq_pad, ld16] (zero padded rows and columns) + ||q||^2
 __global__ void __launch_bounds__(256) prep_queries_kernel(const float* __restrict__ q, int ldq, int d, int64_t nq,
                                                            int64_t nq_pad, __nv_bfloat16* __restrict__ q16, int ld16,
                                                            float* __restrict__ qn, const unsigned int* __restrict__ maxn,
-                                                           float c_round, int is_l2, float* __restrict__ qmargin,
+                                                           float c_round, float c_abs, int is_l2, float* __restrict__ qmargin,
                                                            unsigned int* __restrict__ slots, int NS,
                                                            int* __restrict__ flags) {
     const int lane = threadIdx.x & 31;
     const int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    pdl_launch_dependents();  // the scan's prologue may start now; it waits for this grid before reading anything
     if (blockIdx.x == 0 && threadIdx.x == 0) {
         flags[0] = 0;  // uncertified-query count of this pass (K5 appends)
         flags[-1] = 0; // K5's CTA ticket (the last CTA to finish publishes the count to the host)
@@ -536,7 +596,7 @@ __global__ void __launch_bounds__(256) prep_queries_kernel(const float* __restri
         qn[row] = ss;
         // 2*eps in key space: |<q,x> - <bf16 q, bf16 x>| <= c_round ||q|| max||x||; L2 keys carry 2x that
         const float mx = __uint_as_float(*maxn);
-        qmargin[row] = (is_l2 ? 4.f : 2.f) * c_round * sqrtf(ss * mx) + 1e-6f * (ss + mx);
+        qmargin[row] = (is_l2 ? 4.f : 2.f) * c_round * sqrtf(ss * mx) + c_abs * (ss + mx);
     }
     for (int i = lane; i < NS; i += 32) slots[row * NS + i] = f2ord(FLT_MAX);
 }
@@ -644,6 +704,7 @@ __global__ void __launch_bounds__(RR_THREADS) rerank_kernel(const RerankParams p
     const int64_t q = blockIdx.x;
     const int64_t M = (int64_t)p.S * p.KP;
     const uint64_t* src = p.out_cand + q * M;
+    pdl_wait();  // launched behind the scan with programmatic serialization: its lists are complete from here on
     const long long rr_t0 = p.dbg ? clock64() : 0;
 #define RR_MARK(i) do { if (p.dbg && blockIdx.x == 0 && tid == 0) p.dbg[i] = (unsigned long long)(clock64() - rr_t0); } while (0)
 
@@ -663,11 +724,30 @@ __global__ void __launch_bounds__(RR_THREADS) rerank_kernel(const RerankParams p
 
     // ---- keep only candidates with approximate key <= T (a certified answer never needs the rest:
     //      the cut A_k + 2*eps must lie below T), then sort the few survivors ----
-    for (int64_t i = tid; i < M; i += RR_THREADS) {
-        const uint64_t c = src[i];
-        if (c != COMP_EMPTY && ord2f((uint32_t)(c >> 32)) <= tmin) {
-            const int slot = atomicAdd(&cnt_s, 1);
-            if (slot < TC_MERGE_N) buf[slot] = c;
+    {
+        // two candidates per 16-byte load, four loads in flight per thread before the first is looked at
+        // (KP is 16 or 32, so a query's M = S * KP candidates are an even count at a 16-byte aligned address)
+        const ulonglong2* src2 = reinterpret_cast<const ulonglong2*>(src);
+        const int64_t M2 = M >> 1;
+        const uint32_t tmin_ord = f2ord(tmin);
+        auto keep = [&](uint64_t c) {
+            if (c != COMP_EMPTY && (uint32_t)(c >> 32) <= tmin_ord) {
+                const int slot = atomicAdd(&cnt_s, 1);
+                if (slot < TC_MERGE_N) buf[slot] = c;
+            }
+        };
+        for (int64_t i0 = tid; i0 < M2; i0 += 4 * RR_THREADS) {
+            ulonglong2 v[4];
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                const int64_t i = i0 + (int64_t)u * RR_THREADS;
+                v[u] = i < M2 ? __ldcg(src2 + i) : make_ulonglong2(COMP_EMPTY, COMP_EMPTY);
+            }
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                keep(v[u].x);
+                keep(v[u].y);
+            }
         }
     }
     __syncthreads();
@@ -841,6 +921,23 @@ int make_tmap(CUtensorMap* m, const void* base, int64_t rows, int ld, int box_ro
                      CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return fail("cuTensorMapEncodeTiled failed with code " + std::to_string((int)r));
+    return 0;
+}
+
+// The two tensor maps of a pass change only when the storage is regrown, rows are appended or the batch size
+// changes: they are re-encoded (a driver call each) only then.
+static int cached_tmap(bfk_index* idx, int slot, const void* base, int64_t rows, int box_rows, const CUtensorMap** out) {
+    bfk_index::TmapSlot& c = idx->tmap[slot];
+    static_assert(sizeof(CUtensorMap) <= sizeof(c.map), "tensor map cache slot too small");
+    CUtensorMap* m = reinterpret_cast<CUtensorMap*>(c.map);
+    if (c.base != base || c.rows != rows || c.box_rows != box_rows) {
+        c.base = nullptr;
+        BFK_TRY(make_tmap(m, base, rows, idx->ld16, box_rows));
+        c.base = base;
+        c.rows = rows;
+        c.box_rows = box_rows;
+    }
+    *out = m;
     return 0;
 }
 
@@ -1037,9 +1134,18 @@ static int max_cluster_ctas(int csize, size_t smem) {
     return n * csize;
 }
 
+// BFK_TC_PDL=0 launches the three kernels of a pass strictly one after the other
+static bool pdl_enabled() {
+    static const bool on = [] {
+        const char* e = getenv("BFK_TC_PDL");
+        return e ? atoi(e) != 0 : true;
+    }();
+    return on;
+}
+
 template <int KP, bool PAIR, bool DBG>
 static int launch_scan_tc(const CUtensorMap& tmQ, const CUtensorMap& tmX, const TcParams& p, const TcPlan& pl,
-                          cudaStream_t st) {
+                          cudaStream_t st, bool pdl) {
     auto kern = scan_tc_kernel<KP, PAIR, DBG>;
     static bool attr_set[64] = {false};  // the attribute is per device
     int dev = 0;
@@ -1053,13 +1159,17 @@ static int launch_scan_tc(const CUtensorMap& tmQ, const CUtensorMap& tmX, const 
     cfg.blockDim = dim3(TC_THREADS);
     cfg.dynamicSmemBytes = pl.smem;
     cfg.stream = st;
-    cudaLaunchAttribute attr[1];
+    cudaLaunchAttribute attr[2];
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = (unsigned)pl.csize;
     attr[0].val.clusterDim.y = 1;
     attr[0].val.clusterDim.z = 1;
+    // programmatic dependent launch behind prep_queries_kernel: the prologue (barriers, TMEM, descriptor
+    // prefetch) overlaps its tail; the kernel executes griddepcontrol.wait before it reads prep's outputs
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[1].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
-    cfg.numAttrs = 1;
+    cfg.numAttrs = pdl ? 2 : 1;
     BFK_CUDA(cudaLaunchKernelEx(&cfg, kern, tmQ, tmX, p));
     BFK_CUDA(cudaGetLastError());
     return 0;
@@ -1114,16 +1224,28 @@ static int tc_pass(bfk_index* idx, const float* qc, int ldq, int64_t nqc, int k,
             pl = single;
         }
     }
-    // |<q,x> - <bf16(q),bf16(x)>| <= (2u + u^2) ||q|| ||x|| with u = 2^-9 when both operands are
-    // rounded, u ||q|| ||x|| when the corpus is stored in bf16; + 2^-14 for tensor-core accumulation
-    const float c_round = (idx->storage == BFK_STORE_F32 ? 1.01f / 256.f : 1.01f / 512.f) + 1.0f / 16384.f;
+    // eps: |<q,x> - acc| <= c_round ||q|| ||x||, acc = what the tensor pipe returns for <bf16 q, bf16 x>.
+    //   rounding of the operands: (2u + u^2) with u = 2^-9 when both are rounded to bf16, u when the corpus is
+    //     stored in bf16 (the re-score then reads the same rounded rows);
+    //   accumulation: the products of two bf16 numbers are exact in fp32; the pipe adds ld16 of them in fp32.
+    //     Assuming nothing better than truncation (round toward zero, one ulp = 2^-23 relative per addition, the
+    //     weaker of the two rounding modes it could use), the sum is off by at most ld16 * 2^-23 * sum|q_i x_i|
+    //     <= ld16 * 2^-23 ||q|| ||x||.  That is 2^-14 at ld16 = 512 -- the constant used for every d before --
+    //     and 2^-12 at BFK_MAX_D = 2048, so it is kept as a floor and grows with the row length above it.
+    const float c_acc = (float)std::max(idx->ld16, 512) / 8388608.f;
+    const float c_round = (idx->storage == BFK_STORE_F32 ? 1.01f / 256.f : 1.01f / 512.f) + c_acc;
+    // the fp32 re-score itself (ld16/32 terms per lane, then a 5-step butterfly) and the key's own fma round
+    // with at most (ld16/32 + 8) half-ulps of a value that is at most 2 (||q||^2 + ||x||^2)
+    const float c_abs = (float)(idx->ld16 / 32 + 8) * 2.f / 16777216.f;
     prep_queries_kernel<<<(unsigned)((pl.nq_pad + 7) / 8), 256, 0, st>>>(qc, ldq, idx->d, nqc, pl.nq_pad, w.q16, idx->ld16,
-                                                                        w.qn, idx->maxn, c_round, l2 ? 1 : 0, w.qmargin,
+                                                                        w.qn, idx->maxn, c_round, c_abs, l2 ? 1 : 0, w.qmargin,
                                                                         w.slots, pl.NS, w.flags);
     BFK_CUDA(cudaGetLastError());
-    CUtensorMap tmQ, tmX;
-    BFK_TRY(make_tmap(&tmQ, w.q16, pl.nq_pad, idx->ld16, TC_BM));
-    BFK_TRY(make_tmap(&tmX, idx->x16, idx->ntotal, idx->ld16, TC_BN / pl.csize));  // box = this CTA's slice
+    const CUtensorMap *tmQp, *tmXp;
+    BFK_TRY(cached_tmap(idx, 1, w.q16, pl.nq_pad, TC_BM, &tmQp));
+    BFK_TRY(cached_tmap(idx, 0, idx->x16, idx->ntotal, TC_BN / pl.csize, &tmXp));  // box = this CTA's slice
+    const CUtensorMap& tmQ = *tmQp;
+    const CUtensorMap& tmX = *tmXp;
     TcParams p;
     p.nrm = idx->sel_bias ? idx->sel_bias : idx->nrm;  // a selector search masks rows through the bias
     p.use_bias = (l2 || idx->sel_bias) ? 1 : 0;
@@ -1145,6 +1267,14 @@ static int tc_pass(bfk_index* idx, const float* qc, int ldq, int64_t nqc, int k,
     p.out_thr = w.out_thr;
     p.pend_g = pl.pend_global ? w.pend_g : nullptr;
     p.csize = pl.csize;
+    p.prepass = (pl.J == 1 && pl.G >= k && 2 * pl.S >= pl.G) ? 1 : 0;
+    static const bool prepass_on = [] {
+        const char* e = getenv("BFK_TC_PREPASS");
+        return e ? atoi(e) != 0 : true;
+    }();
+    if (!prepass_on) p.prepass = 0;
+    p.tstamp = nullptr;
+    if (idx->prof_on && idx->prof_ring && idx->prof_used < idx->prof_cap) p.tstamp = idx->prof_ring + 2 * idx->prof_used++;
     static const bool dbg_on = getenv("BFK_TC_DEBUG") != nullptr;
     static const bool parked = getenv("BFK_TC_PARKED") != nullptr;
     p.dbg = dbg_on ? w.dbg : nullptr;
@@ -1155,16 +1285,18 @@ static int tc_pass(bfk_index* idx, const float* qc, int ldq, int64_t nqc, int k,
     // separate instantiation: the single MMA-issuing thread paces the tensor pipe, and even predicated-off
     // diagnostics in its loop cost issue slots
     const bool dbgk = dbg_on || parked;
+    // an event recorded between two kernels keeps them from overlapping: timed / instrumented passes run serially
+    const bool pdl = pdl_enabled() && !ev0 && !ev1 && !dbg_on;
     if (pl.KP == 16) {
-        if (pl.csize == 2 && dbgk) BFK_TRY((launch_scan_tc<16, true, true>(tmQ, tmX, p, pl, st)));
-        else if (pl.csize == 2) BFK_TRY((launch_scan_tc<16, true, false>(tmQ, tmX, p, pl, st)));
-        else if (dbgk) BFK_TRY((launch_scan_tc<16, false, true>(tmQ, tmX, p, pl, st)));
-        else BFK_TRY((launch_scan_tc<16, false, false>(tmQ, tmX, p, pl, st)));
+        if (pl.csize == 2 && dbgk) BFK_TRY((launch_scan_tc<16, true, true>(tmQ, tmX, p, pl, st, pdl)));
+        else if (pl.csize == 2) BFK_TRY((launch_scan_tc<16, true, false>(tmQ, tmX, p, pl, st, pdl)));
+        else if (dbgk) BFK_TRY((launch_scan_tc<16, false, true>(tmQ, tmX, p, pl, st, pdl)));
+        else BFK_TRY((launch_scan_tc<16, false, false>(tmQ, tmX, p, pl, st, pdl)));
     } else {
-        if (pl.csize == 2 && dbgk) BFK_TRY((launch_scan_tc<32, true, true>(tmQ, tmX, p, pl, st)));
-        else if (pl.csize == 2) BFK_TRY((launch_scan_tc<32, true, false>(tmQ, tmX, p, pl, st)));
-        else if (dbgk) BFK_TRY((launch_scan_tc<32, false, true>(tmQ, tmX, p, pl, st)));
-        else BFK_TRY((launch_scan_tc<32, false, false>(tmQ, tmX, p, pl, st)));
+        if (pl.csize == 2 && dbgk) BFK_TRY((launch_scan_tc<32, true, true>(tmQ, tmX, p, pl, st, pdl)));
+        else if (pl.csize == 2) BFK_TRY((launch_scan_tc<32, true, false>(tmQ, tmX, p, pl, st, pdl)));
+        else if (dbgk) BFK_TRY((launch_scan_tc<32, false, true>(tmQ, tmX, p, pl, st, pdl)));
+        else BFK_TRY((launch_scan_tc<32, false, false>(tmQ, tmX, p, pl, st, pdl)));
     }
     if (ev1) cudaEventRecord(ev1, st);
     if (p.dbg) {  // diagnostics only: per-role wait cycles averaged over the CTAs
@@ -1215,8 +1347,20 @@ static int tc_pass(bfk_index* idx, const float* qc, int ldq, int64_t nqc, int k,
     r.flag_list = w.flags + 1;
     r.h_nflag = idx->h_flag_dev;
     r.dbg = p.dbg ? w.dbg + (size_t)pl.grid * 8 + 8 * 64 : nullptr;
-    if ((int64_t)r.S * r.KP <= 1024 && k <= 32) rerank_kernel<128><<<(unsigned)nqc, 128, 0, st>>>(r);
-    else rerank_kernel<512><<<(unsigned)nqc, 512, 0, st>>>(r);
+    {
+        const bool small = (int64_t)r.S * r.KP <= 1024 && k <= 32;
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3((unsigned)nqc);
+        cfg.blockDim = dim3(small ? 128 : 512);
+        cfg.stream = st;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = pdl ? 1 : 0;
+        if (small) BFK_CUDA(cudaLaunchKernelEx(&cfg, rerank_kernel<128>, r));
+        else BFK_CUDA(cudaLaunchKernelEx(&cfg, rerank_kernel<512>, r));
+    }
     BFK_CUDA(cudaGetLastError());
     if (r.dbg) {
         unsigned long long h[16];
@@ -1293,7 +1437,7 @@ static int tc_resolve(bfk_index* idx, const TcPending& c, cudaStream_t st, int64
         for (int j = 0; j < g; j++)
             BFK_CUDA(cudaMemcpyAsync(w.fb_q + (size_t)j * c.ldq, c.qc + (size_t)list[g0 + j] * c.ldq, sizeof(float) * c.ldq,
                                      cudaMemcpyDeviceToDevice, st));
-        BFK_TRY(launch_scan_exact(idx, w.fb_q, c.ldq, g, c.k, w.fb_part, c.fb_nparts, st));
+        BFK_TRY(launch_scan_exact(idx, w.fb_q, c.ldq, g, c.k, w.fb_part, c.fb_nparts, st, idx->sel));
         BFK_TRY(launch_select(w.fb_part, (int64_t)c.fb_nparts * c.k, g, c.k, idx->metric, c.id_offset, w.fb_D, w.fb_I, c.k, st));
         *launches += 2;
         for (int j = 0; j < g; j++) {

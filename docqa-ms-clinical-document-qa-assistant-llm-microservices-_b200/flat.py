@@ -284,6 +284,16 @@ class IndexFlat:
         _lib.check(self._L.bfk_search_finish(self._h, _torch_stream(self.device), ctypes.byref(n)))
         return int(n.value)
 
+    def profile_begin(self) -> None:
+        """Extension (measurement aid): start stamping every tensor-scan launch with the device clock."""
+        _lib.check(self._L.bfk_profile_begin(self._h))
+
+    def profile_end(self) -> tuple[float, int]:
+        """-> (summed scan-kernel milliseconds, number of scan launches) since profile_begin; waits for the GPU."""
+        ms, n = ctypes.c_double(0.0), ctypes.c_int64(0)
+        _lib.check(self._L.bfk_profile_end(self._h, ctypes.byref(ms), ctypes.byref(n)))
+        return float(ms.value), int(n.value)
+
     def reconstruct(self, key, x=None):
         key = int(key)
         if x is None:

@@ -22,9 +22,14 @@
  *     is set, which postpones that to bfk_search_finish; the fp32 scan never waits.
  *   - the index owns all corpus storage; inputs are borrowed for the call; outputs
  *     are caller-allocated.
- *   - concurrent bfk_search on one index is serialised internally; bfk_add /
- *     bfk_remove_ids / bfk_reset must not run concurrently with anything else on
- *     the same index (same rule as faiss.IndexFlat).
+ *   - every entry point that reads or changes an index takes the index's mutex for the length of the
+ *     call: a search from one host thread and an add / reserve / remove_ids / reset from another are
+ *     serialised, never interleaved (faiss.IndexFlat leaves that to the caller).
+ *   - streams: add / add_pooled / encode_add only ENQUEUE the append on `stream`.  The library records
+ *     an event behind every append and makes whatever reads the rows later on a different stream --
+ *     a search, reconstruct / write_index / serialize (which copy on the legacy default stream), a
+ *     regrowth copy -- wait for it first, so rows appended on a non-blocking stream are never read
+ *     before they are written.  Host-pointer calls return only after their own copies have completed.
  */
 #ifndef BFK_H
 #define BFK_H
@@ -143,6 +148,14 @@ int bfk_search_finish(bfk_index* idx, void* stream, int64_t* n_rewritten);
 /* device address of the int holding how many answers of the pending deferred search are not yet
  * certified (NULL when nothing is pending); consumed by bfk_xchg_merge */
 const void* bfk_search_pending_nflag_ptr(bfk_index* idx);
+
+/* Measurement aid (no reference counterpart; bench.py's roofline): between begin and end every tensor-scan
+ * launch of this index stamps the device clock (globaltimer) when its first CTA starts streaming and when its
+ * last CTA leaves -- inside the kernel, so nothing is recorded on the stream between the kernels of a search and
+ * the searches run exactly as they do unprofiled.  end waits for the device and returns the summed scan time
+ * and the number of scan launches (up to 65536 per begin; later launches are not stamped). */
+int bfk_profile_begin(bfk_index* idx);
+int bfk_profile_end(bfk_index* idx, double* scan_ms_sum, int64_t* n_scans);
 
 /* index.reset() / reconstruct / reconstruct_n / remove_ids -- LangChain side paths
  * on the object built at llm-qa/main.py:53-58 */
