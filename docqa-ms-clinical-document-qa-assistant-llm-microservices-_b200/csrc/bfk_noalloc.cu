@@ -23,7 +23,10 @@
 // Set-up: `g_scratch` below is a host-side stand-in for the device array, not an address a
 // kernel can use.  The first call on each device resolves the real device address with
 // cudaGetSymbolAddress (with that device current) and caches it; make that first call
-// outside any stream capture.
+// outside any stream capture.  The scan kernel exists in one variant per (queries rounded up
+// to 1/2/4/8, metric, storage type); the first launch of a variant lets the driver load its
+// code and sets its shared-memory attribute.  A caller that must not trigger any driver work
+// while serving runs each variant it will use once at start-up.
 #include <mutex>
 
 #include "bfk_common.cuh"

@@ -230,7 +230,11 @@ int bfk_enc_encode_add(void* enc, bfk_index* idx, const int64_t* ids, const void
  * Scratch is a fixed 1.25 MiB array inside the library image (held by every GPU that loads
  * libbfk.so until exit) shared by all calls on that GPU: calls that overlap on the GPU race;
  * calls on one stream do not.  The first call on each device resolves the array's device
- * address -- make it before any stream capture.  Larger nq / k / SM counts are rejected. */
+ * address -- make it before any stream capture.  The first call of each kernel variant -- query
+ * count rounded up to 1, 2, 4 or 8, times metric, times storage type -- may also make the driver
+ * load that variant's code and set its shared-memory attribute: run every variant you will
+ * serve once at start-up, and from then on a call leaves cudaMemGetInfo's free bytes untouched.
+ * Larger nq / k / SM counts are rejected. */
 int bfk_search_noalloc(const bfk_index* idx, const float* q_dev, int64_t nq, int64_t k, float* D_dev,
                        int64_t* I_dev, void* stream);
 

@@ -1,0 +1,58 @@
+"""Step / scan timing of the tensor path on config 2 (1M x 384 fp32, L2, k=10), for A/B runs under
+BFK_TC_PDL / BFK_TC_PREPASS: python profiles/step_probe.py [nq ...]
+
+Per batch size: device step time (CUDA events around 50 searches), scan time from the in-kernel device-clock
+stamps of the same 50 searches, scan time from CUDA events around the launch (separate calls, serial launches),
+and the host-buffer (numpy) step time.
+"""
+import os
+import sys
+
+import numpy as np
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import docqa_b200 as bfk  # noqa: E402
+
+n, d, k = int(os.environ.get("PROBE_ROWS", 1_000_000)), 384, 10
+g = torch.Generator(device="cuda").manual_seed(1234)
+xb = torch.randn((n, d), generator=g, device="cuda")
+xb /= xb.norm(dim=1, keepdim=True)
+idx = bfk.IndexFlatL2(d)
+idx.add(xb)
+tag = f"PDL={os.environ.get('BFK_TC_PDL', '1')} PREPASS={os.environ.get('BFK_TC_PREPASS', '1')}"
+for nq in [int(a) for a in sys.argv[1:]] or [1, 64, 1024, 4096]:
+    q = torch.randn((nq, d), generator=g, device="cuda")
+    q /= q.norm(dim=1, keepdim=True)
+    D = torch.empty((nq, k), device="cuda")
+    I = torch.empty((nq, k), dtype=torch.int64, device="cuda")
+    reps = 50 if nq <= 1024 else 10
+    for _ in range(5):
+        idx.search(q, k, D=D, I=I, algo="tensor")
+    torch.cuda.synchronize()
+    idx.profile_begin()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        idx.search(q, k, D=D, I=I, algo="tensor")
+    e1.record()
+    torch.cuda.synchronize()
+    step = e0.elapsed_time(e1) / reps
+    scan_sum, n_scans = idx.profile_end()
+    st = bfk.SearchStats()
+    ev = []
+    for _ in range(10):
+        idx.search(q, k, D=D, I=I, algo="tensor", stats=st)
+        ev.append(st.scan_ms)
+    qn = q.cpu().numpy()
+    Dn, In = np.empty((nq, k), np.float32), np.empty((nq, k), np.int64)
+    for _ in range(5):
+        idx.search(qn, k, D=Dn, I=In, algo="tensor")
+    e0.record()
+    for _ in range(reps):
+        idx.search(qn, k, D=Dn, I=In, algo="tensor")
+    e1.record()
+    torch.cuda.synchronize()
+    host = e0.elapsed_time(e1) / reps
+    print(f"[{tag}] nq={nq}: step {step * 1e3:.1f} us, scan(stamps) {scan_sum / reps * 1e3:.1f} us over {n_scans / reps:.1f} launches, "
+          f"scan(events, serial) {np.mean(ev) * 1e3:.1f} us, host step {host * 1e3:.1f} us, fallback {st.n_fallback}", flush=True)

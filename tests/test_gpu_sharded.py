@@ -70,7 +70,11 @@ def test_sharded_search_nccl():
     import torch
     import torch.multiprocessing as mp
 
+    from tests.conftest import note
+
     world = max(1, min(4, torch.cuda.device_count()))
+    note(f"test_sharded_search_nccl: {torch.cuda.device_count()} GPUs visible, world size {world} "
+         f"({'peer-memory exchange K6x + deferred search exercised' if world > 1 else 'single rank: K6x NOT exercised'})")
     mgr = mp.Manager()
     ret = mgr.dict()
     mp.spawn(_worker, args=(world, _free_port(), ret), nprocs=world, join=True)

@@ -249,3 +249,77 @@ def test_config3_full_size_10m_x_768_bf16_ip(bfk):
     # distances recomputable from the stored (bf16) rows
     rows = torch.from_numpy(idx.reconstruct_n(int(Ih[5, 0]), 1)).cuda()
     assert abs(float((rows[0] * q[5]).sum()) - float(Dh[5, 0])) < 1e-5
+
+
+# ---- the certificate's error bound at large d ("Exactness") --------------------------
+# The margin K5 re-scores inside grows with the row length (tensor-pipe accumulation over ld16 terms); these
+# cases sit at the d where the old constant was not proved: 1024 < d <= BFK_MAX_D.
+
+@pytest.mark.parametrize("metric", [L2, IP])
+@pytest.mark.parametrize("storage", ["f32", "bf16"])
+@pytest.mark.parametrize("d", [1024, 1536, 2048])
+def test_certificate_large_d_random_rows(bfk, d, storage, metric):
+    import torch
+    from tests.conftest import note
+
+    rng = np.random.default_rng(d + metric)
+    xb, xq = unit(rng, 20011, d), unit(rng, 70, d)
+    stored = torch.from_numpy(xb).to(torch.bfloat16).to(torch.float32).numpy() if storage == "bf16" else xb
+    idx = bfk.IndexFlat(d, metric, storage=storage)
+    idx.add(xb)
+    D, I, st = run(bfk, idx, xq, 10)
+    note(f"large_d_random d={d} storage={storage} metric={metric} n_fallback={st.n_fallback} second_pass={st.n_candidates}")
+    check_knn(D, I, xq, stored, 10, metric, tight=True)
+    De, Ie = idx.search(xq, 10, algo="exact")
+    assert (I == Ie).all()
+    np.testing.assert_allclose(D, De, rtol=1e-5, atol=1e-6)
+    assert st.n_fallback <= 8  # i.i.d. rows are certifiable at every d: the bound must not swallow the answer
+
+
+@pytest.mark.parametrize("metric", [L2, IP])
+@pytest.mark.parametrize("d", [1024, 2048])
+def test_certificate_large_d_all_positive_rows_and_wide_norms(bfk, d, metric):
+    """Worst case for the accumulation bound: every product q_i * x_i is positive, so sum|q_i x_i| = <q, x>,
+    and the row norms span three decades (the bound is relative to ||q|| max||x||)."""
+    from tests.conftest import note
+
+    rng = np.random.default_rng(7 * d + metric)
+    n, nq, k = 20011, 40, 10
+    xb = np.abs(rng.standard_normal((n, d))).astype(np.float32)
+    xb *= (10.0 ** rng.uniform(-1.5, 1.5, size=(n, 1)) / np.linalg.norm(xb, axis=1, keepdims=True)).astype(np.float32)
+    xq = np.abs(rng.standard_normal((nq, d))).astype(np.float32)
+    xq /= np.linalg.norm(xq, axis=1, keepdims=True)
+    idx = bfk.IndexFlat(d, metric)
+    idx.add(xb)
+    D, I, st = run(bfk, idx, xq, k)
+    note(f"large_d_positive d={d} metric={metric} n_fallback={st.n_fallback} second_pass={st.n_candidates}")
+    check_knn(D, I, xq, xb, k, metric)
+    De, Ie = idx.search(xq, k, algo="exact")
+    assert (I == Ie).all()
+    np.testing.assert_allclose(D, De, rtol=1e-5, atol=1e-6)
+
+
+@pytest.mark.parametrize("d", [1024, 1536, 2048])
+def test_certificate_large_d_near_ties_fall_back_to_the_exact_scan(bfk, d):
+    """A cluster of 700 rows whose exact distances to the query differ by far less than the margin: more rows
+    sit inside the cut than K5 re-scores (512), so nothing can be certified there; the answer must then come
+    from the fp32 scan on the GPU (n_fallback > 0) and equal it."""
+    from tests.conftest import note
+
+    rng = np.random.default_rng(11 * d)
+    n, k = 20000, 10
+    xb = unit(rng, n, d)
+    v = unit(rng, 1, d)
+    where = rng.choice(n, size=700, replace=False)
+    xb[where] = v + 1e-3 * unit(rng, 700, d)
+    xq = np.concatenate([v + 0.05 * unit(rng, 6, d), unit(rng, 20, d)], axis=0).astype(np.float32)
+    idx = bfk.IndexFlatL2(d)
+    idx.add(xb)
+    D, I, st = run(bfk, idx, xq, k)
+    note(f"large_d_near_ties d={d} n_fallback={st.n_fallback} second_pass={st.n_candidates}")
+    assert st.n_fallback >= 6  # the six queries next to the cluster
+    check_knn(D, I, xq, xb, k, L2)
+    De, Ie = idx.search(xq, k, algo="exact")
+    assert (I == Ie).all()  # the fall-back IS the exact scan, so even inside the near-ties the ids agree
+    np.testing.assert_allclose(D, De, rtol=1e-5, atol=1e-6)
+    assert set(I[:6].reshape(-1).tolist()) <= set(where.tolist())
