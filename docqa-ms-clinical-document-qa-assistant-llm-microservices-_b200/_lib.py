@@ -40,7 +40,7 @@ EXPORTS = [
     "bfk_add_pooled", "bfk_pool_normalize", "bfk_search", "bfk_search_ex", "bfk_search_finish", "bfk_search_pending_nflag_ptr", "bfk_reset",
     "bfk_xchg_create", "bfk_xchg_connect", "bfk_xchg_capacity", "bfk_xchg_merge", "bfk_xchg_last_max_nflag",
     "bfk_xchg_free",
-    "bfk_reconstruct", "bfk_remove_ids", "bfk_write", "bfk_read", "bfk_serialized_size",
+    "bfk_reconstruct", "bfk_remove_ids", "bfk_write", "bfk_write_append", "bfk_read", "bfk_serialized_size",
     "bfk_serialize", "bfk_deserialize", "bfk_normalize_l2", "bfk_merge_topk", "bfk_merge_topk_strided", "bfk_search_noalloc",
     "bfk_enc_create", "bfk_enc_free", "bfk_enc_set_tensor", "bfk_enc_forward", "bfk_enc_encode", "bfk_enc_encode_add",
     "bfk_profile_begin", "bfk_profile_end",
@@ -95,6 +95,7 @@ def load() -> ctypes.CDLL:
     L.bfk_reconstruct.argtypes = [vp, i64, i64, vp, i32]
     L.bfk_remove_ids.argtypes = [vp, vp, i64, ctypes.POINTER(i64)]
     L.bfk_write.argtypes = [vp, ctypes.c_char_p]
+    L.bfk_write_append.argtypes = [vp, ctypes.c_char_p, i64]
     L.bfk_read.argtypes = [ctypes.c_char_p, i32, i32, ctypes.POINTER(vp)]
     L.bfk_serialized_size.argtypes = [vp]
     L.bfk_serialized_size.restype = i64

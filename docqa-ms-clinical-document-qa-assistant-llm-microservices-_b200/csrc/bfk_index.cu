@@ -3,6 +3,8 @@
 // Stands in for the faiss.IndexFlat* object that the reference builds in
 // semantic-indexer/indexer.py:39,104, fills at :41, persists at :27, reloads at :99 and
 // llm-qa/main.py:35, and searches through LangChain at llm-qa/main.py:101,117.
+#include <unistd.h>
+
 #include <algorithm>
 #include <cfloat>
 #include <cstring>
@@ -858,6 +860,59 @@ int bfk_write(const bfk_index* idx, const char* path) {
             rc = fail("write_index: short write");
     }
     if (fclose(f) != 0 && !rc) rc = fail("write_index: close failed");
+    return rc;
+}
+
+// indexer.py:26-30 rewrites the whole file after every message; this appends the rows the file does not hold yet.
+// Order of writes: payload of the new rows past the end of the old payload (a reader of the old header never
+// looks there), flush, then the 45-byte header with the new ntotal / count in ONE write -- the commit point.
+int bfk_write_append(bfk_index* idx, const char* path, int64_t rows_on_disk) {
+    if (!idx || !path) return fail("write_index_append: null argument");
+    DeviceGuard g(idx->device);
+    std::lock_guard<std::mutex> lk(idx->mu);
+    if (rows_on_disk < 0 || rows_on_disk > idx->ntotal)
+        return fail("write_index_append: the file is said to hold " + std::to_string(rows_on_disk) + " rows, the index has " +
+                    std::to_string(idx->ntotal));
+    FILE* f = fopen(path, "r+b");
+    if (!f) return fail(std::string("could not open ") + path + " for appending");
+    uint8_t h[HEADER_BYTES + 4];
+    const size_t got = fread(h, 1, sizeof(h), f);
+    int d, metric;
+    int64_t n, off;
+    int rc = parse_header(h, (int64_t)got, &d, &n, &metric, &off);
+    if (!rc && (d != idx->d || metric != idx->metric || n != rows_on_disk || off != HEADER_BYTES))
+        rc = fail("write_index_append: the file's header (d=" + std::to_string(d) + ", ntotal=" + std::to_string(n) +
+                  ") does not describe the first " + std::to_string(rows_on_disk) + " rows of this index");
+    const int64_t m_total = idx->ntotal - rows_on_disk;
+    if (!rc && m_total > 0) {
+        if (fseeko(f, (off_t)(HEADER_BYTES + (int64_t)sizeof(float) * rows_on_disk * idx->d), SEEK_SET) != 0)
+            rc = fail("write_index_append: seek failed");
+        // the tail leaves the GPU through the pinned staging buffer when it fits (a message is a few rows)
+        const size_t row_bytes = sizeof(float) * (size_t)idx->d;
+        char* pin = (size_t)m_total * row_bytes <= STAGE_BYTES ? stage_buffer(idx) : nullptr;
+        const int64_t chunk = pin ? m_total : std::max<int64_t>(1, (int64_t)((256ull << 20) / row_bytes));
+        std::vector<float> tmp;
+        if (!pin) tmp.resize((size_t)std::min(chunk, m_total) * idx->d);
+        float* buf = pin ? reinterpret_cast<float*>(pin) : tmp.data();
+        for (int64_t j = 0; j < m_total && !rc; j += chunk) {
+            const int64_t m = std::min(chunk, m_total - j);
+            rc = rows_out(idx, rows_on_disk + j, m, buf, 0);
+            if (!rc && fwrite(buf, sizeof(float), (size_t)m * idx->d, f) != (size_t)m * idx->d)
+                rc = fail("write_index_append: short write");
+        }
+        // debris of an append that never committed may reach further than this one: the file ends with its rows
+        if (!rc && (fflush(f) != 0 ||
+                    ftruncate(fileno(f), (off_t)(HEADER_BYTES + (int64_t)sizeof(float) * idx->ntotal * idx->d)) != 0 ||
+                    fdatasync(fileno(f)) != 0))
+            rc = fail("write_index_append: flush failed");
+        if (!rc) {
+            uint8_t nh[HEADER_BYTES];
+            put_header(nh, idx->d, idx->ntotal, idx->metric);
+            if (pwrite(fileno(f), nh, HEADER_BYTES, 0) != (ssize_t)HEADER_BYTES) rc = fail("write_index_append: header write failed");
+            else if (fdatasync(fileno(f)) != 0) rc = fail("write_index_append: flush failed");
+        }
+    }
+    if (fclose(f) != 0 && !rc) rc = fail("write_index_append: close failed");
     return rc;
 }
 

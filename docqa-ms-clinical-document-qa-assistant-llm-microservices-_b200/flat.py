@@ -341,6 +341,14 @@ def write_index(index: IndexFlat, fname) -> None:
     _lib.check(index._L.bfk_write(index._h, os.fsencode(fname)))
 
 
+def write_index_append(index: IndexFlat, fname, rows_on_disk: int) -> None:
+    """Extension of faiss.write_index for indexer.py:26-30 (a full rewrite per message): `fname` already holds
+    the first `rows_on_disk` rows of `index`; only the rows after them are copied off the GPU and appended, then
+    the header is updated in one write.  The file ends up byte-identical to write_index(index, fname).
+    Raises RuntimeError when the file does not match (then write the whole file)."""
+    _lib.check(index._L.bfk_write_append(index._h, os.fsencode(fname), int(rows_on_disk)))
+
+
 def read_index(fname, *, device: int | None = None, storage="f32") -> IndexFlat:
     """faiss.read_index -- indexer.py:99, llm-qa/main.py:35."""
     L = _lib.load()

@@ -167,6 +167,13 @@ int bfk_remove_ids(bfk_index* idx, const int64_t* ids, int64_t n, int64_t* nremo
  * Byte-identical to faiss's IxF2 / IxFI files. */
 int bfk_write(const bfk_index* idx, const char* path);
 int bfk_read(const char* path, int device, int storage, bfk_index** out);
+/* save_state() without the full rewrite -- indexer.py:26-30 calls faiss.write_index on the whole index after
+ * every message (indexer.py:125).  `path` already holds the first rows_on_disk rows of this index, as a file
+ * written by bfk_write / bfk_write_append / faiss; the rows after them are appended (only that tail leaves the
+ * GPU) and the header is then rewritten in one 45-byte write, so the file is byte-identical to what bfk_write
+ * would produce and a concurrent reader sees the old index or the new one.  Fails -- write the whole file
+ * instead -- when the header does not match (other d / metric / row count, rows removed since). */
+int bfk_write_append(bfk_index* idx, const char* path, int64_t rows_on_disk);
 /* faiss.serialize_index / deserialize_index */
 int64_t bfk_serialized_size(const bfk_index* idx);
 int bfk_serialize(const bfk_index* idx, uint8_t* buf, int64_t buf_len);

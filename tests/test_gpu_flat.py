@@ -297,3 +297,66 @@ def test_indexer_host_on_the_gpu_index(bfk, tmp_path):
     vec = Model().encode([meta[1]["text_content"]])
     D, I = raw_index.search(vec, 3)                                             # llm-qa/main.py:101,117
     assert I[0, 0] == 1 and D[0, 0] == 0.0
+
+
+@pytest.mark.parametrize("storage", ["f32", "bf16"])
+def test_write_index_append_is_byte_identical_to_a_full_write(bfk, tmp_path, storage):
+    """bfk_write_append (include/bfk.h): the file grows by the new rows only and equals faiss.write_index's output."""
+    rng = np.random.default_rng(31)
+    d = 384
+    idx = bfk.IndexFlatL2(d, storage=storage)
+    path, full = str(tmp_path / "vector_store.faiss"), str(tmp_path / "full.faiss")
+    idx.add(rng.standard_normal((649, d)).astype(np.float32))
+    bfk.write_index(idx, path)
+    on_disk = 649
+    for n_new in (1, 1, 3, 700, 5000, 0, 1):  # single rows like indexer.py:41, a batch beyond the pinned buffer, nothing
+        if n_new:
+            idx.add(rng.standard_normal((n_new, d)).astype(np.float32))
+        bfk.write_index_append(idx, path, on_disk)
+        on_disk = idx.ntotal
+        bfk.write_index(idx, full)
+        assert open(path, "rb").read() == open(full, "rb").read()
+    back = bfk.read_index(path)
+    assert back.ntotal == idx.ntotal
+    np.testing.assert_array_equal(back.reconstruct_n(0, back.ntotal), idx.reconstruct_n(0, idx.ntotal))
+    # debris past the committed end (an append that crashed before its header write) is overwritten and cut off
+    with open(path, "ab") as f:
+        f.write(b"\xff" * 10_000)
+    idx.add(rng.standard_normal((2, d)).astype(np.float32))
+    bfk.write_index_append(idx, path, on_disk)
+    bfk.write_index(idx, full)
+    assert open(path, "rb").read() == open(full, "rb").read()
+    # a file that does not hold a prefix of this index is refused, not patched
+    with pytest.raises(RuntimeError, match="does not describe"):
+        bfk.write_index_append(idx, path, on_disk)  # stale row count: the header now says ntotal
+    other = bfk.IndexFlatIP(d)
+    other.add(rng.standard_normal((idx.ntotal, d)).astype(np.float32))
+    with pytest.raises(RuntimeError):
+        bfk.write_index_append(other, path, idx.ntotal)
+    with pytest.raises(RuntimeError):
+        bfk.write_index_append(idx, str(tmp_path / "missing.faiss"), 0)
+
+
+def test_indexer_host_appends_on_the_gpu_index(bfk, tmp_path):
+    """The reference's ingestion pattern (one add per chunk, one save per message, indexer.py:37-41,120-125) on
+    the GPU index with append-only saves: the files equal a full rewrite after every message."""
+    import json
+    import pickle
+
+    rng = np.random.default_rng(5)
+
+    class Model:
+        def encode(self, texts):
+            v = rng.standard_normal((len(texts), 384)).astype(np.float32)
+            return v / np.linalg.norm(v, axis=1, keepdims=True)
+
+    ix = bfk.SemanticIndexer(Model(), 384, index_file=str(tmp_path / "vector_store.faiss"),
+                             metadata_file=str(tmp_path / "metadata_store.pkl"))
+    modes = []
+    for m in range(5):
+        assert ix.handle_message(json.dumps({"doc_id": m, "original_text_masked": "t" * 1200}).encode()) is True
+        modes.append(ix.last_save_mode)
+        bfk.write_index(ix.index, str(tmp_path / "full.faiss"))
+        assert open(tmp_path / "vector_store.faiss", "rb").read() == open(tmp_path / "full.faiss", "rb").read()
+        assert pickle.load(open(tmp_path / "metadata_store.pkl", "rb")) == ix.metadata_store
+    assert modes == ["full", "append", "append", "append", "append"] and ix.index.ntotal == 15
