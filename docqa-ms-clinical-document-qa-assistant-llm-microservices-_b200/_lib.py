@@ -80,7 +80,8 @@ def load() -> ctypes.CDLL:
     L.bfk_search_ex.argtypes = [vp, vp, i64, i64, vp, vp, i32, vp, i32, i64, ctypes.POINTER(SearchStats)]
     L.bfk_search_finish.argtypes = [vp, vp, ctypes.POINTER(i64)]
     L.bfk_profile_begin.argtypes = [vp]
-    L.bfk_profile_end.argtypes = [vp, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(i64)]
+    dbl_p = ctypes.POINTER(ctypes.c_double)
+    L.bfk_profile_end.argtypes = [vp, dbl_p, dbl_p, dbl_p, ctypes.POINTER(i64)]
     L.bfk_search_pending_nflag_ptr.argtypes = [vp]
     L.bfk_search_pending_nflag_ptr.restype = vp
     L.bfk_xchg_create.argtypes = [i32, i32, i32, i64, ctypes.POINTER(vp), vp]

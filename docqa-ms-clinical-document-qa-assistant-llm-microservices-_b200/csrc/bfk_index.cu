@@ -685,13 +685,15 @@ int bfk_profile_begin(bfk_index* idx) {
     std::lock_guard<std::mutex> lk(idx->mu);
     constexpr int64_t CAP = 1 << 16;
     if (!idx->prof_ring) {
-        BFK_CUDA(cudaMalloc((void**)&idx->prof_ring, sizeof(unsigned long long) * 2 * CAP));
+        BFK_CUDA(cudaMalloc((void**)&idx->prof_ring, sizeof(unsigned long long) * 4 * CAP));
         idx->prof_cap = CAP;
     }
-    std::vector<unsigned long long> init((size_t)2 * idx->prof_cap);
+    // per pass: [0] first scan CTA in (atomicMin), [1] last scan CTA out (atomicMax),
+    //           [2] prep kernel in (atomicMin),    [3] last K5 CTA out (atomicMax)
+    std::vector<unsigned long long> init((size_t)4 * idx->prof_cap);
     for (int64_t i = 0; i < idx->prof_cap; i++) {
-        init[(size_t)2 * i] = ~0ull;  // earliest start: atomicMin
-        init[(size_t)2 * i + 1] = 0;  // latest end: atomicMax
+        init[(size_t)4 * i] = init[(size_t)4 * i + 2] = ~0ull;
+        init[(size_t)4 * i + 1] = init[(size_t)4 * i + 3] = 0;
     }
     BFK_CUDA(cudaMemcpy(idx->prof_ring, init.data(), init.size() * sizeof(unsigned long long), cudaMemcpyHostToDevice));
     idx->prof_used = 0;
@@ -699,28 +701,37 @@ int bfk_profile_begin(bfk_index* idx) {
     return 0;
 }
 
-int bfk_profile_end(bfk_index* idx, double* scan_ms_sum, int64_t* n_scans) {
+int bfk_profile_end(bfk_index* idx, double* scan_ms_sum, double* pass_ms_sum, double* idle_ms_sum, int64_t* n_scans) {
     if (!idx) return fail("null index");
     if (scan_ms_sum) *scan_ms_sum = 0.0;
+    if (pass_ms_sum) *pass_ms_sum = 0.0;
+    if (idle_ms_sum) *idle_ms_sum = 0.0;
     if (n_scans) *n_scans = 0;
     DeviceGuard g(idx->device);
     std::lock_guard<std::mutex> lk(idx->mu);
     if (!idx->prof_on) return fail("profile_end without profile_begin");
     idx->prof_on = false;
     BFK_CUDA(cudaDeviceSynchronize());
-    std::vector<unsigned long long> h((size_t)2 * idx->prof_used);
+    std::vector<unsigned long long> h((size_t)4 * idx->prof_used);
     if (idx->prof_used)
         BFK_CUDA(cudaMemcpy(h.data(), idx->prof_ring, h.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
-    double ns = 0.0;
+    double scan_ns = 0.0, pass_ns = 0.0, idle_ns = 0.0;
     int64_t n = 0;
+    unsigned long long prev_end = 0;
     for (int64_t i = 0; i < idx->prof_used; i++) {
-        const unsigned long long t0 = h[(size_t)2 * i], t1 = h[(size_t)2 * i + 1];
-        if (t0 != ~0ull && t1 >= t0) {
-            ns += (double)(t1 - t0);
-            n++;
+        const unsigned long long* t = &h[(size_t)4 * i];
+        if (t[0] == ~0ull || t[1] < t[0]) continue;
+        scan_ns += (double)(t[1] - t[0]);
+        n++;
+        if (t[2] != ~0ull && t[3] >= t[2]) {
+            pass_ns += (double)(t[3] - t[2]);
+            if (prev_end && t[2] >= prev_end) idle_ns += (double)(t[2] - prev_end);
+            prev_end = t[3];
         }
     }
-    if (scan_ms_sum) *scan_ms_sum = ns * 1e-6;
+    if (scan_ms_sum) *scan_ms_sum = scan_ns * 1e-6;
+    if (pass_ms_sum) *pass_ms_sum = pass_ns * 1e-6;
+    if (idle_ms_sum) *idle_ms_sum = idle_ns * 1e-6;
     if (n_scans) *n_scans = n;
     return 0;
 }

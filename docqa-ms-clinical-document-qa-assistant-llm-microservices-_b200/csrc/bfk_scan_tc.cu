@@ -85,7 +85,8 @@ struct TcParams {
     int use_bias;        // per-row bias is fetched (L2 norms, or the selector bias for either metric)
     int csize;           // 1: every CTA on its own; 2: CTA pairs (cta_group::2) -- two query tiles share one
                          // corpus stream, each CTA stages only half of every corpus tile
-    unsigned long long* tstamp;  // optional [2]: [0] = earliest CTA start, [1] = latest CTA end (globaltimer ns), else nullptr
+    unsigned long long* tstamp;  // optional [4] (globaltimer ns): [0] earliest scan CTA start, [1] latest scan CTA end,
+                                 // [2] prep kernel start, [3] latest K5 CTA end; else nullptr
     int prepass;         // J == 1: tile 0 is first read for each thread's smallest key only (see the epilogue)
     uint64_t* pend_g;    // global pending lists [grid][TC_BUFCAP][256], or nullptr: lists live in shared memory.
                          // Long streams (several query tiles) append rarely and need the 32 KiB for a 4th
@@ -575,11 +576,12 @@ __global__ void __launch_bounds__(256) prep_queries_kernel(const float* __restri
                                                            float* __restrict__ qn, const unsigned int* __restrict__ maxn,
                                                            float c_round, float c_abs, int is_l2, float* __restrict__ qmargin,
                                                            unsigned int* __restrict__ slots, int NS,
-                                                           int* __restrict__ flags) {
+                                                           int* __restrict__ flags, unsigned long long* tstamp) {
     const int lane = threadIdx.x & 31;
     const int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     pdl_launch_dependents();  // the scan's prologue may start now; it waits for this grid before reading anything
     if (blockIdx.x == 0 && threadIdx.x == 0) {
+        if (tstamp) atomicMin(tstamp + 2, globaltimer_ns());
         flags[0] = 0;  // uncertified-query count of this pass (K5 appends)
         flags[-1] = 0; // K5's CTA ticket (the last CTA to finish publishes the count to the host)
     }
@@ -624,6 +626,7 @@ struct RerankParams {
     int* flag_list;
     int* h_nflag;     // pinned host word (device-mapped): the count, written by the last CTA
     unsigned long long* dbg;  // optional [16] phase clocks of CTA 0 (BFK_TC_DEBUG), else nullptr
+    unsigned long long* tstamp;  // optional: [3] = latest CTA end (globaltimer ns), see TcParams
 };
 
 // Sorts a[0..n) ascending (n a power of two); called by every thread of the CTA, results visible on return.
@@ -885,6 +888,7 @@ __global__ void __launch_bounds__(RR_THREADS) rerank_kernel(const RerankParams p
     }
     // the last CTA to get here hands the count to the host without a separate D2H copy
     if (tid == 0) {
+        if (p.tstamp) atomicMax(p.tstamp + 3, globaltimer_ns());
         __threadfence();
         if (atomicAdd(p.nflag - 1, 1) == (int)gridDim.x - 1) {
             __threadfence();
@@ -1232,6 +1236,8 @@ static int tc_pass(bfk_index* idx, const float* qc, int ldq, int64_t nqc, int k,
     //     weaker of the two rounding modes it could use), the sum is off by at most ld16 * 2^-23 * sum|q_i x_i|
     //     <= ld16 * 2^-23 ||q|| ||x||.  That is 2^-14 at ld16 = 512 -- the constant used for every d before --
     //     and 2^-12 at BFK_MAX_D = 2048, so it is kept as a floor and grows with the row length above it.
+    unsigned long long* ts = nullptr;  // this pass's device-clock stamps (bfk_profile_begin), or none
+    if (idx->prof_on && idx->prof_ring && idx->prof_used < idx->prof_cap) ts = idx->prof_ring + 4 * idx->prof_used++;
     const float c_acc = (float)std::max(idx->ld16, 512) / 8388608.f;
     const float c_round = (idx->storage == BFK_STORE_F32 ? 1.01f / 256.f : 1.01f / 512.f) + c_acc;
     // the fp32 re-score itself (ld16/32 terms per lane, then a 5-step butterfly) and the key's own fma round
@@ -1239,7 +1245,7 @@ static int tc_pass(bfk_index* idx, const float* qc, int ldq, int64_t nqc, int k,
     const float c_abs = (float)(idx->ld16 / 32 + 8) * 2.f / 16777216.f;
     prep_queries_kernel<<<(unsigned)((pl.nq_pad + 7) / 8), 256, 0, st>>>(qc, ldq, idx->d, nqc, pl.nq_pad, w.q16, idx->ld16,
                                                                         w.qn, idx->maxn, c_round, c_abs, l2 ? 1 : 0, w.qmargin,
-                                                                        w.slots, pl.NS, w.flags);
+                                                                        w.slots, pl.NS, w.flags, ts);
     BFK_CUDA(cudaGetLastError());
     const CUtensorMap *tmQp, *tmXp;
     BFK_TRY(cached_tmap(idx, 1, w.q16, pl.nq_pad, TC_BM, &tmQp));
@@ -1273,8 +1279,7 @@ static int tc_pass(bfk_index* idx, const float* qc, int ldq, int64_t nqc, int k,
         return e ? atoi(e) != 0 : true;
     }();
     if (!prepass_on) p.prepass = 0;
-    p.tstamp = nullptr;
-    if (idx->prof_on && idx->prof_ring && idx->prof_used < idx->prof_cap) p.tstamp = idx->prof_ring + 2 * idx->prof_used++;
+    p.tstamp = ts;
     static const bool dbg_on = getenv("BFK_TC_DEBUG") != nullptr;
     static const bool parked = getenv("BFK_TC_PARKED") != nullptr;
     p.dbg = dbg_on ? w.dbg : nullptr;
@@ -1347,6 +1352,7 @@ static int tc_pass(bfk_index* idx, const float* qc, int ldq, int64_t nqc, int k,
     r.flag_list = w.flags + 1;
     r.h_nflag = idx->h_flag_dev;
     r.dbg = p.dbg ? w.dbg + (size_t)pl.grid * 8 + 8 * 64 : nullptr;
+    r.tstamp = ts;
     {
         const bool small = (int64_t)r.S * r.KP <= 1024 && k <= 32;
         cudaLaunchConfig_t cfg = {};

@@ -288,10 +288,14 @@ class IndexFlat:
         """Extension (measurement aid): start stamping every tensor-scan launch with the device clock."""
         _lib.check(self._L.bfk_profile_begin(self._h))
 
-    def profile_end(self) -> tuple[float, int]:
-        """-> (summed scan-kernel milliseconds, number of scan launches) since profile_begin; waits for the GPU."""
-        ms, n = ctypes.c_double(0.0), ctypes.c_int64(0)
-        _lib.check(self._L.bfk_profile_end(self._h, ctypes.byref(ms), ctypes.byref(n)))
+    def profile_end(self, detail: bool = False):
+        """-> (summed scan-kernel milliseconds, number of scan launches) since profile_begin; waits for the GPU.
+        detail=True -> dict with scan_ms, pass_ms (query preparation to re-rank end), idle_ms (device idle
+        between consecutive passes: the host round trip) and n."""
+        ms, ps, idle, n = ctypes.c_double(0.0), ctypes.c_double(0.0), ctypes.c_double(0.0), ctypes.c_int64(0)
+        _lib.check(self._L.bfk_profile_end(self._h, ctypes.byref(ms), ctypes.byref(ps), ctypes.byref(idle), ctypes.byref(n)))
+        if detail:
+            return {"scan_ms": float(ms.value), "pass_ms": float(ps.value), "idle_ms": float(idle.value), "n": int(n.value)}
         return float(ms.value), int(n.value)
 
     def reconstruct(self, key, x=None):

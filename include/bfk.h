@@ -149,13 +149,16 @@ int bfk_search_finish(bfk_index* idx, void* stream, int64_t* n_rewritten);
  * certified (NULL when nothing is pending); consumed by bfk_xchg_merge */
 const void* bfk_search_pending_nflag_ptr(bfk_index* idx);
 
-/* Measurement aid (no reference counterpart; bench.py's roofline): between begin and end every tensor-scan
- * launch of this index stamps the device clock (globaltimer) when its first CTA starts streaming and when its
- * last CTA leaves -- inside the kernel, so nothing is recorded on the stream between the kernels of a search and
- * the searches run exactly as they do unprofiled.  end waits for the device and returns the summed scan time
- * and the number of scan launches (up to 65536 per begin; later launches are not stamped). */
+/* Measurement aid (no reference counterpart; bench.py's roofline): between begin and end every tensor-path
+ * pass of this index stamps the device clock (globaltimer) from inside its kernels -- when its query
+ * preparation starts, when the scan's first CTA starts streaming, when the scan's last CTA leaves, when the
+ * last re-rank CTA leaves -- so nothing is recorded on the stream between the kernels of a search and the
+ * searches run exactly as they do unprofiled.  end waits for the device and returns, summed over the passes
+ * (up to 65536 per begin; later ones are not stamped): scan kernel time; whole-pass time (preparation to
+ * re-rank); device idle time between one pass's end and the next one's start (the host round trip); the
+ * number of passes.  Any output pointer may be NULL. */
 int bfk_profile_begin(bfk_index* idx);
-int bfk_profile_end(bfk_index* idx, double* scan_ms_sum, int64_t* n_scans);
+int bfk_profile_end(bfk_index* idx, double* scan_ms_sum, double* pass_ms_sum, double* idle_ms_sum, int64_t* n_scans);
 
 /* index.reset() / reconstruct / reconstruct_n / remove_ids -- LangChain side paths
  * on the object built at llm-qa/main.py:53-58 */
