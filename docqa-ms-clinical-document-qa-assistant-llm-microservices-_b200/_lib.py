@@ -43,7 +43,7 @@ EXPORTS = [
     "bfk_reconstruct", "bfk_remove_ids", "bfk_write", "bfk_write_append", "bfk_read", "bfk_serialized_size",
     "bfk_serialize", "bfk_deserialize", "bfk_normalize_l2", "bfk_merge_topk", "bfk_merge_topk_strided", "bfk_search_noalloc",
     "bfk_enc_create", "bfk_enc_free", "bfk_enc_set_tensor", "bfk_enc_forward", "bfk_enc_encode", "bfk_enc_encode_add",
-    "bfk_profile_begin", "bfk_profile_end",
+    "bfk_profile_begin", "bfk_profile_end", "bfk_profile_stamps",
     "bfk_search_sel", "bfk_range_search", "bfk_range_result_size", "bfk_range_result_copy", "bfk_range_result_free",
 ]
 
@@ -82,6 +82,8 @@ def load() -> ctypes.CDLL:
     L.bfk_profile_begin.argtypes = [vp]
     dbl_p = ctypes.POINTER(ctypes.c_double)
     L.bfk_profile_end.argtypes = [vp, dbl_p, dbl_p, dbl_p, ctypes.POINTER(i64)]
+    L.bfk_profile_stamps.argtypes = [vp, vp, i64]
+    L.bfk_profile_stamps.restype = i64
     L.bfk_search_pending_nflag_ptr.argtypes = [vp]
     L.bfk_search_pending_nflag_ptr.restype = vp
     L.bfk_xchg_create.argtypes = [i32, i32, i32, i64, ctypes.POINTER(vp), vp]

@@ -83,7 +83,9 @@ struct bfk_index {
     unsigned int* maxn = nullptr;
     bfk::Workspace ws;       // search scratch, grow-only
     cudaEvent_t ws_free = nullptr;  // recorded after the last search that used `ws`
-    int* h_flag = nullptr;          // pinned host word: count of uncertified queries (tensor path)
+    int* h_flag = nullptr;          // pinned host words: [0] count of uncertified queries of the last tensor pass,
+                                    // [1] that pass's sequence number, written after the count (the host polls it)
+    int flag_seq = 0;               // sequence number of the last tensor pass enqueued
     int* h_flag_dev = nullptr;      // the same word as the GPU addresses it (K5's last CTA writes it)
     char* h_stage = nullptr;        // pinned staging for small host-side searches (queries in, (D, I) out)
     // id selector of the search in progress (bfk_search_sel; null otherwise), set and cleared under `mu`:

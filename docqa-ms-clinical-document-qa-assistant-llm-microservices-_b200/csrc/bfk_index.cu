@@ -168,11 +168,12 @@ static int make_index(int d, int metric, int device, int storage, bfk_index** ou
         cudaEventCreateWithFlags(&idx->ws_free, cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreateWithFlags(&idx->rows_ready, cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreateWithFlags(&idx->stage_done, cudaEventDisableTiming) != cudaSuccess ||
-        cudaHostAlloc((void**)&idx->h_flag, sizeof(int), cudaHostAllocMapped) != cudaSuccess ||
+        cudaHostAlloc((void**)&idx->h_flag, 2 * sizeof(int), cudaHostAllocMapped) != cudaSuccess ||
         cudaHostGetDevicePointer((void**)&idx->h_flag_dev, idx->h_flag, 0) != cudaSuccess) {
         delete idx;
         return fail(std::string("index allocation failed: ") + cudaGetErrorString(cudaGetLastError()));
     }
+    idx->h_flag[0] = idx->h_flag[1] = 0;
     *out = idx;
     return 0;
 }
@@ -734,6 +735,19 @@ int bfk_profile_end(bfk_index* idx, double* scan_ms_sum, double* pass_ms_sum, do
     if (idle_ms_sum) *idle_ms_sum = idle_ns * 1e-6;
     if (n_scans) *n_scans = n;
     return 0;
+}
+
+int64_t bfk_profile_stamps(bfk_index* idx, unsigned long long* out, int64_t max_passes) {
+    if (!idx || !out || max_passes < 0) return -1;
+    DeviceGuard g(idx->device);
+    std::lock_guard<std::mutex> lk(idx->mu);
+    const int64_t n = std::min(max_passes, idx->prof_used);
+    if (n > 0 && (cudaDeviceSynchronize() != cudaSuccess ||
+                  cudaMemcpy(out, idx->prof_ring, sizeof(unsigned long long) * 4 * (size_t)n, cudaMemcpyDeviceToHost) != cudaSuccess)) {
+        cudaGetLastError();
+        return -1;
+    }
+    return n;
 }
 
 const void* bfk_search_pending_nflag_ptr(bfk_index* idx) { return idx ? (const void*)search_tensor_pending_nflag(idx) : nullptr; }

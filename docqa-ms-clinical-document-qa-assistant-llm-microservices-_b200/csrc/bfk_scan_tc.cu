@@ -624,7 +624,8 @@ struct RerankParams {
     int64_t* I;
     int* nflag;       // [-1] = CTA ticket, [0] = count, [1..] = list
     int* flag_list;
-    int* h_nflag;     // pinned host word (device-mapped): the count, written by the last CTA
+    int* h_nflag;     // pinned host words (device-mapped): [0] the count, [1] `seq`, written in that order by the last CTA
+    int seq;
     unsigned long long* dbg;  // optional [16] phase clocks of CTA 0 (BFK_TC_DEBUG), else nullptr
     unsigned long long* tstamp;  // optional: [3] = latest CTA end (globaltimer ns), see TcParams
 };
@@ -693,6 +694,32 @@ __device__ void rr_bitonic(uint64_t* a, int n, int tid, int nthr) {
     }
 }
 
+// Sorts a[0..n) ascending, n a power of two.  Up to 256 elements every element's rank is COUNTED: n*n
+// independent compares spread over all threads (NT / n threads per element, each looking at every (NT/n)-th
+// element), one shuffle reduction, one scatter.  The bitonic network on so few elements is a single warp
+// walking a chain of 21-36 dependent exchange steps -- 3 us each time, twice per query, a quarter of K5.
+// Equal composites (only COMP_EMPTY padding repeats) are ordered by position so that ranks stay distinct.
+template <int NT>
+__device__ void rr_sort(uint64_t* a, int n, int tid) {
+    if (n > 256 || n > NT) {
+        rr_bitonic(a, n, tid, NT);
+        return;
+    }
+    __syncthreads();
+    const int P = NT / n;  // power of two, <= 16: the P threads of an element are neighbours in one warp
+    const int e = tid / P, part = tid - e * P;
+    const uint64_t v = a[e];
+    int cnt = 0;
+    for (int j = part; j < n; j += P) {
+        const uint64_t o = a[j];
+        cnt += (o < v || (o == v && j < e)) ? 1 : 0;
+    }
+    for (int o = P >> 1; o > 0; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+    __syncthreads();
+    if (part == 0) a[cnt] = v;
+    __syncthreads();
+}
+
 // RR_THREADS = 512 for long candidate lists (few queries, many streams), 128 when a query has at most 1024
 // candidates (many queries): four times as many queries are then resident per SM.
 template <int RR_THREADS>
@@ -711,6 +738,17 @@ __global__ void __launch_bounds__(RR_THREADS) rerank_kernel(const RerankParams p
     const long long rr_t0 = p.dbg ? clock64() : 0;
 #define RR_MARK(i) do { if (p.dbg && blockIdx.x == 0 && tid == 0) p.dbg[i] = (unsigned long long)(clock64() - rr_t0); } while (0)
 
+    // two candidates per 16-byte load; the first four loads of every thread are issued now, together with the
+    // thresholds and the query, so that the filter below does not start a second round trip to L2
+    // (KP is 16 or 32, so a query's M = S * KP candidates are an even count at a 16-byte aligned address)
+    const ulonglong2* src2 = reinterpret_cast<const ulonglong2*>(src);
+    const int64_t M2 = M >> 1;
+    ulonglong2 pre[4];
+#pragma unroll
+    for (int u = 0; u < 4; u++) {
+        const int64_t i = tid + (int64_t)u * RR_THREADS;
+        pre[u] = i < M2 ? __ldcg(src2 + i) : make_ulonglong2(COMP_EMPTY, COMP_EMPTY);
+    }
     for (int c = tid; c < p.ld32; c += RR_THREADS) q_s[c] = (c < p.ldq) ? p.q[q * p.ldq + c] : 0.f;
     // T = min over streams of the drop threshold: every row some stream dropped has approximate key >= T
     float tmin = FLT_MAX;
@@ -728,10 +766,6 @@ __global__ void __launch_bounds__(RR_THREADS) rerank_kernel(const RerankParams p
     // ---- keep only candidates with approximate key <= T (a certified answer never needs the rest:
     //      the cut A_k + 2*eps must lie below T), then sort the few survivors ----
     {
-        // two candidates per 16-byte load, four loads in flight per thread before the first is looked at
-        // (KP is 16 or 32, so a query's M = S * KP candidates are an even count at a 16-byte aligned address)
-        const ulonglong2* src2 = reinterpret_cast<const ulonglong2*>(src);
-        const int64_t M2 = M >> 1;
         const uint32_t tmin_ord = f2ord(tmin);
         auto keep = [&](uint64_t c) {
             if (c != COMP_EMPTY && (uint32_t)(c >> 32) <= tmin_ord) {
@@ -739,7 +773,12 @@ __global__ void __launch_bounds__(RR_THREADS) rerank_kernel(const RerankParams p
                 if (slot < TC_MERGE_N) buf[slot] = c;
             }
         };
-        for (int64_t i0 = tid; i0 < M2; i0 += 4 * RR_THREADS) {
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            keep(pre[u].x);
+            keep(pre[u].y);
+        }
+        for (int64_t i0 = tid + 4 * (int64_t)RR_THREADS; i0 < M2; i0 += 4 * RR_THREADS) {
             ulonglong2 v[4];
 #pragma unroll
             for (int u = 0; u < 4; u++) {
@@ -761,7 +800,7 @@ __global__ void __launch_bounds__(RR_THREADS) rerank_kernel(const RerankParams p
     while (n < cnt) n <<= 1;
     for (int i = cnt + tid; i < n; i += RR_THREADS) buf[i] = COMP_EMPTY;
     __syncthreads();
-    rr_bitonic(buf, n, tid, RR_THREADS);
+    rr_sort<RR_THREADS>(buf, n, tid);
     RR_MARK(2);
     if (p.dbg && blockIdx.x == 0 && tid == 0) p.dbg[8] = (unsigned long long)total;
 
@@ -865,7 +904,7 @@ __global__ void __launch_bounds__(RR_THREADS) rerank_kernel(const RerankParams p
     }
     __syncthreads();
     RR_MARK(4);
-    rr_bitonic(ex, min(n_ex, TC_RMAX), tid, RR_THREADS);
+    rr_sort<RR_THREADS>(ex, min(n_ex, TC_RMAX), tid);
     RR_MARK(5);
     for (int i = tid; i < p.k; i += RR_THREADS) {
         const uint64_t c = (i < TC_RMAX) ? ex[i] : COMP_EMPTY;
@@ -893,6 +932,9 @@ __global__ void __launch_bounds__(RR_THREADS) rerank_kernel(const RerankParams p
         if (atomicAdd(p.nflag - 1, 1) == (int)gridDim.x - 1) {
             __threadfence();
             *reinterpret_cast<volatile int*>(p.h_nflag) = *reinterpret_cast<volatile int*>(p.nflag);
+            __threadfence_system();
+            // every CTA's (D, I) rows were written and fenced before its ticket: the host may stop waiting here
+            *reinterpret_cast<volatile int*>(p.h_nflag + 1) = p.seq;
             __threadfence_system();
         }
     }
@@ -1017,13 +1059,18 @@ static int64_t tc_chunk_queries(const bfk_index* idx, int64_t nq) {
         const int64_t S = std::max<int64_t>(1, std::min<int64_t>(sms / c, T));
         return (double)std::max<int64_t>((T + S - 1) / S, T / 75) + 16.0;
     };
+    static const int forced = [] {  // experiments: BFK_TC_CHUNK_TILES=c forces passes of c query tiles
+        const char* e = getenv("BFK_TC_CHUNK_TILES");
+        return e ? atoi(e) : 0;
+    }();
+    if (forced > 0) return std::min<int64_t>(forced, std::min<int64_t>(QT, sms)) * TC_BM;
     int64_t best_c = std::min<int64_t>(QT, sms);
     double best = -1.0;
     for (int64_t c = std::min<int64_t>(QT, sms); c >= 1; c--) {
         const int64_t full = QT / c, rest = QT - full * c;
         // even tile counts run as CTA pairs (measured ~4 % faster)
         const double cost = (double)full * pass_cost(c) * ((c & 1) ? 1.04 : 1.0) + (rest ? pass_cost(rest) : 0.0);
-        if (best < 0 || cost < best * 0.97) {  // a smaller chunk has to win clearly
+        if (best < 0 || cost < best * 0.995) {  // ties go to the larger pass (the model tracks measurements within ~2 %)
             best = cost;
             best_c = c;
         }
@@ -1351,6 +1398,7 @@ static int tc_pass(bfk_index* idx, const float* qc, int ldq, int64_t nqc, int k,
     r.nflag = w.flags;
     r.flag_list = w.flags + 1;
     r.h_nflag = idx->h_flag_dev;
+    r.seq = ++idx->flag_seq;
     r.dbg = p.dbg ? w.dbg + (size_t)pl.grid * 8 + 8 * 64 : nullptr;
     r.tstamp = ts;
     {
@@ -1396,10 +1444,37 @@ struct TcPending {
 // Reads the pass's flag list (one stream sync) and settles what was not certified: a second tensor pass
 // over those queries alone, then the exact scan for what is still open.  Returns how many result rows
 // were rewritten through *n_rewritten.
+// Waits until the last tensor pass enqueued on `st` has published its certificate count.  K5's last CTA writes the
+// count and then the pass's sequence number into pinned host memory; polling that word costs a PCIe write's
+// latency, where cudaStreamSynchronize also waits for the kernel to be retired and for the driver to notice.
+// Passes longer than a few hundred microseconds (and any error) fall back to the blocking wait.
+static int wait_pass_published(bfk_index* idx, cudaStream_t st) {
+    static const bool spin_on = [] {
+        const char* e = getenv("BFK_TC_SPIN");
+        return e ? atoi(e) != 0 : true;
+    }();
+    const int want = idx->flag_seq;
+    volatile int* seq = idx->h_flag + 1;
+    if (spin_on) {
+        for (int round = 0; round < 64 && *seq != want; round++) {
+            for (int i = 0; i < 400 && *seq != want; i++) {
+#if defined(__x86_64__)
+                __builtin_ia32_pause();
+#endif
+            }
+            if (*seq != want && cudaStreamQuery(st) != cudaErrorNotReady) break;  // finished, or failed
+        }
+        cudaGetLastError();
+        if (*seq == want) return 0;
+    }
+    BFK_CUDA(cudaStreamSynchronize(st));
+    return 0;
+}
+
 static int tc_resolve(bfk_index* idx, const TcPending& c, cudaStream_t st, int64_t* n_retry, int64_t* n_fallback,
                       int64_t* n_rewritten, int* launches) {
     const TcWs& w = c.w;
-    BFK_CUDA(cudaStreamSynchronize(st));
+    BFK_TRY(wait_pass_published(idx, st));
     int nflag = *idx->h_flag;
     if (n_rewritten) *n_rewritten += nflag;
     if (nflag == 0) return 0;
@@ -1421,7 +1496,7 @@ static int tc_resolve(bfk_index* idx, const TcPending& c, cudaStream_t st, int64
             w.r_D, w.r_I, w.r_list, nflag, c.k, c.Dc, c.Ic);
         BFK_CUDA(cudaGetLastError());
         *launches += 2;
-        BFK_CUDA(cudaStreamSynchronize(st));
+        BFK_CUDA(cudaStreamSynchronize(st));  // the scatter above has to land, too
         const int nflag2 = *idx->h_flag;
         std::vector<int> list2((size_t)nflag2);
         if (nflag2 > 0) {

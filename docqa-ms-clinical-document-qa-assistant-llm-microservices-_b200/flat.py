@@ -298,6 +298,15 @@ class IndexFlat:
             return {"scan_ms": float(ms.value), "pass_ms": float(ps.value), "idle_ms": float(idle.value), "n": int(n.value)}
         return float(ms.value), int(n.value)
 
+    def profile_stamps(self, max_passes: int = 65536) -> np.ndarray:
+        """uint64 [n, 4] device-clock stamps (ns) of the passes since profile_begin: scan start, scan end,
+        preparation start, re-rank end."""
+        out = np.zeros((max_passes, 4), dtype=np.uint64)
+        n = int(self._L.bfk_profile_stamps(self._h, _np_ptr(out), max_passes))
+        if n < 0:
+            raise RuntimeError("profile_stamps failed")
+        return out[:n]
+
     def reconstruct(self, key, x=None):
         key = int(key)
         if x is None:

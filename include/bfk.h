@@ -159,6 +159,10 @@ const void* bfk_search_pending_nflag_ptr(bfk_index* idx);
  * number of passes.  Any output pointer may be NULL. */
 int bfk_profile_begin(bfk_index* idx);
 int bfk_profile_end(bfk_index* idx, double* scan_ms_sum, double* pass_ms_sum, double* idle_ms_sum, int64_t* n_scans);
+/* the raw stamps of the passes since the last begin, in order: out[4 * i + {0, 1, 2, 3}] = scan start, scan end,
+ * preparation start, re-rank end of pass i (nanoseconds of the device clock); returns how many passes were
+ * copied (at most max_passes), -1 on error */
+int64_t bfk_profile_stamps(bfk_index* idx, unsigned long long* out, int64_t max_passes);
 
 /* index.reset() / reconstruct / reconstruct_n / remove_ids -- LangChain side paths
  * on the object built at llm-qa/main.py:53-58 */

@@ -20,7 +20,7 @@ xb = torch.randn((n, d), generator=g, device="cuda")
 xb /= xb.norm(dim=1, keepdim=True)
 idx = bfk.IndexFlatL2(d)
 idx.add(xb)
-tag = f"PDL={os.environ.get('BFK_TC_PDL', '1')} PREPASS={os.environ.get('BFK_TC_PREPASS', '1')}"
+tag = " ".join(f"{k[7:]}={v}" for k, v in sorted(os.environ.items()) if k.startswith("BFK_TC_")) or "defaults"
 for nq in [int(a) for a in sys.argv[1:]] or [1, 64, 1024, 4096]:
     q = torch.randn((nq, d), generator=g, device="cuda")
     q /= q.norm(dim=1, keepdim=True)
@@ -38,7 +38,8 @@ for nq in [int(a) for a in sys.argv[1:]] or [1, 64, 1024, 4096]:
     e1.record()
     torch.cuda.synchronize()
     step = e0.elapsed_time(e1) / reps
-    scan_sum, n_scans = idx.profile_end()
+    prof = idx.profile_end(detail=True)
+    scan_sum, n_scans = prof["scan_ms"], prof["n"]
     st = bfk.SearchStats()
     ev = []
     for _ in range(10):
@@ -54,5 +55,6 @@ for nq in [int(a) for a in sys.argv[1:]] or [1, 64, 1024, 4096]:
     e1.record()
     torch.cuda.synchronize()
     host = e0.elapsed_time(e1) / reps
-    print(f"[{tag}] nq={nq}: step {step * 1e3:.1f} us, scan(stamps) {scan_sum / reps * 1e3:.1f} us over {n_scans / reps:.1f} launches, "
+    print(f"[{tag}] nq={nq}: step {step * 1e3:.1f} us = pass {prof['pass_ms'] / reps * 1e3:.1f} (prep..rerank on the device clock) + "
+          f"idle {prof['idle_ms'] / max(reps - 1, 1) * 1e3:.1f} (rerank end -> next prep start); scan(stamps) {scan_sum / reps * 1e3:.1f} us over {n_scans / reps:.1f} launches, "
           f"scan(events, serial) {np.mean(ev) * 1e3:.1f} us, host step {host * 1e3:.1f} us, fallback {st.n_fallback}", flush=True)
