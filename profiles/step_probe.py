@@ -39,6 +39,9 @@ for nq in [int(a) for a in sys.argv[1:]] or [1, 64, 1024, 4096]:
     torch.cuda.synchronize()
     step = e0.elapsed_time(e1) / reps
     prof = idx.profile_end(detail=True)
+    ts = idx.profile_stamps().astype(np.int64)
+    lead = float(np.mean(ts[:, 0] - ts[:, 2])) * 1e-3   # prep start -> scan streaming
+    trail = float(np.mean(ts[:, 3] - ts[:, 1])) * 1e-3  # scan end -> last K5 CTA out
     scan_sum, n_scans = prof["scan_ms"], prof["n"]
     st = bfk.SearchStats()
     ev = []
@@ -56,5 +59,5 @@ for nq in [int(a) for a in sys.argv[1:]] or [1, 64, 1024, 4096]:
     torch.cuda.synchronize()
     host = e0.elapsed_time(e1) / reps
     print(f"[{tag}] nq={nq}: step {step * 1e3:.1f} us = pass {prof['pass_ms'] / reps * 1e3:.1f} (prep..rerank on the device clock) + "
-          f"idle {prof['idle_ms'] / max(reps - 1, 1) * 1e3:.1f} (rerank end -> next prep start); scan(stamps) {scan_sum / reps * 1e3:.1f} us over {n_scans / reps:.1f} launches, "
+          f"idle {prof['idle_ms'] / max(reps - 1, 1) * 1e3:.1f} (rerank end -> next prep start); prep->scan {lead:.1f}, scan end->K5 end {trail:.1f}; scan(stamps) {scan_sum / reps * 1e3:.1f} us over {n_scans / reps:.1f} launches, "
           f"scan(events, serial) {np.mean(ev) * 1e3:.1f} us, host step {host * 1e3:.1f} us, fallback {st.n_fallback}", flush=True)
