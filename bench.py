@@ -662,7 +662,7 @@ class SearchBench:
                 self.local.add(x[a - r0 : b - r0])
             del x
         if self.world > 1:
-            self.index._record(self.hi - self.lo, self.lo, self.n_total)
+            self.index.set_contiguous_shard(self.lo, self.n_total)
         torch.cuda.synchronize()
         assert self.local.ntotal == self.hi - self.lo
 

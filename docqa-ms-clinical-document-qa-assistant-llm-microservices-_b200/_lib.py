@@ -39,7 +39,7 @@ EXPORTS = [
     "bfk_metric", "bfk_storage", "bfk_device", "bfk_ntotal", "bfk_reserve", "bfk_add",
     "bfk_add_pooled", "bfk_pool_normalize", "bfk_search", "bfk_search_ex", "bfk_search_finish", "bfk_search_pending_nflag_ptr", "bfk_reset",
     "bfk_xchg_create", "bfk_xchg_connect", "bfk_xchg_capacity", "bfk_xchg_merge", "bfk_xchg_last_max_nflag",
-    "bfk_xchg_free",
+    "bfk_xchg_free", "bfk_xchg_set_id_map",
     "bfk_reconstruct", "bfk_remove_ids", "bfk_write", "bfk_write_append", "bfk_read", "bfk_serialized_size",
     "bfk_serialize", "bfk_deserialize", "bfk_normalize_l2", "bfk_merge_topk", "bfk_merge_topk_strided", "bfk_search_noalloc",
     "bfk_enc_create", "bfk_enc_free", "bfk_enc_set_tensor", "bfk_enc_forward", "bfk_enc_encode", "bfk_enc_encode_add",
@@ -94,6 +94,7 @@ def load() -> ctypes.CDLL:
     L.bfk_xchg_last_max_nflag.argtypes = [vp]
     L.bfk_xchg_last_max_nflag.restype = i64
     L.bfk_xchg_free.argtypes = [vp]
+    L.bfk_xchg_set_id_map.argtypes = [vp, i64]
     L.bfk_reset.argtypes = [vp]
     L.bfk_reconstruct.argtypes = [vp, i64, i64, vp, i32]
     L.bfk_remove_ids.argtypes = [vp, vp, i64, ctypes.POINTER(i64)]

@@ -20,6 +20,7 @@
 // Parity double-buffering is enough: a rank can finish search s only after every peer has pushed s, so
 // nobody can be more than one search ahead of anybody else.  The kernels of different ranks run on
 // different GPUs, so waiting on one another cannot deadlock a single GPU's scheduler.
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -36,9 +37,14 @@ struct Xchg {
     unsigned char* local = nullptr;                 // this rank's region (cudaMalloc)
     unsigned char* peer[XCHG_MAX_WORLD] = {nullptr};  // region of rank p as mapped here (peer[rank] == local)
     unsigned long long seq = 0;
-    unsigned long long* d_maxflag = nullptr;        // device word: max uncertified count of the last exchange
+    unsigned long long* d_maxflag = nullptr;        // device word: max uncertified count of the last exchange,
+                                                    // or XCHG_TIMED_OUT when a peer's lists never arrived
     unsigned long long* h_maxflag = nullptr;        // pinned mirror
+    int64_t block_rows = 0;    // > 0: local ids are block-cyclic (bfk_xchg_set_id_map) and made global while pushed
+    long long timeout_cycles = 0;
 };
+
+constexpr unsigned long long XCHG_TIMED_OUT = ~0ull;
 
 struct XchgPeers {
     unsigned char* p[XCHG_MAX_WORLD];
@@ -48,7 +54,8 @@ struct XchgPeers {
 __global__ void __launch_bounds__(256) xchg_push_kernel(XchgPeers peers, int world, int rank, size_t parity_off,
                                                         size_t slot_bytes, size_t flags_off, const float* __restrict__ D,
                                                         const int64_t* __restrict__ I, int64_t nk,
-                                                        const int* __restrict__ nflag, unsigned long long seq) {
+                                                        const int* __restrict__ nflag, unsigned long long seq,
+                                                        int64_t block_rows) {
     const int64_t wd = (nk + 1) / 2;
     const int64_t nwords = 2 + wd + nk;
     const unsigned long long* Dw = reinterpret_cast<const unsigned long long*>(D);  // read pairs of floats
@@ -62,7 +69,12 @@ __global__ void __launch_bounds__(256) xchg_push_kernel(XchgPeers peers, int wor
                 const int64_t j = w - 2;
                 if (2 * j + 1 < nk) v = Dw[j];
                 else v = (unsigned long long)__float_as_uint(D[2 * j]);  // odd tail
-            } else v = (unsigned long long)I[w - 2 - wd];
+            } else {
+                int64_t id = I[w - 2 - wd];
+                // block-cyclic placement: local row l of rank r is global row ((l / B) * W + r) * B + l % B
+                if (block_rows > 0 && id >= 0) id = ((id / block_rows) * world + rank) * block_rows + id % block_rows;
+                v = (unsigned long long)id;
+            }
             dst[w] = v;
         }
     }
@@ -85,8 +97,11 @@ __global__ void __launch_bounds__(256) xchg_push_kernel(XchgPeers peers, int wor
     }
 }
 
+// A peer that does not show up within the time limit (it died, or its process is stuck) must not take this
+// GPU's context with it: the kernel gives up, reports XCHG_TIMED_OUT through the status word the host reads
+// anyway, and the host raises.  (It used to trap, which made the rank lose its whole shard.)
 __global__ void xchg_wait_kernel(unsigned char* local, int world, size_t parity_off, size_t slot_bytes, size_t flags_off,
-                                 unsigned long long seq, unsigned long long* maxflag) {
+                                 unsigned long long seq, unsigned long long* maxflag, long long timeout_cycles) {
     const int lane = threadIdx.x;
     unsigned long long nf = 0;
     if (lane < world) {
@@ -96,13 +111,15 @@ __global__ void xchg_wait_kernel(unsigned char* local, int world, size_t parity_
         for (;;) {
             asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(flag) : "memory");
             if (v >= seq) break;
-            if (clock64() - t0 > 20000000000ll) {  // ~10 s: a peer died or never searched
+            if (clock64() - t0 > timeout_cycles) {
                 printf("libbfk: exchange timed out waiting for rank %d (seq %llu, saw %llu)\n", lane, seq, v);
-                __trap();
+                nf = XCHG_TIMED_OUT;
+                break;
             }
             __nanosleep(200);
         }
-        nf = *reinterpret_cast<const unsigned long long*>(local + parity_off + (size_t)lane * slot_bytes);
+        if (nf != XCHG_TIMED_OUT)
+            nf = *reinterpret_cast<const unsigned long long*>(local + parity_off + (size_t)lane * slot_bytes);
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) nf = max(nf, __shfl_xor_sync(0xffffffffu, nf, o));
@@ -143,6 +160,12 @@ int bfk_xchg_create(int device, int world, int rank, int64_t max_nq_times_k, voi
         return fail(std::string("xchg_create: ") + e);
     }
     cudaDeviceSynchronize();
+    // default limit 60 s (first-call module loads, a paused peer and collective regrowth all fit), BFK_XCHG_TIMEOUT_S overrides
+    {
+        const char* e = getenv("BFK_XCHG_TIMEOUT_S");
+        const double secs = e ? std::max(0.001, atof(e)) : 60.0;
+        x->timeout_cycles = (long long)(secs * 2.0e9);
+    }
     static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
     memcpy(ipc_handle_out, &h, 64);
     x->peer[rank] = x->local;
@@ -190,18 +213,20 @@ int bfk_xchg_merge(void* handle, const float* D_local, const int64_t* I_local, i
     if ((size_t)((2 + (nk + 1) / 2 + nk) * 8) > x->slot_bytes) return fail("xchg_merge: lists larger than the exchange slots");
     DeviceGuard g(x->device);
     cudaStream_t st = (cudaStream_t)stream;
-    x->seq++;
-    const size_t parity_off = (size_t)(x->seq & 1ull) * x->parity_bytes;
+    const unsigned long long seq = x->seq + 1;  // committed below, once both kernels are enqueued
+    const size_t parity_off = (size_t)(seq & 1ull) * x->parity_bytes;
     const size_t flags_off = (size_t)x->world * x->slot_bytes;
     XchgPeers peers;
     for (int p = 0; p < XCHG_MAX_WORLD; p++) peers.p[p] = x->peer[p];
     const int64_t nwords = 2 + (nk + 1) / 2 + nk;
     dim3 grid((unsigned)std::min<int64_t>((nwords + 255) / 256, 32), (unsigned)x->world);
     xchg_push_kernel<<<grid, 256, 0, st>>>(peers, x->world, x->rank, parity_off, x->slot_bytes, flags_off, D_local, I_local,
-                                           nk, nflag_dev, x->seq);
+                                           nk, nflag_dev, seq, x->block_rows);
     BFK_CUDA(cudaGetLastError());
-    xchg_wait_kernel<<<1, 32, 0, st>>>(x->local, x->world, parity_off, x->slot_bytes, flags_off, x->seq, x->d_maxflag);
+    xchg_wait_kernel<<<1, 32, 0, st>>>(x->local, x->world, parity_off, x->slot_bytes, flags_off, seq, x->d_maxflag,
+                                       x->timeout_cycles);
     BFK_CUDA(cudaGetLastError());
+    x->seq = seq;
     // the W lists now sit in the local region: part p = slot p, D after the 2-word header, I after D
     const unsigned char* base = x->local + parity_off;
     const int64_t wd = (nk + 1) / 2;
@@ -212,10 +237,18 @@ int bfk_xchg_merge(void* handle, const float* D_local, const int64_t* I_local, i
     return 0;
 }
 
-// valid after the stream of the last bfk_xchg_merge has been synchronised
+// valid after the stream of the last bfk_xchg_merge has been synchronised; -2: a peer's lists never arrived
 int64_t bfk_xchg_last_max_nflag(void* handle) {
     Xchg* x = (Xchg*)handle;
-    return x ? (int64_t)*x->h_maxflag : -1;
+    if (!x) return -1;
+    return *x->h_maxflag == XCHG_TIMED_OUT ? -2 : (int64_t)*x->h_maxflag;
+}
+
+int bfk_xchg_set_id_map(void* handle, int64_t block_rows) {
+    Xchg* x = (Xchg*)handle;
+    if (!x || block_rows < 0) return fail("xchg_set_id_map: bad argument");
+    x->block_rows = block_rows;
+    return 0;
 }
 
 int bfk_xchg_free(void* handle) {

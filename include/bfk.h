@@ -211,7 +211,11 @@ int bfk_xchg_connect(void* handle, const uint8_t* all_handles);
 int64_t bfk_xchg_capacity(void* handle);
 int bfk_xchg_merge(void* handle, const float* D_local, const int64_t* I_local, int64_t nq, int64_t k, int metric,
                    const int* nflag_dev, float* D_out, int64_t* I_out, void* stream);
-int64_t bfk_xchg_last_max_nflag(void* handle);
+int64_t bfk_xchg_last_max_nflag(void* handle); /* -2: a peer's lists did not arrive within the time limit
+                                                 * (60 s, BFK_XCHG_TIMEOUT_S): recreate the exchange on all ranks */
+/* block_rows > 0: the ids handed to bfk_xchg_merge are LOCAL rows of a block-cyclic placement (global row g
+ * lives on rank (g / block_rows) % world) and are made global while they are pushed; 0: ids are sent as they are */
+int bfk_xchg_set_id_map(void* handle, int64_t block_rows);
 int bfk_xchg_free(void* handle);
 
 /* The sentence encoder feeding the pooling kernel and the index without leaving the GPU:

@@ -23,7 +23,7 @@ def _free_port():
     return p
 
 
-def _worker(rank, world, port, ret):
+def _worker(rank, world, port, ret, tmp):
     import torch
     import torch.distributed as dist
 
@@ -40,13 +40,43 @@ def _worker(rank, world, port, ret):
         xq = rng.standard_normal((70, 384)).astype(np.float32)
         xq /= np.linalg.norm(xq, axis=1, keepdims=True)
         for metric in (bfk.METRIC_L2, bfk.METRIC_INNER_PRODUCT):
-            idx = bfk.ShardedIndexFlat(384, metric, device=rank)
-            idx.add(xb[:25000])  # replicated adds -> two id segments per rank
-            idx.add(xb[25000:])
+            # replicated adds, block-cyclic over the ranks (blocks of 4096 rows here), one-row adds included
+            idx = bfk.ShardedIndexFlat(384, metric, device=rank, block_rows=4096)
+            idx.add(xb[:25000])
+            for i in range(25000, 25010):
+                idx.add(xb[i:i + 1])  # the reference's call shape, indexer.py:41
+            idx.add(xb[25010:])
             assert idx.ntotal == 60001
-            for nq in (1, 5, 70):  # exact path, and the tensor path on each shard
+            assert idx.local.ntotal == sum(min(60001, (b + 1) * 4096) - b * 4096 for b in range(rank, 15, world))
+            single = bfk.IndexFlat(384, metric, device=rank)  # the same rows on one GPU: the answers must be identical
+            single.add(xb)
+            for nq in (1, 5, 70):  # exact path, and the tensor path on each shard; host buffers in and out
                 D, I = idx.search(xq[:nq], 10)
                 check_knn(D, I, xq[:nq], xb, 10, metric, tight=True)
+                Ds, Is = single.search(xq[:nq], 10)
+                assert (I == Is).all() and (D == Ds).all()  # bit for bit: the same fp32 re-score on either side
+            # one faiss-format file written by all ranks, byte-identical to the single-GPU writer (indexer.py:27) ...
+            path = os.path.join(tmp, f"sharded_{metric}.faiss")
+            one = os.path.join(tmp, f"single_{metric}_{rank}.faiss")
+            idx.write_index(path)
+            bfk.write_index(single, one)
+            assert open(path, "rb").read() == open(one, "rb").read()
+            # ... and read back onto the GPUs (indexer.py:99, llm-qa/main.py:35), both placements
+            for placement in ("block_cyclic", "contiguous"):
+                back = bfk.ShardedIndexFlat.read_index(path, device=rank, placement=placement, block_rows=4096)
+                assert back.ntotal == 60001 and back.metric_type == metric
+                Db, Ib = back.search(xq, 10)
+                Ds, Is = single.search(xq, 10)
+                assert (Ib == Is).all() and (Db == Ds).all()
+            np.testing.assert_array_equal(idx.reconstruct_n(4000, 200), xb[4000:4200])
+            # selector over global ids, and rows removed: survivors renumbered and re-dealt over the GPUs
+            Dsel, Isel = idx.search(xq[:9], 5, params=bfk.SearchParameters(sel=bfk.IDSelectorRange(1000, 30000)))
+            check_knn(Dsel, Isel - 1000, xq[:9], xb[1000:30000], 5, metric)
+            gone = np.arange(0, 60001, 7)
+            assert idx.remove_ids(gone) == gone.size
+            keep = np.setdiff1d(np.arange(60001), gone)
+            Dk, Ik = idx.search(xq[:20], 10)
+            check_knn(Dk, Ik, xq[:20], xb[keep], 10, metric, tight=True)
             # contiguous shards with ids global straight from the kernel, CUDA tensors in and out
             idx2 = bfk.ShardedIndexFlat(384, metric, device=rank, storage="bf16")
             lo, hi = bfk.shard_range(60001, rank, world)
@@ -59,14 +89,16 @@ def _worker(rank, world, port, ret):
             dist.broadcast(ref, src=0)
             assert torch.equal(ref, I2)
             # k larger than a shard's share of good rows: padding survives the merge
-            D3, I3 = idx.search(xq[:3], 1000)
-            check_knn(D3, I3, xq[:3], xb, 1000, metric)
+            idx3 = bfk.ShardedIndexFlat(384, metric, device=rank, block_rows=4096)
+            idx3.add(xb[:9000])
+            D3, I3 = idx3.search(xq[:3], 1000)
+            check_knn(D3, I3, xq[:3], xb[:9000], 1000, metric)
         ret[rank] = "ok"
     finally:
         dist.destroy_process_group()
 
 
-def test_sharded_search_nccl():
+def test_sharded_search_nccl(tmp_path):
     import torch
     import torch.multiprocessing as mp
 
@@ -77,7 +109,7 @@ def test_sharded_search_nccl():
          f"({'peer-memory exchange K6x + deferred search exercised' if world > 1 else 'single rank: K6x NOT exercised'})")
     mgr = mp.Manager()
     ret = mgr.dict()
-    mp.spawn(_worker, args=(world, _free_port(), ret), nprocs=world, join=True)
+    mp.spawn(_worker, args=(world, _free_port(), ret, str(tmp_path)), nprocs=world, join=True)
     assert dict(ret) == {r: "ok" for r in range(world)}
 
 
