@@ -59,7 +59,7 @@ static inline int next_pow2(int v) {
 //   x32  [cap, ld32] fp32 master rows, ld32 = round_up(d, 4)   (BFK_STORE_F32 only)
 //   x16  [cap, ld16] bf16 scan copy,   ld16 = round_up(d, 64)  (zero padded)
 //   nrm  [cap]       fp32 squared norms of the stored (fp32 or bf16) rows
-//   maxn [1]         fp32 bits of max_i ||x_i||^2 (monotone under atomicMax)
+//   maxn [2]         fp32 bits of max_i ||x_i||^2 and of max_i ||x_i - bf16(x_i)||^2 (monotone under atomicMax)
 struct Workspace {
     void* ptr = nullptr;
     size_t bytes = 0;
@@ -83,6 +83,8 @@ struct bfk_index {
     unsigned int* maxn = nullptr;
     bfk::Workspace ws;       // search scratch, grow-only
     cudaEvent_t ws_free = nullptr;  // recorded after the last search that used `ws`
+    cudaStream_t ws_stream = nullptr;  // ... and the stream it ran on
+    bool ws_stream_known = false;
     int* h_flag = nullptr;          // pinned host words: [0] count of uncertified queries of the last tensor pass,
                                     // [1] that pass's sequence number, written after the count (the host polls it)
     int flag_seq = 0;               // sequence number of the last tensor pass enqueued

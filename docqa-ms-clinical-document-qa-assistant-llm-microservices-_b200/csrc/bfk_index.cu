@@ -163,8 +163,8 @@ static int make_index(int d, int metric, int device, int storage, bfk_index** ou
         return fail("libbfk is built for sm_100a (B200) only; device compute capability is " +
                     std::to_string(prop.major) + "." + std::to_string(prop.minor));
     }
-    if (cudaMalloc((void**)&idx->maxn, sizeof(unsigned int)) != cudaSuccess ||
-        cudaMemset(idx->maxn, 0, sizeof(unsigned int)) != cudaSuccess ||
+    if (cudaMalloc((void**)&idx->maxn, 2 * sizeof(unsigned int)) != cudaSuccess ||
+        cudaMemset(idx->maxn, 0, 2 * sizeof(unsigned int)) != cudaSuccess ||
         cudaEventCreateWithFlags(&idx->ws_free, cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreateWithFlags(&idx->rows_ready, cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreateWithFlags(&idx->stage_done, cudaEventDisableTiming) != cudaSuccess ||
@@ -282,7 +282,9 @@ static int add_rows(bfk_index* idx, const float* x, int64_t n, int x_is_device, 
     // host rows: stage through device scratch in <= 64 MiB pieces
     const int64_t chunk = std::max<int64_t>(1, (64ll << 20) / (int64_t)(sizeof(float) * idx->d));
     BFK_TRY(ensure_workspace(idx, sizeof(float) * (size_t)std::min(chunk, n) * idx->d));
-    BFK_CUDA(cudaStreamWaitEvent(st, idx->ws_free, 0));
+    if (idx->ws_stream_known && idx->ws_stream != st) BFK_CUDA(cudaStreamWaitEvent(st, idx->ws_free, 0));
+    idx->ws_stream = st;
+    idx->ws_stream_known = true;
     BFK_TRY(wait_rows_ready(idx, st));
     const size_t small_bytes = sizeof(float) * (size_t)n * idx->d;
     char* pin = small_bytes <= STAGE_BYTES ? stage_buffer(idx) : nullptr;
@@ -572,7 +574,10 @@ static int search_locked(bfk_index* idx, const float* q, int64_t nq, int k, floa
     sizing.take<char>(256);
     size_t head = sizing.off;
     BFK_TRY(ensure_workspace(idx, head + tail_bytes + 512));
-    BFK_CUDA(cudaStreamWaitEvent(st, idx->ws_free, 0));
+    // the workspace's previous user: work on the same stream is ordered anyway, another stream has to be waited for
+    if (idx->ws_stream_known && idx->ws_stream != st) BFK_CUDA(cudaStreamWaitEvent(st, idx->ws_free, 0));
+    idx->ws_stream = st;
+    idx->ws_stream_known = true;
     WsCarver ws(idx->ws.ptr);
     float* q_dev = ws.take<float>((size_t)nq * ldq);
     float* D_dev = ws.take<float>((size_t)nq * k);
@@ -760,7 +765,7 @@ int bfk_reset(bfk_index* idx) {
     BFK_CUDA(cudaDeviceSynchronize());
     idx->rows_pending = false;
     idx->ntotal = 0;
-    BFK_CUDA(cudaMemset(idx->maxn, 0, sizeof(unsigned int)));
+    BFK_CUDA(cudaMemset(idx->maxn, 0, 2 * sizeof(unsigned int)));
     return 0;
 }
 

@@ -187,7 +187,7 @@ __global__ void __launch_bounds__(512) pool_norm_kernel(const TokT* __restrict__
     for (int c = tid; c < H; c += nthr) ss += red[c] * red[c];
     ss = block_sum(ss, scratch, tid, nthr);
     const float inv = 1.0f / fmaxf(sqrtf(ss), 1e-12f);
-    float ss2 = 0.f;
+    float ss2 = 0.f, se2 = 0.f;
     const int64_t hi = out16 ? out16_ld : (out32 ? out32_ld : H);
     for (int64_t c = tid; c < hi; c += nthr) {
         float v = (c < H) ? red[c] * inv : 0.f;
@@ -196,14 +196,22 @@ __global__ void __launch_bounds__(512) pool_norm_kernel(const TokT* __restrict__
             __nv_bfloat16 h = __float2bfloat16_rn(v);
             out16[b * out16_ld + c] = h;
             if (!out32) v = __bfloat162float(h);  // bf16-stored index: the norm of what is stored
+            else {
+                const float e = v - __bfloat162float(h);  // what the scan copy loses against the fp32 master row
+                se2 += e * e;
+            }
         }
         ss2 += v * v;
     }
     if (out_nrm) {
         ss2 = block_sum(ss2, scratch, tid, nthr);
+        se2 = block_sum(se2, scratch, tid, nthr);
         if (tid == 0) {
             out_nrm[b] = ss2;
-            if (maxn) atomicMax(maxn, __float_as_uint(ss2));
+            if (maxn) {
+                atomicMax(maxn, __float_as_uint(ss2));
+                if (se2 > 0.f) atomicMax(maxn + 1, __float_as_uint(se2));  // see append_rows_kernel
+            }
         }
     }
 }

@@ -24,16 +24,18 @@ __global__ void __launch_bounds__(256) append_rows_kernel(const float* __restric
     const int lane = threadIdx.x & 31;
     const int64_t warp = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     const int64_t nwarps = (int64_t)gridDim.x * (blockDim.x >> 5);
-    float local_max = 0.f;
+    float local_max = 0.f, local_err = 0.f;
     for (int64_t r = warp; r < n; r += nwarps) {
         const float* s = src + r * src_ld;
-        float ss = 0.f;
+        float ss = 0.f, se = 0.f;
         for (int c = lane; c < ld16; c += 32) {
             float v = (c < d) ? __ldg(s + c) : 0.f;
             __nv_bfloat16 b = __float2bfloat16_rn(v);
             if (STORE_F32) {
                 if (c < ld32) x32[r * ld32 + c] = v;
                 ss += v * v;
+                const float e = v - __bfloat162float(b);  // what the scan copy loses (exact in fp32)
+                se += e * e;
             } else {
                 float vb = __bfloat162float(b);
                 ss += vb * vb;
@@ -41,11 +43,15 @@ __global__ void __launch_bounds__(256) append_rows_kernel(const float* __restric
             x16[r * ld16 + c] = b;
         }
         ss = warp_sum(ss);
+        se = warp_sum(se);
         if (lane == 0) nrm[r] = ss;
         local_max = fmaxf(local_max, ss);
+        local_err = fmaxf(local_err, se);
     }
-    // non-negative floats order like their bit patterns
+    // non-negative floats order like their bit patterns.  maxn[0] = max ||x||^2, maxn[1] = max ||x - bf16(x)||^2
+    // (0 for a bf16-stored index, whose rows ARE the scan copy): both feed K5's error bound
     if (lane == 0 && local_max > 0.f) atomicMax(maxn, __float_as_uint(local_max));
+    if (lane == 0 && local_err > 0.f) atomicMax(maxn + 1, __float_as_uint(local_err));
 }
 
 int launch_append_f32(bfk_index* idx, const float* src_dev, int64_t src_ld, int64_t n, cudaStream_t st) {

@@ -574,7 +574,7 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
 __global__ void __launch_bounds__(256) prep_queries_kernel(const float* __restrict__ q, int ldq, int d, int64_t nq,
                                                            int64_t nq_pad, __nv_bfloat16* __restrict__ q16, int ld16,
                                                            float* __restrict__ qn, const unsigned int* __restrict__ maxn,
-                                                           float c_round, float c_abs, int is_l2, float* __restrict__ qmargin,
+                                                           float c_acc, float c_abs, int is_l2, float* __restrict__ qmargin,
                                                            unsigned int* __restrict__ slots, int NS,
                                                            int* __restrict__ flags, unsigned long long* tstamp) {
     const int lane = threadIdx.x & 31;
@@ -586,19 +586,34 @@ __global__ void __launch_bounds__(256) prep_queries_kernel(const float* __restri
         flags[-1] = 0; // K5's CTA ticket (the last CTA to finish publishes the count to the host)
     }
     if (row >= nq_pad) return;
-    float ss = 0.f;
+    float ss = 0.f, sh = 0.f, se = 0.f;  // ||q||^2, ||bf16 q||^2, ||q - bf16 q||^2
     for (int c = lane; c < ld16; c += 32) {
         float v = (row < nq && c < d) ? q[row * ldq + c] : 0.f;
+        const __nv_bfloat16 b = __float2bfloat16_rn(v);
+        const float vb = __bfloat162float(b);
         ss += v * v;
-        q16[row * ld16 + c] = __float2bfloat16_rn(v);
+        sh += vb * vb;
+        se += (v - vb) * (v - vb);
+        q16[row * ld16 + c] = b;
     }
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
+    for (int o = 16; o > 0; o >>= 1) {
+        ss += __shfl_xor_sync(0xffffffffu, ss, o);
+        sh += __shfl_xor_sync(0xffffffffu, sh, o);
+        se += __shfl_xor_sync(0xffffffffu, se, o);
+    }
     if (lane == 0) {
         qn[row] = ss;
-        // 2*eps in key space: |<q,x> - <bf16 q, bf16 x>| <= c_round ||q|| max||x||; L2 keys carry 2x that
-        const float mx = __uint_as_float(*maxn);
-        qmargin[row] = (is_l2 ? 4.f : 2.f) * c_round * sqrtf(ss * mx) + c_abs * (ss + mx);
+        // eps bounds |<q,x> - acc| for every row x, acc = the tensor pipe's value of <bf16 q, xs> over the scan copy xs:
+        //   <q,x> - <bf16 q, xs> = <q - bf16 q, x> + <bf16 q, x - xs>     (Cauchy-Schwarz on both, with the MEASURED
+        //   rounding losses ||q - bf16 q|| of this query and max ||x - xs|| of the corpus instead of the worst case
+        //   2^-9 per element: about 1.7x tighter, and nothing at all for a bf16-stored corpus, where xs = x)
+        //   + c_acc ||bf16 q|| ||xs||  for the pipe's fp32 accumulation (see tc_pass).
+        // 2*eps in key space: L2 keys carry -2<q,x>, so 4*eps; inner-product keys 2*eps.  1.001: the norms above
+        // are themselves fp32 sums.
+        const float mx = __uint_as_float(maxn[0]), me = __uint_as_float(maxn[1]);
+        const float eps = 1.001f * (sqrtf(se * mx) + sqrtf(sh * me) + c_acc * sqrtf(sh * mx) * 1.004f);
+        qmargin[row] = (is_l2 ? 4.f : 2.f) * eps + c_abs * (ss + mx);
     }
     for (int i = lane; i < NS; i += 32) slots[row * NS + i] = f2ord(FLT_MAX);
 }
@@ -736,6 +751,7 @@ __global__ void __launch_bounds__(RR_THREADS) rerank_kernel(const RerankParams p
     const uint64_t* src = p.out_cand + q * M;
     pdl_wait();  // launched behind the scan with programmatic serialization: its lists are complete from here on
     const long long rr_t0 = p.dbg ? clock64() : 0;
+    const unsigned long long rr_g0 = p.dbg ? globaltimer_ns() : 0ull;
 #define RR_MARK(i) do { if (p.dbg && blockIdx.x == 0 && tid == 0) p.dbg[i] = (unsigned long long)(clock64() - rr_t0); } while (0)
 
     // two candidates per 16-byte load; the first four loads of every thread are issued now, together with the
@@ -749,7 +765,7 @@ __global__ void __launch_bounds__(RR_THREADS) rerank_kernel(const RerankParams p
         const int64_t i = tid + (int64_t)u * RR_THREADS;
         pre[u] = i < M2 ? __ldcg(src2 + i) : make_ulonglong2(COMP_EMPTY, COMP_EMPTY);
     }
-    for (int c = tid; c < p.ld32; c += RR_THREADS) q_s[c] = (c < p.ldq) ? p.q[q * p.ldq + c] : 0.f;
+    for (int c = tid; c < max(p.ld32, p.ld16); c += RR_THREADS) q_s[c] = (c < p.ldq) ? p.q[q * p.ldq + c] : 0.f;  // zero padded: the row loads below run to the padded width
     // T = min over streams of the drop threshold: every row some stream dropped has approximate key >= T
     float tmin = FLT_MAX;
     for (int s = tid; s < p.S; s += RR_THREADS) tmin = fminf(tmin, p.out_thr[q * p.S + s]);
@@ -854,37 +870,78 @@ __global__ void __launch_bounds__(RR_THREADS) rerank_kernel(const RerankParams p
         const uint32_t id1 = (uint32_t)(buf[i] & 0xffffffffu);
         const uint32_t id2 = two ? (uint32_t)(buf[i2] & 0xffffffffu) : id1;
         float acc1 = 0.f, acc2 = 0.f;
+        // All loads of both rows are issued before the first is used (up to four 16-byte loads per row and lane:
+        // d <= 512 in fp32, d <= 1024 in bf16 in one go): written as load-use-load-use the three column steps of a
+        // 384-wide row were three DRAM latencies in a row, 2.5 us of an 8 us kernel.
         if (p.storage == BFK_STORE_F32) {
             const float4* row1 = reinterpret_cast<const float4*>(p.x32 + (size_t)id1 * p.ld32);
             const float4* row2 = reinterpret_cast<const float4*>(p.x32 + (size_t)id2 * p.ld32);
-            for (int c = lane; c < (p.ld32 >> 2); c += 32) {
-                const float4 x1 = __ldg(row1 + c);
-                const float4 x2 = __ldg(row2 + c);
-                const float4 y = *reinterpret_cast<const float4*>(q_s + 4 * c);
-                if (p.is_l2) {
-                    float t0 = x1.x - y.x, t1 = x1.y - y.y, t2 = x1.z - y.z, t3 = x1.w - y.w;
-                    acc1 = fmaf(t0, t0, acc1); acc1 = fmaf(t1, t1, acc1); acc1 = fmaf(t2, t2, acc1); acc1 = fmaf(t3, t3, acc1);
-                    t0 = x2.x - y.x; t1 = x2.y - y.y; t2 = x2.z - y.z; t3 = x2.w - y.w;
-                    acc2 = fmaf(t0, t0, acc2); acc2 = fmaf(t1, t1, acc2); acc2 = fmaf(t2, t2, acc2); acc2 = fmaf(t3, t3, acc2);
-                } else {
-                    acc1 = fmaf(x1.x, y.x, acc1); acc1 = fmaf(x1.y, y.y, acc1); acc1 = fmaf(x1.z, y.z, acc1); acc1 = fmaf(x1.w, y.w, acc1);
-                    acc2 = fmaf(x2.x, y.x, acc2); acc2 = fmaf(x2.y, y.y, acc2); acc2 = fmaf(x2.z, y.z, acc2); acc2 = fmaf(x2.w, y.w, acc2);
+            const int nv = p.ld32 >> 2;
+            for (int c0 = lane; c0 < nv; c0 += 128) {
+                float4 a[4], b[4];
+#pragma unroll
+                for (int u = 0; u < 4; u++) {
+                    const int c = c0 + 32 * u;
+                    if (c < nv) {
+                        a[u] = __ldg(row1 + c);
+                        b[u] = __ldg(row2 + c);
+                    }
+                }
+#pragma unroll
+                for (int u = 0; u < 4; u++) {
+                    const int c = c0 + 32 * u;
+                    if (c < nv) {
+                        const float4 x1 = a[u], x2 = b[u];
+                        const float4 y = *reinterpret_cast<const float4*>(q_s + 4 * c);
+                        if (p.is_l2) {
+                            float t0 = x1.x - y.x, t1 = x1.y - y.y, t2 = x1.z - y.z, t3 = x1.w - y.w;
+                            acc1 = fmaf(t0, t0, acc1); acc1 = fmaf(t1, t1, acc1); acc1 = fmaf(t2, t2, acc1); acc1 = fmaf(t3, t3, acc1);
+                            t0 = x2.x - y.x; t1 = x2.y - y.y; t2 = x2.z - y.z; t3 = x2.w - y.w;
+                            acc2 = fmaf(t0, t0, acc2); acc2 = fmaf(t1, t1, acc2); acc2 = fmaf(t2, t2, acc2); acc2 = fmaf(t3, t3, acc2);
+                        } else {
+                            acc1 = fmaf(x1.x, y.x, acc1); acc1 = fmaf(x1.y, y.y, acc1); acc1 = fmaf(x1.z, y.z, acc1); acc1 = fmaf(x1.w, y.w, acc1);
+                            acc2 = fmaf(x2.x, y.x, acc2); acc2 = fmaf(x2.y, y.y, acc2); acc2 = fmaf(x2.z, y.z, acc2); acc2 = fmaf(x2.w, y.w, acc2);
+                        }
+                    }
                 }
             }
         } else {
-            const __nv_bfloat16* row1 = p.x16 + (size_t)id1 * p.ld16;
-            const __nv_bfloat16* row2 = p.x16 + (size_t)id2 * p.ld16;
-            for (int c = lane; c < p.d; c += 32) {
-                const float x1 = __bfloat162float(row1[c]);
-                const float x2 = __bfloat162float(row2[c]);
-                const float y = q_s[c];
-                if (p.is_l2) {
-                    const float t1 = x1 - y, t2 = x2 - y;
-                    acc1 = fmaf(t1, t1, acc1);
-                    acc2 = fmaf(t2, t2, acc2);
-                } else {
-                    acc1 = fmaf(x1, y, acc1);
-                    acc2 = fmaf(x2, y, acc2);
+            // bf16-stored rows: eight elements per 16-byte load (rows are padded with zeros to 64 columns, q_s likewise)
+            const uint4* row1 = reinterpret_cast<const uint4*>(p.x16 + (size_t)id1 * p.ld16);
+            const uint4* row2 = reinterpret_cast<const uint4*>(p.x16 + (size_t)id2 * p.ld16);
+            const int nv = p.ld16 >> 3;
+            auto fold = [&](const uint4& v, const float* y, float& acc) {
+                const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+                for (int e = 0; e < 4; e++) {
+                    const float lo = __uint_as_float(w[e] << 16), hi = __uint_as_float(w[e] & 0xffff0000u);
+                    if (p.is_l2) {
+                        const float t0 = lo - y[2 * e], t1 = hi - y[2 * e + 1];
+                        acc = fmaf(t0, t0, acc);
+                        acc = fmaf(t1, t1, acc);
+                    } else {
+                        acc = fmaf(lo, y[2 * e], acc);
+                        acc = fmaf(hi, y[2 * e + 1], acc);
+                    }
+                }
+            };
+            for (int c0 = lane; c0 < nv; c0 += 128) {
+                uint4 a[4], b[4];
+#pragma unroll
+                for (int u = 0; u < 4; u++) {
+                    const int c = c0 + 32 * u;
+                    if (c < nv) {
+                        a[u] = __ldg(row1 + c);
+                        b[u] = __ldg(row2 + c);
+                    }
+                }
+#pragma unroll
+                for (int u = 0; u < 4; u++) {
+                    const int c = c0 + 32 * u;
+                    if (c < nv) {
+                        fold(a[u], q_s + 8 * c, acc1);
+                        fold(b[u], q_s + 8 * c, acc2);
+                    }
                 }
             }
         }
@@ -924,6 +981,12 @@ __global__ void __launch_bounds__(RR_THREADS) rerank_kernel(const RerankParams p
     if (tid == 0 && !info[1]) {
         const int slot = atomicAdd(p.nflag, 1);
         p.flag_list[slot] = (int)q;
+    }
+    if (p.dbg && tid == 0) {  // per query: CTA lifetime in cycles, rows re-scored, survivors of the filter, start time
+        p.dbg[16 + 4 * q + 0] = (unsigned long long)(clock64() - rr_t0);
+        p.dbg[16 + 4 * q + 1] = (unsigned long long)R;
+        p.dbg[16 + 4 * q + 2] = (unsigned long long)total;
+        p.dbg[16 + 4 * q + 3] = rr_g0;
     }
     // the last CTA to get here hands the count to the host without a separate D2H copy
     if (tid == 0) {
@@ -1135,7 +1198,7 @@ static void tc_carve(const bfk_index* idx, int64_t nqc, int k, int fb_nparts, ch
     w->fb_D = (float*)take((size_t)8 * k * 4);
     w->fb_I = (int64_t*)take((size_t)8 * k * 8);
     w->fb_part = (uint64_t*)take((size_t)8 * fb_nparts * k * 8);
-    w->dbg = (unsigned long long*)take((size_t)idx->num_sms * 8 * 8 + 8 * 64 * 8 + 16 * 8);  // scan counters, timeline, K5 phases
+    w->dbg = (unsigned long long*)take((size_t)idx->num_sms * 8 * 8 + 8 * 64 * 8 + 16 * 8 + (size_t)nq_pad * 4 * 8);  // scan counters, timeline, K5 phases, K5 per query
     w->pend_g = (uint64_t*)take((size_t)idx->num_sms * TC_BUFCAP * TC_EPI_THREADS * 8);
     const int64_t nr = nqc / 2 + 1;
     w->r_list = (int*)take((size_t)(nr + 1) * 4);
@@ -1278,23 +1341,21 @@ static int tc_pass(bfk_index* idx, const float* qc, int ldq, int64_t nqc, int k,
             pl = single;
         }
     }
-    // eps: |<q,x> - acc| <= c_round ||q|| ||x||, acc = what the tensor pipe returns for <bf16 q, bf16 x>.
-    //   rounding of the operands: (2u + u^2) with u = 2^-9 when both are rounded to bf16, u when the corpus is
-    //     stored in bf16 (the re-score then reads the same rounded rows);
-    //   accumulation: the products of two bf16 numbers are exact in fp32; the pipe adds ld16 of them in fp32.
-    //     Assuming nothing better than truncation (round toward zero, one ulp = 2^-23 relative per addition, the
-    //     weaker of the two rounding modes it could use), the sum is off by at most ld16 * 2^-23 * sum|q_i x_i|
-    //     <= ld16 * 2^-23 ||q|| ||x||.  That is 2^-14 at ld16 = 512 -- the constant used for every d before --
-    //     and 2^-12 at BFK_MAX_D = 2048, so it is kept as a floor and grows with the row length above it.
+    // eps = bound on |<q,x> - acc|, acc = what the tensor pipe returns for <bf16 q, scan copy of x>; put together per
+    // query in prep_queries_kernel from measured rounding losses (see there) plus the accumulation term:
+    //   the products of two bf16 numbers are exact in fp32; the pipe adds ld16 of them in fp32.  Assuming nothing
+    //   better than truncation (round toward zero, one ulp = 2^-23 relative per addition, the weaker of the two
+    //   rounding modes it could use), the sum is off by at most ld16 * 2^-23 * sum|q_i x_i| <= ld16 * 2^-23 ||q|| ||x||.
+    //   That is 2^-14 at ld16 = 512 -- the constant used for every d before -- and 2^-12 at BFK_MAX_D = 2048, so it
+    //   is kept as a floor and grows with the row length above it.
+    const float c_acc = (float)std::max(idx->ld16, 512) / 8388608.f;
     unsigned long long* ts = nullptr;  // this pass's device-clock stamps (bfk_profile_begin), or none
     if (idx->prof_on && idx->prof_ring && idx->prof_used < idx->prof_cap) ts = idx->prof_ring + 4 * idx->prof_used++;
-    const float c_acc = (float)std::max(idx->ld16, 512) / 8388608.f;
-    const float c_round = (idx->storage == BFK_STORE_F32 ? 1.01f / 256.f : 1.01f / 512.f) + c_acc;
     // the fp32 re-score itself (ld16/32 terms per lane, then a 5-step butterfly) and the key's own fma round
     // with at most (ld16/32 + 8) half-ulps of a value that is at most 2 (||q||^2 + ||x||^2)
     const float c_abs = (float)(idx->ld16 / 32 + 8) * 2.f / 16777216.f;
     prep_queries_kernel<<<(unsigned)((pl.nq_pad + 7) / 8), 256, 0, st>>>(qc, ldq, idx->d, nqc, pl.nq_pad, w.q16, idx->ld16,
-                                                                        w.qn, idx->maxn, c_round, c_abs, l2 ? 1 : 0, w.qmargin,
+                                                                        w.qn, idx->maxn, c_acc, c_abs, l2 ? 1 : 0, w.qmargin,
                                                                         w.slots, pl.NS, w.flags, ts);
     BFK_CUDA(cudaGetLastError());
     const CUtensorMap *tmQp, *tmXp;
@@ -1422,7 +1483,25 @@ static int tc_pass(bfk_index* idx, const float* qc, int ldq, int64_t nqc, int k,
     if (r.dbg) {
         unsigned long long h[16];
         BFK_CUDA(cudaMemcpyAsync(h, r.dbg, sizeof(h), cudaMemcpyDeviceToHost, st));
+        std::vector<unsigned long long> pq((size_t)nqc * 4);
+        BFK_CUDA(cudaMemcpyAsync(pq.data(), r.dbg + 16, pq.size() * 8, cudaMemcpyDeviceToHost, st));
         BFK_CUDA(cudaStreamSynchronize(st));
+        {
+            std::vector<unsigned long long> life, rows, surv, start;
+            for (int64_t i = 0; i < nqc; i++) {
+                life.push_back(pq[4 * i]);
+                rows.push_back(pq[4 * i + 1]);
+                surv.push_back(pq[4 * i + 2]);
+                start.push_back(pq[4 * i + 3]);
+            }
+            auto srt = [](std::vector<unsigned long long>& v) { std::sort(v.begin(), v.end()); };
+            srt(life); srt(rows); srt(surv); srt(start);
+            const size_t m = life.size() / 2, l = life.size() - 1;
+            fprintf(stderr, "[bfk rerank, all %lld CTAs] lifetime cycles min/med/max %llu/%llu/%llu | rows re-scored %llu/%llu/%llu | "
+                            "filter survivors %llu/%llu/%llu | start spread %llu ns\n",
+                    (long long)nqc, life[0], life[m], life[l], rows[0], rows[m], rows[l], surv[0], surv[m], surv[l],
+                    start[l] - start[0]);
+        }
         fprintf(stderr, "[bfk rerank, CTA 0, cycles] tmin=%llu filtered=%llu sorted=%llu cut=%llu rescored=%llu sorted2=%llu | survivors=%llu R=%llu\n",
                 h[0], h[1], h[2], h[3], h[4], h[5], h[8], h[9]);
     }

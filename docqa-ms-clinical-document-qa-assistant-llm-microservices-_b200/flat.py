@@ -48,10 +48,14 @@ def _np_ptr(a: np.ndarray) -> ctypes.c_void_p:
     return ctypes.c_void_p(a.ctypes.data)
 
 
-def _torch_stream(device: int) -> ctypes.c_void_p:
+def _torch_stream(device: int):
+    """The current CUDA stream of torch on `device`, as the integer handle the C ABI takes (void*)."""
     import torch
 
-    return ctypes.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+    try:  # the raw handle without building a torch.cuda.Stream object: ~0.2 us instead of ~1.5 us per search
+        return torch._C._cuda_getCurrentRawStream(device)
+    except AttributeError:
+        return torch.cuda.current_stream(device).cuda_stream
 
 
 class IndexFlat:
@@ -177,17 +181,17 @@ class IndexFlat:
             import torch
 
             assert x.is_cuda and x.device.index == self.device, "torch input must live on the index's GPU"
-            xq = x.to(torch.float32).contiguous()
+            xq = x if (x.dtype is torch.float32 and x.is_contiguous()) else x.to(torch.float32).contiguous()
             if D is None:
                 D = torch.empty((n, k), dtype=torch.float32, device=x.device)
             else:
-                assert tuple(D.shape) == (n, k) and D.dtype == torch.float32 and D.is_contiguous()
+                assert D.shape == (n, k) and D.dtype is torch.float32 and D.is_contiguous()
             if I is None:
                 I = torch.empty((n, k), dtype=torch.int64, device=x.device)
             else:
-                assert tuple(I.shape) == (n, k) and I.dtype == torch.int64 and I.is_contiguous()
-            _lib.check(self._L.bfk_search_ex(self._h, ctypes.c_void_p(xq.data_ptr()), n, k,
-                                              ctypes.c_void_p(D.data_ptr()), ctypes.c_void_p(I.data_ptr()), 1,
+                assert I.shape == (n, k) and I.dtype is torch.int64 and I.is_contiguous()
+            # plain integers for the pointer arguments: ctypes converts them itself (argtypes are c_void_p)
+            _lib.check(self._L.bfk_search_ex(self._h, xq.data_ptr(), n, k, D.data_ptr(), I.data_ptr(), 1,
                                               _torch_stream(self.device),
                                               _ALGO[algo] | (_lib.ALGO_FLAG_DEFER if defer else 0), int(id_offset), stp))
             return D, I
