@@ -159,7 +159,9 @@ int tensor_path_supported(const bfk_index* idx, int64_t nq, int k);
 size_t tensor_workspace_bytes(const bfk_index* idx, int64_t nq, int k);
 int search_tensor(bfk_index* idx, const float* q_dev, int ldq, int64_t nq, int k, float* D_dev, int64_t* I_dev,
                   int64_t id_offset, char* ws_tail, size_t ws_tail_bytes, cudaStream_t st,
-                  bfk_search_stats* stats, cudaEvent_t ev0, cudaEvent_t ev1, int defer);
+                  bfk_search_stats* stats, cudaEvent_t ev0, cudaEvent_t ev1, int defer,
+                  const float* q_host = nullptr /* pinned host queries [nq, d]; q_dev then receives a padded copy */,
+                  int out_is_host = 0 /* D_dev / I_dev are pinned host memory written by K5 itself */);
 int search_tensor_finish(bfk_index* idx, cudaStream_t st, int64_t* n_rewritten);
 void search_tensor_forget(bfk_index* idx);
 const int* search_tensor_pending_nflag(bfk_index* idx);

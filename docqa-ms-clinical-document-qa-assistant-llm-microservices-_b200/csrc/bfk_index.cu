@@ -589,9 +589,17 @@ static int search_locked(bfk_index* idx, const float* q, int64_t nq, int k, floa
     // is staged by the driver anyway, synchronously and once per call (queries, D, I: three round trips).
     const size_t q_bytes = sizeof(float) * (size_t)nq * idx->d;
     const size_t out_span = (size_t)((char*)(I_dev + (size_t)nq * k) - (char*)D_dev);  // D, padding, I: contiguous
-    const bool staged = !io_is_device && q_bytes <= STAGE_BYTES && out_span <= STAGE_BYTES;
+    const bool staged = !io_is_device && q_bytes <= STAGE_BYTES / 2 && out_span <= STAGE_BYTES / 2;
     if (staged) stage_buffer(idx);
-    if (staged && idx->h_stage) {
+    // Zero copy for the tensor path: the kernels read the queries from, and write (D, I) to, the pinned staging
+    // buffer themselves (queries in its first half, results in its second).  No copy is enqueued in either
+    // direction and the host only polls the word K5's last CTA writes: two DMA launches, their serialisation with
+    // the kernels and one driver-level stream wait less per search.
+    char* const stage_out = idx->h_stage ? idx->h_stage + STAGE_BYTES / 2 : nullptr;
+    const bool zero_copy = staged && idx->h_stage && algo == BFK_ALGO_TENSOR && !stats && !sel_dev;
+    if (zero_copy) {
+        memcpy(idx->h_stage, q, q_bytes);
+    } else if (staged && idx->h_stage) {
         memcpy(idx->h_stage, q, q_bytes);
         if (ldq != idx->d) BFK_CUDA(cudaMemsetAsync(q_dev, 0, sizeof(float) * (size_t)nq * ldq, st));
         BFK_CUDA(cudaMemcpy2DAsync(q_dev, sizeof(float) * ldq, idx->h_stage, sizeof(float) * idx->d, sizeof(float) * idx->d,
@@ -607,6 +615,10 @@ static int search_locked(bfk_index* idx, const float* q, int64_t nq, int k, floa
     }
     float* D_out = io_is_device ? D : D_dev;
     int64_t* I_out = io_is_device ? I : I_dev;
+    if (zero_copy) {  // same layout as the device pair: D, padding, I
+        D_out = reinterpret_cast<float*>(stage_out);
+        I_out = reinterpret_cast<int64_t*>(stage_out + ((char*)I_dev - (char*)D_dev));
+    }
 
     if (sel_dev) {
         idx->sel = sel_dev;
@@ -631,12 +643,14 @@ static int search_locked(bfk_index* idx, const float* q, int64_t nq, int k, floa
     int rc;
     if (algo == BFK_ALGO_TENSOR) {
         rc = search_tensor(idx, q_dev, ldq, nq, k, D_out, I_out, id_offset, tail, tail_avail, st, stats, ev0, ev1,
-                           (defer || host_defer) ? 1 : 0);
+                           (defer || host_defer) ? 1 : 0, zero_copy ? reinterpret_cast<const float*>(idx->h_stage) : nullptr,
+                           zero_copy ? 1 : 0);
     } else {
         rc = search_exact(idx, q_dev, ldq, nq, k, D_out, I_out, id_offset, tail, tail_avail, st, stats, ev0, ev1);
     }
     const bool staged_out = staged && idx->h_stage;
     auto copy_out = [&]() -> int {
+        if (zero_copy) return 0;  // K5 (or the fall-back's copies) wrote the pinned buffer directly
         if (staged_out) {
             if (cudaMemcpyAsync(idx->h_stage, D_dev, out_span, cudaMemcpyDeviceToHost, st) != cudaSuccess)
                 return fail("search: D2H copy failed");
@@ -648,14 +662,15 @@ static int search_locked(bfk_index* idx, const float* q, int64_t nq, int k, floa
     };
     if (!rc && !io_is_device) rc = copy_out();
     if (!rc && cudaEventRecord(idx->ws_free, st) != cudaSuccess) rc = fail("search: event record failed");
-    if (!rc && (!io_is_device || stats)) {
+    if (!rc && (!io_is_device || stats) && !zero_copy) {
         cudaError_t e = cudaStreamSynchronize(st);
         if (e != cudaSuccess) rc = fail(std::string("search: kernel execution failed: ") + cudaGetErrorString(e));
         if (!rc && st == idx->rows_stream) idx->rows_pending = false;
     }
     if (!rc && host_defer) {
         int64_t rewritten = 0;
-        rc = search_tensor_finish(idx, st, &rewritten);  // the stream is idle: reads the count, re-runs if needed
+        // reads the count (zero copy: polls K5's word in pinned memory instead of waiting for the stream), re-runs if needed
+        rc = search_tensor_finish(idx, st, &rewritten);
         if (!rc && rewritten > 0) {
             rc = copy_out();
             if (!rc && cudaEventRecord(idx->ws_free, st) != cudaSuccess) rc = fail("search: event record failed");
@@ -663,8 +678,9 @@ static int search_locked(bfk_index* idx, const float* q, int64_t nq, int k, floa
         }
     }
     if (!rc && staged_out) {
-        memcpy(D, idx->h_stage, sizeof(float) * (size_t)nq * k);
-        memcpy(I, idx->h_stage + ((char*)I_dev - (char*)D_dev), sizeof(int64_t) * (size_t)nq * k);
+        const char* src = zero_copy ? stage_out : idx->h_stage;
+        memcpy(D, src, sizeof(float) * (size_t)nq * k);
+        memcpy(I, src + ((char*)I_dev - (char*)D_dev), sizeof(int64_t) * (size_t)nq * k);
     }
     if (stats) {
         if (!rc) {

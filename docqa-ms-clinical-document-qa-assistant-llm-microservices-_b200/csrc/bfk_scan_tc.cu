@@ -36,6 +36,7 @@
 
 #include <cfloat>
 #include <cstdlib>
+#include <cstring>
 #include <mutex>
 #include <utility>
 #include <vector>
@@ -576,7 +577,8 @@ __global__ void __launch_bounds__(256) prep_queries_kernel(const float* __restri
                                                            float* __restrict__ qn, const unsigned int* __restrict__ maxn,
                                                            float c_acc, float c_abs, int is_l2, float* __restrict__ qmargin,
                                                            unsigned int* __restrict__ slots, int NS,
-                                                           int* __restrict__ flags, unsigned long long* tstamp) {
+                                                           int* __restrict__ flags, unsigned long long* tstamp,
+                                                           float* __restrict__ q_copy, int ld_copy) {
     const int lane = threadIdx.x & 31;
     const int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     pdl_launch_dependents();  // the scan's prologue may start now; it waits for this grid before reading anything
@@ -595,6 +597,9 @@ __global__ void __launch_bounds__(256) prep_queries_kernel(const float* __restri
         sh += vb * vb;
         se += (v - vb) * (v - vb);
         q16[row * ld16 + c] = b;
+        // the queries may sit in pinned HOST memory (read here once, over PCIe): K5 and the fall-back scan get a
+        // zero-padded fp32 copy in device memory
+        if (q_copy != nullptr && row < nq && c < ld_copy) q_copy[row * ld_copy + c] = v;
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
@@ -639,6 +644,7 @@ struct RerankParams {
     int64_t* I;
     int* nflag;       // [-1] = CTA ticket, [0] = count, [1..] = list
     int* flag_list;
+    int out_is_host;  // D / I point into pinned host memory: results must be visible system-wide before the ticket
     int* h_nflag;     // pinned host words (device-mapped): [0] the count, [1] `seq`, written in that order by the last CTA
     int seq;
     unsigned long long* dbg;  // optional [16] phase clocks of CTA 0 (BFK_TC_DEBUG), else nullptr
@@ -987,8 +993,13 @@ __global__ void __launch_bounds__(RR_THREADS) rerank_kernel(const RerankParams p
         p.dbg[16 + 4 * q + 1] = (unsigned long long)R;
         p.dbg[16 + 4 * q + 2] = (unsigned long long)total;
         p.dbg[16 + 4 * q + 3] = rr_g0;
+        if (q == 0) p.dbg[10] = (unsigned long long)__float_as_uint(p.qmargin[0]);
     }
     // the last CTA to get here hands the count to the host without a separate D2H copy
+    if (p.out_is_host) {  // every thread's (D, I) stores have to reach host memory before this CTA's ticket counts
+        __threadfence_system();
+        __syncthreads();
+    }
     if (tid == 0) {
         if (p.tstamp) atomicMax(p.tstamp + 3, globaltimer_ns());
         __threadfence();
@@ -1314,9 +1325,11 @@ __global__ void __launch_bounds__(256) scatter_results_kernel(const float* __res
 
 // one tensor pass: prep -> K3b scan -> K5 rerank, all enqueued on `st`; w.flags[0] = #uncertified,
 // w.flags[1..] = their indices (relative to qc)
+// q_src / ld_src: where prep reads the fp32 queries -- qc itself, or pinned host memory (then qc receives a copy);
+// out_is_host: D_out / I_out are pinned host memory that K5 writes directly
 static int tc_pass(bfk_index* idx, const float* qc, int ldq, int64_t nqc, int k, float* D_out, int64_t* I_out,
                    int64_t id_offset, const TcWs& w, const TcPlan& plan, cudaStream_t st, cudaEvent_t ev0, cudaEvent_t ev1,
-                   int* launches) {
+                   int* launches, const float* q_src = nullptr, int ld_src = 0, int out_is_host = 0) {
     const bool l2 = idx->metric == BFK_METRIC_L2;
     TcPlan pl = plan;
     // every CTA of the persistent grid must be resident at once for the cluster size chosen; when the pairs do
@@ -1354,9 +1367,10 @@ static int tc_pass(bfk_index* idx, const float* qc, int ldq, int64_t nqc, int k,
     // the fp32 re-score itself (ld16/32 terms per lane, then a 5-step butterfly) and the key's own fma round
     // with at most (ld16/32 + 8) half-ulps of a value that is at most 2 (||q||^2 + ||x||^2)
     const float c_abs = (float)(idx->ld16 / 32 + 8) * 2.f / 16777216.f;
-    prep_queries_kernel<<<(unsigned)((pl.nq_pad + 7) / 8), 256, 0, st>>>(qc, ldq, idx->d, nqc, pl.nq_pad, w.q16, idx->ld16,
-                                                                        w.qn, idx->maxn, c_acc, c_abs, l2 ? 1 : 0, w.qmargin,
-                                                                        w.slots, pl.NS, w.flags, ts);
+    const bool q_remote = q_src != nullptr && q_src != qc;
+    prep_queries_kernel<<<(unsigned)((pl.nq_pad + 7) / 8), 256, 0, st>>>(
+        q_remote ? q_src : qc, q_remote ? ld_src : ldq, idx->d, nqc, pl.nq_pad, w.q16, idx->ld16, w.qn, idx->maxn, c_acc,
+        c_abs, l2 ? 1 : 0, w.qmargin, w.slots, pl.NS, w.flags, ts, q_remote ? const_cast<float*>(qc) : nullptr, ldq);
     BFK_CUDA(cudaGetLastError());
     const CUtensorMap *tmQp, *tmXp;
     BFK_TRY(cached_tmap(idx, 1, w.q16, pl.nq_pad, TC_BM, &tmQp));
@@ -1461,6 +1475,7 @@ static int tc_pass(bfk_index* idx, const float* qc, int ldq, int64_t nqc, int k,
     r.I = I_out;
     r.nflag = w.flags;
     r.flag_list = w.flags + 1;
+    r.out_is_host = out_is_host;
     r.h_nflag = idx->h_flag_dev;
     r.seq = ++idx->flag_seq;
     r.dbg = p.dbg ? w.dbg + (size_t)pl.grid * 8 + 8 * 64 : nullptr;
@@ -1498,9 +1513,9 @@ static int tc_pass(bfk_index* idx, const float* qc, int ldq, int64_t nqc, int k,
             srt(life); srt(rows); srt(surv); srt(start);
             const size_t m = life.size() / 2, l = life.size() - 1;
             fprintf(stderr, "[bfk rerank, all %lld CTAs] lifetime cycles min/med/max %llu/%llu/%llu | rows re-scored %llu/%llu/%llu | "
-                            "filter survivors %llu/%llu/%llu | start spread %llu ns\n",
+                            "filter survivors %llu/%llu/%llu | start spread %llu ns | margin of query 0 (key space) %.6f\n",
                     (long long)nqc, life[0], life[m], life[l], rows[0], rows[m], rows[l], surv[0], surv[m], surv[l],
-                    start[l] - start[0]);
+                    start[l] - start[0], (double)([&] { const uint32_t u = (uint32_t)h[10]; float f; memcpy(&f, &u, 4); return f; }()));
         }
         fprintf(stderr, "[bfk rerank, CTA 0, cycles] tmin=%llu filtered=%llu sorted=%llu cut=%llu rescored=%llu sorted2=%llu | survivors=%llu R=%llu\n",
                 h[0], h[1], h[2], h[3], h[4], h[5], h[8], h[9]);
@@ -1521,6 +1536,7 @@ struct TcPending {
     TcWs w;
     TcPlan pl;
     int fb_nparts;
+    int out_is_host = 0;  // Dc / Ic are pinned host memory
 };
 
 // Reads the pass's flag list (one stream sync) and settles what was not certified: a second tensor pass
@@ -1605,11 +1621,14 @@ static int tc_resolve(bfk_index* idx, const TcPending& c, cudaStream_t st, int64
         *launches += 2;
         for (int j = 0; j < g; j++) {
             const size_t row = (size_t)list[g0 + j] * c.k;
-            BFK_CUDA(cudaMemcpyAsync(c.Dc + row, w.fb_D + (size_t)j * c.k, sizeof(float) * c.k, cudaMemcpyDeviceToDevice, st));
-            BFK_CUDA(cudaMemcpyAsync(c.Ic + row, w.fb_I + (size_t)j * c.k, sizeof(int64_t) * c.k, cudaMemcpyDeviceToDevice, st));
+            // (the destination may be pinned host memory: cudaMemcpyDefault)
+            BFK_CUDA(cudaMemcpyAsync(c.Dc + row, w.fb_D + (size_t)j * c.k, sizeof(float) * c.k, cudaMemcpyDefault, st));
+            BFK_CUDA(cudaMemcpyAsync(c.Ic + row, w.fb_I + (size_t)j * c.k, sizeof(int64_t) * c.k, cudaMemcpyDefault, st));
         }
     }
     *n_fallback += nflag;
+    // rewrites into pinned host memory are copies the caller cannot see coming: they have landed on return
+    if (c.out_is_host) BFK_CUDA(cudaStreamSynchronize(st));
     return 0;
 }
 
@@ -1658,7 +1677,7 @@ void search_tensor_forget(bfk_index* idx) {
 // must settle with search_tensor_finish before trusting the results.
 int search_tensor(bfk_index* idx, const float* q_dev, int ldq, int64_t nq, int k, float* D_dev, int64_t* I_dev,
                   int64_t id_offset, char* ws_tail, size_t ws_tail_bytes, cudaStream_t st, bfk_search_stats* stats,
-                  cudaEvent_t ev0, cudaEvent_t ev1, int defer) {
+                  cudaEvent_t ev0, cudaEvent_t ev1, int defer, const float* q_host, int out_is_host) {
     const int64_t chunk = tc_chunk_queries(idx, nq);
     int launches = 0;
     int64_t n_fallback = 0, n_retry = 0;
@@ -1679,8 +1698,10 @@ int search_tensor(bfk_index* idx, const float* q_dev, int ldq, int64_t nq, int k
         c.Ic = I_dev + (size_t)q0 * k;
         c.id_offset = id_offset;
         c.fb_nparts = fb_nparts;
+        c.out_is_host = out_is_host;
         BFK_TRY(tc_pass(idx, c.qc, ldq, nqc, k, c.Dc, c.Ic, id_offset, c.w, c.pl, st, q0 == 0 ? ev0 : nullptr,
-                        q0 + chunk >= nq ? ev1 : nullptr, &launches));
+                        q0 + chunk >= nq ? ev1 : nullptr, &launches, q_host ? q_host + (size_t)q0 * idx->d : nullptr,
+                        idx->d, out_is_host));
         if (defer && nq <= chunk) {
             std::lock_guard<std::mutex> lk(g_pending_mu);
             g_pending.emplace_back(idx, c);
