@@ -259,7 +259,7 @@ static int rows_out(const bfk_index* idx, int64_t i0, int64_t n, float* out, int
 // buffer the searches use: a cudaMemcpyAsync from pageable memory is staged by the driver anyway, synchronously.
 constexpr size_t STAGE_BYTES = 1 << 20;
 static char* stage_buffer(bfk_index* idx) {
-    if (!idx->h_stage && cudaHostAlloc((void**)&idx->h_stage, STAGE_BYTES, cudaHostAllocDefault) != cudaSuccess) {
+    if (!idx->h_stage && cudaHostAlloc((void**)&idx->h_stage, STAGE_BYTES, cudaHostAllocMapped) != cudaSuccess) {
         cudaGetLastError();
         idx->h_stage = nullptr;
     }
@@ -585,22 +585,56 @@ static int search_locked(bfk_index* idx, const float* q, int64_t nq, int k, floa
     char* tail = ws.take<char>(256);
     size_t tail_avail = idx->ws.bytes - (size_t)(tail - (char*)idx->ws.ptr);
 
-    // Small host-side searches go through one pinned staging buffer: a cudaMemcpyAsync from / to pageable memory
-    // is staged by the driver anyway, synchronously and once per call (queries, D, I: three round trips).
+    // How host-side queries get in and results get out.
+    //   PINNED  the caller's buffer is page-locked (cudaHostAlloc / cudaHostRegister / torch pin_memory): the kernels
+    //           address it directly -- the query preparation reads it over PCIe, K5 writes (D, I) into it;
+    //   STAGED  pageable and small: one memcpy into / out of the index's own pinned buffer, which the kernels address
+    //           the same way (queries in its first half, results in its second);
+    //   COPY    pageable and large, or not the tensor path: cudaMemcpyAsync on the stream, one stream wait at the end.
+    // With PINNED / STAGED nothing is enqueued on the stream but the three kernels, and the host only polls the word
+    // K5's last CTA writes: two DMA launches, their serialisation with the kernels and a driver-level wait less.
+    enum Mode { MODE_DEVICE, MODE_PINNED, MODE_STAGED, MODE_COPY };
     const size_t q_bytes = sizeof(float) * (size_t)nq * idx->d;
     const size_t out_span = (size_t)((char*)(I_dev + (size_t)nq * k) - (char*)D_dev);  // D, padding, I: contiguous
-    const bool staged = !io_is_device && q_bytes <= STAGE_BYTES / 2 && out_span <= STAGE_BYTES / 2;
-    if (staged) stage_buffer(idx);
-    // Zero copy for the tensor path: the kernels read the queries from, and write (D, I) to, the pinned staging
-    // buffer themselves (queries in its first half, results in its second).  No copy is enqueued in either
-    // direction and the host only polls the word K5's last CTA writes: two DMA launches, their serialisation with
-    // the kernels and one driver-level stream wait less per search.
-    char* const stage_out = idx->h_stage ? idx->h_stage + STAGE_BYTES / 2 : nullptr;
-    const bool zero_copy = staged && idx->h_stage && algo == BFK_ALGO_TENSOR && !stats && !sel_dev;
-    if (zero_copy) {
-        memcpy(idx->h_stage, q, q_bytes);
-    } else if (staged && idx->h_stage) {
-        memcpy(idx->h_stage, q, q_bytes);
+    const bool direct_ok = algo == BFK_ALGO_TENSOR && !stats && !sel_dev;  // the exact scan and the selector path copy
+    Mode q_mode = MODE_DEVICE, out_mode = MODE_DEVICE;
+    const float* q_direct = nullptr;  // queries as the GPU addresses them when q_mode is PINNED / STAGED
+    char* stage_out = nullptr;
+    if (!io_is_device) {
+        q_mode = out_mode = MODE_COPY;
+        auto pinned = [](const void* p, void** dev) {
+            cudaPointerAttributes a;
+            if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+                cudaGetLastError();
+                return false;
+            }
+            *dev = a.devicePointer;
+            return a.type == cudaMemoryTypeHost && a.devicePointer != nullptr;
+        };
+        void *qd = nullptr, *Dd = nullptr, *Id = nullptr;
+        if (direct_ok && pinned(q, &qd)) {
+            q_mode = MODE_PINNED;
+            q_direct = static_cast<const float*>(qd);
+        } else if (q_bytes <= STAGE_BYTES / 2 && stage_buffer(idx)) {
+            q_mode = MODE_STAGED;
+            q_direct = reinterpret_cast<const float*>(idx->h_stage);
+        }
+        if (direct_ok && pinned(D, &Dd) && pinned(I, &Id)) out_mode = MODE_PINNED;
+        else if (out_span <= STAGE_BYTES / 2 && stage_buffer(idx)) {
+            out_mode = MODE_STAGED;
+            stage_out = idx->h_stage + STAGE_BYTES / 2;
+        }
+        if (out_mode == MODE_PINNED) {
+            D = static_cast<float*>(Dd);
+            I = static_cast<int64_t*>(Id);
+        }
+    }
+    const bool q_zero_copy = direct_ok && (q_mode == MODE_PINNED || q_mode == MODE_STAGED);
+    const bool out_zero_copy = direct_ok && (out_mode == MODE_PINNED || out_mode == MODE_STAGED);
+    if (q_mode == MODE_STAGED) memcpy(idx->h_stage, q, q_bytes);
+    if (q_zero_copy) {
+        // prep_queries_kernel reads q_direct and leaves a padded fp32 copy in q_dev for K5
+    } else if (q_mode == MODE_STAGED) {
         if (ldq != idx->d) BFK_CUDA(cudaMemsetAsync(q_dev, 0, sizeof(float) * (size_t)nq * ldq, st));
         BFK_CUDA(cudaMemcpy2DAsync(q_dev, sizeof(float) * ldq, idx->h_stage, sizeof(float) * idx->d, sizeof(float) * idx->d,
                                    (size_t)nq, cudaMemcpyHostToDevice, st));
@@ -615,7 +649,10 @@ static int search_locked(bfk_index* idx, const float* q, int64_t nq, int k, floa
     }
     float* D_out = io_is_device ? D : D_dev;
     int64_t* I_out = io_is_device ? I : I_dev;
-    if (zero_copy) {  // same layout as the device pair: D, padding, I
+    if (out_zero_copy && out_mode == MODE_PINNED) {
+        D_out = D;
+        I_out = I;
+    } else if (out_zero_copy) {  // same layout as the device pair: D, padding, I
         D_out = reinterpret_cast<float*>(stage_out);
         I_out = reinterpret_cast<int64_t*>(stage_out + ((char*)I_dev - (char*)D_dev));
     }
@@ -643,16 +680,15 @@ static int search_locked(bfk_index* idx, const float* q, int64_t nq, int k, floa
     int rc;
     if (algo == BFK_ALGO_TENSOR) {
         rc = search_tensor(idx, q_dev, ldq, nq, k, D_out, I_out, id_offset, tail, tail_avail, st, stats, ev0, ev1,
-                           (defer || host_defer) ? 1 : 0, zero_copy ? reinterpret_cast<const float*>(idx->h_stage) : nullptr,
-                           zero_copy ? 1 : 0);
+                           (defer || host_defer) ? 1 : 0, q_zero_copy ? q_direct : nullptr, out_zero_copy ? 1 : 0);
     } else {
         rc = search_exact(idx, q_dev, ldq, nq, k, D_out, I_out, id_offset, tail, tail_avail, st, stats, ev0, ev1);
     }
-    const bool staged_out = staged && idx->h_stage;
+    const bool staged_out = !io_is_device && out_mode == MODE_STAGED;
     auto copy_out = [&]() -> int {
-        if (zero_copy) return 0;  // K5 (or the fall-back's copies) wrote the pinned buffer directly
+        if (out_zero_copy) return 0;  // K5 (or the fall-back's copies) wrote the host buffer directly
         if (staged_out) {
-            if (cudaMemcpyAsync(idx->h_stage, D_dev, out_span, cudaMemcpyDeviceToHost, st) != cudaSuccess)
+            if (cudaMemcpyAsync(stage_out, D_dev, out_span, cudaMemcpyDeviceToHost, st) != cudaSuccess)
                 return fail("search: D2H copy failed");
         } else if (cudaMemcpyAsync(D, D_dev, sizeof(float) * (size_t)nq * k, cudaMemcpyDeviceToHost, st) != cudaSuccess ||
                    cudaMemcpyAsync(I, I_dev, sizeof(int64_t) * (size_t)nq * k, cudaMemcpyDeviceToHost, st) != cudaSuccess) {
@@ -662,7 +698,7 @@ static int search_locked(bfk_index* idx, const float* q, int64_t nq, int k, floa
     };
     if (!rc && !io_is_device) rc = copy_out();
     if (!rc && cudaEventRecord(idx->ws_free, st) != cudaSuccess) rc = fail("search: event record failed");
-    if (!rc && (!io_is_device || stats) && !zero_copy) {
+    if (!rc && (!io_is_device || stats) && !out_zero_copy) {
         cudaError_t e = cudaStreamSynchronize(st);
         if (e != cudaSuccess) rc = fail(std::string("search: kernel execution failed: ") + cudaGetErrorString(e));
         if (!rc && st == idx->rows_stream) idx->rows_pending = false;
@@ -678,9 +714,8 @@ static int search_locked(bfk_index* idx, const float* q, int64_t nq, int k, floa
         }
     }
     if (!rc && staged_out) {
-        const char* src = zero_copy ? stage_out : idx->h_stage;
-        memcpy(D, src, sizeof(float) * (size_t)nq * k);
-        memcpy(I, src + ((char*)I_dev - (char*)D_dev), sizeof(int64_t) * (size_t)nq * k);
+        memcpy(D, stage_out, sizeof(float) * (size_t)nq * k);
+        memcpy(I, stage_out + ((char*)I_dev - (char*)D_dev), sizeof(int64_t) * (size_t)nq * k);
     }
     if (stats) {
         if (!rc) {

@@ -589,8 +589,7 @@ __global__ void __launch_bounds__(256) prep_queries_kernel(const float* __restri
     }
     if (row >= nq_pad) return;
     float ss = 0.f, sh = 0.f, se = 0.f;  // ||q||^2, ||bf16 q||^2, ||q - bf16 q||^2
-    for (int c = lane; c < ld16; c += 32) {
-        float v = (row < nq && c < d) ? q[row * ldq + c] : 0.f;
+    auto take = [&](float v, int c) {
         const __nv_bfloat16 b = __float2bfloat16_rn(v);
         const float vb = __bfloat162float(b);
         ss += v * v;
@@ -600,6 +599,31 @@ __global__ void __launch_bounds__(256) prep_queries_kernel(const float* __restri
         // the queries may sit in pinned HOST memory (read here once, over PCIe): K5 and the fall-back scan get a
         // zero-padded fp32 copy in device memory
         if (q_copy != nullptr && row < nq && c < ld_copy) q_copy[row * ld_copy + c] = v;
+    };
+    const float* src = q + row * ldq;
+    if ((d & 3) == 0 && (ldq & 3) == 0 && (reinterpret_cast<uintptr_t>(q) & 15u) == 0) {
+        // 16-byte loads, four per lane issued before the first is used: a row is one or two round trips to wherever
+        // the queries live (over PCIe when that is pinned host memory), not ld16 / 32 of them
+        for (int c0 = 4 * lane; c0 < ld16; c0 += 512) {
+            float4 v[4];
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                const int c = c0 + 128 * u;
+                v[u] = (row < nq && c < d) ? *reinterpret_cast<const float4*>(src + c) : make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                const int c = c0 + 128 * u;
+                if (c < ld16) {
+                    take(v[u].x, c);
+                    take(v[u].y, c + 1);
+                    take(v[u].z, c + 2);
+                    take(v[u].w, c + 3);
+                }
+            }
+        }
+    } else {
+        for (int c = lane; c < ld16; c += 32) take((row < nq && c < d) ? src[c] : 0.f, c);
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {

@@ -58,6 +58,21 @@ for nq in [int(a) for a in sys.argv[1:]] or [1, 64, 1024, 4096]:
     e1.record()
     torch.cuda.synchronize()
     host = e0.elapsed_time(e1) / reps
+    # the same from page-locked buffers (what bench.py's e2e uses): the kernels address them directly
+    qp = torch.empty((nq, d), dtype=torch.float32, pin_memory=True)
+    qp.copy_(q)
+    Dp = torch.empty((nq, k), dtype=torch.float32, pin_memory=True).numpy()
+    Ip = torch.empty((nq, k), dtype=torch.int64, pin_memory=True).numpy()
+    qpn = qp.numpy()
+    for _ in range(5):
+        idx.search(qpn, k, D=Dp, I=Ip, algo="tensor")
+    e0.record()
+    for _ in range(reps):
+        idx.search(qpn, k, D=Dp, I=Ip, algo="tensor")
+    e1.record()
+    torch.cuda.synchronize()
+    host_pin = e0.elapsed_time(e1) / reps
+    assert (Ip == In).all() and (Ip == I.cpu().numpy()).all()
     print(f"[{tag}] nq={nq}: step {step * 1e3:.1f} us = pass {prof['pass_ms'] / reps * 1e3:.1f} (prep..rerank on the device clock) + "
           f"idle {prof['idle_ms'] / max(reps - 1, 1) * 1e3:.1f} (rerank end -> next prep start); prep->scan {lead:.1f}, scan end->K5 end {trail:.1f}; scan(stamps) {scan_sum / reps * 1e3:.1f} us over {n_scans / reps:.1f} launches, "
-          f"scan(events, serial) {np.mean(ev) * 1e3:.1f} us, host step {host * 1e3:.1f} us, fallback {st.n_fallback}", flush=True)
+          f"scan(events, serial) {np.mean(ev) * 1e3:.1f} us, host step {host * 1e3:.1f} us (pageable) / {host_pin * 1e3:.1f} us (pinned), fallback {st.n_fallback}", flush=True)
