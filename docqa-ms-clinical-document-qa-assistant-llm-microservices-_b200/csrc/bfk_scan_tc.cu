@@ -61,6 +61,34 @@ constexpr int TC_MERGE_N = 4096;
 constexpr int TC_PEND_BYTES = TC_BUFCAP * 256 * 8;  // 32 KiB
 constexpr int TC_TAIL_BYTES = 2 * TC_BN * 4 + (2 * TC_MAX_STAGES + 9) * 8 + 16 + 128 * 4;  // bias + barriers + tmem slot/flag + thr_sh
 
+struct RerankParams {
+    const uint64_t* out_cand;  // [nq_pad][S][KP]
+    const float* out_thr;      // [nq_pad][S]
+    const float* qmargin;      // [nq_pad] 2*eps in key space
+    const float* q;            // [nq][ldq] fp32
+    int ldq;
+    int S;
+    int KP;
+    int k;
+    int is_l2;
+    int storage;
+    const float* x32;
+    int ld32;
+    const __nv_bfloat16* x16;
+    int ld16;
+    int d;
+    int64_t id_offset;
+    float* D;                  // [nq][k]
+    int64_t* I;
+    int* nflag;       // [-1] = CTA ticket, [0] = count, [1..] = list
+    int* flag_list;
+    int out_is_host;  // D / I point into pinned host memory: results must be visible system-wide before the ticket
+    int* h_nflag;     // pinned host words (device-mapped): [0] the count, [1] `seq`, written in that order by the last CTA
+    int seq;
+    unsigned long long* dbg;  // optional [16] phase clocks of CTA 0 (BFK_TC_DEBUG), else nullptr
+    unsigned long long* tstamp;  // optional: [3] = latest CTA end (globaltimer ns), see TcParams
+};
+
 struct TcParams {
     const float* nrm;
     int64_t n;
@@ -88,11 +116,19 @@ struct TcParams {
                          // corpus stream, each CTA stages only half of every corpus tile
     unsigned long long* tstamp;  // optional [4] (globaltimer ns): [0] earliest scan CTA start, [1] latest scan CTA end,
                                  // [2] prep kernel start, [3] latest K5 CTA end; else nullptr
+    int fuse_k5;         // single query tile: K5 runs as the tail of this kernel (the grid meets at `grid_ctr` first)
+    int* grid_ctr;       // zeroed by prep_queries_kernel
+    RerankParams rr;     // K5's arguments when fuse_k5
     int prepass;         // J == 1: tile 0 is first read for each thread's smallest key only (see the epilogue)
     uint64_t* pend_g;    // global pending lists [grid][TC_BUFCAP][256], or nullptr: lists live in shared memory.
                          // Long streams (several query tiles) append rarely and need the 32 KiB for a 4th
                          // corpus stage instead; short streams (nq <= 128) append often and keep them on chip.
 };
+
+template <int RR_THREADS>
+__device__ void rerank_one(const RerankParams& p, const int64_t q, uint64_t* buf, uint64_t* ex, float* q_s, float* red,
+                           int* info, int& cnt_s, const int tid);
+__device__ __forceinline__ void rerank_ticket(const RerankParams& p, int total);
 
 // wait flavour for the single-thread roles + optional cycle accounting
 // (DBG is a template parameter of the kernel: the shipped instantiation carries none of this)
@@ -569,6 +605,43 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
         else tmem_dealloc<512>(tmem_base);
     }
     if (p.tstamp != nullptr && tid == 0) atomicMax(p.tstamp + 1, globaltimer_ns());
+    if constexpr (!PAIR) {
+        if (p.fuse_k5) {
+            // ===== K5 as the tail of the scan (one query tile: nq <= 128) =====
+            // A separate K5 launch starts ~5 us after the scan's last CTA has left (grid drain, memory flush, launch);
+            // here the CTAs of this persistent grid -- all resident, one per SM -- meet at a counter once their lists
+            // are published, and CTA c re-ranks query c, c + grid, ... with all 384 threads in the ring's shared memory.
+            __threadfence();  // this thread's list / threshold stores, before the arrival below
+            __syncthreads();
+            if (tid == 0) {
+                atomicAdd(p.grid_ctr, 1);
+                const long long t0 = clock64();
+                int seen;
+                for (;;) {
+                    asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(seen) : "l"(p.grid_ctr) : "memory");
+                    if (seen >= (int)gridDim.x) break;
+                    if (clock64() - t0 > 4000000000ll) {
+                        printf("libbfk: scan CTAs did not all arrive (block %d saw %d of %d)\n", (int)blockIdx.x, seen, (int)gridDim.x);
+                        __trap();
+                    }
+                    __nanosleep(100);
+                }
+                __threadfence();
+            }
+            __syncthreads();
+            // the ring was last written by TMA (async proxy); it is reused through ordinary stores from here on
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            uint64_t* k5_buf = reinterpret_cast<uint64_t*>(sB);
+            uint64_t* k5_ex = k5_buf + TC_MERGE_N;
+            float* k5_q = reinterpret_cast<float*>(k5_ex + TC_RMAX);
+            float* k5_red = k5_q + BFK_MAX_D;
+            int* k5_info = reinterpret_cast<int*>(k5_red + TC_THREADS / 32);
+            for (int64_t q = blockIdx.x; q < p.nq; q += gridDim.x) {
+                rerank_one<TC_THREADS>(p.rr, q, k5_buf, k5_ex, k5_q, k5_red, k5_info, k5_info[4], tid);
+                if (tid == 0) rerank_ticket(p.rr, p.nq);
+            }
+        }
+    }
 }
 
 // queries fp32 [nq, ldq] -> bf16 [nq_pad, ld16] (zero padded rows and columns) + ||q||^2
@@ -586,6 +659,7 @@ __global__ void __launch_bounds__(256) prep_queries_kernel(const float* __restri
         if (tstamp) atomicMin(tstamp + 2, globaltimer_ns());
         flags[0] = 0;  // uncertified-query count of this pass (K5 appends)
         flags[-1] = 0; // K5's CTA ticket (the last CTA to finish publishes the count to the host)
+        flags[-2] = 0; // arrival counter of the scan CTAs when K5 runs as the scan's tail
     }
     if (row >= nq_pad) return;
     float ss = 0.f, sh = 0.f, se = 0.f;  // ||q||^2, ||bf16 q||^2, ||q - bf16 q||^2
@@ -647,33 +721,6 @@ __global__ void __launch_bounds__(256) prep_queries_kernel(const float* __restri
     for (int i = lane; i < NS; i += 32) slots[row * NS + i] = f2ord(FLT_MAX);
 }
 
-struct RerankParams {
-    const uint64_t* out_cand;  // [nq_pad][S][KP]
-    const float* out_thr;      // [nq_pad][S]
-    const float* qmargin;      // [nq_pad] 2*eps in key space
-    const float* q;            // [nq][ldq] fp32
-    int ldq;
-    int S;
-    int KP;
-    int k;
-    int is_l2;
-    int storage;
-    const float* x32;
-    int ld32;
-    const __nv_bfloat16* x16;
-    int ld16;
-    int d;
-    int64_t id_offset;
-    float* D;                  // [nq][k]
-    int64_t* I;
-    int* nflag;       // [-1] = CTA ticket, [0] = count, [1..] = list
-    int* flag_list;
-    int out_is_host;  // D / I point into pinned host memory: results must be visible system-wide before the ticket
-    int* h_nflag;     // pinned host words (device-mapped): [0] the count, [1] `seq`, written in that order by the last CTA
-    int seq;
-    unsigned long long* dbg;  // optional [16] phase clocks of CTA 0 (BFK_TC_DEBUG), else nullptr
-    unsigned long long* tstamp;  // optional: [3] = latest CTA end (globaltimer ns), see TcParams
-};
 
 // Sorts a[0..n) ascending (n a power of two); called by every thread of the CTA, results visible on return.
 // Up to 64 * (warps in the CTA) elements, warp w keeps elements [64w, 64w + 64) in registers (two per lane):
@@ -746,43 +793,40 @@ __device__ void rr_bitonic(uint64_t* a, int n, int tid, int nthr) {
 // Equal composites (only COMP_EMPTY padding repeats) are ordered by position so that ranks stay distinct.
 template <int NT>
 __device__ void rr_sort(uint64_t* a, int n, int tid) {
-    if (n > 256 || n > NT) {
+    constexpr int NA = NT >= 512 ? 512 : NT >= 256 ? 256 : 128;  // a power of two of the CTA's threads does the counting
+    if (n > 256 || n > NA) {
         rr_bitonic(a, n, tid, NT);
         return;
     }
     __syncthreads();
-    const int P = NT / n;  // power of two, <= 16: the P threads of an element are neighbours in one warp
+    const int P = NA / n;  // power of two, <= 16: the P threads of an element are neighbours in one warp
     const int e = tid / P, part = tid - e * P;
-    const uint64_t v = a[e];
+    uint64_t v = 0;
     int cnt = 0;
-    for (int j = part; j < n; j += P) {
-        const uint64_t o = a[j];
-        cnt += (o < v || (o == v && j < e)) ? 1 : 0;
+    if (tid < NA) {
+        v = a[e];
+        for (int j = part; j < n; j += P) {
+            const uint64_t o = a[j];
+            cnt += (o < v || (o == v && j < e)) ? 1 : 0;
+        }
+        for (int o = P >> 1; o > 0; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
     }
-    for (int o = P >> 1; o > 0; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
     __syncthreads();
-    if (part == 0) a[cnt] = v;
+    if (tid < NA && part == 0) a[cnt] = v;
     __syncthreads();
 }
 
-// RR_THREADS = 512 for long candidate lists (few queries, many streams), 128 when a query has at most 1024
-// candidates (many queries): four times as many queries are then resident per SM.
+// K5 for one query; called by all RR_THREADS threads of a CTA (the stand-alone kernel below, or the tail of the scan
+// kernel when a pass has a single query tile).  buf / ex / q_s / red / info / cnt_s are shared memory.
 template <int RR_THREADS>
-__global__ void __launch_bounds__(RR_THREADS) rerank_kernel(const RerankParams p) {
-    __shared__ uint64_t buf[TC_MERGE_N];
-    __shared__ uint64_t ex[TC_RMAX];
-    __shared__ float q_s[BFK_MAX_D];
-    __shared__ float red[RR_THREADS / 32];
-    __shared__ int info[4];
-    __shared__ int cnt_s;
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int64_t q = blockIdx.x;
+__device__ void rerank_one(const RerankParams& p, const int64_t q, uint64_t* buf, uint64_t* ex, float* q_s, float* red,
+                           int* info, int& cnt_s, const int tid) {
+    const int warp = tid >> 5, lane = tid & 31;
     const int64_t M = (int64_t)p.S * p.KP;
     const uint64_t* src = p.out_cand + q * M;
-    pdl_wait();  // launched behind the scan with programmatic serialization: its lists are complete from here on
     const long long rr_t0 = p.dbg ? clock64() : 0;
     const unsigned long long rr_g0 = p.dbg ? globaltimer_ns() : 0ull;
-#define RR_MARK(i) do { if (p.dbg && blockIdx.x == 0 && tid == 0) p.dbg[i] = (unsigned long long)(clock64() - rr_t0); } while (0)
+#define RR_MARK(i) do { if (p.dbg && q == 0 && tid == 0) p.dbg[i] = (unsigned long long)(clock64() - rr_t0); } while (0)
 
     // two candidates per 16-byte load; the first four loads of every thread are issued now, together with the
     // thresholds and the query, so that the filter below does not start a second round trip to L2
@@ -848,7 +892,7 @@ __global__ void __launch_bounds__(RR_THREADS) rerank_kernel(const RerankParams p
     __syncthreads();
     rr_sort<RR_THREADS>(buf, n, tid);
     RR_MARK(2);
-    if (p.dbg && blockIdx.x == 0 && tid == 0) p.dbg[8] = (unsigned long long)total;
+    if (p.dbg && q == 0 && tid == 0) p.dbg[8] = (unsigned long long)total;
 
     // ---- the cut: A_k + 2*eps in approximate-key space (buf is sorted: the rows inside the cut are a prefix,
     //      counted by all threads at once) ----
@@ -887,7 +931,7 @@ __global__ void __launch_bounds__(RR_THREADS) rerank_kernel(const RerankParams p
     __syncthreads();
     const int R = info[0];
     RR_MARK(3);
-    if (p.dbg && blockIdx.x == 0 && tid == 0) p.dbg[9] = (unsigned long long)R;
+    if (p.dbg && q == 0 && tid == 0) p.dbg[9] = (unsigned long long)R;
     int n_ex = 32;
     while (n_ex < R || n_ex < p.k) n_ex <<= 1;  // <= TC_RMAX since R, k <= TC_RMAX
 
@@ -1019,23 +1063,41 @@ __global__ void __launch_bounds__(RR_THREADS) rerank_kernel(const RerankParams p
         p.dbg[16 + 4 * q + 3] = rr_g0;
         if (q == 0) p.dbg[10] = (unsigned long long)__float_as_uint(p.qmargin[0]);
     }
-    // the last CTA to get here hands the count to the host without a separate D2H copy
-    if (p.out_is_host) {  // every thread's (D, I) stores have to reach host memory before this CTA's ticket counts
-        __threadfence_system();
-        __syncthreads();
-    }
-    if (tid == 0) {
-        if (p.tstamp) atomicMax(p.tstamp + 3, globaltimer_ns());
+    // every thread's (D, I) stores are ordered before the caller's ticket (and reach host memory first when the
+    // outputs are pinned host buffers)
+    if (p.out_is_host) __threadfence_system();
+    else __threadfence();
+    __syncthreads();
+}
+
+// counts this query as done; the last one hands the count of uncertified answers to the host without a separate
+// D2H copy, then the pass's sequence number (the host may be polling it)
+__device__ __forceinline__ void rerank_ticket(const RerankParams& p, int total) {
+    if (p.tstamp) atomicMax(p.tstamp + 3, globaltimer_ns());
+    __threadfence();
+    if (atomicAdd(p.nflag - 1, 1) == total - 1) {
         __threadfence();
-        if (atomicAdd(p.nflag - 1, 1) == (int)gridDim.x - 1) {
-            __threadfence();
-            *reinterpret_cast<volatile int*>(p.h_nflag) = *reinterpret_cast<volatile int*>(p.nflag);
-            __threadfence_system();
-            // every CTA's (D, I) rows were written and fenced before its ticket: the host may stop waiting here
-            *reinterpret_cast<volatile int*>(p.h_nflag + 1) = p.seq;
-            __threadfence_system();
-        }
+        *reinterpret_cast<volatile int*>(p.h_nflag) = *reinterpret_cast<volatile int*>(p.nflag);
+        __threadfence_system();
+        // every query's (D, I) rows were written and fenced before its ticket: the host may stop waiting here
+        *reinterpret_cast<volatile int*>(p.h_nflag + 1) = p.seq;
+        __threadfence_system();
     }
+}
+
+// RR_THREADS = 512 for long candidate lists (few queries, many streams), 128 when a query has at most 1024
+// candidates (many queries): four times as many queries are then resident per SM.
+template <int RR_THREADS>
+__global__ void __launch_bounds__(RR_THREADS) rerank_kernel(const RerankParams p) {
+    __shared__ uint64_t buf[TC_MERGE_N];
+    __shared__ uint64_t ex[TC_RMAX];
+    __shared__ float q_s[BFK_MAX_D];
+    __shared__ float red[RR_THREADS / 32];
+    __shared__ int info[4];
+    __shared__ int cnt_s;
+    pdl_wait();  // launched behind the scan with programmatic serialization: its lists are complete from here on
+    rerank_one<RR_THREADS>(p, (int64_t)blockIdx.x, buf, ex, q_s, red, info, cnt_s, (int)threadIdx.x);
+    if (threadIdx.x == 0) rerank_ticket(p, (int)gridDim.x);
 }
 
 // ---- host side -------------------------------------------------------------------------
@@ -1228,7 +1290,7 @@ static void tc_carve(const bfk_index* idx, int64_t nqc, int k, int fb_nparts, ch
     w->qmargin = (float*)take((size_t)nq_pad * 4);
     w->out_cand = (uint64_t*)take(max_lists * 32 * 8);
     w->out_thr = (float*)take(max_lists * 4);
-    w->flags = (int*)take((size_t)(nqc + 2) * 4) + 1;  // [-1] ticket, [0] count, [1..] list
+    w->flags = (int*)take((size_t)(nqc + 3) * 4) + 2;  // [-2] scan arrivals, [-1] ticket, [0] count, [1..] list
     w->fb_q = (float*)take((size_t)8 * idx->ld32 * 4);
     w->fb_D = (float*)take((size_t)8 * k * 4);
     w->fb_I = (int64_t*)take((size_t)8 * k * 8);
@@ -1434,6 +1496,41 @@ static int tc_pass(bfk_index* idx, const float* qc, int ldq, int64_t nqc, int k,
     p.dbg = dbg_on ? w.dbg : nullptr;
     p.parked = parked ? 1 : 0;
     if (dbg_on) BFK_CUDA(cudaMemsetAsync(w.dbg, 0, (size_t)pl.grid * 64 + 8 * 64 * 8, st));
+    RerankParams r;
+    r.out_cand = w.out_cand;
+    r.out_thr = w.out_thr;
+    r.qmargin = w.qmargin;
+    r.q = qc;
+    r.ldq = ldq;
+    r.S = 2 * pl.S;  // thread-streams
+    r.KP = pl.KP;
+    r.k = k;
+    r.is_l2 = l2 ? 1 : 0;
+    r.storage = idx->storage;
+    r.x32 = idx->x32;
+    r.ld32 = idx->ld32;
+    r.x16 = idx->x16;
+    r.ld16 = idx->ld16;
+    r.d = idx->d;
+    r.id_offset = id_offset;
+    r.D = D_out;
+    r.I = I_out;
+    r.nflag = w.flags;
+    r.flag_list = w.flags + 1;
+    r.out_is_host = out_is_host;
+    r.h_nflag = idx->h_flag_dev;
+    r.seq = ++idx->flag_seq;
+    r.dbg = p.dbg ? w.dbg + (size_t)pl.grid * 8 + 8 * 64 : nullptr;
+    r.tstamp = ts;
+    // a pass with a single query tile (nq <= 128) carries K5 as the tail of the scan kernel
+    static const bool fuse_env = [] {
+        const char* e = getenv("BFK_TC_FUSE_K5");
+        return e ? atoi(e) != 0 : true;
+    }();
+    const bool fuse_k5 = fuse_env && pl.QT == 1 && pl.csize == 1 && !dbg_on && !parked;
+    p.fuse_k5 = fuse_k5 ? 1 : 0;
+    p.grid_ctr = w.flags - 2;
+    p.rr = r;
     if (ev0) cudaEventRecord(ev0, st);
     // the instrumented build of the kernel (wait-cycle counters, timeline marks, parked waits) is a
     // separate instantiation: the single MMA-issuing thread paces the tensor pipe, and even predicated-off
@@ -1478,33 +1575,7 @@ static int tc_pass(bfk_index* idx, const float* qc, int ldq, int64_t nqc, int k,
                         tl[7 * 64 + kb * 4 + 2], tl[7 * 64 + kb * 4 + 3]);
         }
     }
-    RerankParams r;
-    r.out_cand = w.out_cand;
-    r.out_thr = w.out_thr;
-    r.qmargin = w.qmargin;
-    r.q = qc;
-    r.ldq = ldq;
-    r.S = 2 * pl.S;  // thread-streams
-    r.KP = pl.KP;
-    r.k = k;
-    r.is_l2 = l2 ? 1 : 0;
-    r.storage = idx->storage;
-    r.x32 = idx->x32;
-    r.ld32 = idx->ld32;
-    r.x16 = idx->x16;
-    r.ld16 = idx->ld16;
-    r.d = idx->d;
-    r.id_offset = id_offset;
-    r.D = D_out;
-    r.I = I_out;
-    r.nflag = w.flags;
-    r.flag_list = w.flags + 1;
-    r.out_is_host = out_is_host;
-    r.h_nflag = idx->h_flag_dev;
-    r.seq = ++idx->flag_seq;
-    r.dbg = p.dbg ? w.dbg + (size_t)pl.grid * 8 + 8 * 64 : nullptr;
-    r.tstamp = ts;
-    {
+    if (!fuse_k5) {
         const bool small = (int64_t)r.S * r.KP <= 1024 && k <= 32;
         cudaLaunchConfig_t cfg = {};
         cfg.gridDim = dim3((unsigned)nqc);
@@ -1544,7 +1615,7 @@ static int tc_pass(bfk_index* idx, const float* qc, int ldq, int64_t nqc, int k,
         fprintf(stderr, "[bfk rerank, CTA 0, cycles] tmin=%llu filtered=%llu sorted=%llu cut=%llu rescored=%llu sorted2=%llu | survivors=%llu R=%llu\n",
                 h[0], h[1], h[2], h[3], h[4], h[5], h[8], h[9]);
     }
-    *launches += 3;
+    *launches += fuse_k5 ? 2 : 3;
     return 0;
 }
 
