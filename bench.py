@@ -493,17 +493,18 @@ def run_c1i(args):
             wd = os.path.join(tmp, name)
             os.makedirs(wd)
             shutil.copy(src, os.path.join(wd, "vector_store.faiss"))
-            meta0 = [{"text": f"row {i}", "source": "fixture", "type": "note"} for i in range(n0)]
+            meta0 = [{"doc_id": "KB_MTC", "text_content": f"row {i}", "source": "fixture", "type": "knowledge_base"} for i in range(n0)]
             with open(os.path.join(wd, "metadata_store.pkl"), "wb") as f:
                 pickle.dump(meta0, f)
-            ix = indexer_host.SemanticIndexer(index_path=os.path.join(wd, "vector_store.faiss"),
-                                              metadata_path=os.path.join(wd, "metadata_store.pkl"),
-                                              encode=None, incremental_save=incremental)
-            ix.load_state()
+            ix = indexer_host.SemanticIndexer(None, d, index_file=os.path.join(wd, "vector_store.faiss"),
+                                              metadata_file=os.path.join(wd, "metadata_store.pkl"),
+                                              incremental_save=incremental)
+            ix.load_or_build()
             lat = []
             for m in range(n_msg):
                 rows = vec[m * per_msg : (m + 1) * per_msg]
-                metas = [{"text": f"msg {m} chunk {j}", "source": "bench", "type": "note"} for j in range(per_msg)]
+                metas = [{"doc_id": "KB_MTC", "text_content": f"msg {m} chunk {j} " + "x" * 480, "source": f"Dossier Patient {m}",
+                          "type": "patient_file"} for j in range(per_msg)]
                 t0 = time.perf_counter()
                 if batched:
                     ix.add_vectors(rows, metas)
@@ -518,7 +519,7 @@ def run_c1i(args):
                          "messages_per_s": float(n_msg / (lat.sum() * 1e-3))}
         # CPU restatement of indexer.py: numpy rows, full rewrite of both files per message
         xb = xb0.copy()
-        meta = [{"text": f"row {i}", "source": "fixture", "type": "note"} for i in range(n0)]
+        meta = [{"doc_id": "KB_MTC", "text_content": f"row {i}", "source": "fixture", "type": "knowledge_base"} for i in range(n0)]
         wd = os.path.join(tmp, "cpu")
         os.makedirs(wd)
         lat = []
@@ -527,7 +528,8 @@ def run_c1i(args):
             t0 = time.perf_counter()
             for j in range(per_msg):
                 xb = np.concatenate([xb, rows[j : j + 1]], axis=0)
-                meta.append({"text": f"msg {m} chunk {j}", "source": "bench", "type": "note"})
+                meta.append({"doc_id": "KB_MTC", "text_content": f"msg {m} chunk {j} " + "x" * 480, "source": f"Dossier Patient {m}",
+                             "type": "patient_file"})
             with open(os.path.join(wd, "vector_store.faiss"), "wb") as f:
                 f.write(faiss_io.write_index_bytes(xb, metric))
             with open(os.path.join(wd, "metadata_store.pkl"), "wb") as f:

@@ -127,7 +127,7 @@ struct TcParams {
 
 template <int RR_THREADS>
 __device__ void rerank_one(const RerankParams& p, const int64_t q, uint64_t* buf, uint64_t* ex, float* q_s, float* red,
-                           int* info, int& cnt_s, const int tid);
+                           int* info, int& cnt_s, uint32_t* rid, const int tid);
 __device__ __forceinline__ void rerank_ticket(const RerankParams& p, int total);
 
 // wait flavour for the single-thread roles + optional cycle accounting
@@ -636,8 +636,9 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
             float* k5_q = reinterpret_cast<float*>(k5_ex + TC_RMAX);
             float* k5_red = k5_q + BFK_MAX_D;
             int* k5_info = reinterpret_cast<int*>(k5_red + TC_THREADS / 32);
+            uint32_t* k5_rid = reinterpret_cast<uint32_t*>(k5_info + 8);
             for (int64_t q = blockIdx.x; q < p.nq; q += gridDim.x) {
-                rerank_one<TC_THREADS>(p.rr, q, k5_buf, k5_ex, k5_q, k5_red, k5_info, k5_info[4], tid);
+                rerank_one<TC_THREADS>(p.rr, q, k5_buf, k5_ex, k5_q, k5_red, k5_info, k5_info[4], k5_rid, tid);
                 if (tid == 0) rerank_ticket(p.rr, p.nq);
             }
         }
@@ -820,7 +821,7 @@ __device__ void rr_sort(uint64_t* a, int n, int tid) {
 // kernel when a pass has a single query tile).  buf / ex / q_s / red / info / cnt_s are shared memory.
 template <int RR_THREADS>
 __device__ void rerank_one(const RerankParams& p, const int64_t q, uint64_t* buf, uint64_t* ex, float* q_s, float* red,
-                           int* info, int& cnt_s, const int tid) {
+                           int* info, int& cnt_s, uint32_t* rid, const int tid) {
     const int warp = tid >> 5, lane = tid & 31;
     const int64_t M = (int64_t)p.S * p.KP;
     const uint64_t* src = p.out_cand + q * M;
@@ -853,26 +854,43 @@ __device__ void rerank_one(const RerankParams& p, const int64_t q, uint64_t* buf
     for (int w = 1; w < RR_THREADS / 32; w++) tmin = fminf(tmin, red[w]);
     RR_MARK(0);
 
-    // ---- keep only candidates with approximate key <= T (a certified answer never needs the rest:
-    //      the cut A_k + 2*eps must lie below T), then sort the few survivors ----
+    // ---- keep only candidates with approximate key <= T (a certified answer never needs the rest: the cut
+    //      A_k + 2*eps must lie below T).  The survivors are kept as two 32-bit arrays in `buf`'s storage (ordered key,
+    //      row id); appends are aggregated per warp: one shared-memory atomic per warp and step, not per survivor ----
+    uint32_t* skey = reinterpret_cast<uint32_t*>(buf);
+    uint32_t* sid = skey + TC_MERGE_N;
+    int* hist = reinterpret_cast<int*>(ex);  // 256 bins + scratch; `ex` itself is only needed after the cut
+    auto warp_append = [&](bool pred, uint32_t key, uint32_t id, int* counter, uint32_t* keys, uint32_t* ids, int cap) {
+        const unsigned m = __ballot_sync(0xffffffffu, pred);
+        if (m == 0) return;
+        const int leader = __ffs(m) - 1;
+        int base = 0;
+        if (lane == leader) base = atomicAdd(counter, __popc(m));
+        base = __shfl_sync(0xffffffffu, base, leader);
+        if (pred) {
+            const int slot = base + __popc(m & ((1u << lane) - 1u));
+            if (slot < cap) {
+                if (keys) keys[slot] = key;
+                ids[slot] = id;
+            }
+        }
+    };
     {
         const uint32_t tmin_ord = f2ord(tmin);
         auto keep = [&](uint64_t c) {
-            if (c != COMP_EMPTY && (uint32_t)(c >> 32) <= tmin_ord) {
-                const int slot = atomicAdd(&cnt_s, 1);
-                if (slot < TC_MERGE_N) buf[slot] = c;
-            }
+            const uint32_t key = (uint32_t)(c >> 32);
+            warp_append(c != COMP_EMPTY && key <= tmin_ord, key, (uint32_t)c, &cnt_s, skey, sid, TC_MERGE_N);
         };
 #pragma unroll
         for (int u = 0; u < 4; u++) {
             keep(pre[u].x);
             keep(pre[u].y);
         }
-        for (int64_t i0 = tid + 4 * (int64_t)RR_THREADS; i0 < M2; i0 += 4 * RR_THREADS) {
+        for (int64_t b0 = 4 * (int64_t)RR_THREADS; b0 < M2; b0 += 4 * RR_THREADS) {  // same trip count for every thread
             ulonglong2 v[4];
 #pragma unroll
             for (int u = 0; u < 4; u++) {
-                const int64_t i = i0 + (int64_t)u * RR_THREADS;
+                const int64_t i = b0 + tid + (int64_t)u * RR_THREADS;
                 v[u] = i < M2 ? __ldcg(src2 + i) : make_ulonglong2(COMP_EMPTY, COMP_EMPTY);
             }
 #pragma unroll
@@ -886,46 +904,90 @@ __device__ void rerank_one(const RerankParams& p, const int64_t q, uint64_t* buf
     RR_MARK(1);
     const int total = cnt_s;
     const int cnt = min(total, TC_MERGE_N);
-    int n = 64;
-    while (n < cnt) n <<= 1;
-    for (int i = cnt + tid; i < n; i += RR_THREADS) buf[i] = COMP_EMPTY;
-    __syncthreads();
-    rr_sort<RR_THREADS>(buf, n, tid);
-    RR_MARK(2);
     if (p.dbg && q == 0 && tid == 0) p.dbg[8] = (unsigned long long)total;
 
-    // ---- the cut: A_k + 2*eps in approximate-key space (buf is sorted: the rows inside the cut are a prefix,
-    //      counted by all threads at once) ----
+    // ---- A_k = k-th smallest approximate key of the survivors, by radix selection on the ordered 32-bit keys
+    //      (four passes of an 8-bit histogram: linear in the number of survivors, whatever it is; a sort of them --
+    //      what this replaced -- was a third of K5's time) ----
+    const int kk = min(p.k, cnt);
+    uint32_t prefix = 0;
     {
-        const int nvalid = min(cnt, TC_RMAX);
-        const int kk = min(p.k, nvalid);
-        float cut = 0.f;
-        int inside = 0;
-        if (nvalid > 0) {
-            cut = ord2f((uint32_t)(buf[kk - 1] >> 32)) + p.qmargin[q];
-            for (int i = tid; i < nvalid; i += RR_THREADS) inside += ord2f((uint32_t)(buf[i] >> 32)) <= cut ? 1 : 0;
+        int remaining = kk;  // 1-based rank still to find inside the current prefix
+#pragma unroll 1
+        for (int pass = 0; pass < 4 && cnt > 0; pass++) {
+            const int shift = 24 - 8 * pass;
+            if (tid < 256) hist[tid] = 0;
+            __syncthreads();
+            for (int i = tid; i < cnt; i += RR_THREADS) {
+                const uint32_t key = skey[i];
+                if (pass == 0 || (key >> (shift + 8)) == (prefix >> (shift + 8))) atomicAdd(&hist[(key >> shift) & 255u], 1);
+            }
+            __syncthreads();
+            if (warp == 0) {  // lane l owns bins 8l .. 8l+7
+                int h[8], sum = 0;
+#pragma unroll
+                for (int j = 0; j < 8; j++) {
+                    h[j] = hist[8 * lane + j];
+                    sum += h[j];
+                }
+                int incl = sum;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const int t = __shfl_up_sync(0xffffffffu, incl, o);
+                    if (lane >= o) incl += t;
+                }
+                const int before = incl - sum;
+                if (before < remaining && remaining <= incl) {  // exactly one lane
+                    int acc = before, bin = 0;
+#pragma unroll
+                    for (int j = 0; j < 8; j++) {
+                        if (acc < remaining && remaining <= acc + h[j]) {
+                            bin = 8 * lane + j;
+                            hist[257] = remaining - acc;
+                        }
+                        acc += h[j];
+                    }
+                    hist[256] = bin;
+                }
+            }
+            __syncthreads();
+            prefix |= (uint32_t)hist[256] << shift;
+            remaining = hist[257];
+            __syncthreads();
         }
+    }
+    RR_MARK(2);
+
+    // ---- the cut: A_k + 2*eps in approximate-key space; the rows inside it are compacted into `rid` ----
+    {
+        float cut = 0.f;
         if (tid == 0) info[2] = 0;
         __syncthreads();
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) inside += __shfl_xor_sync(0xffffffffu, inside, o);
-        if (lane == 0 && inside) atomicAdd(&info[2], inside);
+        if (cnt > 0) {
+            cut = ord2f(prefix) + p.qmargin[q];
+            const uint32_t cut_ord = f2ord(cut);
+            for (int b0 = 0; b0 < cnt; b0 += RR_THREADS) {
+                const int i = b0 + tid;
+                const bool in = i < cnt && skey[i] <= cut_ord;
+                warp_append(in, 0u, in ? sid[i] : 0u, &info[2], nullptr, rid, TC_RMAX);
+            }
+        }
         __syncthreads();
-        int R = info[2];
         if (tid == 0) {
+            const int inside = info[2];
+            int R = min(inside, TC_RMAX);
             int certified = 1;
-            if (nvalid > 0) {
-                if (R < kk) R = kk;
-                if (!(tmin > cut)) certified = 0;          // a dropped row could still reach the cut
-                if (total > TC_MERGE_N) certified = 0;     // survivors did not fit the sort window
-                if (R == TC_RMAX && cnt > TC_RMAX && ord2f((uint32_t)(buf[TC_RMAX] >> 32)) <= cut)
-                    certified = 0;                         // more rows inside the cut than we re-score
+            if (cnt > 0) {
+                if (!(tmin > cut)) certified = 0;        // a dropped row could still reach the cut
+                if (total > TC_MERGE_N) certified = 0;   // survivors did not fit the window
+                if (inside > TC_RMAX) certified = 0;     // more rows inside the cut than we re-score
             } else {
                 R = 0;
             }
             info[0] = R;
             info[1] = certified;
         }
+        __syncthreads();  // `hist` (aliasing `ex`) is dead from here on
     }
     for (int i = tid; i < TC_RMAX; i += RR_THREADS) ex[i] = COMP_EMPTY;
     __syncthreads();
@@ -941,8 +1003,8 @@ __device__ void rerank_one(const RerankParams& p, const int64_t q, uint64_t* buf
     for (int i = warp; i < R; i += 2 * NW) {
         const int i2 = i + NW;
         const bool two = i2 < R;
-        const uint32_t id1 = (uint32_t)(buf[i] & 0xffffffffu);
-        const uint32_t id2 = two ? (uint32_t)(buf[i2] & 0xffffffffu) : id1;
+        const uint32_t id1 = rid[i];
+        const uint32_t id2 = two ? rid[i2] : id1;
         float acc1 = 0.f, acc2 = 0.f;
         // All loads of both rows are issued before the first is used (up to four 16-byte loads per row and lane:
         // d <= 512 in fp32, d <= 1024 in bf16 in one go): written as load-use-load-use the three column steps of a
@@ -1095,8 +1157,9 @@ __global__ void __launch_bounds__(RR_THREADS) rerank_kernel(const RerankParams p
     __shared__ float red[RR_THREADS / 32];
     __shared__ int info[4];
     __shared__ int cnt_s;
+    __shared__ uint32_t rid[TC_RMAX];  // rows inside the cut
     pdl_wait();  // launched behind the scan with programmatic serialization: its lists are complete from here on
-    rerank_one<RR_THREADS>(p, (int64_t)blockIdx.x, buf, ex, q_s, red, info, cnt_s, (int)threadIdx.x);
+    rerank_one<RR_THREADS>(p, (int64_t)blockIdx.x, buf, ex, q_s, red, info, cnt_s, rid, (int)threadIdx.x);
     if (threadIdx.x == 0) rerank_ticket(p, (int)gridDim.x);
 }
 
@@ -1527,7 +1590,7 @@ static int tc_pass(bfk_index* idx, const float* qc, int ldq, int64_t nqc, int k,
         const char* e = getenv("BFK_TC_FUSE_K5");
         return e ? atoi(e) != 0 : true;
     }();
-    const bool fuse_k5 = fuse_env && pl.QT == 1 && pl.csize == 1 && !dbg_on && !parked;
+    const bool fuse_k5 = fuse_env && pl.QT == 1 && pl.csize == 1;
     p.fuse_k5 = fuse_k5 ? 1 : 0;
     p.grid_ctr = w.flags - 2;
     p.rr = r;
