@@ -61,34 +61,6 @@ constexpr int TC_MERGE_N = 4096;
 constexpr int TC_PEND_BYTES = TC_BUFCAP * 256 * 8;  // 32 KiB
 constexpr int TC_TAIL_BYTES = 2 * TC_BN * 4 + (2 * TC_MAX_STAGES + 9) * 8 + 16 + 128 * 4;  // bias + barriers + tmem slot/flag + thr_sh
 
-struct RerankParams {
-    const uint64_t* out_cand;  // [nq_pad][S][KP]
-    const float* out_thr;      // [nq_pad][S]
-    const float* qmargin;      // [nq_pad] 2*eps in key space
-    const float* q;            // [nq][ldq] fp32
-    int ldq;
-    int S;
-    int KP;
-    int k;
-    int is_l2;
-    int storage;
-    const float* x32;
-    int ld32;
-    const __nv_bfloat16* x16;
-    int ld16;
-    int d;
-    int64_t id_offset;
-    float* D;                  // [nq][k]
-    int64_t* I;
-    int* nflag;       // [-1] = CTA ticket, [0] = count, [1..] = list
-    int* flag_list;
-    int out_is_host;  // D / I point into pinned host memory: results must be visible system-wide before the ticket
-    int* h_nflag;     // pinned host words (device-mapped): [0] the count, [1] `seq`, written in that order by the last CTA
-    int seq;
-    unsigned long long* dbg;  // optional [16] phase clocks of CTA 0 (BFK_TC_DEBUG), else nullptr
-    unsigned long long* tstamp;  // optional: [3] = latest CTA end (globaltimer ns), see TcParams
-};
-
 struct TcParams {
     const float* nrm;
     int64_t n;
@@ -116,19 +88,11 @@ struct TcParams {
                          // corpus stream, each CTA stages only half of every corpus tile
     unsigned long long* tstamp;  // optional [4] (globaltimer ns): [0] earliest scan CTA start, [1] latest scan CTA end,
                                  // [2] prep kernel start, [3] latest K5 CTA end; else nullptr
-    int fuse_k5;         // single query tile: K5 runs as the tail of this kernel (the grid meets at `grid_ctr` first)
-    int* grid_ctr;       // zeroed by prep_queries_kernel
-    RerankParams rr;     // K5's arguments when fuse_k5
     int prepass;         // J == 1: tile 0 is first read for each thread's smallest key only (see the epilogue)
     uint64_t* pend_g;    // global pending lists [grid][TC_BUFCAP][256], or nullptr: lists live in shared memory.
                          // Long streams (several query tiles) append rarely and need the 32 KiB for a 4th
                          // corpus stage instead; short streams (nq <= 128) append often and keep them on chip.
 };
-
-template <int RR_THREADS>
-__device__ void rerank_one(const RerankParams& p, const int64_t q, uint64_t* buf, uint64_t* ex, float* q_s, float* red,
-                           int* info, int& cnt_s, uint32_t* rid, const int tid);
-__device__ __forceinline__ void rerank_ticket(const RerankParams& p, int total);
 
 // wait flavour for the single-thread roles + optional cycle accounting
 // (DBG is a template parameter of the kernel: the shipped instantiation carries none of this)
@@ -605,44 +569,6 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
         else tmem_dealloc<512>(tmem_base);
     }
     if (p.tstamp != nullptr && tid == 0) atomicMax(p.tstamp + 1, globaltimer_ns());
-    if constexpr (!PAIR) {
-        if (p.fuse_k5) {
-            // ===== K5 as the tail of the scan (one query tile: nq <= 128) =====
-            // A separate K5 launch starts ~5 us after the scan's last CTA has left (grid drain, memory flush, launch);
-            // here the CTAs of this persistent grid -- all resident, one per SM -- meet at a counter once their lists
-            // are published, and CTA c re-ranks query c, c + grid, ... with all 384 threads in the ring's shared memory.
-            __threadfence();  // this thread's list / threshold stores, before the arrival below
-            __syncthreads();
-            if (tid == 0) {
-                atomicAdd(p.grid_ctr, 1);
-                const long long t0 = clock64();
-                int seen;
-                for (;;) {
-                    asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(seen) : "l"(p.grid_ctr) : "memory");
-                    if (seen >= (int)gridDim.x) break;
-                    if (clock64() - t0 > 4000000000ll) {
-                        printf("libbfk: scan CTAs did not all arrive (block %d saw %d of %d)\n", (int)blockIdx.x, seen, (int)gridDim.x);
-                        __trap();
-                    }
-                    __nanosleep(100);
-                }
-                __threadfence();
-            }
-            __syncthreads();
-            // the ring was last written by TMA (async proxy); it is reused through ordinary stores from here on
-            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-            uint64_t* k5_buf = reinterpret_cast<uint64_t*>(sB);
-            uint64_t* k5_ex = k5_buf + TC_MERGE_N;
-            float* k5_q = reinterpret_cast<float*>(k5_ex + TC_RMAX);
-            float* k5_red = k5_q + BFK_MAX_D;
-            int* k5_info = reinterpret_cast<int*>(k5_red + TC_THREADS / 32);
-            uint32_t* k5_rid = reinterpret_cast<uint32_t*>(k5_info + 8);
-            for (int64_t q = blockIdx.x; q < p.nq; q += gridDim.x) {
-                rerank_one<TC_THREADS>(p.rr, q, k5_buf, k5_ex, k5_q, k5_red, k5_info, k5_info[4], k5_rid, tid);
-                if (tid == 0) rerank_ticket(p.rr, p.nq);
-            }
-        }
-    }
 }
 
 // queries fp32 [nq, ldq] -> bf16 [nq_pad, ld16] (zero padded rows and columns) + ||q||^2
@@ -660,7 +586,6 @@ __global__ void __launch_bounds__(256) prep_queries_kernel(const float* __restri
         if (tstamp) atomicMin(tstamp + 2, globaltimer_ns());
         flags[0] = 0;  // uncertified-query count of this pass (K5 appends)
         flags[-1] = 0; // K5's CTA ticket (the last CTA to finish publishes the count to the host)
-        flags[-2] = 0; // arrival counter of the scan CTAs when K5 runs as the scan's tail
     }
     if (row >= nq_pad) return;
     float ss = 0.f, sh = 0.f, se = 0.f;  // ||q||^2, ||bf16 q||^2, ||q - bf16 q||^2
@@ -722,6 +647,33 @@ __global__ void __launch_bounds__(256) prep_queries_kernel(const float* __restri
     for (int i = lane; i < NS; i += 32) slots[row * NS + i] = f2ord(FLT_MAX);
 }
 
+struct RerankParams {
+    const uint64_t* out_cand;  // [nq_pad][S][KP]
+    const float* out_thr;      // [nq_pad][S]
+    const float* qmargin;      // [nq_pad] 2*eps in key space
+    const float* q;            // [nq][ldq] fp32
+    int ldq;
+    int S;
+    int KP;
+    int k;
+    int is_l2;
+    int storage;
+    const float* x32;
+    int ld32;
+    const __nv_bfloat16* x16;
+    int ld16;
+    int d;
+    int64_t id_offset;
+    float* D;                  // [nq][k]
+    int64_t* I;
+    int* nflag;       // [-1] = CTA ticket, [0] = count, [1..] = list
+    int* flag_list;
+    int out_is_host;  // D / I point into pinned host memory: results must be visible system-wide before the ticket
+    int* h_nflag;     // pinned host words (device-mapped): [0] the count, [1] `seq`, written in that order by the last CTA
+    int seq;
+    unsigned long long* dbg;  // optional [16] phase clocks of CTA 0 (BFK_TC_DEBUG), else nullptr
+    unsigned long long* tstamp;  // optional: [3] = latest CTA end (globaltimer ns), see TcParams
+};
 
 // Sorts a[0..n) ascending (n a power of two); called by every thread of the CTA, results visible on return.
 // Up to 64 * (warps in the CTA) elements, warp w keeps elements [64w, 64w + 64) in registers (two per lane):
@@ -794,40 +746,43 @@ __device__ void rr_bitonic(uint64_t* a, int n, int tid, int nthr) {
 // Equal composites (only COMP_EMPTY padding repeats) are ordered by position so that ranks stay distinct.
 template <int NT>
 __device__ void rr_sort(uint64_t* a, int n, int tid) {
-    constexpr int NA = NT >= 512 ? 512 : NT >= 256 ? 256 : 128;  // a power of two of the CTA's threads does the counting
-    if (n > 256 || n > NA) {
+    if (n > 256 || n > NT) {
         rr_bitonic(a, n, tid, NT);
         return;
     }
     __syncthreads();
-    const int P = NA / n;  // power of two, <= 16: the P threads of an element are neighbours in one warp
+    const int P = NT / n;  // power of two, <= 16: the P threads of an element are neighbours in one warp
     const int e = tid / P, part = tid - e * P;
-    uint64_t v = 0;
+    const uint64_t v = a[e];
     int cnt = 0;
-    if (tid < NA) {
-        v = a[e];
-        for (int j = part; j < n; j += P) {
-            const uint64_t o = a[j];
-            cnt += (o < v || (o == v && j < e)) ? 1 : 0;
-        }
-        for (int o = P >> 1; o > 0; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+    for (int j = part; j < n; j += P) {
+        const uint64_t o = a[j];
+        cnt += (o < v || (o == v && j < e)) ? 1 : 0;
     }
+    for (int o = P >> 1; o > 0; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
     __syncthreads();
-    if (tid < NA && part == 0) a[cnt] = v;
+    if (part == 0) a[cnt] = v;
     __syncthreads();
 }
 
-// K5 for one query; called by all RR_THREADS threads of a CTA (the stand-alone kernel below, or the tail of the scan
-// kernel when a pass has a single query tile).  buf / ex / q_s / red / info / cnt_s are shared memory.
+// RR_THREADS = 512 for long candidate lists (few queries, many streams), 128 when a query has at most 1024
+// candidates (many queries): four times as many queries are then resident per SM.
 template <int RR_THREADS>
-__device__ void rerank_one(const RerankParams& p, const int64_t q, uint64_t* buf, uint64_t* ex, float* q_s, float* red,
-                           int* info, int& cnt_s, uint32_t* rid, const int tid) {
-    const int warp = tid >> 5, lane = tid & 31;
+__global__ void __launch_bounds__(RR_THREADS) rerank_kernel(const RerankParams p) {
+    __shared__ uint64_t buf[TC_MERGE_N];
+    __shared__ uint64_t ex[TC_RMAX];
+    __shared__ float q_s[BFK_MAX_D];
+    __shared__ float red[RR_THREADS / 32];
+    __shared__ int info[4];
+    __shared__ int cnt_s;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int64_t q = blockIdx.x;
     const int64_t M = (int64_t)p.S * p.KP;
     const uint64_t* src = p.out_cand + q * M;
+    pdl_wait();  // launched behind the scan with programmatic serialization: its lists are complete from here on
     const long long rr_t0 = p.dbg ? clock64() : 0;
     const unsigned long long rr_g0 = p.dbg ? globaltimer_ns() : 0ull;
-#define RR_MARK(i) do { if (p.dbg && q == 0 && tid == 0) p.dbg[i] = (unsigned long long)(clock64() - rr_t0); } while (0)
+#define RR_MARK(i) do { if (p.dbg && blockIdx.x == 0 && tid == 0) p.dbg[i] = (unsigned long long)(clock64() - rr_t0); } while (0)
 
     // two candidates per 16-byte load; the first four loads of every thread are issued now, together with the
     // thresholds and the query, so that the filter below does not start a second round trip to L2
@@ -854,43 +809,26 @@ __device__ void rerank_one(const RerankParams& p, const int64_t q, uint64_t* buf
     for (int w = 1; w < RR_THREADS / 32; w++) tmin = fminf(tmin, red[w]);
     RR_MARK(0);
 
-    // ---- keep only candidates with approximate key <= T (a certified answer never needs the rest: the cut
-    //      A_k + 2*eps must lie below T).  The survivors are kept as two 32-bit arrays in `buf`'s storage (ordered key,
-    //      row id); appends are aggregated per warp: one shared-memory atomic per warp and step, not per survivor ----
-    uint32_t* skey = reinterpret_cast<uint32_t*>(buf);
-    uint32_t* sid = skey + TC_MERGE_N;
-    int* hist = reinterpret_cast<int*>(ex);  // 256 bins + scratch; `ex` itself is only needed after the cut
-    auto warp_append = [&](bool pred, uint32_t key, uint32_t id, int* counter, uint32_t* keys, uint32_t* ids, int cap) {
-        const unsigned m = __ballot_sync(0xffffffffu, pred);
-        if (m == 0) return;
-        const int leader = __ffs(m) - 1;
-        int base = 0;
-        if (lane == leader) base = atomicAdd(counter, __popc(m));
-        base = __shfl_sync(0xffffffffu, base, leader);
-        if (pred) {
-            const int slot = base + __popc(m & ((1u << lane) - 1u));
-            if (slot < cap) {
-                if (keys) keys[slot] = key;
-                ids[slot] = id;
-            }
-        }
-    };
+    // ---- keep only candidates with approximate key <= T (a certified answer never needs the rest:
+    //      the cut A_k + 2*eps must lie below T), then sort the few survivors ----
     {
         const uint32_t tmin_ord = f2ord(tmin);
         auto keep = [&](uint64_t c) {
-            const uint32_t key = (uint32_t)(c >> 32);
-            warp_append(c != COMP_EMPTY && key <= tmin_ord, key, (uint32_t)c, &cnt_s, skey, sid, TC_MERGE_N);
+            if (c != COMP_EMPTY && (uint32_t)(c >> 32) <= tmin_ord) {
+                const int slot = atomicAdd(&cnt_s, 1);
+                if (slot < TC_MERGE_N) buf[slot] = c;
+            }
         };
 #pragma unroll
         for (int u = 0; u < 4; u++) {
             keep(pre[u].x);
             keep(pre[u].y);
         }
-        for (int64_t b0 = 4 * (int64_t)RR_THREADS; b0 < M2; b0 += 4 * RR_THREADS) {  // same trip count for every thread
+        for (int64_t i0 = tid + 4 * (int64_t)RR_THREADS; i0 < M2; i0 += 4 * RR_THREADS) {
             ulonglong2 v[4];
 #pragma unroll
             for (int u = 0; u < 4; u++) {
-                const int64_t i = b0 + tid + (int64_t)u * RR_THREADS;
+                const int64_t i = i0 + (int64_t)u * RR_THREADS;
                 v[u] = i < M2 ? __ldcg(src2 + i) : make_ulonglong2(COMP_EMPTY, COMP_EMPTY);
             }
 #pragma unroll
@@ -904,96 +842,52 @@ __device__ void rerank_one(const RerankParams& p, const int64_t q, uint64_t* buf
     RR_MARK(1);
     const int total = cnt_s;
     const int cnt = min(total, TC_MERGE_N);
-    if (p.dbg && q == 0 && tid == 0) p.dbg[8] = (unsigned long long)total;
-
-    // ---- A_k = k-th smallest approximate key of the survivors, by radix selection on the ordered 32-bit keys
-    //      (four passes of an 8-bit histogram: linear in the number of survivors, whatever it is; a sort of them --
-    //      what this replaced -- was a third of K5's time) ----
-    const int kk = min(p.k, cnt);
-    uint32_t prefix = 0;
-    {
-        int remaining = kk;  // 1-based rank still to find inside the current prefix
-#pragma unroll 1
-        for (int pass = 0; pass < 4 && cnt > 0; pass++) {
-            const int shift = 24 - 8 * pass;
-            if (tid < 256) hist[tid] = 0;
-            __syncthreads();
-            for (int i = tid; i < cnt; i += RR_THREADS) {
-                const uint32_t key = skey[i];
-                if (pass == 0 || (key >> (shift + 8)) == (prefix >> (shift + 8))) atomicAdd(&hist[(key >> shift) & 255u], 1);
-            }
-            __syncthreads();
-            if (warp == 0) {  // lane l owns bins 8l .. 8l+7
-                int h[8], sum = 0;
-#pragma unroll
-                for (int j = 0; j < 8; j++) {
-                    h[j] = hist[8 * lane + j];
-                    sum += h[j];
-                }
-                int incl = sum;
-#pragma unroll
-                for (int o = 1; o < 32; o <<= 1) {
-                    const int t = __shfl_up_sync(0xffffffffu, incl, o);
-                    if (lane >= o) incl += t;
-                }
-                const int before = incl - sum;
-                if (before < remaining && remaining <= incl) {  // exactly one lane
-                    int acc = before, bin = 0;
-#pragma unroll
-                    for (int j = 0; j < 8; j++) {
-                        if (acc < remaining && remaining <= acc + h[j]) {
-                            bin = 8 * lane + j;
-                            hist[257] = remaining - acc;
-                        }
-                        acc += h[j];
-                    }
-                    hist[256] = bin;
-                }
-            }
-            __syncthreads();
-            prefix |= (uint32_t)hist[256] << shift;
-            remaining = hist[257];
-            __syncthreads();
-        }
-    }
+    int n = 64;
+    while (n < cnt) n <<= 1;
+    for (int i = cnt + tid; i < n; i += RR_THREADS) buf[i] = COMP_EMPTY;
+    __syncthreads();
+    rr_sort<RR_THREADS>(buf, n, tid);
     RR_MARK(2);
+    if (p.dbg && blockIdx.x == 0 && tid == 0) p.dbg[8] = (unsigned long long)total;
 
-    // ---- the cut: A_k + 2*eps in approximate-key space; the rows inside it are compacted into `rid` ----
+    // ---- the cut: A_k + 2*eps in approximate-key space (buf is sorted: the rows inside the cut are a prefix,
+    //      counted by all threads at once) ----
     {
+        const int nvalid = min(cnt, TC_RMAX);
+        const int kk = min(p.k, nvalid);
         float cut = 0.f;
+        int inside = 0;
+        if (nvalid > 0) {
+            cut = ord2f((uint32_t)(buf[kk - 1] >> 32)) + p.qmargin[q];
+            for (int i = tid; i < nvalid; i += RR_THREADS) inside += ord2f((uint32_t)(buf[i] >> 32)) <= cut ? 1 : 0;
+        }
         if (tid == 0) info[2] = 0;
         __syncthreads();
-        if (cnt > 0) {
-            cut = ord2f(prefix) + p.qmargin[q];
-            const uint32_t cut_ord = f2ord(cut);
-            for (int b0 = 0; b0 < cnt; b0 += RR_THREADS) {
-                const int i = b0 + tid;
-                const bool in = i < cnt && skey[i] <= cut_ord;
-                warp_append(in, 0u, in ? sid[i] : 0u, &info[2], nullptr, rid, TC_RMAX);
-            }
-        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) inside += __shfl_xor_sync(0xffffffffu, inside, o);
+        if (lane == 0 && inside) atomicAdd(&info[2], inside);
         __syncthreads();
+        int R = info[2];
         if (tid == 0) {
-            const int inside = info[2];
-            int R = min(inside, TC_RMAX);
             int certified = 1;
-            if (cnt > 0) {
-                if (!(tmin > cut)) certified = 0;        // a dropped row could still reach the cut
-                if (total > TC_MERGE_N) certified = 0;   // survivors did not fit the window
-                if (inside > TC_RMAX) certified = 0;     // more rows inside the cut than we re-score
+            if (nvalid > 0) {
+                if (R < kk) R = kk;
+                if (!(tmin > cut)) certified = 0;          // a dropped row could still reach the cut
+                if (total > TC_MERGE_N) certified = 0;     // survivors did not fit the sort window
+                if (R == TC_RMAX && cnt > TC_RMAX && ord2f((uint32_t)(buf[TC_RMAX] >> 32)) <= cut)
+                    certified = 0;                         // more rows inside the cut than we re-score
             } else {
                 R = 0;
             }
             info[0] = R;
             info[1] = certified;
         }
-        __syncthreads();  // `hist` (aliasing `ex`) is dead from here on
     }
     for (int i = tid; i < TC_RMAX; i += RR_THREADS) ex[i] = COMP_EMPTY;
     __syncthreads();
     const int R = info[0];
     RR_MARK(3);
-    if (p.dbg && q == 0 && tid == 0) p.dbg[9] = (unsigned long long)R;
+    if (p.dbg && blockIdx.x == 0 && tid == 0) p.dbg[9] = (unsigned long long)R;
     int n_ex = 32;
     while (n_ex < R || n_ex < p.k) n_ex <<= 1;  // <= TC_RMAX since R, k <= TC_RMAX
 
@@ -1003,8 +897,8 @@ __device__ void rerank_one(const RerankParams& p, const int64_t q, uint64_t* buf
     for (int i = warp; i < R; i += 2 * NW) {
         const int i2 = i + NW;
         const bool two = i2 < R;
-        const uint32_t id1 = rid[i];
-        const uint32_t id2 = two ? rid[i2] : id1;
+        const uint32_t id1 = (uint32_t)(buf[i] & 0xffffffffu);
+        const uint32_t id2 = two ? (uint32_t)(buf[i2] & 0xffffffffu) : id1;
         float acc1 = 0.f, acc2 = 0.f;
         // All loads of both rows are issued before the first is used (up to four 16-byte loads per row and lane:
         // d <= 512 in fp32, d <= 1024 in bf16 in one go): written as load-use-load-use the three column steps of a
@@ -1125,42 +1019,23 @@ __device__ void rerank_one(const RerankParams& p, const int64_t q, uint64_t* buf
         p.dbg[16 + 4 * q + 3] = rr_g0;
         if (q == 0) p.dbg[10] = (unsigned long long)__float_as_uint(p.qmargin[0]);
     }
-    // every thread's (D, I) stores are ordered before the caller's ticket (and reach host memory first when the
-    // outputs are pinned host buffers)
-    if (p.out_is_host) __threadfence_system();
-    else __threadfence();
-    __syncthreads();
-}
-
-// counts this query as done; the last one hands the count of uncertified answers to the host without a separate
-// D2H copy, then the pass's sequence number (the host may be polling it)
-__device__ __forceinline__ void rerank_ticket(const RerankParams& p, int total) {
-    if (p.tstamp) atomicMax(p.tstamp + 3, globaltimer_ns());
-    __threadfence();
-    if (atomicAdd(p.nflag - 1, 1) == total - 1) {
-        __threadfence();
-        *reinterpret_cast<volatile int*>(p.h_nflag) = *reinterpret_cast<volatile int*>(p.nflag);
+    // the last CTA to get here hands the count to the host without a separate D2H copy
+    if (p.out_is_host) {  // every thread's (D, I) stores have to reach host memory before this CTA's ticket counts
         __threadfence_system();
-        // every query's (D, I) rows were written and fenced before its ticket: the host may stop waiting here
-        *reinterpret_cast<volatile int*>(p.h_nflag + 1) = p.seq;
-        __threadfence_system();
+        __syncthreads();
     }
-}
-
-// RR_THREADS = 512 for long candidate lists (few queries, many streams), 128 when a query has at most 1024
-// candidates (many queries): four times as many queries are then resident per SM.
-template <int RR_THREADS>
-__global__ void __launch_bounds__(RR_THREADS) rerank_kernel(const RerankParams p) {
-    __shared__ uint64_t buf[TC_MERGE_N];
-    __shared__ uint64_t ex[TC_RMAX];
-    __shared__ float q_s[BFK_MAX_D];
-    __shared__ float red[RR_THREADS / 32];
-    __shared__ int info[4];
-    __shared__ int cnt_s;
-    __shared__ uint32_t rid[TC_RMAX];  // rows inside the cut
-    pdl_wait();  // launched behind the scan with programmatic serialization: its lists are complete from here on
-    rerank_one<RR_THREADS>(p, (int64_t)blockIdx.x, buf, ex, q_s, red, info, cnt_s, rid, (int)threadIdx.x);
-    if (threadIdx.x == 0) rerank_ticket(p, (int)gridDim.x);
+    if (tid == 0) {
+        if (p.tstamp) atomicMax(p.tstamp + 3, globaltimer_ns());
+        __threadfence();
+        if (atomicAdd(p.nflag - 1, 1) == (int)gridDim.x - 1) {
+            __threadfence();
+            *reinterpret_cast<volatile int*>(p.h_nflag) = *reinterpret_cast<volatile int*>(p.nflag);
+            __threadfence_system();
+            // every CTA's (D, I) rows were written and fenced before its ticket: the host may stop waiting here
+            *reinterpret_cast<volatile int*>(p.h_nflag + 1) = p.seq;
+            __threadfence_system();
+        }
+    }
 }
 
 // ---- host side -------------------------------------------------------------------------
@@ -1353,7 +1228,7 @@ static void tc_carve(const bfk_index* idx, int64_t nqc, int k, int fb_nparts, ch
     w->qmargin = (float*)take((size_t)nq_pad * 4);
     w->out_cand = (uint64_t*)take(max_lists * 32 * 8);
     w->out_thr = (float*)take(max_lists * 4);
-    w->flags = (int*)take((size_t)(nqc + 3) * 4) + 2;  // [-2] scan arrivals, [-1] ticket, [0] count, [1..] list
+    w->flags = (int*)take((size_t)(nqc + 2) * 4) + 1;  // [-1] ticket, [0] count, [1..] list
     w->fb_q = (float*)take((size_t)8 * idx->ld32 * 4);
     w->fb_D = (float*)take((size_t)8 * k * 4);
     w->fb_I = (int64_t*)take((size_t)8 * k * 8);
@@ -1559,41 +1434,6 @@ static int tc_pass(bfk_index* idx, const float* qc, int ldq, int64_t nqc, int k,
     p.dbg = dbg_on ? w.dbg : nullptr;
     p.parked = parked ? 1 : 0;
     if (dbg_on) BFK_CUDA(cudaMemsetAsync(w.dbg, 0, (size_t)pl.grid * 64 + 8 * 64 * 8, st));
-    RerankParams r;
-    r.out_cand = w.out_cand;
-    r.out_thr = w.out_thr;
-    r.qmargin = w.qmargin;
-    r.q = qc;
-    r.ldq = ldq;
-    r.S = 2 * pl.S;  // thread-streams
-    r.KP = pl.KP;
-    r.k = k;
-    r.is_l2 = l2 ? 1 : 0;
-    r.storage = idx->storage;
-    r.x32 = idx->x32;
-    r.ld32 = idx->ld32;
-    r.x16 = idx->x16;
-    r.ld16 = idx->ld16;
-    r.d = idx->d;
-    r.id_offset = id_offset;
-    r.D = D_out;
-    r.I = I_out;
-    r.nflag = w.flags;
-    r.flag_list = w.flags + 1;
-    r.out_is_host = out_is_host;
-    r.h_nflag = idx->h_flag_dev;
-    r.seq = ++idx->flag_seq;
-    r.dbg = p.dbg ? w.dbg + (size_t)pl.grid * 8 + 8 * 64 : nullptr;
-    r.tstamp = ts;
-    // a pass with a single query tile (nq <= 128) carries K5 as the tail of the scan kernel
-    static const bool fuse_env = [] {
-        const char* e = getenv("BFK_TC_FUSE_K5");
-        return e ? atoi(e) != 0 : true;
-    }();
-    const bool fuse_k5 = fuse_env && pl.QT == 1 && pl.csize == 1;
-    p.fuse_k5 = fuse_k5 ? 1 : 0;
-    p.grid_ctr = w.flags - 2;
-    p.rr = r;
     if (ev0) cudaEventRecord(ev0, st);
     // the instrumented build of the kernel (wait-cycle counters, timeline marks, parked waits) is a
     // separate instantiation: the single MMA-issuing thread paces the tensor pipe, and even predicated-off
@@ -1638,7 +1478,33 @@ static int tc_pass(bfk_index* idx, const float* qc, int ldq, int64_t nqc, int k,
                         tl[7 * 64 + kb * 4 + 2], tl[7 * 64 + kb * 4 + 3]);
         }
     }
-    if (!fuse_k5) {
+    RerankParams r;
+    r.out_cand = w.out_cand;
+    r.out_thr = w.out_thr;
+    r.qmargin = w.qmargin;
+    r.q = qc;
+    r.ldq = ldq;
+    r.S = 2 * pl.S;  // thread-streams
+    r.KP = pl.KP;
+    r.k = k;
+    r.is_l2 = l2 ? 1 : 0;
+    r.storage = idx->storage;
+    r.x32 = idx->x32;
+    r.ld32 = idx->ld32;
+    r.x16 = idx->x16;
+    r.ld16 = idx->ld16;
+    r.d = idx->d;
+    r.id_offset = id_offset;
+    r.D = D_out;
+    r.I = I_out;
+    r.nflag = w.flags;
+    r.flag_list = w.flags + 1;
+    r.out_is_host = out_is_host;
+    r.h_nflag = idx->h_flag_dev;
+    r.seq = ++idx->flag_seq;
+    r.dbg = p.dbg ? w.dbg + (size_t)pl.grid * 8 + 8 * 64 : nullptr;
+    r.tstamp = ts;
+    {
         const bool small = (int64_t)r.S * r.KP <= 1024 && k <= 32;
         cudaLaunchConfig_t cfg = {};
         cfg.gridDim = dim3((unsigned)nqc);
@@ -1678,7 +1544,7 @@ static int tc_pass(bfk_index* idx, const float* qc, int ldq, int64_t nqc, int k,
         fprintf(stderr, "[bfk rerank, CTA 0, cycles] tmin=%llu filtered=%llu sorted=%llu cut=%llu rescored=%llu sorted2=%llu | survivors=%llu R=%llu\n",
                 h[0], h[1], h[2], h[3], h[4], h[5], h[8], h[9]);
     }
-    *launches += fuse_k5 ? 2 : 3;
+    *launches += 3;
     return 0;
 }
 
