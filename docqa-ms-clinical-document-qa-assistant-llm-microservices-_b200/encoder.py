@@ -148,8 +148,19 @@ class MiniLMEncoder:
         return self.forward(ids, mask), mask
 
     def encode(self, texts):
-        """SentenceTransformer.encode(list[str]) -> float32 numpy [n, hidden]."""
+        """SentenceTransformer.encode(list[str]) -> float32 numpy [n, hidden] (indexer.py:37: the text as it is)."""
         single = isinstance(texts, str)
         ids, mask = self._tokenize([texts] if single else texts)
         out = self.encode_ids(ids, mask).cpu().numpy()
         return out[0] if single else out
+
+    # ---- langchain HuggingFaceEmbeddings-shaped entry points (llm-qa/main.py:25) -------------------
+    # HuggingFaceEmbeddings replaces every newline by a space before it encodes, on the document side and on the
+    # query side alike (SURVEY section 2.2); llm-qa embeds its questions through it, so a question with line breaks
+    # must be embedded the same way here or it lands somewhere else in the index.
+    def embed_documents(self, texts) -> list[list[float]]:
+        texts = [t.replace("\n", " ") for t in texts]
+        return self.encode(texts).tolist() if texts else []
+
+    def embed_query(self, text: str) -> list[float]:
+        return self.embed_documents([text])[0]

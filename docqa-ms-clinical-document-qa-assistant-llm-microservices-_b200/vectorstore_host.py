@@ -23,6 +23,7 @@ product); -1 ids are skipped.  Extension: `exact_filter=True` lowers the filter 
 """
 from __future__ import annotations
 
+import math
 import operator
 import pickle
 import uuid
@@ -34,6 +35,7 @@ from .idselect import IDSelectorBitmap, SearchParameters
 
 EUCLIDEAN_DISTANCE = "EUCLIDEAN_DISTANCE"
 MAX_INNER_PRODUCT = "MAX_INNER_PRODUCT"
+COSINE = "COSINE"
 
 
 @dataclass
@@ -297,6 +299,27 @@ class FlatVectorStore:
         self.index_to_docstore_id = {i: _id for i, _id in enumerate(remaining)}
         return True
 
+    # ---- relevance scores (what VectorStoreRetriever uses for search_type="similarity_score_threshold") ------
+    def _relevance_fn(self):
+        """langchain_community FAISS._select_relevance_score_fn: distance -> relevance in [0, 1]."""
+        if self.distance_strategy == MAX_INNER_PRODUCT:
+            return lambda s: 1.0 - s if s > 0 else -1.0 * s   # _max_inner_product_relevance_score_fn
+        if self.distance_strategy == EUCLIDEAN_DISTANCE:
+            return lambda s: 1.0 - s / math.sqrt(2)            # _euclidean_relevance_score_fn (unit-norm embeddings)
+        if self.distance_strategy == COSINE:
+            return lambda s: 1.0 - s
+        raise ValueError(f"Unknown distance strategy {self.distance_strategy}")
+
+    def similarity_search_with_relevance_scores(self, query: str, k: int = 4, filter=None, fetch_k: int = 20, **kwargs):
+        """(doc, relevance) pairs, relevance in [0, 1]; `score_threshold` keeps relevance >= threshold -- the
+        opposite sense of the raw-distance threshold of similarity_search_with_score, as in LangChain."""
+        score_threshold = kwargs.pop("score_threshold", None)
+        fn = self._relevance_fn()
+        docs = [(doc, fn(s)) for doc, s in self.similarity_search_with_score(query, k, filter=filter, fetch_k=fetch_k, **kwargs)]
+        if score_threshold is not None:
+            docs = [(doc, r) for doc, r in docs if r >= score_threshold]
+        return docs
+
     def merge_from(self, target: "FlatVectorStore") -> None:
         starting_len = len(self.index_to_docstore_id)
         full_info = []
@@ -329,6 +352,8 @@ class Retriever:
     def invoke(self, query: str, **_):
         if self.search_type == "mmr":
             return self.vectorstore.max_marginal_relevance_search(query, **self.search_kwargs)
+        if self.search_type == "similarity_score_threshold":  # relevance >= threshold, as VectorStoreRetriever does
+            return [d for d, _ in self.vectorstore.similarity_search_with_relevance_scores(query, **self.search_kwargs)]
         return self.vectorstore.similarity_search(query, **self.search_kwargs)
 
     get_relevant_documents = invoke

@@ -165,3 +165,21 @@ def test_indexer_with_the_gpu_encoder(bfk, tmp_path):
     assert I[:, 0].tolist() == [0, 1, 2, 3, 4]
     ix.save_state()
     assert bfk.read_index(ix.index_file).ntotal == 40
+
+
+def test_query_side_replaces_newlines_like_huggingface_embeddings(bfk):
+    """llm-qa/main.py:25 embeds questions through langchain's HuggingFaceEmbeddings, which turns every newline into a
+    space first; embed_query / embed_documents do the same, encode() (indexer.py:37) leaves the text alone."""
+
+    class SpaceTokenizer(FakeTokenizer):  # splits on blanks only, so a newline inside a word changes the tokens
+        def __call__(self, texts, **kw):
+            return super().__call__([t.replace(" ", "\t") .replace("\n", "\\n").replace("\t", " ") for t in texts], **kw)
+
+    m = hf_model(layers=1, vocab=400)
+    enc = bfk.MiniLMEncoder.from_hf_model(m, tokenizer=SpaceTokenizer(400))
+    q = "douleur thoracique\ndepuis trois jours"
+    flat = enc.encode([q.replace("\n", " ")])[0]
+    np.testing.assert_array_equal(np.array(enc.embed_query(q), dtype=np.float32), flat)
+    np.testing.assert_array_equal(np.array(enc.embed_documents([q, "a b"])[0], dtype=np.float32), flat)
+    assert not np.allclose(enc.encode([q])[0], flat)  # the raw text tokenises differently
+    assert enc.embed_documents([]) == []

@@ -74,8 +74,17 @@ def test_filter_threshold_and_exact_filter(tmp_path):
     near = store.similarity_search_with_score(q, k=10, filter=lambda m: m["source"] == "herbs.csv", fetch_k=30,
                                               score_threshold=1.0)
     assert near and all(s <= 1.0 for _, s in near)
-    th = store.as_retriever(search_type="similarity_score_threshold", search_kwargs={"score_threshold": 1e-9, "k": 5})
+    # the retriever's threshold is a RELEVANCE in [0, 1] (1 - d / sqrt(2) for L2), kept when >= threshold, as
+    # VectorStoreRetriever -> similarity_search_with_relevance_scores does; the raw-distance sense above is the
+    # opposite one
+    th = store.as_retriever(search_type="similarity_score_threshold", search_kwargs={"score_threshold": 0.999, "k": 5})
     assert [d.page_content for d in th.invoke(q)] == [q]
+    rel = store.similarity_search_with_relevance_scores(q, k=5)
+    raw = store.similarity_search_with_score(q, k=5)
+    assert [r for _, r in rel] == pytest.approx([1.0 - s / np.sqrt(2.0) for _, s in raw])
+    assert rel[0][1] == pytest.approx(1.0, abs=1e-6) and all(a[1] >= b[1] for a, b in zip(rel, rel[1:]))
+    loose = store.as_retriever(search_type="similarity_score_threshold", search_kwargs={"score_threshold": 0.0, "k": 5})
+    assert len(loose.invoke(q)) == len([1 for _, r in rel if r >= 0.0])
     with pytest.raises(ValueError):
         store.as_retriever(search_type="bogus")
 
