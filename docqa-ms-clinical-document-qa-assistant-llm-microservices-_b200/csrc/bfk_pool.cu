@@ -13,6 +13,7 @@
 #include <cstdlib>
 
 #include "bfk_common.cuh"
+#include "bfk_ptx.cuh"
 
 namespace bfk {
 
@@ -216,12 +217,270 @@ __global__ void __launch_bounds__(512) pool_norm_kernel(const TokT* __restrict__
     }
 }
 
+// ---- streaming form: persistent CTAs, token rows arrive by bulk copies --------------------------------------
+// The kernel above is one CTA per chunk with register-staged 128-bit loads: every chunk pays a prologue (mask
+// read, block sum) and an epilogue (fold, normalise, store) during which its CTA streams nothing -- 0.83 of the
+// measured HBM bandwidth on full bf16 chunks, 0.66 on ragged ones, whose smaller payload hides the bubbles even
+// less.  Here a CTA lives for the whole call.  Warp 8 is the producer: it reads the attention mask of the NEXT
+// chunk while the current one streams, finds its last valid token, and copies the valid prefix of the chunk --
+// token rows are contiguous, so 16 rows are ONE `cp.async.bulk` -- into a ring of shared-memory stages with
+// mbarrier completion.  Warps 0-7 consume: thread = (token group, 16-byte column vector), conflict-free LDS.128,
+// fp32 accumulation, tokens whose mask is 0 inside the prefix are skipped (never multiplied: a masked row may
+// hold anything).  While the consumers fold and store one chunk, the producer is already filling the ring with
+// the next one, so HBM never sees the epilogue.
+constexpr int PS_CWARPS = 8;
+constexpr int PS_CTHREADS = PS_CWARPS * 32;
+constexpr int PS_THREADS = PS_CTHREADS + 32;
+constexpr int PS_MAX_STAGES = 8;
+constexpr int PS_MAX_T = 512;  // mask values of one chunk live in the producer's registers (16 per lane)
+
+__device__ __forceinline__ void ps_consumer_sync() { asm volatile("bar.sync 1, %0;" ::"n"(PS_CTHREADS) : "memory"); }
+
+__device__ __forceinline__ float ps_consumer_sum(float v, float* red, int tid) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    ps_consumer_sync();
+    if ((tid & 31) == 0) red[tid >> 5] = v;
+    ps_consumer_sync();
+    float s = 0.f;
+#pragma unroll
+    for (int w = 0; w < PS_CWARPS; w++) s += red[w];
+    return s;
+}
+
+struct PoolStreamParams {
+    const void* tok;
+    const void* mask;
+    int mask_dtype;
+    int64_t B;
+    int T, H, CV, TG;
+    int stage_tok, stages, stage_bytes, row_bytes;
+    float* out32;
+    int64_t out32_ld;
+    __nv_bfloat16* out16;
+    int64_t out16_ld;
+    float* out_nrm;
+    unsigned int* maxn;
+};
+
+template <typename TokT>
+__global__ void __launch_bounds__(PS_THREADS, 2) pool_stream_kernel(const PoolStreamParams p) {
+    constexpr int VEC = TokLoad<TokT>::VEC;
+    extern __shared__ __align__(128) unsigned char ps_smem[];
+    unsigned char* ring = ps_smem;
+    float* mask_f = reinterpret_cast<float*>(ring + (size_t)p.stages * p.stage_bytes);  // [2][T]
+    float* red = mask_f + 2 * p.T;                                                    // [TG][CV*VEC]
+    float* scratch = red + p.TG * p.CV * VEC;                                         // [32]
+    float* meta_cnt = scratch + 32;                                                   // [2] sum of the mask
+    int* meta_tmax = reinterpret_cast<int*>(meta_cnt + 2);                            // [2] last valid token + 1
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(meta_tmax + 2);                  // (8-byte aligned by the host's sizes)
+    uint64_t* empty_bar = full_bar + PS_MAX_STAGES;
+    uint64_t* meta_ready = empty_bar + PS_MAX_STAGES;  // [2] the producer has published mask_f / meta of this parity
+    uint64_t* mask_free = meta_ready + 2;              // [2] the consumers are done with them
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+
+    if (tid == 0) {
+        for (int i = 0; i < p.stages; i++) {
+            mbar_init(&full_bar[i], 1);
+            mbar_init(&empty_bar[i], PS_CTHREADS);
+        }
+        for (int i = 0; i < 2; i++) {
+            mbar_init(&meta_ready[i], 1);
+            mbar_init(&mask_free[i], PS_CTHREADS);
+        }
+        fence_mbar_init();
+    }
+    __syncthreads();
+
+    if (warp == PS_CWARPS) {
+        // ===================== producer =====================
+        float mreg[PS_MAX_T / 32];
+        auto fetch_mask = [&](int64_t b) {
+#pragma unroll
+            for (int j = 0; j < PS_MAX_T / 32; j++) {
+                const int t = lane + 32 * j;
+                mreg[j] = t < p.T ? load_mask(p.mask, p.mask_dtype, b * p.T + t) : 0.f;
+            }
+        };
+        if ((int64_t)blockIdx.x < p.B) fetch_mask(blockIdx.x);
+        uint32_t st = 0, ph = 0;
+        int it = 0;
+        for (int64_t b = blockIdx.x; b < p.B; b += gridDim.x, it++) {
+            const int par = it & 1;
+            const uint32_t mph = (uint32_t)(it >> 1) & 1u;
+            int tmax = 0;
+            float cnt = 0.f;
+#pragma unroll
+            for (int j = 0; j < PS_MAX_T / 32; j++) {
+                cnt += mreg[j];
+                if (mreg[j] != 0.f) tmax = lane + 32 * j + 1;
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+                tmax = max(tmax, __shfl_xor_sync(0xffffffffu, tmax, o));
+            }
+            mbar_wait(&mask_free[par], mph ^ 1u);  // the chunk that used this parity two chunks ago is finished
+#pragma unroll
+            for (int j = 0; j < PS_MAX_T / 32; j++) {
+                const int t = lane + 32 * j;
+                if (t < p.T) mask_f[par * p.T + t] = mreg[j];
+            }
+            if (lane == 0) {
+                meta_cnt[par] = cnt;
+                meta_tmax[par] = tmax;
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&meta_ready[par]);
+            const int64_t nb = b + gridDim.x;
+            if (nb < p.B) fetch_mask(nb);  // in flight while this chunk's rows are being requested
+            if (lane == 0) {
+                const unsigned char* src = reinterpret_cast<const unsigned char*>(p.tok) + (size_t)b * p.T * p.row_bytes;
+                for (int t0 = 0; t0 < tmax; t0 += p.stage_tok) {
+                    const uint32_t bytes = (uint32_t)min(p.stage_tok, tmax - t0) * (uint32_t)p.row_bytes;
+                    mbar_wait(&empty_bar[st], ph ^ 1u);
+                    mbar_expect_tx(&full_bar[st], bytes);
+                    bulk_g2s(ring + (size_t)st * p.stage_bytes, src + (size_t)t0 * p.row_bytes, bytes, &full_bar[st]);
+                    if (++st == (uint32_t)p.stages) {
+                        st = 0;
+                        ph ^= 1u;
+                    }
+                }
+            }
+            __syncwarp();
+        }
+        return;
+    }
+
+    // ===================== consumers =====================
+    const int cv = tid % p.CV, tg = tid / p.CV;
+    const bool active = tg < p.TG;
+    uint32_t st = 0, ph = 0;
+    int it = 0;
+    for (int64_t b = blockIdx.x; b < p.B; b += gridDim.x, it++) {
+        const int par = it & 1;
+        mbar_wait(&meta_ready[par], (uint32_t)(it >> 1) & 1u);
+        const int tmax = meta_tmax[par];
+        const float cnt = meta_cnt[par];
+        const float* mf = mask_f + par * p.T;
+        float acc[VEC];
+#pragma unroll
+        for (int e = 0; e < VEC; e++) acc[e] = 0.f;
+        for (int t0 = 0; t0 < tmax; t0 += p.stage_tok) {
+            const int rows = min(p.stage_tok, tmax - t0);
+            mbar_wait(&full_bar[st], ph);
+            if (active) {
+                const unsigned char* base = ring + (size_t)st * p.stage_bytes + (size_t)cv * 16;
+                for (int r = tg; r < rows; r += p.TG) {
+                    const float m = mf[t0 + r];
+                    if (m != 0.f) TokLoad<TokT>::fma(*reinterpret_cast<const uint4*>(base + (size_t)r * p.row_bytes), m, acc);
+                }
+            }
+            mbar_arrive(&empty_bar[st]);
+            if (++st == (uint32_t)p.stages) {
+                st = 0;
+                ph ^= 1u;
+            }
+        }
+        // ---- fold the token groups, normalise, store (the producer is already streaming the next chunk) ----
+        if (active) {
+#pragma unroll
+            for (int e = 0; e < VEC; e++) red[(tg * p.CV + cv) * VEC + e] = acc[e];
+        }
+        ps_consumer_sync();
+        for (int c = tid; c < p.H; c += PS_CTHREADS) {
+            float s = 0.f;
+            for (int g = 0; g < p.TG; g++) s += red[g * p.CV * VEC + c];
+            red[c] = s / fmaxf(cnt, 1e-9f);  // group 0's slot now holds e[c]
+        }
+        ps_consumer_sync();
+        float ss = 0.f;
+        for (int c = tid; c < p.H; c += PS_CTHREADS) ss += red[c] * red[c];
+        ss = ps_consumer_sum(ss, scratch, tid);
+        const float inv = 1.0f / fmaxf(sqrtf(ss), 1e-12f);
+        float ss2 = 0.f, se2 = 0.f;
+        const int64_t hi = p.out16 ? p.out16_ld : (p.out32 ? p.out32_ld : p.H);
+        for (int64_t c = tid; c < hi; c += PS_CTHREADS) {
+            float v = (c < p.H) ? red[c] * inv : 0.f;
+            if (p.out32 && c < p.out32_ld) p.out32[b * p.out32_ld + c] = v;
+            if (p.out16) {
+                __nv_bfloat16 h = __float2bfloat16_rn(v);
+                p.out16[b * p.out16_ld + c] = h;
+                if (!p.out32) v = __bfloat162float(h);  // bf16-stored index: the norm of what is stored
+                else {
+                    const float e = v - __bfloat162float(h);  // what the scan copy loses against the fp32 master row
+                    se2 += e * e;
+                }
+            }
+            ss2 += v * v;
+        }
+        if (p.out_nrm) {
+            ss2 = ps_consumer_sum(ss2, scratch, tid);
+            se2 = ps_consumer_sum(se2, scratch, tid);
+            if (tid == 0) {
+                p.out_nrm[b] = ss2;
+                if (p.maxn) {
+                    atomicMax(p.maxn, __float_as_uint(ss2));
+                    if (se2 > 0.f) atomicMax(p.maxn + 1, __float_as_uint(se2));
+                }
+            }
+        }
+        ps_consumer_sync();          // everyone is done with red / scratch / mask_f of this chunk
+        mbar_arrive(&mask_free[par]);
+    }
+}
+
 template <typename TokT>
 static int launch_pool_t(const TokT* tok, const void* mask, int mask_dtype, int64_t B, int T, int H, float* out32,
                          int64_t out32_ld, __nv_bfloat16* out16, int64_t out16_ld, float* out_nrm, unsigned int* maxn,
                          cudaStream_t st) {
     constexpr int VEC = TokLoad<TokT>::VEC;
     const bool vec = (H % VEC == 0) && ((reinterpret_cast<uintptr_t>(tok) & 15u) == 0);
+    // the streaming kernel: 16-byte aligned rows, the chunk's mask in the producer's registers, >= 2 ring stages
+    static const bool stream_on = [] {
+        const char* e = getenv("BFK_POOL_STREAM");
+        return e ? atoi(e) != 0 : true;
+    }();
+    if (stream_on && vec && T <= PS_MAX_T && H / VEC <= PS_CTHREADS) {
+        PoolStreamParams q;
+        q.row_bytes = H * (int)sizeof(TokT);
+        q.stage_tok = std::max(1, std::min(16, 24576 / q.row_bytes));
+        q.stage_bytes = q.stage_tok * q.row_bytes;  // a multiple of 16
+        q.CV = H / VEC;
+        q.TG = std::max(1, std::min(PS_CTHREADS / q.CV, q.stage_tok));
+        const size_t fixed = sizeof(float) * ((size_t)2 * T + (size_t)q.TG * H + 36) + 8 * (2 * PS_MAX_STAGES + 4) + 128;
+        q.stages = (int)std::min<size_t>(PS_MAX_STAGES, (size_t)(98304) / (size_t)q.stage_bytes);
+        if (q.stages >= 2) {
+            const size_t smem = (size_t)q.stages * q.stage_bytes + fixed;
+            q.tok = tok;
+            q.mask = mask;
+            q.mask_dtype = mask_dtype;
+            q.B = B;
+            q.T = T;
+            q.H = H;
+            q.out32 = out32;
+            q.out32_ld = out32_ld;
+            q.out16 = out16;
+            q.out16_ld = out16_ld;
+            q.out_nrm = out_nrm;
+            q.maxn = maxn;
+            auto kern = pool_stream_kernel<TokT>;
+            static bool attr_set[64] = {false};  // per instantiation and device
+            int dev = 0, sms = 148;
+            BFK_CUDA(cudaGetDevice(&dev));
+            if (dev < 0 || dev >= 64 || !attr_set[dev]) {
+                BFK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
+                if (dev >= 0 && dev < 64) attr_set[dev] = true;
+            }
+            cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+            if (smem <= 112 * 1024) {
+                const unsigned grid = (unsigned)std::min<int64_t>(B, (int64_t)sms * 2);  // two resident CTAs per SM
+                kern<<<grid, PS_THREADS, smem, st>>>(q);
+                BFK_CUDA(cudaGetLastError());
+                return 0;
+            }
+        }
+    }
     const int vw = vec ? VEC : 1;
     const int CV = H / vw;
     if (CV > 512) return fail("pool_normalize: hidden size too large for this (unaligned) layout");
