@@ -227,7 +227,9 @@ __global__ void __launch_bounds__(512) pool_norm_kernel(const TokT* __restrict__
 // mbarrier completion.  Warps 0-7 consume: thread = (token group, 16-byte column vector), conflict-free LDS.128,
 // fp32 accumulation, tokens whose mask is 0 inside the prefix are skipped (never multiplied: a masked row may
 // hold anything).  While the consumers fold and store one chunk, the producer is already filling the ring with
-// the next one, so HBM never sees the epilogue.
+// the next one, so HBM never sees the epilogue.  Measured (bench.py --workload c4, fraction of the measured copy
+// bandwidth; the copy moves half reads and half writes, a pure read stream can exceed it): bf16 full 0.83 -> 1.04,
+// bf16 ragged 0.66 -> 0.83, fp32 full 0.92 -> 1.08, fp32 ragged 0.85 -> 0.99.
 constexpr int PS_CWARPS = 8;
 constexpr int PS_CTHREADS = PS_CWARPS * 32;
 constexpr int PS_THREADS = PS_CTHREADS + 32;
@@ -371,9 +373,20 @@ __global__ void __launch_bounds__(PS_THREADS, 2) pool_stream_kernel(const PoolSt
             mbar_wait(&full_bar[st], ph);
             if (active) {
                 const unsigned char* base = ring + (size_t)st * p.stage_bytes + (size_t)cv * 16;
-                for (int r = tg; r < rows; r += p.TG) {
-                    const float m = mf[t0 + r];
-                    if (m != 0.f) TokLoad<TokT>::fma(*reinterpret_cast<const uint4*>(base + (size_t)r * p.row_bytes), m, acc);
+                // four rows per step: their LDS.128 are issued together, then folded in (a row whose mask is 0 is
+                // neither read nor multiplied)
+                for (int r0 = tg; r0 < rows; r0 += 4 * p.TG) {
+                    uint4 v[4];
+                    float m[4];
+#pragma unroll
+                    for (int u = 0; u < 4; u++) {
+                        const int r = r0 + u * p.TG;
+                        m[u] = r < rows ? mf[t0 + r] : 0.f;
+                        if (m[u] != 0.f) v[u] = *reinterpret_cast<const uint4*>(base + (size_t)r * p.row_bytes);
+                    }
+#pragma unroll
+                    for (int u = 0; u < 4; u++)
+                        if (m[u] != 0.f) TokLoad<TokT>::fma(v[u], m[u], acc);
                 }
             }
             mbar_arrive(&empty_bar[st]);
@@ -444,7 +457,10 @@ static int launch_pool_t(const TokT* tok, const void* mask, int mask_dtype, int6
     if (stream_on && vec && T <= PS_MAX_T && H / VEC <= PS_CTHREADS) {
         PoolStreamParams q;
         q.row_bytes = H * (int)sizeof(TokT);
-        q.stage_tok = std::max(1, std::min(16, 24576 / q.row_bytes));
+        // stage = up to 32 token rows, at most 24 KB.  Measured at T=256, H=384 (fraction of the measured copy
+        // bandwidth, bf16 full / bf16 ragged): 8 rows 0.60 / 0.49, 16 rows 0.97 / 0.76, 32 rows 1.04 / 0.83, 64 rows
+        // 1.05 / 0.84 -- the per-stage barrier round trip has to be spread over enough rows per thread
+        q.stage_tok = std::max(1, std::min(32, 24576 / q.row_bytes));
         q.stage_bytes = q.stage_tok * q.row_bytes;  // a multiple of 16
         q.CV = H / VEC;
         q.TG = std::max(1, std::min(PS_CTHREADS / q.CV, q.stage_tok));
