@@ -14,8 +14,8 @@ cap r02_ncu_scan_c2_nq1 scan_tc_kernel 2 python profiles/ncu_probe.py 1
 cap r02_ncu_scan_c2_nq4096 scan_tc_kernel 4 python profiles/ncu_probe.py 4096
 cap r02_ncu_scan_c3shape_nq2048 scan_tc_kernel 2 python profiles/ncu_probe.py 2048 2000000 768 100 ip bf16
 cap r02_ncu_rerank_c2_nq64 rerank_kernel 2 python profiles/ncu_probe.py 64
-cap r02_ncu_pool_bf16_full pool_norm_kernel 3 python profiles/pool_probe.py bf16 full
-cap r02_ncu_pool_bf16_ragged pool_norm_kernel 3 python profiles/pool_probe.py bf16 ragged
+cap r02_ncu_pool_stream_bf16_full pool_stream_kernel 3 python profiles/pool_probe.py bf16 full
+cap r02_ncu_pool_stream_bf16_ragged pool_stream_kernel 3 python profiles/pool_probe.py bf16 ragged
 # head line launch (100M x 384 bf16-stored, nq=64): DRAM bytes only, one pass, no replay of a 12 ms kernel x 40
 timeout 900 ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum,gpu__time_duration.sum --clock-control none -k regex:scan_tc_kernel -s 2 -c 1 --csv --log-file gpurun_out/r02_ncu_scan_c5_nq64_dram.csv python profiles/ncu_probe.py 64 100000000 384 10 l2 bf16 > gpurun_out/r02_ncu_scan_c5_plain.log 2>&1
 tail -3 gpurun_out/r02_ncu_scan_c5_nq64_dram.csv

@@ -360,3 +360,77 @@ def test_indexer_host_appends_on_the_gpu_index(bfk, tmp_path):
         assert open(tmp_path / "vector_store.faiss", "rb").read() == open(tmp_path / "full.faiss", "rb").read()
         assert pickle.load(open(tmp_path / "metadata_store.pkl", "rb")) == ix.metadata_store
     assert modes == ["full", "append", "append", "append", "append"] and ix.index.ntotal == 15
+
+
+def test_host_buffers_pinned_staged_and_large(bfk):
+    """The three ways host queries / results travel (csrc/bfk_index.cu search_locked): page-locked buffers the kernels
+    address directly, small pageable ones through the index's pinned staging buffer, large pageable ones by copies.
+    All must give the answer of the device-resident call, bit for bit."""
+    import torch
+
+    rng = np.random.default_rng(41)
+    d, n, k = 384, 50_000, 10
+    xb = rng.standard_normal((n, d)).astype(np.float32)
+    xb /= np.linalg.norm(xb, axis=1, keepdims=True)
+    idx = bfk.IndexFlatL2(d)
+    idx.add(xb)
+    for nq in (1, 64, 700):  # 700 x 384 x 4 B = 1.05 MB: beyond the 512 KB staging half
+        q = rng.standard_normal((nq, d)).astype(np.float32)
+        q /= np.linalg.norm(q, axis=1, keepdims=True)
+        Dd, Id = idx.search(torch.from_numpy(q).cuda(), k, algo="tensor")
+        Dd, Id = Dd.cpu().numpy(), Id.cpu().numpy()
+        check_knn(Dd, Id, q, xb, k, flat_ref.METRIC_L2, tight=True)
+        # pageable in, pageable out
+        Dp, Ip = idx.search(q, k, algo="tensor")
+        assert (Ip == Id).all() and (Dp == Dd).all()
+        # page-locked in and out, twice (the second call finds the buffers holding the first answer)
+        qp = torch.empty((nq, d), dtype=torch.float32, pin_memory=True)
+        qp.copy_(torch.from_numpy(q))
+        Dpin = torch.full((nq, k), -1.0, dtype=torch.float32, pin_memory=True)
+        Ipin = torch.full((nq, k), -5, dtype=torch.int64, pin_memory=True)
+        for _ in range(2):
+            idx.search(qp.numpy(), k, D=Dpin.numpy(), I=Ipin.numpy(), algo="tensor")
+            assert (Ipin.numpy() == Id).all() and (Dpin.numpy() == Dd).all()
+            Dpin.fill_(-1.0)
+            Ipin.fill_(-5)
+        # mixed: pinned queries, pageable results
+        Dm, Im = idx.search(qp.numpy(), k, algo="tensor")
+        assert (Im == Id).all() and (Dm == Dd).all()
+    # an index whose every answer needs the fall-back (identical rows) through the pinned route: the rewritten
+    # rows must have reached the host buffers when the call returns
+    same = np.repeat(xb[:1], 3000, axis=0)
+    idx2 = bfk.IndexFlatL2(d)
+    idx2.add(same)
+    qp = torch.empty((12, d), dtype=torch.float32, pin_memory=True)
+    qp.copy_(torch.from_numpy(xb[1:13]))
+    Dpin = torch.empty((12, k), dtype=torch.float32, pin_memory=True)
+    Ipin = torch.empty((12, k), dtype=torch.int64, pin_memory=True)
+    idx2.search(qp.numpy(), k, D=Dpin.numpy(), I=Ipin.numpy(), algo="tensor")
+    assert (Ipin.numpy() == np.arange(k)[None, :]).all()
+
+
+def test_profile_stamps_bracket_the_scan(bfk):
+    """bfk_profile_begin / end / stamps (include/bfk.h): per tensor pass, preparation start <= scan start <= scan end
+    <= re-rank end on the device clock, and the summed scan time is below the summed pass time."""
+    import torch
+
+    rng = np.random.default_rng(43)
+    xb = torch.from_numpy(rng.standard_normal((200_000, 384)).astype(np.float32)).cuda()
+    idx = bfk.IndexFlatL2(384)
+    idx.add(xb)
+    q = torch.from_numpy(rng.standard_normal((64, 384)).astype(np.float32)).cuda()
+    idx.search(q, 10, algo="tensor")
+    idx.profile_begin()
+    for _ in range(7):
+        idx.search(q, 10, algo="tensor")
+    prof = idx.profile_end(detail=True)
+    ts = idx.profile_stamps().astype(np.int64)
+    assert prof["n"] == 7 and ts.shape == (7, 4)
+    assert (ts[:, 2] <= ts[:, 0]).all() and (ts[:, 0] < ts[:, 1]).all() and (ts[:, 1] <= ts[:, 3]).all()
+    assert (np.diff(ts[:, 2]) > 0).all()  # passes in order
+    assert 0 < prof["scan_ms"] <= prof["pass_ms"] and prof["idle_ms"] >= 0
+    np.testing.assert_allclose(prof["scan_ms"], (ts[:, 1] - ts[:, 0]).sum() * 1e-6, rtol=1e-9)
+    # unprofiled searches leave no stamps behind; end without begin is an error, not a crash
+    idx.search(q, 10, algo="tensor")
+    with pytest.raises(RuntimeError):
+        idx.profile_end()
