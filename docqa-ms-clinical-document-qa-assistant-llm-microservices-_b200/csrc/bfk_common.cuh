@@ -65,6 +65,14 @@ struct Workspace {
     size_t bytes = 0;
 };
 
+// a device array that grows in place (bfk_vmem.cu): address range reserved once, physical memory mapped in chunks
+struct VmArray;
+int vm_create(int device, size_t va_bytes, VmArray** out);  // non-zero: virtual memory management unavailable
+int vm_grow(VmArray* a, size_t bytes);                       // non-zero: out of device memory (array unchanged)
+void* vm_ptr(const VmArray* a);
+size_t vm_mapped(const VmArray* a);
+void vm_destroy(VmArray* a);
+
 }  // namespace bfk
 
 struct bfk_index {
@@ -80,6 +88,11 @@ struct bfk_index {
     float* x32 = nullptr;
     __nv_bfloat16* x16 = nullptr;
     float* nrm = nullptr;
+    // the three arrays above live in growable virtual-memory arrays when the driver offers them (growth maps more
+    // physical memory behind the same addresses: no copy, no second resident copy); all null -> cudaMalloc + copy
+    bfk::VmArray* vm32 = nullptr;
+    bfk::VmArray* vm16 = nullptr;
+    bfk::VmArray* vmn = nullptr;
     unsigned int* maxn = nullptr;
     bfk::Workspace ws;       // search scratch, grow-only
     cudaEvent_t ws_free = nullptr;  // recorded after the last search that used `ws`

@@ -32,36 +32,157 @@ static int check_device(int device) {
     return 0;
 }
 
-static int free_storage(bfk_index* idx) {
-    if (idx->x32) cudaFree(idx->x32);
-    if (idx->x16) cudaFree(idx->x16);
-    if (idx->nrm) cudaFree(idx->nrm);
-    idx->x32 = nullptr;
-    idx->x16 = nullptr;
-    idx->nrm = nullptr;
-    idx->cap = 0;
+// ---- corpus storage: x32 / x16 / nrm ------------------------------------------------------------------
+struct StorageSet {
+    float* x32 = nullptr;
+    __nv_bfloat16* x16 = nullptr;
+    float* nrm = nullptr;
+    VmArray *vm32 = nullptr, *vm16 = nullptr, *vmn = nullptr;
+    int64_t cap = 0;
+};
+
+static size_t bytes32(const bfk_index* idx, int64_t rows) { return sizeof(float) * (size_t)rows * idx->ld32; }
+static size_t bytes16(const bfk_index* idx, int64_t rows) { return sizeof(__nv_bfloat16) * (size_t)rows * idx->ld16; }
+// norms are fetched a whole 256-row tile at a time (1 KiB bulk copies): pad to the tile
+static size_t bytesn(int64_t rows) { return sizeof(float) * (size_t)round_up(rows, 256); }
+
+static void free_set(StorageSet* s) {
+    if (s->vm16) {
+        vm_destroy(s->vm32);
+        vm_destroy(s->vm16);
+        vm_destroy(s->vmn);
+    } else {
+        if (s->x32) cudaFree(s->x32);
+        if (s->x16) cudaFree(s->x16);
+        if (s->nrm) cudaFree(s->nrm);
+    }
+    *s = StorageSet();
+}
+
+// rows the mapped (or allocated) bytes of a virtual-memory set hold
+static int64_t vm_rows(const bfk_index* idx, const StorageSet& s) {
+    int64_t rows = (int64_t)(vm_mapped(s.vm16) / (sizeof(__nv_bfloat16) * (size_t)idx->ld16));
+    if (s.vm32) rows = std::min<int64_t>(rows, (int64_t)(vm_mapped(s.vm32) / (sizeof(float) * (size_t)idx->ld32)));
+    int64_t nrows = (int64_t)(vm_mapped(s.vmn) / sizeof(float));
+    nrows -= nrows % 256;  // the padded tile must fit as well
+    return std::min(rows, nrows);
+}
+
+static int vm_set_grow(const bfk_index* idx, StorageSet* s, int64_t rows) {
+    if (s->vm32 && vm_grow(s->vm32, bytes32(idx, rows))) return 1;
+    if (vm_grow(s->vm16, bytes16(idx, rows))) return 1;
+    if (vm_grow(s->vmn, bytesn(rows))) return 1;
+    s->cap = vm_rows(idx, *s);
     return 0;
 }
 
-static int alloc_storage(bfk_index* idx, int64_t cap, float** x32, __nv_bfloat16** x16, float** nrm) {
-    *x32 = nullptr;
-    *x16 = nullptr;
-    *nrm = nullptr;
+// a fresh set with room for `cap` rows: growable arrays when the driver has virtual memory management, else cudaMalloc
+static int alloc_set(const bfk_index* idx, int64_t cap, StorageSet* out) {
+    *out = StorageSet();
+    StorageSet s;
+    // address space for as many rows as the GPU's memory could ever hold (a reservation costs nothing)
+    size_t free_b = 0, total_b = 0;
+    const size_t row_all = bytes16(idx, 1) + 4 + (idx->storage == BFK_STORE_F32 ? bytes32(idx, 1) : 0);
+    if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess && total_b > 0) {
+        const int64_t max_rows = std::max<int64_t>(std::min<int64_t>(0x7fffffffll, (int64_t)(total_b / row_all)), cap);
+        bool ok = vm_create(idx->device, bytes16(idx, max_rows), &s.vm16) == 0 && vm_create(idx->device, bytesn(max_rows), &s.vmn) == 0;
+        if (ok && idx->storage == BFK_STORE_F32) ok = vm_create(idx->device, bytes32(idx, max_rows), &s.vm32) == 0;
+        if (ok && vm_set_grow(idx, &s, std::max<int64_t>(cap, 1)) == 0) {
+            s.x32 = static_cast<float*>(vm_ptr(s.vm32));
+            s.x16 = static_cast<__nv_bfloat16*>(vm_ptr(s.vm16));
+            s.nrm = static_cast<float*>(vm_ptr(s.vmn));
+            *out = s;
+            return 0;
+        }
+        const bool had_vm = s.vm16 != nullptr && s.vmn != nullptr && (idx->storage != BFK_STORE_F32 || s.vm32 != nullptr);
+        vm_destroy(s.vm32);
+        vm_destroy(s.vm16);
+        vm_destroy(s.vmn);
+        s = StorageSet();
+        if (had_vm) return 1;  // reservations worked, the memory itself ran out
+    } else {
+        cudaGetLastError();
+    }
     cudaError_t e = cudaSuccess;
-    if (idx->storage == BFK_STORE_F32) e = cudaMalloc((void**)x32, sizeof(float) * (size_t)cap * idx->ld32);
-    if (e == cudaSuccess) e = cudaMalloc((void**)x16, sizeof(__nv_bfloat16) * (size_t)cap * idx->ld16);
-    // norms are fetched a whole 256-row tile at a time (1 KiB bulk copies): pad to the tile
-    if (e == cudaSuccess) e = cudaMalloc((void**)nrm, sizeof(float) * (size_t)round_up(cap, 256));
+    if (idx->storage == BFK_STORE_F32) e = cudaMalloc((void**)&s.x32, bytes32(idx, cap));
+    if (e == cudaSuccess) e = cudaMalloc((void**)&s.x16, bytes16(idx, cap));
+    if (e == cudaSuccess) e = cudaMalloc((void**)&s.nrm, bytesn(cap));
     if (e != cudaSuccess) {
         cudaGetLastError();
-        if (*x32) cudaFree(*x32);
-        if (*x16) cudaFree(*x16);
-        if (*nrm) cudaFree(*nrm);
-        *x32 = nullptr;
-        *x16 = nullptr;
-        *nrm = nullptr;
+        free_set(&s);
         return 1;
     }
+    s.cap = cap;
+    *out = s;
+    return 0;
+}
+
+static StorageSet current_set(const bfk_index* idx) {
+    StorageSet s;
+    s.x32 = idx->x32;
+    s.x16 = idx->x16;
+    s.nrm = idx->nrm;
+    s.vm32 = idx->vm32;
+    s.vm16 = idx->vm16;
+    s.vmn = idx->vmn;
+    s.cap = idx->cap;
+    return s;
+}
+
+static void adopt_set(bfk_index* idx, const StorageSet& s) {
+    idx->x32 = s.x32;
+    idx->x16 = s.x16;
+    idx->nrm = s.nrm;
+    idx->vm32 = s.vm32;
+    idx->vm16 = s.vm16;
+    idx->vmn = s.vmn;
+    idx->cap = s.cap;
+}
+
+static int free_storage(bfk_index* idx) {
+    StorageSet s = current_set(idx);
+    free_set(&s);
+    adopt_set(idx, s);
+    return 0;
+}
+
+// copies the first `rows` rows of the index into another set, on `st`
+static int copy_rows_to(const bfk_index* idx, const StorageSet& dst, int64_t rows, cudaStream_t st) {
+    if (rows <= 0) return 0;
+    if (dst.x32) BFK_CUDA(cudaMemcpyAsync(dst.x32, idx->x32, bytes32(idx, rows), cudaMemcpyDeviceToDevice, st));
+    BFK_CUDA(cudaMemcpyAsync(dst.x16, idx->x16, bytes16(idx, rows), cudaMemcpyDeviceToDevice, st));
+    BFK_CUDA(cudaMemcpyAsync(dst.nrm, idx->nrm, sizeof(float) * (size_t)rows, cudaMemcpyDeviceToDevice, st));
+    return 0;
+}
+
+// room for `want` rows (at least `need`): in place when the storage is growable, else a larger copy
+static int grow_storage(bfk_index* idx, int64_t need, int64_t want, cudaStream_t st, const char* who) {
+    if (idx->vm16 || idx->cap == 0) {
+        if (idx->cap == 0 && !idx->vm16) {  // first rows: this decides between the two kinds of storage
+            StorageSet s;
+            if (alloc_set(idx, want, &s) && (want == need || alloc_set(idx, need, &s)))
+                return fail(std::string(who) + ": out of device memory for " + std::to_string(need) + " rows");
+            adopt_set(idx, s);
+            return 0;
+        }
+        StorageSet s = current_set(idx);
+        if (vm_set_grow(idx, &s, want) && (want == need || vm_set_grow(idx, &s, need)))
+            return fail(std::string(who) + ": out of device memory growing the index to " + std::to_string(need) + " rows");
+        idx->cap = s.cap;
+        return 0;
+    }
+    StorageSet s;
+    if (alloc_set(idx, want, &s) && (want == need || alloc_set(idx, need, &s)))
+        return fail(std::string(who) + ": out of device memory growing the index to " + std::to_string(need) + " rows");
+    BFK_TRY(wait_rows_ready(idx, st));
+    int rc = copy_rows_to(idx, s, idx->ntotal, st);
+    if (!rc && cudaStreamSynchronize(st) != cudaSuccess) rc = fail(std::string(who) + ": copy failed");
+    if (rc) {
+        free_set(&s);
+        return rc;
+    }
+    free_storage(idx);
+    adopt_set(idx, s);
     return 0;
 }
 
@@ -78,33 +199,13 @@ int mark_rows_ready(bfk_index* idx, cudaStream_t st) {
     return 0;
 }
 
-// grow corpus storage to hold at least `need` rows (amortised doubling); idx->mu is held
+// grow corpus storage to hold at least `need` rows; idx->mu is held.  Growable storage adds a quarter (mapping is
+// cheap and nothing is copied), the cudaMalloc fall-back doubles (every regrowth copies everything)
 int ensure_capacity(bfk_index* idx, int64_t need, cudaStream_t st) {
     if (need <= idx->cap) return 0;
-    BFK_TRY(wait_rows_ready(idx, st));
-    int64_t want = std::max<int64_t>(std::max<int64_t>(need, idx->cap * 2), 1024);
-    float* x32;
-    __nv_bfloat16* x16;
-    float* nrm;
-    if (alloc_storage(idx, want, &x32, &x16, &nrm)) {
-        want = need;  // doubling did not fit in HBM: take exactly what is needed
-        if (alloc_storage(idx, want, &x32, &x16, &nrm))
-            return fail("out of device memory growing the index to " + std::to_string(need) + " rows");
-    }
-    if (idx->ntotal > 0) {
-        if (x32) BFK_CUDA(cudaMemcpyAsync(x32, idx->x32, sizeof(float) * (size_t)idx->ntotal * idx->ld32,
-                                          cudaMemcpyDeviceToDevice, st));
-        BFK_CUDA(cudaMemcpyAsync(x16, idx->x16, sizeof(__nv_bfloat16) * (size_t)idx->ntotal * idx->ld16,
-                                 cudaMemcpyDeviceToDevice, st));
-        BFK_CUDA(cudaMemcpyAsync(nrm, idx->nrm, sizeof(float) * (size_t)idx->ntotal, cudaMemcpyDeviceToDevice, st));
-        BFK_CUDA(cudaStreamSynchronize(st));
-    }
-    free_storage(idx);
-    idx->x32 = x32;
-    idx->x16 = x16;
-    idx->nrm = nrm;
-    idx->cap = want;
-    return 0;
+    const int64_t want = idx->vm16 ? std::max<int64_t>(need, idx->cap + std::max<int64_t>(idx->cap / 4, 1024))
+                                   : std::max<int64_t>(std::max<int64_t>(need, idx->cap * 2), 1024);
+    return grow_storage(idx, need, want, st, "add");
 }
 
 int grow_for(bfk_index* idx, int64_t need, cudaStream_t st) {
@@ -372,34 +473,9 @@ int bfk_reserve(bfk_index* idx, int64_t n) {
     std::lock_guard<std::mutex> lk(idx->mu);
     if (n <= idx->cap) return 0;
     BFK_TRY(search_tensor_finish(idx, 0, nullptr));
-    // exact-size allocation: callers reserve when they know the final size
-    float* x32;
-    __nv_bfloat16* x16;
-    float* nrm;
-    if (alloc_storage(idx, n, &x32, &x16, &nrm)) return fail("reserve: out of device memory");
-    cudaStream_t st = 0;
-    int rc = wait_rows_ready(idx, st);  // rows appended on another (non-blocking) stream must have landed
-    if (!rc && idx->ntotal > 0) {
-        cudaError_t e = cudaSuccess;
-        if (x32) e = cudaMemcpyAsync(x32, idx->x32, sizeof(float) * (size_t)idx->ntotal * idx->ld32, cudaMemcpyDeviceToDevice, st);
-        if (e == cudaSuccess)
-            e = cudaMemcpyAsync(x16, idx->x16, sizeof(__nv_bfloat16) * (size_t)idx->ntotal * idx->ld16, cudaMemcpyDeviceToDevice, st);
-        if (e == cudaSuccess) e = cudaMemcpyAsync(nrm, idx->nrm, sizeof(float) * (size_t)idx->ntotal, cudaMemcpyDeviceToDevice, st);
-        if (e != cudaSuccess) rc = fail(std::string("reserve: copy failed: ") + cudaGetErrorString(e));
-    }
-    if (!rc && cudaStreamSynchronize(st) != cudaSuccess) rc = fail("reserve: copy failed");
-    if (rc) {
-        if (x32) cudaFree(x32);
-        cudaFree(x16);
-        cudaFree(nrm);
-        return rc;
-    }
-    free_storage(idx);
-    idx->x32 = x32;
-    idx->x16 = x16;
-    idx->nrm = nrm;
-    idx->cap = n;
-    return 0;
+    // exact size: callers reserve when they know the final row count (growable storage maps up to it in place;
+    // the cudaMalloc fall-back allocates it and copies what is stored, on the legacy stream)
+    return grow_storage(idx, n, n, 0, "reserve");
 }
 
 int bfk_add(bfk_index* idx, const float* x, int64_t n, int x_is_device, void* stream) {
@@ -847,23 +923,21 @@ int bfk_remove_ids(bfk_index* idx, const int64_t* ids, int64_t n, int64_t* nremo
     BFK_CUDA(cudaDeviceSynchronize());
     idx->rows_pending = false;
     // IndexFlatCodes::remove_ids keeps the surviving rows in order: move each kept segment down
-    // through fresh buffers (device copies must not overlap)
-    float* x32;
-    __nv_bfloat16* x16;
-    float* nrm;
+    // through a fresh set of arrays (device copies must not overlap)
     const int64_t left = idx->ntotal - (int64_t)rm.size();
     const int64_t newcap = std::max<int64_t>(left, 1024);
-    if (alloc_storage(idx, newcap, &x32, &x16, &nrm)) return fail("remove_ids: out of device memory");
+    StorageSet ns;
+    if (alloc_set(idx, newcap, &ns)) return fail("remove_ids: out of device memory");
     int64_t dst = 0, src = 0;
     cudaStream_t st = 0;
     auto copy_seg = [&](int64_t s, int64_t e) -> int {
         int64_t m = e - s;
         if (m <= 0) return 0;
-        if (x32) BFK_CUDA(cudaMemcpyAsync(x32 + (size_t)dst * idx->ld32, idx->x32 + (size_t)s * idx->ld32,
-                                          sizeof(float) * (size_t)m * idx->ld32, cudaMemcpyDeviceToDevice, st));
-        BFK_CUDA(cudaMemcpyAsync(x16 + (size_t)dst * idx->ld16, idx->x16 + (size_t)s * idx->ld16,
+        if (ns.x32) BFK_CUDA(cudaMemcpyAsync(ns.x32 + (size_t)dst * idx->ld32, idx->x32 + (size_t)s * idx->ld32,
+                                             sizeof(float) * (size_t)m * idx->ld32, cudaMemcpyDeviceToDevice, st));
+        BFK_CUDA(cudaMemcpyAsync(ns.x16 + (size_t)dst * idx->ld16, idx->x16 + (size_t)s * idx->ld16,
                                  sizeof(__nv_bfloat16) * (size_t)m * idx->ld16, cudaMemcpyDeviceToDevice, st));
-        BFK_CUDA(cudaMemcpyAsync(nrm + dst, idx->nrm + s, sizeof(float) * (size_t)m, cudaMemcpyDeviceToDevice, st));
+        BFK_CUDA(cudaMemcpyAsync(ns.nrm + dst, idx->nrm + s, sizeof(float) * (size_t)m, cudaMemcpyDeviceToDevice, st));
         dst += m;
         return 0;
     };
@@ -875,17 +949,15 @@ int bfk_remove_ids(bfk_index* idx, const int64_t* ids, int64_t n, int64_t* nremo
     if (!rc) rc = copy_seg(src, idx->ntotal);
     if (!rc && cudaStreamSynchronize(st) != cudaSuccess) rc = fail("remove_ids: copy failed");
     if (rc) {
-        if (x32) cudaFree(x32);
-        cudaFree(x16);
-        cudaFree(nrm);
+        free_set(&ns);
         return rc;
     }
     free_storage(idx);
-    idx->x32 = x32;
-    idx->x16 = x16;
-    idx->nrm = nrm;
-    idx->cap = newcap;
+    adopt_set(idx, ns);
     idx->ntotal = left;
+    // the tensor maps describe the old arrays
+    idx->tmap[0].base = nullptr;
+    idx->tmap[1].base = nullptr;
     if (nremoved) *nremoved = (int64_t)rm.size();
     return 0;
 }
