@@ -96,7 +96,8 @@ int bfk_storage(const bfk_index* idx);
 int bfk_device(const bfk_index* idx);
 int64_t bfk_ntotal(const bfk_index* idx);
 
-/* pre-size the corpus storage (no faiss counterpart; avoids regrowth copies) */
+/* pre-size the corpus storage (no faiss counterpart): maps device memory for n rows at once.  Growth itself
+ * copies nothing -- the storage is a reserved address range with physical memory mapped behind it as rows arrive */
 int bfk_reserve(bfk_index* idx, int64_t n);
 
 /* index.add(float32[n, d]) -- indexer.py:41.  Copies; ids are sequential. */
