@@ -100,7 +100,8 @@ struct bfk_index {
     bool ws_stream_known = false;
     int* h_flag = nullptr;          // pinned host words: [0] count of uncertified queries of the last tensor pass,
                                     // [1] that pass's sequence number, written after the count (the host polls it)
-    int flag_seq = 0;               // sequence number of the last tensor pass enqueued
+    int flag_seq = 0;               // sequence number of the last tensor pass / host-notifying search enqueued
+    int* sel_ticket = nullptr;      // device word for K4's "last CTA" ticket (SelectNotify)
     int* h_flag_dev = nullptr;      // the same word as the GPU addresses it (K5's last CTA writes it)
     char* h_stage = nullptr;        // pinned staging for small host-side searches (queries in, (D, I) out)
     // id selector of the search in progress (bfk_search_sel; null otherwise), set and cleared under `mu`:
@@ -158,9 +159,19 @@ int scan_exact_workspace(const bfk_index* idx, int nq, int k, size_t* bytes, int
 //   sel: optional id selector bitmap on the device (bit i <=> row i may be returned), else nullptr
 int launch_scan_exact(const bfk_index* idx, const float* q_dev /*[nq, ldq]*/, int ldq, int nq, int k,
                       uint64_t* part, int nparts, cudaStream_t st, const unsigned char* sel);
-// K4/K6: per query, top-k of m composite keys -> (D, I)
+// K4/K6: per query, top-k of m composite keys -> (D, I).  `nt` (optional): D / I are pinned host memory and the
+// last CTA writes `seq` to the pinned word *h_seq once every query's rows have reached the host
+struct SelectNotify {
+    int* ticket;  // device word, 0 between searches
+    int* h_seq;   // pinned host word as the GPU addresses it
+    int seq;
+};
 int launch_select(const uint64_t* cand, int64_t m_per_query, int64_t nq, int k, int metric,
-                  int64_t id_offset, float* D, int64_t* I, int64_t out_ld, cudaStream_t st);
+                  int64_t id_offset, float* D, int64_t* I, int64_t out_ld, cudaStream_t st,
+                  const SelectNotify* nt = nullptr);
+// waits until the pass / search that carries sequence number idx->flag_seq has published it in idx->h_flag[1]
+// (polls the pinned word; falls back to a blocking stream wait for long passes and on errors)
+int wait_flag_seq(bfk_index* idx, cudaStream_t st);
 // K6 front end: pack (D, I) lists into composite keys
 int launch_pack_parts(const float* Dparts, const int64_t* Iparts, int nparts, int64_t nq, int k,
                       int metric, uint64_t* cand, cudaStream_t st);

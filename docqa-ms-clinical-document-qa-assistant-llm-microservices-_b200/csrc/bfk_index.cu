@@ -266,6 +266,8 @@ static int make_index(int d, int metric, int device, int storage, bfk_index** ou
     }
     if (cudaMalloc((void**)&idx->maxn, 2 * sizeof(unsigned int)) != cudaSuccess ||
         cudaMemset(idx->maxn, 0, 2 * sizeof(unsigned int)) != cudaSuccess ||
+        cudaMalloc((void**)&idx->sel_ticket, sizeof(int)) != cudaSuccess ||
+        cudaMemset(idx->sel_ticket, 0, sizeof(int)) != cudaSuccess ||
         cudaEventCreateWithFlags(&idx->ws_free, cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreateWithFlags(&idx->rows_ready, cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreateWithFlags(&idx->stage_done, cudaEventDisableTiming) != cudaSuccess ||
@@ -418,7 +420,8 @@ static int add_rows(bfk_index* idx, const float* x, int64_t n, int x_is_device, 
 // ---- search orchestration ---------------------------------------------------
 static int search_exact(bfk_index* idx, const float* q_dev, int ldq, int64_t nq, int k, float* D_dev,
                         int64_t* I_dev, int64_t id_offset, char* ws_tail, size_t ws_tail_bytes,
-                        cudaStream_t st, bfk_search_stats* stats, cudaEvent_t ev0, cudaEvent_t ev1);
+                        cudaStream_t st, bfk_search_stats* stats, cudaEvent_t ev0, cudaEvent_t ev1,
+                        const SelectNotify* nt = nullptr);
 
 }  // namespace bfk
 
@@ -450,6 +453,7 @@ int bfk_free(bfk_index* idx) {
     free_storage(idx);
     if (idx->ws.ptr) cudaFree(idx->ws.ptr);
     if (idx->maxn) cudaFree(idx->maxn);
+    if (idx->sel_ticket) cudaFree(idx->sel_ticket);
     if (idx->ws_free) cudaEventDestroy(idx->ws_free);
     if (idx->rows_ready) cudaEventDestroy(idx->rows_ready);
     if (idx->stage_done) cudaEventDestroy(idx->stage_done);
@@ -672,7 +676,7 @@ static int search_locked(bfk_index* idx, const float* q, int64_t nq, int k, floa
     enum Mode { MODE_DEVICE, MODE_PINNED, MODE_STAGED, MODE_COPY };
     const size_t q_bytes = sizeof(float) * (size_t)nq * idx->d;
     const size_t out_span = (size_t)((char*)(I_dev + (size_t)nq * k) - (char*)D_dev);  // D, padding, I: contiguous
-    const bool direct_ok = algo == BFK_ALGO_TENSOR && !stats && !sel_dev;  // the exact scan and the selector path copy
+    const bool direct_ok = !stats && !sel_dev;  // timed and selector searches go through copies
     Mode q_mode = MODE_DEVICE, out_mode = MODE_DEVICE;
     const float* q_direct = nullptr;  // queries as the GPU addresses them when q_mode is PINNED / STAGED
     char* stage_out = nullptr;
@@ -688,14 +692,22 @@ static int search_locked(bfk_index* idx, const float* q, int64_t nq, int k, floa
             return a.type == cudaMemoryTypeHost && a.devicePointer != nullptr;
         };
         void *qd = nullptr, *Dd = nullptr, *Id = nullptr;
-        if (direct_ok && pinned(q, &qd)) {
+        // a few KB are cheaper to memcpy through the staging buffer than to ask the driver about (~1 us per pointer):
+        // the reference's own call is one 384-float query and 3 results (llm-qa/main.py:101)
+        const bool tiny = q_bytes <= 16384 && out_span <= 16384 && stage_buffer(idx) != nullptr;
+        if (tiny) {
+            q_mode = out_mode = MODE_STAGED;
+            q_direct = reinterpret_cast<const float*>(idx->h_stage);
+            stage_out = idx->h_stage + STAGE_BYTES / 2;
+        } else if (direct_ok && pinned(q, &qd)) {
             q_mode = MODE_PINNED;
             q_direct = static_cast<const float*>(qd);
         } else if (q_bytes <= STAGE_BYTES / 2 && stage_buffer(idx)) {
             q_mode = MODE_STAGED;
             q_direct = reinterpret_cast<const float*>(idx->h_stage);
         }
-        if (direct_ok && pinned(D, &Dd) && pinned(I, &Id)) out_mode = MODE_PINNED;
+        if (tiny) {
+        } else if (direct_ok && pinned(D, &Dd) && pinned(I, &Id)) out_mode = MODE_PINNED;
         else if (out_span <= STAGE_BYTES / 2 && stage_buffer(idx)) {
             out_mode = MODE_STAGED;
             stage_out = idx->h_stage + STAGE_BYTES / 2;
@@ -705,7 +717,10 @@ static int search_locked(bfk_index* idx, const float* q, int64_t nq, int k, floa
             I = static_cast<int64_t*>(Id);
         }
     }
-    const bool q_zero_copy = direct_ok && (q_mode == MODE_PINNED || q_mode == MODE_STAGED);
+    // the fp32 scan reads the queries once per CTA: over PCIe that only pays while (queries x CTAs) stays small --
+    // the reference's 649-row index is 21 CTAs x 1.5 KB; larger scans get their queries by one DMA copy instead
+    const bool q_direct_ok = direct_ok && (algo == BFK_ALGO_TENSOR || q_bytes * (size_t)std::max(nparts, 1) <= 65536);
+    const bool q_zero_copy = q_direct_ok && (q_mode == MODE_PINNED || q_mode == MODE_STAGED);
     const bool out_zero_copy = direct_ok && (out_mode == MODE_PINNED || out_mode == MODE_STAGED);
     if (q_mode == MODE_STAGED) memcpy(idx->h_stage, q, q_bytes);
     if (q_zero_copy) {
@@ -714,6 +729,10 @@ static int search_locked(bfk_index* idx, const float* q, int64_t nq, int k, floa
         if (ldq != idx->d) BFK_CUDA(cudaMemsetAsync(q_dev, 0, sizeof(float) * (size_t)nq * ldq, st));
         BFK_CUDA(cudaMemcpy2DAsync(q_dev, sizeof(float) * ldq, idx->h_stage, sizeof(float) * idx->d, sizeof(float) * idx->d,
                                    (size_t)nq, cudaMemcpyHostToDevice, st));
+    } else if (q_mode == MODE_PINNED) {
+        if (ldq != idx->d) BFK_CUDA(cudaMemsetAsync(q_dev, 0, sizeof(float) * (size_t)nq * ldq, st));
+        BFK_CUDA(cudaMemcpy2DAsync(q_dev, sizeof(float) * ldq, q, sizeof(float) * idx->d, sizeof(float) * idx->d, (size_t)nq,
+                                   cudaMemcpyHostToDevice, st));
     } else if (io_is_device && ldq == idx->d && !defer && (reinterpret_cast<uintptr_t>(q) & 15u) == 0) {
         // device queries whose row stride already is the padded one: read them in place (a deferred search
         // keeps its own copy, its retry may run after the caller has let go of the buffer)
@@ -758,7 +777,12 @@ static int search_locked(bfk_index* idx, const float* q, int64_t nq, int k, floa
         rc = search_tensor(idx, q_dev, ldq, nq, k, D_out, I_out, id_offset, tail, tail_avail, st, stats, ev0, ev1,
                            (defer || host_defer) ? 1 : 0, q_zero_copy ? q_direct : nullptr, out_zero_copy ? 1 : 0);
     } else {
-        rc = search_exact(idx, q_dev, ldq, nq, k, D_out, I_out, id_offset, tail, tail_avail, st, stats, ev0, ev1);
+        // the fp32 scan reads the queries where they are (pinned host memory included: one read per CTA at kernel
+        // start, row stride d), K4 writes (D, I) to the host and publishes a sequence number the host polls
+        SelectNotify nt{idx->sel_ticket, idx->h_flag_dev + 1, 0};
+        if (out_zero_copy) nt.seq = ++idx->flag_seq;
+        rc = search_exact(idx, q_zero_copy ? q_direct : q_dev, q_zero_copy ? idx->d : ldq, nq, k, D_out, I_out, id_offset,
+                          tail, tail_avail, st, stats, ev0, ev1, out_zero_copy ? &nt : nullptr);
     }
     const bool staged_out = !io_is_device && out_mode == MODE_STAGED;
     auto copy_out = [&]() -> int {
@@ -789,6 +813,7 @@ static int search_locked(bfk_index* idx, const float* q, int64_t nq, int k, floa
             if (!rc && cudaStreamSynchronize(st) != cudaSuccess) rc = fail("search: kernel execution failed");
         }
     }
+    if (!rc && out_zero_copy && algo == BFK_ALGO_EXACT_SIMT) rc = wait_flag_seq(idx, st);
     if (!rc && staged_out) {
         memcpy(D, stage_out, sizeof(float) * (size_t)nq * k);
         memcpy(I, stage_out + ((char*)I_dev - (char*)D_dev), sizeof(int64_t) * (size_t)nq * k);
@@ -1108,7 +1133,8 @@ namespace bfk {
 // Exact path: groups of <= 8 queries, one corpus pass per group, then one select launch.
 static int search_exact(bfk_index* idx, const float* q_dev, int ldq, int64_t nq, int k, float* D_dev,
                         int64_t* I_dev, int64_t id_offset, char* ws_tail, size_t ws_tail_bytes,
-                        cudaStream_t st, bfk_search_stats* stats, cudaEvent_t ev0, cudaEvent_t ev1) {
+                        cudaStream_t st, bfk_search_stats* stats, cudaEvent_t ev0, cudaEvent_t ev1,
+                        const SelectNotify* nt) {
     size_t scratch = 0;
     int nparts = 0;
     BFK_TRY(scan_exact_workspace(idx, (int)std::min<int64_t>(nq, 8), k, &scratch, &nparts));
@@ -1124,7 +1150,7 @@ static int search_exact(bfk_index* idx, const float* q_dev, int ldq, int64_t nq,
         q0 += g;
     }
     if (stats) cudaEventRecord(ev1, st);
-    BFK_TRY(launch_select(part, (int64_t)nparts * k, nq, k, idx->metric, id_offset, D_dev, I_dev, k, st));
+    BFK_TRY(launch_select(part, (int64_t)nparts * k, nq, k, idx->metric, id_offset, D_dev, I_dev, k, st, nt));
     launches++;
     if (stats) {
         stats->n_launches = launches;

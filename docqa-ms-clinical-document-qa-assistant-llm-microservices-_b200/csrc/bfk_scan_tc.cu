@@ -1570,7 +1570,7 @@ struct TcPending {
 // count and then the pass's sequence number into pinned host memory; polling that word costs a PCIe write's
 // latency, where cudaStreamSynchronize also waits for the kernel to be retired and for the driver to notice.
 // Passes longer than a few hundred microseconds (and any error) fall back to the blocking wait.
-static int wait_pass_published(bfk_index* idx, cudaStream_t st) {
+int wait_flag_seq(bfk_index* idx, cudaStream_t st) {
     static const bool spin_on = [] {
         const char* e = getenv("BFK_TC_SPIN");
         return e ? atoi(e) != 0 : true;
@@ -1596,7 +1596,7 @@ static int wait_pass_published(bfk_index* idx, cudaStream_t st) {
 static int tc_resolve(bfk_index* idx, const TcPending& c, cudaStream_t st, int64_t* n_retry, int64_t* n_fallback,
                       int64_t* n_rewritten, int* launches) {
     const TcWs& w = c.w;
-    BFK_TRY(wait_pass_published(idx, st));
+    BFK_TRY(wait_flag_seq(idx, st));
     int nflag = *idx->h_flag;
     if (n_rewritten) *n_rewritten += nflag;
     if (nflag == 0) return 0;

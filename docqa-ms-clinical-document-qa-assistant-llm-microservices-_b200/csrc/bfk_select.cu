@@ -44,7 +44,7 @@ __global__ void __launch_bounds__(SEL_THREADS) select_topk_kernel(const uint64_t
                                                                   const int64_t* __restrict__ gather, int64_t gather_q_stride,
                                                                   int64_t gather_p_stride, int gather_k,
                                                                   float* __restrict__ D, int64_t* __restrict__ I,
-                                                                  int64_t out_ld) {
+                                                                  int64_t out_ld, const SelectNotify nt) {
     __shared__ uint64_t buf[SEL_N];
     __shared__ unsigned long long gmin[128];
     __shared__ unsigned long long bound_s;
@@ -127,14 +127,26 @@ __global__ void __launch_bounds__(SEL_THREADS) select_topk_kernel(const uint64_t
         D[q * out_ld + i] = dv;
         I[q * out_ld + i] = iv;
     }
+    if (nt.h_seq != nullptr) {
+        // (D, I) are pinned host memory and the host is polling: every query's rows must have reached it before
+        // the last CTA publishes the sequence number (it also re-arms the ticket for the next search)
+        __threadfence_system();
+        __syncthreads();
+        if (tid == 0 && atomicAdd(nt.ticket, 1) == (int)gridDim.x - 1) {
+            *nt.ticket = 0;
+            __threadfence();
+            *reinterpret_cast<volatile int*>(nt.h_seq) = nt.seq;
+            __threadfence_system();
+        }
+    }
 }
 
 int launch_select(const uint64_t* cand, int64_t m_per_query, int64_t nq, int k, int metric, int64_t id_offset,
-                  float* D, int64_t* I, int64_t out_ld, cudaStream_t st) {
+                  float* D, int64_t* I, int64_t out_ld, cudaStream_t st, const SelectNotify* nt) {
     if (nq <= 0) return 0;
     // every caller hands over ascending lists of length k (K3a's per-CTA lists)
     select_topk_kernel<<<(unsigned)nq, SEL_THREADS, 0, st>>>(cand, m_per_query, k, k, metric, id_offset, nullptr, 0, 0,
-                                                            1, D, I, out_ld);
+                                                            1, D, I, out_ld, nt ? *nt : SelectNotify{nullptr, nullptr, 0});
     BFK_CUDA(cudaGetLastError());
     return 0;
 }
@@ -214,7 +226,7 @@ extern "C" int bfk_merge_topk_strided(const float* Dparts, int64_t d_part_stride
     int rc = cudaGetLastError() == cudaSuccess ? 0 : fail("merge_topk: launch failed");
     if (!rc) {
         select_topk_kernel<<<(unsigned)nq, SEL_THREADS, 0, st>>>(cand, (int64_t)nparts * k, (int)k, (int)k, metric, 0,
-                                                                Iparts, k, i_part_stride, (int)k, D, I, k);
+                                                                Iparts, k, i_part_stride, (int)k, D, I, k, SelectNotify{nullptr, nullptr, 0});
         if (cudaGetLastError() != cudaSuccess) rc = fail("merge_topk: launch failed");
     }
     cudaFreeAsync(cand, st);
