@@ -77,7 +77,10 @@ class IndexFlat:
     # -- attributes faiss exposes ------------------------------------------------
     @property
     def d(self) -> int:
-        return int(self._L.bfk_dim(self._h))
+        d = self.__dict__.get("_d")  # fixed at construction: one ctypes call per index, not one per search
+        if d is None:
+            d = self.__dict__["_d"] = int(self._L.bfk_dim(self._h))
+        return d
 
     @property
     def ntotal(self) -> int:
@@ -206,7 +209,8 @@ class IndexFlat:
         else:
             assert I.shape == (n, k)
             assert I.dtype == np.int64 and I.flags.c_contiguous
-        _lib.check(self._L.bfk_search_ex(self._h, _np_ptr(x), n, k, _np_ptr(D), _np_ptr(I), 0, None,
+        # plain integer addresses: ctypes converts them for the c_void_p parameters itself
+        _lib.check(self._L.bfk_search_ex(self._h, x.ctypes.data, n, k, D.ctypes.data, I.ctypes.data, 0, None,
                                           _ALGO[algo], int(id_offset), stp))
         return D, I
 
