@@ -157,8 +157,20 @@ int launch_pool(const void* tok, int tok_dtype, const void* mask, int mask_dtype
 //   part [nq][nparts][k] composite keys; returns nparts through *nparts_out
 int scan_exact_workspace(const bfk_index* idx, int nq, int k, size_t* bytes, int* nparts_out);
 //   sel: optional id selector bitmap on the device (bit i <=> row i may be returned), else nullptr
+//   fuse: optional -- where (D, I) go when the scan's last CTA may merge the lists itself (small searches);
+//         *fused tells whether it will (then no launch_select is needed)
+struct ScanFuse {
+    float* D;
+    int64_t* I;
+    int64_t out_ld;
+    int64_t id_offset;
+    int* ticket;  // device word, 0 between searches
+    int* h_seq;   // optional pinned host word that receives `seq` once (D, I) are complete
+    int seq;
+};
 int launch_scan_exact(const bfk_index* idx, const float* q_dev /*[nq, ldq]*/, int ldq, int nq, int k,
-                      uint64_t* part, int nparts, cudaStream_t st, const unsigned char* sel);
+                      uint64_t* part, int nparts, cudaStream_t st, const unsigned char* sel,
+                      const ScanFuse* fuse = nullptr, bool* fused = nullptr);
 // K4/K6: per query, top-k of m composite keys -> (D, I).  `nt` (optional): D / I are pinned host memory and the
 // last CTA writes `seq` to the pinned word *h_seq once every query's rows have reached the host
 struct SelectNotify {

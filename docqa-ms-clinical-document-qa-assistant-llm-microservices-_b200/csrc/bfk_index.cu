@@ -1143,15 +1143,25 @@ static int search_exact(bfk_index* idx, const float* q_dev, int ldq, int64_t nq,
     uint64_t* part = (uint64_t*)ws_tail;
     int launches = 0;
     if (stats) cudaEventRecord(ev0, st);
-    for (int64_t q0 = 0; q0 < nq;) {
-        int g = (int)std::min<int64_t>(nq - q0, 8);
-        BFK_TRY(launch_scan_exact(idx, q_dev + (size_t)q0 * ldq, ldq, g, k, part + (size_t)q0 * nparts * k, nparts, st, idx->sel));
+    bool fused = false;
+    if (nq <= 8 && !stats) {
+        // one corpus pass: its last CTA may merge the per-CTA lists itself (decided by launch_scan_exact)
+        ScanFuse sf{D_dev, I_dev, (int64_t)k, id_offset, idx->sel_ticket, nt ? nt->h_seq : nullptr, nt ? nt->seq : 0};
+        BFK_TRY(launch_scan_exact(idx, q_dev, ldq, (int)nq, k, part, nparts, st, idx->sel, &sf, &fused));
         launches++;
-        q0 += g;
+    } else {
+        for (int64_t q0 = 0; q0 < nq;) {
+            int g = (int)std::min<int64_t>(nq - q0, 8);
+            BFK_TRY(launch_scan_exact(idx, q_dev + (size_t)q0 * ldq, ldq, g, k, part + (size_t)q0 * nparts * k, nparts, st, idx->sel));
+            launches++;
+            q0 += g;
+        }
     }
     if (stats) cudaEventRecord(ev1, st);
-    BFK_TRY(launch_select(part, (int64_t)nparts * k, nq, k, idx->metric, id_offset, D_dev, I_dev, k, st, nt));
-    launches++;
+    if (!fused) {
+        BFK_TRY(launch_select(part, (int64_t)nparts * k, nq, k, idx->metric, id_offset, D_dev, I_dev, k, st, nt));
+        launches++;
+    }
     if (stats) {
         stats->n_launches = launches;
         stats->algo_used = BFK_ALGO_EXACT_SIMT;

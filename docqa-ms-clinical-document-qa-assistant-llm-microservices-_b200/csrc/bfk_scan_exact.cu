@@ -94,6 +94,18 @@ struct ScanExactParams {
     uint64_t* part;      // [nq_real][nparts][k]
     int nparts;
     const unsigned char* sel;  // optional id selector bitmap (bit i <=> row i admitted), else null
+    // K4 folded into this kernel (small searches: the second launch and the gap before it cost more than the merge):
+    // the last CTA to publish its lists merges them and writes (D, I) itself
+    int fuse;
+    int metric;
+    int merge_n;               // power of two >= nparts * k (and >= k): the sort window
+    int64_t id_offset;
+    float* D;                  // [nq_real][out_ld]
+    int64_t* I;
+    int64_t out_ld;
+    int* ticket;               // device word, 0 between searches
+    int* h_seq;                // optional pinned host word: the sequence number below is written there at the end
+    int seq;
 };
 
 template <int NQ, int R, bool IS_L2, typename RowT>
@@ -278,6 +290,51 @@ __global__ void __launch_bounds__(SE_THREADS, 1) scan_exact_kernel(const ScanExa
             for (int i = tid; i < p.k; i += SE_CTHREADS) dst[i] = cj[i];
         }
     }
+    if (p.fuse) {
+        __shared__ int last_s;
+        __threadfence();  // this CTA's lists, before its ticket
+        consumer_sync();
+        if (tid == 0) last_s = (atomicAdd(p.ticket, 1) == (int)gridDim.x - 1) ? 1 : 0;
+        consumer_sync();
+        if (last_s) {
+            if (tid == 0) *p.ticket = 0;  // re-armed for the next search
+            __threadfence();
+            // the ring was last written by bulk copies (async proxy); it is the merge window now
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            uint64_t* buf = reinterpret_cast<uint64_t*>(tiles);
+            const int m = p.nparts * p.k;
+            for (int j = 0; j < p.nq_real; j++) {
+                const uint64_t* src = p.part + (size_t)j * m;
+                for (int i = tid; i < p.merge_n; i += SE_CTHREADS) buf[i] = i < m ? __ldcg(src + i) : COMP_EMPTY;
+                consumer_sync();
+                consumer_bitonic_sort(buf, p.merge_n, tid);
+                for (int i = tid; i < p.k; i += SE_CTHREADS) {
+                    const uint64_t c = buf[i];
+                    float dv;
+                    int64_t iv;
+                    if (c == COMP_EMPTY) {  // faiss's padding
+                        dv = (p.metric == BFK_METRIC_L2) ? FLT_MAX : -FLT_MAX;
+                        iv = -1;
+                    } else {
+                        const float key = ord2f((uint32_t)(c >> 32));
+                        dv = (p.metric == BFK_METRIC_L2) ? key : -key;
+                        iv = (int64_t)(c & 0xffffffffu) + p.id_offset;
+                    }
+                    p.D[(size_t)j * p.out_ld + i] = dv;
+                    p.I[(size_t)j * p.out_ld + i] = iv;
+                }
+                consumer_sync();
+            }
+            if (p.h_seq != nullptr) {  // (D, I) are pinned host memory and the host polls this word
+                __threadfence_system();
+                consumer_sync();
+                if (tid == 0) {
+                    *reinterpret_cast<volatile int*>(p.h_seq) = p.seq;
+                    __threadfence_system();
+                }
+            }
+        }
+    }
 }
 
 // ---- host side ---------------------------------------------------------------
@@ -364,7 +421,8 @@ static int launch_nq(int NQ, int R, const ScanExactParams& p, size_t smem, int g
 
 // nq <= 8 queries; part is [nq][nparts][k]
 int launch_scan_exact(const bfk_index* idx, const float* q_dev, int ldq, int nq, int k, uint64_t* part, int nparts,
-                      cudaStream_t st, const unsigned char* sel) {
+                      cudaStream_t st, const unsigned char* sel, const ScanFuse* fuse, bool* fused) {
+    if (fused) *fused = false;
     ScanExactPlan pl;
     BFK_TRY(plan_scan_exact(idx, nq, k, &pl));
     if (pl.grid != nparts) {
@@ -395,6 +453,29 @@ int launch_scan_exact(const bfk_index* idx, const float* q_dev, int ldq, int nq,
         p.part = part + (size_t)q0 * nparts * k;
         p.nparts = nparts;
         p.sel = sel;
+        p.fuse = 0;
+        p.ticket = nullptr;
+        p.h_seq = nullptr;
+        if (fuse && q0 == 0 && g == nq) {
+            // one launch covers the search: its last CTA can merge, if the lists are few enough for one CTA to sort
+            // quickly (beyond that K4's one-CTA-per-query launch is faster) and the window fits the ring
+            int n = 32;
+            while (n < nparts * k || n < k) n <<= 1;
+            const size_t ring = (size_t)sub.stages * (size_t)(SE_CWARPS * sub.R) * (size_t)p.ld * (f32 ? 4 : 2);
+            if ((int64_t)nq * n <= 2048 && (size_t)n * 8 <= ring) {
+                p.fuse = 1;
+                p.metric = idx->metric;
+                p.merge_n = n;
+                p.id_offset = fuse->id_offset;
+                p.D = fuse->D;
+                p.I = fuse->I;
+                p.out_ld = fuse->out_ld;
+                p.ticket = fuse->ticket;
+                p.h_seq = fuse->h_seq;
+                p.seq = fuse->seq;
+                if (fused) *fused = true;
+            }
+        }
         const bool l2 = idx->metric == BFK_METRIC_L2;
         int rc;
         if (f32)
