@@ -1158,7 +1158,11 @@ static int64_t tc_chunk_queries(const bfk_index* idx, int64_t nq) {
         // fewer than 8 streams per query tile run the long lists (KP = 32: more registers, costlier inserts):
         // measured 2410 us for nq = 4096 as 3072 + 1024 against 2335 us as 2 x 2048
         const double long_lists = S < 8 ? 1.05 : 1.0;
-        return ((double)std::max<int64_t>((T + S - 1) / S, T / 75) + 16.0) * long_lists;
+        // every pass reads the corpus from HBM once more.  That is never the bottleneck of a tensor-bound pass, but
+        // it is not free either (L2 misses in front of the ring, and power on a power-capped part): config 3 as
+        // 8 passes of 512 queries (148 SMs busy) measured 57.3 ms, as 2 passes of 2048 (144 SMs) 52.3 ms.  A third of
+        // the corpus read time charged on top of the compute time reproduces both that and the 1M x 384 measurements.
+        return ((double)std::max<int64_t>((T + S - 1) / S, T / 75) + 16.0) * long_lists + 0.3 * (double)(T / 75);
     };
     static const int forced = [] {  // experiments: BFK_TC_CHUNK_TILES=c forces passes of c query tiles
         const char* e = getenv("BFK_TC_CHUNK_TILES");
