@@ -95,9 +95,10 @@ struct bfk_index {
     bfk::VmArray* vmn = nullptr;
     unsigned int* maxn = nullptr;
     bfk::Workspace ws;       // search scratch, grow-only
-    cudaEvent_t ws_free = nullptr;  // recorded after the last search that used `ws`
+    cudaEvent_t ws_free = nullptr;  // recorded (lazily, see ws_settle) behind the last work that used `ws`
     cudaStream_t ws_stream = nullptr;  // ... and the stream it ran on
     bool ws_stream_known = false;
+    bool ws_dirty = false;          // work using `ws` was enqueued on ws_stream and no event has been recorded behind it yet
     int* h_flag = nullptr;          // pinned host words: [0] count of uncertified queries of the last tensor pass,
                                     // [1] that pass's sequence number, written after the count (the host polls it)
     int flag_seq = 0;               // sequence number of the last tensor pass / host-notifying search enqueued

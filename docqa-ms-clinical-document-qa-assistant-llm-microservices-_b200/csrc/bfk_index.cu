@@ -213,9 +213,35 @@ int grow_for(bfk_index* idx, int64_t need, cudaStream_t st) {
     return ensure_capacity(idx, need, st);
 }
 
+// The workspace's last user is remembered as (stream, "dirty") instead of recording an event after every search:
+// the event is only recorded -- on that stream, behind the work in question -- when somebody actually has to wait for
+// it (another stream uses the workspace, or it is regrown).  One driver call less on every search's critical path.
+static int ws_settle(bfk_index* idx) {
+    if (!idx->ws_dirty) return 0;
+    idx->ws_dirty = false;
+    if (cudaEventRecord(idx->ws_free, idx->ws_stream) != cudaSuccess) {
+        cudaGetLastError();  // the stream is gone: everything on it has completed or will have after this
+        BFK_CUDA(cudaDeviceSynchronize());
+        BFK_CUDA(cudaEventRecord(idx->ws_free, 0));
+    }
+    return 0;
+}
+
+static int ws_acquire(bfk_index* idx, cudaStream_t st) {
+    if (idx->ws_stream_known && idx->ws_stream != st) {
+        BFK_TRY(ws_settle(idx));
+        BFK_CUDA(cudaStreamWaitEvent(st, idx->ws_free, 0));
+    }
+    idx->ws_stream = st;
+    idx->ws_stream_known = true;
+    idx->ws_dirty = true;  // the caller is about to enqueue work on it
+    return 0;
+}
+
 int ensure_workspace(bfk_index* idx, size_t bytes) {
     if (bytes <= idx->ws.bytes) return 0;
     // the previous buffer may still be in use by an enqueued search
+    BFK_TRY(ws_settle(idx));
     if (idx->ws_free) BFK_CUDA(cudaEventSynchronize(idx->ws_free));
     if (idx->ws.ptr) cudaFree(idx->ws.ptr);
     idx->ws.ptr = nullptr;
@@ -385,9 +411,7 @@ static int add_rows(bfk_index* idx, const float* x, int64_t n, int x_is_device, 
     // host rows: stage through device scratch in <= 64 MiB pieces
     const int64_t chunk = std::max<int64_t>(1, (64ll << 20) / (int64_t)(sizeof(float) * idx->d));
     BFK_TRY(ensure_workspace(idx, sizeof(float) * (size_t)std::min(chunk, n) * idx->d));
-    if (idx->ws_stream_known && idx->ws_stream != st) BFK_CUDA(cudaStreamWaitEvent(st, idx->ws_free, 0));
-    idx->ws_stream = st;
-    idx->ws_stream_known = true;
+    BFK_TRY(ws_acquire(idx, st));
     BFK_TRY(wait_rows_ready(idx, st));
     const size_t small_bytes = sizeof(float) * (size_t)n * idx->d;
     char* pin = small_bytes <= STAGE_BYTES ? stage_buffer(idx) : nullptr;
@@ -406,14 +430,12 @@ static int add_rows(bfk_index* idx, const float* x, int64_t n, int x_is_device, 
         // return): the copy out of them must have happened.  Rows that came through the pinned buffer only wait
         // for that copy; their append kernel stays enqueued and `rows_ready` orders every later reader behind it.
         if (pin) {
-            BFK_CUDA(cudaEventRecord(idx->ws_free, st));
             BFK_TRY(mark_rows_ready(idx, st));
             BFK_CUDA(cudaEventSynchronize(idx->stage_done));
             return 0;
         }
         BFK_CUDA(cudaStreamSynchronize(st));
     }
-    BFK_CUDA(cudaEventRecord(idx->ws_free, st));
     return 0;
 }
 
@@ -655,9 +677,7 @@ static int search_locked(bfk_index* idx, const float* q, int64_t nq, int k, floa
     size_t head = sizing.off;
     BFK_TRY(ensure_workspace(idx, head + tail_bytes + 512));
     // the workspace's previous user: work on the same stream is ordered anyway, another stream has to be waited for
-    if (idx->ws_stream_known && idx->ws_stream != st) BFK_CUDA(cudaStreamWaitEvent(st, idx->ws_free, 0));
-    idx->ws_stream = st;
-    idx->ws_stream_known = true;
+    BFK_TRY(ws_acquire(idx, st));
     WsCarver ws(idx->ws.ptr);
     float* q_dev = ws.take<float>((size_t)nq * ldq);
     float* D_dev = ws.take<float>((size_t)nq * k);
@@ -797,7 +817,6 @@ static int search_locked(bfk_index* idx, const float* q, int64_t nq, int k, floa
         return 0;
     };
     if (!rc && !io_is_device) rc = copy_out();
-    if (!rc && cudaEventRecord(idx->ws_free, st) != cudaSuccess) rc = fail("search: event record failed");
     if (!rc && (!io_is_device || stats) && !out_zero_copy) {
         cudaError_t e = cudaStreamSynchronize(st);
         if (e != cudaSuccess) rc = fail(std::string("search: kernel execution failed: ") + cudaGetErrorString(e));
@@ -809,7 +828,6 @@ static int search_locked(bfk_index* idx, const float* q, int64_t nq, int k, floa
         rc = search_tensor_finish(idx, st, &rewritten);
         if (!rc && rewritten > 0) {
             rc = copy_out();
-            if (!rc && cudaEventRecord(idx->ws_free, st) != cudaSuccess) rc = fail("search: event record failed");
             if (!rc && cudaStreamSynchronize(st) != cudaSuccess) rc = fail("search: kernel execution failed");
         }
     }

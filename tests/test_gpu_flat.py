@@ -505,3 +505,51 @@ def test_cudamalloc_storage_fallback_in_a_fresh_process():
     out = subprocess.run([sys.executable, "-c", code], cwd=root, capture_output=True, text=True, timeout=300,
                          env={**os.environ, "BFK_VMEM": "0", "PYTHONPATH": root})
     assert out.returncode == 0 and "fallback ok" in out.stdout, out.stderr[-2000:]
+
+
+def test_streams_appends_and_searches_on_different_torch_streams(bfk, tmp_path):
+    """add() with device rows only enqueues the append on the caller's stream (torch streams are non-blocking: the
+    legacy stream does not wait for them).  Readers on other streams -- a search, reconstruct / write_index, a
+    regrowth -- must still see the rows: the library orders them behind the append with an event."""
+    import torch
+
+    rng = np.random.default_rng(53)
+    d = 384
+    side, other = torch.cuda.Stream(), torch.cuda.Stream()
+    idx = bfk.IndexFlatL2(d)
+    host = []
+    for step in range(6):
+        x = rng.standard_normal((30_000, d)).astype(np.float32)
+        host.append(x)
+        with torch.cuda.stream(side):
+            xd = torch.from_numpy(x).to("cuda", non_blocking=False)
+            big = torch.randn((4096, 4096), device="cuda")
+            for _ in range(3):
+                big = big @ big  # keeps `side` busy so that the append really is still pending afterwards
+            big = big.clamp(-1, 1)
+            idx.add(xd)  # enqueued behind the matmuls
+        n = idx.ntotal
+        # immediately, from the host (legacy stream) and from another torch stream
+        got = idx.reconstruct_n(n - 100, 100)
+        np.testing.assert_array_equal(got, x[-100:])
+        with torch.cuda.stream(other):
+            q = torch.from_numpy(x[-5:]).to("cuda")
+            D, I = idx.search(q, 1)
+            other.synchronize()
+        assert I[:, 0].tolist() == list(range(n - 5, n)) and (D[:, 0] == 0).all()
+        D2, I2 = idx.search(x[:3], 1)  # numpy in, legacy stream
+        assert I2[:, 0].tolist() == list(range(n - 30_000, n - 30_000 + 3))
+    xb = np.concatenate(host)
+    path = str(tmp_path / "streams.faiss")
+    bfk.write_index(idx, path)
+    assert open(path, "rb").read() == faiss_io.write_index_bytes(xb, 1)
+    # the workspace is shared by searches on both streams: alternate them without host waits in between
+    qs = torch.from_numpy(xb[:64]).to("cuda")
+    outs = []
+    for i in range(6):
+        st = side if i % 2 == 0 else other
+        with torch.cuda.stream(st):
+            outs.append(idx.search(qs, 3, algo="tensor"))
+    torch.cuda.synchronize()
+    for D, I in outs:
+        assert I[:, 0].tolist() == list(range(64))
