@@ -57,6 +57,28 @@ __device__ void consumer_bitonic_sort(uint64_t* a, int n, int tid) {
     }
 }
 
+// the same for short arrays (n <= 256, a power of two): every element's rank is counted -- n*n independent compares
+// over the 256 consumer threads, three barriers in all -- instead of a network of up to 36 barrier-separated steps.
+// Equal composites (only COMP_EMPTY padding repeats) are ordered by position, so ranks are distinct.
+__device__ void consumer_sort(uint64_t* a, int n, int tid) {
+    if (n > SE_CTHREADS) {
+        consumer_bitonic_sort(a, n, tid);
+        return;
+    }
+    const int P = SE_CTHREADS / n;  // threads per element: neighbours in one warp (P <= 8 as n >= 32)
+    const int e = tid / P, part = tid - e * P;
+    const uint64_t v = a[e];
+    int cnt = 0;
+    for (int j = part; j < n; j += P) {
+        const uint64_t o = a[j];
+        cnt += (o < v || (o == v && j < e)) ? 1 : 0;
+    }
+    for (int o = P >> 1; o > 0; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+    consumer_sync();
+    if (part == 0) a[cnt] = v;
+    consumer_sync();
+}
+
 template <typename RowT>
 struct RowVec;
 template <>
@@ -285,7 +307,12 @@ __global__ void __launch_bounds__(SE_THREADS, 1) scan_exact_kernel(const ScanExa
     for (int j = 0; j < NQ; j++) {
         if (j < p.nq_real) {
             uint64_t* cj = cand + (size_t)j * p.cap;
-            consumer_bitonic_sort(cj, p.cap, tid);
+            // slots past the count hold COMP_EMPTY: only the filled prefix (rounded up to a power of two that also
+            // covers k) needs ordering
+            int ns = 32;
+            const int filled = *reinterpret_cast<volatile int*>(&cnt_s[j]);
+            while (ns < filled || ns < p.k) ns <<= 1;
+            consumer_sort(cj, min(ns, p.cap), tid);
             uint64_t* dst = p.part + ((size_t)j * p.nparts + blockIdx.x) * p.k;
             for (int i = tid; i < p.k; i += SE_CTHREADS) dst[i] = cj[i];
         }
@@ -307,7 +334,7 @@ __global__ void __launch_bounds__(SE_THREADS, 1) scan_exact_kernel(const ScanExa
                 const uint64_t* src = p.part + (size_t)j * m;
                 for (int i = tid; i < p.merge_n; i += SE_CTHREADS) buf[i] = i < m ? __ldcg(src + i) : COMP_EMPTY;
                 consumer_sync();
-                consumer_bitonic_sort(buf, p.merge_n, tid);
+                consumer_sort(buf, p.merge_n, tid);
                 for (int i = tid; i < p.k; i += SE_CTHREADS) {
                     const uint64_t c = buf[i];
                     float dv;
