@@ -769,7 +769,10 @@ __device__ void rr_sort(uint64_t* a, int n, int tid) {
 // candidates (many queries): four times as many queries are then resident per SM.
 template <int RR_THREADS>
 __global__ void __launch_bounds__(RR_THREADS) rerank_kernel(const RerankParams p) {
-    __shared__ uint64_t buf[TC_MERGE_N];
+    // the 128-thread form only ever sees <= 1024 candidates per query: an 8 KB window instead of 32 KB (five CTAs per
+    // SM instead of four; measured no faster -- at 2048 queries K5 is bound by the ~60 MB of scattered row reads)
+    constexpr int MERGE_N = RR_THREADS == 128 ? 1024 : TC_MERGE_N;
+    __shared__ uint64_t buf[MERGE_N];
     __shared__ uint64_t ex[TC_RMAX];
     __shared__ float q_s[BFK_MAX_D];
     __shared__ float red[RR_THREADS / 32];
@@ -816,7 +819,7 @@ __global__ void __launch_bounds__(RR_THREADS) rerank_kernel(const RerankParams p
         auto keep = [&](uint64_t c) {
             if (c != COMP_EMPTY && (uint32_t)(c >> 32) <= tmin_ord) {
                 const int slot = atomicAdd(&cnt_s, 1);
-                if (slot < TC_MERGE_N) buf[slot] = c;
+                if (slot < MERGE_N) buf[slot] = c;
             }
         };
 #pragma unroll
@@ -841,7 +844,7 @@ __global__ void __launch_bounds__(RR_THREADS) rerank_kernel(const RerankParams p
     __syncthreads();
     RR_MARK(1);
     const int total = cnt_s;
-    const int cnt = min(total, TC_MERGE_N);
+    const int cnt = min(total, MERGE_N);
     int n = 64;
     while (n < cnt) n <<= 1;
     for (int i = cnt + tid; i < n; i += RR_THREADS) buf[i] = COMP_EMPTY;
@@ -873,7 +876,7 @@ __global__ void __launch_bounds__(RR_THREADS) rerank_kernel(const RerankParams p
             if (nvalid > 0) {
                 if (R < kk) R = kk;
                 if (!(tmin > cut)) certified = 0;          // a dropped row could still reach the cut
-                if (total > TC_MERGE_N) certified = 0;     // survivors did not fit the sort window
+                if (total > MERGE_N) certified = 0;        // survivors did not fit the sort window
                 if (R == TC_RMAX && cnt > TC_RMAX && ord2f((uint32_t)(buf[TC_RMAX] >> 32)) <= cut)
                     certified = 0;                         // more rows inside the cut than we re-score
             } else {
