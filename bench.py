@@ -10,8 +10,9 @@ split row-wise over the N ranks (strong scaling; at N = 1 the whole 77 GB corpus
 At N = 1 the line also carries, as extra keys, the other BASELINE configs measured in the same run:
 `c2` (1M x 384 fp32, batches 1/64/1024/4096: the configuration the metric is quoted on), `c3`
 (10M x 768 bf16-stored, IndexFlatIP, k = 100, batch 4096), `c4` (pool + normalise + cast + add),
-`c4e` (encoder -> pool -> add) and `c1` (the reference's own 649-row index, single-query latency),
-each with its own `roofline` / `e2e` / `cpu_baseline`.
+`c4e` (encoder -> pool -> add), `c1` (the reference's own 649-row index, single-query latency) and `c1i` (the
+reference's ingestion pattern: one add per chunk, one save per message), each with its own `roofline` / `e2e` /
+`cpu_baseline`.
 
 Prints ONE JSON line (rank 0).  `value` = queries/s with queries and results resident in HBM;
 `e2e` = the same through the public numpy API with host buffers (H2D + D2H inside the timed
@@ -935,7 +936,10 @@ def main():
                 so.free()
             except Exception as e:  # an extra must not take the head line down with it
                 line[other] = {"error": f"{type(e).__name__}: {e}"}
-        for other, fn in (("c4", lambda: run_c4(sub, with_cpu=with_cpu)), ("c4e", lambda: run_c4e(sub)), ("c1", lambda: run_c1(sub))):
+        ing = argparse.Namespace(**vars(sub))
+        ing.rows = 300  # messages: enough for stable medians, a couple of seconds in all
+        for other, fn in (("c4", lambda: run_c4(sub, with_cpu=with_cpu)), ("c4e", lambda: run_c4e(sub)), ("c1", lambda: run_c1(sub)),
+                          ("c1i", lambda: run_c1i(ing))):
             try:
                 line[other] = fn()
             except Exception as e:
