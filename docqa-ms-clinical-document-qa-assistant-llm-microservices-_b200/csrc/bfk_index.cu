@@ -690,9 +690,10 @@ static int search_locked(bfk_index* idx, const float* q, int64_t nq, int k, floa
     //           address it directly -- the query preparation reads it over PCIe, K5 writes (D, I) into it;
     //   STAGED  pageable and small: one memcpy into / out of the index's own pinned buffer, which the kernels address
     //           the same way (queries in its first half, results in its second);
-    //   COPY    pageable and large, or not the tensor path: cudaMemcpyAsync on the stream, one stream wait at the end.
-    // With PINNED / STAGED nothing is enqueued on the stream but the three kernels, and the host only polls the word
-    // K5's last CTA writes: two DMA launches, their serialisation with the kernels and a driver-level wait less.
+    //   COPY    pageable and large (or a timed / selector search): cudaMemcpyAsync on the stream, one stream wait at the end.
+    // With PINNED / STAGED nothing is enqueued on the stream but the kernels, and the host only polls the word the last
+    // CTA of K5 (tensor path) or of K3a / K4 (fp32 path) writes: two DMA launches, their serialisation with the kernels
+    // and a driver-level wait less.
     enum Mode { MODE_DEVICE, MODE_PINNED, MODE_STAGED, MODE_COPY };
     const size_t q_bytes = sizeof(float) * (size_t)nq * idx->d;
     const size_t out_span = (size_t)((char*)(I_dev + (size_t)nq * k) - (char*)D_dev);  // D, padding, I: contiguous
