@@ -288,7 +288,24 @@ __global__ void __launch_bounds__(EB_THREADS) enc_attention_blk_kernel(const Enc
     }
     if (warp == 0) tmem_alloc<128>(tmem_slot);
 
-    // ---- stage Q (this thread's row), K (all T rows) and the mask bias ----
+    // ---- stage Q (this thread's row), K (all T rows) and the mask bias; on the way, ||q||^2 of the row and the
+    //      largest ||k||^2 of the head: every score obeys s <= ||q|| max||k|| (Cauchy-Schwarz) ----
+    auto sumsq = [](const uint4 (&w)[4]) {
+        float s = 0.f;
+#pragma unroll
+        for (int c = 0; c < 4; c++) {
+            const uint32_t e[4] = {w[c].x, w[c].y, w[c].z, w[c].w};
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                const float lo = __uint_as_float(e[i] << 16), hi = __uint_as_float(e[i] & 0xffff0000u);
+                s = fmaf(lo, lo, s);
+                s = fmaf(hi, hi, s);
+            }
+        }
+        return s;
+    };
+    float qn2 = 0.f, kn2 = 0.f;
+    int any_key = 0;  // some key of the chunk is not masked
     {
         const int q = mt * 128 + tid;
         uint4 v[4] = {make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0)};
@@ -297,6 +314,7 @@ __global__ void __launch_bounds__(EB_THREADS) enc_attention_blk_kernel(const Enc
 #pragma unroll
             for (int c = 0; c < 4; c++) v[c] = __ldg(src + c);
         }
+        qn2 = sumsq(v);
 #pragma unroll
         for (int c = 0; c < 4; c++) *reinterpret_cast<uint4*>(smem + EB_Q_OFF + sw64_off(tid, c)) = v[c];
     }
@@ -305,23 +323,42 @@ __global__ void __launch_bounds__(EB_THREADS) enc_attention_blk_kernel(const Enc
         uint4 kv[4];
 #pragma unroll
         for (int c = 0; c < 4; c++) kv[c] = __ldg(ksrc + c);
+        kn2 = fmaxf(kn2, sumsq(kv));
 #pragma unroll
         for (int c = 0; c < 4; c++) *reinterpret_cast<uint4*>(smem + EB_K_OFF + sw64_off(t, c)) = kv[c];
-        mb[t] = p.mask_bias[row0 + t];
+        const float bias = p.mask_bias[row0 + t];
+        mb[t] = bias;
+        any_key |= bias == 0.f ? 1 : 0;
     }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) kn2 = fmaxf(kn2, __shfl_xor_sync(0xffffffffu, kn2, o));
+    float* kmax_s = reinterpret_cast<float*>(tmem_slot + 2);  // [4] one per warp
+    if ((tid & 31) == 0) kmax_s[warp] = kn2;
     fence_proxy_async_smem();
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
+    kn2 = fmaxf(fmaxf(kmax_s[0], kmax_s[1]), fmaxf(kmax_s[2], kmax_s[3]));
     const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(tmem_slot);
     const uint32_t lane_addr = tmem_base + ((uint32_t)(warp * 32) << 16);
     const uint64_t dq = make_smem_desc_sw64(smem_u32(smem + EB_Q_OFF));
     uint32_t ph_s = 0, ph_o = 0;  // phases of bars[0] / bars[1]
     uint32_t r[2][32];
 
-    // ---- pass 1: row maximum over all keys, 128 keys at a time ----
-    float mx = -INFINITY;
-    for (int k0 = 0; k0 < T; k0 += 128) {
+    // ---- the softmax shift ----
+    // Any mx >= the row's largest score gives the same softmax; it need not be the maximum itself.  The bound
+    // ||q|| max||k|| (in the exp2 domain, mask bias <= 0) costs nothing, and p = exp2(s - mx) keeps its relative
+    // precision however far mx lies above the true maximum -- fp32 and bf16 share their exponent range -- as long as
+    // nothing underflows: with the bound at most 100 (2^-100 is far inside the range) the first pass over the keys,
+    // a quarter of this kernel, is skipped.  Rows of a CTA whose bound is larger take the exact maximum as before.
+    const float mhat = sqrtf(qn2 * kn2) * p.scale_log2 * 1.0001f + 1e-3f;
+    // (a chunk whose every key is masked keeps the exact maximum too: its scores all carry the -1e30 bias and the
+    // softmax over them is uniform, which only the true maximum reproduces)
+    const bool no_key = __syncthreads_or(any_key) == 0;
+    const bool exact_max = __syncthreads_or(mhat > 100.f ? 1 : 0) != 0 || no_key;
+    float mx = exact_max ? -INFINITY : mhat;
+    // ---- pass 1 (only when the bound is not usable): row maximum over all keys, 128 keys at a time ----
+    for (int k0 = 0; exact_max && k0 < T; k0 += 128) {
         const int n1 = min(128, T - k0);
         if (warp == 0) {
             if (elect_one()) {
