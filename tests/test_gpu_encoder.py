@@ -183,3 +183,28 @@ def test_query_side_replaces_newlines_like_huggingface_embeddings(bfk):
     np.testing.assert_array_equal(np.array(enc.embed_documents([q, "a b"])[0], dtype=np.float32), flat)
     assert not np.allclose(enc.encode([q])[0], flat)  # the raw text tokenises differently
     assert enc.embed_documents([]) == []
+
+
+def test_attention_softmax_shift_both_routes(bfk):
+    """The attention kernel shifts the softmax by the bound ||q|| max||k|| and only computes the true row maximum
+    when that bound is too large (> 100 in the exp2 domain) or when every key of the chunk is masked.  Large query /
+    key projections force the second route, an all-zero attention mask the third; all must match BertModel."""
+    import torch
+
+    m = hf_model(layers=1, vocab=300)
+    with torch.no_grad():  # scores of a few hundred: far beyond what the bound may be used for
+        for name in ("query", "key"):
+            getattr(m.encoder.layer[0].attention.self, name).weight.mul_(14.0)
+    enc = bfk.MiniLMEncoder.from_hf_model(m)
+    ids, mask = inputs(4, 128, 300)
+    mask[3, :] = 0  # a chunk with no valid token at all
+    with torch.no_grad():
+        want = m(input_ids=torch.from_numpy(ids), attention_mask=torch.from_numpy(mask)).last_hidden_state.numpy()
+    got = enc.forward(torch.from_numpy(ids).cuda(), torch.from_numpy(mask).cuda()).float().cpu().numpy()
+    assert np.isfinite(got).all()
+    valid = mask.astype(bool)
+    err = np.abs(got - want)[valid]
+    # sharply peaked softmaxes amplify the bf16 rounding of the scores: a looser bound than the default weights get
+    assert err.max() <= 0.25 and err.mean() <= 0.02, (err.max(), err.mean())
+    # the fully masked chunk attends uniformly, as transformers' finite additive mask makes it
+    assert np.abs(got[3] - want[3]).max() <= 0.08, np.abs(got[3] - want[3]).max()
