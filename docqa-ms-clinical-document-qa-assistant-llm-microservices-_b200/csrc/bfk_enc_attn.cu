@@ -53,6 +53,7 @@ struct EncAttnParams {
     __nv_bfloat16* ctx;         // [B*T, H]
     int T, H;
     float scale_log2;           // log2(e) / sqrt(head_dim)
+    float shift_limit;          // the bound ||q|| max||k|| replaces the row maximum while it is <= this (100; 0 = never)
 };
 
 __global__ void __launch_bounds__(EA_THREADS) enc_attention_kernel(const EncAttnParams p) {
@@ -355,7 +356,7 @@ __global__ void __launch_bounds__(EB_THREADS) enc_attention_blk_kernel(const Enc
     // (a chunk whose every key is masked keeps the exact maximum too: its scores all carry the -1e30 bias and the
     // softmax over them is uniform, which only the true maximum reproduces)
     const bool no_key = __syncthreads_or(any_key) == 0;
-    const bool exact_max = __syncthreads_or(mhat > 100.f ? 1 : 0) != 0 || no_key;
+    const bool exact_max = __syncthreads_or(mhat > p.shift_limit ? 1 : 0) != 0 || no_key;
     float mx = exact_max ? -INFINITY : mhat;
     // ---- pass 1 (only when the bound is not usable): row maximum over all keys, 128 keys at a time ----
     for (int k0 = 0; exact_max && k0 < T; k0 += 128) {
@@ -513,6 +514,11 @@ int launch_enc_attention(const __nv_bfloat16* qkv, const float* mask_bias, __nv_
     p.T = T;
     p.H = H;
     p.scale_log2 = 1.4426950408889634f / sqrtf((float)EA_DH);
+    static const bool exact_shift = [] {  // BFK_ENC_SHIFT=exact: always the true row maximum (tests, comparisons)
+        const char* e = getenv("BFK_ENC_SHIFT");
+        return e && e[0] == 'e';
+    }();
+    p.shift_limit = exact_shift ? 0.f : 100.f;
     dim3 grid((unsigned)((T + 127) / 128), (unsigned)heads, (unsigned)B);
     if (whole_row) enc_attention_kernel<<<grid, EA_THREADS, EA_SMEM, st>>>(p);
     else enc_attention_blk_kernel<<<grid, EB_THREADS, EB_SMEM, st>>>(p);
