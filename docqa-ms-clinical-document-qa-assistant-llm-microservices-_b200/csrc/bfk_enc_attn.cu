@@ -40,6 +40,11 @@ __device__ __forceinline__ float ex2_fast(float x) {
     return y;
 }
 
+__device__ __forceinline__ uint32_t pack_bf16x2_rn(float lo, float hi) {
+    const __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
+    return *reinterpret_cast<const uint32_t*>(&v);
+}
+
 __device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
 // byte offset of 16-byte chunk `c` (0..7) of row `r` inside a [rows x 128 B] tile, 128-byte swizzle
@@ -53,7 +58,8 @@ struct EncAttnParams {
     __nv_bfloat16* ctx;         // [B*T, H]
     int T, H;
     float scale_log2;           // log2(e) / sqrt(head_dim)
-    float shift_limit;          // the bound ||q|| max||k|| replaces the row maximum while it is <= this (100; 0 = never)
+    float shift_limit;          // the bound ||q|| max||k|| replaces the row maximum while it is <= this (60; 0 = never)
+    unsigned long long* trace;  // debugging (BFK_ENC_ATTN_TRACE): [128] clock64 stamps of one CTA, or null
 };
 
 __global__ void __launch_bounds__(EA_THREADS) enc_attention_kernel(const EncAttnParams p) {
@@ -235,23 +241,29 @@ __global__ void __launch_bounds__(EA_THREADS) enc_attention_kernel(const EncAttn
     }
 }
 
-// ---- E3b: the same attention in 64-key blocks, four to five CTAs per SM -----------------------------------
+// ---- E3b: the same attention in 64-key blocks, four CTAs per SM -------------------------------------------
 // enc_attention_kernel above keeps a whole 128 x T score tile in TMEM (256 columns): two CTAs per SM, each one
 // serial latency chain (ncu: 24 % of the warps active, 465 us per layer).  This variant needs 128 TMEM columns
-// and 45 KB of shared memory per CTA, so four or five chains overlap on an SM:
-//   pass 1  S = Q K^T in 128-key pieces (columns 0..127) only to find the row maximum;
-//   pass 2  per 64-key block j: S_j recomputed into columns 0..63 (two MMAs -- cheaper than keeping it),
-//           p = exp2(s - max) in the row's thread, P_j (bf16) and V_j^T staged in shared memory,
-//           O (+)= P_j V_j into columns 64..95.  The softmax is the exact two-pass one, no rescaling.
+// and 55 KB of shared memory per CTA, so four chains overlap on an SM.  One CTA per (head, chunk): K is staged
+// once for the chunk's one or two 128-query tiles; thread == query row == TMEM lane.
+//   pass 1  (only when the cheap bound on the row maximum is unusable) S = Q K^T in 128-key pieces for the maximum;
+//   pass 2  per 64-key block j: S_j into columns 0..63, p = exp2(s - max) in the row's thread, P_j (bf16) and
+//           V_j^T staged in shared memory, O (+)= P_j V_j into columns 64..111.  S_{j+1} is issued together with
+//           P_j V_j, so it is complete by the time the threads come back for it.
+// The row sums come out of the same MMA: V^T carries a 33rd row of ones (N = 48), so column 96 of O is
+// sum_j p_j -- of the bf16-rounded p that are really multiplied.  A block whose keys are all masked is skipped
+// (its p are zero); a block without masked keys needs no per-key test.
 // Q and K use the 64-byte swizzle (their rows are 64 bytes: head dimension 32), P and V^T the 128-byte one.
+// (Two threads per row -- 256-thread CTAs, eight warps per scheduler -- was measured slower: 372 us against 287 us
+// per layer of 512 chunks x 256 tokens.)
 constexpr int EB_THREADS = 128;
-constexpr int EB_Q_OFF = 0;                 // [128 x 64 B]            8 KiB
-constexpr int EB_K_OFF = 8 * 1024;          // [T x 64 B]          <= 16 KiB
-constexpr int EB_V_OFF = 24 * 1024;         // [32 dims x 128 B]       4 KiB (one 64-token block)
-constexpr int EB_P_OFF = 28 * 1024;         // [128 x 128 B]          16 KiB (one 64-key block)
-constexpr int EB_MB_OFF = 44 * 1024;        // [256] fp32 mask bias
-constexpr int EB_BAR_OFF = EB_MB_OFF + EA_MAXT * 4;
-constexpr int EB_SMEM = EB_BAR_OFF + 64 + 1024 /*alignment*/;
+constexpr int EB_ON = 48;                   // N of the P V product: 32 dims, the ones row, padding to a multiple of 16
+constexpr int EB_Q_OFF = 0;                 // [2 tiles][128 x 64 B]  16 KiB
+constexpr int EB_K_OFF = 16 * 1024;         // [T x 64 B]          <= 16 KiB
+constexpr int EB_V_OFF = 32 * 1024;         // [48 rows x 128 B]       6 KiB (one 64-token block; rows 32..47 constant)
+constexpr int EB_P_OFF = 38 * 1024;         // [128 x 128 B]          16 KiB (one 64-key block)
+constexpr int EB_BAR_OFF = 54 * 1024;
+constexpr int EB_SMEM = EB_BAR_OFF + 128;
 
 // byte offset of 16-byte chunk `c` (0..3) of row `r` inside a [rows x 64 B] tile, 64-byte swizzle
 __device__ __forceinline__ uint32_t sw64_off(int r, int c) {
@@ -268,19 +280,27 @@ __device__ __forceinline__ uint64_t make_smem_desc_sw64(uint32_t smem_addr_bytes
     return d;
 }
 
-__global__ void __launch_bounds__(EB_THREADS) enc_attention_blk_kernel(const EncAttnParams p) {
+#define EB_MARK(ev) do { if (trace) trace[(ev)] = (unsigned long long)clock64(); } while (0)
+
+__global__ void __launch_bounds__(EB_THREADS, 4) enc_attention_blk_kernel(const EncAttnParams p) {
+    // four CTAs per SM leave no room for alignment slack: the kernel has no static shared memory, so the dynamic
+    // window starts on a 1 KiB boundary (the swizzled operand tiles need it); anything else is refused
     extern __shared__ __align__(1024) unsigned char smem_raw[];
-    const uint32_t raw = smem_u32(smem_raw);
-    unsigned char* smem = smem_raw + ((1024u - (raw & 1023u)) & 1023u);
-    float* mb = reinterpret_cast<float*>(smem + EB_MB_OFF);
+    unsigned char* smem = smem_raw;
+    if ((smem_u32(smem_raw) & 1023u) != 0u) __trap();
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + EB_BAR_OFF);  // [0] scores ready, [1] O block accumulated
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2);
+    float* kmax_s = reinterpret_cast<float*>(tmem_slot + 2);  // [4] one per warp
+    uint32_t* keep_s = tmem_slot + 8;                         // [8] bit t%32 of word t/32: key t is not masked
 
-    const int tid = threadIdx.x, warp = tid >> 5;
-    const int mt = blockIdx.x, h = blockIdx.y;
-    const int64_t b = blockIdx.z;
-    const int T = p.T, ld = 3 * p.H, NB = T >> 6;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int h = blockIdx.x;
+    const int64_t b = blockIdx.y;
+    const int T = p.T, ld = 3 * p.H, NB = T >> 6, QT = (T + 127) >> 7;
     const int64_t row0 = b * T;
+    // BFK_ENC_ATTN_TRACE: thread 0 of one CTA in the middle of the grid records clock64 at every phase boundary
+    unsigned long long* trace = (p.trace != nullptr && tid == 0 && blockIdx.x == 5 && blockIdx.y == gridDim.y / 2) ? p.trace : nullptr;
+    EB_MARK(0);
 
     if (tid == 0) {
         mbar_init(&bars[0], 1);
@@ -288,9 +308,11 @@ __global__ void __launch_bounds__(EB_THREADS) enc_attention_blk_kernel(const Enc
         fence_mbar_init();
     }
     if (warp == 0) tmem_alloc<128>(tmem_slot);
+    EB_MARK(1);
 
-    // ---- stage Q (this thread's row), K (all T rows) and the mask bias; on the way, ||q||^2 of the row and the
-    //      largest ||k||^2 of the head: every score obeys s <= ||q|| max||k|| (Cauchy-Schwarz) ----
+    // ---- stage Q (this thread's row of each 128-query tile), K (all T rows) and the mask: every load is issued
+    //      before the first one is used (one round trip to L2 / HBM instead of three).  On the way, ||q||^2 of the
+    //      rows and the largest ||k||^2 of the head: every score obeys s <= ||q|| max||k|| (Cauchy-Schwarz) ----
     auto sumsq = [](const uint4 (&w)[4]) {
         float s = 0.f;
 #pragma unroll
@@ -305,187 +327,253 @@ __global__ void __launch_bounds__(EB_THREADS) enc_attention_blk_kernel(const Enc
         }
         return s;
     };
-    float qn2 = 0.f, kn2 = 0.f;
-    int any_key = 0;  // some key of the chunk is not masked
+    float qn2[2] = {0.f, 0.f}, kn2 = 0.f;
     {
-        const int q = mt * 128 + tid;
-        uint4 v[4] = {make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0)};
-        if (q < T) {
-            const uint4* src = reinterpret_cast<const uint4*>(p.qkv + (size_t)(row0 + q) * ld + h * EA_DH);
+        uint4 qv[2][4], kv[2][4];
+        float bias[2] = {-1e30f, -1e30f};
 #pragma unroll
-            for (int c = 0; c < 4; c++) v[c] = __ldg(src + c);
+        for (int i = 0; i < 2; i++) {
+            const int t = tid + i * EB_THREADS;  // T is a multiple of 64: t < T is warp-uniform
+#pragma unroll
+            for (int c = 0; c < 4; c++) qv[i][c] = kv[i][c] = make_uint4(0, 0, 0, 0);
+            if (t < T) {
+                const uint4* qsrc = reinterpret_cast<const uint4*>(p.qkv + (size_t)(row0 + t) * ld + h * EA_DH);
+                const uint4* ksrc = reinterpret_cast<const uint4*>(p.qkv + (size_t)(row0 + t) * ld + p.H + h * EA_DH);
+#pragma unroll
+                for (int c = 0; c < 4; c++) {
+                    qv[i][c] = __ldg(qsrc + c);
+                    kv[i][c] = __ldg(ksrc + c);
+                }
+                bias[i] = p.mask_bias[row0 + t];
+            }
         }
-        qn2 = sumsq(v);
+        EB_MARK(2);
 #pragma unroll
-        for (int c = 0; c < 4; c++) *reinterpret_cast<uint4*>(smem + EB_Q_OFF + sw64_off(tid, c)) = v[c];
+        for (int i = 0; i < 2; i++) {
+            const int t = tid + i * EB_THREADS;
+            if (i < QT) {  // rows past T inside the last tile are zero
+                qn2[i] = sumsq(qv[i]);
+#pragma unroll
+                for (int c = 0; c < 4; c++) *reinterpret_cast<uint4*>(smem + EB_Q_OFF + i * 8192 + sw64_off(tid, c)) = qv[i][c];
+            }
+            if (t < T) {
+                kn2 = fmaxf(kn2, sumsq(kv[i]));
+#pragma unroll
+                for (int c = 0; c < 4; c++) *reinterpret_cast<uint4*>(smem + EB_K_OFF + sw64_off(t, c)) = kv[i][c];
+                const uint32_t keep = __ballot_sync(0xffffffffu, bias[i] == 0.f);
+                if (lane == 0) keep_s[t >> 5] = keep;
+            }
+        }
     }
-    for (int t = tid; t < T; t += EB_THREADS) {
-        const uint4* ksrc = reinterpret_cast<const uint4*>(p.qkv + (size_t)(row0 + t) * ld + p.H + h * EA_DH);
-        uint4 kv[4];
-#pragma unroll
-        for (int c = 0; c < 4; c++) kv[c] = __ldg(ksrc + c);
-        kn2 = fmaxf(kn2, sumsq(kv));
-#pragma unroll
-        for (int c = 0; c < 4; c++) *reinterpret_cast<uint4*>(smem + EB_K_OFF + sw64_off(t, c)) = kv[c];
-        const float bias = p.mask_bias[row0 + t];
-        mb[t] = bias;
-        any_key |= bias == 0.f ? 1 : 0;
+    EB_MARK(3);
+    // rows 32..47 of V^T never change: row 32 is all ones (the row sums), the rest zero; a row is 128 contiguous
+    // bytes whatever the swizzle does inside it
+    {
+        const uint32_t w = tid < 8 ? 0x3f803f80u : 0u;
+        *reinterpret_cast<uint4*>(smem + EB_V_OFF + 32 * 128 + tid * 16) = make_uint4(w, w, w, w);
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) kn2 = fmaxf(kn2, __shfl_xor_sync(0xffffffffu, kn2, o));
-    float* kmax_s = reinterpret_cast<float*>(tmem_slot + 2);  // [4] one per warp
-    if ((tid & 31) == 0) kmax_s[warp] = kn2;
+    if (lane == 0) kmax_s[warp] = kn2;
     fence_proxy_async_smem();
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
+    EB_MARK(4);
     kn2 = fmaxf(fmaxf(kmax_s[0], kmax_s[1]), fmaxf(kmax_s[2], kmax_s[3]));
     const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(tmem_slot);
     const uint32_t lane_addr = tmem_base + ((uint32_t)(warp * 32) << 16);
-    const uint64_t dq = make_smem_desc_sw64(smem_u32(smem + EB_Q_OFF));
     uint32_t ph_s = 0, ph_o = 0;  // phases of bars[0] / bars[1]
     uint32_t r[2][32];
 
+    // which 64-key blocks take part, and which of them have no masked key (CTA-uniform)
+    uint32_t act = 0, full = 0;
+    for (int j = 0; j < NB; j++) {
+        const uint32_t w0 = keep_s[2 * j], w1 = keep_s[2 * j + 1];
+        if (w0 | w1) act |= 1u << j;
+        if ((w0 & w1) == 0xffffffffu) full |= 1u << j;
+    }
+    // A chunk whose every key is masked: all its scores carry the same -1e30 bias, which swallows them in fp32, and
+    // the softmax is uniform over all T keys.  Scale 0 and shift 0 over all blocks give exactly that.
+    const bool no_key = act == 0;
+    if (no_key) act = full = (1u << NB) - 1u;
+    const float scale = no_key ? 0.f : p.scale_log2;
+
     // ---- the softmax shift ----
     // Any mx >= the row's largest score gives the same softmax; it need not be the maximum itself.  The bound
-    // ||q|| max||k|| (in the exp2 domain, mask bias <= 0) costs nothing, and p = exp2(s - mx) keeps its relative
-    // precision however far mx lies above the true maximum -- fp32 and bf16 share their exponent range -- as long as
-    // nothing underflows: with the bound at most 100 (2^-100 is far inside the range) the first pass over the keys,
-    // a quarter of this kernel, is skipped.  Rows of a CTA whose bound is larger take the exact maximum as before.
-    const float mhat = sqrtf(qn2 * kn2) * p.scale_log2 * 1.0001f + 1e-3f;
-    // (a chunk whose every key is masked keeps the exact maximum too: its scores all carry the -1e30 bias and the
-    // softmax over them is uniform, which only the true maximum reproduces)
-    const bool no_key = __syncthreads_or(any_key) == 0;
-    const bool exact_max = __syncthreads_or(mhat > p.shift_limit ? 1 : 0) != 0 || no_key;
-    float mx = exact_max ? -INFINITY : mhat;
-    // ---- pass 1 (only when the bound is not usable): row maximum over all keys, 128 keys at a time ----
-    for (int k0 = 0; exact_max && k0 < T; k0 += 128) {
-        const int n1 = min(128, T - k0);
-        if (warp == 0) {
-            if (elect_one()) {
-                const uint32_t idesc = make_idesc_bf16(128, n1);
-                const uint64_t dk = make_smem_desc_sw64(smem_u32(smem + EB_K_OFF + k0 * 64));
-#pragma unroll
-                for (int kk = 0; kk < EA_DH / 16; kk++) umma_bf16(tmem_base, dq + 2 * kk, dk + 2 * kk, idesc, kk != 0 ? 1u : 0u);
-                umma_commit(&bars[0]);
-            }
-            __syncwarp();
-        }
-        mbar_wait(&bars[0], ph_s);
-        ph_s ^= 1u;
-        tc_fence_after();
-        tmem_ld_32x32(lane_addr, r[0]);
-        for (int c = 0; c < n1; c += 64) {
-            tmem_ld_wait();
-            tmem_ld_32x32(lane_addr + c + 32, r[1]);
-#pragma unroll
-            for (int j = 0; j < 32; j++) mx = fmaxf(mx, fmaf(__uint_as_float(r[0][j]), p.scale_log2, mb[k0 + c + j]));
-            tmem_ld_wait();
-            if (c + 64 < n1) tmem_ld_32x32(lane_addr + c + 64, r[0]);
-#pragma unroll
-            for (int j = 0; j < 32; j++) mx = fmaxf(mx, fmaf(__uint_as_float(r[1][j]), p.scale_log2, mb[k0 + c + 32 + j]));
-        }
-        tc_fence_before();
-        __syncthreads();  // every row has read this piece before the next MMA overwrites the columns
-        tc_fence_after();
-    }
+    // ||q|| max||k|| (in the exp2 domain) costs nothing, and p = exp2(s - mx) keeps its relative precision however
+    // far mx lies above the true maximum -- fp32 and bf16 share their exponent range -- as long as nothing
+    // underflows: |s| <= mx, so with the bound at most 60 every p is >= 2^-120, a normal number in both formats,
+    // and the first pass over the keys, a quarter of this kernel, is skipped.  CTAs with a larger bound take the
+    // exact maximum as before.
+    const float mhat0 = sqrtf(qn2[0] * kn2) * scale * 1.0001f + 1e-3f;
+    const float mhat1 = sqrtf(qn2[1] * kn2) * scale * 1.0001f + 1e-3f;
+    const bool exact_max = __syncthreads_or(fmaxf(mhat0, mhat1) > p.shift_limit ? 1 : 0) != 0 && !no_key;
 
-    // ---- pass 2: per 64-key block, p = exp2(s - max), O += P_j V_j ----
-    float sum = 0.f;
-    const uint32_t idesc_s = make_idesc_bf16(128, 64), idesc_o = make_idesc_bf16(128, EA_DH);
+    const uint32_t idesc_s = make_idesc_bf16(128, 64), idesc_o = make_idesc_bf16(128, EB_ON);
     const int tt = tid >> 1, hf = tid & 1;  // V staging: token of the block, 16-dim half
     unsigned char* Pb = smem + EB_P_OFF;
     unsigned char* Vb = smem + EB_V_OFF;
-    for (int j = 0; j < NB; j++) {
-        if (warp == 0) {
-            if (elect_one()) {
-                const uint64_t dk = make_smem_desc_sw64(smem_u32(smem + EB_K_OFF + j * 64 * 64));
+    auto issue_scores = [&](int mt, int j) {  // warp 0, converged: S_j = Q_mt K_j^T into columns 0..63
+        if (elect_one()) {
+            const uint64_t dq = make_smem_desc_sw64(smem_u32(smem + EB_Q_OFF + mt * 8192));
+            const uint64_t dk = make_smem_desc_sw64(smem_u32(smem + EB_K_OFF + j * 64 * 64));
 #pragma unroll
-                for (int kk = 0; kk < EA_DH / 16; kk++) umma_bf16(tmem_base, dq + 2 * kk, dk + 2 * kk, idesc_s, kk != 0 ? 1u : 0u);
-                umma_commit(&bars[0]);
-            }
-            __syncwarp();
+            for (int kk = 0; kk < EA_DH / 16; kk++) umma_bf16(tmem_base, dq + 2 * kk, dk + 2 * kk, idesc_s, kk != 0 ? 1u : 0u);
+            umma_commit(&bars[0]);
         }
-        // this block's V rows travel to registers while the MMA runs
-        const uint4* vsrc =
-            reinterpret_cast<const uint4*>(p.qkv + (size_t)(row0 + j * 64 + tt) * ld + 2 * p.H + h * EA_DH + hf * 16);
-        uint4 vv[2];
-        vv[0] = __ldg(vsrc);
-        vv[1] = __ldg(vsrc + 1);
-        mbar_wait(&bars[0], ph_s);
-        ph_s ^= 1u;
-        tc_fence_after();
-        tmem_ld_32x32(lane_addr, r[0]);
-        tmem_ld_32x32(lane_addr + 32, r[1]);
-        tmem_ld_wait();
-        // P and V^T of the previous block are free once its P V product has completed
-        if (j > 0) {
-            mbar_wait(&bars[1], ph_o);
-            ph_o ^= 1u;
-        }
-#pragma unroll
-        for (int hh = 0; hh < 2; hh++) {
-            uint32_t pk[16];
-#pragma unroll
-            for (int jj = 0; jj < 16; jj++) {
-                const int c = j * 64 + hh * 32 + 2 * jj;
-                const float p0 = ex2_fast(fmaf(__uint_as_float(r[hh][2 * jj]), p.scale_log2, mb[c]) - mx);
-                const float p1 = ex2_fast(fmaf(__uint_as_float(r[hh][2 * jj + 1]), p.scale_log2, mb[c + 1]) - mx);
-                const __nv_bfloat162 pb = __floats2bfloat162_rn(p0, p1);
-                sum += __bfloat162float(pb.x) + __bfloat162float(pb.y);  // normalise by what is really multiplied
-                pk[jj] = *reinterpret_cast<const uint32_t*>(&pb);
-            }
-#pragma unroll
-            for (int i = 0; i < 4; i++)
-                *reinterpret_cast<uint4*>(Pb + sw128_off(tid, hh * 4 + i)) = make_uint4(pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);
-        }
-        {
-            const unsigned short* ve = reinterpret_cast<const unsigned short*>(vv);
-#pragma unroll
-            for (int e = 0; e < 16; e++)
-                *reinterpret_cast<unsigned short*>(Vb + sw128_off(hf * 16 + e, tt >> 3) + (tt & 7) * 2) = ve[e];
-        }
-        fence_proxy_async_smem();
-        tc_fence_before();
-        __syncthreads();
-        tc_fence_after();
-        if (warp == 0) {
-            if (elect_one()) {
-                const uint64_t dp = make_smem_desc_sw128(smem_u32(Pb));
-                const uint64_t dv = make_smem_desc_sw128(smem_u32(Vb));
-#pragma unroll
-                for (int kk = 0; kk < 4; kk++) umma_bf16(tmem_base + 64, dp + 2 * kk, dv + 2 * kk, idesc_o, (j | kk) != 0 ? 1u : 0u);
-                umma_commit(&bars[1]);
-            }
-            __syncwarp();
-        }
-    }
-    mbar_wait(&bars[1], ph_o);
-    tc_fence_after();
+        __syncwarp();
+    };
+    const int j_first = __ffs(act) - 1;
+    if (!exact_max && warp == 0) issue_scores(0, j_first);
+    EB_MARK(5);
 
-    // ---- normalise and store ----
-    tmem_ld_32x32(lane_addr + 64, r[0]);
-    tmem_ld_wait();
-    const int q = mt * 128 + tid;
-    if (q < T) {
-        const float inv = 1.0f / sum;
-        uint32_t o[16];
+    for (int mt = 0; mt < QT; mt++) {
+        float mx = exact_max ? -INFINITY : (mt == 0 ? mhat0 : mhat1);
+        // ---- pass 1 (only when the bound is not usable): row maximum over the kept keys, 128 keys at a time ----
+        for (int k0 = 0; exact_max && k0 < T; k0 += 128) {
+            const int n1 = min(128, T - k0);
+            if (warp == 0) {
+                if (elect_one()) {
+                    const uint32_t idesc = make_idesc_bf16(128, n1);
+                    const uint64_t dq = make_smem_desc_sw64(smem_u32(smem + EB_Q_OFF + mt * 8192));
+                    const uint64_t dk = make_smem_desc_sw64(smem_u32(smem + EB_K_OFF + k0 * 64));
 #pragma unroll
-        for (int jj = 0; jj < 16; jj++) {
-            const __nv_bfloat162 ob =
-                __floats2bfloat162_rn(__uint_as_float(r[0][2 * jj]) * inv, __uint_as_float(r[0][2 * jj + 1]) * inv);
-            o[jj] = *reinterpret_cast<const uint32_t*>(&ob);
+                    for (int kk = 0; kk < EA_DH / 16; kk++) umma_bf16(tmem_base, dq + 2 * kk, dk + 2 * kk, idesc, kk != 0 ? 1u : 0u);
+                    umma_commit(&bars[0]);
+                }
+                __syncwarp();
+            }
+            mbar_wait(&bars[0], ph_s);
+            ph_s ^= 1u;
+            tc_fence_after();
+            for (int c = 0; c < n1; c += 32) {
+                tmem_ld_32x32(lane_addr + c, r[0]);
+                tmem_ld_wait();
+                const uint32_t w = keep_s[(k0 + c) >> 5];
+#pragma unroll
+                for (int j = 0; j < 32; j++)
+                    if ((w >> j) & 1u) mx = fmaxf(mx, __uint_as_float(r[0][j]) * scale);
+            }
+            tc_fence_before();
+            __syncthreads();  // every row has read this piece before the next MMA overwrites the columns
+            tc_fence_after();
         }
-        uint4* dst = reinterpret_cast<uint4*>(p.ctx + (size_t)(row0 + q) * p.H + h * EA_DH);
+        if (exact_max && warp == 0) issue_scores(mt, j_first);
+
+        // ---- pass 2: per 64-key block, p = exp2(s - max), O += P_j V_j ----
+        const float neg_mx = -mx;
+        bool first = true;
+        int ev = 8 + mt * 32;
+        for (int j = 0; j < NB; j++) {
+            if (!((act >> j) & 1u)) continue;
+            EB_MARK(ev + 0);
+            // this block's V rows travel to registers while the MMA runs
+            const uint4* vsrc =
+                reinterpret_cast<const uint4*>(p.qkv + (size_t)(row0 + j * 64 + tt) * ld + 2 * p.H + h * EA_DH + hf * 16);
+            uint4 vv[2];
+            vv[0] = __ldg(vsrc);
+            vv[1] = __ldg(vsrc + 1);
+            mbar_wait(&bars[0], ph_s);
+            ph_s ^= 1u;
+            tc_fence_after();
+            EB_MARK(ev + 1);
+            tmem_ld_32x32(lane_addr, r[0]);
+            tmem_ld_32x32(lane_addr + 32, r[1]);
+            tmem_ld_wait();
+            EB_MARK(ev + 2);
+            // P and V^T of the previous block are free once its P V product has completed (a new tile starts after
+            // the previous tile's last product has been waited for)
+            if (!first) {
+                mbar_wait(&bars[1], ph_o);
+                ph_o ^= 1u;
+            }
+            EB_MARK(ev + 3);
+            const bool unmasked = (full >> j) & 1u;
 #pragma unroll
-        for (int i = 0; i < 4; i++) dst[i] = make_uint4(o[4 * i], o[4 * i + 1], o[4 * i + 2], o[4 * i + 3]);
-    }
-    tc_fence_before();
-    __syncthreads();
-    if (warp == 0) {
+            for (int hh = 0; hh < 2; hh++) {
+                uint32_t pk[16];
+                if (unmasked) {
+#pragma unroll
+                    for (int jj = 0; jj < 16; jj++) {
+                        const float p0 = ex2_fast(fmaf(__uint_as_float(r[hh][2 * jj]), scale, neg_mx));
+                        const float p1 = ex2_fast(fmaf(__uint_as_float(r[hh][2 * jj + 1]), scale, neg_mx));
+                        pk[jj] = pack_bf16x2_rn(p0, p1);
+                    }
+                } else {
+                    const uint32_t w = keep_s[2 * j + hh];
+#pragma unroll
+                    for (int jj = 0; jj < 16; jj++) {
+                        const float p0 = (w >> (2 * jj)) & 1u ? ex2_fast(fmaf(__uint_as_float(r[hh][2 * jj]), scale, neg_mx)) : 0.f;
+                        const float p1 = (w >> (2 * jj + 1)) & 1u ? ex2_fast(fmaf(__uint_as_float(r[hh][2 * jj + 1]), scale, neg_mx)) : 0.f;
+                        pk[jj] = pack_bf16x2_rn(p0, p1);
+                    }
+                }
+#pragma unroll
+                for (int i = 0; i < 4; i++)
+                    *reinterpret_cast<uint4*>(Pb + sw128_off(tid, hh * 4 + i)) = make_uint4(pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);
+            }
+            EB_MARK(ev + 4);
+            {
+                const unsigned short* ve = reinterpret_cast<const unsigned short*>(vv);
+#pragma unroll
+                for (int e = 0; e < 16; e++)
+                    *reinterpret_cast<unsigned short*>(Vb + sw128_off(hf * 16 + e, tt >> 3) + (tt & 7) * 2) = ve[e];
+            }
+            EB_MARK(ev + 5);
+            fence_proxy_async_smem();
+            tc_fence_before();
+            __syncthreads();  // every row has its scores in registers and P_j, V_j^T in shared memory
+            tc_fence_after();
+            EB_MARK(ev + 6);
+            if (warp == 0) {
+                // the next scores first (the threads wait for them next): the next block of this tile, or the first
+                // block of the next tile when its shift needs no pass 1
+                const uint32_t rest = act >> (j + 1);
+                if (rest) issue_scores(mt, j + __ffs(rest));
+                else if (!exact_max && mt + 1 < QT) issue_scores(mt + 1, j_first);
+                if (elect_one()) {
+                    const uint64_t dp = make_smem_desc_sw128(smem_u32(Pb));
+                    const uint64_t dv = make_smem_desc_sw128(smem_u32(Vb));
+#pragma unroll
+                    for (int kk = 0; kk < 4; kk++)
+                        umma_bf16(tmem_base + 64, dp + 2 * kk, dv + 2 * kk, idesc_o, (!first || kk != 0) ? 1u : 0u);
+                    umma_commit(&bars[1]);
+                }
+                __syncwarp();
+            }
+            first = false;
+            ev += 7;
+        }
+        EB_MARK(ev);
+        mbar_wait(&bars[1], ph_o);
+        ph_o ^= 1u;
         tc_fence_after();
-        tmem_dealloc<128>(tmem_base);
+        EB_MARK(ev + 1);
+
+        // ---- normalise and store: columns 64..95 = O, column 96 = the row sum ----
+        uint32_t rs[16];
+        tmem_ld_32x32(lane_addr + 64, r[0]);
+        tmem_ld_32x16(lane_addr + 96, rs);
+        tmem_ld_wait();
+        const int q = mt * 128 + tid;
+        if (q < T) {
+            const float inv = 1.0f / __uint_as_float(rs[0]);
+            uint32_t o[16];
+#pragma unroll
+            for (int jj = 0; jj < 16; jj++)
+                o[jj] = pack_bf16x2_rn(__uint_as_float(r[0][2 * jj]) * inv, __uint_as_float(r[0][2 * jj + 1]) * inv);
+            uint4* dst = reinterpret_cast<uint4*>(p.ctx + (size_t)(row0 + q) * p.H + h * EA_DH);
+#pragma unroll
+            for (int i = 0; i < 4; i++) dst[i] = make_uint4(o[4 * i], o[4 * i + 1], o[4 * i + 2], o[4 * i + 3]);
+        }
+        tc_fence_before();
+        __syncthreads();  // O has been read by every row before the next tile's first product overwrites it
+        tc_fence_after();
+        EB_MARK(ev + 2);
     }
+    if (warp == 0) tmem_dealloc<128>(tmem_base);
+    EB_MARK(7);
 }
 
 
@@ -518,10 +606,33 @@ int launch_enc_attention(const __nv_bfloat16* qkv, const float* mask_bias, __nv_
         const char* e = getenv("BFK_ENC_SHIFT");
         return e && e[0] == 'e';
     }();
-    p.shift_limit = exact_shift ? 0.f : 100.f;
-    dim3 grid((unsigned)((T + 127) / 128), (unsigned)heads, (unsigned)B);
-    if (whole_row) enc_attention_kernel<<<grid, EA_THREADS, EA_SMEM, st>>>(p);
-    else enc_attention_blk_kernel<<<grid, EB_THREADS, EB_SMEM, st>>>(p);
+    p.shift_limit = exact_shift ? 0.f : 60.f;
+    p.trace = nullptr;
+    static const bool trace_on = getenv("BFK_ENC_ATTN_TRACE") != nullptr;
+    if (trace_on && !whole_row) {  // debugging: synchronous, one CTA's phase timeline on stderr
+        unsigned long long* d = nullptr;
+        BFK_CUDA(cudaMalloc((void**)&d, 128 * 8));
+        BFK_CUDA(cudaMemset(d, 0, 128 * 8));
+        p.trace = d;
+        dim3 grid((unsigned)heads, (unsigned)B);
+        enc_attention_blk_kernel<<<grid, EB_THREADS, EB_SMEM, st>>>(p);
+        BFK_CUDA(cudaStreamSynchronize(st));
+        unsigned long long hst[128];
+        BFK_CUDA(cudaMemcpy(hst, d, sizeof(hst), cudaMemcpyDeviceToHost));
+        cudaFree(d);
+        fprintf(stderr, "[bfk attn trace] B=%lld T=%d:", (long long)B, T);
+        for (int i = 1; i < 128; i++)
+            if (hst[i]) fprintf(stderr, " %d:%lld", i, (long long)(hst[i] - hst[0]));
+        fprintf(stderr, "\n");
+        return 0;
+    }
+    if (whole_row) {
+        dim3 grid((unsigned)((T + 127) / 128), (unsigned)heads, (unsigned)B);
+        enc_attention_kernel<<<grid, EA_THREADS, EA_SMEM, st>>>(p);
+    } else {
+        dim3 grid((unsigned)heads, (unsigned)B);  // one CTA per (head, chunk): K is staged once for its query tiles
+        enc_attention_blk_kernel<<<grid, EB_THREADS, EB_SMEM, st>>>(p);
+    }
     BFK_CUDA(cudaGetLastError());
     return 0;
 }

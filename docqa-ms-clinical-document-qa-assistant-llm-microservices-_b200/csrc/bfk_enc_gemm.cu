@@ -39,14 +39,16 @@ constexpr int EG_A_BYTES = EG_BM * EG_BK * 2;         // 16 KiB
 constexpr int EG_TAIL = 256 /*barriers*/ + 2 * 2 * 128 * 8 /*LayerNorm partial sums, double-buffered*/ +
                         8 * 2048 /*per-warp load/store staging*/ + 3 * 384 * 4 /*bias, gamma, beta of a 384-wide tile*/;
 
-template <int BN>
+template <int BN, bool PAIR>
 struct EgShape {
-    static constexpr int BNB = BN == 384 ? 128 : BN;   // N of one tcgen05.mma
+    static constexpr int BNB = PAIR ? 192 : (BN == 384 ? 128 : BN);  // N of one tcgen05.mma
     static constexpr int NBLK = BN / BNB;
     static constexpr int NACC = BN == 192 ? 2 : 1;     // accumulators (256 TMEM columns apart)
-    static constexpr int B_BYTES = BN * EG_BK * 2;
+    static constexpr int B_ROWS = PAIR ? BNB / 2 : BNB;  // rows of a W block this CTA stages (a pair splits them)
+    static constexpr int B_BLOCK = B_ROWS * EG_BK * 2;
+    static constexpr int B_BYTES = NBLK * B_BLOCK;
     static constexpr int STAGE = EG_A_BYTES + B_BYTES;
-    static constexpr int STAGES = BN == 192 ? 5 : 3;
+    static constexpr int STAGES = PAIR ? (BN == 192 ? 7 : 5) : (BN == 192 ? 5 : 3);
     static constexpr int SMEM = STAGES * STAGE + 1024 /*alignment*/ + EG_TAIL;
 };
 
@@ -98,10 +100,11 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
 
 __device__ __forceinline__ void eg_epi_sync() { asm volatile("bar.sync 3, 256;" ::: "memory"); }
 
-template <int EPI, int BN>
+template <int EPI, int BN, bool PAIR>
 __global__ void __launch_bounds__(EG_THREADS, 1)
 enc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW, const EncGemmParams p) {
-    using S = EgShape<BN>;
+    using S = EgShape<BN, PAIR>;
+    constexpr uint32_t CS = PAIR ? 2u : 1u;  // CTAs per tile group
     constexpr int STAGES = S::STAGES, STAGE = S::STAGE, NACC = S::NACC;
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     const uint32_t raw = smem_u32(smem_raw);
@@ -121,17 +124,21 @@ enc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int KB = p.K / EG_BK;
     const int n_tiles = p.N / BN;
-    const int m_tiles = (p.M + EG_BM - 1) / EG_BM;
+    // a pair works on 256 rows at a time: CTA rank r owns rows [256 g + 128 r, + 128) of group g
+    const int m_tiles = (p.M + (int)CS * EG_BM - 1) / ((int)CS * EG_BM);
     const int tiles = m_tiles * n_tiles;
+    const int first_tile = blockIdx.x / CS, tile_step = gridDim.x / CS;
 
     if (tid == 0) {
+        // pair: the leader's full / tempty barriers collect both CTAs; empty / tfull exist per CTA and are
+        // signalled together by the leader's multicast commits
         for (int i = 0; i < STAGES; i++) {
-            mbar_init(&full_bar[i], 1);
+            mbar_init(&full_bar[i], CS);
             mbar_init(&empty_bar[i], 1);
         }
         for (int a = 0; a < 2; a++) {
             mbar_init(&tfull_bar[a], 1);
-            mbar_init(&tempty_bar[a], EG_EPI_THREADS);
+            mbar_init(&tempty_bar[a], EG_EPI_THREADS * CS);
         }
         fence_mbar_init();
     }
@@ -147,31 +154,51 @@ enc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
             par_s[2 * BN + i] = p.beta[i];
         }
     }
-    if (warp == 2) tmem_alloc<512>(tmem_slot);
+    if (warp == 2) {
+        if constexpr (PAIR) tmem_alloc2<512>(tmem_slot);
+        else tmem_alloc<512>(tmem_slot);
+    }
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmA);
         tma_prefetch_desc(&tmW);
     }
     tc_fence_before();
     __syncthreads();
+    if constexpr (PAIR) cluster_sync_all();  // the peer's barriers are initialised before anyone signals them
     tc_fence_after();
     const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(tmem_slot);
+    uint32_t crank = 0u;
+    if constexpr (PAIR) crank = cluster_ctarank();
+    const bool leader = crank == 0;
 
     if (warp == 0) {
         // ===================== TMA producer =====================
         if (lane == 0) {
             uint32_t st = 0, ph = 0;
-            for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
-                const int mt = tile / n_tiles, nt = tile - mt * n_tiles;
+            for (int tile = first_tile; tile < tiles; tile += tile_step) {
+                const int mg = tile / n_tiles, nt = tile - mg * n_tiles;
+                const int mt = mg * (int)CS + (int)crank;
                 for (int kb = 0; kb < KB; kb++) {
                     mbar_wait(&empty_bar[st], ph ^ 1u);
                     unsigned char* stage = ring + (size_t)st * STAGE;
-                    mbar_expect_tx(&full_bar[st], (uint32_t)STAGE);
-                    tma_load_2d(stage, &tmA, kb * EG_BK, mt * EG_BM, &full_bar[st]);
+                    if constexpr (!PAIR) {
+                        mbar_expect_tx(&full_bar[st], (uint32_t)STAGE);
+                        tma_load_2d(stage, &tmA, kb * EG_BK, mt * EG_BM, &full_bar[st]);
 #pragma unroll
-                    for (int nb = 0; nb < S::NBLK; nb++)
-                        tma_load_2d(stage + EG_A_BYTES + nb * (S::BNB * EG_BK * 2), &tmW, kb * EG_BK,
-                                    nt * BN + nb * S::BNB, &full_bar[st]);
+                        for (int nb = 0; nb < S::NBLK; nb++)
+                            tma_load_2d(stage + EG_A_BYTES + nb * S::B_BLOCK, &tmW, kb * EG_BK, nt * BN + nb * S::BNB,
+                                        &full_bar[st]);
+                    } else {
+                        // each CTA stages its own 128 rows of A and its half of every W block in its own shared
+                        // memory (the 256 x 192 MMA reads both halves); all bytes are accounted on the leader's barrier
+                        if (leader) mbar_expect_tx(&full_bar[st], 2u * (uint32_t)STAGE);
+                        tma_load_2d_2sm(stage, &tmA, kb * EG_BK, mt * EG_BM, &full_bar[st]);
+#pragma unroll
+                        for (int nb = 0; nb < S::NBLK; nb++)
+                            tma_load_2d_2sm(stage + EG_A_BYTES + nb * S::B_BLOCK, &tmW, kb * EG_BK,
+                                            nt * BN + nb * S::BNB + (int)crank * S::B_ROWS, &full_bar[st]);
+                        if (!leader) mbar_arrive_remote(&full_bar[st], 0);
+                    }
                     if (++st == STAGES) {
                         st = 0;
                         ph ^= 1u;
@@ -179,17 +206,17 @@ enc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                 }
             }
         }
-    } else if (warp == 1) {
-        // ===================== MMA issuer (converged warp, one elected lane) =====================
-        const uint32_t idesc = make_idesc_bf16(EG_BM, S::BNB);
+    } else if (warp == 1 && leader) {
+        // ===================== MMA issuer (converged warp, one elected lane; the pair's leader only) =====================
+        const uint32_t idesc = make_idesc_bf16((int)CS * EG_BM, S::BNB);
         const uint64_t desc_hi = make_smem_desc_sw128(0) & 0xffffffff00000000ull;
         const uint32_t desc_lo0 = (uint32_t)(make_smem_desc_sw128(0) & 0xffffffffull);
         const uint32_t ring_lo = desc_lo0 + ((smem_u32(ring) & 0x3ffffu) >> 4);
         uint32_t st = 0, ph = 0, tcount = 0;
-        for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x, tcount++) {
+        for (int tile = first_tile; tile < tiles; tile += tile_step, tcount++) {
             const uint32_t a = NACC == 2 ? (tcount & 1u) : 0u;
             const uint32_t aph = NACC == 2 ? ((tcount >> 1) & 1u) : (tcount & 1u);
-            mbar_wait(&tempty_bar[a], aph ^ 1u);  // the epilogue has drained this accumulator
+            mbar_wait(&tempty_bar[a], aph ^ 1u);  // the epilogue (of both CTAs) has drained this accumulator
             tc_fence_after();
             const uint32_t d_tmem = tmem_base + a * 256;
             for (int kb = 0; kb < KB; kb++) {
@@ -203,11 +230,13 @@ enc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                         const uint64_t da = desc_hi | (uint64_t)(a_lo + 2 * kk);
 #pragma unroll
                         for (int nb = 0; nb < S::NBLK; nb++) {
-                            const uint64_t db = desc_hi | (uint64_t)(b_lo + nb * ((S::BNB * EG_BK * 2) >> 4) + 2 * kk);
-                            umma_bf16(d_tmem + nb * S::BNB, da, db, idesc, (kb | kk) != 0 ? 1u : 0u);
+                            const uint64_t db = desc_hi | (uint64_t)(b_lo + nb * (S::B_BLOCK >> 4) + 2 * kk);
+                            if constexpr (PAIR) umma_bf16_2sm(d_tmem + nb * S::BNB, da, db, idesc, (kb | kk) != 0 ? 1u : 0u);
+                            else umma_bf16(d_tmem + nb * S::BNB, da, db, idesc, (kb | kk) != 0 ? 1u : 0u);
                         }
                     }
-                    umma_commit(&empty_bar[st]);
+                    if constexpr (PAIR) umma_commit_2sm(&empty_bar[st]);  // frees the stage in both CTAs
+                    else umma_commit(&empty_bar[st]);
                 }
                 __syncwarp();
                 if (++st == STAGES) {
@@ -215,7 +244,10 @@ enc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                     ph ^= 1u;
                 }
             }
-            if (elect_one()) umma_commit(&tfull_bar[a]);
+            if (elect_one()) {
+                if constexpr (PAIR) umma_commit_2sm(&tfull_bar[a]);  // accumulator complete, in both CTAs
+                else umma_commit(&tfull_bar[a]);
+            }
             __syncwarp();
         }
     } else if (warp >= 4) {
@@ -270,8 +302,9 @@ enc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
             __syncwarp();
         };
         uint32_t tcount = 0;
-        for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x, tcount++) {
-            const int mt = tile / n_tiles, nt = tile - mt * n_tiles;
+        for (int tile = first_tile; tile < tiles; tile += tile_step, tcount++) {
+            const int mg = tile / n_tiles, nt = tile - mg * n_tiles;
+            const int mt = mg * (int)CS + (int)crank;
             const int n0 = nt * BN + half * HC;  // first global column of this thread
             const uint32_t a = NACC == 2 ? (tcount & 1u) : 0u;
             const uint32_t aph = NACC == 2 ? ((tcount >> 1) & 1u) : (tcount & 1u);
@@ -378,34 +411,58 @@ enc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                 }
             }
             tc_fence_before();
-            mbar_arrive(&tempty_bar[a]);
+            if (leader) mbar_arrive(&tempty_bar[a]);
+            else mbar_arrive_remote(&tempty_bar[a], 0);  // the MMA issuer lives in the leader CTA
         }
     }
 
     tc_fence_before();
     __syncthreads();
+    if constexpr (PAIR) cluster_sync_all();  // nobody leaves while the peer may still signal its barriers
     if (warp == 2) {
         tc_fence_after();
-        tmem_dealloc<512>(tmem_base);
+        if constexpr (PAIR) tmem_dealloc2<512>(tmem_base);
+        else tmem_dealloc<512>(tmem_base);
     }
 }
 
-template <int EPI, int BN>
+template <int EPI, int BN, bool PAIR>
 static int launch_enc_gemm_t(const CUtensorMap& tmA, const CUtensorMap& tmW, const EncGemmParams& p, int num_sms,
                              cudaStream_t st) {
-    auto kern = enc_gemm_kernel<EPI, BN>;
+    auto kern = enc_gemm_kernel<EPI, BN, PAIR>;
+    using S = EgShape<BN, PAIR>;
     static bool attr_set[64] = {false};
     int dev = 0;
     BFK_CUDA(cudaGetDevice(&dev));
     if (dev < 0 || dev >= 64 || !attr_set[dev]) {
-        BFK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, EgShape<BN>::SMEM));
+        BFK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::SMEM));
         if (dev >= 0 && dev < 64) attr_set[dev] = true;
     }
-    const int tiles = ((p.M + EG_BM - 1) / EG_BM) * (p.N / BN);
-    const int grid = std::max(1, std::min(tiles, num_sms));
-    kern<<<grid, EG_THREADS, EgShape<BN>::SMEM, st>>>(tmA, tmW, p);
+    constexpr int CS = PAIR ? 2 : 1;
+    const int tiles = ((p.M + CS * EG_BM - 1) / (CS * EG_BM)) * (p.N / BN);
+    const int grid = CS * std::max(1, std::min(tiles, num_sms / CS));
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)grid);
+    cfg.blockDim = dim3(EG_THREADS);
+    cfg.dynamicSmemBytes = S::SMEM;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = (unsigned)CS;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    BFK_CUDA(cudaLaunchKernelEx(&cfg, kern, tmA, tmW, p));
     BFK_CUDA(cudaGetLastError());
     return 0;
+}
+
+template <int EPI, int BN>
+static int launch_enc_gemm_p(bool pair, const CUtensorMap& tmA, const CUtensorMap& tmW, const EncGemmParams& p, int num_sms,
+                             cudaStream_t st) {
+    return pair ? launch_enc_gemm_t<EPI, BN, true>(tmA, tmW, p, num_sms, st)
+                : launch_enc_gemm_t<EPI, BN, false>(tmA, tmW, p, num_sms, st);
 }
 
 // A [M, K] bf16 (ld = K), W [N, K] bf16 (ld = K); out [M, ldo] bf16
@@ -416,9 +473,18 @@ int launch_enc_gemm(int epi, const __nv_bfloat16* A, const __nv_bfloat16* W, int
     if (N % 192 != 0 || K % EG_BK != 0) return fail("encoder gemm: N must be a multiple of 192 and K of 64");
     if (N > 2176) return fail("encoder gemm: N > 2176 does not fit the on-chip bias vector");
     if (epi == EPI_RES_LN && N != 384) return fail("encoder gemm: the LayerNorm epilogue needs N == 384");
+    // CTA pairs (cta_group::2, a 256-row tile group whose W blocks are split between the two CTAs) once there are
+    // at least two 128-row tiles: a lone CTA re-reads 128 x 64 of A and BN x 64 of W per 128 x BN x 64 of MMA work
+    // and all four layer shapes ran at the L2 slices' throughput limit, not the tensor pipe's.
+    // BFK_ENC_PAIR=0 keeps single CTAs.
+    static const bool pair_on = [] {
+        const char* e = getenv("BFK_ENC_PAIR");
+        return e ? atoi(e) != 0 : true;
+    }();
+    const bool pair = pair_on && M > EG_BM;
     CUtensorMap tmA, tmW;
     BFK_TRY(make_tmap(&tmA, A, M, K, EG_BM));
-    BFK_TRY(make_tmap(&tmW, W, N, K, epi == EPI_RES_LN ? 128 : 192));
+    BFK_TRY(make_tmap(&tmW, W, N, K, pair ? 96 : (epi == EPI_RES_LN ? 128 : 192)));
     EncGemmParams p;
     p.M = M;
     p.N = N;
@@ -431,16 +497,16 @@ int launch_enc_gemm(int epi, const __nv_bfloat16* A, const __nv_bfloat16* W, int
     p.out = out;
     p.ldo = ldo;
     switch (epi) {
-        case EPI_BIAS: return launch_enc_gemm_t<EPI_BIAS, 192>(tmA, tmW, p, num_sms, st);
+        case EPI_BIAS: return launch_enc_gemm_p<EPI_BIAS, 192>(pair, tmA, tmW, p, num_sms, st);
         case EPI_GELU: {
             static const bool erf = [] {
                 const char* e = getenv("BFK_ENC_GELU");
                 return e && e[0] == 'e';
             }();
-            return erf ? launch_enc_gemm_t<EPI_GELU_ERF, 192>(tmA, tmW, p, num_sms, st)
-                       : launch_enc_gemm_t<EPI_GELU, 192>(tmA, tmW, p, num_sms, st);
+            return erf ? launch_enc_gemm_p<EPI_GELU_ERF, 192>(pair, tmA, tmW, p, num_sms, st)
+                       : launch_enc_gemm_p<EPI_GELU, 192>(pair, tmA, tmW, p, num_sms, st);
         }
-        case EPI_RES_LN: return launch_enc_gemm_t<EPI_RES_LN, 384>(tmA, tmW, p, num_sms, st);
+        case EPI_RES_LN: return launch_enc_gemm_p<EPI_RES_LN, 384>(pair, tmA, tmW, p, num_sms, st);
         default: return fail("encoder gemm: unknown epilogue");
     }
 }

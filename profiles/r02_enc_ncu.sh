@@ -1,0 +1,14 @@
+#!/bin/bash
+# ncu --set full of the encoder's kernels as launched for a 512-chunk x 256-token micro-batch
+cd "$(dirname "$0")/.." && mkdir -p gpurun_out
+NCU="ncu --set full --clock-control none --import-source on"
+for k in ${KERNELS:-attn gelu ln qkv}; do
+  case $k in
+    attn) kern=enc_attention_blk_kernel; skip=7;;
+    gelu) kern='enc_gemm_kernel<1'; skip=7;;
+    ln) kern='enc_gemm_kernel<2'; skip=15;;   # odd index = the K=1536 layer
+    qkv) kern='enc_gemm_kernel<0'; skip=7;;
+  esac
+  timeout 600 $NCU -k "regex:$kern" -s $skip -c 1 -f -o gpurun_out/r02_ncu_enc_$k python profiles/enc_probe.py 512 256 > gpurun_out/r02_ncu_enc_$k.log 2>&1 || tail -5 gpurun_out/r02_ncu_enc_$k.log
+done
+ls -la gpurun_out/r02_ncu_enc_*.ncu-rep

@@ -49,6 +49,30 @@ def test_last_hidden_state_matches_bert(bfk, layers, B, T):
     assert np.abs(orc - want)[valid].max() < 1e-3
 
 
+def test_attention_masks_with_holes_and_empty_blocks(bfk):
+    """Masks that are not prefixes: scattered holes (64-key blocks with some keys masked), a chunk whose middle 64-key
+    blocks are masked entirely (the kernel skips them) and one whose first block is (the product then starts at a
+    later block).  Compared with BertModel on the tokens the mask keeps."""
+    import torch
+
+    m = hf_model(layers=2, vocab=400)
+    enc = bfk.MiniLMEncoder.from_hf_model(m)
+    ids, mask = inputs(5, 256, 400)
+    rng = np.random.default_rng(11)
+    mask[:] = 1
+    mask[1] = rng.random(256) > 0.3
+    mask[2, 64:192] = 0
+    mask[3, :64] = 0
+    mask[4, :200] = 0
+    mask[4, 230:] = 0
+    with torch.no_grad():
+        want = m(input_ids=torch.from_numpy(ids), attention_mask=torch.from_numpy(mask)).last_hidden_state.numpy()
+    got = enc.forward(torch.from_numpy(ids).cuda(), torch.from_numpy(mask).cuda()).float().cpu().numpy()
+    assert np.isfinite(got).all()
+    err = np.abs(got - want)[mask.astype(bool)]
+    assert err.max() <= 0.07 and err.mean() <= 0.008, (err.max(), err.mean())
+
+
 def test_embeddings_and_fused_add(bfk):
     import torch
 
@@ -187,7 +211,7 @@ def test_query_side_replaces_newlines_like_huggingface_embeddings(bfk):
 
 def test_attention_softmax_shift_routes():
     """The attention kernel shifts the softmax by the bound ||q|| max||k|| and only computes the true row maximum when
-    that bound is too large (> 100 in the exp2 domain; BFK_ENC_SHIFT=exact forces it) or when every key of the chunk
+    that bound is too large (> 60 in the exp2 domain; BFK_ENC_SHIFT=exact forces it) or when every key of the chunk
     is masked.  Both settings must meet the encoder's bar against BertModel and agree with each other; a chunk with an
     all-zero attention mask stays finite (its token states are never pooled: the mask that hides them is the pooling mask)."""
     import os
