@@ -18,6 +18,7 @@
 
 #include "bfk_common.cuh"
 #include "bfk_ptx.cuh"
+#include "bfk_tmap.cuh"
 
 namespace bfk {
 
@@ -577,6 +578,366 @@ __global__ void __launch_bounds__(EB_THREADS, 4) enc_attention_blk_kernel(const 
 }
 
 
+// ---- E3c: warp-specialised attention ---------------------------------------------------------------------
+// The timeline of one enc_attention_blk_kernel CTA (BFK_ENC_ATTN_TRACE) showed 4.4 k cycles per 64-key block of
+// which the 64 exponentials are 1.1-2.5 k: the rest is the row threads themselves waiting for the scores, issuing
+// the MMAs (~1 k cycles in warp 0), staging V^T with 2-byte stores and meeting at a CTA-wide barrier.  Here the
+// row threads only do: scores from TMEM -> exp2 -> P into shared memory.  One CTA per (head, chunk), 10 warps:
+//   warps 0-3 / 4-7  softmax group A / B: the chunk's first / second 128-query tile, thread == row == TMEM lane
+//   warp 8           issues every MMA (scores of the next block as soon as a group has read the current ones)
+//   warp 9           stages V: 64-token blocks in their natural [token][32 dims] layout, double-buffered -- the
+//                    P V product reads V as an MN-major operand, so nothing is transposed
+// and mbarriers between them instead of CTA-wide barriers:
+//   s_full[g]   scores of the group's next block are in TMEM            (tcgen05.commit)
+//   s_free[g]   the group's 128 threads hold them in registers          -> the next scores may be issued
+//   p_full[g]   the group's P block is in shared memory                 -> P V and the row sums may be issued
+//   pv_done[g]  that product has completed                              (tcgen05.commit) -> P may be overwritten
+//   v_full[s] / v_free[s]  V slot s staged / consumed by the products of both groups
+// TMEM: 256 columns (per group: scores 0..63, O 64..95, row sums 96..111), 75 KB of shared memory: two CTAs,
+// i.e. four query tiles, per SM as before.  The row sums are a second small product P x ones (N = 16).
+constexpr int EW_THREADS = 320;
+constexpr int EW_Q_OFF = 0;                 // [2 tiles][128 x 64 B]       16 KiB, 64-byte swizzle
+constexpr int EW_K_OFF = 16 * 1024;         // [T x 64 B]               <= 16 KiB, 64-byte swizzle
+constexpr int EW_V_OFF = 32 * 1024;         // [2 slots][64 tokens x 64 B]  8 KiB, 64-byte swizzle
+constexpr int EW_P_OFF = 40 * 1024;         // [2 groups][128 x 128 B]     32 KiB, 128-byte swizzle
+constexpr int EW_ONE_OFF = 72 * 1024;       // [16 rows x 128 B]            2 KiB: row 0 = ones
+constexpr int EW_BAR_OFF = 74 * 1024;
+constexpr int EW_SMEM = EW_BAR_OFF + 256 + 1024 /*alignment*/;
+enum { EW_S_FULL = 0, EW_S_FREE = 2, EW_P_FULL = 4, EW_PV_DONE = 6, EW_V_FULL = 8, EW_V_FREE = 10, EW_P1 = 12, EW_KQ = 13, EW_NBAR = 14 };
+
+// 2^x for x <= 0 on the FMA pipe: round x to n + f with |f| <= 1/2 (magic-number rounding), a cubic for 2^f
+// (relative error 1e-4, a bf16 result keeps 2^-9) and n added to the exponent field
+__device__ __forceinline__ float ex2_poly(float x) {
+    x = fmaxf(x, -125.f);
+    const float t = x + 12582912.f;
+    const float f = x - (t - 12582912.f);
+    float y = fmaf(0.0555041087f, f, 0.2402265069f);
+    y = fmaf(y, f, 0.6931471806f);
+    y = fmaf(y, f, 1.0f);
+    return __int_as_float(__float_as_int(y) + (__float_as_int(t) << 23));
+}
+
+// XM: how the exponentials are computed: 0 = all on the SFU (MUFU.EX2), 1 = none at all (timing experiment, wrong
+// results), n >= 2 = one of every n on the FMA pipe (ex2_poly)
+template <int XM>
+__global__ void __launch_bounds__(EW_THREADS, 2)
+enc_attention_ws_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmCTX, const EncAttnParams p) {
+    extern __shared__ __align__(1024) unsigned char smem_raw[];
+    const uint32_t raw = smem_u32(smem_raw);
+    unsigned char* smem = smem_raw + ((1024u - (raw & 1023u)) & 1023u);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + EW_BAR_OFF);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + EW_NBAR + 1);
+    float* kmax_s = reinterpret_cast<float*>(tmem_slot + 2);  // [8] one per warp
+    uint32_t* keep_s = tmem_slot + 12;                        // [8] bit t%32 of word t/32: key t is not masked
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int h = blockIdx.x;
+    const int64_t b = blockIdx.y;
+    const int T = p.T, NB = T >> 6, QT = (T + 127) >> 7;
+    const int64_t row0 = b * T;
+
+    if (tid == 0) {
+        for (int g = 0; g < 2; g++) {
+            mbar_init(&bars[EW_S_FULL + g], 1);
+            mbar_init(&bars[EW_S_FREE + g], 128);
+            mbar_init(&bars[EW_P_FULL + g], 128);
+            mbar_init(&bars[EW_PV_DONE + g], 1);
+            mbar_init(&bars[EW_V_FULL + g], 1);
+            mbar_init(&bars[EW_V_FREE + g], 1);
+        }
+        mbar_init(&bars[EW_P1], 1);
+        mbar_init(&bars[EW_KQ], 1);
+        fence_mbar_init();
+    }
+    if (warp == 8) tmem_alloc<256>(tmem_slot);
+    if (warp == 9 && lane == 0) {
+        tma_prefetch_desc(&tmQKV);
+        tma_prefetch_desc(&tmCTX);
+    }
+    __syncthreads();
+
+    // ---- stage Q and K of the head: 64-row boxes of 64 bytes through TMA (the 64-byte swizzle is the layout the
+    //      MMA descriptors expect).  Thread-per-row loads of 64-byte rows 2304 bytes apart cost 32 LSU wavefronts
+    //      per instruction, and ncu showed the LSU data pipe -- not the SFU, not the tensor pipe -- as this
+    //      kernel's busiest unit (58 % of peak over the whole kernel) ----
+    if (warp == 9) {
+        if (lane == 0) {
+            mbar_expect_tx(&bars[EW_KQ], 2u * (uint32_t)NB * 4096u);
+            for (int i = 0; i < NB; i++) {
+                tma_load_2d(smem + EW_Q_OFF + i * 4096, &tmQKV, h * EA_DH, (int)(row0 + i * 64), &bars[EW_KQ]);
+                tma_load_2d(smem + EW_K_OFF + i * 4096, &tmQKV, p.H + h * EA_DH, (int)(row0 + i * 64), &bars[EW_KQ]);
+            }
+        }
+        // the ones operand of the row sums: [16 rows x 128 B], row 0 = 1.0 (a row is 128 contiguous bytes whatever
+        // the swizzle does inside it)
+        for (int i = lane; i < 128; i += 32) {
+            const uint32_t w = i < 8 ? 0x3f803f80u : 0u;
+            *reinterpret_cast<uint4*>(smem + EW_ONE_OFF + i * 16) = make_uint4(w, w, w, w);
+        }
+    } else if (warp < 8) {
+        const bool in = tid < T;  // T is a multiple of 64: warp-uniform
+        const float bias = in ? p.mask_bias[row0 + tid] : -1e30f;
+        const uint32_t keep = __ballot_sync(0xffffffffu, bias == 0.f);
+        if (lane == 0) keep_s[warp] = keep;
+        if (!in && tid < QT * 128)  // query rows past T inside the last tile are zero
+            for (int c = 0; c < 4; c++) *reinterpret_cast<uint4*>(smem + EW_Q_OFF + sw64_off(tid, c)) = make_uint4(0, 0, 0, 0);
+    }
+    fence_proxy_async_smem();
+    mbar_wait(&bars[EW_KQ], 0);
+    // ||q||^2 per row and the largest ||k||^2 of the head: every score obeys s <= ||q|| max||k|| (Cauchy-Schwarz)
+    auto sumsq_row = [&](const unsigned char* tile, int r) {
+        float acc = 0.f;
+#pragma unroll
+        for (int c = 0; c < 4; c++) {
+            const uint4 w = *reinterpret_cast<const uint4*>(tile + sw64_off(r, c));
+            const uint32_t e[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                const float lo = __uint_as_float(e[i] << 16), hi = __uint_as_float(e[i] & 0xffff0000u);
+                acc = fmaf(lo, lo, acc);
+                acc = fmaf(hi, hi, acc);
+            }
+        }
+        return acc;
+    };
+    float qn2 = 0.f;
+    if (warp < 8) {
+        float kn = 0.f;
+        if (tid < T) {
+            qn2 = sumsq_row(smem + EW_Q_OFF, tid);
+            kn = sumsq_row(smem + EW_K_OFF, tid);
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) kn = fmaxf(kn, __shfl_xor_sync(0xffffffffu, kn, o));
+        if (lane == 0) kmax_s[warp] = kn;
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const float kn2 = fmaxf(fmaxf(fmaxf(kmax_s[0], kmax_s[1]), fmaxf(kmax_s[2], kmax_s[3])),
+                            fmaxf(fmaxf(kmax_s[4], kmax_s[5]), fmaxf(kmax_s[6], kmax_s[7])));
+    const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(tmem_slot);
+
+    // which 64-key blocks take part, and which of them have no masked key (CTA-uniform)
+    uint32_t act = 0, full = 0;
+    for (int j = 0; j < NB; j++) {
+        const uint32_t w0 = keep_s[2 * j], w1 = keep_s[2 * j + 1];
+        if (w0 | w1) act |= 1u << j;
+        if ((w0 & w1) == 0xffffffffu) full |= 1u << j;
+    }
+    // A chunk whose every key is masked: all its scores carry the same -1e30 bias, which swallows them in fp32, and
+    // the softmax is uniform over all T keys.  Scale 0 and shift 0 over all blocks give exactly that.
+    const bool no_key = act == 0;
+    if (no_key) act = full = (1u << NB) - 1u;
+    const float scale = no_key ? 0.f : p.scale_log2;
+
+    // the softmax shift: see enc_attention_blk_kernel
+    const int g = warp >> 2, row = tid & 127;  // softmax roles (warps 0-7)
+    const float mhat = sqrtf(qn2 * kn2) * scale * 1.0001f + 1e-3f;
+    const bool exact_max = __syncthreads_or(mhat > p.shift_limit ? 1 : 0) != 0 && !no_key;
+    const uint32_t lane_addr = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)(g & 1) * 128u;
+    float mx = mhat;
+    if (exact_max) {
+        // ---- pass 1 (only when the bound is not usable): the exact row maximum over the kept keys, 128 keys at a
+        //      time, both tiles at once into their groups' columns ----
+        mx = -INFINITY;
+        uint32_t ph = 0;
+        uint32_t r[32];
+        for (int k0 = 0; k0 < T; k0 += 128) {
+            const int n1 = min(128, T - k0);
+            if (warp == 8) {
+                if (elect_one()) {
+                    const uint32_t idesc = make_idesc_bf16(128, n1);
+                    for (int gg = 0; gg < QT; gg++) {
+                        const uint64_t dq = make_smem_desc_sw64(smem_u32(smem + EW_Q_OFF + gg * 8192));
+                        const uint64_t dk = make_smem_desc_sw64(smem_u32(smem + EW_K_OFF + k0 * 64));
+#pragma unroll
+                        for (int kk = 0; kk < EA_DH / 16; kk++)
+                            umma_bf16(tmem_base + gg * 128, dq + 2 * kk, dk + 2 * kk, idesc, kk != 0 ? 1u : 0u);
+                    }
+                    umma_commit(&bars[EW_P1]);
+                }
+                __syncwarp();
+            }
+            mbar_wait(&bars[EW_P1], ph);
+            ph ^= 1u;
+            tc_fence_after();
+            if (warp < 8 && g < QT) {
+                for (int c = 0; c < n1; c += 32) {
+                    tmem_ld_32x32(lane_addr + c, r);
+                    tmem_ld_wait();
+                    const uint32_t w = keep_s[(k0 + c) >> 5];
+#pragma unroll
+                    for (int j = 0; j < 32; j++)
+                        if ((w >> j) & 1u) mx = fmaxf(mx, __uint_as_float(r[j]) * scale);
+                }
+            }
+            tc_fence_before();
+            __syncthreads();  // every row has read this piece before the next MMA overwrites the columns
+            tc_fence_after();
+        }
+    }
+
+    const int j_first = __ffs(act) - 1;
+    const int nact = __popc(act);
+    if (warp < 8) {
+        // ===================== softmax groups =====================
+        if (g < QT) {
+            const float neg_mx = -mx;
+            unsigned char* Pb = smem + EW_P_OFF + g * 16384;
+            uint32_t r[2][32];
+            int idx = 0;
+            for (int j = 0; j < NB; j++) {
+                if (!((act >> j) & 1u)) continue;
+                mbar_wait(&bars[EW_S_FULL + g], idx & 1);
+                tc_fence_after();
+                tmem_ld_32x32(lane_addr, r[0]);
+                tmem_ld_32x32(lane_addr + 32, r[1]);
+                tmem_ld_wait();
+                tc_fence_before();
+                mbar_arrive(&bars[EW_S_FREE + g]);  // the next block's scores may overwrite the columns
+                const bool unmasked = (full >> j) & 1u;
+                uint32_t pk[32];
+#pragma unroll
+                for (int hh = 0; hh < 2; hh++) {
+                    if (unmasked) {
+#pragma unroll
+                        for (int jj = 0; jj < 16; jj++) {
+                            const float x0 = fmaf(__uint_as_float(r[hh][2 * jj]), scale, neg_mx);
+                            const float x1 = fmaf(__uint_as_float(r[hh][2 * jj + 1]), scale, neg_mx);
+                            float p0, p1;
+                            if (XM == 1) {
+                                p0 = x0;
+                                p1 = x1;
+                            } else {
+                                p0 = (XM >= 2 && (2 * jj) % (XM >= 2 ? XM : 1) == XM - 1) ? ex2_poly(x0) : ex2_fast(x0);
+                                p1 = (XM >= 2 && (2 * jj + 1) % (XM >= 2 ? XM : 1) == XM - 1) ? ex2_poly(x1) : ex2_fast(x1);
+                            }
+                            pk[hh * 16 + jj] = pack_bf16x2_rn(p0, p1);
+                        }
+                    } else {
+                        const uint32_t w = keep_s[2 * j + hh];
+#pragma unroll
+                        for (int jj = 0; jj < 16; jj++) {
+                            const float p0 = (w >> (2 * jj)) & 1u ? ex2_fast(fmaf(__uint_as_float(r[hh][2 * jj]), scale, neg_mx)) : 0.f;
+                            const float p1 = (w >> (2 * jj + 1)) & 1u ? ex2_fast(fmaf(__uint_as_float(r[hh][2 * jj + 1]), scale, neg_mx)) : 0.f;
+                            pk[hh * 16 + jj] = pack_bf16x2_rn(p0, p1);
+                        }
+                    }
+                }
+                // the previous block's product has read P
+                if (idx > 0) mbar_wait(&bars[EW_PV_DONE + g], (idx - 1) & 1);
+#pragma unroll
+                for (int i = 0; i < 8; i++)
+                    *reinterpret_cast<uint4*>(Pb + sw128_off(row, i)) = make_uint4(pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);
+                fence_proxy_async_smem();
+                mbar_arrive(&bars[EW_P_FULL + g]);
+                idx++;
+            }
+            mbar_wait(&bars[EW_PV_DONE + g], (nact - 1) & 1);
+            tc_fence_after();
+            // ---- normalise and store: columns 64..95 = O, column 96 = the row sum ----
+            uint32_t rs[16];
+            tmem_ld_32x32(lane_addr + 64, r[0]);
+            tmem_ld_32x16(lane_addr + 96, rs);
+            tmem_ld_wait();
+            {
+                // the context rows leave through the group's P buffer (free now) and one TMA store per 64 rows
+                const float inv = 1.0f / __uint_as_float(rs[0]);
+                uint32_t o[16];
+#pragma unroll
+                for (int jj = 0; jj < 16; jj++)
+                    o[jj] = pack_bf16x2_rn(__uint_as_float(r[0][2 * jj]) * inv, __uint_as_float(r[0][2 * jj + 1]) * inv);
+#pragma unroll
+                for (int i = 0; i < 4; i++)
+                    *reinterpret_cast<uint4*>(Pb + sw64_off(row, i)) = make_uint4(o[4 * i], o[4 * i + 1], o[4 * i + 2], o[4 * i + 3]);
+                fence_proxy_async_smem();
+                asm volatile("bar.sync %0, 128;" ::"r"(1 + g) : "memory");
+                if (row == 0) {
+                    for (int hf = 0; hf < 2; hf++)
+                        if (g * 128 + hf * 64 < T)
+                            tma_store_2d(&tmCTX, h * EA_DH, (int)(row0 + g * 128 + hf * 64), Pb + hf * 4096);
+                    bulk_commit_group();
+                    bulk_wait_group_read0();
+                }
+            }
+        }
+    } else if (warp == 8) {
+        // ===================== MMA issuer (converged warp, one elected lane issues) =====================
+        const uint32_t idesc_s = make_idesc_bf16(128, 64);
+        const uint32_t idesc_o = make_idesc_bf16(128, EA_DH) | (1u << 16);  // B = V is MN-major: [token][dim]
+        const uint32_t idesc_1 = make_idesc_bf16(128, 16);
+        const uint64_t d_one = make_smem_desc_sw128(smem_u32(smem + EW_ONE_OFF));
+        auto issue_scores = [&](int gg, int j) {
+            if (elect_one()) {
+                const uint64_t dq = make_smem_desc_sw64(smem_u32(smem + EW_Q_OFF + gg * 8192));
+                const uint64_t dk = make_smem_desc_sw64(smem_u32(smem + EW_K_OFF + j * 64 * 64));
+#pragma unroll
+                for (int kk = 0; kk < EA_DH / 16; kk++)
+                    umma_bf16(tmem_base + gg * 128, dq + 2 * kk, dk + 2 * kk, idesc_s, kk != 0 ? 1u : 0u);
+                umma_commit(&bars[EW_S_FULL + gg]);
+            }
+            __syncwarp();
+        };
+        for (int gg = 0; gg < QT; gg++) issue_scores(gg, j_first);
+        int idx = 0;
+        for (int j = 0; j < NB; j++) {
+            if (!((act >> j) & 1u)) continue;
+            const int slot = idx & 1, use = idx >> 1;
+            const uint32_t rest = act >> (j + 1);
+            if (rest) {
+                const int jn = j + __ffs(rest);
+                for (int gg = 0; gg < QT; gg++) {
+                    mbar_wait(&bars[EW_S_FREE + gg], idx & 1);
+                    tc_fence_after();
+                    issue_scores(gg, jn);
+                }
+            }
+            mbar_wait(&bars[EW_V_FULL + slot], use & 1);
+            for (int gg = 0; gg < QT; gg++) {
+                mbar_wait(&bars[EW_P_FULL + gg], idx & 1);
+                tc_fence_after();
+                if (elect_one()) {
+                    const uint64_t dp = make_smem_desc_sw128(smem_u32(smem + EW_P_OFF + gg * 16384));
+                    const uint64_t dv = make_smem_desc_sw64(smem_u32(smem + EW_V_OFF + slot * 4096));
+#pragma unroll
+                    for (int kk = 0; kk < 4; kk++) {  // 16 keys per step: 32 bytes along a P row, two 8-token groups of V
+                        umma_bf16(tmem_base + gg * 128 + 64, dp + 2 * kk, dv + 64 * kk, idesc_o, (idx | kk) != 0 ? 1u : 0u);
+                        umma_bf16(tmem_base + gg * 128 + 96, dp + 2 * kk, d_one + 2 * kk, idesc_1, (idx | kk) != 0 ? 1u : 0u);
+                    }
+                    umma_commit(&bars[EW_PV_DONE + gg]);
+                }
+                __syncwarp();
+            }
+            if (elect_one()) umma_commit(&bars[EW_V_FREE + slot]);  // both groups' products have read the slot
+            __syncwarp();
+            idx++;
+        }
+        // nobody waits for the last commit on either slot: see them land before the CTA gives its shared memory back
+        for (int k = nact - 1; k >= 0 && k >= nact - 2; k--) mbar_wait(&bars[EW_V_FREE + (k & 1)], (k >> 1) & 1);
+    } else {
+        // ===================== V loader: one 64-token block per TMA box, two slots =====================
+        if (lane == 0) {
+            int idx = 0;
+            for (int j = 0; j < NB; j++) {
+                if (!((act >> j) & 1u)) continue;
+                const int slot = idx & 1, use = idx >> 1;
+                if (use > 0) mbar_wait(&bars[EW_V_FREE + slot], (use - 1) & 1);
+                mbar_expect_tx(&bars[EW_V_FULL + slot], 4096u);
+                tma_load_2d(smem + EW_V_OFF + slot * 4096, &tmQKV, 2 * p.H + h * EA_DH, (int)(row0 + j * 64), &bars[EW_V_FULL + slot]);
+                idx++;
+            }
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 8) {
+        tc_fence_after();
+        tmem_dealloc<256>(tmem_base);
+    }
+}
+
 int launch_enc_attention(const __nv_bfloat16* qkv, const float* mask_bias, __nv_bfloat16* ctx, int64_t B, int T, int H,
                          int heads, cudaStream_t st) {
     if (B <= 0) return 0;
@@ -584,15 +945,20 @@ int launch_enc_attention(const __nv_bfloat16* qkv, const float* mask_bias, __nv_
     if (T <= 0 || T > EA_MAXT || (T & 63)) return fail("encoder attention: sequence length must be a multiple of 64, <= 256");
     if (B > 65535) return fail("encoder attention: more than 65535 chunks per launch");
     static bool attr_set[64] = {false};
-    static const bool whole_row = [] {  // BFK_ENC_ATTN=row: the first version (whole score row in TMEM)
+    static const int variant = [] {  // BFK_ENC_ATTN=row: the first version (whole score row in TMEM); =blk: the second
         const char* e = getenv("BFK_ENC_ATTN");
-        return e && e[0] == 'r';
+        return e && e[0] == 'r' ? 0 : e && e[0] == 'b' ? 1 : 2;
     }();
+    const bool whole_row = variant == 0;
     int dev = 0;
     BFK_CUDA(cudaGetDevice(&dev));
     if (dev < 0 || dev >= 64 || !attr_set[dev]) {
         BFK_CUDA(cudaFuncSetAttribute(enc_attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, EA_SMEM));
         BFK_CUDA(cudaFuncSetAttribute(enc_attention_blk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, EB_SMEM));
+        BFK_CUDA(cudaFuncSetAttribute(enc_attention_ws_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, EW_SMEM));
+        BFK_CUDA(cudaFuncSetAttribute(enc_attention_ws_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, EW_SMEM));
+        BFK_CUDA(cudaFuncSetAttribute(enc_attention_ws_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, EW_SMEM));
+        BFK_CUDA(cudaFuncSetAttribute(enc_attention_ws_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, EW_SMEM));
         if (dev >= 0 && dev < 64) attr_set[dev] = true;
     }
     EncAttnParams p;
@@ -609,7 +975,7 @@ int launch_enc_attention(const __nv_bfloat16* qkv, const float* mask_bias, __nv_
     p.shift_limit = exact_shift ? 0.f : 60.f;
     p.trace = nullptr;
     static const bool trace_on = getenv("BFK_ENC_ATTN_TRACE") != nullptr;
-    if (trace_on && !whole_row) {  // debugging: synchronous, one CTA's phase timeline on stderr
+    if (trace_on && variant == 1) {  // debugging: synchronous, one CTA's phase timeline on stderr
         unsigned long long* d = nullptr;
         BFK_CUDA(cudaMalloc((void**)&d, 128 * 8));
         BFK_CUDA(cudaMemset(d, 0, 128 * 8));
@@ -631,7 +997,20 @@ int launch_enc_attention(const __nv_bfloat16* qkv, const float* mask_bias, __nv_
         enc_attention_kernel<<<grid, EA_THREADS, EA_SMEM, st>>>(p);
     } else {
         dim3 grid((unsigned)heads, (unsigned)B);  // one CTA per (head, chunk): K is staged once for its query tiles
-        enc_attention_blk_kernel<<<grid, EB_THREADS, EB_SMEM, st>>>(p);
+        if (variant == 1) enc_attention_blk_kernel<<<grid, EB_THREADS, EB_SMEM, st>>>(p);
+        else {
+            static const int xm = [] {
+                const char* e = getenv("BFK_ENC_EXP");
+                return e ? atoi(e) : 0;
+            }();
+            CUtensorMap tmQKV, tmCTX;
+            BFK_TRY(make_tmap_head(&tmQKV, qkv, B * T, 3 * H, 64));
+            BFK_TRY(make_tmap_head(&tmCTX, ctx, B * T, H, 64));
+            if (xm == 1) enc_attention_ws_kernel<1><<<grid, EW_THREADS, EW_SMEM, st>>>(tmQKV, tmCTX, p);
+            else if (xm == 2) enc_attention_ws_kernel<2><<<grid, EW_THREADS, EW_SMEM, st>>>(tmQKV, tmCTX, p);
+            else if (xm == 4) enc_attention_ws_kernel<4><<<grid, EW_THREADS, EW_SMEM, st>>>(tmQKV, tmCTX, p);
+            else enc_attention_ws_kernel<0><<<grid, EW_THREADS, EW_SMEM, st>>>(tmQKV, tmCTX, p);
+        }
     }
     BFK_CUDA(cudaGetLastError());
     return 0;

@@ -1071,6 +1071,20 @@ int make_tmap(CUtensorMap* m, const void* base, int64_t rows, int ld, int box_ro
     return 0;
 }
 
+int make_tmap_head(CUtensorMap* m, const void* base, int64_t rows, int ld, int box_rows) {
+    EncodeTiledFn enc = get_encode_fn();
+    if (!enc) return fail("cuTensorMapEncodeTiled is not available from this driver");
+    cuuint64_t gdim[2] = {(cuuint64_t)ld, (cuuint64_t)std::max<int64_t>(rows, 1)};
+    cuuint64_t gstr[1] = {(cuuint64_t)ld * 2};
+    cuuint32_t box[2] = {32, (cuuint32_t)box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstr, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail("cuTensorMapEncodeTiled failed with code " + std::to_string((int)r));
+    return 0;
+}
+
 // The two tensor maps of a pass change only when the storage is regrown, rows are appended or the batch size
 // changes: they are re-encoded (a driver call each) only then.
 static int cached_tmap(bfk_index* idx, int slot, const void* base, int64_t rows, int box_rows, const CUtensorMap** out) {

@@ -4,7 +4,7 @@ cd "$(dirname "$0")/.." && mkdir -p gpurun_out
 NCU="ncu --set full --clock-control none --import-source on"
 for k in ${KERNELS:-attn gelu ln qkv}; do
   case $k in
-    attn) kern=enc_attention_blk_kernel; skip=7;;
+    attn) kern=enc_attention; skip=7;;
     gelu) kern='enc_gemm_kernel<1'; skip=7;;
     ln) kern='enc_gemm_kernel<2'; skip=15;;   # odd index = the K=1536 layer
     qkv) kern='enc_gemm_kernel<0'; skip=7;;
