@@ -605,21 +605,6 @@ constexpr int EW_BAR_OFF = 74 * 1024;
 constexpr int EW_SMEM = EW_BAR_OFF + 256 + 1024 /*alignment*/;
 enum { EW_S_FULL = 0, EW_S_FREE = 2, EW_P_FULL = 4, EW_PV_DONE = 6, EW_V_FULL = 8, EW_V_FREE = 10, EW_P1 = 12, EW_KQ = 13, EW_NBAR = 14 };
 
-// 2^x for x <= 0 on the FMA pipe: round x to n + f with |f| <= 1/2 (magic-number rounding), a cubic for 2^f
-// (relative error 1e-4, a bf16 result keeps 2^-9) and n added to the exponent field
-__device__ __forceinline__ float ex2_poly(float x) {
-    x = fmaxf(x, -125.f);
-    const float t = x + 12582912.f;
-    const float f = x - (t - 12582912.f);
-    float y = fmaf(0.0555041087f, f, 0.2402265069f);
-    y = fmaf(y, f, 0.6931471806f);
-    y = fmaf(y, f, 1.0f);
-    return __int_as_float(__float_as_int(y) + (__float_as_int(t) << 23));
-}
-
-// XM: how the exponentials are computed: 0 = all on the SFU (MUFU.EX2), 1 = none at all (timing experiment, wrong
-// results), n >= 2 = one of every n on the FMA pipe (ex2_poly)
-template <int XM>
 __global__ void __launch_bounds__(EW_THREADS, 2)
 enc_attention_ws_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmCTX, const EncAttnParams p) {
     extern __shared__ __align__(1024) unsigned char smem_raw[];
@@ -805,15 +790,7 @@ enc_attention_ws_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
                         for (int jj = 0; jj < 16; jj++) {
                             const float x0 = fmaf(__uint_as_float(r[hh][2 * jj]), scale, neg_mx);
                             const float x1 = fmaf(__uint_as_float(r[hh][2 * jj + 1]), scale, neg_mx);
-                            float p0, p1;
-                            if (XM == 1) {
-                                p0 = x0;
-                                p1 = x1;
-                            } else {
-                                p0 = (XM >= 2 && (2 * jj) % (XM >= 2 ? XM : 1) == XM - 1) ? ex2_poly(x0) : ex2_fast(x0);
-                                p1 = (XM >= 2 && (2 * jj + 1) % (XM >= 2 ? XM : 1) == XM - 1) ? ex2_poly(x1) : ex2_fast(x1);
-                            }
-                            pk[hh * 16 + jj] = pack_bf16x2_rn(p0, p1);
+                            pk[hh * 16 + jj] = pack_bf16x2_rn(ex2_fast(x0), ex2_fast(x1));
                         }
                     } else {
                         const uint32_t w = keep_s[2 * j + hh];
@@ -955,10 +932,7 @@ int launch_enc_attention(const __nv_bfloat16* qkv, const float* mask_bias, __nv_
     if (dev < 0 || dev >= 64 || !attr_set[dev]) {
         BFK_CUDA(cudaFuncSetAttribute(enc_attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, EA_SMEM));
         BFK_CUDA(cudaFuncSetAttribute(enc_attention_blk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, EB_SMEM));
-        BFK_CUDA(cudaFuncSetAttribute(enc_attention_ws_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, EW_SMEM));
-        BFK_CUDA(cudaFuncSetAttribute(enc_attention_ws_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, EW_SMEM));
-        BFK_CUDA(cudaFuncSetAttribute(enc_attention_ws_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, EW_SMEM));
-        BFK_CUDA(cudaFuncSetAttribute(enc_attention_ws_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, EW_SMEM));
+        BFK_CUDA(cudaFuncSetAttribute(enc_attention_ws_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, EW_SMEM));
         if (dev >= 0 && dev < 64) attr_set[dev] = true;
     }
     EncAttnParams p;
@@ -975,7 +949,7 @@ int launch_enc_attention(const __nv_bfloat16* qkv, const float* mask_bias, __nv_
     p.shift_limit = exact_shift ? 0.f : 60.f;
     p.trace = nullptr;
     static const bool trace_on = getenv("BFK_ENC_ATTN_TRACE") != nullptr;
-    if (trace_on && variant == 1) {  // debugging: synchronous, one CTA's phase timeline on stderr
+    if (trace_on && variant == 1) {  // debugging (the blocked kernel): synchronous, one CTA's phase timeline on stderr
         unsigned long long* d = nullptr;
         BFK_CUDA(cudaMalloc((void**)&d, 128 * 8));
         BFK_CUDA(cudaMemset(d, 0, 128 * 8));
@@ -999,17 +973,10 @@ int launch_enc_attention(const __nv_bfloat16* qkv, const float* mask_bias, __nv_
         dim3 grid((unsigned)heads, (unsigned)B);  // one CTA per (head, chunk): K is staged once for its query tiles
         if (variant == 1) enc_attention_blk_kernel<<<grid, EB_THREADS, EB_SMEM, st>>>(p);
         else {
-            static const int xm = [] {
-                const char* e = getenv("BFK_ENC_EXP");
-                return e ? atoi(e) : 0;
-            }();
             CUtensorMap tmQKV, tmCTX;
             BFK_TRY(make_tmap_head(&tmQKV, qkv, B * T, 3 * H, 64));
             BFK_TRY(make_tmap_head(&tmCTX, ctx, B * T, H, 64));
-            if (xm == 1) enc_attention_ws_kernel<1><<<grid, EW_THREADS, EW_SMEM, st>>>(tmQKV, tmCTX, p);
-            else if (xm == 2) enc_attention_ws_kernel<2><<<grid, EW_THREADS, EW_SMEM, st>>>(tmQKV, tmCTX, p);
-            else if (xm == 4) enc_attention_ws_kernel<4><<<grid, EW_THREADS, EW_SMEM, st>>>(tmQKV, tmCTX, p);
-            else enc_attention_ws_kernel<0><<<grid, EW_THREADS, EW_SMEM, st>>>(tmQKV, tmCTX, p);
+            enc_attention_ws_kernel<<<grid, EW_THREADS, EW_SMEM, st>>>(tmQKV, tmCTX, p);
         }
     }
     BFK_CUDA(cudaGetLastError());
