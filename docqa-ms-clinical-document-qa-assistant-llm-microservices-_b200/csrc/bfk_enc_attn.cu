@@ -915,6 +915,399 @@ enc_attention_ws_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
     }
 }
 
+// ---- E3d: the same roles in persistent CTAs ----------------------------------------------------------------
+// enc_attention_ws_kernel's timeline (clock64 stamps of one row): of the 18.3 k cycles a CTA lives, 5.4 k pass
+// before the first block (barrier init, TMEM allocation, the Q/K round trip, the norms behind two CTA-wide
+// barriers) and 1.7 k after the last.  Here two CTAs per SM stay resident and walk over the (head, chunk) items:
+//   * Q and K of item i+1 land in a second buffer while item i is computed; warp 9 also derives the item's
+//     "meta" from them ahead of time -- which key blocks take part, which have no masked key, and the softmax
+//     shift.  The shift is the same for every row of the item: sqrt(max||q||^2 max||k||^2) bounds every score of
+//     the item, and a common shift is as good as a per-row one while nothing underflows (see the blocked kernel);
+//   * the MMA warp issues the first scores of item i+1 as soon as the rows have read the last scores of item i,
+//     so a row goes from its last block straight into the epilogue and from there into ready scores;
+//   * barriers are initialised and TMEM is allocated once per CTA; phases run on across items.
+// An item whose bound is too large for the shift takes the exact row maxima in a first sweep over its key
+// blocks (scores only) through the same pipeline, then the normal sweep.
+constexpr int EP_THREADS = 320;
+constexpr int EP_QK_OFF = 0;                // [2 buffers][Q 16 KiB | K 16 KiB], 64-byte swizzle
+constexpr int EP_V_OFF = 64 * 1024;         // [2 slots][64 tokens x 64 B]  8 KiB, 64-byte swizzle
+constexpr int EP_P_OFF = 72 * 1024;         // [2 groups][128 x 128 B]     32 KiB, 128-byte swizzle (also the output staging)
+constexpr int EP_ONE_OFF = 104 * 1024;      // [16 rows x 128 B]            2 KiB: row 0 = ones
+constexpr int EP_META_OFF = 106 * 1024;     // [2 buffers][16 words]
+constexpr int EP_BAR_OFF = EP_META_OFF + 128;
+constexpr int EP_SMEM = EP_BAR_OFF + 256 + 1024 /*alignment*/;
+enum { EP_S_FULL = 0, EP_S_FREE = 2, EP_P_FULL = 4, EP_PV_DONE = 6, EP_V_FULL = 8, EP_V_FREE = 10, EP_O_FREE = 12,
+       EP_KQ_FULL = 14, EP_KQ_FREE = 16, EP_META_FULL = 18, EP_NBAR = 20 };
+// meta words: [0..7] keep bits, [8] act, [9] full, [10] flags (1 = exact maxima, 2 = no key kept), [11] shift (float)
+
+struct EncAttnPersist {
+    int T, H, heads;
+    int64_t items;      // chunks x heads
+    float scale_log2, shift_limit;
+    const float* mask_bias;
+    __nv_bfloat16* ctx;
+};
+
+__global__ void __launch_bounds__(EP_THREADS, 2)
+enc_attention_pws_kernel(const __grid_constant__ CUtensorMap tmQKV, const EncAttnPersist p) {
+    extern __shared__ __align__(1024) unsigned char smem_raw[];
+    const uint32_t raw = smem_u32(smem_raw);
+    unsigned char* smem = smem_raw + ((1024u - (raw & 1023u)) & 1023u);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + EP_BAR_OFF);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + EP_NBAR);
+    volatile uint32_t* meta_all = reinterpret_cast<volatile uint32_t*>(smem + EP_META_OFF);
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int T = p.T, NB = T >> 6, QT = (T + 127) >> 7;
+
+    if (tid == 0) {
+        for (int g = 0; g < 2; g++) {
+            mbar_init(&bars[EP_S_FULL + g], 1);
+            mbar_init(&bars[EP_S_FREE + g], 128);
+            mbar_init(&bars[EP_P_FULL + g], 128);
+            mbar_init(&bars[EP_PV_DONE + g], 1);
+            mbar_init(&bars[EP_V_FULL + g], 1);
+            mbar_init(&bars[EP_V_FREE + g], 1);
+            mbar_init(&bars[EP_O_FREE + g], 128);
+            mbar_init(&bars[EP_KQ_FULL + g], 1);
+            mbar_init(&bars[EP_KQ_FREE + g], 1);
+            mbar_init(&bars[EP_META_FULL + g], 1);
+        }
+        fence_mbar_init();
+    }
+    if (warp == 8) tmem_alloc<256>(tmem_slot);
+    if (warp == 9) {
+        if (lane == 0) tma_prefetch_desc(&tmQKV);
+        // the ones operand of the row sums: [16 rows x 128 B], row 0 = 1.0 (a row is 128 contiguous bytes whatever
+        // the swizzle does inside it)
+        for (int i = lane; i < 128; i += 32) {
+            const uint32_t w = i < 8 ? 0x3f803f80u : 0u;
+            *reinterpret_cast<uint4*>(smem + EP_ONE_OFF + i * 16) = make_uint4(w, w, w, w);
+        }
+        // query rows past T inside the last tile stay zero in both buffers (TMA only writes rows < T)
+        for (int r = T + lane; r < QT * 128; r += 32)
+            for (int bf = 0; bf < 2; bf++)
+                for (int c = 0; c < 4; c++) *reinterpret_cast<uint4*>(smem + EP_QK_OFF + bf * 32768 + sw64_off(r, c)) = make_uint4(0, 0, 0, 0);
+        fence_proxy_async_smem();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(tmem_slot);
+    const int64_t first = blockIdx.x, step = gridDim.x;
+
+    if (warp < 8) {
+        // ===================== softmax groups: thread == query row == TMEM lane =====================
+        const int g = warp >> 2, row = tid & 127;
+        if (g < QT) {
+            const uint32_t lane_addr = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)g * 128u;
+            unsigned char* Pb = smem + EP_P_OFF + g * 16384;
+            uint32_t n_it = 0, sjob = 0, pblk = 0;  // items, score jobs and P blocks this group has been through
+            uint32_t r[2][32];
+            for (int64_t it = first; it < p.items; it += step, n_it++) {
+                const int buf = n_it & 1;
+                const int h = (int)(it % p.heads);
+                const int64_t row0 = (it / p.heads) * T;
+                mbar_wait(&bars[EP_META_FULL + buf], (n_it >> 1) & 1);
+                const volatile uint32_t* meta = meta_all + buf * 16;
+                const uint32_t act = meta[8], full = meta[9], flags = meta[10];
+                const bool exact = flags & 1u;
+                const float scale = (flags & 2u) ? 0.f : p.scale_log2;
+                float mx = __uint_as_float(meta[11]);
+                if (exact) {
+                    // first sweep: the exact row maximum over the kept keys
+                    mx = -INFINITY;
+                    for (int j = 0; j < NB; j++) {
+                        if (!((act >> j) & 1u)) continue;
+                        mbar_wait(&bars[EP_S_FULL + g], sjob & 1);
+                        tc_fence_after();
+                        tmem_ld_32x32(lane_addr, r[0]);
+                        tmem_ld_32x32(lane_addr + 32, r[1]);
+                        tmem_ld_wait();
+                        tc_fence_before();
+                        mbar_arrive(&bars[EP_S_FREE + g]);
+                        sjob++;
+#pragma unroll
+                        for (int hh = 0; hh < 2; hh++) {
+                            const uint32_t w = meta[2 * j + hh];
+#pragma unroll
+                            for (int k = 0; k < 32; k++)
+                                if ((w >> k) & 1u) mx = fmaxf(mx, __uint_as_float(r[hh][k]) * scale);
+                        }
+                    }
+                }
+                const float neg_mx = -mx;
+                bool first_blk = true;
+                for (int j = 0; j < NB; j++) {
+                    if (!((act >> j) & 1u)) continue;
+                    mbar_wait(&bars[EP_S_FULL + g], sjob & 1);
+                    tc_fence_after();
+                    tmem_ld_32x32(lane_addr, r[0]);
+                    tmem_ld_32x32(lane_addr + 32, r[1]);
+                    tmem_ld_wait();
+                    tc_fence_before();
+                    mbar_arrive(&bars[EP_S_FREE + g]);  // the next scores may overwrite the columns
+                    sjob++;
+                    const bool unmasked = (full >> j) & 1u;
+                    uint32_t pk[32];
+#pragma unroll
+                    for (int hh = 0; hh < 2; hh++) {
+                        if (unmasked) {
+#pragma unroll
+                            for (int jj = 0; jj < 16; jj++) {
+                                const float x0 = fmaf(__uint_as_float(r[hh][2 * jj]), scale, neg_mx);
+                                const float x1 = fmaf(__uint_as_float(r[hh][2 * jj + 1]), scale, neg_mx);
+                                pk[hh * 16 + jj] = pack_bf16x2_rn(ex2_fast(x0), ex2_fast(x1));
+                            }
+                        } else {
+                            const uint32_t w = meta[2 * j + hh];
+#pragma unroll
+                            for (int jj = 0; jj < 16; jj++) {
+                                const float p0 = (w >> (2 * jj)) & 1u ? ex2_fast(fmaf(__uint_as_float(r[hh][2 * jj]), scale, neg_mx)) : 0.f;
+                                const float p1 = (w >> (2 * jj + 1)) & 1u ? ex2_fast(fmaf(__uint_as_float(r[hh][2 * jj + 1]), scale, neg_mx)) : 0.f;
+                                pk[hh * 16 + jj] = pack_bf16x2_rn(p0, p1);
+                            }
+                        }
+                    }
+                    // the previous block's product has read P (an item's first block: waited for in the epilogue)
+                    if (!first_blk) mbar_wait(&bars[EP_PV_DONE + g], (pblk - 1) & 1);
+#pragma unroll
+                    for (int i = 0; i < 8; i++)
+                        *reinterpret_cast<uint4*>(Pb + sw128_off(row, i)) = make_uint4(pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);
+                    fence_proxy_async_smem();
+                    mbar_arrive(&bars[EP_P_FULL + g]);
+                    pblk++;
+                    first_blk = false;
+                }
+                mbar_wait(&bars[EP_PV_DONE + g], (pblk - 1) & 1);
+                tc_fence_after();
+                // ---- normalise and store: columns 64..95 = O, column 96 = the row sum ----
+                uint32_t rs[16];
+                tmem_ld_32x32(lane_addr + 64, r[0]);
+                tmem_ld_32x16(lane_addr + 96, rs);
+                tmem_ld_wait();
+                tc_fence_before();
+                mbar_arrive(&bars[EP_O_FREE + g]);  // the next item's first product may overwrite O
+                const float inv = 1.0f / __uint_as_float(rs[0]);
+                uint32_t o[16];
+#pragma unroll
+                for (int jj = 0; jj < 16; jj++)
+                    o[jj] = pack_bf16x2_rn(__uint_as_float(r[0][2 * jj]) * inv, __uint_as_float(r[0][2 * jj + 1]) * inv);
+                // through the group's P buffer (free: its last product has completed) so that four lanes store one
+                // 64-byte row: thread-per-row stores cost 32 LSU wavefronts per instruction
+#pragma unroll
+                for (int i = 0; i < 4; i++)
+                    *reinterpret_cast<uint4*>(Pb + sw64_off(row, i)) = make_uint4(o[4 * i], o[4 * i + 1], o[4 * i + 2], o[4 * i + 3]);
+                asm volatile("bar.sync %0, 128;" ::"r"(1 + g) : "memory");
+#pragma unroll
+                for (int i = 0; i < 4; i++) {
+                    const int rr = (warp & 3) * 32 + 8 * i + (lane >> 2), c = lane & 3;
+                    const uint4 v = *reinterpret_cast<const uint4*>(Pb + sw64_off(rr, c));
+                    const int q = g * 128 + rr;
+                    if (q < T) *reinterpret_cast<uint4*>(p.ctx + (size_t)(row0 + q) * p.H + h * EA_DH + c * 8) = v;
+                }
+                asm volatile("bar.sync %0, 128;" ::"r"(1 + g) : "memory");  // staging read before the next P block lands
+            }
+        }
+    } else if (warp == 8) {
+        // ===================== MMA issuer (converged warp, one elected lane issues) =====================
+        const uint32_t idesc_s = make_idesc_bf16(128, 64);
+        const uint32_t idesc_o = make_idesc_bf16(128, EA_DH) | (1u << 16);  // B = V is MN-major: [token][dim]
+        const uint32_t idesc_1 = make_idesc_bf16(128, 16);
+        const uint64_t d_one = make_smem_desc_sw128(smem_u32(smem + EP_ONE_OFF));
+        uint32_t n_it = 0, sjob = 0, pblk = 0, vuse = 0;  // score jobs issued, products issued, V slots consumed
+        for (int64_t it = first; it < p.items; it += step, n_it++) {
+            const int buf = n_it & 1;
+            mbar_wait(&bars[EP_META_FULL + buf], (n_it >> 1) & 1);  // implies Q and K of the item have landed
+            const volatile uint32_t* meta = meta_all + buf * 16;
+            const uint32_t act = meta[8];
+            const bool exact = meta[10] & 1u;
+            const int nact = __popc(act);
+            const int njobs = exact ? 2 * nact : nact;
+            const unsigned char* Qb = smem + EP_QK_OFF + buf * 32768;
+            const unsigned char* Kb = Qb + 16384;
+            auto issue_scores = [&](int gg, int j, bool last) {
+                if (elect_one()) {
+                    const uint64_t dq = make_smem_desc_sw64(smem_u32(Qb + gg * 8192));
+                    const uint64_t dk = make_smem_desc_sw64(smem_u32(Kb + j * 64 * 64));
+#pragma unroll
+                    for (int kk = 0; kk < EA_DH / 16; kk++)
+                        umma_bf16(tmem_base + gg * 128, dq + 2 * kk, dk + 2 * kk, idesc_s, kk != 0 ? 1u : 0u);
+                    umma_commit(&bars[EP_S_FULL + gg]);
+                    if (last && gg == QT - 1) umma_commit(&bars[EP_KQ_FREE + buf]);  // Q and K of the item have been read
+                }
+                __syncwarp();
+            };
+            // job k of the item reads key block blk(k): the k-th set bit of act, twice over when exact
+            auto blk_of = [&](int k) {
+                int kk = k >= nact ? k - nact : k;
+                uint32_t a = act;
+                for (int i = 0; i < kk; i++) a &= a - 1;
+                return __ffs(a) - 1;
+            };
+            // the item's first scores: the rows have read the previous item's last ones
+            for (int gg = 0; gg < QT; gg++) {
+                if (sjob > 0) {
+                    mbar_wait(&bars[EP_S_FREE + gg], (sjob - 1) & 1);
+                    tc_fence_after();
+                }
+                issue_scores(gg, blk_of(0), njobs == 1);
+            }
+            for (int k = 0; k < njobs; k++, sjob++) {
+                if (k + 1 < njobs) {
+                    const int jn = blk_of(k + 1);
+                    for (int gg = 0; gg < QT; gg++) {
+                        mbar_wait(&bars[EP_S_FREE + gg], sjob & 1);
+                        tc_fence_after();
+                        issue_scores(gg, jn, k + 2 == njobs);
+                    }
+                }
+                if (exact && k < nact) continue;  // first sweep: scores only
+                const bool first_blk = exact ? k == nact : k == 0;
+                const int slot = vuse & 1;
+                mbar_wait(&bars[EP_V_FULL + slot], (vuse >> 1) & 1);
+                for (int gg = 0; gg < QT; gg++) {
+                    mbar_wait(&bars[EP_P_FULL + gg], pblk & 1);
+                    if (first_blk && n_it > 0) mbar_wait(&bars[EP_O_FREE + gg], (n_it - 1) & 1);  // the rows have read the previous O
+                    tc_fence_after();
+                    if (elect_one()) {
+                        const uint64_t dp = make_smem_desc_sw128(smem_u32(smem + EP_P_OFF + gg * 16384));
+                        const uint64_t dv = make_smem_desc_sw64(smem_u32(smem + EP_V_OFF + slot * 4096));
+#pragma unroll
+                        for (int kk = 0; kk < 4; kk++) {  // 16 keys per step: 32 bytes along a P row, two 8-token groups of V
+                            umma_bf16(tmem_base + gg * 128 + 64, dp + 2 * kk, dv + 64 * kk, idesc_o, (!first_blk || kk != 0) ? 1u : 0u);
+                            umma_bf16(tmem_base + gg * 128 + 96, dp + 2 * kk, d_one + 2 * kk, idesc_1, (!first_blk || kk != 0) ? 1u : 0u);
+                        }
+                        umma_commit(&bars[EP_PV_DONE + gg]);
+                    }
+                    __syncwarp();
+                }
+                if (elect_one()) umma_commit(&bars[EP_V_FREE + slot]);  // both groups' products have read the slot
+                __syncwarp();
+                pblk++;
+                vuse++;
+            }
+        }
+        // nobody waits for the last commits on the V slots and the Q/K buffers: see them land before the CTA gives
+        // its shared memory back
+        for (uint32_t k = vuse; k > 0 && k + 2 > vuse; k--) mbar_wait(&bars[EP_V_FREE + ((k - 1) & 1)], ((k - 1) >> 1) & 1);
+        for (uint32_t k = n_it; k > 0 && k + 2 > n_it; k--) mbar_wait(&bars[EP_KQ_FREE + ((k - 1) & 1)], ((k - 1) >> 1) & 1);
+    } else {
+        // ===================== loader: Q / K of the next item, its meta, V blocks of the current one =====================
+        uint32_t n_it = 0, vuse = 0;
+        auto load_qk = [&](int64_t it, uint32_t n) {  // lane 0
+            const int buf = n & 1;
+            if (n >= 2) mbar_wait(&bars[EP_KQ_FREE + buf], ((n >> 1) - 1) & 1);
+            const int h = (int)(it % p.heads);
+            const int64_t row0 = (it / p.heads) * T;
+            unsigned char* Qb = smem + EP_QK_OFF + buf * 32768;
+            mbar_expect_tx(&bars[EP_KQ_FULL + buf], 2u * (uint32_t)NB * 4096u);
+            for (int i = 0; i < NB; i++) {
+                tma_load_2d(Qb + i * 4096, &tmQKV, h * EA_DH, (int)(row0 + i * 64), &bars[EP_KQ_FULL + buf]);
+                tma_load_2d(Qb + 16384 + i * 4096, &tmQKV, p.H + h * EA_DH, (int)(row0 + i * 64), &bars[EP_KQ_FULL + buf]);
+            }
+        };
+        auto sumsq_row = [&](const unsigned char* tile, int r) {
+            float acc = 0.f;
+#pragma unroll
+            for (int c = 0; c < 4; c++) {
+                const uint4 w = *reinterpret_cast<const uint4*>(tile + sw64_off(r, c));
+                const uint32_t e[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+                for (int i = 0; i < 4; i++) {
+                    const float lo = __uint_as_float(e[i] << 16), hi = __uint_as_float(e[i] & 0xffff0000u);
+                    acc = fmaf(lo, lo, acc);
+                    acc = fmaf(hi, hi, acc);
+                }
+            }
+            return acc;
+        };
+        // whole warp.  The buffer's previous tenant is item n - 2; `prev_use` = V slots consumed up to and including
+        // that item: once its last product has completed, no row and no MMA looks at its meta any more.
+        auto make_meta = [&](int64_t it, uint32_t n, uint32_t prev_use) {
+            const int buf = n & 1;
+            if (prev_use > 0) mbar_wait(&bars[EP_V_FREE + ((prev_use - 1) & 1)], ((prev_use - 1) >> 1) & 1);
+            const int64_t row0 = (it / p.heads) * T;
+            volatile uint32_t* meta = meta_all + buf * 16;
+            uint32_t act = 0, full = 0;
+            for (int w = 0; w < 2 * NB; w++) {
+                const uint32_t keep = __ballot_sync(0xffffffffu, p.mask_bias[row0 + w * 32 + lane] == 0.f);
+                if (lane == 0) meta[w] = keep;
+                if (keep) act |= 1u << (w >> 1);
+                if (keep != 0xffffffffu) full |= 1u << (w >> 1);  // collects the blocks that are NOT full
+            }
+            full = ~full & ((1u << NB) - 1u);
+            const bool no_key = act == 0;
+            if (no_key) act = full = (1u << NB) - 1u;
+            mbar_wait(&bars[EP_KQ_FULL + buf], (n >> 1) & 1);
+            const unsigned char* Qb = smem + EP_QK_OFF + buf * 32768;
+            float qm = 0.f, km = 0.f;
+            for (int r = lane; r < T; r += 32) {
+                qm = fmaxf(qm, sumsq_row(Qb, r));
+                km = fmaxf(km, sumsq_row(Qb + 16384, r));
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                qm = fmaxf(qm, __shfl_xor_sync(0xffffffffu, qm, o));
+                km = fmaxf(km, __shfl_xor_sync(0xffffffffu, km, o));
+            }
+            // every score of the item obeys |s| <= max||q|| max||k|| (Cauchy-Schwarz)
+            const float mhat = no_key ? 1e-3f : sqrtf(qm * km) * p.scale_log2 * 1.0001f + 1e-3f;
+            const bool exact = mhat > p.shift_limit && !no_key;
+            if (lane == 0) {
+                meta[8] = act;
+                meta[9] = full;
+                meta[10] = (exact ? 1u : 0u) | (no_key ? 2u : 0u);
+                meta[11] = __float_as_uint(mhat);
+                __threadfence_block();
+                mbar_arrive(&bars[EP_META_FULL + buf]);
+            }
+            __syncwarp();
+        };
+        if (first < p.items) {
+            if (lane == 0) load_qk(first, 0);
+            __syncwarp();
+            make_meta(first, 0, 0);
+        }
+        for (int64_t it = first; it < p.items; it += step, n_it++) {
+            const int buf = n_it & 1;
+            const int64_t nxt = it + step;
+            if (nxt < p.items && lane == 0) load_qk(nxt, n_it + 1);
+            __syncwarp();
+            const int h = (int)(it % p.heads);
+            const int64_t row0 = (it / p.heads) * T;
+            const uint32_t act = meta_all[buf * 16 + 8];
+            const uint32_t use0 = vuse;  // V slots consumed by the items before this one
+            int idx = 0;
+            bool meta_done = nxt >= p.items;
+            for (int j = 0; j < NB; j++) {
+                if (!((act >> j) & 1u)) continue;
+                if (idx == 2 && !meta_done) {  // two V blocks are under way: time for the next item's meta
+                    make_meta(nxt, n_it + 1, use0);
+                    meta_done = true;
+                }
+                if (lane == 0) {
+                    const int slot = vuse & 1;
+                    if (vuse >= 2) mbar_wait(&bars[EP_V_FREE + slot], ((vuse >> 1) - 1) & 1);
+                    mbar_expect_tx(&bars[EP_V_FULL + slot], 4096u);
+                    tma_load_2d(smem + EP_V_OFF + slot * 4096, &tmQKV, 2 * p.H + h * EA_DH, (int)(row0 + j * 64), &bars[EP_V_FULL + slot]);
+                }
+                __syncwarp();
+                vuse++;
+                idx++;
+            }
+            if (!meta_done) make_meta(nxt, n_it + 1, use0);
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 8) {
+        tc_fence_after();
+        tmem_dealloc<256>(tmem_base);
+    }
+}
+
 int launch_enc_attention(const __nv_bfloat16* qkv, const float* mask_bias, __nv_bfloat16* ctx, int64_t B, int T, int H,
                          int heads, cudaStream_t st) {
     if (B <= 0) return 0;
@@ -924,7 +1317,7 @@ int launch_enc_attention(const __nv_bfloat16* qkv, const float* mask_bias, __nv_
     static bool attr_set[64] = {false};
     static const int variant = [] {  // BFK_ENC_ATTN=row: the first version (whole score row in TMEM); =blk: the second
         const char* e = getenv("BFK_ENC_ATTN");
-        return e && e[0] == 'r' ? 0 : e && e[0] == 'b' ? 1 : 2;
+        return e && e[0] == 'r' ? 0 : e && e[0] == 'b' ? 1 : e && e[0] == 'w' ? 2 : 3;
     }();
     const bool whole_row = variant == 0;
     int dev = 0;
@@ -933,6 +1326,7 @@ int launch_enc_attention(const __nv_bfloat16* qkv, const float* mask_bias, __nv_
         BFK_CUDA(cudaFuncSetAttribute(enc_attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, EA_SMEM));
         BFK_CUDA(cudaFuncSetAttribute(enc_attention_blk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, EB_SMEM));
         BFK_CUDA(cudaFuncSetAttribute(enc_attention_ws_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, EW_SMEM));
+        BFK_CUDA(cudaFuncSetAttribute(enc_attention_pws_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, EP_SMEM));
         if (dev >= 0 && dev < 64) attr_set[dev] = true;
     }
     EncAttnParams p;
@@ -972,7 +1366,23 @@ int launch_enc_attention(const __nv_bfloat16* qkv, const float* mask_bias, __nv_
     } else {
         dim3 grid((unsigned)heads, (unsigned)B);  // one CTA per (head, chunk): K is staged once for its query tiles
         if (variant == 1) enc_attention_blk_kernel<<<grid, EB_THREADS, EB_SMEM, st>>>(p);
-        else {
+        else if (variant == 3) {
+            CUtensorMap tmQKV;
+            BFK_TRY(make_tmap_head(&tmQKV, qkv, B * T, 3 * H, 64));
+            EncAttnPersist pp;
+            pp.T = T;
+            pp.H = H;
+            pp.heads = heads;
+            pp.items = B * heads;
+            pp.scale_log2 = p.scale_log2;
+            pp.shift_limit = p.shift_limit;
+            pp.mask_bias = mask_bias;
+            pp.ctx = ctx;
+            int num_sms = 148;
+            cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev);
+            const unsigned ctas = (unsigned)std::min<int64_t>(pp.items, 2 * (int64_t)num_sms);
+            enc_attention_pws_kernel<<<ctas, EP_THREADS, EP_SMEM, st>>>(tmQKV, pp);
+        } else {
             CUtensorMap tmQKV, tmCTX;
             BFK_TRY(make_tmap_head(&tmQKV, qkv, B * T, 3 * H, 64));
             BFK_TRY(make_tmap_head(&tmCTX, ctx, B * T, H, 64));
