@@ -22,9 +22,23 @@
 // swizzle; the MMA warp (converged, one elected lane) issues tcgen05.mma M=128, N=128 x3 or N=192, K=16.
 // Persistent grid; 8 epilogue warps, thread = (output row = TMEM lane, column half), TMEM loads of the next
 // 32 columns in flight while the current ones are finished.
+//
+// Round 2, in the order the measurements asked for them (BFK_ENC_GEMM_DEBUG prints where each role waits):
+//   PAIR  two CTAs as one tcgen05.mma.cta_group::2 (M = 256): each CTA stages its own 128 rows of A and half of
+//         every W block.  A lone CTA pulled 40 KB through L2 per 128 x 192 x 64 of MMA work and all four layer
+//         shapes sat at the L2 slices' throughput limit (2.0 GB in 169 us for the intermediate layer).
+//   ARES  (K = 384, 192-wide tiles) the CTA's 128 x 384 slice of A stays in shared memory while the pair sweeps
+//         the N tiles of its rows; the ring carries W blocks only.  Each pair owns a contiguous range of the
+//         row-group-major tile sequence, so pairs change row groups at different times.
+//   192-wide tiles store through TMA (one 32 x 32 box per chunk and warp) instead of 4 shared loads + 4 global
+//         stores per lane: the LSU data pipe was the busiest unit of the QKV projection (67 % of peak).
+//   LayerNorm tiles pull their residual rows into L2 (and the first chunk into registers) while the tile's MMAs
+//         run: their epilogue had half of its samples in long-scoreboard stalls on those loads.
 #include <cuda.h>
 
+#include <cstdio>
 #include <cstdlib>
+#include <vector>
 
 #include "bfk_common.cuh"
 #include "bfk_ptx.cuh"
@@ -36,10 +50,12 @@ constexpr int EG_BM = 128, EG_BK = 64;
 constexpr int EG_THREADS = 384;                       // 4 control warps + 8 epilogue warps
 constexpr int EG_EPI_THREADS = 256;
 constexpr int EG_A_BYTES = EG_BM * EG_BK * 2;         // 16 KiB
-constexpr int EG_TAIL = 256 /*barriers*/ + 2 * 2 * 128 * 8 /*LayerNorm partial sums, double-buffered*/ +
-                        8 * 2048 /*per-warp load/store staging*/ + 3 * 384 * 4 /*bias, gamma, beta of a 384-wide tile*/;
+constexpr int EG_BARS = 512;
+constexpr int EG_ARES_KB = 6;                         // K-blocks of a resident A tile (K = 384)
+constexpr int EG_FIXED = EG_BARS /*barriers*/ + 2 * 2 * 128 * 8 /*LayerNorm partial sums, double-buffered*/ +
+                         3 * 384 * 4 /*bias, gamma, beta of a 384-wide tile*/;
 
-template <int BN, bool PAIR>
+template <int BN, bool PAIR, bool ARES = false>
 struct EgShape {
     static constexpr int BNB = PAIR ? 192 : (BN == 384 ? 128 : BN);  // N of one tcgen05.mma
     static constexpr int NBLK = BN / BNB;
@@ -47,9 +63,16 @@ struct EgShape {
     static constexpr int B_ROWS = PAIR ? BNB / 2 : BNB;  // rows of a W block this CTA stages (a pair splits them)
     static constexpr int B_BLOCK = B_ROWS * EG_BK * 2;
     static constexpr int B_BYTES = NBLK * B_BLOCK;
-    static constexpr int STAGE = EG_A_BYTES + B_BYTES;
-    static constexpr int STAGES = PAIR ? (BN == 192 ? 7 : 5) : (BN == 192 ? 5 : 3);
-    static constexpr int SMEM = STAGES * STAGE + 1024 /*alignment*/ + EG_TAIL;
+    // ARES: the CTA's 128 x 384 A tile stays in shared memory while the pair sweeps all N tiles of its rows; the
+    // ring then carries W blocks only
+    static constexpr int A_RES = ARES ? EG_ARES_KB * EG_A_BYTES : 0;
+    static constexpr int STAGE = ARES ? B_BYTES : EG_A_BYTES + B_BYTES;
+    static constexpr int STAGES = BN == 192 ? (ARES ? 7 : PAIR ? 6 : 4) : (PAIR ? 5 : 3);
+    static constexpr int RING_END = A_RES + STAGES * STAGE;
+    // per-warp staging between registers and global memory: 192-wide tiles store through TMA from two 2 KiB
+    // buffers per warp, the LayerNorm tiles transpose through one
+    static constexpr int STG_WARP = BN == 192 ? 4096 : 2048;
+    static constexpr int SMEM = RING_END + 1024 /*alignment*/ + EG_FIXED + 8 * STG_WARP;
 };
 
 enum { EPI_BIAS = 0, EPI_GELU = 1, EPI_RES_LN = 2, EPI_GELU_ERF = 3 };
@@ -63,6 +86,7 @@ struct EncGemmParams {
     float eps;
     __nv_bfloat16* out;              // [M, ldo]
     int ldo;
+    unsigned long long* dbg;         // BFK_ENC_GEMM_DEBUG: [grid][8] cycles each role spent waiting, or null
 };
 
 // exact-GELU through Abramowitz-Stegun 7.1.26 (|erf error| <= 1.5e-7, far below the bf16 rounding of the
@@ -98,36 +122,80 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
     return *reinterpret_cast<const uint32_t*>(&v);
 }
 
+#define EG_WAIT(bar, parity, slot)                                                  \
+    do {                                                                            \
+        const long long _t0 = p.dbg ? clock64() : 0;                                \
+        mbar_wait(bar, parity);                                                     \
+        if (p.dbg) dbg_acc[slot] += (unsigned long long)(clock64() - _t0);          \
+    } while (0)
+
 __device__ __forceinline__ void eg_epi_sync() { asm volatile("bar.sync 3, 256;" ::: "memory"); }
 
-template <int EPI, int BN, bool PAIR>
+template <int EPI, int BN, bool PAIR, bool ARES>
 __global__ void __launch_bounds__(EG_THREADS, 1)
-enc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW, const EncGemmParams p) {
-    using S = EgShape<BN, PAIR>;
+enc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
+                const __grid_constant__ CUtensorMap tmO, const EncGemmParams p) {
+    static_assert(!ARES || (PAIR && BN == 192), "the resident-A form exists for paired 192-wide tiles");
+    using S = EgShape<BN, PAIR, ARES>;
     constexpr uint32_t CS = PAIR ? 2u : 1u;  // CTAs per tile group
     constexpr int STAGES = S::STAGES, STAGE = S::STAGE, NACC = S::NACC;
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     const uint32_t raw = smem_u32(smem_raw);
     unsigned char* smem = smem_raw + ((1024u - (raw & 1023u)) & 1023u);
-    unsigned char* ring = smem;
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * STAGE);
+    unsigned char* a_res = smem;                  // ARES: [6 K-blocks][128 x 64] of this CTA's rows
+    unsigned char* ring = smem + S::A_RES;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + S::RING_END);
     uint64_t* full_bar = bars;                    // [stages]
     uint64_t* empty_bar = bars + STAGES;          // [stages]
     uint64_t* tfull_bar = bars + 2 * STAGES;      // [NACC] accumulator complete
     uint64_t* tempty_bar = tfull_bar + 2;         // [NACC] accumulator drained (256 epilogue threads)
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
-    float2* ln_part = reinterpret_cast<float2*>(smem + STAGES * STAGE + 256);  // [2 parities][2 halves][128 rows]
-    float* par_s = reinterpret_cast<float*>(smem + STAGES * STAGE + 256 + 4096);  // [3][384] bias | gamma | beta
+    uint64_t* afull_bar = tempty_bar + 2;         // [6] ARES: K-block of the resident A tile has landed (both CTAs)
+    uint64_t* afree_bar = afull_bar + EG_ARES_KB; // [6] ARES: the last MMA that reads it has completed
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(afree_bar + EG_ARES_KB);
+    float2* ln_part = reinterpret_cast<float2*>(smem + S::RING_END + EG_BARS);  // [2 parities][2 halves][128 rows]
+    float* par_s = reinterpret_cast<float*>(smem + S::RING_END + EG_BARS + 4096);  // [3][384] bias | gamma | beta
     float* bias_s = reinterpret_cast<float*>(ln_part);  // bias / GELU kernels: the whole bias vector (N <= 2176 floats)
-    unsigned char* stg_all = smem + STAGES * STAGE + 256 + 4096 + 3 * 384 * 4;    // [8 warps][32 rows x 64 B]
+    unsigned char* stg_all = smem + S::RING_END + EG_BARS + 4096 + 3 * 384 * 4;    // [8 warps][32 rows x 64 B]
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    unsigned long long dbg_acc[2] = {0, 0};
+    const long long dbg_t0 = p.dbg ? clock64() : 0;
     const int KB = p.K / EG_BK;
     const int n_tiles = p.N / BN;
     // a pair works on 256 rows at a time: CTA rank r owns rows [256 g + 128 r, + 128) of group g
     const int m_tiles = (p.M + (int)CS * EG_BM - 1) / ((int)CS * EG_BM);
     const int tiles = m_tiles * n_tiles;
     const int first_tile = blockIdx.x / CS, tile_step = gridDim.x / CS;
+    // the q-th tile of this CTA (pair): round-robin over all tiles, or -- ARES -- a contiguous range of the
+    // row-group-major tile sequence, so that a pair sweeps the N tiles of a row group with its A tile in place.
+    // The ranges start at different offsets inside a group (3072 tiles / 74 pairs), so the pairs change row
+    // groups at different times: when they all did it together, 14 MB of A tiles were asked of HBM at once and
+    // every group started with a 5.7 k-cycle wait (3.7 k remain: a block can only be requested once the previous
+    // group's last MMA over it has completed, 2.3 k cycles before it is needed; pulling the next group's rows into
+    // L2 a group ahead with prefetch.global.L2 from an idle warp changed nothing and was taken out again).  grp = row groups this pair has started before this tile's,
+    // first / last = the tile is the first / last one of its row group inside the range.
+    const int npairs = gridDim.x / CS;
+    const int t_begin = (int)((int64_t)tiles * first_tile / npairs), t_end = (int)((int64_t)tiles * (first_tile + 1) / npairs);
+    const int mg_begin = ARES ? t_begin / n_tiles : 0;
+    int grp = 0;
+    bool first = false, last = false;
+    auto tile_at = [&](int q, int& mg, int& nt) {
+        if constexpr (ARES) {
+            const int t = t_begin + q;
+            if (t >= t_end) return false;
+            mg = t / n_tiles;
+            nt = t - mg * n_tiles;
+            grp = mg - mg_begin;
+            first = q == 0 || nt == 0;
+            last = t == t_end - 1 || nt == n_tiles - 1;
+            return true;
+        } else {
+            const int tile = first_tile + q * tile_step;
+            mg = tile / n_tiles;
+            nt = tile - mg * n_tiles;
+            return tile < tiles;
+        }
+    };
 
     if (tid == 0) {
         // pair: the leader's full / tempty barriers collect both CTAs; empty / tfull exist per CTA and are
@@ -139,6 +207,10 @@ enc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         for (int a = 0; a < 2; a++) {
             mbar_init(&tfull_bar[a], 1);
             mbar_init(&tempty_bar[a], EG_EPI_THREADS * CS);
+        }
+        for (int i = 0; i < EG_ARES_KB; i++) {
+            mbar_init(&afull_bar[i], CS);
+            mbar_init(&afree_bar[i], 1);
         }
         fence_mbar_init();
     }
@@ -161,6 +233,7 @@ enc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmA);
         tma_prefetch_desc(&tmW);
+        if constexpr (EPI != EPI_RES_LN) tma_prefetch_desc(&tmO);
     }
     tc_fence_before();
     __syncthreads();
@@ -175,13 +248,31 @@ enc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         // ===================== TMA producer =====================
         if (lane == 0) {
             uint32_t st = 0, ph = 0;
-            for (int tile = first_tile; tile < tiles; tile += tile_step) {
-                const int mg = tile / n_tiles, nt = tile - mg * n_tiles;
+            unsigned long long dbg_issue = 0;
+            int mg, nt;
+            for (int q = 0; tile_at(q, mg, nt); q++) {
                 const int mt = mg * (int)CS + (int)crank;
                 for (int kb = 0; kb < KB; kb++) {
-                    mbar_wait(&empty_bar[st], ph ^ 1u);
+                    if constexpr (ARES) {
+                        if (first) {
+                            // the next row group's K-block replaces this one as soon as the last N tile's MMAs over it
+                            // have completed -- while the MMAs over the later K-blocks still run
+                            const uint32_t gph = (uint32_t)grp & 1u;
+                            EG_WAIT(&afree_bar[kb], gph ^ 1u, 1);
+                            if (leader) mbar_expect_tx(&afull_bar[kb], 2u * (uint32_t)EG_A_BYTES);
+                            tma_load_2d_2sm(a_res + kb * EG_A_BYTES, &tmA, kb * EG_BK, mt * EG_BM, &afull_bar[kb]);
+                            if (!leader) mbar_arrive_remote(&afull_bar[kb], 0);
+                        }
+                    }
+                    EG_WAIT(&empty_bar[st], ph ^ 1u, 0);
                     unsigned char* stage = ring + (size_t)st * STAGE;
-                    if constexpr (!PAIR) {
+                    if constexpr (ARES) {
+                        const long long _t1 = p.dbg ? clock64() : 0;
+                        if (leader) mbar_expect_tx(&full_bar[st], 2u * (uint32_t)STAGE);
+                        tma_load_2d_2sm(stage, &tmW, kb * EG_BK, nt * BN + (int)crank * S::B_ROWS, &full_bar[st]);
+                        if (!leader) mbar_arrive_remote(&full_bar[st], 0);
+                        if (p.dbg) dbg_issue += (unsigned long long)(clock64() - _t1);
+                    } else if constexpr (!PAIR) {
                         mbar_expect_tx(&full_bar[st], (uint32_t)STAGE);
                         tma_load_2d(stage, &tmA, kb * EG_BK, mt * EG_BM, &full_bar[st]);
 #pragma unroll
@@ -205,6 +296,11 @@ enc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                     }
                 }
             }
+            if (p.dbg) {
+                p.dbg[blockIdx.x * 8 + 0] = dbg_acc[0];  // producer: waiting for a free ring stage
+                p.dbg[blockIdx.x * 8 + 1] = dbg_acc[1];  //           ... for a free resident-A block
+                p.dbg[blockIdx.x * 8 + 5] = dbg_issue;   //           inside expect_tx + the W load (+ remote arrive)
+            }
         }
     } else if (warp == 1 && leader) {
         // ===================== MMA issuer (converged warp, one elected lane; the pair's leader only) =====================
@@ -212,18 +308,28 @@ enc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         const uint64_t desc_hi = make_smem_desc_sw128(0) & 0xffffffff00000000ull;
         const uint32_t desc_lo0 = (uint32_t)(make_smem_desc_sw128(0) & 0xffffffffull);
         const uint32_t ring_lo = desc_lo0 + ((smem_u32(ring) & 0x3ffffu) >> 4);
+        const uint32_t ares_lo = desc_lo0 + ((smem_u32(a_res) & 0x3ffffu) >> 4);
+        unsigned long long dbg_afull = 0;
         uint32_t st = 0, ph = 0, tcount = 0;
-        for (int tile = first_tile; tile < tiles; tile += tile_step, tcount++) {
+        int mg, nt;
+        for (int q = 0; tile_at(q, mg, nt); q++, tcount++) {
             const uint32_t a = NACC == 2 ? (tcount & 1u) : 0u;
             const uint32_t aph = NACC == 2 ? ((tcount >> 1) & 1u) : (tcount & 1u);
-            mbar_wait(&tempty_bar[a], aph ^ 1u);  // the epilogue (of both CTAs) has drained this accumulator
+            EG_WAIT(&tempty_bar[a], aph ^ 1u, 0);  // the epilogue (of both CTAs) has drained this accumulator
             tc_fence_after();
             const uint32_t d_tmem = tmem_base + a * 256;
             for (int kb = 0; kb < KB; kb++) {
-                mbar_wait(&full_bar[st], ph);
+                if constexpr (ARES) {
+                    if (first) {
+                        const long long _t2 = p.dbg ? clock64() : 0;
+                        mbar_wait(&afull_bar[kb], (uint32_t)grp & 1u);
+                        if (p.dbg) dbg_afull += (unsigned long long)(clock64() - _t2);
+                    }
+                }
+                EG_WAIT(&full_bar[st], ph, 1);
                 tc_fence_after();
-                const uint32_t a_lo = ring_lo + st * (STAGE >> 4);
-                const uint32_t b_lo = a_lo + (EG_A_BYTES >> 4);
+                const uint32_t a_lo = ARES ? ares_lo + kb * (EG_A_BYTES >> 4) : ring_lo + st * (STAGE >> 4);
+                const uint32_t b_lo = ARES ? ring_lo + st * (STAGE >> 4) : a_lo + (EG_A_BYTES >> 4);
                 if (elect_one()) {
 #pragma unroll
                     for (int kk = 0; kk < 4; kk++) {
@@ -237,6 +343,9 @@ enc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                     }
                     if constexpr (PAIR) umma_commit_2sm(&empty_bar[st]);  // frees the stage in both CTAs
                     else umma_commit(&empty_bar[st]);
+                    if constexpr (ARES) {
+                        if (last) umma_commit_2sm(&afree_bar[kb]);  // this row group is done with the K-block
+                    }
                 }
                 __syncwarp();
                 if (++st == STAGES) {
@@ -250,6 +359,13 @@ enc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
             }
             __syncwarp();
         }
+        if (p.dbg && lane == 0) {
+            p.dbg[blockIdx.x * 8 + 2] = dbg_acc[0];  // MMA issuer: waiting for a drained accumulator
+            p.dbg[blockIdx.x * 8 + 3] = dbg_acc[1];  //             ... for operands (ring stages)
+            p.dbg[blockIdx.x * 8 + 4] = dbg_afull;   //             ... for resident-A blocks
+            p.dbg[blockIdx.x * 8 + 6] = (unsigned long long)(clock64() - dbg_t0);
+            p.dbg[blockIdx.x * 8 + 7] = tcount;
+        }
     } else if (warp >= 4) {
         // ===================== epilogue: thread == (output row, column half) =====================
         constexpr int HC = BN / 2;     // columns per thread
@@ -260,7 +376,7 @@ enc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         // Stores go through a 2 KB per-warp transpose: thread = row would write 16 bytes to 32 different rows per
         // instruction (32 partial-sector requests; ncu: the epilogue sat in stall_lg with the LSU queue full).
         // Staged, four lanes cover 64 contiguous bytes of a row and one instruction touches 8 rows.
-        unsigned char* stg = stg_all + (warp - 4) * 2048;
+        unsigned char* stg = stg_all + (warp - 4) * S::STG_WARP;
         const int wrow0 = ((warp - 4) & 3) * 32;  // first tile row of this warp
         auto store32 = [&](const uint32_t (&o)[16], __nv_bfloat16* out_col0, int64_t m_tile0) {
             // o = this lane's row, 32 bf16 columns; out_col0 = out + first global column of the chunk
@@ -277,6 +393,29 @@ enc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                 if (mm < p.M) *reinterpret_cast<uint4*>(out_col0 + (size_t)mm * p.ldo + c * 8) = v;
             }
             __syncwarp();
+        };
+        // 192-wide tiles: the same staged rows (the formula above is the 64-byte-swizzled [32 rows x 64 B] box) leave
+        // through one TMA store per chunk instead of 4 shared loads + 4 global stores per lane: the epilogue's
+        // shared-memory and store traffic had the LSU data pipe at 67 % of its peak (ncu, QKV projection) and set the
+        // tile time, not the MMAs.  Two buffers per warp: a buffer is rewritten once the store before last has read it.
+        uint32_t n_stores = 0;
+        auto store32_tma = [&](const uint32_t (&o)[16], int col0, int64_t m_tile0) {
+            unsigned char* buf = stg + (n_stores & 1u) * 2048;
+            if (n_stores >= 2) {
+                if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+                __syncwarp();
+            }
+#pragma unroll
+            for (int i = 0; i < 4; i++)
+                *reinterpret_cast<uint4*>(buf + lane * 64 + ((i ^ ((lane >> 1) & 3)) << 4)) =
+                    make_uint4(o[4 * i], o[4 * i + 1], o[4 * i + 2], o[4 * i + 3]);
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            __syncwarp();
+            if (lane == 0) {
+                tma_store_2d(&tmO, col0, (int)(m_tile0 + wrow0), buf);
+                bulk_commit_group();
+            }
+            n_stores++;
         };
         // the mirror image for the residual rows: a coalesced read of 32 rows x 64 bytes (res_fetch, issued one
         // chunk ahead so its latency hides under the previous chunk's arithmetic), then every lane picks up its
@@ -302,13 +441,27 @@ enc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
             __syncwarp();
         };
         uint32_t tcount = 0;
-        for (int tile = first_tile; tile < tiles; tile += tile_step, tcount++) {
-            const int mg = tile / n_tiles, nt = tile - mg * n_tiles;
+        int mg, nt;
+        for (int q = 0; tile_at(q, mg, nt); q++, tcount++) {
             const int mt = mg * (int)CS + (int)crank;
             const int n0 = nt * BN + half * HC;  // first global column of this thread
             const uint32_t a = NACC == 2 ? (tcount & 1u) : 0u;
             const uint32_t aph = NACC == 2 ? ((tcount >> 1) & 1u) : (tcount & 1u);
-            mbar_wait(&tfull_bar[a], aph);
+            uint4 gres[4];  // LayerNorm epilogue: residual chunk in flight
+            if constexpr (EPI == EPI_RES_LN) {
+                // This kernel has one accumulator, so these threads idle while the tile's MMAs run: the tile's residual
+                // rows (128 x 768 bytes, last touched a kernel ago) are pulled into L2 now, and the first chunk into
+                // registers -- the epilogue then never waits for HBM (ncu had it in long-scoreboard stalls for half
+                // of its samples).
+                const int64_t m0 = (int64_t)mt * EG_BM;
+                for (int i = et; i < EG_BM * 6; i += EG_EPI_THREADS) {  // 6 lines of 128 bytes per row
+                    const int64_t mm = m0 + i / 6;
+                    if (mm < p.M)
+                        asm volatile("prefetch.global.L2 [%0];" ::"l"(p.residual + (size_t)mm * BN + (i % 6) * 64));
+                }
+                res_fetch(p.residual + half * HC, m0, gres);
+            }
+            EG_WAIT(&tfull_bar[a], aph, 0);
             tc_fence_after();
             const uint32_t acc_addr = lane_addr + a * 256;
             uint32_t r[2][32];
@@ -316,8 +469,6 @@ enc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                 const __nv_bfloat16* res0 = p.residual + half * HC;  // first residual column of this thread
                 const float* bias = par_s + half * HC;
                 float s1 = 0.f, s2 = 0.f;
-                uint4 gres[4];  // residual chunk in flight
-                res_fetch(res0, (int64_t)mt * EG_BM, gres);
                 // one 32-column chunk of pass 1: v = acc + bias + residual, accumulate sum and sum of squares, and
                 // write v back over the accumulator so that pass 2 needs neither the residual nor the bias again
                 auto stats32 = [&](uint32_t (&rv)[32], int ch) {
@@ -407,13 +558,15 @@ enc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                         }
                         o[j] = pack_bf16x2(v0, v1);
                     }
-                    store32(o, p.out + n0 + ch * 32, (int64_t)mt * EG_BM);
+                    store32_tma(o, n0 + ch * 32, (int64_t)mt * EG_BM);
                 }
             }
             tc_fence_before();
             if (leader) mbar_arrive(&tempty_bar[a]);
             else mbar_arrive_remote(&tempty_bar[a], 0);  // the MMA issuer lives in the leader CTA
         }
+        if (lane == 0) bulk_wait_group_read0();  // the last stores have read their staging buffers
+
     }
 
     tc_fence_before();
@@ -426,11 +579,11 @@ enc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     }
 }
 
-template <int EPI, int BN, bool PAIR>
-static int launch_enc_gemm_t(const CUtensorMap& tmA, const CUtensorMap& tmW, const EncGemmParams& p, int num_sms,
-                             cudaStream_t st) {
-    auto kern = enc_gemm_kernel<EPI, BN, PAIR>;
-    using S = EgShape<BN, PAIR>;
+template <int EPI, int BN, bool PAIR, bool ARES>
+static int launch_enc_gemm_t(const CUtensorMap& tmA, const CUtensorMap& tmW, const CUtensorMap& tmO, const EncGemmParams& p,
+                             int num_sms, cudaStream_t st) {
+    auto kern = enc_gemm_kernel<EPI, BN, PAIR, ARES>;
+    using S = EgShape<BN, PAIR, ARES>;
     static bool attr_set[64] = {false};
     int dev = 0;
     BFK_CUDA(cudaGetDevice(&dev));
@@ -439,8 +592,9 @@ static int launch_enc_gemm_t(const CUtensorMap& tmA, const CUtensorMap& tmW, con
         if (dev >= 0 && dev < 64) attr_set[dev] = true;
     }
     constexpr int CS = PAIR ? 2 : 1;
-    const int tiles = ((p.M + CS * EG_BM - 1) / (CS * EG_BM)) * (p.N / BN);
-    const int grid = CS * std::max(1, std::min(tiles, num_sms / CS));
+    const int m_groups = (p.M + CS * EG_BM - 1) / (CS * EG_BM);
+    const int units = m_groups * (p.N / BN);  // tiles
+    const int grid = CS * std::max(1, std::min(units, num_sms / CS));
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)grid);
     cfg.blockDim = dim3(EG_THREADS);
@@ -453,16 +607,42 @@ static int launch_enc_gemm_t(const CUtensorMap& tmA, const CUtensorMap& tmW, con
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    BFK_CUDA(cudaLaunchKernelEx(&cfg, kern, tmA, tmW, p));
+    static const bool debug = getenv("BFK_ENC_GEMM_DEBUG") != nullptr;
+    if (debug) {  // synchronous: where each role of each CTA waited, on stderr
+        EncGemmParams pd = p;
+        BFK_CUDA(cudaMalloc((void**)&pd.dbg, (size_t)grid * 128));
+        BFK_CUDA(cudaMemset(pd.dbg, 0, (size_t)grid * 128));
+        BFK_CUDA(cudaLaunchKernelEx(&cfg, kern, tmA, tmW, tmO, pd));
+        BFK_CUDA(cudaStreamSynchronize(st));
+        std::vector<unsigned long long> h((size_t)grid * 16);
+        BFK_CUDA(cudaMemcpy(h.data(), pd.dbg, (size_t)grid * 128, cudaMemcpyDeviceToHost));
+        double a[8] = {0};
+        int nl = 0;
+        for (int i = 0; i < grid; i += CS) {  // leaders
+            for (int k = 0; k < 8; k++) a[k] += (double)h[(size_t)i * 8 + k];
+            nl++;
+        }
+        fprintf(stderr,
+                "[bfk enc gemm EPI=%d BN=%d pair=%d ares=%d M=%d N=%d K=%d] per leader CTA, cycles: life %.0f tiles %.1f | producer waits "
+                "ring %.0f a-block %.0f, issuing W loads %.0f | mma waits accumulator %.0f ring stages %.0f a-blocks %.0f\n",
+                EPI, BN, (int)PAIR, (int)ARES, p.M, p.N, p.K, a[6] / nl, a[7] / nl, a[0] / nl, a[1] / nl, a[5] / nl, a[2] / nl, a[3] / nl,
+                a[4] / nl);
+        return 0;
+    }
+    BFK_CUDA(cudaLaunchKernelEx(&cfg, kern, tmA, tmW, tmO, p));
     BFK_CUDA(cudaGetLastError());
     return 0;
 }
 
+// mode: 0 = single CTAs, 1 = CTA pairs, 2 = CTA pairs with the A tile resident across the N tiles
 template <int EPI, int BN>
-static int launch_enc_gemm_p(bool pair, const CUtensorMap& tmA, const CUtensorMap& tmW, const EncGemmParams& p, int num_sms,
-                             cudaStream_t st) {
-    return pair ? launch_enc_gemm_t<EPI, BN, true>(tmA, tmW, p, num_sms, st)
-                : launch_enc_gemm_t<EPI, BN, false>(tmA, tmW, p, num_sms, st);
+static int launch_enc_gemm_p(int mode, const CUtensorMap& tmA, const CUtensorMap& tmW, const CUtensorMap& tmO,
+                             const EncGemmParams& p, int num_sms, cudaStream_t st) {
+    if constexpr (BN == 192) {
+        if (mode == 2) return launch_enc_gemm_t<EPI, BN, true, true>(tmA, tmW, tmO, p, num_sms, st);
+    }
+    return mode >= 1 ? launch_enc_gemm_t<EPI, BN, true, false>(tmA, tmW, tmO, p, num_sms, st)
+                     : launch_enc_gemm_t<EPI, BN, false, false>(tmA, tmW, tmO, p, num_sms, st);
 }
 
 // A [M, K] bf16 (ld = K), W [N, K] bf16 (ld = K); out [M, ldo] bf16
@@ -482,8 +662,18 @@ int launch_enc_gemm(int epi, const __nv_bfloat16* A, const __nv_bfloat16* W, int
         return e ? atoi(e) != 0 : true;
     }();
     const bool pair = pair_on && M > EG_BM;
-    CUtensorMap tmA, tmW;
+    // With K = 384 a CTA's whole 128 x K slice of A fits beside the ring: it is loaded once per row group instead of
+    // once per N tile (QKV: 6 tiles, intermediate: 8), which halves what the pair pulls through L2.  BFK_ENC_ARES=0
+    // keeps the streamed form.
+    static const bool ares_on = [] {
+        const char* e = getenv("BFK_ENC_ARES");
+        return e ? atoi(e) != 0 : true;
+    }();
+    const int mode = !pair ? 0 : (ares_on && K == EG_ARES_KB * EG_BK && epi != EPI_RES_LN && N > 192) ? 2 : 1;
+    CUtensorMap tmA, tmW, tmO;
     BFK_TRY(make_tmap(&tmA, A, M, K, EG_BM));
+    if (epi == EPI_RES_LN) tmO = CUtensorMap();  // unused: the LayerNorm tiles store from registers
+    else BFK_TRY(make_tmap_head(&tmO, out, M, ldo, 32));
     BFK_TRY(make_tmap(&tmW, W, N, K, pair ? 96 : (epi == EPI_RES_LN ? 128 : 192)));
     EncGemmParams p;
     p.M = M;
@@ -496,17 +686,18 @@ int launch_enc_gemm(int epi, const __nv_bfloat16* A, const __nv_bfloat16* W, int
     p.eps = eps;
     p.out = out;
     p.ldo = ldo;
+    p.dbg = nullptr;
     switch (epi) {
-        case EPI_BIAS: return launch_enc_gemm_p<EPI_BIAS, 192>(pair, tmA, tmW, p, num_sms, st);
+        case EPI_BIAS: return launch_enc_gemm_p<EPI_BIAS, 192>(mode, tmA, tmW, tmO, p, num_sms, st);
         case EPI_GELU: {
             static const bool erf = [] {
                 const char* e = getenv("BFK_ENC_GELU");
                 return e && e[0] == 'e';
             }();
-            return erf ? launch_enc_gemm_p<EPI_GELU_ERF, 192>(pair, tmA, tmW, p, num_sms, st)
-                       : launch_enc_gemm_p<EPI_GELU, 192>(pair, tmA, tmW, p, num_sms, st);
+            return erf ? launch_enc_gemm_p<EPI_GELU_ERF, 192>(mode, tmA, tmW, tmO, p, num_sms, st)
+                       : launch_enc_gemm_p<EPI_GELU, 192>(mode, tmA, tmW, tmO, p, num_sms, st);
         }
-        case EPI_RES_LN: return launch_enc_gemm_p<EPI_RES_LN, 384>(pair, tmA, tmW, p, num_sms, st);
+        case EPI_RES_LN: return launch_enc_gemm_p<EPI_RES_LN, 384>(mode, tmA, tmW, tmO, p, num_sms, st);
         default: return fail("encoder gemm: unknown epilogue");
     }
 }
