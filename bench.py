@@ -627,13 +627,15 @@ def run_c4e(args):
         "config": {"workload": f"c4e: {B} chunks x {T} tokens, BERT 6x384 (12 heads, 1536) random weights -> mean pool -> index.add",
                    "l2_policy": "4 rotating id buffers; activations of a step (2 GB) far exceed the 126 MB L2"},
         "e2e": {"value": B / (ms_e2e * 1e-3), "unit": "chunks/s", "h2d_bytes_per_step": B * T * 16, "d2h_bytes_per_step": 8},
-        "gpu_launches": steps * (1 + 5 * L + 1), "clocks": clocks,
-        "roofline": {"bound": "tensor", "kernel": "enc_gemm_kernel (+ enc_attention_kernel)", "achieved": ach, "peak": pk["tf"],
+        # per micro-batch of 131072 tokens: embed + 5 kernels per layer + pool/append
+        "gpu_launches": steps * -(-B * T // 131072) * (1 + 5 * L + 1), "clocks": clocks,
+        "roofline": {"bound": "tensor", "kernel": "enc_gemm_kernel (+ enc_attention_pws_kernel)", "achieved": ach, "peak": pk["tf"],
                      "unit": "TFLOP/s", "frac": ach / pk["tf"], "frac_of_spec": ach / SPEC_BF16_TFLOPS,
                      "frac_of_sustained": (ach / pk["tf_sustained"]) if pk["tf_sustained"] else None,
                      "peak_kind": pk["kind"] + " burst bf16 GEMM", "flops_per_launch": (gemm_flop + attn_flop) * B,
                      "launch_ms": ms, "traffic": None,
-                     "note": "whole forward pass (31 launches) against the tensor peak; per-kernel split in profiles/"},
+                     "note": "whole forward pass (32 launches per 512-chunk micro-batch) against the tensor peak; per-kernel "
+                             "split in profiles/r02_launches_encoder.csv"},
         "cpu_baseline": None,
     }
 
