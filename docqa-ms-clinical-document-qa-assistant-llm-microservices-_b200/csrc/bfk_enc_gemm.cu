@@ -469,6 +469,7 @@ enc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                 const __nv_bfloat16* res0 = p.residual + half * HC;  // first residual column of this thread
                 const float* bias = par_s + half * HC;
                 float s1 = 0.f, s2 = 0.f;
+                const long long _e0 = p.dbg ? clock64() : 0;
                 // one 32-column chunk of pass 1: v = acc + bias + residual, accumulate sum and sum of squares, and
                 // write v back over the accumulator so that pass 2 needs neither the residual nor the bias again
                 auto stats32 = [&](uint32_t (&rv)[32], int ch) {
@@ -503,9 +504,11 @@ enc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                     stats32(r[1], ch + 1);
                 }
                 tmem_st_wait();
+                const long long _e1 = p.dbg ? clock64() : 0;
                 float2* part = ln_part + (tcount & 1u) * 256;
                 part[half * 128 + row] = make_float2(s1, s2);
                 eg_epi_sync();
+                const long long _e2 = p.dbg ? clock64() : 0;
                 const float2 other = part[(half ^ 1) * 128 + row];
                 s1 += other.x;
                 s2 += other.y;
@@ -534,6 +537,12 @@ enc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                     tmem_ld_wait();
                     if (ch + 2 < NCH) tmem_ld_32x32(acc_addr + (ch + 2) * 32, r[0]);
                     norm32(r[1], ch + 1);
+                }
+                if (p.dbg && et == 0) {  // row 0: cycles in pass 1, at the row-statistics barrier, in pass 2
+                    unsigned long long* d = p.dbg + (size_t)gridDim.x * 8 + blockIdx.x * 8;
+                    d[0] += (unsigned long long)(_e1 - _e0);
+                    d[1] += (unsigned long long)(_e2 - _e1);
+                    d[2] += (unsigned long long)(clock64() - _e2);
                 }
             } else {
                 const float* bias = bias_s + n0;
@@ -616,6 +625,13 @@ static int launch_enc_gemm_t(const CUtensorMap& tmA, const CUtensorMap& tmW, con
         BFK_CUDA(cudaStreamSynchronize(st));
         std::vector<unsigned long long> h((size_t)grid * 16);
         BFK_CUDA(cudaMemcpy(h.data(), pd.dbg, (size_t)grid * 128, cudaMemcpyDeviceToHost));
+        if (EPI == EPI_RES_LN) {
+            double e[3] = {0, 0, 0};
+            for (int i = 0; i < grid; i += CS)
+                for (int k = 0; k < 3; k++) e[k] += (double)h[(size_t)grid * 8 + (size_t)i * 8 + k];
+            fprintf(stderr, "[bfk enc gemm] LayerNorm epilogue, row 0 of the leader CTAs, cycles per CTA: pass 1 %.0f, statistics barrier %.0f, pass 2 %.0f\n",
+                    e[0] / (grid / CS), e[1] / (grid / CS), e[2] / (grid / CS));
+        }
         double a[8] = {0};
         int nl = 0;
         for (int i = 0; i < grid; i += CS) {  // leaders
