@@ -1053,10 +1053,11 @@ enc_attention_pws_kernel(const __grid_constant__ CUtensorMap tmQKV, const EncAtt
 #pragma unroll
                     for (int hh = 0; hh < 2; hh++) {
                         if (unmasked) {
+                            const uint64_t scale2 = f2_pack(scale, scale), nmx2 = f2_pack(neg_mx, neg_mx);
 #pragma unroll
-                            for (int jj = 0; jj < 16; jj++) {
-                                const float x0 = fmaf(__uint_as_float(r[hh][2 * jj]), scale, neg_mx);
-                                const float x1 = fmaf(__uint_as_float(r[hh][2 * jj + 1]), scale, neg_mx);
+                            for (int jj = 0; jj < 16; jj++) {  // s * scale - mx for two keys per FFMA2
+                                float x0, x1;
+                                f2_unpack(f2_fma(f2_pack_bits(r[hh][2 * jj], r[hh][2 * jj + 1]), scale2, nmx2), x0, x1);
                                 pk[hh * 16 + jj] = pack_bf16x2_rn(ex2_fast(x0), ex2_fast(x1));
                             }
                         } else {

@@ -233,7 +233,7 @@ enc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmA);
         tma_prefetch_desc(&tmW);
-        if constexpr (EPI != EPI_RES_LN) tma_prefetch_desc(&tmO);
+        tma_prefetch_desc(&tmO);
     }
     tc_fence_before();
     __syncthreads();
@@ -399,10 +399,14 @@ enc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         // shared-memory and store traffic had the LSU data pipe at 67 % of its peak (ncu, QKV projection) and set the
         // tile time, not the MMAs.  Two buffers per warp: a buffer is rewritten once the store before last has read it.
         uint32_t n_stores = 0;
+        constexpr int NBUF = S::STG_WARP / 2048;  // staging buffers per warp
         auto store32_tma = [&](const uint32_t (&o)[16], int col0, int64_t m_tile0) {
-            unsigned char* buf = stg + (n_stores & 1u) * 2048;
-            if (n_stores >= 2) {
-                if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+            unsigned char* buf = stg + (n_stores % NBUF) * 2048;
+            if (n_stores >= NBUF) {
+                if (lane == 0) {
+                    if constexpr (NBUF == 2) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+                    else asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+                }
                 __syncwarp();
             }
 #pragma unroll
@@ -466,9 +470,12 @@ enc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
             const uint32_t acc_addr = lane_addr + a * 256;
             uint32_t r[2][32];
             if constexpr (EPI == EPI_RES_LN) {
+                if (lane == 0) bulk_wait_group_read0();  // the previous tile's stores have read the staging buffer
+                __syncwarp();
                 const __nv_bfloat16* res0 = p.residual + half * HC;  // first residual column of this thread
                 const float* bias = par_s + half * HC;
                 float s1 = 0.f, s2 = 0.f;
+                uint64_t s1_2 = 0ull, s2_2 = 0ull;  // (even, odd) column partial sums
                 const long long _e0 = p.dbg ? clock64() : 0;
                 // one 32-column chunk of pass 1: v = acc + bias + residual, accumulate sum and sum of squares, and
                 // write v back over the accumulator so that pass 2 needs neither the residual nor the bias again
@@ -478,14 +485,18 @@ enc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                     if (ch + 1 < NCH) res_fetch(res0 + (ch + 1) * 32, (int64_t)mt * EG_BM, gres);
                     const uint32_t* rw = reinterpret_cast<const uint32_t*>(rr);
 #pragma unroll
-                    for (int j = 0; j < 16; j++) {
-                        const float2 bb = reinterpret_cast<const float2*>(bias + ch * 32)[j];
-                        const float v0 = __uint_as_float(rv[2 * j]) + bb.x + __uint_as_float(rw[j] << 16);
-                        const float v1 = __uint_as_float(rv[2 * j + 1]) + bb.y + __uint_as_float(rw[j] & 0xffff0000u);
-                        s1 += v0 + v1;
-                        s2 = fmaf(v0, v0, fmaf(v1, v1, s2));
-                        rv[2 * j] = __float_as_uint(v0);
-                        rv[2 * j + 1] = __float_as_uint(v1);
+                    for (int j = 0; j < 16; j += 2) {  // four columns per round, two-wide fp32 arithmetic
+                        const float4 bb = reinterpret_cast<const float4*>(bias + ch * 32)[j >> 1];
+#pragma unroll
+                        for (int k = 0; k < 2; k++) {
+                            const uint64_t acc2 = f2_pack_bits(rv[2 * (j + k)], rv[2 * (j + k) + 1]);
+                            const uint64_t b2 = k == 0 ? f2_pack(bb.x, bb.y) : f2_pack(bb.z, bb.w);
+                            const uint64_t res2 = f2_pack_bits(rw[j + k] << 16, rw[j + k] & 0xffff0000u);
+                            const uint64_t v2 = f2_add(f2_add(acc2, b2), res2);
+                            s1_2 = f2_add(s1_2, v2);
+                            s2_2 = f2_fma(v2, v2, s2_2);
+                            f2_unpack_bits(v2, rv[2 * (j + k)], rv[2 * (j + k) + 1]);
+                        }
                     }
                     tmem_st_32x32(acc_addr + ch * 32, rv);
                 };
@@ -504,6 +515,13 @@ enc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                     stats32(r[1], ch + 1);
                 }
                 tmem_st_wait();
+                {
+                    float a0, a1, b0, b1;
+                    f2_unpack(s1_2, a0, a1);
+                    f2_unpack(s2_2, b0, b1);
+                    s1 = a0 + a1;
+                    s2 = b0 + b1;
+                }
                 const long long _e1 = p.dbg ? clock64() : 0;
                 float2* part = ln_part + (tcount & 1u) * 256;
                 part[half * 128 + row] = make_float2(s1, s2);
@@ -517,16 +535,25 @@ enc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                 const float rstd = rsqrtf(var + p.eps);
                 const float* gamma = par_s + BN + half * HC;
                 const float* beta = par_s + 2 * BN + half * HC;
+                // (v - mean) rstd gamma + beta as two two-wide FMAs: v * rstd + (-mean rstd), then * gamma + beta
+                const uint64_t a2 = f2_pack(rstd, rstd), b2 = f2_pack(-mean * rstd, -mean * rstd);
                 auto norm32 = [&](const uint32_t (&rv)[32], int ch) {
                     uint32_t o[16];
 #pragma unroll
-                    for (int j = 0; j < 16; j++) {
-                        const float2 gg = reinterpret_cast<const float2*>(gamma + ch * 32)[j];
-                        const float2 be = reinterpret_cast<const float2*>(beta + ch * 32)[j];
-                        const float v0 = __uint_as_float(rv[2 * j]), v1 = __uint_as_float(rv[2 * j + 1]);
-                        o[j] = pack_bf16x2(fmaf((v0 - mean) * rstd, gg.x, be.x), fmaf((v1 - mean) * rstd, gg.y, be.y));
+                    for (int j = 0; j < 16; j += 2) {
+                        const float4 gg = reinterpret_cast<const float4*>(gamma + ch * 32)[j >> 1];
+                        const float4 be = reinterpret_cast<const float4*>(beta + ch * 32)[j >> 1];
+#pragma unroll
+                        for (int k = 0; k < 2; k++) {
+                            const uint64_t t2 = f2_fma(f2_pack_bits(rv[2 * (j + k)], rv[2 * (j + k) + 1]), a2, b2);
+                            const uint64_t y2 = f2_fma(t2, k == 0 ? f2_pack(gg.x, gg.y) : f2_pack(gg.z, gg.w),
+                                                       k == 0 ? f2_pack(be.x, be.y) : f2_pack(be.z, be.w));
+                            float y0, y1;
+                            f2_unpack(y2, y0, y1);
+                            o[j + k] = pack_bf16x2(y0, y1);
+                        }
                     }
-                    store32(o, p.out + half * HC + ch * 32, (int64_t)mt * EG_BM);
+                    store32_tma(o, half * HC + ch * 32, (int64_t)mt * EG_BM);
                 };
                 tmem_ld_32x32(acc_addr, r[0]);
 #pragma unroll 1
@@ -553,19 +580,32 @@ enc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                     if (ch + 1 < NCH) tmem_ld_32x32(acc_addr + (ch + 1) * 32, r[(ch + 1) & 1]);
                     uint32_t o[16];
 #pragma unroll
-                    for (int j = 0; j < 16; j++) {
-                        const float2 bb = reinterpret_cast<const float2*>(bias + ch * 32)[j];
-                        float v0 = __uint_as_float(r[ch & 1][2 * j]) + bb.x;
-                        float v1 = __uint_as_float(r[ch & 1][2 * j + 1]) + bb.y;
-                        if constexpr (EPI == EPI_GELU) {
-                            v0 = gelu_tanh(v0);
-                            v1 = gelu_tanh(v1);
+                    for (int j = 0; j < 16; j += 2) {  // four columns per round, two-wide fp32 arithmetic
+                        const float4 bb = reinterpret_cast<const float4*>(bias + ch * 32)[j >> 1];
+#pragma unroll
+                        for (int k = 0; k < 2; k++) {
+                            const uint64_t x2 = f2_add(f2_pack_bits(r[ch & 1][2 * (j + k)], r[ch & 1][2 * (j + k) + 1]),
+                                                       k == 0 ? f2_pack(bb.x, bb.y) : f2_pack(bb.z, bb.w));
+                            float v0, v1;
+                            if constexpr (EPI == EPI_GELU) {
+                                // gelu_tanh on the pair: u = x (c1 x^2 + c0), 0.5 x (1 + tanh u)
+                                const uint64_t w2 = f2_fma(f2_mul(x2, x2), f2_pack(0.0356774081f, 0.0356774081f),
+                                                           f2_pack(0.7978845608f, 0.7978845608f));
+                                float u0, u1, t0, t1;
+                                f2_unpack(f2_mul(x2, w2), u0, u1);
+                                asm("tanh.approx.f32 %0, %1;" : "=f"(t0) : "f"(u0));
+                                asm("tanh.approx.f32 %0, %1;" : "=f"(t1) : "f"(u1));
+                                const uint64_t hx2 = f2_mul(x2, f2_pack(0.5f, 0.5f));
+                                f2_unpack(f2_fma(hx2, f2_pack(t0, t1), hx2), v0, v1);
+                            } else {
+                                f2_unpack(x2, v0, v1);
+                                if constexpr (EPI == EPI_GELU_ERF) {
+                                    v0 = gelu_erf(v0);
+                                    v1 = gelu_erf(v1);
+                                }
+                            }
+                            o[j + k] = pack_bf16x2(v0, v1);
                         }
-                        if constexpr (EPI == EPI_GELU_ERF) {
-                            v0 = gelu_erf(v0);
-                            v1 = gelu_erf(v1);
-                        }
-                        o[j] = pack_bf16x2(v0, v1);
                     }
                     store32_tma(o, n0 + ch * 32, (int64_t)mt * EG_BM);
                 }
@@ -688,8 +728,7 @@ int launch_enc_gemm(int epi, const __nv_bfloat16* A, const __nv_bfloat16* W, int
     const int mode = !pair ? 0 : (ares_on && K == EG_ARES_KB * EG_BK && epi != EPI_RES_LN && N > 192) ? 2 : 1;
     CUtensorMap tmA, tmW, tmO;
     BFK_TRY(make_tmap(&tmA, A, M, K, EG_BM));
-    if (epi == EPI_RES_LN) tmO = CUtensorMap();  // unused: the LayerNorm tiles store from registers
-    else BFK_TRY(make_tmap_head(&tmO, out, M, ldo, 32));
+    BFK_TRY(make_tmap_head(&tmO, out, M, ldo, 32));
     BFK_TRY(make_tmap(&tmW, W, N, K, pair ? 96 : (epi == EPI_RES_LN ? 128 : 192)));
     EncGemmParams p;
     p.M = M;
