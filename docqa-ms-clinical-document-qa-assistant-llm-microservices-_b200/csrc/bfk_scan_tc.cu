@@ -471,16 +471,15 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
             // 16 columns at a time, kept as a rolled loop (two register sets, next load in flight while
             // the current set is filtered): the fully unrolled form of this loop was 58 KB of SASS and
             // stalled on instruction fetch
+            const uint64_t scale2 = f2_pack(scale, scale);
             auto process16 = [&](const uint32_t (&r)[16], int c0) {
                 const float4* b4 = reinterpret_cast<const float4*>(bias + c0);
                 float kk[16];
 #pragma unroll
-                for (int j4 = 0; j4 < 4; j4++) {
+                for (int j4 = 0; j4 < 4; j4++) {  // key = scale * dot + bias, two columns per FFMA2 (same rounding as fmaf)
                     const float4 b = b4[j4];
-                    kk[4 * j4 + 0] = fmaf(scale, __uint_as_float(r[4 * j4 + 0]), b.x);
-                    kk[4 * j4 + 1] = fmaf(scale, __uint_as_float(r[4 * j4 + 1]), b.y);
-                    kk[4 * j4 + 2] = fmaf(scale, __uint_as_float(r[4 * j4 + 2]), b.z);
-                    kk[4 * j4 + 3] = fmaf(scale, __uint_as_float(r[4 * j4 + 3]), b.w);
+                    f2_unpack(f2_fma(scale2, f2_pack_bits(r[4 * j4 + 0], r[4 * j4 + 1]), f2_pack(b.x, b.y)), kk[4 * j4 + 0], kk[4 * j4 + 1]);
+                    f2_unpack(f2_fma(scale2, f2_pack_bits(r[4 * j4 + 2], r[4 * j4 + 3]), f2_pack(b.z, b.w)), kk[4 * j4 + 2], kk[4 * j4 + 3]);
                 }
                 // per-quad minima: the slow path below only touches quads that hold a survivor
                 float m4[4];
