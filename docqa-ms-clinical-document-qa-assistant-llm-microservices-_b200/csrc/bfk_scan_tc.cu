@@ -34,6 +34,8 @@
 // at large nq.  Algorithmic bytes per launch: N*ld16*2 + N*4 (norms, L2) + nq*d*2 + lists.
 #include <cuda.h>
 
+#include <type_traits>
+
 #include <cfloat>
 #include <cstdlib>
 #include <cstring>
@@ -472,20 +474,32 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
             // the current set is filtered): the fully unrolled form of this loop was 58 KB of SASS and
             // stalled on instruction fetch
             const uint64_t scale2 = f2_pack(scale, scale);
-            auto process16 = [&](const uint32_t (&r)[16], int c0) {
-                const float4* b4 = reinterpret_cast<const float4*>(bias + c0);
-                float kk[16];
+            // NOBIAS (inner product, no selector, not the ragged last tile): the key is just -dot, so the 16 FMAs and
+            // the four bias loads of a group are not needed to find out that it holds no survivor
+            auto process16 = [&](const uint32_t (&r)[16], int c0, auto nobias) {
+                constexpr bool NOBIAS = decltype(nobias)::value;
+                float kk[16], m4[4];  // keys, and per-quad minima: the slow path below only touches quads that hold a survivor
+                if constexpr (NOBIAS) {
+                    // min of the keys of a quad = -(max of its dots); the keys themselves (0 - dot, the value the FMA
+                    // with a zero bias gives, signed zeros included) are only formed where they are stored
 #pragma unroll
-                for (int j4 = 0; j4 < 4; j4++) {  // key = scale * dot + bias, two columns per FFMA2 (same rounding as fmaf)
-                    const float4 b = b4[j4];
-                    f2_unpack(f2_fma(scale2, f2_pack_bits(r[4 * j4 + 0], r[4 * j4 + 1]), f2_pack(b.x, b.y)), kk[4 * j4 + 0], kk[4 * j4 + 1]);
-                    f2_unpack(f2_fma(scale2, f2_pack_bits(r[4 * j4 + 2], r[4 * j4 + 3]), f2_pack(b.z, b.w)), kk[4 * j4 + 2], kk[4 * j4 + 3]);
+                    for (int j4 = 0; j4 < 4; j4++)
+                        m4[j4] = 0.f - fmaxf(fmaxf(__uint_as_float(r[4 * j4 + 0]), __uint_as_float(r[4 * j4 + 1])),
+                                             fmaxf(__uint_as_float(r[4 * j4 + 2]), __uint_as_float(r[4 * j4 + 3])));
+#pragma unroll
+                    for (int i = 0; i < 16; i++) kk[i] = 0.f - __uint_as_float(r[i]);
+                } else {
+                    const float4* b4 = reinterpret_cast<const float4*>(bias + c0);
+#pragma unroll
+                    for (int j4 = 0; j4 < 4; j4++) {  // key = scale * dot + bias, two columns per FFMA2 (same rounding as fmaf)
+                        const float4 b = b4[j4];
+                        f2_unpack(f2_fma(scale2, f2_pack_bits(r[4 * j4 + 0], r[4 * j4 + 1]), f2_pack(b.x, b.y)), kk[4 * j4 + 0], kk[4 * j4 + 1]);
+                        f2_unpack(f2_fma(scale2, f2_pack_bits(r[4 * j4 + 2], r[4 * j4 + 3]), f2_pack(b.z, b.w)), kk[4 * j4 + 2], kk[4 * j4 + 3]);
+                    }
+#pragma unroll
+                    for (int j4 = 0; j4 < 4; j4++)
+                        m4[j4] = fminf(fminf(kk[4 * j4 + 0], kk[4 * j4 + 1]), fminf(kk[4 * j4 + 2], kk[4 * j4 + 3]));
                 }
-                // per-quad minima: the slow path below only touches quads that hold a survivor
-                float m4[4];
-#pragma unroll
-                for (int j4 = 0; j4 < 4; j4++)
-                    m4[j4] = fminf(fminf(kk[4 * j4 + 0], kk[4 * j4 + 1]), fminf(kk[4 * j4 + 2], kk[4 * j4 + 3]));
                 const float kmin = fminf(fminf(m4[0], m4[1]), fminf(m4[2], m4[3]));
                 // after the first tiles most groups of 16 have no survivor in any lane.  The lanes of a warp
                 // are 32 different queries with 32 different thresholds, so once one lane has a survivor the
@@ -522,14 +536,26 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
             };
             uint32_t ra[16], rb[16];
             tmem_ld_32x16(taddr, ra);
+            if (!p.is_l2 && !p.use_bias && (t + 1) * TC_BN <= p.n) {
 #pragma unroll 1
-            for (int sc = 0; sc < 8; sc += 2) {
-                tmem_ld_wait();
-                tmem_ld_32x16(taddr + (sc + 1) * 16, rb);
-                process16(ra, sc * 16);
-                tmem_ld_wait();
-                if (sc + 2 < 8) tmem_ld_32x16(taddr + (sc + 2) * 16, ra);
-                process16(rb, (sc + 1) * 16);
+                for (int sc = 0; sc < 8; sc += 2) {
+                    tmem_ld_wait();
+                    tmem_ld_32x16(taddr + (sc + 1) * 16, rb);
+                    process16(ra, sc * 16, std::true_type());
+                    tmem_ld_wait();
+                    if (sc + 2 < 8) tmem_ld_32x16(taddr + (sc + 2) * 16, ra);
+                    process16(rb, (sc + 1) * 16, std::true_type());
+                }
+            } else {
+#pragma unroll 1
+                for (int sc = 0; sc < 8; sc += 2) {
+                    tmem_ld_wait();
+                    tmem_ld_32x16(taddr + (sc + 1) * 16, rb);
+                    process16(ra, sc * 16, std::false_type());
+                    tmem_ld_wait();
+                    if (sc + 2 < 8) tmem_ld_32x16(taddr + (sc + 2) * 16, ra);
+                    process16(rb, (sc + 1) * 16, std::false_type());
+                }
             }
             tc_fence_before();
             mbar_arrive(&tlocal_bar[a]);
