@@ -1284,7 +1284,7 @@ enc_attention_pws_kernel(const __grid_constant__ CUtensorMap tmQKV, const EncAtt
             for (int j = 0; j < NB; j++) {
                 if (!((act >> j) & 1u)) continue;
                 if (idx == 2 && !meta_done) {  // two V blocks are under way: time for the next item's meta
-                    make_meta(nxt, n_it + 1, use0);
+                    make_meta(nxt, n_it + 1, 0);  // (the second block's slot wait has already seen the previous item out)
                     meta_done = true;
                 }
                 if (lane == 0) {
@@ -1297,7 +1297,9 @@ enc_attention_pws_kernel(const __grid_constant__ CUtensorMap tmQKV, const EncAtt
                 vuse++;
                 idx++;
             }
-            if (!meta_done) make_meta(nxt, n_it + 1, use0);
+            // with a single block issued, nothing has waited for the previous item's last product yet -- and no new use
+            // of that product's slot exists, so waiting for its phase here cannot be overtaken by the next one
+            if (!meta_done) make_meta(nxt, n_it + 1, idx >= 2 ? 0 : use0);
         }
     }
 
