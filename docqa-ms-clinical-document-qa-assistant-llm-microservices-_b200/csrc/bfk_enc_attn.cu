@@ -1,8 +1,15 @@
-// E1 `enc_embed_ln_kernel`, E3 `enc_attention_kernel`: the non-GEMM parts of the sentence encoder
+// E1 `enc_embed_ln_kernel`, E3 attention: the non-GEMM parts of the sentence encoder
 // (transformers BertEmbeddings and BertSelfAttention as run by
 // SentenceTransformer('all-MiniLM-L6-v2') for semantic-indexer/indexer.py:21,37 and llm-qa/main.py:25).
 //
-// E3, one CTA per (128-query tile, head, chunk), 8 warps, two threads per query row (row == TMEM lane; each
+// Four attention kernels live here, in the order they were written; the last one ships, the others stay selectable
+// (BFK_ENC_ATTN=row|blk|ws) and tested, as the measured steps between them:
+//   enc_attention_kernel      whole 128 x T score tile in TMEM                       465 us per layer (512 chunks x 256 tokens)
+//   enc_attention_blk_kernel  64-key blocks, four CTAs per SM, one softmax shift      344 -> 287 us
+//   enc_attention_ws_kernel   warp-specialised roles over mbarriers, TMA staging     217 us
+//   enc_attention_pws_kernel  the same in persistent CTAs with the next item prefetched  198 us
+//
+// enc_attention_kernel: one CTA per (128-query tile, head, chunk), 8 warps, two threads per query row (row == TMEM lane; each
 // owns half of the key columns and exchanges its row max / row sum with its partner through shared memory):
 //   1. Q [128 x 32], K [T x 32] and V^T [32 x T] of this head are written into shared memory in the
 //      128-byte-swizzled K-major layout tcgen05 reads (the rows are 64 bytes, so the upper half of each
