@@ -10,6 +10,7 @@
 // Per layer: E2 GEMM (QKV, bias) -> E3 attention -> E2 GEMM (+ residual + LayerNorm) -> E2 GEMM (GELU)
 //            -> E2 GEMM (+ residual + LayerNorm); E1 embeds; K1 pools.  Chunks are processed in micro-batches
 // so the activations (7.7 KB per token) stay bounded.
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -118,7 +119,13 @@ static int forward_rows(Encoder* e, const int64_t* ids, const void* mask, int ma
 
 static int64_t micro_batch(const Encoder* e, int T) {
     (void)e;
-    return std::max<int64_t>(1, (int64_t)(1 << 17) / T);  // <= 131072 tokens (1 GB of activations) per pass
+    // tokens per pass (7.7 KB of activations each); BFK_ENC_MB_TOKENS overrides the default for experiments
+    static const int64_t tokens = [] {
+        const char* s = getenv("BFK_ENC_MB_TOKENS");
+        const long long v = s ? atoll(s) : 0;
+        return (int64_t)(v >= 256 ? v : (1 << 17));
+    }();
+    return std::max<int64_t>(1, tokens / T);
 }
 
 }  // namespace bfk
