@@ -27,9 +27,10 @@
 //   PAIR  two CTAs as one tcgen05.mma.cta_group::2 (M = 256): each CTA stages its own 128 rows of A and half of
 //         every W block.  A lone CTA pulled 40 KB through L2 per 128 x 192 x 64 of MMA work and all four layer
 //         shapes sat at the L2 slices' throughput limit (2.0 GB in 169 us for the intermediate layer).
-//   ARES  (K = 384, 192-wide tiles) the CTA's 128 x 384 slice of A stays in shared memory while the pair sweeps
-//         the N tiles of its rows; the ring carries W blocks only.  Each pair owns a contiguous range of the
-//         row-group-major tile sequence, so pairs change row groups at different times.
+//   ARES  (K = 384, 192-wide tiles; BFK_ENC_ARES=1, off by default: measured 5-7 % slower) the CTA's 128 x 384 slice
+//         of A stays in shared memory while the pair sweeps the N tiles of its rows; the ring carries W blocks
+//         only.  Each pair owns a contiguous range of the row-group-major tile sequence, so pairs change row groups
+//         at different times.
 //   All tiles store through TMA (one 32 x 32 box per chunk and warp) instead of 4 shared loads + 4 global
 //         stores per lane: the LSU data pipe was the busiest unit of the QKV projection (67 % of peak), and pass 2
 //         of the LayerNorm epilogue went from 7.4-8 k to 5.2-5.8 k cycles per tile.
@@ -720,12 +721,14 @@ int launch_enc_gemm(int epi, const __nv_bfloat16* A, const __nv_bfloat16* W, int
         return e ? atoi(e) != 0 : true;
     }();
     const bool pair = pair_on && M > EG_BM;
-    // With K = 384 a CTA's whole 128 x K slice of A fits beside the ring: it is loaded once per row group instead of
-    // once per N tile (QKV: 6 tiles, intermediate: 8), which halves what the pair pulls through L2.  BFK_ENC_ARES=0
-    // keeps the streamed form.
+    // With K = 384 a CTA's whole 128 x K slice of A fits beside the ring: loaded once per row group instead of once
+    // per N tile (QKV: 6 tiles, intermediate: 8), it halves what the pair pulls through L2.  Measured with everything
+    // else in place it LOSES 5-7 % of CTA life (QKV 164.6 k vs 155.8 k cycles, intermediate 218.5 k vs 202.6 k:
+    // profiles/r02_enc_ares_ab.log) -- what it saves in ring-stage waits it spends waiting for A blocks at every
+    // row-group change -- so it is off unless BFK_ENC_ARES=1.
     static const bool ares_on = [] {
         const char* e = getenv("BFK_ENC_ARES");
-        return e ? atoi(e) != 0 : true;
+        return e ? atoi(e) != 0 : false;
     }();
     const int mode = !pair ? 0 : (ares_on && K == EG_ARES_KB * EG_BK && epi != EPI_RES_LN && N > 192) ? 2 : 1;
     CUtensorMap tmA, tmW, tmO;

@@ -243,10 +243,10 @@ def test_attention_softmax_shift_routes():
     assert abs(res["exact"][1] - res["bound"][1]) <= 2e-4, res  # the shift changes nothing but rounding
 
 
-@pytest.mark.parametrize("env", ["BFK_ENC_ATTN=ws", "BFK_ENC_ATTN=blk", "BFK_ENC_ATTN=row", "BFK_ENC_PAIR=0", "BFK_ENC_ARES=0"])
+@pytest.mark.parametrize("env", ["BFK_ENC_ATTN=ws", "BFK_ENC_ATTN=blk", "BFK_ENC_ATTN=row", "BFK_ENC_PAIR=0", "BFK_ENC_ARES=1"])
 def test_selectable_kernel_variants_in_fresh_processes(env):
     """The earlier attention kernels (warp-specialised per item, blocked, whole-row) and the GEMM without CTA pairs /
-    without the resident A tile stay selectable through the environment (read once per process): each must meet the
+    with the resident A tile stay selectable through the environment (read once per process): each must meet the
     encoder's bar against BertModel on ragged masks, a mask with holes and a chunk with masked key blocks."""
     import os
     import subprocess
